@@ -1,0 +1,186 @@
+/*
+ * hf_b200.h -- C ABI of the B200-native differentiable `heightfield` shape.
+ *
+ * This is the drop-in boundary: every entry point replaces one method (or one accel hook)
+ * that a Mitsuba 3 `Shape` plugin provides. Citations are into the reference tree
+ * (/root/reference): include/mitsuba/render/shape.h unless noted. The reference reaches the
+ * hardware through Dr.Jit tracing + Embree user geometry / OptiX custom primitives
+ * (src/render/shape.cpp:109-360); this library replaces that route for this one shape with
+ * hand-written sm_100a kernels. There is no CPU fallback: every compute entry point fails with
+ * HF_ERR_CUDA when no CUDA device is usable.
+ *
+ * Conventions
+ *   - Plain C types only. Pointers named d_* (and all pointers inside hf_rays / hf_prelim /
+ *     hf_si / hf_si_adj) are CUDA DEVICE pointers unless the entry point ends in `_host`.
+ *   - Structure-of-arrays, fp32 IEEE, indices uint32. A miss is encoded as t = +inf
+ *     (include/mitsuba/render/interaction.h:639-646).
+ *   - All launches are asynchronous on the `stream` argument (a cudaStream_t passed as void*;
+ *     NULL = the legacy default stream).
+ *   - Return value: 0 = HF_OK, otherwise an hf_status; hf_last_error() gives the message of the
+ *     last failure on the calling thread. No exception crosses the ABI.
+ *   - A context is bound to one device and is not thread-safe (one context per GPU).
+ */
+#ifndef HF_B200_H
+#define HF_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define HF_B200_ABI_VERSION 1
+
+typedef enum {
+    HF_OK = 0,
+    HF_ERR_INVALID = 1,      /* bad argument (reference: Throw(...) in the plugin constructor) */
+    HF_ERR_CUDA = 2,         /* CUDA runtime failure, or no usable device */
+    HF_ERR_NCCL = 3,         /* NCCL missing or failed */
+    HF_ERR_STATE = 4         /* call order (e.g. query before heights were set) */
+} hf_status;
+
+/* RayFlags, bit-identical to include/mitsuba/render/interaction.h:19-69 */
+enum {
+    HF_RAY_MINIMAL      = 0x1,
+    HF_RAY_UV           = 0x2,
+    HF_RAY_DPDUV        = 0x4,
+    HF_RAY_SHADINGFRAME = 0x8,
+    HF_RAY_FOLLOWSHAPE  = 0x80,
+    HF_RAY_DETACHSHAPE  = 0x100,
+    HF_RAY_ALL          = 0x2 | 0x4 | 0x8
+};
+
+typedef struct hf_ctx hf_ctx;
+
+/* Plugin constructor arguments (reference: Shape(props) src/render/shape.cpp:22-78 consumes
+ * `to_world`; pattern for gridded data: src/textures/bitmap.cpp:124-143, 259-263). */
+typedef struct {
+    uint32_t width, height;        /* texels; cells are (width-1) x (height-1); both >= 2 */
+    float    max_height;           /* z = max_height * h */
+    float    to_world[12];         /* row-major 3x4 affine */
+    float    to_object[12];        /* used iff has_to_object != 0; else fp64 inverse of to_world */
+    int32_t  has_to_object;
+    int32_t  flip_normals;
+    int32_t  device;               /* CUDA ordinal */
+} hf_desc;
+
+typedef struct {
+    const float *ox, *oy, *oz, *dx, *dy, *dz, *maxt;
+    const uint8_t *active;         /* nullable: all active */
+} hf_rays;
+
+/* PreliminaryIntersection3f (interaction.h:586-691): shape_index is the constant (uint32)-1,
+ * shape = this, instance = null -- not stored. */
+typedef struct {
+    float *t, *u, *v;
+    uint32_t *prim_index;          /* 2*(cy*(width-1)+cx) + k */
+} hf_prelim;
+
+/* SurfaceInteraction3f fields in world space; NULL pointers are skipped. */
+typedef struct {
+    float *t;
+    float *px, *py, *pz;
+    float *nx, *ny, *nz;
+    float *uvx, *uvy;
+    float *dpdu_x, *dpdu_y, *dpdu_z;
+    float *dpdv_x, *dpdv_y, *dpdv_z;
+    float *shn_x, *shn_y, *shn_z;
+    float *shs_x, *shs_y, *shs_z;
+    float *sht_x, *sht_y, *sht_z;
+    float *wi_x, *wi_y, *wi_z;
+} hf_si;
+
+/* Upstream adjoints of SurfaceInteraction3f fields; NULL = zero. sh_frame.n shares n. */
+typedef struct {
+    const float *t;
+    const float *px, *py, *pz;
+    const float *nx, *ny, *nz;
+    const float *uvx, *uvy;
+    const float *dpdu_x, *dpdu_y, *dpdu_z;
+    const float *dpdv_x, *dpdv_y, *dpdv_z;
+} hf_si_adj;
+
+/* src/python/python/ad/optimizers.py:263-302 */
+typedef struct {
+    float lr, beta1, beta2, epsilon;
+    int32_t mask_updates;
+} hf_adam;
+
+typedef struct {
+    uint64_t rays, nodes, leaves, hits;   /* accumulated by the *_counted intersect entry */
+} hf_stats;
+
+/* ---- life cycle ---------------------------------------------------------------------- */
+const char *hf_last_error(void);
+int hf_abi_version(void);
+
+/* plugin constructor / destructor (class.h:195-224, plugin.cpp:174-200) */
+int hf_create(hf_ctx **out, const hf_desc *desc);
+int hf_destroy(hf_ctx *ctx);
+
+/* ---- traverse()-exposed parameters (shape.h:533-550; linearcurve.cpp:364-382) -------- */
+/* "heights": row-major (height, width). src may be host or device memory. */
+int hf_set_heights(hf_ctx *ctx, const float *src, int src_on_device, void *stream);
+int hf_heights(hf_ctx *ctx, float **d_heights);          /* device pointer, caller may write in place */
+int hf_grad(hf_ctx *ctx, float **d_grad);                /* d(loss)/d(heights), same layout */
+int hf_zero_grad(hf_ctx *ctx, void *stream);
+int hf_set_to_world(hf_ctx *ctx, const float to_world[12], const float *to_object_or_null);
+int hf_set_max_height(hf_ctx *ctx, float max_height);
+/* parameters_changed(): rebuild the min/max pyramid, refresh the bbox (shape.h:534; the
+ * reference instead re-commits Embree / rebuilds the OptiX GAS, scene.cpp:343-367) */
+int hf_parameters_changed(hf_ctx *ctx, void *stream);
+int hf_parameters_grad_enabled(hf_ctx *ctx, int *enabled); /* shape.h:550 */
+int hf_set_grad_enabled(hf_ctx *ctx, int enabled);
+
+/* ---- queries ------------------------------------------------------------------------- */
+int hf_bbox(hf_ctx *ctx, float out_min_max[6]);          /* shape.h:253 (synchronises) */
+int hf_primitive_count(hf_ctx *ctx, uint32_t *count);    /* shape.h:432: 2*(W-1)*(H-1) */
+int hf_size(hf_ctx *ctx, uint32_t *width, uint32_t *height);
+
+/* shape.h:137-138 ray_intersect_preliminary */
+int hf_ray_intersect_preliminary(hf_ctx *ctx, const hf_rays *rays, const hf_prelim *out, size_t n, void *stream);
+/* shape.h:153 ray_test */
+int hf_ray_test(hf_ctx *ctx, const hf_rays *rays, uint8_t *d_hit, size_t n, void *stream);
+/* shape.h:179-183 compute_surface_interaction + interaction.h:476-499 finalize_surface_interaction */
+int hf_compute_surface_interaction(hf_ctx *ctx, const hf_rays *rays, const hf_prelim *pi, uint32_t ray_flags,
+                                   const hf_si *out, size_t n, void *stream);
+/* shape.h:197 ray_intersect = preliminary + surface interaction in one launch (prelim_out nullable) */
+int hf_ray_intersect(hf_ctx *ctx, const hf_rays *rays, uint32_t ray_flags, const hf_prelim *prelim_out,
+                     const hf_si *out, size_t n, void *stream);
+/* reverse-mode AD of compute_surface_interaction w.r.t. "heights" (mesh.cpp:695-789 on the hit
+ * triangle; gather adjoint = scatter_reduce(Add), ext/drjit/src/autodiff/autodiff.cpp:1309-1328) */
+int hf_backward(hf_ctx *ctx, const hf_rays *rays, const hf_prelim *pi, const hf_si_adj *adj, uint32_t ray_flags,
+                size_t n, void *stream);
+
+/* same as hf_ray_intersect_preliminary, also accumulating traversal counters (slower) */
+int hf_ray_intersect_preliminary_counted(hf_ctx *ctx, const hf_rays *rays, const hf_prelim *out, size_t n, void *stream);
+int hf_stats_get(hf_ctx *ctx, hf_stats *out, int reset);
+
+/* ---- optimiser + multi-GPU (caller side in the reference) ----------------------------- */
+int hf_adam_step(hf_ctx *ctx, const hf_adam *cfg, void *stream);   /* updates heights in place, t += 1 */
+int hf_adam_reset(hf_ctx *ctx, void *stream);
+
+/* one NCCL communicator per context; the unique id is created on rank 0 and shipped by the caller */
+int hf_comm_unique_id(uint8_t out_id[128]);
+int hf_comm_init(hf_ctx *ctx, int rank, int nranks, const uint8_t id[128]);
+int hf_comm_destroy(hf_ctx *ctx);
+int hf_allreduce_grad(hf_ctx *ctx, void *stream);                  /* ncclAllReduce(grad, fp32, sum) */
+
+/* ---- host-buffer entry points (the llvm_ad_rgb caller keeps its arrays in host memory) ---
+ * rays / outputs / adjoints are HOST pointers (pinned memory gives full PCIe bandwidth; use
+ * hf_host_alloc). The call stages chunks through device buffers, overlapping H2D, kernels and
+ * D2H on internal streams, and returns after everything has landed. */
+int hf_host_alloc(void **out, size_t bytes);
+int hf_host_free(void *p);
+int hf_ray_intersect_host(hf_ctx *ctx, const hf_rays *h_rays, uint32_t ray_flags, const hf_prelim *h_prelim_out,
+                          const hf_si *h_out, size_t n);
+/* forward + backward in one pass over host rays and host adjoints; the gradient is accumulated into
+ * the context's device grad grid and, when h_grad_out != NULL, copied out (height*width floats). */
+int hf_forward_backward_host(hf_ctx *ctx, const hf_rays *h_rays, const hf_si_adj *h_adj, uint32_t ray_flags,
+                             const hf_prelim *h_prelim_out, const hf_si *h_out, float *h_grad_out, size_t n);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* HF_B200_H */

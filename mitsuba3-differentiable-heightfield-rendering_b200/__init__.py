@@ -1,0 +1,581 @@
+"""B200-native differentiable `heightfield` shape: host-side mirror of the Mitsuba 3 Shape plugin
+interface (include/mitsuba/render/shape.h:137-197, 253, 432, 533-550) over the C ABI of
+include/hf_b200.h.
+
+Everything that computes runs in lib/libhf_b200.so (hand-written sm_100a kernels). PyTorch is used
+only for device memory, streams and torch.distributed plumbing. There is no CPU fallback: importing
+works anywhere, but constructing a Heightfield without the compiled library or without a CUDA
+device raises.
+
+Reference-facing names (citations into /root/reference):
+    load_dict({'type': 'heightfield', ...})      src/core/plugin.cpp:174-200
+    Heightfield.ray_intersect_preliminary        shape.h:137
+    Heightfield.ray_test                         shape.h:153
+    Heightfield.compute_surface_interaction      shape.h:179-183
+    Heightfield.ray_intersect                    shape.h:197
+    Heightfield.bbox / primitive_count           shape.h:253 / 432
+    traverse(shape) -> SceneParameters           src/python/python/util.py:292, 185-232
+    Adam                                         src/python/python/ad/optimizers.py:203-309
+"""
+from __future__ import annotations
+
+import ctypes as C
+import enum
+import os
+
+import numpy as np
+import torch
+
+__all__ = ["RayFlags", "Ray3f", "PreliminaryIntersection3f", "SurfaceInteraction3f", "Heightfield",
+           "load_dict", "traverse", "SceneParameters", "Adam", "lib_path", "HeightfieldError"]
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = os.path.join(_HERE, "lib", "libhf_b200.so")
+_f32p = C.POINTER(C.c_float)
+
+
+def lib_path() -> str:
+    return _LIB
+
+
+class HeightfieldError(RuntimeError):
+    pass
+
+
+class RayFlags(enum.IntFlag):
+    """Bit-identical to include/mitsuba/render/interaction.h:19-69."""
+    Empty = 0x0
+    Minimal = 0x1
+    UV = 0x2
+    dPdUV = 0x4
+    ShadingFrame = 0x8
+    dNGdUV = 0x10
+    dNSdUV = 0x20
+    BoundaryTest = 0x40
+    FollowShape = 0x80
+    DetachShape = 0x100
+    All = 0x2 | 0x4 | 0x8
+    AllNonDifferentiable = 0x2 | 0x4 | 0x8 | 0x100
+
+
+# ---- ctypes mirror of include/hf_b200.h ------------------------------------------------------
+class _Desc(C.Structure):
+    _fields_ = [("width", C.c_uint32), ("height", C.c_uint32), ("max_height", C.c_float),
+                ("to_world", C.c_float * 12), ("to_object", C.c_float * 12), ("has_to_object", C.c_int32),
+                ("flip_normals", C.c_int32), ("device", C.c_int32)]
+
+
+class _Rays(C.Structure):
+    _fields_ = [(k, C.c_void_p) for k in ("ox", "oy", "oz", "dx", "dy", "dz", "maxt", "active")]
+
+
+class _Prelim(C.Structure):
+    _fields_ = [(k, C.c_void_p) for k in ("t", "u", "v", "prim_index")]
+
+
+SI_FIELDS = ("t", "px", "py", "pz", "nx", "ny", "nz", "uvx", "uvy",
+             "dpdu_x", "dpdu_y", "dpdu_z", "dpdv_x", "dpdv_y", "dpdv_z",
+             "shn_x", "shn_y", "shn_z", "shs_x", "shs_y", "shs_z", "sht_x", "sht_y", "sht_z",
+             "wi_x", "wi_y", "wi_z")
+ADJ_FIELDS = SI_FIELDS[:15]
+
+
+class _SI(C.Structure):
+    _fields_ = [(k, C.c_void_p) for k in SI_FIELDS]
+
+
+class _Adj(C.Structure):
+    _fields_ = [(k, C.c_void_p) for k in ADJ_FIELDS]
+
+
+class _Adam(C.Structure):
+    _fields_ = [("lr", C.c_float), ("beta1", C.c_float), ("beta2", C.c_float), ("epsilon", C.c_float),
+                ("mask_updates", C.c_int32)]
+
+
+class _Stats(C.Structure):
+    _fields_ = [(k, C.c_uint64) for k in ("rays", "nodes", "leaves", "hits")]
+
+
+_lib = None
+
+
+def _load():
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(_LIB):
+        raise HeightfieldError(
+            f"compiled CUDA library missing: {_LIB}. Build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+            f"(nvcc, sm_100a). There is no CPU fallback.")
+    L = C.CDLL(_LIB)
+    L.hf_last_error.restype = C.c_char_p
+    vp, sz, u32 = C.c_void_p, C.c_size_t, C.c_uint32
+    sig = {
+        "hf_abi_version": [],
+        "hf_create": [C.POINTER(vp), C.POINTER(_Desc)],
+        "hf_destroy": [vp],
+        "hf_set_heights": [vp, vp, C.c_int, vp],
+        "hf_heights": [vp, C.POINTER(vp)],
+        "hf_grad": [vp, C.POINTER(vp)],
+        "hf_zero_grad": [vp, vp],
+        "hf_set_to_world": [vp, _f32p, _f32p],
+        "hf_set_max_height": [vp, C.c_float],
+        "hf_parameters_changed": [vp, vp],
+        "hf_parameters_grad_enabled": [vp, C.POINTER(C.c_int)],
+        "hf_set_grad_enabled": [vp, C.c_int],
+        "hf_bbox": [vp, _f32p],
+        "hf_primitive_count": [vp, C.POINTER(u32)],
+        "hf_size": [vp, C.POINTER(u32), C.POINTER(u32)],
+        "hf_ray_intersect_preliminary": [vp, C.POINTER(_Rays), C.POINTER(_Prelim), sz, vp],
+        "hf_ray_intersect_preliminary_counted": [vp, C.POINTER(_Rays), C.POINTER(_Prelim), sz, vp],
+        "hf_stats_get": [vp, C.POINTER(_Stats), C.c_int],
+        "hf_ray_test": [vp, C.POINTER(_Rays), vp, sz, vp],
+        "hf_compute_surface_interaction": [vp, C.POINTER(_Rays), C.POINTER(_Prelim), u32, C.POINTER(_SI), sz, vp],
+        "hf_ray_intersect": [vp, C.POINTER(_Rays), u32, C.POINTER(_Prelim), C.POINTER(_SI), sz, vp],
+        "hf_backward": [vp, C.POINTER(_Rays), C.POINTER(_Prelim), C.POINTER(_Adj), u32, sz, vp],
+        "hf_adam_step": [vp, C.POINTER(_Adam), vp],
+        "hf_adam_reset": [vp, vp],
+        "hf_comm_unique_id": [C.POINTER(C.c_uint8)],
+        "hf_comm_init": [vp, C.c_int, C.c_int, C.POINTER(C.c_uint8)],
+        "hf_comm_destroy": [vp],
+        "hf_allreduce_grad": [vp, vp],
+        "hf_host_alloc": [C.POINTER(vp), sz],
+        "hf_host_free": [vp],
+        "hf_ray_intersect_host": [vp, C.POINTER(_Rays), u32, C.POINTER(_Prelim), C.POINTER(_SI), sz],
+        "hf_forward_backward_host": [vp, C.POINTER(_Rays), C.POINTER(_Adj), u32, C.POINTER(_Prelim), C.POINTER(_SI), vp, sz],
+    }
+    for name, args in sig.items():
+        fn = getattr(L, name)
+        fn.argtypes = args
+        fn.restype = C.c_int
+    _lib = L
+    return L
+
+
+def _check(rc):
+    if rc != 0:
+        raise HeightfieldError(_load().hf_last_error().decode("utf-8", "replace"))
+
+
+def _stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _ptr(t):
+    return C.c_void_p(t.data_ptr()) if t is not None else None
+
+
+class _DevView:
+    """Zero-copy torch view of a device buffer owned by the C library."""
+
+    def __init__(self, ptr, shape, owner):
+        self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": "<f4", "data": (int(ptr), False),
+                                         "version": 3, "strides": None}
+        self._owner = owner
+
+
+# ---- records (interaction.h) --------------------------------------------------------------
+def _soa(x, rows, name, device):
+    t = torch.as_tensor(x, dtype=torch.float32, device=device)
+    if t.dim() == 2 and t.shape[0] != rows and t.shape[1] == rows:
+        t = t.t()
+    if t.dim() != 2 or t.shape[0] != rows:
+        raise HeightfieldError(f"{name}: expected shape ({rows}, N) or (N, {rows})")
+    return t.contiguous()
+
+
+class Ray3f:
+    """SoA ray batch on the device: o, d are (3, N) tensors, maxt is (N,)."""
+
+    def __init__(self, o, d, maxt=None, device="cuda"):
+        self.o = _soa(o, 3, "o", device)
+        self.d = _soa(d, 3, "d", device)
+        n = self.o.shape[1]
+        if maxt is None:
+            self.maxt = torch.full((n,), float("inf"), dtype=torch.float32, device=self.o.device)
+        else:
+            self.maxt = torch.as_tensor(maxt, dtype=torch.float32, device=self.o.device).expand(n).contiguous()
+
+    def __len__(self):
+        return self.o.shape[1]
+
+    def _c(self, active=None):
+        return _Rays(_ptr(self.o[0]), _ptr(self.o[1]), _ptr(self.o[2]), _ptr(self.d[0]), _ptr(self.d[1]), _ptr(self.d[2]),
+                     _ptr(self.maxt), _ptr(active))
+
+
+class PreliminaryIntersection3f:
+    """interaction.h:586-691; invalid <=> t == +inf (639-646)."""
+
+    def __init__(self, n, device, shape=None):
+        self.t = torch.empty(n, dtype=torch.float32, device=device)
+        self.prim_uv = torch.empty((2, n), dtype=torch.float32, device=device)
+        self.prim_index = torch.empty(n, dtype=torch.int32, device=device)   # uint32 bit pattern
+        self.shape_index = 0xFFFFFFFF     # rectangle.cpp:222-223
+        self.shape = shape
+
+    def is_valid(self):
+        return self.t != float("inf")
+
+    def _c(self):
+        return _Prelim(_ptr(self.t), _ptr(self.prim_uv[0]), _ptr(self.prim_uv[1]), _ptr(self.prim_index))
+
+    def compute_surface_interaction(self, ray, ray_flags=RayFlags.All, active=None):
+        """interaction.h:658-684"""
+        return self.shape.compute_surface_interaction(ray, self, ray_flags, active=active)
+
+
+class SurfaceInteraction3f:
+    def __init__(self, n, device, shape=None):
+        z = lambda r: torch.empty((r, n), dtype=torch.float32, device=device)
+        self.t = torch.empty(n, dtype=torch.float32, device=device)
+        self.p, self.n, self.uv = z(3), z(3), z(2)
+        self.dp_du, self.dp_dv = z(3), z(3)
+        self.sh_n, self.sh_s, self.sh_t, self.wi = z(3), z(3), z(3), z(3)
+        self.prim_index = None
+        self.shape = shape
+
+    def is_valid(self):
+        return self.t != float("inf")
+
+    def _c(self):
+        f = {"t": self.t}
+        for name, t in (("p", self.p), ("n", self.n), ("dpdu_", self.dp_du), ("dpdv_", self.dp_dv), ("shn_", self.sh_n),
+                        ("shs_", self.sh_s), ("sht_", self.sh_t), ("wi_", self.wi)):
+            for k, ax in enumerate("xyz"):
+                f[name + ax] = t[k]
+        f["uvx"], f["uvy"] = self.uv[0], self.uv[1]
+        return _SI(**{k: _ptr(f[k]) for k in SI_FIELDS})
+
+
+def _adj_struct(adj, n, device):
+    """adj: dict with any of t (N,), p (3,N), n (3,N), uv (2,N), dp_du (3,N), dp_dv (3,N)."""
+    keep, f = [], {}
+    def put(names, val, rows):
+        t = torch.as_tensor(val, dtype=torch.float32, device=device)
+        t = t.reshape(rows, n).contiguous() if rows > 1 else t.reshape(n).contiguous()
+        keep.append(t)
+        if rows == 1:
+            f[names[0]] = t
+        else:
+            for k, nm in enumerate(names):
+                f[nm] = t[k]
+    for key, names in (("t", ("t",)), ("p", ("px", "py", "pz")), ("n", ("nx", "ny", "nz")), ("uv", ("uvx", "uvy")),
+                       ("dp_du", ("dpdu_x", "dpdu_y", "dpdu_z")), ("dp_dv", ("dpdv_x", "dpdv_y", "dpdv_z"))):
+        if key in adj and adj[key] is not None:
+            put(names, adj[key], len(names))
+    unknown = set(adj) - {"t", "p", "n", "uv", "dp_du", "dp_dv"}
+    if unknown:
+        raise HeightfieldError(f"unknown adjoint fields: {sorted(unknown)}")
+    return _Adj(**{k: _ptr(f.get(k)) for k in ADJ_FIELDS}), keep
+
+
+# ---- the shape ------------------------------------------------------------------------------
+class Heightfield:
+    """`heightfield` Shape plugin (definition: DESIGN.md).
+
+    Properties (constructor dict, cf. Shape(props) src/render/shape.cpp:22-78 and
+    src/textures/bitmap.cpp:124-143): `heights` ((H, W) array / tensor) XOR `filename` (.npy),
+    `max_height` (default 1), `to_world` (3x4 or 4x4, default identity), `flip_normals` (default False).
+    """
+
+    def __init__(self, props: dict, device=None):
+        props = dict(props)
+        if props.pop("type", "heightfield") != "heightfield":
+            raise HeightfieldError("this plugin only implements type='heightfield'")
+        if ("heights" in props) == ("filename" in props):
+            raise HeightfieldError("heightfield: specify exactly one of `heights` or `filename`")
+        if not torch.cuda.is_available():
+            raise HeightfieldError("no CUDA device: the heightfield plugin has no CPU fallback")
+        L = _load()
+        dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        self.device = dev
+        h = props.pop("heights", None)
+        if h is None:
+            h = np.load(props.pop("filename"))
+        h = torch.as_tensor(h, dtype=torch.float32)
+        if h.dim() == 3 and h.shape[2] == 1:      # (H, W, 1) tensors as in bitmap.cpp:259-263
+            h = h[:, :, 0]
+        if h.dim() != 2:
+            raise HeightfieldError("heightfield: `heights` must have shape (H, W)")
+        self.H, self.W = int(h.shape[0]), int(h.shape[1])
+        tw = props.pop("to_world", None)
+        tw = np.eye(4, dtype=np.float32) if tw is None else np.asarray(
+            tw.cpu() if isinstance(tw, torch.Tensor) else tw, dtype=np.float32)
+        tw = tw.reshape(-1)[:12].reshape(3, 4)
+        self._to_world = tw.copy()
+        self._max_height = float(props.pop("max_height", 1.0))
+        self.flip_normals = bool(props.pop("flip_normals", False))
+        to_object = props.pop("to_object", None)
+        if props:
+            raise HeightfieldError(f"heightfield: unreferenced properties {sorted(props)}")   # Properties::mark_queried semantics
+
+        d = _Desc()
+        d.width, d.height, d.max_height = self.W, self.H, self._max_height
+        d.to_world[:] = tw.reshape(-1).tolist()
+        if to_object is not None:
+            d.to_object[:] = np.asarray(to_object, dtype=np.float32).reshape(-1)[:12].tolist()
+            d.has_to_object = 1
+        d.flip_normals, d.device = int(self.flip_normals), dev.index or 0
+        self._ctx = C.c_void_p()
+        _check(L.hf_create(C.byref(self._ctx), C.byref(d)))
+        hp, gp = C.c_void_p(), C.c_void_p()
+        _check(L.hf_heights(self._ctx, C.byref(hp)))
+        _check(L.hf_grad(self._ctx, C.byref(gp)))
+        with torch.cuda.device(dev):
+            self.heights = torch.as_tensor(_DevView(hp.value, (self.H, self.W), self), device=dev)
+            self.grad = torch.as_tensor(_DevView(gp.value, (self.H, self.W), self), device=dev)
+            self.heights.copy_(h.to(dev))
+        self.parameters_changed()
+
+    def __del__(self):
+        try:
+            if getattr(self, "_ctx", None) and _lib is not None:
+                _lib.hf_destroy(self._ctx)
+                self._ctx = None
+        except Exception:
+            pass
+
+    # -- traverse()/parameters_changed (shape.h:533-550) ------------------------------------
+    @property
+    def max_height(self):
+        return self._max_height
+
+    @max_height.setter
+    def max_height(self, v):
+        self._max_height = float(v)
+        _check(_load().hf_set_max_height(self._ctx, self._max_height))
+
+    @property
+    def to_world(self):
+        return self._to_world
+
+    @to_world.setter
+    def to_world(self, m):
+        m = np.asarray(m, dtype=np.float32).reshape(-1)[:12].reshape(3, 4).copy()
+        arr = (C.c_float * 12)(*m.reshape(-1).tolist())
+        _check(_load().hf_set_to_world(self._ctx, arr, None))
+        self._to_world = m
+
+    def traverse(self, callback=None):
+        params = {"heights": self.heights, "max_height": self._max_height, "to_world": self._to_world}
+        if callback is not None:
+            for k, v in params.items():
+                callback(k, v)
+        return params
+
+    def parameters_changed(self, keys=()):
+        """Rebuild the acceleration data (min/max pyramid) after a parameter update."""
+        with torch.cuda.device(self.device):
+            _check(_load().hf_parameters_changed(self._ctx, _stream()))
+
+    def parameters_grad_enabled(self):
+        e = C.c_int()
+        _check(_load().hf_parameters_grad_enabled(self._ctx, C.byref(e)))
+        return bool(e.value)
+
+    def set_grad_enabled(self, enabled=True):
+        _check(_load().hf_set_grad_enabled(self._ctx, int(enabled)))
+
+    def zero_grad(self):
+        with torch.cuda.device(self.device):
+            _check(_load().hf_zero_grad(self._ctx, _stream()))
+
+    # -- queries ----------------------------------------------------------------------------
+    def bbox(self):
+        out = (C.c_float * 6)()
+        _check(_load().hf_bbox(self._ctx, out))
+        return np.array(out[:], dtype=np.float32)
+
+    def primitive_count(self):
+        n = C.c_uint32()
+        _check(_load().hf_primitive_count(self._ctx, C.byref(n)))
+        return n.value
+
+    def _mask(self, active, n):
+        if active is None:
+            return None
+        a = torch.as_tensor(active, device=self.device).to(torch.uint8).contiguous()
+        if a.numel() != n:
+            raise HeightfieldError("active mask has the wrong length")
+        return a
+
+    def ray_intersect_preliminary(self, ray: Ray3f, active=None, counted=False):
+        n = len(ray)
+        pi = PreliminaryIntersection3f(n, self.device, self)
+        a = self._mask(active, n)
+        r, p = ray._c(a), pi._c()
+        fn = _load().hf_ray_intersect_preliminary_counted if counted else _load().hf_ray_intersect_preliminary
+        with torch.cuda.device(self.device):
+            _check(fn(self._ctx, C.byref(r), C.byref(p), n, _stream()))
+        return pi
+
+    def ray_test(self, ray: Ray3f, active=None):
+        n = len(ray)
+        hit = torch.empty(n, dtype=torch.uint8, device=self.device)
+        a = self._mask(active, n)
+        r = ray._c(a)
+        with torch.cuda.device(self.device):
+            _check(_load().hf_ray_test(self._ctx, C.byref(r), _ptr(hit), n, _stream()))
+        return hit.bool()
+
+    def compute_surface_interaction(self, ray: Ray3f, pi: PreliminaryIntersection3f, ray_flags=RayFlags.All,
+                                    recursion_depth=0, active=None):
+        n = len(ray)
+        si = SurfaceInteraction3f(n, self.device, self)
+        a = self._mask(active, n)
+        r, p, s = ray._c(a), pi._c(), si._c()
+        with torch.cuda.device(self.device):
+            _check(_load().hf_compute_surface_interaction(self._ctx, C.byref(r), C.byref(p), int(ray_flags), C.byref(s), n, _stream()))
+        si.prim_index = pi.prim_index
+        return si
+
+    def ray_intersect(self, ray: Ray3f, ray_flags=RayFlags.All, active=None, return_prelim=False):
+        n = len(ray)
+        si = SurfaceInteraction3f(n, self.device, self)
+        pi = PreliminaryIntersection3f(n, self.device, self)
+        a = self._mask(active, n)
+        r, p, s = ray._c(a), pi._c(), si._c()
+        with torch.cuda.device(self.device):
+            _check(_load().hf_ray_intersect(self._ctx, C.byref(r), int(ray_flags), C.byref(p), C.byref(s), n, _stream()))
+        si.prim_index = pi.prim_index
+        return (si, pi) if return_prelim else si
+
+    def backward(self, ray: Ray3f, pi: PreliminaryIntersection3f, adjoints: dict, ray_flags=RayFlags.All, active=None):
+        """Accumulate d(loss)/d(heights) into self.grad given upstream adjoints of si fields
+        (reverse mode of compute_surface_interaction, src/render/mesh.cpp:695-789)."""
+        n = len(ray)
+        a = self._mask(active, n)
+        adj, keep = _adj_struct(adjoints, n, self.device)
+        r, p = ray._c(a), pi._c()
+        with torch.cuda.device(self.device):
+            _check(_load().hf_backward(self._ctx, C.byref(r), C.byref(p), C.byref(adj), int(ray_flags), n, _stream()))
+        del keep
+
+    def stats(self, reset=True):
+        s = _Stats()
+        _check(_load().hf_stats_get(self._ctx, C.byref(s), int(reset)))
+        return {"rays": s.rays, "nodes": s.nodes, "leaves": s.leaves, "hits": s.hits}
+
+    # -- optimiser / multi-GPU --------------------------------------------------------------
+    def adam_step(self, lr, beta_1=0.9, beta_2=0.999, epsilon=1e-8, mask_updates=False):
+        cfg = _Adam(lr, beta_1, beta_2, epsilon, int(mask_updates))
+        with torch.cuda.device(self.device):
+            _check(_load().hf_adam_step(self._ctx, C.byref(cfg), _stream()))
+
+    def adam_reset(self):
+        with torch.cuda.device(self.device):
+            _check(_load().hf_adam_reset(self._ctx, _stream()))
+
+    def comm_init(self, rank, world_size, unique_id: bytes):
+        buf = (C.c_uint8 * 128).from_buffer_copy(unique_id)
+        with torch.cuda.device(self.device):
+            _check(_load().hf_comm_init(self._ctx, rank, world_size, buf))
+
+    def allreduce_grad(self):
+        with torch.cuda.device(self.device):
+            _check(_load().hf_allreduce_grad(self._ctx, _stream()))
+
+    # -- host-buffer path (llvm_ad_rgb keeps its arrays in host memory) ------------------------
+    def forward_backward_host(self, h_rays: dict, h_adj: dict, h_si: dict, h_grad, n, ray_flags=RayFlags.All,
+                              h_prelim: dict | None = None):
+        """All arguments are dicts of 1-D HOST torch tensors (pinned for full PCIe speed), keyed by the C field
+        names of hf_rays / hf_si_adj / hf_si / hf_prelim. h_grad: (H, W) host tensor or None."""
+        r = _Rays(**{k: _ptr(h_rays.get(k)) for k in ("ox", "oy", "oz", "dx", "dy", "dz", "maxt", "active")})
+        a = _Adj(**{k: _ptr(h_adj.get(k)) for k in ADJ_FIELDS})
+        s = _SI(**{k: _ptr(h_si.get(k)) for k in SI_FIELDS})
+        p = _Prelim(**{k: _ptr(h_prelim.get(k)) for k in ("t", "u", "v", "prim_index")}) if h_prelim else None
+        with torch.cuda.device(self.device):
+            _check(_load().hf_forward_backward_host(self._ctx, C.byref(r), C.byref(a), int(ray_flags),
+                                                    C.byref(p) if p is not None else None, C.byref(s), _ptr(h_grad), n))
+
+    def ray_intersect_host(self, h_rays: dict, h_si: dict, n, ray_flags=RayFlags.All, h_prelim: dict | None = None):
+        r = _Rays(**{k: _ptr(h_rays.get(k)) for k in ("ox", "oy", "oz", "dx", "dy", "dz", "maxt", "active")})
+        s = _SI(**{k: _ptr(h_si.get(k)) for k in SI_FIELDS})
+        p = _Prelim(**{k: _ptr(h_prelim.get(k)) for k in ("t", "u", "v", "prim_index")}) if h_prelim else None
+        with torch.cuda.device(self.device):
+            _check(_load().hf_ray_intersect_host(self._ctx, C.byref(r), int(ray_flags),
+                                                 C.byref(p) if p is not None else None, C.byref(s), n))
+
+    def __repr__(self):
+        return (f"Heightfield[\n  size = {self.W}x{self.H},\n  max_height = {self._max_height},\n"
+                f"  primitive_count = {self.primitive_count()},\n  flip_normals = {self.flip_normals}\n]")
+
+
+def comm_unique_id() -> bytes:
+    buf = (C.c_uint8 * 128)()
+    _check(_load().hf_comm_unique_id(buf))
+    return bytes(buf)
+
+
+def load_dict(d: dict, device=None):
+    """mi.load_dict for the one plugin this package implements (src/core/plugin.cpp:174-200)."""
+    if d.get("type") != "heightfield":
+        raise HeightfieldError(f"plugin '{d.get('type')}' is not provided by this package (only 'heightfield')")
+    return Heightfield(d, device=device)
+
+
+class SceneParameters(dict):
+    """src/python/python/util.py:185-232: dictionary of exposed parameters + update()."""
+
+    def __init__(self, shape: Heightfield, prefix=""):
+        super().__init__()
+        self._shape, self._prefix, self._dirty = shape, prefix, set()
+        for k, v in shape.traverse().items():
+            dict.__setitem__(self, prefix + k, v)
+
+    def __setitem__(self, key, value):
+        if key not in self:
+            raise KeyError(key)
+        base = key[len(self._prefix):]
+        if base == "heights":
+            value = torch.as_tensor(value, dtype=torch.float32, device=self._shape.device)
+            if tuple(value.shape) != (self._shape.H, self._shape.W):     # cf. bitmap.cpp:272-287
+                raise HeightfieldError("heights: size mismatch on update")
+            self._shape.heights.copy_(value)
+            value = self._shape.heights
+        elif base == "max_height":
+            self._shape.max_height = value
+        elif base == "to_world":
+            self._shape.to_world = value
+            value = self._shape.to_world
+        dict.__setitem__(self, key, value)
+        self._dirty.add(base)
+
+    def set_dirty(self, key):
+        self._dirty.add(key[len(self._prefix):])
+
+    def update(self, values=None):
+        if values:
+            for k, v in dict(values).items():
+                self[k] = v
+        keys = sorted(self._dirty)
+        self._dirty.clear()
+        if keys:
+            self._shape.parameters_changed(keys)
+        return keys
+
+
+def traverse(shape: Heightfield, prefix=""):
+    return SceneParameters(shape, prefix)
+
+
+class Adam:
+    """src/python/python/ad/optimizers.py:203-309 for the heightfield's `heights` parameter. The update runs
+    in one fused kernel on the library's own buffers (state m, v live next to the heights)."""
+
+    def __init__(self, lr, beta_1=0.9, beta_2=0.999, epsilon=1e-8, mask_updates=False, params: SceneParameters = None):
+        assert 0 <= beta_1 < 1 and 0 <= beta_2 < 1 and lr > 0 and epsilon > 0
+        self.lr, self.beta_1, self.beta_2, self.epsilon, self.mask_updates = lr, beta_1, beta_2, epsilon, mask_updates
+        self.params = params
+        if params is not None:
+            params._shape.adam_reset()
+
+    def step(self):
+        s = self.params._shape
+        s.adam_step(self.lr, self.beta_1, self.beta_2, self.epsilon, self.mask_updates)
+        self.params.set_dirty(self.params._prefix + "heights")
+
+    def reset(self, key=None):
+        self.params._shape.adam_reset()

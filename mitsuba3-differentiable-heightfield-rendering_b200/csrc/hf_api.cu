@@ -1,0 +1,633 @@
+// hf_api.cu -- context object and the C ABI of include/hf_b200.h (host side, C++).
+//
+// One hf_ctx == one `heightfield` shape instance on one GPU. It owns the traverse()-exposed
+// parameter ("heights"), its gradient, the Adam state and the shape's acceleration data
+// (min/max pyramid), i.e. what the reference keeps in Dr.Jit arrays plus Embree/OptiX handles
+// (src/render/shape.cpp:109-360). No CPU fallback exists: without a CUDA device every entry
+// point that computes returns HF_ERR_CUDA.
+#include <dlfcn.h>
+#include <math.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <algorithm>
+#include <new>
+#include <vector>
+
+#include "hf_kernels.h"
+
+// ------------------------------------------------------------------------------------------
+// errors
+// ------------------------------------------------------------------------------------------
+static thread_local char g_err[512] = "";
+
+static int fail(int code, const char *fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+    return code;
+}
+
+#define CU(call)                                                                                  \
+    do {                                                                                          \
+        cudaError_t e_ = (call);                                                                  \
+        if (e_ != cudaSuccess)                                                                    \
+            return fail(HF_ERR_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+    } while (0)
+
+#define CHECK_CTX(ctx) do { if (!(ctx)) return fail(HF_ERR_INVALID, "null context"); } while (0)
+
+extern "C" const char *hf_last_error(void) { return g_err; }
+extern "C" int hf_abi_version(void) { return HF_B200_ABI_VERSION; }
+
+// ------------------------------------------------------------------------------------------
+// NCCL through dlopen: the library has no link-time dependency on NCCL and loads without it
+// ------------------------------------------------------------------------------------------
+typedef struct { char internal[128]; } hf_nccl_uid;
+typedef void *hf_nccl_comm;
+struct NcclApi {
+    void *handle = nullptr;
+    int (*GetUniqueId)(hf_nccl_uid *) = nullptr;
+    int (*CommInitRank)(hf_nccl_comm *, int, hf_nccl_uid, int) = nullptr;
+    int (*CommDestroy)(hf_nccl_comm) = nullptr;
+    int (*AllReduce)(const void *, void *, size_t, int, int, hf_nccl_comm, cudaStream_t) = nullptr;
+    const char *(*GetErrorString)(int) = nullptr;
+};
+static NcclApi g_nccl;
+
+static int nccl_load() {
+    if (g_nccl.handle) return HF_OK;
+    const char *names[] = { "libnccl.so.2", "libnccl.so" };
+    void *h = nullptr;
+    for (const char *nm : names) { h = dlopen(nm, RTLD_NOW | RTLD_GLOBAL); if (h) break; }
+    if (!h) return fail(HF_ERR_NCCL, "cannot dlopen libnccl.so.2: %s", dlerror());
+    NcclApi a;
+    a.handle = h;
+    a.GetUniqueId = (int (*)(hf_nccl_uid *)) dlsym(h, "ncclGetUniqueId");
+    a.CommInitRank = (int (*)(hf_nccl_comm *, int, hf_nccl_uid, int)) dlsym(h, "ncclCommInitRank");
+    a.CommDestroy = (int (*)(hf_nccl_comm)) dlsym(h, "ncclCommDestroy");
+    a.AllReduce = (int (*)(const void *, void *, size_t, int, int, hf_nccl_comm, cudaStream_t)) dlsym(h, "ncclAllReduce");
+    a.GetErrorString = (const char *(*) (int) ) dlsym(h, "ncclGetErrorString");
+    if (!a.GetUniqueId || !a.CommInitRank || !a.CommDestroy || !a.AllReduce || !a.GetErrorString)
+        return fail(HF_ERR_NCCL, "libnccl is missing a required symbol");
+    g_nccl = a;
+    return HF_OK;
+}
+#define NC(call)                                                                                  \
+    do {                                                                                          \
+        int r_ = (call);                                                                          \
+        if (r_ != 0) return fail(HF_ERR_NCCL, "%s failed: %s", #call, g_nccl.GetErrorString(r_)); \
+    } while (0)
+
+// ------------------------------------------------------------------------------------------
+// context
+// ------------------------------------------------------------------------------------------
+#define HF_TOP_NODE_CAP 1366          // (32^2 + 16^2 + ... + 1) rounded up to even: 10.9 KB of shared memory
+#define HF_HOST_CHUNK (size_t(1) << 21)
+#define HF_HOST_SLOTS 2
+#define HF_SLAB_FLOATS 53             // rays 7 + prelim 4 + si 26 + adj 15 + active mask
+
+struct HostSlot {
+    cudaStream_t stream = nullptr;
+    float *slab = nullptr;            // HF_HOST_CHUNK * HF_SLAB_FLOATS floats
+};
+
+struct hf_ctx {
+    int device = 0;
+    int num_sms = 0;
+    uint32_t W = 0, H = 0;
+    HfParams P;
+    HfLaunchInfo li;
+    size_t pyr_nodes = 0;
+    float *d_heights = nullptr, *d_grad = nullptr, *d_m = nullptr, *d_v = nullptr;
+    float2 *d_pyr = nullptr;
+    unsigned long long *d_counters = nullptr;
+    bool have_heights = false, accel_valid = false;
+    int grad_enabled = 1;
+    int adam_t = 0;
+    hf_nccl_comm comm = nullptr;
+    int nranks = 1;
+    HostSlot slots[HF_HOST_SLOTS];
+    bool slots_ready = false;
+};
+
+static void invert_affine(const float m[12], float out[12]) {
+    // fp64 inverse of the 3x4 affine, rounded to fp32 (definition of to_object)
+    double a[3][3], t[3];
+    for (int r = 0; r < 3; ++r) { for (int c = 0; c < 3; ++c) a[r][c] = m[r * 4 + c]; t[r] = m[r * 4 + 3]; }
+    double det = a[0][0] * (a[1][1] * a[2][2] - a[1][2] * a[2][1]) - a[0][1] * (a[1][0] * a[2][2] - a[1][2] * a[2][0]) +
+                 a[0][2] * (a[1][0] * a[2][1] - a[1][1] * a[2][0]);
+    double id = 1.0 / det, inv[3][3];
+    inv[0][0] = (a[1][1] * a[2][2] - a[1][2] * a[2][1]) * id;
+    inv[0][1] = (a[0][2] * a[2][1] - a[0][1] * a[2][2]) * id;
+    inv[0][2] = (a[0][1] * a[1][2] - a[0][2] * a[1][1]) * id;
+    inv[1][0] = (a[1][2] * a[2][0] - a[1][0] * a[2][2]) * id;
+    inv[1][1] = (a[0][0] * a[2][2] - a[0][2] * a[2][0]) * id;
+    inv[1][2] = (a[0][2] * a[1][0] - a[0][0] * a[1][2]) * id;
+    inv[2][0] = (a[1][0] * a[2][1] - a[1][1] * a[2][0]) * id;
+    inv[2][1] = (a[0][1] * a[2][0] - a[0][0] * a[2][1]) * id;
+    inv[2][2] = (a[0][0] * a[1][1] - a[0][1] * a[1][0]) * id;
+    for (int r = 0; r < 3; ++r) {
+        for (int c = 0; c < 3; ++c) out[r * 4 + c] = (float) inv[r][c];
+        out[r * 4 + 3] = (float) -(inv[r][0] * t[0] + inv[r][1] * t[1] + inv[r][2] * t[2]);
+    }
+}
+
+static int set_transform(hf_ctx *c, const float to_world[12], const float *to_object) {
+    for (int i = 0; i < 12; ++i) if (!isfinite(to_world[i])) return fail(HF_ERR_INVALID, "to_world has a non-finite entry");
+    memcpy(c->P.to_world, to_world, sizeof(float) * 12);
+    if (to_object) memcpy(c->P.to_object, to_object, sizeof(float) * 12);
+    else invert_affine(to_world, c->P.to_object);
+    for (int i = 0; i < 12; ++i) if (!isfinite(c->P.to_object[i])) return fail(HF_ERR_INVALID, "to_world is singular");
+    return HF_OK;
+}
+
+static void layout_pyramid(hf_ctx *c) {
+    HfParams &P = c->P;
+    int L = 1;
+    while (((P.NX + (1 << L) - 1) >> L) > 1 || ((P.NY + (1 << L) - 1) >> L) > 1) L++;
+    P.Ltop = L;
+    size_t off = 0;
+    std::vector<size_t> cnt(HF_MAX_LEVELS, 0);
+    for (int l = 0; l < HF_MAX_LEVELS; ++l) { P.lvl_off[l] = 0; P.lvl_w[l] = 0; }
+    for (int l = 1; l <= L; ++l) {
+        int w = (P.NX + (1 << l) - 1) >> l, h = (P.NY + (1 << l) - 1) >> l;
+        P.lvl_off[l] = (int) off; P.lvl_w[l] = w;
+        cnt[l] = ((size_t) w * h + 1) & ~size_t(1);     // even node count: every level starts 16-byte aligned
+        off += cnt[l];
+    }
+    c->pyr_nodes = off;
+    // levels >= Ls are staged in shared memory by the intersection kernel
+    int Ls = L;
+    size_t top = cnt[L];
+    while (Ls > 1 && top + cnt[Ls - 1] <= HF_TOP_NODE_CAP) { Ls--; top += cnt[Ls]; }
+    c->li.top_level_start = Ls;
+    c->li.top_nodes = (int) top;
+    c->li.top_off = P.lvl_off[Ls];
+    c->li.num_sms = c->num_sms;
+}
+
+extern "C" int hf_create(hf_ctx **out, const hf_desc *desc) {
+    if (!out || !desc) return fail(HF_ERR_INVALID, "null argument");
+    *out = nullptr;
+    if (desc->width < 2 || desc->height < 2) return fail(HF_ERR_INVALID, "heightfield needs at least 2x2 texels (got %ux%u)", desc->width, desc->height);
+    if (desc->width > (1u << 23) || desc->height > (1u << 23)) return fail(HF_ERR_INVALID, "heightfield side exceeds 2^23 texels");
+    if ((uint64_t) (desc->width - 1) * (desc->height - 1) > 0x7fffffffull) return fail(HF_ERR_INVALID, "prim_index would overflow uint32");
+    if (!isfinite(desc->max_height)) return fail(HF_ERR_INVALID, "max_height is not finite");
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0) return fail(HF_ERR_CUDA, "no CUDA device available (%s); this library has no CPU path", e != cudaSuccess ? cudaGetErrorString(e) : "count = 0");
+    if (desc->device < 0 || desc->device >= ndev) return fail(HF_ERR_INVALID, "device ordinal %d out of range", desc->device);
+    CU(cudaSetDevice(desc->device));
+
+    hf_ctx *c = new (std::nothrow) hf_ctx();
+    if (!c) return fail(HF_ERR_INVALID, "out of host memory");
+    c->device = desc->device;
+    cudaDeviceProp prop;
+    e = cudaGetDeviceProperties(&prop, desc->device);
+    if (e != cudaSuccess) { delete c; return fail(HF_ERR_CUDA, "cudaGetDeviceProperties: %s", cudaGetErrorString(e)); }
+    c->num_sms = prop.multiProcessorCount;
+    c->W = desc->width; c->H = desc->height;
+
+    HfParams &P = c->P;
+    memset(&P, 0, sizeof(P));
+    P.W = (int) desc->width; P.H = (int) desc->height; P.NX = P.W - 1; P.NY = P.H - 1;
+    P.flip_normals = desc->flip_normals ? 1 : 0;
+    P.mh = desc->max_height;
+    P.rw = 1.0f / (float) P.NX; P.rh = 1.0f / (float) P.NY;
+    P.x0 = (float) (-(P.W - 1)) * P.rw; P.y0 = (float) (-(P.H - 1)) * P.rh;
+    P.sgx = 0.5f * (float) P.NX; P.sgy = 0.5f * (float) P.NY;
+    int rc = set_transform(c, desc->to_world, desc->has_to_object ? desc->to_object : nullptr);
+    if (rc) { delete c; return rc; }
+    layout_pyramid(c);
+
+    const size_t texels = (size_t) c->W * c->H;
+    cudaError_t e1 = cudaMalloc(&c->d_heights, texels * sizeof(float));
+    cudaError_t e2 = cudaMalloc(&c->d_grad, texels * sizeof(float));
+    cudaError_t e3 = cudaMalloc(&c->d_pyr, c->pyr_nodes * sizeof(float2));
+    cudaError_t e4 = cudaMalloc(&c->d_counters, 4 * sizeof(unsigned long long));
+    if (e1 || e2 || e3 || e4) { hf_destroy(c); return fail(HF_ERR_CUDA, "cudaMalloc failed for a %ux%u heightfield", c->W, c->H); }
+    cudaMemset(c->d_grad, 0, texels * sizeof(float));
+    cudaMemset(c->d_pyr, 0, c->pyr_nodes * sizeof(float2));
+    cudaMemset(c->d_counters, 0, 4 * sizeof(unsigned long long));
+    P.heights = c->d_heights;
+    P.pyr = c->d_pyr;
+    *out = c;
+    return HF_OK;
+}
+
+extern "C" int hf_destroy(hf_ctx *c) {
+    if (!c) return HF_OK;
+    cudaSetDevice(c->device);
+    if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
+    for (auto &s : c->slots) { if (s.slab) cudaFree(s.slab); if (s.stream) cudaStreamDestroy(s.stream); }
+    cudaFree(c->d_heights); cudaFree(c->d_grad); cudaFree(c->d_m); cudaFree(c->d_v); cudaFree(c->d_pyr); cudaFree(c->d_counters);
+    delete c;
+    return HF_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// parameters
+// ------------------------------------------------------------------------------------------
+extern "C" int hf_set_heights(hf_ctx *c, const float *src, int src_on_device, void *stream) {
+    CHECK_CTX(c);
+    if (!src) return fail(HF_ERR_INVALID, "null heights");
+    CU(cudaSetDevice(c->device));
+    CU(cudaMemcpyAsync(c->d_heights, src, (size_t) c->W * c->H * sizeof(float),
+                       src_on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, (cudaStream_t) stream));
+    c->have_heights = true;
+    c->accel_valid = false;
+    return HF_OK;
+}
+
+extern "C" int hf_heights(hf_ctx *c, float **d) {
+    CHECK_CTX(c);
+    if (!d) return fail(HF_ERR_INVALID, "null out pointer");
+    *d = c->d_heights;
+    c->have_heights = true;       // the caller may fill the buffer in place, then call hf_parameters_changed
+    return HF_OK;
+}
+
+extern "C" int hf_grad(hf_ctx *c, float **d) {
+    CHECK_CTX(c);
+    if (!d) return fail(HF_ERR_INVALID, "null out pointer");
+    *d = c->d_grad;
+    return HF_OK;
+}
+
+extern "C" int hf_zero_grad(hf_ctx *c, void *stream) {
+    CHECK_CTX(c);
+    CU(cudaSetDevice(c->device));
+    CU(cudaMemsetAsync(c->d_grad, 0, (size_t) c->W * c->H * sizeof(float), (cudaStream_t) stream));
+    return HF_OK;
+}
+
+extern "C" int hf_set_to_world(hf_ctx *c, const float to_world[12], const float *to_object) {
+    CHECK_CTX(c);
+    if (!to_world) return fail(HF_ERR_INVALID, "null to_world");
+    return set_transform(c, to_world, to_object);
+}
+
+extern "C" int hf_set_max_height(hf_ctx *c, float mh) {
+    CHECK_CTX(c);
+    if (!isfinite(mh)) return fail(HF_ERR_INVALID, "max_height is not finite");
+    c->P.mh = mh;
+    c->accel_valid = false;
+    return HF_OK;
+}
+
+extern "C" int hf_parameters_changed(hf_ctx *c, void *stream) {
+    CHECK_CTX(c);
+    if (!c->have_heights) return fail(HF_ERR_STATE, "heights were never set");
+    CU(cudaSetDevice(c->device));
+    CU(hf_launch_pyramid(c->P, c->d_pyr, (cudaStream_t) stream));
+    c->accel_valid = true;
+    return HF_OK;
+}
+
+extern "C" int hf_parameters_grad_enabled(hf_ctx *c, int *enabled) {
+    CHECK_CTX(c);
+    if (!enabled) return fail(HF_ERR_INVALID, "null out pointer");
+    *enabled = c->grad_enabled;
+    return HF_OK;
+}
+
+extern "C" int hf_set_grad_enabled(hf_ctx *c, int enabled) {
+    CHECK_CTX(c);
+    c->grad_enabled = enabled ? 1 : 0;
+    return HF_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// queries
+// ------------------------------------------------------------------------------------------
+#define NEED_ACCEL(c) do { if (!(c)->accel_valid) return fail(HF_ERR_STATE, "acceleration data is stale: call hf_parameters_changed after setting heights / max_height"); } while (0)
+
+static inline void xform_point_host(const float m[12], const float p[3], float out[3]) {
+    for (int r = 0; r < 3; ++r) {
+        float v = m[r * 4 + 3];
+        v = fmaf(m[r * 4 + 0], p[0], v); v = fmaf(m[r * 4 + 1], p[1], v); v = fmaf(m[r * 4 + 2], p[2], v);
+        out[r] = v;
+    }
+}
+
+extern "C" int hf_bbox(hf_ctx *c, float out[6]) {
+    CHECK_CTX(c);
+    if (!out) return fail(HF_ERR_INVALID, "null out pointer");
+    NEED_ACCEL(c);
+    CU(cudaSetDevice(c->device));
+    float2 top;
+    CU(cudaDeviceSynchronize());
+    CU(cudaMemcpy(&top, c->d_pyr + c->P.lvl_off[c->P.Ltop], sizeof(float2), cudaMemcpyDeviceToHost));
+    const HfParams &P = c->P;
+    float lo[3] = { P.x0, P.y0, top.x };
+    float hi[3] = { (float) (P.W - 1) * P.rw, (float) (P.H - 1) * P.rh, top.y };
+    for (int a = 0; a < 3; ++a) { out[a] = INFINITY; out[3 + a] = -INFINITY; }
+    for (int k = 0; k < 8; ++k) {
+        float q[3] = { (k & 1) ? hi[0] : lo[0], (k & 2) ? hi[1] : lo[1], (k & 4) ? hi[2] : lo[2] }, w[3];
+        xform_point_host(P.to_world, q, w);
+        for (int a = 0; a < 3; ++a) { out[a] = fminf(out[a], w[a]); out[3 + a] = fmaxf(out[3 + a], w[a]); }
+    }
+    return HF_OK;
+}
+
+extern "C" int hf_primitive_count(hf_ctx *c, uint32_t *count) {
+    CHECK_CTX(c);
+    if (!count) return fail(HF_ERR_INVALID, "null out pointer");
+    *count = 2u * (c->W - 1u) * (c->H - 1u);
+    return HF_OK;
+}
+
+extern "C" int hf_size(hf_ctx *c, uint32_t *w, uint32_t *h) {
+    CHECK_CTX(c);
+    if (w) *w = c->W;
+    if (h) *h = c->H;
+    return HF_OK;
+}
+
+static int check_rays(const hf_rays *r) {
+    if (!r) return fail(HF_ERR_INVALID, "null rays");
+    if (!r->ox || !r->oy || !r->oz || !r->dx || !r->dy || !r->dz || !r->maxt) return fail(HF_ERR_INVALID, "ray batch has a null component");
+    return HF_OK;
+}
+static int check_prelim(const hf_prelim *p) {
+    if (!p || !p->t || !p->u || !p->v || !p->prim_index) return fail(HF_ERR_INVALID, "preliminary intersection has a null component");
+    return HF_OK;
+}
+
+extern "C" int hf_ray_intersect_preliminary(hf_ctx *c, const hf_rays *rays, const hf_prelim *out, size_t n, void *stream) {
+    CHECK_CTX(c);
+    int rc;
+    if ((rc = check_rays(rays)) || (rc = check_prelim(out))) return rc;
+    NEED_ACCEL(c);
+    CU(cudaSetDevice(c->device));
+    hf_si none; memset(&none, 0, sizeof(none));
+    CU(hf_launch_intersect(c->P, c->li, HF_MODE_PRELIM, *rays, *out, none, nullptr, 0, n, c->d_counters, (cudaStream_t) stream));
+    return HF_OK;
+}
+
+extern "C" int hf_ray_intersect_preliminary_counted(hf_ctx *c, const hf_rays *rays, const hf_prelim *out, size_t n, void *stream) {
+    CHECK_CTX(c);
+    int rc;
+    if ((rc = check_rays(rays)) || (rc = check_prelim(out))) return rc;
+    NEED_ACCEL(c);
+    CU(cudaSetDevice(c->device));
+    hf_si none; memset(&none, 0, sizeof(none));
+    CU(hf_launch_intersect(c->P, c->li, HF_MODE_COUNTED, *rays, *out, none, nullptr, 0, n, c->d_counters, (cudaStream_t) stream));
+    return HF_OK;
+}
+
+extern "C" int hf_stats_get(hf_ctx *c, hf_stats *out, int reset) {
+    CHECK_CTX(c);
+    if (!out) return fail(HF_ERR_INVALID, "null out pointer");
+    CU(cudaSetDevice(c->device));
+    unsigned long long h[4];
+    CU(cudaDeviceSynchronize());
+    CU(cudaMemcpy(h, c->d_counters, sizeof(h), cudaMemcpyDeviceToHost));
+    out->rays = h[0]; out->nodes = h[1]; out->leaves = h[2]; out->hits = h[3];
+    if (reset) CU(cudaMemset(c->d_counters, 0, sizeof(h)));
+    return HF_OK;
+}
+
+extern "C" int hf_ray_test(hf_ctx *c, const hf_rays *rays, uint8_t *d_hit, size_t n, void *stream) {
+    CHECK_CTX(c);
+    int rc;
+    if ((rc = check_rays(rays))) return rc;
+    if (!d_hit) return fail(HF_ERR_INVALID, "null hit buffer");
+    NEED_ACCEL(c);
+    CU(cudaSetDevice(c->device));
+    hf_si none; memset(&none, 0, sizeof(none));
+    hf_prelim nop; memset(&nop, 0, sizeof(nop));
+    CU(hf_launch_intersect(c->P, c->li, HF_MODE_TEST, *rays, nop, none, d_hit, 0, n, c->d_counters, (cudaStream_t) stream));
+    return HF_OK;
+}
+
+static int check_flags(uint32_t flags) {
+    // src/render/mesh.cpp:709-711
+    if ((flags & HF_RAY_DETACHSHAPE) && (flags & HF_RAY_FOLLOWSHAPE))
+        return fail(HF_ERR_INVALID, "Invalid combination of RayFlags: DetachShape | FollowShape");
+    return HF_OK;
+}
+
+extern "C" int hf_compute_surface_interaction(hf_ctx *c, const hf_rays *rays, const hf_prelim *pi, uint32_t flags,
+                                              const hf_si *out, size_t n, void *stream) {
+    CHECK_CTX(c);
+    int rc;
+    if ((rc = check_rays(rays)) || (rc = check_prelim(pi)) || (rc = check_flags(flags))) return rc;
+    if (!out) return fail(HF_ERR_INVALID, "null surface interaction");
+    if (!c->have_heights) return fail(HF_ERR_STATE, "heights were never set");
+    CU(cudaSetDevice(c->device));
+    CU(hf_launch_surface_interaction(c->P, c->li, *rays, *pi, flags, *out, n, (cudaStream_t) stream));
+    return HF_OK;
+}
+
+extern "C" int hf_ray_intersect(hf_ctx *c, const hf_rays *rays, uint32_t flags, const hf_prelim *prelim_out,
+                                const hf_si *out, size_t n, void *stream) {
+    CHECK_CTX(c);
+    int rc;
+    if ((rc = check_rays(rays)) || (rc = check_flags(flags))) return rc;
+    if (!out) return fail(HF_ERR_INVALID, "null surface interaction");
+    if (prelim_out && (rc = check_prelim(prelim_out))) return rc;
+    NEED_ACCEL(c);
+    CU(cudaSetDevice(c->device));
+    hf_prelim nop; memset(&nop, 0, sizeof(nop));
+    CU(hf_launch_intersect(c->P, c->li, HF_MODE_FUSED_SI, *rays, prelim_out ? *prelim_out : nop, *out, nullptr, flags, n,
+                           c->d_counters, (cudaStream_t) stream));
+    return HF_OK;
+}
+
+extern "C" int hf_backward(hf_ctx *c, const hf_rays *rays, const hf_prelim *pi, const hf_si_adj *adj, uint32_t flags,
+                           size_t n, void *stream) {
+    CHECK_CTX(c);
+    int rc;
+    if ((rc = check_rays(rays)) || (rc = check_prelim(pi)) || (rc = check_flags(flags))) return rc;
+    if (!adj) return fail(HF_ERR_INVALID, "null adjoints");
+    if (!c->have_heights) return fail(HF_ERR_STATE, "heights were never set");
+    if (!c->grad_enabled) return HF_OK;        // parameters_grad_enabled() == false: nothing to accumulate
+    CU(cudaSetDevice(c->device));
+    CU(hf_launch_backward(c->P, c->li, *rays, *pi, *adj, flags, c->d_grad, n, (cudaStream_t) stream));
+    return HF_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// optimiser + collective
+// ------------------------------------------------------------------------------------------
+extern "C" int hf_adam_reset(hf_ctx *c, void *stream) {
+    CHECK_CTX(c);
+    CU(cudaSetDevice(c->device));
+    const size_t bytes = (size_t) c->W * c->H * sizeof(float);
+    if (!c->d_m) { CU(cudaMalloc(&c->d_m, bytes)); }
+    if (!c->d_v) { CU(cudaMalloc(&c->d_v, bytes)); }
+    CU(cudaMemsetAsync(c->d_m, 0, bytes, (cudaStream_t) stream));
+    CU(cudaMemsetAsync(c->d_v, 0, bytes, (cudaStream_t) stream));
+    c->adam_t = 0;
+    return HF_OK;
+}
+
+extern "C" int hf_adam_step(hf_ctx *c, const hf_adam *cfg, void *stream) {
+    CHECK_CTX(c);
+    if (!cfg) return fail(HF_ERR_INVALID, "null Adam configuration");
+    // optimizers.py:243-244
+    if (!(cfg->beta1 >= 0.f && cfg->beta1 < 1.f && cfg->beta2 >= 0.f && cfg->beta2 < 1.f && cfg->lr > 0.f && cfg->epsilon > 0.f))
+        return fail(HF_ERR_INVALID, "Adam: need 0 <= beta < 1, lr > 0, epsilon > 0");
+    if (!c->have_heights) return fail(HF_ERR_STATE, "heights were never set");
+    if (!c->d_m || !c->d_v) { int rc = hf_adam_reset(c, stream); if (rc) return rc; }
+    CU(cudaSetDevice(c->device));
+    c->adam_t += 1;
+    // optimizers.py:266-269: lr_scale in Python doubles, then an opaque fp32
+    const double b1 = (double) cfg->beta1, b2 = (double) cfg->beta2;
+    const float lr_scale = (float) (sqrt(1.0 - pow(b2, c->adam_t)) / (1.0 - pow(b1, c->adam_t)));
+    const float lr_t = cfg->lr * lr_scale;
+    CU(hf_launch_adam(c->d_heights, c->d_grad, c->d_m, c->d_v, (size_t) c->W * c->H, lr_t, cfg->beta1, cfg->beta2,
+                      (float) (1.0 - b1), (float) (1.0 - b2), cfg->epsilon, cfg->mask_updates, c->num_sms, (cudaStream_t) stream));
+    c->accel_valid = false;       // heights moved: the caller runs hf_parameters_changed (SceneParameters.update)
+    return HF_OK;
+}
+
+extern "C" int hf_comm_unique_id(uint8_t out_id[128]) {
+    if (!out_id) return fail(HF_ERR_INVALID, "null id buffer");
+    int rc = nccl_load();
+    if (rc) return rc;
+    hf_nccl_uid id;
+    NC(g_nccl.GetUniqueId(&id));
+    memcpy(out_id, id.internal, 128);
+    return HF_OK;
+}
+
+extern "C" int hf_comm_init(hf_ctx *c, int rank, int nranks, const uint8_t id_bytes[128]) {
+    CHECK_CTX(c);
+    if (!id_bytes || nranks < 1 || rank < 0 || rank >= nranks) return fail(HF_ERR_INVALID, "bad communicator arguments");
+    int rc = nccl_load();
+    if (rc) return rc;
+    CU(cudaSetDevice(c->device));
+    if (c->comm) { g_nccl.CommDestroy(c->comm); c->comm = nullptr; }
+    hf_nccl_uid id;
+    memcpy(id.internal, id_bytes, 128);
+    NC(g_nccl.CommInitRank(&c->comm, nranks, id, rank));
+    c->nranks = nranks;
+    return HF_OK;
+}
+
+extern "C" int hf_comm_destroy(hf_ctx *c) {
+    CHECK_CTX(c);
+    if (c->comm) { NC(g_nccl.CommDestroy(c->comm)); c->comm = nullptr; }
+    c->nranks = 1;
+    return HF_OK;
+}
+
+extern "C" int hf_allreduce_grad(hf_ctx *c, void *stream) {
+    CHECK_CTX(c);
+    if (!c->comm) return fail(HF_ERR_STATE, "hf_comm_init was not called");
+    CU(cudaSetDevice(c->device));
+    // ncclFloat32 = 7, ncclSum = 0
+    NC(g_nccl.AllReduce(c->d_grad, c->d_grad, (size_t) c->W * c->H, 7, 0, c->comm, (cudaStream_t) stream));
+    return HF_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// host-buffer entry points: chunked, double-buffered H2D -> kernels -> D2H
+// ------------------------------------------------------------------------------------------
+extern "C" int hf_host_alloc(void **out, size_t bytes) {
+    if (!out) return fail(HF_ERR_INVALID, "null out pointer");
+    CU(cudaHostAlloc(out, bytes ? bytes : 1, cudaHostAllocDefault));
+    return HF_OK;
+}
+extern "C" int hf_host_free(void *p) {
+    if (p) CU(cudaFreeHost(p));
+    return HF_OK;
+}
+
+static int ensure_slots(hf_ctx *c) {
+    if (c->slots_ready) return HF_OK;
+    for (auto &s : c->slots) {
+        CU(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
+        CU(cudaMalloc(&s.slab, HF_HOST_CHUNK * HF_SLAB_FLOATS * sizeof(float)));
+    }
+    c->slots_ready = true;
+    return HF_OK;
+}
+
+#define SI_NFIELDS 26
+#define ADJ_NFIELDS 15
+
+static int host_pipeline(hf_ctx *c, const hf_rays *hr, const hf_si_adj *hadj, uint32_t flags, const hf_prelim *hpre,
+                         const hf_si *hsi, float *h_grad_out, size_t n, bool backward) {
+    int rc;
+    if ((rc = check_rays(hr)) || (rc = check_flags(flags))) return rc;
+    if (hpre && (rc = check_prelim(hpre))) return rc;
+    if (backward && !hadj) return fail(HF_ERR_INVALID, "null adjoints");
+    NEED_ACCEL(c);
+    CU(cudaSetDevice(c->device));
+    if ((rc = ensure_slots(c))) return rc;
+    // order after whatever the caller queued on the legacy stream (heights upload, pyramid build)
+    CU(cudaDeviceSynchronize());
+
+    float *const *hsi_f = reinterpret_cast<float *const *>(hsi);
+    const float *const *hadj_f = reinterpret_cast<const float *const *>(hadj);
+    const float *hray_f[7] = { hr->ox, hr->oy, hr->oz, hr->dx, hr->dy, hr->dz, hr->maxt };
+
+    size_t chunk_idx = 0;
+    for (size_t base = 0; base < n; base += HF_HOST_CHUNK, ++chunk_idx) {
+        const size_t m = std::min(HF_HOST_CHUNK, n - base);
+        HostSlot &s = c->slots[chunk_idx % HF_HOST_SLOTS];
+        float *slab = s.slab;
+        auto field = [&](int k) { return slab + (size_t) k * HF_HOST_CHUNK; };
+
+        hf_rays dr; memset(&dr, 0, sizeof(dr));
+        const float **drf = reinterpret_cast<const float **>(&dr);
+        for (int k = 0; k < 7; ++k) {
+            CU(cudaMemcpyAsync(field(k), hray_f[k] + base, m * sizeof(float), cudaMemcpyHostToDevice, s.stream));
+            drf[k] = field(k);
+        }
+        if (hr->active) {
+            uint8_t *da = reinterpret_cast<uint8_t *>(field(52));
+            CU(cudaMemcpyAsync(da, hr->active + base, m, cudaMemcpyHostToDevice, s.stream));
+            dr.active = da;
+        }
+        hf_prelim dp;
+        dp.t = field(7); dp.u = field(8); dp.v = field(9); dp.prim_index = reinterpret_cast<uint32_t *>(field(10));
+        hf_si dsi; memset(&dsi, 0, sizeof(dsi));
+        float **dsif = reinterpret_cast<float **>(&dsi);
+        if (hsi) for (int k = 0; k < SI_NFIELDS; ++k) if (hsi_f[k]) dsif[k] = field(11 + k);
+        hf_si_adj dadj; memset(&dadj, 0, sizeof(dadj));
+        const float **dadjf = reinterpret_cast<const float **>(&dadj);
+        if (backward) {
+            int slot = 37;
+            for (int k = 0; k < ADJ_NFIELDS; ++k) if (hadj_f[k]) {
+                CU(cudaMemcpyAsync(field(slot), hadj_f[k] + base, m * sizeof(float), cudaMemcpyHostToDevice, s.stream));
+                dadjf[k] = field(slot);
+                ++slot;
+            }
+        }
+
+        CU(hf_launch_intersect(c->P, c->li, HF_MODE_FUSED_SI, dr, dp, dsi, nullptr, flags, m, c->d_counters, s.stream));
+        if (backward && c->grad_enabled)
+            CU(hf_launch_backward(c->P, c->li, dr, dp, dadj, flags, c->d_grad, m, s.stream));
+
+        if (hpre) {
+            CU(cudaMemcpyAsync(hpre->t + base, dp.t, m * sizeof(float), cudaMemcpyDeviceToHost, s.stream));
+            CU(cudaMemcpyAsync(hpre->u + base, dp.u, m * sizeof(float), cudaMemcpyDeviceToHost, s.stream));
+            CU(cudaMemcpyAsync(hpre->v + base, dp.v, m * sizeof(float), cudaMemcpyDeviceToHost, s.stream));
+            CU(cudaMemcpyAsync(hpre->prim_index + base, dp.prim_index, m * sizeof(uint32_t), cudaMemcpyDeviceToHost, s.stream));
+        }
+        if (hsi) for (int k = 0; k < SI_NFIELDS; ++k) if (hsi_f[k])
+            CU(cudaMemcpyAsync(hsi_f[k] + base, dsif[k], m * sizeof(float), cudaMemcpyDeviceToHost, s.stream));
+    }
+    for (auto &s : c->slots) CU(cudaStreamSynchronize(s.stream));
+    if (h_grad_out) CU(cudaMemcpy(h_grad_out, c->d_grad, (size_t) c->W * c->H * sizeof(float), cudaMemcpyDeviceToHost));
+    return HF_OK;
+}
+
+extern "C" int hf_ray_intersect_host(hf_ctx *c, const hf_rays *h_rays, uint32_t flags, const hf_prelim *h_prelim_out,
+                                     const hf_si *h_out, size_t n) {
+    CHECK_CTX(c);
+    return host_pipeline(c, h_rays, nullptr, flags, h_prelim_out, h_out, nullptr, n, false);
+}
+
+extern "C" int hf_forward_backward_host(hf_ctx *c, const hf_rays *h_rays, const hf_si_adj *h_adj, uint32_t flags,
+                                        const hf_prelim *h_prelim_out, const hf_si *h_out, float *h_grad_out, size_t n) {
+    CHECK_CTX(c);
+    return host_pipeline(c, h_rays, h_adj, flags, h_prelim_out, h_out, h_grad_out, n, true);
+}

@@ -1,0 +1,672 @@
+// hf_kernels.cu -- hand-written sm_100a kernels of the differentiable heightfield path.
+//
+//   hf_pyramid_tile_kernel / hf_pyramid_top_kernel : min/max mip pyramid (the shape's acceleration
+//        data; replaces the Embree re-commit / OptiX GAS rebuild of src/render/scene.cpp:343-367)
+//   hf_intersect_kernel      : hierarchical DDA + two Moeller-Trumbore triangles per cell
+//        (Shape::ray_intersect_preliminary / ray_test / ray_intersect, shape.h:137-197)
+//   hf_si_kernel             : Shape::compute_surface_interaction (+ finalize), shape.h:179-183
+//   hf_backward_kernel       : reverse mode w.r.t. the hit cell's texels, warp-aggregated atomics
+//   hf_adam_kernel           : src/python/python/ad/optimizers.py:263-302
+//
+// Compiled with -fmad=false: see hf_device.cuh.
+#include "hf_kernels.h"
+
+#define HF_BLOCK 256
+#define FULL_MASK 0xffffffffu
+
+// ------------------------------------------------------------------------------------------
+// small PTX helpers: mbarrier + 1-D bulk copy (TMA engine, SASS UBLKCP) for pyramid staging
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t) __cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void *dst_smem, const void *src_gmem, uint32_t bytes, uint64_t *bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_u32(dst_smem)), "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint64_t *bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                 : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+    return ok != 0;
+}
+
+// ------------------------------------------------------------------------------------------
+// Pyramid build
+// ------------------------------------------------------------------------------------------
+#define PT 64                      // cells per tile edge
+#define PT_LEVELS 6                // levels 1..6 come out of one tile
+
+__global__ void __launch_bounds__(256) hf_pyramid_tile_kernel(const __grid_constant__ HfParams P, float2 *__restrict__ pyr) {
+    __shared__ float s_z[(PT + 1) * (PT + 1)];
+    __shared__ float2 s_lv[1024 + 256 + 64 + 16 + 4 + 1];
+
+    const int tx0 = blockIdx.x * PT, ty0 = blockIdx.y * PT;      // first cell == first texel of the tile
+    const int tw = min(PT + 1, P.W - tx0), th = min(PT + 1, P.H - ty0);   // valid texels in the tile
+
+    for (int idx = threadIdx.x; idx < (PT + 1) * (PT + 1); idx += blockDim.x) {
+        int j = idx / (PT + 1), i = idx - j * (PT + 1);
+        float z = 0.f;
+        if (i < tw && j < th) z = P.mh * __ldg(P.heights + (size_t) (ty0 + j) * P.W + (tx0 + i));
+        s_z[idx] = z;
+    }
+    __syncthreads();
+
+    // level 1: node covers texels [2lx, 2lx+2] x [2ly, 2ly+2], clamped to the grid
+    {
+        const int lw = P.lvl_w[1], lh = (P.NY + 1) >> 1;
+        const int gx0 = blockIdx.x * 32, gy0 = blockIdx.y * 32;
+        for (int idx = threadIdx.x; idx < 1024; idx += blockDim.x) {
+            int ly = idx >> 5, lx = idx & 31;
+            float mn = HF_INF, mx = -HF_INF;
+            if (gx0 + lx < lw && gy0 + ly < lh) {
+                int i1 = min(2 * lx + 2, tw - 1), j1 = min(2 * ly + 2, th - 1);
+                for (int j = 2 * ly; j <= j1; ++j)
+                    for (int i = 2 * lx; i <= i1; ++i) {
+                        float z = s_z[j * (PT + 1) + i];
+                        mn = fminf(mn, z); mx = fmaxf(mx, z);
+                    }
+                pyr[(size_t) P.lvl_off[1] + (size_t) (gy0 + ly) * lw + (gx0 + lx)] = make_float2(mn, mx);
+            }
+            s_lv[idx] = make_float2(mn, mx);     // absent nodes hold (+inf,-inf): neutral for min/max
+        }
+    }
+    __syncthreads();
+
+    // levels 2..6 from shared memory
+    int src_off = 0, src_dim = 32;
+    for (int l = 2; l <= PT_LEVELS; ++l) {
+        const int dim = src_dim >> 1, dst_off = src_off + src_dim * src_dim;
+        if (l <= P.Ltop) {
+            const int lw = P.lvl_w[l], lh = (P.NY + (1 << l) - 1) >> l;
+            const int gx0 = blockIdx.x * dim, gy0 = blockIdx.y * dim;
+            for (int idx = threadIdx.x; idx < dim * dim; idx += blockDim.x) {
+                int ly = idx / dim, lx = idx - ly * dim;
+                float2 a = s_lv[src_off + (2 * ly) * src_dim + 2 * lx], b = s_lv[src_off + (2 * ly) * src_dim + 2 * lx + 1];
+                float2 c = s_lv[src_off + (2 * ly + 1) * src_dim + 2 * lx], d = s_lv[src_off + (2 * ly + 1) * src_dim + 2 * lx + 1];
+                float mn = fminf(fminf(a.x, b.x), fminf(c.x, d.x)), mx = fmaxf(fmaxf(a.y, b.y), fmaxf(c.y, d.y));
+                s_lv[dst_off + idx] = make_float2(mn, mx);
+                if (gx0 + lx < lw && gy0 + ly < lh)
+                    pyr[(size_t) P.lvl_off[l] + (size_t) (gy0 + ly) * lw + (gx0 + lx)] = make_float2(mn, mx);
+            }
+        }
+        __syncthreads();
+        src_off = dst_off; src_dim = dim;
+    }
+}
+
+// levels PT_LEVELS+1 .. Ltop: one CTA walks up through global memory
+__global__ void __launch_bounds__(1024) hf_pyramid_top_kernel(const __grid_constant__ HfParams P, float2 *__restrict__ pyr) {
+    for (int l = PT_LEVELS + 1; l <= P.Ltop; ++l) {
+        const int sw = P.lvl_w[l - 1], sh = (P.NY + (1 << (l - 1)) - 1) >> (l - 1);
+        const int lw = P.lvl_w[l], lh = (P.NY + (1 << l) - 1) >> l;
+        const float2 *src = pyr + P.lvl_off[l - 1];
+        float2 *dst = pyr + P.lvl_off[l];
+        for (int idx = threadIdx.x; idx < lw * lh; idx += blockDim.x) {
+            int ny = idx / lw, nx = idx - ny * lw;
+            float mn = HF_INF, mx = -HF_INF;
+            #pragma unroll
+            for (int dj = 0; dj < 2; ++dj)
+                #pragma unroll
+                for (int di = 0; di < 2; ++di) {
+                    int i = 2 * nx + di, j = 2 * ny + dj;
+                    if (i < sw && j < sh) { float2 c = src[(size_t) j * sw + i]; mn = fminf(mn, c.x); mx = fmaxf(mx, c.y); }
+                }
+            dst[idx] = make_float2(mn, mx);
+        }
+        __syncthreads();
+    }
+}
+
+cudaError_t hf_launch_pyramid(const HfParams &P, float2 *pyr, cudaStream_t s) {
+    dim3 grid((P.NX + PT - 1) / PT, (P.NY + PT - 1) / PT);
+    hf_pyramid_tile_kernel<<<grid, 256, 0, s>>>(P, pyr);
+    if (P.Ltop > PT_LEVELS) hf_pyramid_top_kernel<<<1, 1024, 0, s>>>(P, pyr);
+    return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------------------------------
+// Traversal
+// ------------------------------------------------------------------------------------------
+struct TopCache {               // shared-memory view of pyramid levels >= Ls, plus per-level tables
+    const int *off;             // [HF_MAX_LEVELS] node offset of each level
+    const int *w;               // [HF_MAX_LEVELS] nodes per row
+    const float2 *nodes;        // levels Ls..Ltop
+    int Ls, base;               // base = off[Ls]
+};
+
+struct HitRec {
+    float t, u, v;
+    uint32_t prim;
+    int cx, cy;
+    float z00, z10, z01, z11;
+};
+
+__device__ __forceinline__ int floor_clamp(float x, int lo, int hi) {
+    if (!(x > (float) lo)) return lo;
+    if (!(x < (float) hi)) return hi;
+    return __float2int_rd(x);
+}
+
+// Object-space ray (o, d, maxt). Front-to-back walk: the first cell with a hit is the closest hit.
+// The arithmetic mirrors oracle/hf_oracle.c::traverse (the canonical traversal of the byte model).
+template <bool COUNT>
+__device__ __forceinline__ bool traverse(const HfParams &P, const TopCache &C, f3 o, f3 d, float maxt, HitRec &h,
+                                         uint32_t &cn, uint32_t &cl) {
+    const int NX = P.NX, NY = P.NY, Ltop = P.Ltop;
+    if (d.x == 0.f && d.y == 0.f && d.z == 0.f) return false;
+    if (!(maxt >= 0.f)) return false;
+
+    const float ogx = (o.x - P.x0) * P.sgx, ogy = (o.y - P.y0) * P.sgy;
+    const float dgx = d.x * P.sgx, dgy = d.y * P.sgy;
+    const float oz = o.z, dz = d.z;
+    const float idx = __fdiv_rn(1.0f, dgx), idy = __fdiv_rn(1.0f, dgy), idz = __fdiv_rn(1.0f, dz);
+    const bool zx = dgx == 0.f, zy = dgy == 0.f;
+
+    float t0 = 0.f, t1 = maxt;
+    if (!zx) {
+        float a = (0.f - ogx) * idx, b = ((float) NX - ogx) * idx;
+        t0 = fmaxf(t0, fminf(a, b)); t1 = fminf(t1, fmaxf(a, b));
+    } else if (ogx < 0.f || ogx > (float) NX) return false;
+    if (!zy) {
+        float a = (0.f - ogy) * idy, b = ((float) NY - ogy) * idy;
+        t0 = fmaxf(t0, fminf(a, b)); t1 = fminf(t1, fmaxf(a, b));
+    } else if (ogy < 0.f || ogy > (float) NY) return false;
+    {
+        const float2 top = C.nodes[C.off[Ltop] - C.base];
+        const float pad = HF_Z_SLACK * fmaxf(fabsf(top.x), fabsf(top.y)) + HF_Z_SLACK * fabsf(oz);
+        if (dz != 0.f) {
+            float a = (top.x - pad - oz) * idz, b = (top.y + pad - oz) * idz;
+            float tn = fminf(a, b), tf = fmaxf(a, b);
+            tn -= fabsf(tn) * HF_Z_SLACK; tf += fabsf(tf) * HF_Z_SLACK;
+            t0 = fmaxf(t0, tn); t1 = fminf(t1, tf);
+        } else if (oz < top.x - pad || oz > top.y + pad) return false;
+    }
+    if (!(t0 <= t1)) return false;
+
+    const float epsz = HF_Z_SLACK * (fabsf(oz) + fabsf(t1 * dz));
+    const bool sx = dgx > 0.f, sy = dgy > 0.f;
+
+    int ix = floor_clamp(fmaf(t0, dgx, ogx), 0, NX - 1);
+    int iy = floor_clamp(fmaf(t0, dgy, ogy), 0, NY - 1);
+    int L = Ltop;
+    float t = t0;
+    bool alive = true;
+    const float *__restrict__ H = P.heights;
+
+    for (;;) {
+        bool cand = false;
+        // phase 1: walk nodes until a leaf cell overlaps the ray's z interval, or the ray ends
+        while (alive && !cand) {
+            const int nx = ix >> L, ny = iy >> L;
+            const int bx = sx ? min((nx + 1) << L, NX) : (nx << L);
+            const int by = sy ? min((ny + 1) << L, NY) : (ny << L);
+            const float tx = zx ? HF_INF : ((float) bx - ogx) * idx;
+            const float ty = zy ? HF_INF : ((float) by - ogy) * idy;
+            float te = fminf(tx, ty);
+            const bool last = !(te < t1);
+            if (last) te = t1;
+            const float za = fmaf(t, dz, oz), zb = fmaf(te, dz, oz);
+            const float zlo = fminf(za, zb) - epsz, zhi = fmaxf(za, zb) + epsz;
+
+            if (L > 0) {
+                const int ni = C.off[L] + ny * C.w[L] + nx;
+                const float2 node = (L >= C.Ls) ? C.nodes[ni - C.base] : __ldg(P.pyr + ni);
+                if (COUNT) cn++;
+                if (zlo <= node.y && zhi >= node.x) { L--; continue; }
+            } else {
+                const float *row0 = H + (size_t) iy * P.W + ix;
+                const float z00 = P.mh * __ldg(row0), z10 = P.mh * __ldg(row0 + 1);
+                const float z01 = P.mh * __ldg(row0 + P.W), z11 = P.mh * __ldg(row0 + P.W + 1);
+                const float mn = fminf(fminf(z00, z10), fminf(z01, z11));
+                const float mx = fmaxf(fmaxf(z00, z10), fmaxf(z01, z11));
+                if (COUNT) cl++;
+                if (zlo <= mx && zhi >= mn) {
+                    cand = true;
+                    h.cx = ix; h.cy = iy; h.z00 = z00; h.z10 = z10; h.z01 = z01; h.z11 = z11;
+                }
+            }
+            // advance to the next node (also after a candidate: phase 2 resumes from there on a miss)
+            if (last) { alive = false; break; }
+            const int ox_ = ix, oy_ = iy;
+            const bool stepx = tx <= ty, stepy = ty <= tx;
+            if (stepx) ix = sx ? bx : bx - 1;
+            else {
+                const int lo = nx << L, hi = min(((nx + 1) << L) - 1, NX - 1);
+                const int q = floor_clamp(fmaf(te, dgx, ogx), lo, hi);
+                ix = sx ? max(q, ox_) : (dgx < 0.f ? min(q, ox_) : ox_);
+            }
+            if (stepy) iy = sy ? by : by - 1;
+            else {
+                const int lo = ny << L, hi = min(((ny + 1) << L) - 1, NY - 1);
+                const int q = floor_clamp(fmaf(te, dgy, ogy), lo, hi);
+                iy = sy ? max(q, oy_) : (dgy < 0.f ? min(q, oy_) : oy_);
+            }
+            if (ix < 0 || ix >= NX || iy < 0 || iy >= NY) { alive = false; break; }
+            t = te;
+            if (L < Ltop && ((((ix ^ ox_) | (iy ^ oy_)) >> (L + 1)) != 0)) L++;
+        }
+        if (!cand) return false;
+        // phase 2: the per-cell primitive
+        if (cell_intersect(P, h.cx, h.cy, h.z00, h.z10, h.z01, h.z11, o, d, maxt, h.t, h.u, h.v, h.prim)) return true;
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// Surface interaction (src/render/mesh.cpp:672-903 on the hit triangle in object space, mapped to
+// world like src/shapes/rectangle.cpp:250-323; finalize per interaction.h:257-266, 476-499)
+// ------------------------------------------------------------------------------------------
+#define STF(ptr, val) do { if (ptr) __stcs((ptr) + i, (val)); } while (0)
+
+__device__ __forceinline__ void write_si_invalid(const hf_si &S, size_t i, f3 dw) {
+    STF(S.t, HF_INF);
+    STF(S.px, 0.f); STF(S.py, 0.f); STF(S.pz, 0.f);
+    STF(S.nx, 0.f); STF(S.ny, 0.f); STF(S.nz, 0.f);
+    STF(S.uvx, 0.f); STF(S.uvy, 0.f);
+    STF(S.dpdu_x, 0.f); STF(S.dpdu_y, 0.f); STF(S.dpdu_z, 0.f);
+    STF(S.dpdv_x, 0.f); STF(S.dpdv_y, 0.f); STF(S.dpdv_z, 0.f);
+    STF(S.shn_x, 0.f); STF(S.shn_y, 0.f); STF(S.shn_z, 0.f);
+    STF(S.shs_x, 0.f); STF(S.shs_y, 0.f); STF(S.shs_z, 0.f);
+    STF(S.sht_x, 0.f); STF(S.sht_y, 0.f); STF(S.sht_z, 0.f);
+    STF(S.wi_x, -dw.x); STF(S.wi_y, -dw.y); STF(S.wi_z, -dw.z);
+}
+
+__device__ __forceinline__ void write_si(const HfParams &P, const hf_si &S, size_t i, uint32_t flags,
+                                         f3 ow, f3 dw, float t_in, float b1, float b2, f3 p0, f3 p1, f3 p2) {
+    const float b0 = 1.f - b1 - b2;
+    const f3 dp0 = sub3(p1, p0), dp1 = sub3(p2, p0);
+    // mesh.cpp:748
+    const f3 po = mk3(fmaf(p0.x, b0, fmaf(p1.x, b1, p2.x * b2)),
+                      fmaf(p0.y, b0, fmaf(p1.y, b1, p2.y * b2)),
+                      fmaf(p0.z, b0, fmaf(p1.z, b1, p2.z * b2)));
+    // mesh.cpp:757
+    const f3 no = normalize3(cross3(dp0, dp1));
+    const f3 pw = xform_point(P.to_world, po);
+    f3 nw = normalize3(xform_normal(P.to_object, no));
+
+    const float u0x = tex(p0.x), u0y = tex(p0.y), u1x = tex(p1.x), u1y = tex(p1.y), u2x = tex(p2.x), u2y = tex(p2.y);
+    const float uvx = fmaf(u2x, b2, fmaf(u1x, b1, u0x * b0));
+    const float uvy = fmaf(u2y, b2, fmaf(u1y, b1, u0y * b0));
+
+    f3 dpdu, dpdv;
+    bool have = false;
+    if (flags & HF_RAY_DPDUV) {      // mesh.cpp:778-789
+        const float d0x = u1x - u0x, d0y = u1y - u0y, d1x = u2x - u0x, d1y = u2y - u0y;
+        const float det = fmaf(d0x, d1y, -(d0y * d1x));
+        const float inv_det = rcp_llvm(det);
+        if (det != 0.f) {
+            f3 du = mk3(fmaf(d1y, dp0.x, -(d0y * dp1.x)) * inv_det, fmaf(d1y, dp0.y, -(d0y * dp1.y)) * inv_det,
+                        fmaf(d1y, dp0.z, -(d0y * dp1.z)) * inv_det);
+            f3 dv = mk3(fmaf(-d1x, dp0.x, d0x * dp1.x) * inv_det, fmaf(-d1x, dp0.y, d0x * dp1.y) * inv_det,
+                        fmaf(-d1x, dp0.z, d0x * dp1.z) * inv_det);
+            dpdu = xform_vector(P.to_world, du);
+            dpdv = xform_vector(P.to_world, dv);
+            have = true;
+        }
+    }
+    if (!have) coordinate_system(nw, dpdu, dpdv);       // mesh.cpp:762
+    if (P.flip_normals) nw = neg3(nw);                  // mesh.cpp:837-840
+
+    float t = t_in;
+    if (flags & HF_RAY_FOLLOWSHAPE)                     // mesh.cpp:751-752
+        t = __fsqrt_rn(__fdiv_rn(sqnorm3(sub3(pw, ow)), sqnorm3(dw)));
+
+    STF(S.t, t);
+    STF(S.px, pw.x); STF(S.py, pw.y); STF(S.pz, pw.z);
+    STF(S.nx, nw.x); STF(S.ny, nw.y); STF(S.nz, nw.z);
+    STF(S.uvx, uvx); STF(S.uvy, uvy);
+    STF(S.dpdu_x, dpdu.x); STF(S.dpdu_y, dpdu.y); STF(S.dpdu_z, dpdu.z);
+    STF(S.dpdv_x, dpdv.x); STF(S.dpdv_y, dpdv.y); STF(S.dpdv_z, dpdv.z);
+    STF(S.shn_x, nw.x); STF(S.shn_y, nw.y); STF(S.shn_z, nw.z);
+
+    const bool want_frame = S.shs_x || S.shs_y || S.shs_z || S.sht_x || S.sht_y || S.sht_z || S.wi_x || S.wi_y || S.wi_z;
+    if (want_frame) {
+        f3 ss = mk3(0.f, 0.f, 0.f), st = mk3(0.f, 0.f, 0.f);
+        if (flags & HF_RAY_SHADINGFRAME) {              // interaction.h:257-266
+            const float nd = -dot3(nw, dpdu);
+            ss = normalize3(mk3(fmaf(nw.x, nd, dpdu.x), fmaf(nw.y, nd, dpdu.y), fmaf(nw.z, nd, dpdu.z)));
+            if (dpdu.x == 0.f && dpdu.y == 0.f && dpdu.z == 0.f) { f3 tmp; coordinate_system(nw, ss, tmp); }
+            st = cross3(nw, ss);
+        }
+        const f3 md = neg3(dw);
+        STF(S.shs_x, ss.x); STF(S.shs_y, ss.y); STF(S.shs_z, ss.z);
+        STF(S.sht_x, st.x); STF(S.sht_y, st.y); STF(S.sht_z, st.z);
+        STF(S.wi_x, dot3(md, ss)); STF(S.wi_y, dot3(md, st)); STF(S.wi_z, dot3(md, nw));
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// Intersection kernel (persistent CTAs, one ray per thread per tile of HF_BLOCK rays)
+// ------------------------------------------------------------------------------------------
+template <int MODE>
+__global__ void __launch_bounds__(HF_BLOCK, 4)
+hf_intersect_kernel(const __grid_constant__ HfParams P, const HfLaunchInfo li, const hf_rays R, const hf_prelim O,
+                    const hf_si S, uint8_t *__restrict__ hit_out, const uint32_t flags, const size_t n,
+                    unsigned long long *__restrict__ counters) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    float2 *s_nodes = reinterpret_cast<float2 *>(smem_raw);                       // 16-byte aligned (bulk copy)
+    int *s_off = reinterpret_cast<int *>(smem_raw + (size_t) li.top_nodes * sizeof(float2));
+    int *s_w = s_off + HF_MAX_LEVELS;
+    __shared__ __align__(8) uint64_t s_bar;
+
+    // stage the top of the pyramid with one bulk async copy (TMA engine), tables by plain stores
+    if (threadIdx.x == 0) {
+        mbar_init(&s_bar, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (threadIdx.x < HF_MAX_LEVELS) { s_off[threadIdx.x] = P.lvl_off[threadIdx.x]; s_w[threadIdx.x] = P.lvl_w[threadIdx.x]; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const uint32_t bytes = (uint32_t) li.top_nodes * (uint32_t) sizeof(float2);
+        mbar_expect_tx(&s_bar, bytes);
+        bulk_g2s(s_nodes, P.pyr + li.top_off, bytes, &s_bar);
+    }
+    {
+        uint32_t spins = 0;
+        while (!mbar_try_wait(&s_bar, 0)) { if (++spins > (1u << 24)) __trap(); }
+    }
+
+    TopCache C;
+    C.off = s_off; C.w = s_w; C.nodes = s_nodes; C.Ls = li.top_level_start; C.base = li.top_off;
+
+    unsigned long long acc_nodes = 0, acc_leaves = 0, acc_hits = 0;
+
+    const size_t ntiles = (n + HF_BLOCK - 1) / HF_BLOCK;
+    for (size_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        const size_t i = tile * HF_BLOCK + threadIdx.x;
+        if (i >= n) continue;
+        const f3 ow = mk3(__ldcs(R.ox + i), __ldcs(R.oy + i), __ldcs(R.oz + i));
+        const f3 dw = mk3(__ldcs(R.dx + i), __ldcs(R.dy + i), __ldcs(R.dz + i));
+        const float maxt = __ldcs(R.maxt + i);
+        const bool active = R.active ? (R.active[i] != 0) : true;
+
+        HitRec h;
+        uint32_t cn = 0, cl = 0;
+        bool hit = false;
+        f3 o, d;
+        if (active) {
+            // Transform::transform_affine(ray), src/shapes/rectangle.cpp:206-214: t is preserved
+            o = xform_point(P.to_object, ow);
+            d = xform_vector(P.to_object, dw);
+            hit = traverse<MODE == HF_MODE_COUNTED>(P, C, o, d, maxt, h, cn, cl);
+        }
+
+        if (MODE == HF_MODE_TEST) {
+            hit_out[i] = hit ? 1 : 0;
+            continue;
+        }
+        if (O.t) {
+            __stcs(O.t + i, hit ? h.t : HF_INF);
+            __stcs(O.u + i, hit ? h.u : 0.f);
+            __stcs(O.v + i, hit ? h.v : 0.f);
+            __stcs(O.prim_index + i, hit ? h.prim : 0u);
+        }
+        if (MODE == HF_MODE_FUSED_SI) {
+            if (hit) {
+                // vertices of the hit triangle straight from the cell registers
+                const float x0 = vtx(h.cx, P.W, P.rw), x1 = vtx(h.cx + 1, P.W, P.rw);
+                const float y0 = vtx(h.cy, P.H, P.rh), y1 = vtx(h.cy + 1, P.H, P.rh);
+                const f3 p0 = mk3(x1, y0, h.z10);
+                f3 p1, p2;
+                if ((h.prim & 1u) == 0u) { p1 = mk3(x0, y1, h.z01); p2 = mk3(x0, y0, h.z00); }
+                else { p1 = mk3(x1, y1, h.z11); p2 = mk3(x0, y1, h.z01); }
+                write_si(P, S, i, flags, ow, dw, h.t, h.u, h.v, p0, p1, p2);
+            } else {
+                write_si_invalid(S, i, dw);
+            }
+        }
+        if (MODE == HF_MODE_COUNTED) { acc_nodes += cn; acc_leaves += cl; acc_hits += hit ? 1 : 0; }
+    }
+
+    if (MODE == HF_MODE_COUNTED) {
+        #pragma unroll
+        for (int s = 16; s > 0; s >>= 1) {
+            acc_nodes += __shfl_xor_sync(FULL_MASK, acc_nodes, s);
+            acc_leaves += __shfl_xor_sync(FULL_MASK, acc_leaves, s);
+            acc_hits += __shfl_xor_sync(FULL_MASK, acc_hits, s);
+        }
+        if ((threadIdx.x & 31) == 0) {
+            atomicAdd(counters + 1, acc_nodes);
+            atomicAdd(counters + 2, acc_leaves);
+            atomicAdd(counters + 3, acc_hits);
+        }
+        if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(counters + 0, (unsigned long long) n);
+    }
+}
+
+static inline int hf_grid_for(size_t n, int num_sms, int ctas_per_sm) {
+    size_t ntiles = (n + HF_BLOCK - 1) / HF_BLOCK;
+    size_t cap = (size_t) num_sms * ctas_per_sm;
+    return (int) (ntiles < cap ? (ntiles ? ntiles : 1) : cap);
+}
+
+cudaError_t hf_launch_intersect(const HfParams &P, const HfLaunchInfo &li, int mode, const hf_rays &rays,
+                                const hf_prelim &prelim, const hf_si &si, uint8_t *d_hit, uint32_t flags,
+                                size_t n, unsigned long long *d_counters, cudaStream_t s) {
+    if (n == 0) return cudaSuccess;
+    const size_t smem = (size_t) li.top_nodes * sizeof(float2) + 2 * HF_MAX_LEVELS * sizeof(int);
+    const int grid = hf_grid_for(n, li.num_sms, 8);
+    switch (mode) {
+        case HF_MODE_PRELIM:
+            hf_intersect_kernel<HF_MODE_PRELIM><<<grid, HF_BLOCK, smem, s>>>(P, li, rays, prelim, si, d_hit, flags, n, d_counters); break;
+        case HF_MODE_FUSED_SI:
+            hf_intersect_kernel<HF_MODE_FUSED_SI><<<grid, HF_BLOCK, smem, s>>>(P, li, rays, prelim, si, d_hit, flags, n, d_counters); break;
+        case HF_MODE_TEST:
+            hf_intersect_kernel<HF_MODE_TEST><<<grid, HF_BLOCK, smem, s>>>(P, li, rays, prelim, si, d_hit, flags, n, d_counters); break;
+        default:
+            hf_intersect_kernel<HF_MODE_COUNTED><<<grid, HF_BLOCK, smem, s>>>(P, li, rays, prelim, si, d_hit, flags, n, d_counters); break;
+    }
+    return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------------------------------
+// Stand-alone compute_surface_interaction
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(HF_BLOCK)
+hf_si_kernel(const __grid_constant__ HfParams P, const hf_rays R, const hf_prelim PI, const uint32_t flags,
+             const hf_si S, const size_t n) {
+    for (size_t i = (size_t) blockIdx.x * HF_BLOCK + threadIdx.x; i < n; i += (size_t) gridDim.x * HF_BLOCK) {
+        const f3 ow = mk3(__ldcs(R.ox + i), __ldcs(R.oy + i), __ldcs(R.oz + i));
+        const f3 dw = mk3(__ldcs(R.dx + i), __ldcs(R.dy + i), __ldcs(R.dz + i));
+        const float t = __ldcs(PI.t + i);
+        const bool active = R.active ? (R.active[i] != 0) : true;
+        if (!active || t == HF_INF) { write_si_invalid(S, i, dw); continue; }
+        const float u = __ldcs(PI.u + i), v = __ldcs(PI.v + i);
+        const uint32_t prim = __ldcs(PI.prim_index + i);
+        f3 p0, p1, p2; uint32_t i0, i1, i2;
+        cell_triangle(P, prim, p0, p1, p2, i0, i1, i2);
+        write_si(P, S, i, flags, ow, dw, t, u, v, p0, p1, p2);
+    }
+}
+
+cudaError_t hf_launch_surface_interaction(const HfParams &P, const HfLaunchInfo &li, const hf_rays &rays,
+                                          const hf_prelim &pi, uint32_t flags, const hf_si &si, size_t n, cudaStream_t s) {
+    if (n == 0) return cudaSuccess;
+    hf_si_kernel<<<hf_grid_for(n, li.num_sms, 8), HF_BLOCK, 0, s>>>(P, rays, pi, flags, si, n);
+    return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------------------------------
+// Backward: adjoint of (t, p, n, uv, dp_du, dp_dv) w.r.t. the three texels of the hit triangle,
+// closed form (the hit stays on the ray: p = o + t d), accumulated with warp-aggregated atomics.
+// ------------------------------------------------------------------------------------------
+
+// One RED per distinct address per warp: match.any on the texel index, then a log-step segmented
+// reduction inside each peer group (cf. the reference JIT's reduce_add_f32,
+// ext/drjit/ext/drjit-core/src/cuda_eval.cpp:805-888, which walks its peers serially).
+__device__ __forceinline__ void warp_aggregated_add(float *__restrict__ grad, uint32_t idx, float val, bool valid) {
+    const unsigned act = __ballot_sync(FULL_MASK, valid);
+    if (!valid) return;
+    const unsigned lane = threadIdx.x & 31u;
+    unsigned peers = __match_any_sync(act, idx);
+    const bool leader = (peers & ((1u << lane) - 1u)) == 0u;
+    unsigned rel = __popc(peers & ((1u << lane) - 1u));        // my rank inside the group
+    peers &= (0xfffffffeu << lane);                            // peers above me
+    while (__any_sync(act, peers != 0u)) {
+        const int next = __ffs((int) peers);                   // 1-based lane of the next peer above, 0 = none
+        const float other = __shfl_sync(act, val, next ? next - 1 : (int) lane);
+        if (next) val += other;
+        // ranks that are odd retire: drop them from everybody's peer set
+        const unsigned retired = __ballot_sync(act, (rel & 1u) != 0u);
+        peers &= ~retired;
+        rel >>= 1;
+    }
+    if (leader) atomicAdd(grad + idx, val);
+}
+
+__global__ void __launch_bounds__(HF_BLOCK)
+hf_backward_kernel(const __grid_constant__ HfParams P, const hf_rays R, const hf_prelim PI, const hf_si_adj A,
+                   const uint32_t flags, float *__restrict__ grad, const size_t n) {
+    const size_t ntiles = (n + HF_BLOCK - 1) / HF_BLOCK;
+    for (size_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        const size_t i = tile * HF_BLOCK + threadIdx.x;
+        bool valid = i < n;
+        float t = HF_INF;
+        if (valid) {
+            t = __ldcs(PI.t + i);
+            valid = (t != HF_INF) && (R.active ? (R.active[i] != 0) : true);
+        }
+        uint32_t i0 = 0, i1 = 0, i2 = 0;
+        float g0 = 0.f, g1 = 0.f, g2 = 0.f;
+        if (valid) {
+            const f3 ow = mk3(__ldcs(R.ox + i), __ldcs(R.oy + i), __ldcs(R.oz + i));
+            const f3 dw = mk3(__ldcs(R.dx + i), __ldcs(R.dy + i), __ldcs(R.dz + i));
+            const f3 o = xform_point(P.to_object, ow), d = xform_vector(P.to_object, dw);
+            const float u = __ldcs(PI.u + i), v = __ldcs(PI.v + i);
+            const uint32_t prim = __ldcs(PI.prim_index + i);
+            f3 p0, p1, p2;
+            cell_triangle(P, prim, p0, p1, p2, i0, i1, i2);
+            const f3 e1 = sub3(p1, p0), e2 = sub3(p2, p0);
+            const f3 c = cross3(e1, e2);
+
+            #define LDA(ptr) ((ptr) ? __ldcs((ptr) + i) : 0.f)
+            const float a_t = LDA(A.t);
+            const f3 a_pw = mk3(LDA(A.px), LDA(A.py), LDA(A.pz));
+            f3 a_nw = mk3(LDA(A.nx), LDA(A.ny), LDA(A.nz));
+            const float a_uvx = LDA(A.uvx), a_uvy = LDA(A.uvy);
+            const f3 a_duw = mk3(LDA(A.dpdu_x), LDA(A.dpdu_y), LDA(A.dpdu_z));
+            const f3 a_dvw = mk3(LDA(A.dpdv_x), LDA(A.dpdv_y), LDA(A.dpdv_z));
+            #undef LDA
+            if (P.flip_normals) a_nw = neg3(a_nw);
+
+            f3 a_p = lin_T(P.to_world, a_pw);
+            const f3 a_du = lin_T(P.to_world, a_duw), a_dv = lin_T(P.to_world, a_dvw);
+
+            // n_w = normalize(TO^T normalize(c))
+            const float inv_clen = rsqrtf(dot3(c, c));
+            const f3 no = mk3(c.x * inv_clen, c.y * inv_clen, c.z * inv_clen);
+            const f3 m = lin_T(P.to_object, no);
+            const float inv_mlen = rsqrtf(dot3(m, m));
+            const f3 nw = mk3(m.x * inv_mlen, m.y * inv_mlen, m.z * inv_mlen);
+            const float dn = dot3(nw, a_nw);
+            const f3 a_m = mk3((a_nw.x - nw.x * dn) * inv_mlen, (a_nw.y - nw.y * dn) * inv_mlen, (a_nw.z - nw.z * dn) * inv_mlen);
+            const f3 a_no = lin(P.to_object, a_m);
+            const float dno = dot3(no, a_no);
+            const f3 a_c = mk3((a_no.x - no.x * dno) * inv_clen, (a_no.y - no.y * dno) * inv_clen, (a_no.z - no.z * dno) * inv_clen);
+            f3 a_e1 = cross3(e2, a_c), a_e2 = cross3(a_c, e1);
+
+            const float u0x = tex(p0.x), u0y = tex(p0.y), u1x = tex(p1.x), u1y = tex(p1.y), u2x = tex(p2.x), u2y = tex(p2.y);
+            const float d0x = u1x - u0x, d0y = u1y - u0y, d1x = u2x - u0x, d1y = u2y - u0y;
+            if (flags & HF_RAY_DPDUV) {
+                const float det = d0x * d1y - d0y * d1x;
+                if (det != 0.f) {
+                    const float r = 1.0f / det;
+                    const float k11 = d1y * r, k12 = -d1x * r, k21 = -d0y * r, k22 = d0x * r;
+                    a_e1 = mk3(a_e1.x + a_du.x * k11 + a_dv.x * k12, a_e1.y + a_du.y * k11 + a_dv.y * k12, a_e1.z + a_du.z * k11 + a_dv.z * k12);
+                    a_e2 = mk3(a_e2.x + a_du.x * k21 + a_dv.x * k22, a_e2.y + a_du.y * k21 + a_dv.y * k22, a_e2.z + a_du.z * k21 + a_dv.z * k22);
+                }
+            }
+
+            const float b1 = u, b2 = v, b0 = 1.f - u - v;
+            float wz;       // z component of the adjoint that is distributed with the barycentrics
+            if (flags & HF_RAY_FOLLOWSHAPE) {
+                // mesh.cpp:728-729, 751-752: barycentrics detached, t = sqrt(|p-o|^2/|d|^2)
+                const f3 po = mk3(p0.x * b0 + p1.x * b1 + p2.x * b2, p0.y * b0 + p1.y * b1 + p2.y * b2, p0.z * b0 + p1.z * b1 + p2.z * b2);
+                const f3 pw = xform_point(P.to_world, po);
+                const f3 rel = sub3(pw, ow);
+                const float dd = dot3(dw, dw);
+                const float tt = sqrtf(dot3(rel, rel) / dd);
+                if (tt > 0.f) {
+                    const float k = a_t / (tt * dd);
+                    const f3 extra = lin_T(P.to_world, mk3(rel.x * k, rel.y * k, rel.z * k));
+                    a_p = mk3(a_p.x + extra.x, a_p.y + extra.y, a_p.z + extra.z);
+                }
+                wz = a_p.z;
+            } else {
+                const float a_tt = a_t + dot3(d, a_p);
+                const float a_u = d0x * a_uvx + d0y * a_uvy;
+                const float a_v = d1x * a_uvx + d1y * a_uvy;
+                const f3 pvec = cross3(d, e2);
+                const float det = dot3(e1, pvec);
+                const f3 de1 = cross3(d, e1);
+                wz = (-a_tt * c.z - a_u * pvec.z + a_v * de1.z) / det;
+            }
+            g0 = P.mh * (wz * b0 - (a_e1.z + a_e2.z));
+            g1 = P.mh * (wz * b1 + a_e1.z);
+            g2 = P.mh * (wz * b2 + a_e2.z);
+        }
+        // whole warp participates (inactive lanes pass valid = false)
+        warp_aggregated_add(grad, i0, g0, valid);
+        warp_aggregated_add(grad, i1, g1, valid);
+        warp_aggregated_add(grad, i2, g2, valid);
+    }
+}
+
+cudaError_t hf_launch_backward(const HfParams &P, const HfLaunchInfo &li, const hf_rays &rays, const hf_prelim &pi,
+                               const hf_si_adj &adj, uint32_t flags, float *grad, size_t n, cudaStream_t s) {
+    if (n == 0 || (flags & HF_RAY_DETACHSHAPE)) return cudaSuccess;   // mesh.cpp:713-717
+    hf_backward_kernel<<<hf_grid_for(n, li.num_sms, 8), HF_BLOCK, 0, s>>>(P, rays, pi, adj, flags, grad, n);
+    return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------------------------------
+// Adam (src/python/python/ad/optimizers.py:263-302), fp32, op order of the LLVM lowering
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ void adam_one(float &p, float g, float &m, float &v, float lr_t, float b1, float b2,
+                                         float omb1, float omb2, float eps, int mask) {
+    float m_t = b1 * m + omb1 * g;
+    float v_t = b2 * v + omb2 * (g * g);
+    const bool nz = g != 0.f;
+    if (mask && !nz) { m_t = m; v_t = v; }
+    m = m_t; v = v_t;
+    float step = __fdiv_rn(lr_t * m_t, __fsqrt_rn(v_t) + eps);
+    if (mask && !nz) step = 0.f;
+    p = p - step;
+}
+
+__global__ void __launch_bounds__(256)
+hf_adam_kernel(float *__restrict__ p, const float *__restrict__ g, float *__restrict__ m, float *__restrict__ v,
+               const size_t n, const float lr_t, const float b1, const float b2, const float omb1, const float omb2,
+               const float eps, const int mask) {
+    const size_t n4 = n / 4;
+    float4 *p4 = reinterpret_cast<float4 *>(p), *m4 = reinterpret_cast<float4 *>(m), *v4 = reinterpret_cast<float4 *>(v);
+    const float4 *g4 = reinterpret_cast<const float4 *>(g);
+    for (size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (size_t) gridDim.x * blockDim.x) {
+        float4 pp = p4[i], gg = g4[i], mm = m4[i], vv = v4[i];
+        adam_one(pp.x, gg.x, mm.x, vv.x, lr_t, b1, b2, omb1, omb2, eps, mask);
+        adam_one(pp.y, gg.y, mm.y, vv.y, lr_t, b1, b2, omb1, omb2, eps, mask);
+        adam_one(pp.z, gg.z, mm.z, vv.z, lr_t, b1, b2, omb1, omb2, eps, mask);
+        adam_one(pp.w, gg.w, mm.w, vv.w, lr_t, b1, b2, omb1, omb2, eps, mask);
+        p4[i] = pp; m4[i] = mm; v4[i] = vv;
+    }
+    for (size_t i = n4 * 4 + (size_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t) gridDim.x * blockDim.x) {
+        float pp = p[i], mm = m[i], vv = v[i];
+        adam_one(pp, g[i], mm, vv, lr_t, b1, b2, omb1, omb2, eps, mask);
+        p[i] = pp; m[i] = mm; v[i] = vv;
+    }
+}
+
+cudaError_t hf_launch_adam(float *p, const float *g, float *m, float *v, size_t n, float lr_t, float beta1,
+                           float beta2, float omb1, float omb2, float eps, int mask_updates, int num_sms, cudaStream_t s) {
+    if (n == 0) return cudaSuccess;
+    size_t blocks = (n / 4 + 255) / 256;
+    size_t cap = (size_t) num_sms * 8;
+    int grid = (int) (blocks < cap ? (blocks ? blocks : 1) : cap);
+    hf_adam_kernel<<<grid, 256, 0, s>>>(p, g, m, v, n, lr_t, beta1, beta2, omb1, omb2, eps, mask_updates);
+    return cudaGetLastError();
+}
