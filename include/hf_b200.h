@@ -137,6 +137,11 @@ int hf_set_grad_enabled(hf_ctx *ctx, int enabled);
 int hf_bbox(hf_ctx *ctx, float out_min_max[6]);          /* shape.h:253 (synchronises) */
 int hf_primitive_count(hf_ctx *ctx, uint32_t *count);    /* shape.h:432: 2*(W-1)*(H-1) */
 int hf_size(hf_ctx *ctx, uint32_t *width, uint32_t *height);
+/* acceleration data of the shape (what Embree / OptiX hold for the reference, shape.h:446-474): level l in
+ * 1..levels covers 2^l x 2^l cells per node; *d_nodes = device pointer to width*height interleaved (min,max)
+ * pairs of z = max_height*h, row-major. levels/width/height/d_nodes are each nullable. */
+int hf_pyramid_level(hf_ctx *ctx, uint32_t level, uint32_t *levels, uint32_t *width, uint32_t *height,
+                     const float **d_nodes);
 
 /* shape.h:137-138 ray_intersect_preliminary */
 int hf_ray_intersect_preliminary(hf_ctx *ctx, const hf_rays *rays, const hf_prelim *out, size_t n, void *stream);

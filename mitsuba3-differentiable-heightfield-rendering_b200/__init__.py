@@ -127,6 +127,7 @@ def _load():
         "hf_bbox": [vp, _f32p],
         "hf_primitive_count": [vp, C.POINTER(u32)],
         "hf_size": [vp, C.POINTER(u32), C.POINTER(u32)],
+        "hf_pyramid_level": [vp, u32, C.POINTER(u32), C.POINTER(u32), C.POINTER(u32), C.POINTER(vp)],
         "hf_ray_intersect_preliminary": [vp, C.POINTER(_Rays), C.POINTER(_Prelim), sz, vp],
         "hf_ray_intersect_preliminary_counted": [vp, C.POINTER(_Rays), C.POINTER(_Prelim), sz, vp],
         "hf_stats_get": [vp, C.POINTER(_Stats), C.c_int],
@@ -392,6 +393,19 @@ class Heightfield:
         n = C.c_uint32()
         _check(_load().hf_primitive_count(self._ctx, C.byref(n)))
         return n.value
+
+    def pyramid_levels(self):
+        """Acceleration data as a list of (h, w, 2) (min,max) device tensors for levels 1..Ltop (zero-copy views)."""
+        L = _load()
+        nl = C.c_uint32()
+        _check(L.hf_pyramid_level(self._ctx, 0, C.byref(nl), None, None, None))
+        out = []
+        for l in range(1, nl.value + 1):
+            w, h, ptr = C.c_uint32(), C.c_uint32(), C.c_void_p()
+            _check(L.hf_pyramid_level(self._ctx, l, None, C.byref(w), C.byref(h), C.byref(ptr)))
+            with torch.cuda.device(self.device):
+                out.append(torch.as_tensor(_DevView(ptr.value, (h.value, w.value, 2), self), device=self.device))
+        return out
 
     def _mask(self, active, n):
         if active is None:

@@ -347,6 +347,20 @@ extern "C" int hf_size(hf_ctx *c, uint32_t *w, uint32_t *h) {
     return HF_OK;
 }
 
+extern "C" int hf_pyramid_level(hf_ctx *c, uint32_t level, uint32_t *levels, uint32_t *w, uint32_t *h, const float **d_nodes) {
+    CHECK_CTX(c);
+    const HfParams &P = c->P;
+    if (levels) *levels = (uint32_t) P.Ltop;
+    if (level < 1 || level > (uint32_t) P.Ltop) {
+        if (w || h || d_nodes) return fail(HF_ERR_INVALID, "pyramid level %u out of range 1..%d", level, P.Ltop);
+        return HF_OK;
+    }
+    if (w) *w = (uint32_t) P.lvl_w[level];
+    if (h) *h = (uint32_t) ((P.NY + (1 << level) - 1) >> level);
+    if (d_nodes) *d_nodes = reinterpret_cast<const float *>(c->d_pyr + P.lvl_off[level]);
+    return HF_OK;
+}
+
 static int check_rays(const hf_rays *r) {
     if (!r) return fail(HF_ERR_INVALID, "null rays");
     if (!r->ox || !r->oy || !r->oz || !r->dx || !r->dy || !r->dz || !r->maxt) return fail(HF_ERR_INVALID, "ray batch has a null component");

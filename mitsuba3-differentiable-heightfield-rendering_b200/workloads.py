@@ -73,7 +73,8 @@ def fbm_heights(n: int, octaves: int = 8, seed: int = 0xC3, base_freq: float = 4
 
 # ---- cameras ----------------------------------------------------------------------------------
 def _normalize(v):
-    return v / math.sqrt(sum(c * c for c in v))
+    n = math.sqrt(sum(c * c for c in v))
+    return tuple(c / n for c in v)
 
 
 def _cross(a, b):

@@ -1,0 +1,409 @@
+"""GPU parity tests: the sm_100a kernels, called through the C ABI (include/hf_b200.h via the ctypes host mirror),
+against the CPU oracle on identical seeded inputs.
+
+Tolerances (BASELINE.json north star): hit/miss mask and prim_index bit-exact away from cell-edge ties; t and
+normals within 1e-5 relative; height gradients within 1e-4 relative. Because the kernels use the oracle's op order
+(explicit fmaf, IEEE div/sqrt, no contraction) the forward quantities are in fact expected to be BIT-IDENTICAL and
+the tests assert that; only the gradient (fp32 atomics in arbitrary order vs fp64 accumulation) needs a tolerance.
+
+The heightfield level is "parity unpinned" (the plugin is absent from the reference snapshot); the
+triangle level is pinned by the reference's known answers (test_mesh.py test10/15/16), repeated here on the GPU.
+"""
+import numpy as np
+import pytest
+import torch
+
+from util import adversarial_rays, random_heights, random_rays
+
+pytestmark = pytest.mark.gpu
+f32 = np.float32
+
+
+@pytest.fixture(scope="module")
+def hf():
+    import hfb200
+    return hfb200
+
+
+def _mk(hf, oracle, h, mh=1.0, to_world=None, flip=False):
+    props = {"type": "heightfield", "heights": torch.from_numpy(np.ascontiguousarray(h)), "max_height": mh,
+             "flip_normals": flip}
+    if to_world is not None:
+        props["to_world"] = to_world
+    g = hf.load_dict(props)
+    c = oracle.OracleHeightfield(h, mh, to_world=to_world, flip_normals=flip)
+    return g, c
+
+
+def _rays(hf, oracle, o, d, maxt=None, active=None):
+    ray = hf.Ray3f(torch.from_numpy(o.T.copy()), torch.from_numpy(d.T.copy()),
+                   None if maxt is None else torch.from_numpy(maxt))
+    return ray, oracle.Rays(o, d, maxt, active)
+
+
+def _np(t):
+    return t.detach().cpu().numpy()
+
+
+def _same_bits(a, b):
+    a = np.asarray(a, f32); b = np.asarray(b, f32)
+    return (a.view(np.uint32) == b.view(np.uint32)) | (np.isnan(a) & np.isnan(b))
+
+
+SI_MAP = {"p": ("px", "py", "pz"), "n": ("nx", "ny", "nz"), "uv": ("uvx", "uvy"), "dp_du": ("dpdu_x", "dpdu_y", "dpdu_z"),
+          "dp_dv": ("dpdv_x", "dpdv_y", "dpdv_z"), "sh_n": ("shn_x", "shn_y", "shn_z"), "sh_s": ("shs_x", "shs_y", "shs_z"),
+          "sh_t": ("sht_x", "sht_y", "sht_z"), "wi": ("wi_x", "wi_y", "wi_z")}
+
+
+def _si_dict(si):
+    out = {"t": _np(si.t)}
+    for k, names in SI_MAP.items():
+        a = _np(getattr(si, k))
+        for i, nm in enumerate(names):
+            out[nm] = a[i]
+    return out
+
+
+def _adj_np(adj):
+    out = {}
+    for k, v in adj.items():
+        v = np.asarray(v, f32)
+        if k == "t":
+            out["t"] = v
+        else:
+            for i, nm in enumerate(SI_MAP[k]):
+                out[nm] = v[i]
+    return out
+
+
+# ---- acceleration data -------------------------------------------------------------------------------
+@pytest.mark.parametrize("H,W", [(2, 2), (3, 2), (5, 7), (37, 50), (64, 65), (129, 200), (257, 1025)])
+def test_pyramid_bit_exact(hf, oracle, H, W):
+    rng = np.random.default_rng(H * 7 + W)
+    h = rng.uniform(-1, 2, (H, W)).astype(f32)
+    g, c = _mk(hf, oracle, h, -0.8)
+    lv_g, lv_c = g.pyramid_levels(), c.pyramid_levels()
+    assert len(lv_g) == len(lv_c)
+    for a, b in zip(lv_g, lv_c):
+        assert tuple(a.shape) == b.shape
+        assert np.array_equal(_np(a), b)
+    assert np.array_equal(g.bbox(), c.bbox())
+    assert g.primitive_count() == c.primitive_count() == 2 * (H - 1) * (W - 1)
+
+
+# ---- the reference's known answers, on the GPU ---------------------------------------------------------
+def test_test10_known_answers(hf, oracle):
+    """src/render/tests/test_mesh.py:257-292 on the flat 2x2 field (== rectangle.obj)."""
+    g, _ = _mk(hf, oracle, np.zeros((2, 2), f32))
+    ray = hf.Ray3f(torch.tensor([[-0.3, 0.3], [-0.3, 0.3], [-10.0, -10.0]]), torch.tensor([[0.0, 0.0], [0.0, 0.0], [1.0, 1.0]]))
+    pi = g.ray_intersect_preliminary(ray)
+    assert np.allclose(_np(pi.t), 10)
+    assert _np(pi.prim_index).tolist() == [0, 1]
+    assert np.allclose(_np(pi.prim_uv).T, [[0.35, 0.3], [0.3, 0.35]])
+    si = pi.compute_surface_interaction(ray)
+    assert np.allclose(_np(si.p).T, [[-0.3, -0.3, 0], [0.3, 0.3, 0]], atol=1e-6)
+    assert np.allclose(_np(si.uv).T, [[0.35, 0.35], [0.65, 0.65]])
+    assert np.allclose(_np(si.dp_du).T, [[2, 0, 0]] * 2) and np.allclose(_np(si.dp_dv).T, [[0, 2, 0]] * 2)
+    assert np.allclose(_np(si.n).T, [[0, 0, 1]] * 2)
+    assert g.ray_test(ray).tolist() == [True, True]
+
+
+def test_test16_known_answers(hf, oracle):
+    """test_mesh.py:536-671 (see tests/test_oracle.py::test_test16_params_backward for the vertex mapping)."""
+    g, _ = _mk(hf, oracle, np.zeros((2, 2), f32))
+    ray = hf.Ray3f(torch.tensor([[0.99999], [0.99999], [-10.0]]), torch.tensor([[0.0], [0.0], [1.0]]))
+    pi = g.ray_intersect_preliminary(ray)
+
+    def grad(adj):
+        g.zero_grad()
+        g.backward(ray, pi, adj)
+        return _np(g.grad).ravel().copy()
+
+    z1, o1 = torch.zeros(3, 1), torch.ones(1)
+    assert np.allclose(grad({"t": o1}), [0, 0, 0, 1], atol=1e-5)
+    assert np.allclose(grad({"p": torch.tensor([[0.0], [0.0], [1.0]])}), [0, 0, 0, 1], atol=1e-5)
+    assert np.allclose(grad({"n": torch.tensor([[1.0], [0.0], [0.0]])}), [0, 0, 0.5, -0.5], atol=1e-5)
+    assert np.allclose(grad({"n": torch.tensor([[0.0], [1.0], [0.0]])}), [0, 0.5, 0, -0.5], atol=1e-5)
+    assert np.allclose(grad({"dp_du": torch.tensor([[0.0], [0.0], [1.0]])}), [0, 0, -1, 1], atol=1e-5)
+    assert np.allclose(grad({"dp_dv": torch.tensor([[0.0], [0.0], [1.0]])}), [0, -1, 0, 1], atol=1e-5)
+    assert np.all(grad({"p": z1}) == 0)
+
+
+# ---- forward parity -----------------------------------------------------------------------------------
+CASES = [(2, 2, "noise", None), (3, 2, "noise", None), (5, 7, "smooth", None), (17, 17, "smooth", "affine"),
+         (33, 20, "noise", None), (64, 65, "smooth", "affine"), (12, 12, "flat", None), (256, 256, "smooth", None),
+         (100, 517, "noise", "affine")]
+AFFINE = np.array([[1.5 * np.cos(0.4), -np.sin(0.4), 0.1, 0.3], [1.5 * np.sin(0.4), np.cos(0.4), 0.0, -0.2],
+                   [0.0, 0.2, 2.0, 0.5]], f32)
+
+
+@pytest.mark.parametrize("H,W,kind,xf", CASES)
+def test_forward_bit_exact_vs_oracle(hf, oracle, H, W, kind, xf):
+    rng = np.random.default_rng(H * 131 + W)
+    h = random_heights(rng, H, W, kind)
+    tw = AFFINE if xf else None
+    g, c = _mk(hf, oracle, h, 0.7, to_world=tw, flip=(H % 2 == 1))
+    o, d = random_rays(rng, 20000)
+    ao, ad = adversarial_rays(W, H, 0.7)
+    o, d = np.concatenate([o, ao]), np.concatenate([d, ad])
+    if tw is not None:
+        o = (o @ tw[:, :3].T + tw[:, 3]).astype(f32); d = (d @ tw[:, :3].T).astype(f32)
+    n = o.shape[0]
+    maxt = np.where(rng.uniform(size=n) < 0.15, rng.uniform(0.5, 4, n), np.inf).astype(f32)
+    active = rng.uniform(size=n) < 0.9
+    ray, cr = _rays(hf, oracle, o, d, maxt, active)
+    act_t = torch.from_numpy(active)
+
+    pc = c.ray_intersect_preliminary(cr)
+    pg = g.ray_intersect_preliminary(ray, active=act_t)
+    t, u, v, prim = _np(pg.t), _np(pg.prim_uv[0]), _np(pg.prim_uv[1]), _np(pg.prim_index).view(np.uint32)
+    same = _same_bits(t, pc.t) & _same_bits(u, pc.u) & _same_bits(v, pc.v) & (prim == pc.prim_index)
+    assert same.all(), f"{(~same).sum()} of {n} preliminary intersections differ from the oracle DDA: {np.nonzero(~same)[0][:8]}"
+    assert not np.isfinite(t[~active]).any()
+    assert np.array_equal(_np(g.ray_test(ray, active=act_t)), pc.valid())
+
+    # against brute force: identical away from cell-edge ties (the north-star contract)
+    if H * W <= 70 * 70:
+        pb = c.ray_intersect_preliminary(cr, brute=True)
+        both = np.isfinite(t) & pb.valid()
+        diff = (np.isfinite(t) != pb.valid()) | (both & ((prim != pb.prim_index) | (t != pb.t)))
+        edge = lambda uu, vv: np.minimum.reduce([np.abs(uu), np.abs(vv), np.abs(1 - uu - vv)])
+        near = (np.isfinite(t) & (edge(u, v) < 1e-5)) | (pb.valid() & (edge(pb.u, pb.v) < 1e-5))
+        with np.errstate(invalid="ignore"):
+            tie = both & (np.abs(t - pb.t) <= 4 * np.spacing(np.abs(pb.t)))
+        assert (diff & ~near & ~tie).sum() == 0
+
+    for flags in (oracle.RF_ALL, oracle.RF_UV, oracle.RF_ALL | oracle.RF_FOLLOWSHAPE):
+        sc = c.compute_surface_interaction(cr, pc, ray_flags=flags)
+        sg = _si_dict(g.compute_surface_interaction(ray, pg, ray_flags=flags, active=act_t))
+        for k in sc:
+            ok = _same_bits(sg[k], sc[k])
+            assert ok.all(), f"si.{k} differs in {(~ok).sum()} lanes (flags={flags:#x}); first {np.nonzero(~ok)[0][:5]}"
+    # fused ray_intersect == preliminary + compute_surface_interaction
+    sf, pf = g.ray_intersect(ray, active=act_t, return_prelim=True)
+    sfd, s2 = _si_dict(sf), _si_dict(g.compute_surface_interaction(ray, pg, active=act_t))
+    for k in s2:
+        assert _same_bits(sfd[k], s2[k]).all(), k
+    assert torch.equal(pf.t, pg.t) and torch.equal(pf.prim_index, pg.prim_index)
+
+
+def test_c1_config_parity(hf, oracle):
+    """BASELINE.json configs[0]: 256^2 sine heightfield, 256^2 image, 1 spp primary rays + d/d(heights)."""
+    from hfb200 import workloads as wl
+    h = wl.sine_heights(256)
+    cam = wl.CONFIGS["C1"]["camera"]
+    o, d = wl.camera_rays(cam["origin"], cam["target"], cam["up"], cam["fov"], 256, 256, 1, jitter=False)
+    n = o.shape[1]
+    g, c = _mk(hf, oracle, h.numpy(), 0.25)
+    ray = hf.Ray3f(o, d)
+    cr = oracle.Rays(o.numpy().T, d.numpy().T)
+    pc = c.ray_intersect_preliminary(cr)
+    si, pg = g.ray_intersect(ray, return_prelim=True)
+    assert _same_bits(_np(pg.t), pc.t).all() and np.array_equal(_np(pg.prim_index).view(np.uint32), pc.prim_index)
+    assert 0.85 < pc.valid().mean() < 1.0
+    adj = wl.hashed_adjoints(n, seed=1)
+    g.zero_grad(); g.backward(ray, pg, adj)
+    ref = c.backward(cr, pc, _adj_np({k: v.numpy() for k, v in adj.items()}), literal=True)
+    got = _np(g.grad).astype(np.float64)
+    assert np.linalg.norm(got - ref) <= 1e-4 * np.linalg.norm(ref)
+    big = np.abs(ref) > 1e-3 * np.abs(ref).max()
+    assert np.max(np.abs(got - ref)[big] / np.abs(ref)[big]) < 1e-4
+    # d(image)/d(heights) for Lambert shading max(0, n.l): the image adjoint of a unit image gradient
+    l = np.array([0.3, 0.2, 1.0]); l /= np.linalg.norm(l)
+    nrm = _np(si.n)
+    lit = (nrm * l[:, None].astype(f32)).sum(0) > 0
+    adj_n = torch.from_numpy((l[:, None] * lit[None, :]).astype(f32))
+    g.zero_grad(); g.backward(ray, pg, {"n": adj_n})
+    ref = c.backward(cr, pc, _adj_np({"n": adj_n.numpy()}), literal=True)
+    got = _np(g.grad).astype(np.float64)
+    assert np.linalg.norm(got - ref) <= 1e-4 * np.linalg.norm(ref)
+
+
+# ---- backward parity ----------------------------------------------------------------------------------
+@pytest.mark.parametrize("H,W,flags_extra,xf", [(9, 11, 0, None), (40, 33, 0, "affine"), (40, 33, 0x80, "affine"),
+                                                (128, 128, 0, None), (6, 7, 0, "affine")])
+def test_backward_vs_oracle_fp64(hf, oracle, H, W, flags_extra, xf):
+    rng = np.random.default_rng(H + 1000 * W + flags_extra)
+    h = random_heights(rng, H, W)
+    tw = AFFINE if xf else None
+    g, c = _mk(hf, oracle, h, 0.6, to_world=tw, flip=(W % 2 == 1))
+    o, d = random_rays(rng, 50000)
+    if tw is not None:
+        o = (o @ tw[:, :3].T + tw[:, 3]).astype(f32); d = (d @ tw[:, :3].T).astype(f32)
+    n = o.shape[0]
+    ray, cr = _rays(hf, oracle, o, d)
+    pg = g.ray_intersect_preliminary(ray)
+    pc = c.ray_intersect_preliminary(cr)
+    adj = {"t": rng.normal(size=n).astype(f32), "p": rng.normal(size=(3, n)).astype(f32), "n": rng.normal(size=(3, n)).astype(f32),
+           "uv": rng.normal(size=(2, n)).astype(f32), "dp_du": rng.normal(size=(3, n)).astype(f32),
+           "dp_dv": rng.normal(size=(3, n)).astype(f32)}
+    flags = oracle.RF_ALL | flags_extra
+    g.zero_grad()
+    g.backward(ray, pg, {k: torch.from_numpy(v) for k, v in adj.items()}, ray_flags=flags)
+    got = _np(g.grad).astype(np.float64)
+    for literal in (True, False):
+        ref = c.backward(cr, pc, _adj_np(adj), ray_flags=flags, literal=literal)
+        assert np.linalg.norm(got - ref) <= 1e-4 * np.linalg.norm(ref), (literal, np.linalg.norm(got - ref) / np.linalg.norm(ref))
+    big = np.abs(ref) > 1e-3 * np.abs(ref).max()
+    assert np.max(np.abs(got - ref)[big] / np.abs(ref)[big]) < 1e-4
+    # DetachShape: no gradient at all (mesh.cpp:713-717)
+    g.zero_grad()
+    g.backward(ray, pg, {"t": torch.from_numpy(adj["t"])}, ray_flags=oracle.RF_ALL | oracle.RF_DETACHSHAPE)
+    assert float(g.grad.abs().max()) == 0.0
+    # gradient accumulates across calls, zero_grad resets
+    g.backward(ray, pg, {"t": torch.from_numpy(adj["t"])})
+    g1 = g.grad.clone()
+    g.backward(ray, pg, {"t": torch.from_numpy(adj["t"])})
+    assert torch.allclose(g.grad, 2 * g1, rtol=1e-5, atol=1e-6 * float(g1.abs().max()))
+
+
+def test_backward_heavy_contention(hf, oracle):
+    """64 spp onto a coarse field: every warp hits 1-2 cells (the warp-aggregation path)."""
+    from hfb200 import workloads as wl
+    rng = np.random.default_rng(4)
+    h = random_heights(rng, 17, 17)
+    g, c = _mk(hf, oracle, h, 0.3)
+    o, d = wl.camera_rays((0, -2.5, 1.8), (0, 0, 0), (0, 0, 1), 40.0, 64, 64, 64, seed=3)
+    n = o.shape[1]
+    ray = hf.Ray3f(o, d)
+    cr = oracle.Rays(o.numpy().T, d.numpy().T)
+    pg = g.ray_intersect_preliminary(ray); pc = c.ray_intersect_preliminary(cr)
+    assert _same_bits(_np(pg.t), pc.t).all()
+    adj = wl.hashed_adjoints(n, seed=9)
+    g.zero_grad(); g.backward(ray, pg, adj)
+    ref = c.backward(cr, pc, _adj_np({k: v.numpy() for k, v in adj.items()}), literal=False)
+    got = _np(g.grad).astype(np.float64)
+    assert np.linalg.norm(got - ref) <= 1e-4 * np.linalg.norm(ref)
+
+
+# ---- optimiser + parameter updates ----------------------------------------------------------------------
+def test_adam_bit_exact_and_traverse(hf, oracle):
+    rng = np.random.default_rng(12)
+    H, W = 33, 47
+    h = random_heights(rng, H, W)
+    g, c = _mk(hf, oracle, h, 0.5)
+    params = hf.traverse(g)
+    assert set(params) == {"heights", "max_height", "to_world"}
+    opt = hf.Adam(lr=1e-2, params=params)
+    p = h.copy(); m = np.zeros_like(p); v = np.zeros_like(p)
+    for t in range(1, 5):
+        gr = rng.normal(size=(H, W)).astype(f32); gr[::3, ::2] = 0
+        g.grad.copy_(torch.from_numpy(gr))
+        opt.mask_updates = (t % 2 == 0)
+        opt.step()
+        keys = params.update()
+        assert keys == ["heights"]
+        oracle.adam_step(p, gr, m, v, lr=1e-2, t=t, mask_updates=(t % 2 == 0))
+        assert np.array_equal(_np(g.heights), p)
+    # the acceleration data follows the update
+    c2 = oracle.OracleHeightfield(p, 0.5)
+    for a, b in zip(g.pyramid_levels(), c2.pyramid_levels()):
+        assert np.array_equal(_np(a), b)
+    # parameter update through SceneParameters (util.py:185-232)
+    params["heights"] = torch.from_numpy(h)
+    params["max_height"] = 0.25
+    params.update()
+    c3 = oracle.OracleHeightfield(h, 0.25)
+    assert np.array_equal(g.bbox(), c3.bbox())
+    with pytest.raises(hf.HeightfieldError):
+        params["heights"] = torch.zeros(3, 3)
+
+
+def test_error_behaviour(hf, oracle):
+    with pytest.raises(hf.HeightfieldError):
+        hf.load_dict({"type": "sphere"})
+    with pytest.raises(hf.HeightfieldError):
+        hf.load_dict({"type": "heightfield"})
+    with pytest.raises(hf.HeightfieldError):
+        hf.load_dict({"type": "heightfield", "heights": torch.zeros(1, 5)})
+    with pytest.raises(hf.HeightfieldError):
+        hf.load_dict({"type": "heightfield", "heights": torch.zeros(4, 4), "bogus": 1})
+    g, _ = _mk(hf, oracle, np.zeros((4, 4), f32))
+    ray = hf.Ray3f(torch.zeros(3, 4), torch.ones(3, 4))
+    pi = g.ray_intersect_preliminary(ray)
+    with pytest.raises(hf.HeightfieldError, match="DetachShape"):
+        g.compute_surface_interaction(ray, pi, ray_flags=0x80 | 0x100)
+    n0 = hf.Ray3f(torch.zeros(3, 0), torch.zeros(3, 0))
+    assert g.ray_intersect_preliminary(n0).t.numel() == 0       # empty batch
+
+
+# ---- host-buffer entry points (the llvm_ad_rgb caller's arrays live in host memory) -------------------------
+def test_host_api_matches_device_api(hf, oracle):
+    from hfb200 import workloads as wl
+    rng = np.random.default_rng(21)
+    H, W = 200, 150
+    h = random_heights(rng, H, W)
+    g, c = _mk(hf, oracle, h, 0.4)
+    n = (1 << 21) + 12345            # more than one staging chunk, ragged tail
+    o, d = wl.hemisphere_rays(n, seed=5)
+    adj = wl.hashed_adjoints(n, seed=2)
+    ray = hf.Ray3f(o, d)
+    si, pi = g.ray_intersect(ray, return_prelim=True)
+    g.zero_grad(); g.backward(ray, pi, adj)
+    grad_dev = g.grad.clone()
+
+    pin = lambda x: x.contiguous().pin_memory()
+    hr = {"ox": pin(o[0]), "oy": pin(o[1]), "oz": pin(o[2]), "dx": pin(d[0]), "dy": pin(d[1]), "dz": pin(d[2]),
+          "maxt": pin(torch.full((n,), float("inf")))}
+    ha = {"t": pin(adj["t"]), "px": pin(adj["p"][0]), "py": pin(adj["p"][1]), "pz": pin(adj["p"][2]),
+          "nx": pin(adj["n"][0]), "ny": pin(adj["n"][1]), "nz": pin(adj["n"][2]), "uvx": pin(adj["uv"][0]), "uvy": pin(adj["uv"][1])}
+    hs = {k: torch.empty(n).pin_memory() for k in ("t", "px", "py", "pz", "nx", "ny", "nz", "uvx", "uvy")}
+    hp = {"t": torch.empty(n).pin_memory(), "u": torch.empty(n).pin_memory(), "v": torch.empty(n).pin_memory(),
+          "prim_index": torch.empty(n, dtype=torch.int32).pin_memory()}
+    hg = torch.empty(H, W).pin_memory()
+    g.zero_grad()
+    torch.cuda.synchronize()
+    g.forward_backward_host(hr, ha, hs, hg, n, h_prelim=hp)
+    assert torch.equal(hp["t"], pi.t.cpu()) and torch.equal(hp["prim_index"], pi.prim_index.cpu())
+    assert torch.equal(hs["px"], si.p[0].cpu()) and torch.equal(hs["nz"], si.n[2].cpu()) and torch.equal(hs["uvy"], si.uv[1].cpu())
+    assert torch.allclose(hg, grad_dev.cpu(), rtol=1e-4, atol=1e-5 * float(grad_dev.abs().max()))
+    # oracle spot check on a subset
+    idx = rng.choice(n, 20000, replace=False)
+    cr = oracle.Rays(o.numpy().T[idx], d.numpy().T[idx])
+    pc = c.ray_intersect_preliminary(cr)
+    assert _same_bits(hp["t"].numpy()[idx], pc.t).all()
+
+
+# ---- full-size properties (sizes the oracle cannot finish: size-independent invariants) -------------------------
+def test_full_size_invariants(hf, oracle):
+    """4096^2 heights (BASELINE.json C3 field), 4 M primary rays: p = o + t d, hits inside the bbox, ray_test ==
+    is_valid, backward linear in the adjoints, a sampled subset bit-exact against the oracle, sum rule for dt."""
+    from hfb200 import workloads as wl
+    dev = "cuda"
+    h = wl.fbm_heights(4096, octaves=8, seed=0xC3, device=dev)
+    g = hf.load_dict({"type": "heightfield", "heights": h, "max_height": 0.3})
+    o, d = wl.config_rays("C3", device=dev, image=256, spp=64, tile=32)
+    n = o.shape[1]
+    ray = hf.Ray3f(o, d)
+    si, pi = g.ray_intersect(ray, return_prelim=True)
+    ok = pi.is_valid()
+    assert 0.3 < float(ok.float().mean()) <= 1.0
+    assert torch.equal(g.ray_test(ray), ok)
+    onray = o + pi.t * d
+    err = ((si.p - onray).abs().max(0).values)[ok]
+    assert float(err.max()) < 2e-5 * 4
+    bb = g.bbox()
+    p_ok = si.p[:, ok]
+    assert bool((p_ok >= torch.tensor(bb[:3], device=dev)[:, None] - 1e-4).all()) and bool((p_ok <= torch.tensor(bb[3:], device=dev)[:, None] + 1e-4).all())
+    assert float((si.n[:, ok].norm(dim=0) - 1).abs().max()) < 1e-5
+    prim = pi.prim_index[ok].to(torch.int64) & 0xFFFFFFFF
+    assert int(prim.max()) < g.primitive_count()
+    # linearity + accumulation
+    adj = wl.hashed_adjoints(n, seed=1, device=dev)
+    g.zero_grad(); g.backward(ray, pi, adj); g1 = g.grad.clone()
+    g.zero_grad(); g.backward(ray, pi, {k: 2 * v for k, v in adj.items()}); g2 = g.grad.clone()
+    assert torch.allclose(g2, 2 * g1, rtol=1e-4, atol=1e-5 * float(g1.abs().max()))
+    # sampled subset against the oracle (rays are independent units)
+    idx = torch.randperm(n, device=dev)[:30000]
+    hc = h.cpu().numpy()
+    c = oracle.OracleHeightfield(hc, 0.3)
+    cr = oracle.Rays(o[:, idx].T.cpu().numpy(), d[:, idx].T.cpu().numpy())
+    pc = c.ray_intersect_preliminary(cr)
+    assert _same_bits(_np(pi.t[idx]), pc.t).all()
+    assert np.array_equal(_np(pi.prim_index[idx]).view(np.uint32), pc.prim_index)
+    # whole-batch gradient against the oracle's fp64 accumulation
+    cr_all = oracle.Rays(o.T.cpu().numpy(), d.T.cpu().numpy())
+    pc_all = oracle.Prelim(t=_np(pi.t), u=_np(pi.prim_uv[0]), v=_np(pi.prim_uv[1]), prim_index=_np(pi.prim_index).view(np.uint32))
+    ref = c.backward(cr_all, pc_all, _adj_np({k: v.cpu().numpy() for k, v in adj.items()}), literal=False)
+    got = _np(g1).astype(np.float64)
+    assert np.linalg.norm(got - ref) <= 1e-4 * np.linalg.norm(ref)
