@@ -1,0 +1,399 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the differentiable heightfield path.
+
+    python bench.py --gpus N --steps K --warmup W            (N > 1: launched by torch.distributed.run)
+    python bench.py --impl reference ...                       (CPU arm: the oracle port on the host cores)
+
+Metric (BASELINE.json): Mrays/s for forward + backward (intersection + surface interaction, then the adjoint
+w.r.t. the height texels) on the C3 workload: 4096^2 fBm heights, 1024^2 image x 64 spp = 67,108,864 primary rays
+per step. A step = zero_grad -> hf_ray_intersect (fused preliminary + surface interaction) -> hf_backward
+[-> one NCCL allreduce of the gradient grid when N > 1]. Rays are sharded by 32x32-pixel image tile across ranks, so
+total work is fixed as N grows ("strong" scaling, as BASELINE.json configs[2] states: one step at 1/2/4/8 B200).
+
+`value`   : device-resident inputs, CUDA-event timed, max over ranks.
+`e2e`     : the same step through the C ABI's host-buffer entry point (hf_forward_backward_host) with pinned HOST
+            arrays: H2D of rays + adjoints and D2H of the results + gradient are inside the timed region.
+`roofline`: the dominant kernel (hf_intersect_kernel<FUSED_SI>) against the measured HBM copy bandwidth, with the
+            ALGORITHMIC byte model of SURVEY.md 8(d): 76 B/ray of I/O + 8 B per pyramid node + 16 B per leaf cell
+            visited by the canonical traversal (counted on this batch by the counting variant of the kernel, which
+            tests/ pin to the oracle's counters).
+`cpu_baseline`: the oracle port (CPU restatement of the reference's llvm_ad_rgb arithmetic; the reference plugin
+            itself is absent from the snapshot and the reference cannot be built here -- SURVEY.md F1/F2) on all
+            host cores, on a bounded sample of the same rays.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import numpy as np
+import torch
+
+METRIC = "Mrays/s fwd+bwd heightfield intersect+grad (4096^2 heights, 1024^2 image x 64 spp)"
+B_IO_FWD = 76          # ray 28 + prelim 16 + si (p 12, n 12, uv 8)              SURVEY.md 8(d)
+B_IO_BWD = 92 + 16     # ray 28 + prelim 16 + adjoints 36 + 3 atomics 12, + re-fetch of the hit cell 16
+
+
+def peaks():
+    try:
+        p = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        return float(p["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.proc, self.path = index, None, None
+
+    def start(self):
+        try:
+            fd, self.path = tempfile.mkstemp(suffix=".csv")
+            os.close(fd)
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
+                                          "-lms", "100"], stdout=open(self.path, "w"), stderr=subprocess.DEVNULL)
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        if self.proc is None:
+            return out
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        for line in open(self.path):
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for name, val in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[5:9]):
+                if val.lower().startswith("active"):
+                    reasons.add(name)
+        os.unlink(self.path)
+        if sm:
+            out.update(sm_mhz=float(np.median(sm)), sm_max_mhz=float(max(mx)), reasons=sorted(reasons), samples=len(sm))
+        return out
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--heights", type=int, default=4096, help="heightfield side (C3: 4096)")
+    ap.add_argument("--image", type=int, default=1024, help="image side (C3: 1024)")
+    ap.add_argument("--spp", type=int, default=64)
+    ap.add_argument("--tile", type=int, default=32)
+    ap.add_argument("--cpu-sample", type=int, default=1 << 23, help="rays in the bounded CPU sample")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    return ap.parse_args()
+
+
+def workload_name(a):
+    if (a.heights, a.image, a.spp) == (4096, 1024, 64):
+        return "C3: 4096^2 fBm heightfield (8 octaves, seed 0xC3), 1024^2 image x 64 spp primary rays, fwd+bwd"
+    return f"reduced: {a.heights}^2 fBm heightfield, {a.image}^2 image x {a.spp} spp primary rays, fwd+bwd"
+
+
+def adj_to_c(adj):
+    return {"t": adj["t"], "px": adj["p"][0], "py": adj["p"][1], "pz": adj["p"][2], "nx": adj["n"][0], "ny": adj["n"][1],
+            "nz": adj["n"][2], "uvx": adj["uv"][0], "uvy": adj["uv"][1]}
+
+
+# ---------------------------------------------------------------------------------------------------------
+# CPU arm: the oracle port on the host cores (cpu_baseline leg and --impl reference)
+# ---------------------------------------------------------------------------------------------------------
+def cpu_sample(a, heights_np, n_sample):
+    """A bounded, strided sample of the step's rays (whole pixels: all spp of every k-th pixel)."""
+    from hfb200 import workloads as wl
+    cam = wl.CONFIGS["C3"]["camera"]
+    npix = a.image * a.image
+    want_pix = max(1, min(npix, n_sample // a.spp))
+    stride = max(1, npix // want_pix)
+    pix = torch.arange(0, npix, stride, dtype=torch.int64)[:want_pix]
+    o, d = wl.camera_rays(cam["origin"], cam["target"], cam["up"], cam["fov"], a.image, a.image, a.spp, seed=0, pixels=pix)
+    adj = wl.hashed_adjoints(o.shape[1], seed=1)
+    return o, d, adj
+
+
+def cpu_step(O, c, r, adj_np):
+    """One forward + backward pass of the oracle over the sample; returns seconds."""
+    t0 = time.perf_counter()
+    pi = c.ray_intersect_preliminary(r)
+    c.compute_surface_interaction(r, pi, ray_flags=O.RF_ALL, fields=("t", "px", "py", "pz", "nx", "ny", "nz", "uvx", "uvy"))
+    c.backward(r, pi, adj_np, ray_flags=O.RF_ALL, literal=False)
+    return time.perf_counter() - t0
+
+
+def run_cpu(a, heights_np, steps, warmup):
+    from oracle import hf_oracle as O
+    O.build()
+    cores = os.cpu_count() or 1
+    O.set_threads(cores)
+    o, d, adj = cpu_sample(a, heights_np, a.cpu_sample)
+    c = O.OracleHeightfield(heights_np, 0.3)
+    t0 = time.perf_counter(); c._pyramid(); t_pyr = time.perf_counter() - t0
+    r = O.Rays(o.numpy().T, d.numpy().T)
+    adj_np = {k: v.numpy() for k, v in adj_to_c(adj).items()}
+    for _ in range(warmup):
+        cpu_step(O, c, r, adj_np)
+    times = [cpu_step(O, c, r, adj_np) for _ in range(steps)]
+    n = r.n
+    return {"mrays": n / (sum(times) / len(times)) / 1e6, "best_mrays": n / min(times) / 1e6, "n": n, "cores": cores,
+            "threads": O.get_threads(), "ms_per_step": 1e3 * sum(times) / len(times), "pyramid_ms": 1e3 * t_pyr}
+
+
+def main_reference(a):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from hfb200 import workloads as wl
+    h = wl.fbm_heights(a.heights, octaves=8, seed=0xC3).numpy()
+    res = run_cpu(a, h, max(1, a.steps), max(1, min(a.warmup, 2)))
+    sample = f"{res['n']} rays = all {a.spp} spp of every k-th pixel of the {a.image}^2 image (1/{max(1, a.image * a.image * a.spp // res['n'])} of the step)"
+    line = {"impl": "reference", "metric": METRIC, "value": res["mrays"], "unit": "Mrays/s", "n_gpus": a.gpus, "steps": a.steps,
+            "warmup": a.warmup, "ms_per_step": res["ms_per_step"], "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic", "config": {"workload": workload_name(a), "sample": sample},
+            "cpu_baseline": {"value": res["mrays"], "unit": "Mrays/s", "cores": res["threads"], "kind": "port", "sample": sample,
+                             "note": "CPU restatement of the reference llvm_ad_rgb arithmetic (oracle/hf_oracle.c, OpenMP); the reference "
+                                     "plugin is absent from the snapshot and Mitsuba cannot be built here (SURVEY.md F1/F2)"},
+            "e2e": {"value": res["mrays"], "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+# ---------------------------------------------------------------------------------------------------------
+# GPU arm
+# ---------------------------------------------------------------------------------------------------------
+def main_ours(a):
+    import torch.distributed as dist
+    import hfb200
+    from hfb200 import workloads as wl
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the heightfield path has no CPU fallback (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+
+    # ---- workload (synthetic, identical on every rank; rays sharded by image tile) ----
+    h = wl.fbm_heights(a.heights, octaves=8, seed=0xC3, device=dev)
+    shape = hfb200.load_dict({"type": "heightfield", "heights": h, "max_height": 0.3}, device=dev)
+    cam = wl.CONFIGS["C3"]["camera"]
+    pix = wl.tile_pixels(a.image, a.image, a.tile, rank, world, device=dev)
+    o, d = wl.camera_rays(cam["origin"], cam["target"], cam["up"], cam["fov"], a.image, a.image, a.spp, seed=0, device=dev, pixels=pix)
+    n_local = o.shape[1]
+    n_total = a.image * a.image * a.spp
+    ray = hfb200.Ray3f(o, d)
+    adj = wl.hashed_adjoints(n_local, seed=1 + rank, device=dev)
+    adj_c = shape.prepare_adjoints(adj, n_local)
+    fields = ("t", "p", "n", "uv")
+    si = hfb200.SurfaceInteraction3f(n_local, dev, shape, fields)
+    pi = hfb200.PreliminaryIntersection3f(n_local, dev, shape)
+    del pix
+    torch.cuda.empty_cache()
+
+    if world > 1:
+        ids = [None] * world
+        dist.all_gather_object(ids, hfb200.comm_unique_id() if rank == 0 else None)
+        shape.comm_init(rank, world, ids[0])
+
+    ev = lambda: torch.cuda.Event(enable_timing=True)
+    k_fwd, k_bwd = [], []
+
+    def step(record=False):
+        shape.zero_grad()
+        if record:
+            e0, e1, e2 = ev(), ev(), ev()
+            e0.record()
+        shape.ray_intersect(ray, out=(si, pi))
+        if record:
+            e1.record()
+        shape.backward(ray, pi, adj_c)
+        if record:
+            e2.record()
+            k_fwd.append((e0, e1)); k_bwd.append((e1, e2))
+        if world > 1:
+            shape.allreduce_grad()
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        barrier()
+        s, e = ev(), ev()
+        s.record()
+        for _ in range(steps):
+            fn()
+        e.record()
+        barrier()
+        ms = torch.tensor([s.elapsed_time(e)], device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item())
+
+    for _ in range(max(a.warmup, 3)):
+        step()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+        time.sleep(0.3)
+    ms_total = timed(lambda: step(True), a.steps)
+    clocks = sampler.stop() if rank == 0 else None
+    ms_step = ms_total / a.steps
+    value = n_total / (ms_step * 1e-3) / 1e6
+    ms_fwd = float(np.mean([x.elapsed_time(y) for x, y in k_fwd]))
+    ms_bwd = float(np.mean([x.elapsed_time(y) for x, y in k_bwd]))
+    grad_checksum = float(shape.grad.double().abs().sum().item())
+    hits = float(pi.is_valid().float().mean().item())
+
+    # ---- secondary modes (extras; not the headline) ----
+    pi2 = hfb200.PreliminaryIntersection3f(n_local, dev, shape)
+    ms_isect = timed(lambda: shape.ray_intersect_preliminary(ray, out=pi2), a.steps) / a.steps
+    params = hfb200.traverse(shape)
+    opt = hfb200.Adam(lr=1e-3, params=params)
+
+    def full_step():
+        step()
+        opt.step()
+        params.update()
+
+    full_step()
+    ms_full = timed(full_step, a.steps) / a.steps
+    params["heights"] = h           # restore the field for the legs below
+    params.update()
+
+    # ---- traversal counters for the algorithmic byte model (outside every timed region) ----
+    shape.stats(reset=True)
+    shape.ray_intersect_preliminary(ray, counted=True, out=pi2)
+    st = shape.stats(reset=True)
+    cnt = torch.tensor([st["rays"], st["nodes"], st["leaves"], st["hits"]], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(cnt)
+    rays_c, nodes_c, leaves_c, hits_c = [float(x) for x in cnt.tolist()]
+    n_node, n_leaf = nodes_c / rays_c, leaves_c / rays_c
+    b_trav = 8.0 * n_node + 16.0 * n_leaf
+    del pi2
+
+    # ---- e2e: host buffers through hf_forward_backward_host ----
+    e2e = None
+    if not a.no_e2e:
+        e2e = run_e2e(a, shape, ray, adj, n_local, n_total, world, dev, timed)
+
+    if rank != 0:
+        if world > 1:
+            dist.barrier()
+            dist.destroy_process_group()
+        return
+
+    peak, peak_src = peaks()
+    bpr_fwd = B_IO_FWD + b_trav
+    ach_fwd = n_local * bpr_fwd / (ms_fwd * 1e-3) / 1e9
+    ach_bwd = n_local * (28 + 16 + 36 + hits * (12 + 16)) / (ms_bwd * 1e-3) / 1e9
+    line = {
+        "metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": a.steps, "warmup": max(a.warmup, 3),
+        "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": workload_name(a), "rays_per_step": n_total, "rays_per_gpu": n_local, "sharding": f"{a.tile}x{a.tile}-pixel image tiles, round-robin",
+                   "collective": "ncclAllReduce(grad 64 MiB fp32, sum) per step" if world > 1 else "none (1 GPU)",
+                   "l2": "inputs exceed L2 (ray + adjoint + output SoA > 5 GB per step vs 126 MB L2); no explicit flush",
+                   "si_fields": "t,p,n,uv", "hit_fraction": hits},
+        "clocks": clocks,
+        "gpu_launches": 2 * a.steps,
+        "kernels_per_step": ["hf_intersect_kernel<FUSED_SI>", "hf_backward_kernel"],
+        "roofline": {"bound": "hbm", "kernel": "hf_intersect_kernel<FUSED_SI>", "achieved": ach_fwd, "peak": peak, "unit": "GB/s",
+                     "frac": ach_fwd / peak, "traffic": None, "peak_source": peak_src, "bytes_per_ray": bpr_fwd,
+                     "model": f"76 B I/O + 8 B x {n_node:.2f} nodes + 16 B x {n_leaf:.2f} leaves (canonical traversal, counted on this batch)",
+                     "io_only_frac": n_local * B_IO_FWD / (ms_fwd * 1e-3) / 1e9 / peak, "kernel_ms": ms_fwd,
+                     "backward": {"kernel": "hf_backward_kernel", "kernel_ms": ms_bwd, "achieved": ach_bwd, "frac": ach_bwd / peak,
+                                  "bytes_per_ray": 80 + hits * 28}},
+        "extras": {"intersect_only_mrays": n_total / (ms_isect * 1e-3) / 1e6, "intersect_only_ms": ms_isect,
+                   "full_step_mrays": n_total / (ms_full * 1e-3) / 1e6, "full_step_ms": ms_full,
+                   "full_step": "zero_grad + intersect/SI + backward + allreduce + Adam + pyramid rebuild",
+                   "grad_abs_sum": grad_checksum, "mean_nodes_per_ray": n_node, "mean_leaves_per_ray": n_leaf},
+    }
+    if e2e is not None:
+        line["e2e"] = e2e
+    if world == 1 and not a.no_cpu:
+        res = run_cpu(a, h.cpu().numpy(), 2, 1)
+        line["cpu_baseline"] = {"value": res["best_mrays"], "unit": "Mrays/s", "cores": res["threads"], "kind": "port",
+                                "sample": f"{res['n']} rays (all {a.spp} spp of every k-th pixel), best of 2 after 1 warm-up",
+                                "ms": res["ms_per_step"]}
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def run_e2e(a, shape, ray, adj, n_local, n_total, world, dev, timed):
+    """The step through the reference-facing host-buffer call: every step copies the rays + adjoints host->device
+    from pinned memory and the preliminary intersection, t/p/n/uv and the gradient grid device->host."""
+    pin = lambda x: x.detach().to("cpu").contiguous().pin_memory()
+    hr = {"ox": pin(ray.o[0]), "oy": pin(ray.o[1]), "oz": pin(ray.o[2]), "dx": pin(ray.d[0]), "dy": pin(ray.d[1]), "dz": pin(ray.d[2]),
+          "maxt": pin(ray.maxt)}
+    ha = {k: pin(v) for k, v in adj_to_c(adj).items()}
+    names = ("t", "px", "py", "pz", "nx", "ny", "nz", "uvx", "uvy")
+    hs = {k: torch.empty(n_local, dtype=torch.float32).pin_memory() for k in names}
+    hp = {"t": torch.empty(n_local).pin_memory(), "u": torch.empty(n_local).pin_memory(), "v": torch.empty(n_local).pin_memory(),
+          "prim_index": torch.empty(n_local, dtype=torch.int32).pin_memory()}
+    hg = torch.empty(shape.H, shape.W, dtype=torch.float32).pin_memory()
+    h2d = n_local * 4 * (len(hr) + len(ha))
+    d2h = n_local * 4 * (len(hs) + len(hp)) + hg.numel() * 4
+
+    def step():
+        shape.zero_grad()
+        torch.cuda.current_stream().synchronize()
+        if world > 1:
+            # gradient must be summed before it is read back: forward+backward, allreduce, then the D2H of the grid
+            shape.forward_backward_host(hr, ha, hs, None, n_local, h_prelim=hp)
+            shape.allreduce_grad()
+            hg.copy_(shape.grad, non_blocking=True)
+            torch.cuda.current_stream().synchronize()
+        else:
+            shape.forward_backward_host(hr, ha, hs, hg, n_local, h_prelim=hp)
+
+    steps = max(2, min(a.steps, 5))
+    step()
+    ms = timed(step, steps) / steps
+    return {"value": n_total / (ms * 1e-3) / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+            "ms_per_step": ms, "steps": steps, "api": "hf_forward_backward_host (pinned host SoA in, host SoA + gradient grid out)",
+            "result_checksum": float(hg.double().abs().sum().item())}
+
+
+def main():
+    a = parse_args()
+    if a.impl == "reference":
+        main_reference(a)
+    else:
+        main_ours(a)
+
+
+if __name__ == "__main__":
+    main()

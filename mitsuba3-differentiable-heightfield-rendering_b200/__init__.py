@@ -228,12 +228,20 @@ class PreliminaryIntersection3f:
 
 
 class SurfaceInteraction3f:
-    def __init__(self, n, device, shape=None):
-        z = lambda r: torch.empty((r, n), dtype=torch.float32, device=device)
-        self.t = torch.empty(n, dtype=torch.float32, device=device)
-        self.p, self.n, self.uv = z(3), z(3), z(2)
-        self.dp_du, self.dp_dv = z(3), z(3)
-        self.sh_n, self.sh_s, self.sh_t, self.wi = z(3), z(3), z(3), z(3)
+    """World-space record (interaction.h). `fields` selects which members are materialised; the kernels skip the
+    rest (null pointers in hf_si). Default: everything RayFlags.All produces."""
+    ALL_FIELDS = ("t", "p", "n", "uv", "dp_du", "dp_dv", "sh_n", "sh_s", "sh_t", "wi")
+    _ROWS = {"p": 3, "n": 3, "uv": 2, "dp_du": 3, "dp_dv": 3, "sh_n": 3, "sh_s": 3, "sh_t": 3, "wi": 3}
+    _CNAMES = {"p": "p", "n": "n", "dp_du": "dpdu_", "dp_dv": "dpdv_", "sh_n": "shn_", "sh_s": "shs_", "sh_t": "sht_", "wi": "wi_"}
+
+    def __init__(self, n, device, shape=None, fields=None):
+        fields = self.ALL_FIELDS if fields is None else tuple(fields)
+        unknown = set(fields) - set(self.ALL_FIELDS)
+        if unknown:
+            raise HeightfieldError(f"unknown surface interaction fields: {sorted(unknown)}")
+        self.t = torch.empty(n, dtype=torch.float32, device=device) if "t" in fields else None
+        for k, rows in self._ROWS.items():
+            setattr(self, k, torch.empty((rows, n), dtype=torch.float32, device=device) if k in fields else None)
         self.prim_index = None
         self.shape = shape
 
@@ -242,11 +250,11 @@ class SurfaceInteraction3f:
 
     def _c(self):
         f = {"t": self.t}
-        for name, t in (("p", self.p), ("n", self.n), ("dpdu_", self.dp_du), ("dpdv_", self.dp_dv), ("shn_", self.sh_n),
-                        ("shs_", self.sh_s), ("sht_", self.sh_t), ("wi_", self.wi)):
+        for key, cname in self._CNAMES.items():
+            t = getattr(self, key)
             for k, ax in enumerate("xyz"):
-                f[name + ax] = t[k]
-        f["uvx"], f["uvy"] = self.uv[0], self.uv[1]
+                f[cname + ax] = t[k] if t is not None else None
+        f["uvx"], f["uvy"] = (self.uv[0], self.uv[1]) if self.uv is not None else (None, None)
         return _SI(**{k: _ptr(f[k]) for k in SI_FIELDS})
 
 
@@ -415,9 +423,9 @@ class Heightfield:
             raise HeightfieldError("active mask has the wrong length")
         return a
 
-    def ray_intersect_preliminary(self, ray: Ray3f, active=None, counted=False):
+    def ray_intersect_preliminary(self, ray: Ray3f, active=None, counted=False, out=None):
         n = len(ray)
-        pi = PreliminaryIntersection3f(n, self.device, self)
+        pi = out if out is not None else PreliminaryIntersection3f(n, self.device, self)
         a = self._mask(active, n)
         r, p = ray._c(a), pi._c()
         fn = _load().hf_ray_intersect_preliminary_counted if counted else _load().hf_ray_intersect_preliminary
@@ -435,9 +443,9 @@ class Heightfield:
         return hit.bool()
 
     def compute_surface_interaction(self, ray: Ray3f, pi: PreliminaryIntersection3f, ray_flags=RayFlags.All,
-                                    recursion_depth=0, active=None):
+                                    recursion_depth=0, active=None, fields=None, out=None):
         n = len(ray)
-        si = SurfaceInteraction3f(n, self.device, self)
+        si = out if out is not None else SurfaceInteraction3f(n, self.device, self, fields)
         a = self._mask(active, n)
         r, p, s = ray._c(a), pi._c(), si._c()
         with torch.cuda.device(self.device):
@@ -445,10 +453,11 @@ class Heightfield:
         si.prim_index = pi.prim_index
         return si
 
-    def ray_intersect(self, ray: Ray3f, ray_flags=RayFlags.All, active=None, return_prelim=False):
+    def ray_intersect(self, ray: Ray3f, ray_flags=RayFlags.All, active=None, return_prelim=False, fields=None, out=None):
+        """out = (si, pi) reuses preallocated records (no allocation on the hot path)."""
         n = len(ray)
-        si = SurfaceInteraction3f(n, self.device, self)
-        pi = PreliminaryIntersection3f(n, self.device, self)
+        si, pi = out if out is not None else (SurfaceInteraction3f(n, self.device, self, fields),
+                                              PreliminaryIntersection3f(n, self.device, self))
         a = self._mask(active, n)
         r, p, s = ray._c(a), pi._c(), si._c()
         with torch.cuda.device(self.device):
@@ -456,16 +465,21 @@ class Heightfield:
         si.prim_index = pi.prim_index
         return (si, pi) if return_prelim else si
 
-    def backward(self, ray: Ray3f, pi: PreliminaryIntersection3f, adjoints: dict, ray_flags=RayFlags.All, active=None):
+    def backward(self, ray: Ray3f, pi: PreliminaryIntersection3f, adjoints, ray_flags=RayFlags.All, active=None):
         """Accumulate d(loss)/d(heights) into self.grad given upstream adjoints of si fields
-        (reverse mode of compute_surface_interaction, src/render/mesh.cpp:695-789)."""
+        (reverse mode of compute_surface_interaction, src/render/mesh.cpp:695-789). `adjoints` is a dict
+        (t (N,), p/n/dp_du/dp_dv (3,N), uv (2,N)) or the result of prepare_adjoints()."""
         n = len(ray)
         a = self._mask(active, n)
-        adj, keep = _adj_struct(adjoints, n, self.device)
+        adj, keep = adjoints if isinstance(adjoints, tuple) else _adj_struct(adjoints, n, self.device)
         r, p = ray._c(a), pi._c()
         with torch.cuda.device(self.device):
             _check(_load().hf_backward(self._ctx, C.byref(r), C.byref(p), C.byref(adj), int(ray_flags), n, _stream()))
         del keep
+
+    def prepare_adjoints(self, adjoints: dict, n):
+        """Validate / lay out an adjoint dict once so that backward() does no tensor work per call."""
+        return _adj_struct(adjoints, n, self.device)
 
     def stats(self, reset=True):
         s = _Stats()

@@ -227,7 +227,9 @@ def test_backward_vs_oracle_fp64(hf, oracle, H, W, flags_extra, xf):
     h = random_heights(rng, H, W)
     tw = AFFINE if xf else None
     g, c = _mk(hf, oracle, h, 0.6, to_world=tw, flip=(W % 2 == 1))
-    o, d = random_rays(rng, 50000)
+    # ray density of the real workloads (tens of rays per texel): the per-texel criterion below is about fp32
+    # atomic accumulation, whose error grows with the number of cancelling terms per texel
+    o, d = random_rays(rng, min(50000, 60 * H * W))
     if tw is not None:
         o = (o @ tw[:, :3].T + tw[:, 3]).astype(f32); d = (d @ tw[:, :3].T).astype(f32)
     n = o.shape[0]
