@@ -373,6 +373,7 @@ static int check_prelim(const hf_prelim *p) {
 
 extern "C" int hf_ray_intersect_preliminary(hf_ctx *c, const hf_rays *rays, const hf_prelim *out, size_t n, void *stream) {
     CHECK_CTX(c);
+    if (n == 0) return HF_OK;      // empty batch: nothing to do, pointers may be null
     int rc;
     if ((rc = check_rays(rays)) || (rc = check_prelim(out))) return rc;
     NEED_ACCEL(c);
@@ -384,6 +385,7 @@ extern "C" int hf_ray_intersect_preliminary(hf_ctx *c, const hf_rays *rays, cons
 
 extern "C" int hf_ray_intersect_preliminary_counted(hf_ctx *c, const hf_rays *rays, const hf_prelim *out, size_t n, void *stream) {
     CHECK_CTX(c);
+    if (n == 0) return HF_OK;      // empty batch: nothing to do, pointers may be null
     int rc;
     if ((rc = check_rays(rays)) || (rc = check_prelim(out))) return rc;
     NEED_ACCEL(c);
@@ -407,6 +409,7 @@ extern "C" int hf_stats_get(hf_ctx *c, hf_stats *out, int reset) {
 
 extern "C" int hf_ray_test(hf_ctx *c, const hf_rays *rays, uint8_t *d_hit, size_t n, void *stream) {
     CHECK_CTX(c);
+    if (n == 0) return HF_OK;      // empty batch: nothing to do, pointers may be null
     int rc;
     if ((rc = check_rays(rays))) return rc;
     if (!d_hit) return fail(HF_ERR_INVALID, "null hit buffer");
@@ -428,6 +431,7 @@ static int check_flags(uint32_t flags) {
 extern "C" int hf_compute_surface_interaction(hf_ctx *c, const hf_rays *rays, const hf_prelim *pi, uint32_t flags,
                                               const hf_si *out, size_t n, void *stream) {
     CHECK_CTX(c);
+    if (n == 0) return HF_OK;      // empty batch: nothing to do, pointers may be null
     int rc;
     if ((rc = check_rays(rays)) || (rc = check_prelim(pi)) || (rc = check_flags(flags))) return rc;
     if (!out) return fail(HF_ERR_INVALID, "null surface interaction");
@@ -440,6 +444,7 @@ extern "C" int hf_compute_surface_interaction(hf_ctx *c, const hf_rays *rays, co
 extern "C" int hf_ray_intersect(hf_ctx *c, const hf_rays *rays, uint32_t flags, const hf_prelim *prelim_out,
                                 const hf_si *out, size_t n, void *stream) {
     CHECK_CTX(c);
+    if (n == 0) return HF_OK;      // empty batch: nothing to do, pointers may be null
     int rc;
     if ((rc = check_rays(rays)) || (rc = check_flags(flags))) return rc;
     if (!out) return fail(HF_ERR_INVALID, "null surface interaction");
@@ -455,6 +460,7 @@ extern "C" int hf_ray_intersect(hf_ctx *c, const hf_rays *rays, uint32_t flags, 
 extern "C" int hf_backward(hf_ctx *c, const hf_rays *rays, const hf_prelim *pi, const hf_si_adj *adj, uint32_t flags,
                            size_t n, void *stream) {
     CHECK_CTX(c);
+    if (n == 0) return HF_OK;      // empty batch: nothing to do, pointers may be null
     int rc;
     if ((rc = check_rays(rays)) || (rc = check_prelim(pi)) || (rc = check_flags(flags))) return rc;
     if (!adj) return fail(HF_ERR_INVALID, "null adjoints");
@@ -569,8 +575,9 @@ static int ensure_slots(hf_ctx *c) {
 static int host_pipeline(hf_ctx *c, const hf_rays *hr, const hf_si_adj *hadj, uint32_t flags, const hf_prelim *hpre,
                          const hf_si *hsi, float *h_grad_out, size_t n, bool backward) {
     int rc;
-    if ((rc = check_rays(hr)) || (rc = check_flags(flags))) return rc;
-    if (hpre && (rc = check_prelim(hpre))) return rc;
+    if (n == 0 && !h_grad_out) return HF_OK;
+    if (n > 0 && ((rc = check_rays(hr)) || (rc = check_flags(flags)))) return rc;
+    if (n > 0 && hpre && (rc = check_prelim(hpre))) return rc;
     if (backward && !hadj) return fail(HF_ERR_INVALID, "null adjoints");
     NEED_ACCEL(c);
     CU(cudaSetDevice(c->device));

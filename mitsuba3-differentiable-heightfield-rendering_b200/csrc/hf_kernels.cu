@@ -10,6 +10,7 @@
 //
 // Compiled with -fmad=false: see hf_device.cuh.
 #include "hf_kernels.h"
+#include "hf_traverse.cuh"
 
 #define HF_BLOCK 256
 #define FULL_MASK 0xffffffffu
@@ -153,8 +154,9 @@ __device__ __forceinline__ int floor_clamp(float x, int lo, int hi) {
     return __float2int_rd(x);
 }
 
+// CANONICAL traversal: mirrors oracle/hf_oracle.c::traverse step for step. It defines N_node / N_leaf of the byte
+// model and runs only in the counting entry point; the production walk is hf_traverse.cuh.
 // Object-space ray (o, d, maxt). Front-to-back walk: the first cell with a hit is the closest hit.
-// The arithmetic mirrors oracle/hf_oracle.c::traverse (the canonical traversal of the byte model).
 template <bool COUNT>
 __device__ __forceinline__ bool traverse(const HfParams &P, const TopCache &C, f3 o, f3 d, float maxt, HitRec &h,
                                          uint32_t &cn, uint32_t &cl) {
@@ -439,6 +441,106 @@ hf_intersect_kernel(const __grid_constant__ HfParams P, const HfLaunchInfo li, c
     }
 }
 
+// ------------------------------------------------------------------------------------------
+// Production intersection kernel: warp-uniform walk (hf_traverse.cuh) + per-cell primitive + fused surface interaction.
+// Persistent CTAs; one ray per thread per tile of HF_BLOCK rays; SoA ray loads / result stores are fully coalesced
+// streaming accesses (ld.cs / st.cs: the ray stream must not evict the pyramid and the texels from L1/L2).
+// The coarse levels of the pyramid are staged in shared memory by one bulk async copy (TMA engine); the level table
+// holds generic pointers, so the walk reads a node with one load whether the level lives in shared or global memory.
+// ------------------------------------------------------------------------------------------
+template <int MODE>
+__global__ void __launch_bounds__(HF_BLOCK, 4)
+hf_intersect_fast_kernel(const __grid_constant__ HfParams P, const HfLaunchInfo li, const hf_rays R, const hf_prelim O,
+                         const hf_si S, uint8_t *__restrict__ hit_out, const uint32_t flags, const size_t n) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    HfLevel *s_lvl = reinterpret_cast<HfLevel *>(smem_raw);                                   // HF_MAX_LEVELS entries
+    float2 *s_nodes = reinterpret_cast<float2 *>(smem_raw + HF_MAX_LEVELS * sizeof(HfLevel));   // levels >= li.top_level_start
+    __shared__ __align__(8) uint64_t s_bar;
+
+    if (threadIdx.x == 0) {
+        mbar_init(&s_bar, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (threadIdx.x < HF_MAX_LEVELS) {
+        const int l = threadIdx.x;
+        HfLevel e;
+        e.nodes = (li.top_nodes > 0 && l >= li.top_level_start) ? (s_nodes + (P.lvl_off[l] - li.top_off)) : (P.pyr + P.lvl_off[l]);
+        e.w = P.lvl_w[l]; e.pad = 0;
+        s_lvl[l] = e;
+    }
+    __syncthreads();
+    if (li.top_nodes > 0) {
+        if (threadIdx.x == 0) {
+            const uint32_t bytes = (uint32_t) li.top_nodes * (uint32_t) sizeof(float2);
+            mbar_expect_tx(&s_bar, bytes);
+            bulk_g2s(s_nodes, P.pyr + li.top_off, bytes, &s_bar);
+        }
+        uint32_t spins = 0;
+        while (!mbar_try_wait(&s_bar, 0)) { if (++spins > (1u << 24)) __trap(); }
+    }
+
+    HfGrid G;
+    G.W = P.W; G.NX = P.NX; G.NY = P.NY; G.Ltop = P.Ltop; G.mh = P.mh;
+    G.x0 = P.x0; G.y0 = P.y0; G.sgx = P.sgx; G.sgy = P.sgy;
+    G.heights = P.heights; G.lvl = s_lvl;
+    {
+        const float2 top = s_lvl[P.Ltop].nodes[0];
+        G.top_min = top.x; G.top_max = top.y;
+    }
+
+    const size_t ntiles = (n + HF_BLOCK - 1) / HF_BLOCK;
+    for (size_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        const size_t i = tile * HF_BLOCK + threadIdx.x;
+        if (i >= n) continue;
+        const f3 ow = mk3(__ldcs(R.ox + i), __ldcs(R.oy + i), __ldcs(R.oz + i));
+        const f3 dw = mk3(__ldcs(R.dx + i), __ldcs(R.dy + i), __ldcs(R.dz + i));
+        const float maxt = __ldcs(R.maxt + i);
+        const bool active = R.active ? (R.active[i] != 0) : true;
+
+        bool hit = false;
+        HfCand c;
+        float ht = HF_INF, hu = 0.f, hv = 0.f;
+        uint32_t hprim = 0u;
+        if (active) {
+            // Transform::transform_affine(ray), src/shapes/rectangle.cpp:206-214: t is preserved
+            const f3 o = xform_point(P.to_object, ow), d = xform_vector(P.to_object, dw);
+            HfWalk w;
+            if (hf_walk_init(G, o.x, o.y, o.z, d.x, d.y, d.z, maxt, w)) {
+                // lanes leave hf_walk_next at different iterations and reconverge here, so the per-cell primitive
+                // runs for all candidate lanes of the warp together
+                while (hf_walk_next(G, w, c)) {
+                    if (cell_intersect(P, c.cx, c.cy, c.z00, c.z10, c.z01, c.z11, o, d, maxt, ht, hu, hv, hprim)) { hit = true; break; }
+                }
+            }
+        }
+
+        if (MODE == HF_MODE_TEST) {
+            hit_out[i] = hit ? 1 : 0;
+            continue;
+        }
+        if (O.t) {
+            __stcs(O.t + i, hit ? ht : HF_INF);
+            __stcs(O.u + i, hit ? hu : 0.f);
+            __stcs(O.v + i, hit ? hv : 0.f);
+            __stcs(O.prim_index + i, hit ? hprim : 0u);
+        }
+        if (MODE == HF_MODE_FUSED_SI) {
+            if (hit) {
+                // vertices of the hit triangle straight from the candidate-cell registers
+                const float x0 = vtx(c.cx, P.W, P.rw), x1 = vtx(c.cx + 1, P.W, P.rw);
+                const float y0 = vtx(c.cy, P.H, P.rh), y1 = vtx(c.cy + 1, P.H, P.rh);
+                const f3 p0 = mk3(x1, y0, c.z10);
+                f3 p1, p2;
+                if ((hprim & 1u) == 0u) { p1 = mk3(x0, y1, c.z01); p2 = mk3(x0, y0, c.z00); }
+                else { p1 = mk3(x1, y1, c.z11); p2 = mk3(x0, y1, c.z01); }
+                write_si(P, S, i, flags, ow, dw, ht, hu, hv, p0, p1, p2);
+            } else {
+                write_si_invalid(S, i, dw);
+            }
+        }
+    }
+}
+
 static inline int hf_grid_for(size_t n, int num_sms, int ctas_per_sm) {
     size_t ntiles = (n + HF_BLOCK - 1) / HF_BLOCK;
     size_t cap = (size_t) num_sms * ctas_per_sm;
@@ -449,17 +551,20 @@ cudaError_t hf_launch_intersect(const HfParams &P, const HfLaunchInfo &li, int m
                                 const hf_prelim &prelim, const hf_si &si, uint8_t *d_hit, uint32_t flags,
                                 size_t n, unsigned long long *d_counters, cudaStream_t s) {
     if (n == 0) return cudaSuccess;
-    const size_t smem = (size_t) li.top_nodes * sizeof(float2) + 2 * HF_MAX_LEVELS * sizeof(int);
     const int grid = hf_grid_for(n, li.num_sms, 8);
+    if (mode == HF_MODE_COUNTED) {
+        const size_t smem = (size_t) li.top_nodes * sizeof(float2) + 2 * HF_MAX_LEVELS * sizeof(int);
+        hf_intersect_kernel<HF_MODE_COUNTED><<<grid, HF_BLOCK, smem, s>>>(P, li, rays, prelim, si, d_hit, flags, n, d_counters);
+        return cudaGetLastError();
+    }
+    const size_t smem = HF_MAX_LEVELS * sizeof(HfLevel) + (size_t) li.top_nodes * sizeof(float2);
     switch (mode) {
         case HF_MODE_PRELIM:
-            hf_intersect_kernel<HF_MODE_PRELIM><<<grid, HF_BLOCK, smem, s>>>(P, li, rays, prelim, si, d_hit, flags, n, d_counters); break;
+            hf_intersect_fast_kernel<HF_MODE_PRELIM><<<grid, HF_BLOCK, smem, s>>>(P, li, rays, prelim, si, d_hit, flags, n); break;
         case HF_MODE_FUSED_SI:
-            hf_intersect_kernel<HF_MODE_FUSED_SI><<<grid, HF_BLOCK, smem, s>>>(P, li, rays, prelim, si, d_hit, flags, n, d_counters); break;
-        case HF_MODE_TEST:
-            hf_intersect_kernel<HF_MODE_TEST><<<grid, HF_BLOCK, smem, s>>>(P, li, rays, prelim, si, d_hit, flags, n, d_counters); break;
+            hf_intersect_fast_kernel<HF_MODE_FUSED_SI><<<grid, HF_BLOCK, smem, s>>>(P, li, rays, prelim, si, d_hit, flags, n); break;
         default:
-            hf_intersect_kernel<HF_MODE_COUNTED><<<grid, HF_BLOCK, smem, s>>>(P, li, rays, prelim, si, d_hit, flags, n, d_counters); break;
+            hf_intersect_fast_kernel<HF_MODE_TEST><<<grid, HF_BLOCK, smem, s>>>(P, li, rays, prelim, si, d_hit, flags, n); break;
     }
     return cudaGetLastError();
 }

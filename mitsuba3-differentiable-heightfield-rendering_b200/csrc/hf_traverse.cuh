@@ -1,0 +1,206 @@
+// hf_traverse.cuh -- the production traversal: warp-uniform hierarchical DDA over the min/max pyramid.
+//
+// Same geometry and the same position arithmetic as the canonical traversal that defines the byte model
+// (oracle/hf_oracle.c::traverse, mirrored on the device by traverse_canonical in hf_kernels.cu), so it inherits its
+// conservativeness; what changes is the control structure, which is what the SMs pay for:
+//   * ONE loop body for "descend", "step" and "leaf": every lane of a warp executes the same instructions each
+//     iteration and updates its state through selects (the canonical form serialises three divergent paths);
+//   * the walk starts at level min(Ltop, HF_START_LEVEL) instead of the root (the root-side levels always overlap
+//     at the entry point), and after a step it may pop several levels at once (HF_POP_LEVELS) when the step crossed
+//     a coarse node boundary;
+//   * no per-iteration clamps of the node bounds to the grid: the ray's [t0, t1] is already clipped to the grid slab.
+// A lane leaves the loop when it holds a candidate cell whose z range overlaps the ray (the caller then runs the
+// per-cell primitive for all such lanes together) or when the ray is finished.
+//
+// The file compiles as CUDA (device code) and as plain C++ (host): the host build exists ONLY so that tests/ can
+// check the walk against brute force on millions of rays without a GPU (tests/trav_host.cpp). The shipped library
+// never calls the host instantiation.
+#pragma once
+#include <math.h>
+#include <stdint.h>
+
+#ifdef __CUDACC__
+#define HF_HD __device__ __forceinline__
+#define HF_LDG(p) __ldg(p)
+#else
+#define HF_HD static inline
+#define HF_LDG(p) (*(p))
+struct float2 { float x, y; };
+#endif
+
+#ifndef HF_START_LEVEL
+#define HF_START_LEVEL 8
+#endif
+#ifndef HF_POP_LEVELS
+#define HF_POP_LEVELS 1
+#endif
+
+#define HF_TRAV_SLACK 9.5367431640625e-07f   // 2^-20, identical to HF_Z_SLACK / HFO_Z_SLACK
+
+struct __attribute__((aligned(16))) HfLevel {   // one pyramid level; `nodes` may point to global OR shared memory (generic address)
+    const float2 *nodes;       // row-major (min,max) of z = max_height*h
+    int w;                     // nodes per row
+    int pad;
+};
+
+struct HfGrid {                // what the walk needs to know about the shape
+    int W, NX, NY, Ltop;
+    float mh;                  // max_height
+    float x0, y0, sgx, sgy;    // object -> grid units
+    const float *heights;      // (H, W)
+    const HfLevel *lvl;        // [level 1..Ltop]; the table itself sits in shared memory on the device
+    float top_min, top_max;    // root node
+};
+
+struct HfWalk {                // per-ray state, lives in registers
+    float ogx, ogy, dgx, dgy, oz, dz;
+    float idx, idy;            // 1/dg; after hf_walk_init: 0 when the component is zero ...
+    float infx, infy;          // ... and +inf here (0 otherwise), so that t_exit = fma(b - og, id, inf) needs no select
+    float t1, epsz, za;        // za = ray z at the entry of the current node
+    int ix, iy, L;
+    int sx, sy;                // 1 when the ray moves towards +x / +y
+    bool alive;
+};
+
+struct HfCand {                // a leaf cell whose z range overlaps the ray
+    int cx, cy;
+    float z00, z10, z01, z11;
+};
+
+HF_HD int hf_floor_sat(float x) {
+#ifdef __CUDACC__
+    return __float2int_rd(x);                      // saturating; NaN -> 0
+#else
+    if (!(x == x)) return 0;
+    if (x >= 2147483520.0f) return 2147483647;
+    if (x <= -2147483648.0f) return (-2147483647 - 1);
+    return (int) floorf(x);
+#endif
+}
+HF_HD int hf_imin(int a, int b) { return a < b ? a : b; }
+HF_HD int hf_imax(int a, int b) { return a > b ? a : b; }
+HF_HD int hf_msb(unsigned v) {                     // index of the highest set bit, v != 0
+#ifdef __CUDACC__
+    return 31 - __clz((int) v);
+#else
+    return 31 - __builtin_clz(v);
+#endif
+}
+
+// Clip the object-space ray against the shape's box and set up the walk. Returns false when the ray cannot hit.
+// Arithmetic identical to the canonical traversal (slab semantics of include/mitsuba/core/bbox.h:303-327).
+HF_HD bool hf_walk_init(const HfGrid &G, float ox, float oy, float oz, float dx, float dy, float dz, float maxt, HfWalk &w) {
+    w.alive = false;
+    if (dx == 0.f && dy == 0.f && dz == 0.f) return false;
+    if (!(maxt >= 0.f)) return false;
+    const int NX = G.NX, NY = G.NY;
+    w.ogx = (ox - G.x0) * G.sgx; w.ogy = (oy - G.y0) * G.sgy;
+    w.dgx = dx * G.sgx; w.dgy = dy * G.sgy;
+    w.oz = oz; w.dz = dz;
+    w.idx = 1.0f / w.dgx; w.idy = 1.0f / w.dgy;
+    const float idz = 1.0f / dz;
+    float t0 = 0.f, t1 = maxt;
+    if (w.dgx != 0.f) {
+        float a = (0.f - w.ogx) * w.idx, b = ((float) NX - w.ogx) * w.idx;
+        t0 = fmaxf(t0, fminf(a, b)); t1 = fminf(t1, fmaxf(a, b));
+    } else if (w.ogx < 0.f || w.ogx > (float) NX) return false;
+    if (w.dgy != 0.f) {
+        float a = (0.f - w.ogy) * w.idy, b = ((float) NY - w.ogy) * w.idy;
+        t0 = fmaxf(t0, fminf(a, b)); t1 = fminf(t1, fmaxf(a, b));
+    } else if (w.ogy < 0.f || w.ogy > (float) NY) return false;
+    {
+        const float pad = HF_TRAV_SLACK * fmaxf(fabsf(G.top_min), fabsf(G.top_max)) + HF_TRAV_SLACK * fabsf(oz);
+        if (dz != 0.f) {
+            float a = (G.top_min - pad - oz) * idz, b = (G.top_max + pad - oz) * idz;
+            float tn = fminf(a, b), tf = fmaxf(a, b);
+            tn -= fabsf(tn) * HF_TRAV_SLACK; tf += fabsf(tf) * HF_TRAV_SLACK;
+            t0 = fmaxf(t0, tn); t1 = fminf(t1, tf);
+        } else if (oz < G.top_min - pad || oz > G.top_max + pad) return false;
+    }
+    if (!(t0 <= t1)) return false;
+    w.t1 = t1;
+    w.epsz = HF_TRAV_SLACK * (fabsf(oz) + fabsf(t1 * dz));
+    w.sx = w.dgx > 0.f ? 1 : 0; w.sy = w.dgy > 0.f ? 1 : 0;
+    w.ix = hf_imin(hf_imax(hf_floor_sat(fmaf(t0, w.dgx, w.ogx)), 0), NX - 1);
+    w.iy = hf_imin(hf_imax(hf_floor_sat(fmaf(t0, w.dgy, w.ogy)), 0), NY - 1);
+    w.L = hf_imin(G.Ltop, HF_START_LEVEL);
+    w.za = fmaf(t0, dz, oz);
+    const float inf = INFINITY;
+    w.infx = w.dgx != 0.f ? 0.f : inf; w.infy = w.dgy != 0.f ? 0.f : inf;
+    if (w.dgx == 0.f) w.idx = 0.f;
+    if (w.dgy == 0.f) w.idy = 0.f;
+    w.alive = true;
+    return true;
+}
+
+// Advance the walk until a leaf cell overlaps the ray's z interval (returns true, cell in `c`, and the state is
+// already moved past that cell so that a failed primitive test simply calls again) or the ray is finished (false).
+// `iters` (host statistics only) counts loop iterations.
+HF_HD bool hf_walk_next(const HfGrid &G, HfWalk &w, HfCand &c
+#ifndef __CUDACC__
+                        , unsigned *iters = nullptr
+#endif
+) {
+    if (!w.alive) return false;
+    const int NX = G.NX, NY = G.NY, Ltop = G.Ltop;
+    for (;;) {
+#ifndef __CUDACC__
+        if (iters) ++*iters;
+#endif
+        const int L = w.L, ix = w.ix, iy = w.iy;
+        const int nx = ix >> L, ny = iy >> L;
+        const int lox = nx << L, loy = ny << L, span = 1 << L;
+        const int bx = w.sx ? lox + span : lox, by = w.sy ? loy + span : loy;      // exit planes of this node
+        // (float(b) - og) * id, exactly as the canonical walk; the fma only adds +0 or +inf
+        const float tx = fmaf((float) bx - w.ogx, w.idx, w.infx);
+        const float ty = fmaf((float) by - w.ogy, w.idy, w.infy);
+        const float tmin = fminf(tx, ty);
+        const bool last = !(tmin < w.t1);
+        const float te = fminf(tmin, w.t1);
+        const float zb = fmaf(te, w.dz, w.oz);
+        const float zlo = fminf(w.za, zb) - w.epsz, zhi = fmaxf(w.za, zb) + w.epsz;
+
+        float mn, mx;
+        if (L > 0) {
+            const HfLevel lv = G.lvl[L];
+            const float2 nd = lv.nodes[ny * lv.w + nx];
+            mn = nd.x; mx = nd.y;
+        } else {
+            const float *row0 = G.heights + ((size_t) iy * (size_t) G.W + (size_t) ix);
+            c.z00 = G.mh * HF_LDG(row0); c.z10 = G.mh * HF_LDG(row0 + 1);
+            c.z01 = G.mh * HF_LDG(row0 + G.W); c.z11 = G.mh * HF_LDG(row0 + G.W + 1);
+            mn = fminf(fminf(c.z00, c.z10), fminf(c.z01, c.z11));
+            mx = fmaxf(fmaxf(c.z00, c.z10), fmaxf(c.z01, c.z11));
+            c.cx = ix; c.cy = iy;
+        }
+        const bool overlap = (zlo <= mx) && (zhi >= mn);
+        const bool desc = overlap && (L > 0);
+        const bool found = overlap && (L == 0);
+
+        // the step, computed by every lane and committed unless the lane descends
+        const bool stepx = tx <= ty, stepy = ty <= tx;
+        const int qx = hf_floor_sat(fmaf(te, w.dgx, w.ogx)), qy = hf_floor_sat(fmaf(te, w.dgy, w.ogy));
+        const int hix = hf_imin(lox + span - 1, NX - 1), hiy = hf_imin(loy + span - 1, NY - 1);
+        // non-stepped axis: position at the exit, kept inside the node and monotone along the ray
+        const int rx = hf_imin(hf_imax(qx, w.sx ? ix : lox), w.sx ? hix : ix);
+        const int ry = hf_imin(hf_imax(qy, w.sy ? iy : loy), w.sy ? hiy : iy);
+        const int nix = stepx ? (w.sx ? bx : bx - 1) : rx;
+        const int niy = stepy ? (w.sy ? by : by - 1) : ry;
+        const bool outside = ((unsigned) nix >= (unsigned) NX) || ((unsigned) niy >= (unsigned) NY);
+        const unsigned m = (unsigned) ((nix ^ ix) | (niy ^ iy));
+#if HF_POP_LEVELS == 1
+        const int nL = ((m >> (L + 1)) != 0u && L < Ltop) ? L + 1 : L;                  // left the parent node: go up one level
+#else
+        const int b = hf_msb(m | 1u);                                                   // coarsest node boundary crossed
+        const int nL = hf_imin(hf_imin(hf_imax(b, L), L + HF_POP_LEVELS), Ltop);
+#endif
+
+        w.L = desc ? L - 1 : nL;
+        w.ix = desc ? ix : nix;
+        w.iy = desc ? iy : niy;
+        w.za = desc ? w.za : zb;
+        w.alive = desc ? true : !(last || outside);
+        if (found) return true;
+        if (!w.alive) return false;
+    }
+}

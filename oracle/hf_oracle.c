@@ -208,6 +208,12 @@ static inline int cell_intersect(const grid_t *g, int cx, int cy,
     return 0;
 }
 
+int hfo_cell_intersect(const hfo_shape *s, int32_t cx, int32_t cy, const float o[3], const float d[3], float maxt,
+                       float *t, float *u, float *v, uint32_t *prim) {
+    grid_t g = make_grid(s);
+    return cell_intersect(&g, cx, cy, o, d, maxt, t, u, v, prim);
+}
+
 /* ---------------------------------------------------------------------- */
 /* Min/max pyramid                                                         */
 /* ---------------------------------------------------------------------- */

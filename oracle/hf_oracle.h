@@ -99,6 +99,11 @@ void hfo_interpolate_and_normal(const float p0[3], const float p1[3], const floa
 void hfo_xform_point(const float m[12], const float p[3], float out[3]);
 void hfo_xform_vector(const float m[12], const float v[3], float out[3]);
 
+/* The per-cell primitive on cell (cx, cy): both triangles, closest wins, tie -> smaller index.
+ * o, d are OBJECT-space. Returns 1 on a hit. (Hook for tests/trav_host.cpp.) */
+int hfo_cell_intersect(const hfo_shape *s, int32_t cx, int32_t cy, const float o[3], const float d[3], float maxt,
+                       float *t, float *u, float *v, uint32_t *prim);
+
 /* Vertex / texcoord synthesis of the heightfield definition */
 float hfo_vertex_x(int32_t i, int32_t W);
 

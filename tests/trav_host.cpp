@@ -1,0 +1,67 @@
+// trav_host.cpp -- HOST instantiation of the production walk (csrc/hf_traverse.cuh) for CPU-side testing.
+// TEST INFRASTRUCTURE: compiled by tests/test_traversal_host.py with g++ and linked against the oracle, whose
+// per-cell primitive and pyramid it borrows; the shipped CUDA library contains none of this.
+//
+// It answers two questions without a GPU: (1) is the warp-uniform walk conservative -- same closest hit as the
+// oracle's brute force / canonical DDA on millions of random + adversarial rays; (2) how many loop iterations and
+// primitive rounds does a warp of 32 consecutive rays need under a given HF_START_LEVEL / HF_POP_LEVELS.
+#include <stdlib.h>
+#include <string.h>
+#include <vector>
+
+#include "../mitsuba3-differentiable-heightfield-rendering_b200/csrc/hf_traverse.cuh"
+#include "../oracle/hf_oracle.h"
+
+extern "C" int trav_host_intersect(const hfo_shape *s, const hfo_rays *r, size_t n, hfo_prelim *out,
+                                   uint32_t *iters, uint32_t *cands) {
+    hfo_pyramid *p = hfo_pyramid_build(s);
+    const int Ltop = hfo_pyramid_levels(p);
+    std::vector<HfLevel> lvl(Ltop + 1);
+    lvl[0].nodes = nullptr; lvl[0].w = 0;
+    for (int l = 1; l <= Ltop; ++l) {
+        int w, h;
+        hfo_pyramid_level_dims(p, l, &w, &h);
+        lvl[l].nodes = reinterpret_cast<const float2 *>(hfo_pyramid_level_data(p, l));   // interleaved (min,max)
+        lvl[l].w = w;
+    }
+    HfGrid G;
+    G.W = s->W; G.NX = s->W - 1; G.NY = s->H - 1; G.Ltop = Ltop; G.mh = s->max_height;
+    const float rw = 1.0f / (float) G.NX, rh = 1.0f / (float) G.NY;
+    G.x0 = (float) (-(s->W - 1)) * rw; G.y0 = (float) (-(s->H - 1)) * rh;
+    G.sgx = 0.5f * (float) G.NX; G.sgy = 0.5f * (float) G.NY;
+    G.heights = s->heights; G.lvl = lvl.data();
+    G.top_min = lvl[Ltop].nodes[0].x; G.top_max = lvl[Ltop].nodes[0].y;
+
+    #pragma omp parallel for schedule(dynamic, 1024)
+    for (long long ii = 0; ii < (long long) n; ++ii) {
+        const size_t i = (size_t) ii;
+        unsigned it = 0, nc = 0;
+        float bt = INFINITY, bu = 0.f, bv = 0.f; uint32_t bp = 0;
+        if (!r->active || r->active[i]) {
+            const float *m = s->to_object;
+            const float ow[3] = { r->ox[i], r->oy[i], r->oz[i] }, dw[3] = { r->dx[i], r->dy[i], r->dz[i] };
+            float o[3], d[3];
+            for (int a = 0; a < 3; ++a) {        // transform.h:104-111, 129-139
+                float v = m[4 * a + 3];
+                v = fmaf(m[4 * a + 0], ow[0], v); v = fmaf(m[4 * a + 1], ow[1], v); v = fmaf(m[4 * a + 2], ow[2], v);
+                o[a] = v;
+                float q = m[4 * a + 0] * dw[0];
+                q = fmaf(m[4 * a + 1], dw[1], q); q = fmaf(m[4 * a + 2], dw[2], q);
+                d[a] = q;
+            }
+            HfWalk w; HfCand c;
+            if (hf_walk_init(G, o[0], o[1], o[2], d[0], d[1], d[2], r->maxt[i], w)) {
+                while (hf_walk_next(G, w, c, &it)) {
+                    ++nc;
+                    float t, u, v; uint32_t prim;
+                    if (hfo_cell_intersect(s, c.cx, c.cy, o, d, r->maxt[i], &t, &u, &v, &prim)) { bt = t; bu = u; bv = v; bp = prim; break; }
+                }
+            }
+        }
+        out->t[i] = bt; out->u[i] = bu; out->v[i] = bv; out->prim_index[i] = bp;
+        if (iters) iters[i] = it;
+        if (cands) cands[i] = nc;
+    }
+    hfo_pyramid_free(p);
+    return 0;
+}
