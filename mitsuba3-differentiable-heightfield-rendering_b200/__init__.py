@@ -30,7 +30,7 @@ __all__ = ["RayFlags", "Ray3f", "PreliminaryIntersection3f", "SurfaceInteraction
            "load_dict", "traverse", "SceneParameters", "Adam", "lib_path", "HeightfieldError"]
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-_LIB = os.path.join(_HERE, "lib", "libhf_b200.so")
+_LIB = os.environ.get("HF_B200_LIB") or os.path.join(_HERE, "lib", "libhf_b200.so")   # override: kernel experiments only
 _f32p = C.POINTER(C.c_float)
 
 

@@ -448,13 +448,16 @@ hf_intersect_kernel(const __grid_constant__ HfParams P, const HfLaunchInfo li, c
 // The coarse levels of the pyramid are staged in shared memory by one bulk async copy (TMA engine); the level table
 // holds generic pointers, so the walk reads a node with one load whether the level lives in shared or global memory.
 // ------------------------------------------------------------------------------------------
+#ifndef HF_MIN_CTAS
+#define HF_MIN_CTAS 4
+#endif
 template <int MODE>
-__global__ void __launch_bounds__(HF_BLOCK, 4)
+__global__ void __launch_bounds__(HF_BLOCK, HF_MIN_CTAS)
 hf_intersect_fast_kernel(const __grid_constant__ HfParams P, const HfLaunchInfo li, const hf_rays R, const hf_prelim O,
                          const hf_si S, uint8_t *__restrict__ hit_out, const uint32_t flags, const size_t n) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    HfLevel *s_lvl = reinterpret_cast<HfLevel *>(smem_raw);                                   // HF_MAX_LEVELS entries
-    float2 *s_nodes = reinterpret_cast<float2 *>(smem_raw + HF_MAX_LEVELS * sizeof(HfLevel));   // levels >= li.top_level_start
+    HfLevel *s_lvl = hf_s_lvl;                                                                // static __shared__ (hf_traverse.cuh)
+    float2 *s_nodes = reinterpret_cast<float2 *>(smem_raw);                                   // levels >= li.top_level_start
     __shared__ __align__(8) uint64_t s_bar;
 
     if (threadIdx.x == 0) {
@@ -533,9 +536,18 @@ hf_intersect_fast_kernel(const __grid_constant__ HfParams P, const HfLaunchInfo 
                 f3 p1, p2;
                 if ((hprim & 1u) == 0u) { p1 = mk3(x0, y1, c.z01); p2 = mk3(x0, y0, c.z00); }
                 else { p1 = mk3(x1, y1, c.z11); p2 = mk3(x0, y1, c.z01); }
-                write_si(P, S, i, flags, ow, dw, ht, hu, hv, p0, p1, p2);
+                // the world-space ray is only needed by FollowShape and wi: re-read it (L2) instead of keeping six
+                // registers alive across the walk
+                f3 ow2 = mk3(0.f, 0.f, 0.f), dw2 = ow2;
+                if ((flags & HF_RAY_FOLLOWSHAPE) || S.wi_x || S.wi_y || S.wi_z) {
+                    ow2 = mk3(__ldcs(R.ox + i), __ldcs(R.oy + i), __ldcs(R.oz + i));
+                    dw2 = mk3(__ldcs(R.dx + i), __ldcs(R.dy + i), __ldcs(R.dz + i));
+                }
+                write_si(P, S, i, flags, ow2, dw2, ht, hu, hv, p0, p1, p2);
             } else {
-                write_si_invalid(S, i, dw);
+                f3 dw2 = mk3(0.f, 0.f, 0.f);
+                if (S.wi_x || S.wi_y || S.wi_z) dw2 = mk3(__ldcs(R.dx + i), __ldcs(R.dy + i), __ldcs(R.dz + i));
+                write_si_invalid(S, i, dw2);
             }
         }
     }
@@ -557,7 +569,7 @@ cudaError_t hf_launch_intersect(const HfParams &P, const HfLaunchInfo &li, int m
         hf_intersect_kernel<HF_MODE_COUNTED><<<grid, HF_BLOCK, smem, s>>>(P, li, rays, prelim, si, d_hit, flags, n, d_counters);
         return cudaGetLastError();
     }
-    const size_t smem = HF_MAX_LEVELS * sizeof(HfLevel) + (size_t) li.top_nodes * sizeof(float2);
+    const size_t smem = (size_t) li.top_nodes * sizeof(float2);
     switch (mode) {
         case HF_MODE_PRELIM:
             hf_intersect_fast_kernel<HF_MODE_PRELIM><<<grid, HF_BLOCK, smem, s>>>(P, li, rays, prelim, si, d_hit, flags, n); break;

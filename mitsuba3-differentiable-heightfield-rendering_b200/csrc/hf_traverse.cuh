@@ -8,7 +8,9 @@
 //   * the walk starts at level min(Ltop, HF_START_LEVEL) instead of the root (the root-side levels always overlap
 //     at the entry point), and after a step it may pop several levels at once (HF_POP_LEVELS) when the step crossed
 //     a coarse node boundary;
-//   * no per-iteration clamps of the node bounds to the grid: the ray's [t0, t1] is already clipped to the grid slab.
+//   * no per-iteration clamps of the node bounds to the grid: the ray's [t0, t1] is already clipped to the grid slab;
+//   * a descending lane clips its entry point to the node's z slab [min, max] (the ray-vs-box clip the root gets, applied
+//     at every level), which skips the children in front of the point where the ray can first touch the node's content.
 // A lane leaves the loop when it holds a candidate cell whose z range overlaps the ray (the caller then runs the
 // per-cell primitive for all such lanes together) or when the ray is finished.
 //
@@ -22,7 +24,9 @@
 #ifdef __CUDACC__
 #define HF_HD __device__ __forceinline__
 #define HF_LDG(p) __ldg(p)
+#define HF_RCP(x) __frcp_rn(x)
 #else
+#define HF_RCP(x) (1.0f / (x))
 #define HF_HD static inline
 #define HF_LDG(p) (*(p))
 struct float2 { float x, y; };
@@ -34,6 +38,9 @@ struct float2 { float x, y; };
 #ifndef HF_POP_LEVELS
 #define HF_POP_LEVELS 1
 #endif
+#ifndef HF_DESC_LEVELS
+#define HF_DESC_LEVELS 2      // levels dropped per descent (the slab clip places the entry cell, so skipping a level is cheap)
+#endif
 
 #define HF_TRAV_SLACK 9.5367431640625e-07f   // 2^-20, identical to HF_Z_SLACK / HFO_Z_SLACK
 
@@ -42,6 +49,11 @@ struct __attribute__((aligned(16))) HfLevel {   // one pyramid level; `nodes` ma
     int w;                     // nodes per row
     int pad;
 };
+
+#ifdef __CUDACC__
+#define HF_LVL_ENTRIES 26
+__shared__ HfLevel hf_s_lvl[HF_LVL_ENTRIES];      // filled by the kernel prologue
+#endif
 
 struct HfGrid {                // what the walk needs to know about the shape
     int W, NX, NY, Ltop;
@@ -56,7 +68,11 @@ struct HfWalk {                // per-ray state, lives in registers
     float ogx, ogy, dgx, dgy, oz, dz;
     float idx, idy;            // 1/dg; after hf_walk_init: 0 when the component is zero ...
     float infx, infy;          // ... and +inf here (0 otherwise), so that t_exit = fma(b - og, id, inf) needs no select
-    float t1, epsz, za;        // za = ray z at the entry of the current node
+    float t1, epsz;
+    float t;                   // ray parameter at the entry of the current node
+    float idz;                 // 1/dz (0 when dz == 0)
+    float zeps;                // +epsz for a descending ray (enters a node's z slab through its max), -epsz otherwise
+    float ogxb, ogyb;          // og backed off against the direction of travel: cells derived from t are never ahead of the ray
     int ix, iy, L;
     int sx, sy;                // 1 when the ray moves towards +x / +y
     bool alive;
@@ -97,8 +113,8 @@ HF_HD bool hf_walk_init(const HfGrid &G, float ox, float oy, float oz, float dx,
     w.ogx = (ox - G.x0) * G.sgx; w.ogy = (oy - G.y0) * G.sgy;
     w.dgx = dx * G.sgx; w.dgy = dy * G.sgy;
     w.oz = oz; w.dz = dz;
-    w.idx = 1.0f / w.dgx; w.idy = 1.0f / w.dgy;
-    const float idz = 1.0f / dz;
+    w.idx = HF_RCP(w.dgx); w.idy = HF_RCP(w.dgy);           // correctly rounded on both sides (== 1.0f / x)
+    const float idz = HF_RCP(dz);
     float t0 = 0.f, t1 = maxt;
     if (w.dgx != 0.f) {
         float a = (0.f - w.ogx) * w.idx, b = ((float) NX - w.ogx) * w.idx;
@@ -124,7 +140,14 @@ HF_HD bool hf_walk_init(const HfGrid &G, float ox, float oy, float oz, float dx,
     w.ix = hf_imin(hf_imax(hf_floor_sat(fmaf(t0, w.dgx, w.ogx)), 0), NX - 1);
     w.iy = hf_imin(hf_imax(hf_floor_sat(fmaf(t0, w.dgy, w.ogy)), 0), NY - 1);
     w.L = hf_imin(G.Ltop, HF_START_LEVEL);
-    w.za = fmaf(t0, dz, oz);
+    w.t = t0;
+    w.idz = dz != 0.f ? idz : 0.f;
+    w.zeps = dz < 0.f ? w.epsz : -w.epsz;
+    {   // 4 ulp of the largest grid coordinate the ray reaches: a cell derived from a ray parameter is never ahead of the true one
+        const float ex = 2.384185791015625e-07f * (fabsf(w.ogx) + fabsf(t1 * w.dgx));
+        const float ey = 2.384185791015625e-07f * (fabsf(w.ogy) + fabsf(t1 * w.dgy));
+        w.ogxb = w.ogx + (w.sx ? -ex : ex); w.ogyb = w.ogy + (w.sy ? -ey : ey);
+    }
     const float inf = INFINITY;
     w.infx = w.dgx != 0.f ? 0.f : inf; w.infy = w.dgy != 0.f ? 0.f : inf;
     if (w.dgx == 0.f) w.idx = 0.f;
@@ -157,16 +180,20 @@ HF_HD bool hf_walk_next(const HfGrid &G, HfWalk &w, HfCand &c
         const float tmin = fminf(tx, ty);
         const bool last = !(tmin < w.t1);
         const float te = fminf(tmin, w.t1);
-        const float zb = fmaf(te, w.dz, w.oz);
-        const float zlo = fminf(w.za, zb) - w.epsz, zhi = fmaxf(w.za, zb) + w.epsz;
+        const float za = fmaf(w.t, w.dz, w.oz), zb = fmaf(te, w.dz, w.oz);
+        const float zlo = fminf(za, zb) - w.epsz, zhi = fmaxf(za, zb) + w.epsz;
 
         float mn, mx;
         if (L > 0) {
+#ifdef __CUDACC__
+            const HfLevel lv = hf_s_lvl[L];           // the table is a __shared__ array: the address is L*16 + a constant
+#else
             const HfLevel lv = G.lvl[L];
+#endif
             const float2 nd = lv.nodes[ny * lv.w + nx];
             mn = nd.x; mx = nd.y;
         } else {
-            const float *row0 = G.heights + ((size_t) iy * (size_t) G.W + (size_t) ix);
+            const float *row0 = G.heights + (unsigned) (iy * G.W + ix);          // W*H < 2^32 (checked by hf_create)
             c.z00 = G.mh * HF_LDG(row0); c.z10 = G.mh * HF_LDG(row0 + 1);
             c.z01 = G.mh * HF_LDG(row0 + G.W); c.z11 = G.mh * HF_LDG(row0 + G.W + 1);
             mn = fminf(fminf(c.z00, c.z10), fminf(c.z01, c.z11));
@@ -177,15 +204,23 @@ HF_HD bool hf_walk_next(const HfGrid &G, HfWalk &w, HfCand &c
         const bool desc = overlap && (L > 0);
         const bool found = overlap && (L == 0);
 
-        // the step, computed by every lane and committed unless the lane descends
+        // Descending lanes first clip their entry point to the node's z slab [mn, mx]: before the ray crosses
+        // zbnd it cannot touch anything inside this node, so the children in front of that point are skipped.
+        const float zbnd = (w.dz < 0.f ? mx : mn) + w.zeps;
+        float ts = (zbnd - w.oz) * w.idz;
+        ts -= fabsf(ts) * HF_TRAV_SLACK;                                  // never later than the true crossing
+        const float tc = fminf(fmaxf(w.t, ts), te);
+        // tq: the parameter the next cell is derived from -- the clipped entry (descend) or the node's exit (step)
+        const float tq = desc ? tc : te;
         const bool stepx = tx <= ty, stepy = ty <= tx;
-        const int qx = hf_floor_sat(fmaf(te, w.dgx, w.ogx)), qy = hf_floor_sat(fmaf(te, w.dgy, w.ogy));
+        const int qx = hf_floor_sat(fmaf(tq, w.dgx, w.ogxb)), qy = hf_floor_sat(fmaf(tq, w.dgy, w.ogyb));
         const int hix = hf_imin(lox + span - 1, NX - 1), hiy = hf_imin(loy + span - 1, NY - 1);
-        // non-stepped axis: position at the exit, kept inside the node and monotone along the ray
+        // position at tq, kept inside the node and monotone along the ray
         const int rx = hf_imin(hf_imax(qx, w.sx ? ix : lox), w.sx ? hix : ix);
         const int ry = hf_imin(hf_imax(qy, w.sy ? iy : loy), w.sy ? hiy : iy);
-        const int nix = stepx ? (w.sx ? bx : bx - 1) : rx;
-        const int niy = stepy ? (w.sy ? by : by - 1) : ry;
+        // a step leaves the node through the plane(s) reached first; a descent stays inside
+        const int nix = (stepx && !desc) ? (w.sx ? bx : bx - 1) : rx;
+        const int niy = (stepy && !desc) ? (w.sy ? by : by - 1) : ry;
         const bool outside = ((unsigned) nix >= (unsigned) NX) || ((unsigned) niy >= (unsigned) NY);
         const unsigned m = (unsigned) ((nix ^ ix) | (niy ^ iy));
 #if HF_POP_LEVELS == 1
@@ -195,10 +230,14 @@ HF_HD bool hf_walk_next(const HfGrid &G, HfWalk &w, HfCand &c
         const int nL = hf_imin(hf_imin(hf_imax(b, L), L + HF_POP_LEVELS), Ltop);
 #endif
 
-        w.L = desc ? L - 1 : nL;
-        w.ix = desc ? ix : nix;
-        w.iy = desc ? iy : niy;
-        w.za = desc ? w.za : zb;
+#if !defined(__CUDACC__) && defined(HF_WALK_HIST)
+        { extern unsigned long long hf_walk_hist[3][32];
+          _Pragma("omp atomic") hf_walk_hist[desc ? 0 : (found ? 2 : 1)][L]++; }
+#endif
+        w.L = desc ? hf_imax(L - HF_DESC_LEVELS, 0) : nL;
+        w.ix = nix;
+        w.iy = niy;
+        w.t = tq;
         w.alive = desc ? true : !(last || outside);
         if (found) return true;
         if (!w.alive) return false;

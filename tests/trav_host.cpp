@@ -9,11 +9,16 @@
 #include <string.h>
 #include <vector>
 
+#ifdef HF_WALK_HIST
+unsigned long long hf_walk_hist[3][32];
+extern "C" unsigned long long *trav_host_hist(void) { return &hf_walk_hist[0][0]; }
+#endif
 #include "../mitsuba3-differentiable-heightfield-rendering_b200/csrc/hf_traverse.cuh"
 #include "../oracle/hf_oracle.h"
 
+// rounds (nullable): uint32[n][8], loop iterations spent in each call of hf_walk_next (candidate round)
 extern "C" int trav_host_intersect(const hfo_shape *s, const hfo_rays *r, size_t n, hfo_prelim *out,
-                                   uint32_t *iters, uint32_t *cands) {
+                                   uint32_t *iters, uint32_t *cands, uint32_t *rounds) {
     hfo_pyramid *p = hfo_pyramid_build(s);
     const int Ltop = hfo_pyramid_levels(p);
     std::vector<HfLevel> lvl(Ltop + 1);
@@ -51,7 +56,11 @@ extern "C" int trav_host_intersect(const hfo_shape *s, const hfo_rays *r, size_t
             }
             HfWalk w; HfCand c;
             if (hf_walk_init(G, o[0], o[1], o[2], d[0], d[1], d[2], r->maxt[i], w)) {
-                while (hf_walk_next(G, w, c, &it)) {
+                for (;;) {
+                    const unsigned before = it;
+                    const bool more = hf_walk_next(G, w, c, &it);
+                    if (rounds && nc < 8) rounds[8 * i + nc] = it - before;
+                    if (!more) break;
                     ++nc;
                     float t, u, v; uint32_t prim;
                     if (hfo_cell_intersect(s, c.cx, c.cy, o, d, r->maxt[i], &t, &u, &v, &prim)) { bt = t; bu = u; bv = v; bp = prim; break; }

@@ -1,0 +1,12 @@
+#!/bin/bash
+# Dev tool: time the intersect kernel for every experiment build lib/libhf_b200*.so (run under gpurun).
+cd "$(dirname "$0")/.."
+for so in mitsuba3-differentiable-heightfield-rendering_b200/lib/libhf_b200*.so; do
+  HF_B200_LIB=$PWD/$so python bench.py --steps 3 --warmup 3 --no-e2e --no-cpu "$@" 2>&1 | python -c "
+import sys, json
+for line in sys.stdin:
+    if line.startswith('{'):
+        d = json.loads(line)
+        print('$(basename $so)', 'fwdSI_ms %.3f' % d['roofline']['kernel_ms'], 'isect_ms %.3f' % d['extras']['intersect_only_ms'], 'bwd_ms %.3f' % d['roofline']['backward']['kernel_ms'], 'value %.0f' % d['value'], 'frac %.3f' % d['roofline']['frac'], 'sm_mhz', d['clocks']['sm_mhz'])
+"
+done

@@ -15,13 +15,15 @@ def build(start, pop):
                            f"-DHF_POP_LEVELS={pop}", "-o", so, os.path.join(ROOT, "tests/trav_host.cpp"), "-L" + os.path.join(ROOT, "oracle/_build"),
                            "-lhf_oracle", "-Wl,-rpath," + os.path.join(ROOT, "oracle/_build")])
     L = C.CDLL(so)
-    L.trav_host_intersect.argtypes = [C.POINTER(O._Shape), C.POINTER(O._Rays), C.c_size_t, C.POINTER(O._Prelim), O._u32p, O._u32p]
+    L.trav_host_intersect.argtypes = [C.POINTER(O._Shape), C.POINTER(O._Rays), C.c_size_t, C.POINTER(O._Prelim), O._u32p, O._u32p, O._u32p]
     return L
 
 def run(L, hf, rays):
     out = O.Prelim(rays.n); it = np.zeros(rays.n, np.uint32); nc = np.zeros(rays.n, np.uint32)
+    run.rounds = np.zeros((rays.n, 8), np.uint32)
     s, r, o = hf._shape(), rays.c(), out.c()
-    L.trav_host_intersect(C.byref(s), C.byref(r), rays.n, C.byref(o), it.ctypes.data_as(O._u32p), nc.ctypes.data_as(O._u32p))
+    L.trav_host_intersect(C.byref(s), C.byref(r), rays.n, C.byref(o), it.ctypes.data_as(O._u32p), nc.ctypes.data_as(O._u32p),
+                          run.rounds.ctypes.data_as(O._u32p))
     return out, it, nc
 
 def check(L):
@@ -60,5 +62,10 @@ if __name__ == "__main__":
         same = (out.t.view(np.uint32) == ref.t.view(np.uint32)) & (out.prim_index == ref.prim_index)
         w_it = it.reshape(-1, 32).max(1); w_nc = nc.reshape(-1, 32).max(1)
         hitw = ref.valid().reshape(-1, 32).any(1)
+        rd = run.rounds.reshape(-1, 32, 8)
+        lockstep = rd.max(1).sum(1)            # sum over rounds of the slowest lane of the round
+        lanes = it.reshape(-1, 32).sum(1)
+        print(f"   per hit warp: lock-step rounds {lockstep[hitw].mean():.2f} iterations vs slowest lane {w_it[hitw].mean():.2f}; "
+              f"lane utilisation {lanes[hitw].sum() / (32.0 * lockstep[hitw].sum()):.3f}")
         print(f"start {s:2d} pop {p:2d}: mismatches(random/adv) {bad}, C3 mismatches {(~same).sum()}; iters/ray {it.mean():.2f} (hit rays {it[ref.valid()].mean():.2f}); "
               f"warp-max iters: all {w_it.mean():.2f}, hit warps {w_it[hitw].mean():.2f}; cand rounds/hit warp {w_nc[hitw].mean():.2f} (per hit ray {nc[ref.valid()].mean():.2f})")
