@@ -9,6 +9,7 @@
 #include <math.h>
 #include <stdarg.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <algorithm>
@@ -167,6 +168,13 @@ static void layout_pyramid(hf_ctx *c) {
     c->li.top_nodes = (int) top;
     c->li.top_off = P.lvl_off[Ls];
     c->li.num_sms = c->num_sms;
+    {   // HF_B200_BUNDLES=1 selects the bundled kernel (hf_intersect_beam_kernel). Measured on C3 (profiles/): it removes 40 % of
+        // the walk's instructions but pays them back in the shuffle reductions that find the bundle bounds of a generic ray
+        // array, so the plain kernel stays the default for ray-array entry points; the fused render step, which knows its
+        // bundles analytically, always marches them.
+        const char *e = getenv("HF_B200_BUNDLES");
+        c->li.use_bundles = (e && e[0] == '1') ? 1 : 0;
+    }
 }
 
 extern "C" int hf_create(hf_ctx **out, const hf_desc *desc) {
@@ -207,11 +215,11 @@ extern "C" int hf_create(hf_ctx **out, const hf_desc *desc) {
     cudaError_t e1 = cudaMalloc(&c->d_heights, texels * sizeof(float));
     cudaError_t e2 = cudaMalloc(&c->d_grad, texels * sizeof(float));
     cudaError_t e3 = cudaMalloc(&c->d_pyr, c->pyr_nodes * sizeof(float2));
-    cudaError_t e4 = cudaMalloc(&c->d_counters, 4 * sizeof(unsigned long long));
+    cudaError_t e4 = cudaMalloc(&c->d_counters, 8 * sizeof(unsigned long long));
     if (e1 || e2 || e3 || e4) { hf_destroy(c); return fail(HF_ERR_CUDA, "cudaMalloc failed for a %ux%u heightfield", c->W, c->H); }
     cudaMemset(c->d_grad, 0, texels * sizeof(float));
     cudaMemset(c->d_pyr, 0, c->pyr_nodes * sizeof(float2));
-    cudaMemset(c->d_counters, 0, 4 * sizeof(unsigned long long));
+    cudaMemset(c->d_counters, 0, 8 * sizeof(unsigned long long));
     P.heights = c->d_heights;
     P.pyr = c->d_pyr;
     *out = c;

@@ -448,13 +448,71 @@ hf_intersect_kernel(const __grid_constant__ HfParams P, const HfLaunchInfo li, c
 // The coarse levels of the pyramid are staged in shared memory by one bulk async copy (TMA engine); the level table
 // holds generic pointers, so the walk reads a node with one load whether the level lives in shared or global memory.
 // ------------------------------------------------------------------------------------------
-#ifndef HF_MIN_CTAS
-#define HF_MIN_CTAS 4
-#endif
+// One ray through the production walk: load, transform, walk + per-cell primitive, store (+ fused surface interaction).
+// t_start / L_start come from the bundle march (hf_beam_enter) or are 0 / HF_START_LEVEL.
 template <int MODE>
-__global__ void __launch_bounds__(HF_BLOCK, HF_MIN_CTAS)
-hf_intersect_fast_kernel(const __grid_constant__ HfParams P, const HfLaunchInfo li, const hf_rays R, const hf_prelim O,
-                         const hf_si S, uint8_t *__restrict__ hit_out, const uint32_t flags, const size_t n) {
+__device__ __forceinline__ void hf_process_ray(const HfParams &P, const HfGrid &G, const hf_rays &R, const hf_prelim &O,
+                                               const hf_si &S, uint8_t *__restrict__ hit_out, const uint32_t flags,
+                                               const size_t i, const float t_start, const int L_start) {
+    const f3 ow = mk3(__ldcs(R.ox + i), __ldcs(R.oy + i), __ldcs(R.oz + i));
+    const f3 dw = mk3(__ldcs(R.dx + i), __ldcs(R.dy + i), __ldcs(R.dz + i));
+    const float maxt = __ldcs(R.maxt + i);
+    const bool active = R.active ? (R.active[i] != 0) : true;
+
+    bool hit = false;
+    HfCand c;
+    float ht = HF_INF, hu = 0.f, hv = 0.f;
+    uint32_t hprim = 0u;
+    if (active) {
+        // Transform::transform_affine(ray), src/shapes/rectangle.cpp:206-214: t is preserved
+        const f3 o = xform_point(P.to_object, ow), d = xform_vector(P.to_object, dw);
+        HfWalk w;
+        if (hf_walk_init(G, o.x, o.y, o.z, d.x, d.y, d.z, maxt, w, t_start, L_start)) {
+            // lanes leave hf_walk_next at different iterations and reconverge here, so the per-cell primitive
+            // runs for all candidate lanes of the warp together
+            while (hf_walk_next(G, w, c)) {
+                if (cell_intersect(P, c.cx, c.cy, c.z00, c.z10, c.z01, c.z11, o, d, maxt, ht, hu, hv, hprim)) { hit = true; break; }
+            }
+        }
+    }
+
+    if (MODE == HF_MODE_TEST) {
+        hit_out[i] = hit ? 1 : 0;
+        return;
+    }
+    if (O.t) {
+        __stcs(O.t + i, hit ? ht : HF_INF);
+        __stcs(O.u + i, hit ? hu : 0.f);
+        __stcs(O.v + i, hit ? hv : 0.f);
+        __stcs(O.prim_index + i, hit ? hprim : 0u);
+    }
+    if (MODE == HF_MODE_FUSED_SI) {
+        if (hit) {
+            // vertices of the hit triangle straight from the candidate-cell registers
+            const float x0 = vtx(c.cx, P.W, P.rw), x1 = vtx(c.cx + 1, P.W, P.rw);
+            const float y0 = vtx(c.cy, P.H, P.rh), y1 = vtx(c.cy + 1, P.H, P.rh);
+            const f3 p0 = mk3(x1, y0, c.z10);
+            f3 p1, p2;
+            if ((hprim & 1u) == 0u) { p1 = mk3(x0, y1, c.z01); p2 = mk3(x0, y0, c.z00); }
+            else { p1 = mk3(x1, y1, c.z11); p2 = mk3(x0, y1, c.z01); }
+            // the world-space ray is only needed by FollowShape and wi: re-read it (L2) instead of keeping six
+            // registers alive across the walk
+            f3 ow2 = mk3(0.f, 0.f, 0.f), dw2 = ow2;
+            if ((flags & HF_RAY_FOLLOWSHAPE) || S.wi_x || S.wi_y || S.wi_z) {
+                ow2 = mk3(__ldcs(R.ox + i), __ldcs(R.oy + i), __ldcs(R.oz + i));
+                dw2 = mk3(__ldcs(R.dx + i), __ldcs(R.dy + i), __ldcs(R.dz + i));
+            }
+            write_si(P, S, i, flags, ow2, dw2, ht, hu, hv, p0, p1, p2);
+        } else {
+            f3 dw2 = mk3(0.f, 0.f, 0.f);
+            if (S.wi_x || S.wi_y || S.wi_z) dw2 = mk3(__ldcs(R.dx + i), __ldcs(R.dy + i), __ldcs(R.dz + i));
+            write_si_invalid(S, i, dw2);
+        }
+    }
+}
+
+// Kernel prologue shared by the walk kernels: level table in shared memory, coarse levels staged by one bulk async copy.
+__device__ __forceinline__ void hf_stage_pyramid(const HfParams &P, const HfLaunchInfo &li, HfGrid &G) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     HfLevel *s_lvl = hf_s_lvl;                                                                // static __shared__ (hf_traverse.cuh)
     float2 *s_nodes = reinterpret_cast<float2 *>(smem_raw);                                   // levels >= li.top_level_start
@@ -482,7 +540,6 @@ hf_intersect_fast_kernel(const __grid_constant__ HfParams P, const HfLaunchInfo 
         while (!mbar_try_wait(&s_bar, 0)) { if (++spins > (1u << 24)) __trap(); }
     }
 
-    HfGrid G;
     G.W = P.W; G.NX = P.NX; G.NY = P.NY; G.Ltop = P.Ltop; G.mh = P.mh;
     G.x0 = P.x0; G.y0 = P.y0; G.sgx = P.sgx; G.sgy = P.sgy;
     G.heights = P.heights; G.lvl = s_lvl;
@@ -491,64 +548,103 @@ hf_intersect_fast_kernel(const __grid_constant__ HfParams P, const HfLaunchInfo 
         G.top_min = top.x; G.top_max = top.y;
     }
 
+}
+
+#ifndef HF_MIN_CTAS
+#define HF_MIN_CTAS 4
+#endif
+template <int MODE>
+__global__ void __launch_bounds__(HF_BLOCK, HF_MIN_CTAS)
+hf_intersect_fast_kernel(const __grid_constant__ HfParams P, const HfLaunchInfo li, const hf_rays R, const hf_prelim O,
+                         const hf_si S, uint8_t *__restrict__ hit_out, const uint32_t flags, const size_t n) {
+    HfGrid G;
+    hf_stage_pyramid(P, li, G);
+
     const size_t ntiles = (n + HF_BLOCK - 1) / HF_BLOCK;
     for (size_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
         const size_t i = tile * HF_BLOCK + threadIdx.x;
         if (i >= n) continue;
-        const f3 ow = mk3(__ldcs(R.ox + i), __ldcs(R.oy + i), __ldcs(R.oz + i));
-        const f3 dw = mk3(__ldcs(R.dx + i), __ldcs(R.dy + i), __ldcs(R.dz + i));
-        const float maxt = __ldcs(R.maxt + i);
-        const bool active = R.active ? (R.active[i] != 0) : true;
+        hf_process_ray<MODE>(P, G, R, O, S, hit_out, flags, i, 0.f, HF_START_LEVEL);
+    }
+}
 
-        bool hit = false;
-        HfCand c;
-        float ht = HF_INF, hu = 0.f, hv = 0.f;
-        uint32_t hprim = 0u;
-        if (active) {
-            // Transform::transform_affine(ray), src/shapes/rectangle.cpp:206-214: t is preserved
-            const f3 o = xform_point(P.to_object, ow), d = xform_vector(P.to_object, dw);
-            HfWalk w;
-            if (hf_walk_init(G, o.x, o.y, o.z, d.x, d.y, d.z, maxt, w)) {
-                // lanes leave hf_walk_next at different iterations and reconverge here, so the per-cell primitive
-                // runs for all candidate lanes of the warp together
-                while (hf_walk_next(G, w, c)) {
-                    if (cell_intersect(P, c.cx, c.cy, c.z00, c.z10, c.z01, c.z11, o, d, maxt, ht, hu, hv, hprim)) { hit = true; break; }
-                }
+// ------------------------------------------------------------------------------------------
+// Bundled intersection kernel. A warp owns a tile of 32 x 32 = 1024 consecutive rays:
+//   phase A  for each of its 32 groups of 32 consecutive rays, lanes load one ray each and the warp reduces the
+//            component-wise bounds of the object-space directions (shuffles); lane g keeps the bounds of group g.
+//            A group qualifies as a bundle when all its rays leave from one bit-identical origin (primary rays).
+//   phase B  every lane marches ITS bundle through the pyramid (hf_beam_enter): 32 different bundles per warp
+//            instruction instead of 32 copies of the same coarse descent.
+//   phase C  group by group, every lane walks its own ray from the bundle's entry parameter (broadcast by shuffle).
+// Rays that do not form a bundle (different origins, a single active ray) start at 0 as in the plain kernel.
+// Phase A reads the rays with default caching so that phase C finds them in L2; phase C streams (ld.cs / st.cs).
+// ------------------------------------------------------------------------------------------
+#define HF_WARP_TILE 1024
+template <int MODE>
+__global__ void __launch_bounds__(HF_BLOCK, HF_MIN_CTAS)
+hf_intersect_beam_kernel(const __grid_constant__ HfParams P, const HfLaunchInfo li, const hf_rays R, const hf_prelim O,
+                         const hf_si S, uint8_t *__restrict__ hit_out, const uint32_t flags, const size_t n,
+                         unsigned long long *__restrict__ sched) {
+    HfGrid G;
+    hf_stage_pyramid(P, li, G);
+
+    const unsigned lane = threadIdx.x & 31u;
+    const size_t nwt = (n + HF_WARP_TILE - 1) / HF_WARP_TILE;
+    for (;;) {
+        // dynamic tile fetch: tiles differ several-fold in cost (hit / miss regions), a static deal leaves SMs idle at the end
+        unsigned long long wt = 0;
+        if (lane == 0) wt = atomicAdd(sched, 1ull);
+        wt = __shfl_sync(FULL_MASK, wt, 0);
+        if (wt >= nwt) break;
+        const size_t base = (size_t) wt * HF_WARP_TILE;
+        // ---- phase A: bundle bounds, lane g <- group g
+        HfBeam B;
+        B.ogx = B.ogy = B.oz = 0.f; B.dxl = B.dyl = B.dzl = 0.f; B.dxh = B.dyh = B.dzh = 0.f;
+        bool bundle = false;
+        #pragma unroll 2
+        for (unsigned g = 0; g < 32u; ++g) {
+            const size_t i = base + (size_t) g * 32u + lane;
+            bool valid = i < n;
+            if (valid && R.active) valid = R.active[i] != 0;
+            f3 o = mk3(0.f, 0.f, 0.f), d = o;
+            if (valid) {
+                const f3 ow = mk3(__ldg(R.ox + i), __ldg(R.oy + i), __ldg(R.oz + i));
+                const f3 dw = mk3(__ldg(R.dx + i), __ldg(R.dy + i), __ldg(R.dz + i));
+                o = xform_point(P.to_object, ow); d = xform_vector(P.to_object, dw);
+            }
+            const unsigned vm = __ballot_sync(FULL_MASK, valid);
+            const int first = __ffs((int) vm) - 1;
+            const float ox0 = __shfl_sync(FULL_MASK, o.x, first & 31), oy0 = __shfl_sync(FULL_MASK, o.y, first & 31),
+                        oz0 = __shfl_sync(FULL_MASK, o.z, first & 31);
+            const bool fin = (d.x == d.x) && (d.y == d.y) && (d.z == d.z);
+            const bool same = __all_sync(FULL_MASK, !valid || (o.x == ox0 && o.y == oy0 && o.z == oz0 && fin));
+            const float dgx = d.x * P.sgx, dgy = d.y * P.sgy;
+            float xl = valid ? dgx : HF_INF, xh = valid ? dgx : -HF_INF, yl = valid ? dgy : HF_INF, yh = valid ? dgy : -HF_INF;
+            float zl = valid ? d.z : HF_INF, zh = valid ? d.z : -HF_INF;
+            #pragma unroll
+            for (int sft = 16; sft > 0; sft >>= 1) {
+                xl = fminf(xl, __shfl_xor_sync(FULL_MASK, xl, sft)); xh = fmaxf(xh, __shfl_xor_sync(FULL_MASK, xh, sft));
+                yl = fminf(yl, __shfl_xor_sync(FULL_MASK, yl, sft)); yh = fmaxf(yh, __shfl_xor_sync(FULL_MASK, yh, sft));
+                zl = fminf(zl, __shfl_xor_sync(FULL_MASK, zl, sft)); zh = fmaxf(zh, __shfl_xor_sync(FULL_MASK, zh, sft));
+            }
+            if (lane == g) {
+                bundle = same && (__popc(vm) > 1);
+                B.ogx = (ox0 - P.x0) * P.sgx; B.ogy = (oy0 - P.y0) * P.sgy; B.oz = oz0;
+                B.dxl = xl; B.dxh = xh; B.dyl = yl; B.dyh = yh; B.dzl = zl; B.dzh = zh;
             }
         }
-
-        if (MODE == HF_MODE_TEST) {
-            hit_out[i] = hit ? 1 : 0;
-            continue;
-        }
-        if (O.t) {
-            __stcs(O.t + i, hit ? ht : HF_INF);
-            __stcs(O.u + i, hit ? hu : 0.f);
-            __stcs(O.v + i, hit ? hv : 0.f);
-            __stcs(O.prim_index + i, hit ? hprim : 0u);
-        }
-        if (MODE == HF_MODE_FUSED_SI) {
-            if (hit) {
-                // vertices of the hit triangle straight from the candidate-cell registers
-                const float x0 = vtx(c.cx, P.W, P.rw), x1 = vtx(c.cx + 1, P.W, P.rw);
-                const float y0 = vtx(c.cy, P.H, P.rh), y1 = vtx(c.cy + 1, P.H, P.rh);
-                const f3 p0 = mk3(x1, y0, c.z10);
-                f3 p1, p2;
-                if ((hprim & 1u) == 0u) { p1 = mk3(x0, y1, c.z01); p2 = mk3(x0, y0, c.z00); }
-                else { p1 = mk3(x1, y1, c.z11); p2 = mk3(x0, y1, c.z01); }
-                // the world-space ray is only needed by FollowShape and wi: re-read it (L2) instead of keeping six
-                // registers alive across the walk
-                f3 ow2 = mk3(0.f, 0.f, 0.f), dw2 = ow2;
-                if ((flags & HF_RAY_FOLLOWSHAPE) || S.wi_x || S.wi_y || S.wi_z) {
-                    ow2 = mk3(__ldcs(R.ox + i), __ldcs(R.oy + i), __ldcs(R.oz + i));
-                    dw2 = mk3(__ldcs(R.dx + i), __ldcs(R.dy + i), __ldcs(R.dz + i));
-                }
-                write_si(P, S, i, flags, ow2, dw2, ht, hu, hv, p0, p1, p2);
-            } else {
-                f3 dw2 = mk3(0.f, 0.f, 0.f);
-                if (S.wi_x || S.wi_y || S.wi_z) dw2 = mk3(__ldcs(R.dx + i), __ldcs(R.dy + i), __ldcs(R.dz + i));
-                write_si_invalid(S, i, dw2);
-            }
+        // ---- phase B: one bundle per lane
+        float t_enter = 0.f;
+        int L_start = HF_START_LEVEL;
+        if (bundle) t_enter = hf_beam_enter(G, B, L_start);
+        __syncwarp();
+        // ---- phase C: per-ray walks from the bundle entry
+        for (unsigned g = 0; g < 32u; ++g) {
+            const float ts = __shfl_sync(FULL_MASK, t_enter, g);
+            const int ls = __shfl_sync(FULL_MASK, L_start, g);
+            const size_t i = base + (size_t) g * 32u + lane;
+            if (i < n) hf_process_ray<MODE>(P, G, R, O, S, hit_out, flags, i, ts, ls);
+            __syncwarp();
         }
     }
 }
@@ -570,6 +666,19 @@ cudaError_t hf_launch_intersect(const HfParams &P, const HfLaunchInfo &li, int m
         return cudaGetLastError();
     }
     const size_t smem = (size_t) li.top_nodes * sizeof(float2);
+    if (li.use_bundles && mode != HF_MODE_TEST) {
+        const size_t nwt = (n + HF_WARP_TILE - 1) / HF_WARP_TILE, nct = (nwt + HF_BLOCK / 32 - 1) / (HF_BLOCK / 32);
+        const size_t cap = (size_t) li.num_sms * HF_MIN_CTAS;
+        const int bgrid = (int) (nct < cap ? nct : cap);
+        unsigned long long *sched = d_counters + 4;
+        cudaError_t e = cudaMemsetAsync(sched, 0, sizeof(unsigned long long), s);
+        if (e != cudaSuccess) return e;
+        if (mode == HF_MODE_PRELIM)
+            hf_intersect_beam_kernel<HF_MODE_PRELIM><<<bgrid, HF_BLOCK, smem, s>>>(P, li, rays, prelim, si, d_hit, flags, n, sched);
+        else
+            hf_intersect_beam_kernel<HF_MODE_FUSED_SI><<<bgrid, HF_BLOCK, smem, s>>>(P, li, rays, prelim, si, d_hit, flags, n, sched);
+        return cudaGetLastError();
+    }
     switch (mode) {
         case HF_MODE_PRELIM:
             hf_intersect_fast_kernel<HF_MODE_PRELIM><<<grid, HF_BLOCK, smem, s>>>(P, li, rays, prelim, si, d_hit, flags, n); break;

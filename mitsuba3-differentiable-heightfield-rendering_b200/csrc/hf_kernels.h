@@ -12,6 +12,7 @@ struct HfLaunchInfo {
     int top_level_start;     // Ls: pyramid levels >= Ls are staged in shared memory
     int top_nodes;           // node count of levels Ls..Ltop (padded to even)
     int top_off;             // node offset of level Ls
+    int use_bundles;         // 1: bundled kernel (hf_intersect_beam_kernel), 0: plain per-ray kernel
 };
 
 enum HfIntersectMode { HF_MODE_PRELIM = 0, HF_MODE_FUSED_SI = 1, HF_MODE_TEST = 2, HF_MODE_COUNTED = 3 };

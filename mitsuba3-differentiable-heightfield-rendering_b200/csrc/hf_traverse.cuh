@@ -105,7 +105,10 @@ HF_HD int hf_msb(unsigned v) {                     // index of the highest set b
 
 // Clip the object-space ray against the shape's box and set up the walk. Returns false when the ray cannot hit.
 // Arithmetic identical to the canonical traversal (slab semantics of include/mitsuba/core/bbox.h:303-327).
-HF_HD bool hf_walk_init(const HfGrid &G, float ox, float oy, float oz, float dx, float dy, float dz, float maxt, HfWalk &w) {
+// t_start / L_start: the walk may begin at a ray parameter > 0 and at a finer level when the caller knows that the ray
+// cannot touch the surface before t_start (hf_beam_enter below); t_start = 0, L_start = HF_START_LEVEL is the plain walk.
+HF_HD bool hf_walk_init(const HfGrid &G, float ox, float oy, float oz, float dx, float dy, float dz, float maxt, HfWalk &w,
+                        float t_start = 0.f, int L_start = HF_START_LEVEL) {
     w.alive = false;
     if (dx == 0.f && dy == 0.f && dz == 0.f) return false;
     if (!(maxt >= 0.f)) return false;
@@ -137,17 +140,25 @@ HF_HD bool hf_walk_init(const HfGrid &G, float ox, float oy, float oz, float dx,
     w.t1 = t1;
     w.epsz = HF_TRAV_SLACK * (fabsf(oz) + fabsf(t1 * dz));
     w.sx = w.dgx > 0.f ? 1 : 0; w.sy = w.dgy > 0.f ? 1 : 0;
-    w.ix = hf_imin(hf_imax(hf_floor_sat(fmaf(t0, w.dgx, w.ogx)), 0), NX - 1);
-    w.iy = hf_imin(hf_imax(hf_floor_sat(fmaf(t0, w.dgy, w.ogy)), 0), NY - 1);
-    w.L = hf_imin(G.Ltop, HF_START_LEVEL);
-    w.t = t0;
-    w.idz = dz != 0.f ? idz : 0.f;
-    w.zeps = dz < 0.f ? w.epsz : -w.epsz;
     {   // 4 ulp of the largest grid coordinate the ray reaches: a cell derived from a ray parameter is never ahead of the true one
         const float ex = 2.384185791015625e-07f * (fabsf(w.ogx) + fabsf(t1 * w.dgx));
         const float ey = 2.384185791015625e-07f * (fabsf(w.ogy) + fabsf(t1 * w.dgy));
         w.ogxb = w.ogx + (w.sx ? -ex : ex); w.ogyb = w.ogy + (w.sy ? -ey : ey);
     }
+    if (t_start > t0) {            // nothing can be hit before t_start: enter the grid there, one cell back at most
+        if (!(t_start <= t1)) return false;
+        t0 = t_start;
+        w.ix = hf_imin(hf_imax(hf_floor_sat(fmaf(t0, w.dgx, w.ogxb)), 0), NX - 1);
+        w.iy = hf_imin(hf_imax(hf_floor_sat(fmaf(t0, w.dgy, w.ogyb)), 0), NY - 1);
+        w.L = hf_imin(G.Ltop, L_start);
+    } else {
+        w.ix = hf_imin(hf_imax(hf_floor_sat(fmaf(t0, w.dgx, w.ogx)), 0), NX - 1);
+        w.iy = hf_imin(hf_imax(hf_floor_sat(fmaf(t0, w.dgy, w.ogy)), 0), NY - 1);
+        w.L = hf_imin(G.Ltop, HF_START_LEVEL);
+    }
+    w.t = t0;
+    w.idz = dz != 0.f ? idz : 0.f;
+    w.zeps = dz < 0.f ? w.epsz : -w.epsz;
     const float inf = INFINITY;
     w.infx = w.dgx != 0.f ? 0.f : inf; w.infy = w.dgy != 0.f ? 0.f : inf;
     if (w.dgx == 0.f) w.idx = 0.f;
@@ -242,4 +253,109 @@ HF_HD bool hf_walk_next(const HfGrid &G, HfWalk &w, HfCand &c
         if (found) return true;
         if (!w.alive) return false;
     }
+}
+
+// ------------------------------------------------------------------------------------------------------------------
+// Bundle entry: a conservative lower bound of the first-hit parameter shared by a bundle of rays with ONE origin
+// (primary rays of a pixel / an image tile: the 32 consecutive rays a warp loads differ only by a sub-pixel jitter).
+//
+// One lane marches the whole bundle with interval arithmetic: over the parameter segment [t, te] the bundle sweeps the
+// grid-space box  og + [t, te] * [d_lo, d_hi]  (s >= 0, so the extremes sit at the segment ends); the box is covered by at
+// most 2 x 2 nodes of a pyramid level whose node edge is at least the box edge, and if the box's z range clears the
+// (min, max) of those nodes no ray of the bundle can touch a triangle there. The segment doubles after two successes and
+// halves (one level down) after a failure; the march stops when the level is too fine for the bundle's own width. Every
+// ray of the bundle then starts its own walk at the returned parameter, a few cells in front of its hit, instead of at
+// the grid boundary -- which removes most iterations of the per-ray walk and most of the divergence between lanes.
+// Conservative by construction: padding of 1/32 cell + 2^-18 relative on the footprint, HF_TRAV_SLACK on z.
+// ------------------------------------------------------------------------------------------------------------------
+#ifndef HF_BEAM_START_LEVEL
+#define HF_BEAM_START_LEVEL 8
+#endif
+#ifndef HF_BEAM_MAX_ITERS
+#define HF_BEAM_MAX_ITERS 96
+#endif
+#ifndef HF_BEAM_ROOM_FRAC
+#define HF_BEAM_ROOM_FRAC 0.25f
+#endif
+#define HF_BEAM_ALL_MISS 3.0e38f
+
+struct HfBeam {
+    float ogx, ogy, oz;                     // common origin: grid units in x, y; object space z
+    float dxl, dxh, dyl, dyh, dzl, dzh;     // component-wise bounds of (dgx, dgy, dz) over the bundle
+};
+
+// slab [lo, hi] against origin o and direction interval [dl, dh]: narrows [ta, tb] to parameters at which SOME ray of the
+// bundle can be inside the slab (lower bound of every entry, upper bound of every exit)
+HF_HD void hf_beam_slab(float o, float lo, float hi, float dl, float dh, float &ta, float &tb) {
+    if (dl > 0.f) {
+        if (o < lo) ta = fmaxf(ta, (lo - o) / dh);
+        tb = fminf(tb, o < hi ? (hi - o) / dl : -1.f);
+    } else if (dh < 0.f) {
+        if (o > hi) ta = fmaxf(ta, (o - hi) / -dl);
+        tb = fminf(tb, o > lo ? (o - lo) / -dh : -1.f);
+    }
+    // an interval containing 0 constrains nothing (rays that stay outside the slab are sorted out by their own clip)
+}
+
+HF_HD float hf_beam_enter(const HfGrid &G, const HfBeam &b, int &L_start
+#ifndef __CUDACC__
+                          , unsigned *iters = nullptr
+#endif
+) {
+    const int NX = G.NX, NY = G.NY, Ltop = G.Ltop;
+    L_start = hf_imin(Ltop, HF_START_LEVEL);
+    float ta = 0.f, tb = INFINITY;
+    hf_beam_slab(b.ogx, 0.f, (float) NX, b.dxl, b.dxh, ta, tb);
+    hf_beam_slab(b.ogy, 0.f, (float) NY, b.dyl, b.dyh, ta, tb);
+    const float zpad = HF_TRAV_SLACK * (fmaxf(fabsf(G.top_min), fabsf(G.top_max)) + fabsf(b.oz));
+    hf_beam_slab(b.oz, G.top_min - zpad, G.top_max + zpad, b.dzl, b.dzh, ta, tb);
+    ta -= ta * 3.814697265625e-06f; tb += fabsf(tb) * 3.814697265625e-06f;     // 2^-18
+    if (!(ta <= tb)) return HF_BEAM_ALL_MISS;
+    const float dmax = fmaxf(fmaxf(fabsf(b.dxl), fabsf(b.dxh)), fmaxf(fabsf(b.dyl), fabsf(b.dyh)));
+    const float dwid = fmaxf(b.dxh - b.dxl, b.dyh - b.dyl);
+    if (!(dmax > 0.f) || !(tb < INFINITY)) return ta;          // vertical bundle or unbounded range: nothing to march
+    const float rdmax = 1.0f / dmax;
+    const float zmag = fabsf(b.oz) + tb * fmaxf(fabsf(b.dzl), fabsf(b.dzh));
+    const float epsz = 2.f * HF_TRAV_SLACK * zmag;
+    const float pad = 0.03125f + 3.814697265625e-06f * (fmaxf(fabsf(b.ogx), fabsf(b.ogy)) + tb * dmax);
+
+    int L = hf_imin(Ltop, HF_BEAM_START_LEVEL), grow = 0;
+    float t = ta;
+    for (int it = 0; it < HF_BEAM_MAX_ITERS; ++it) {
+#ifndef __CUDACC__
+        if (iters) ++*iters;
+#endif
+        const float span = (float) (1 << L);
+        const float room = span - t * dwid - 1.f;
+        if (room < HF_BEAM_ROOM_FRAC * span) break;                         // the level is too fine for the bundle's own width
+        const float te = fminf(t + room * rdmax, tb);
+        const float xl = b.ogx + fminf(t * b.dxl, te * b.dxl) - pad, xh = b.ogx + fmaxf(t * b.dxh, te * b.dxh) + pad;
+        const float yl = b.ogy + fminf(t * b.dyl, te * b.dyl) - pad, yh = b.ogy + fmaxf(t * b.dyh, te * b.dyh) + pad;
+        const float zl = b.oz + fminf(t * b.dzl, te * b.dzl) - epsz, zh = b.oz + fmaxf(t * b.dzh, te * b.dzh) + epsz;
+        const bool outside = (xh < 0.f) || (xl > (float) NX) || (yh < 0.f) || (yl > (float) NY);
+        const int cxl = hf_imin(hf_imax(hf_floor_sat(xl), 0), NX - 1), cxh = hf_imin(hf_imax(hf_floor_sat(xh), 0), NX - 1);
+        const int cyl = hf_imin(hf_imax(hf_floor_sat(yl), 0), NY - 1), cyh = hf_imin(hf_imax(hf_floor_sat(yh), 0), NY - 1);
+        const unsigned ext = (unsigned) hf_imax(cxh - cxl, cyh - cyl);
+        const int Lq = hf_imin(hf_imax(hf_imax(L, ext ? hf_msb(ext) + 1 : 0), 1), Ltop);     // 2^Lq >= ext + 1: at most 2 nodes per axis
+#ifdef __CUDACC__
+        const HfLevel lv = hf_s_lvl[Lq];
+#else
+        const HfLevel lv = G.lvl[Lq];
+#endif
+        const int nxl = cxl >> Lq, nxh = cxh >> Lq, nyl = cyl >> Lq, nyh = cyh >> Lq;
+        const float2 a0 = lv.nodes[nyl * lv.w + nxl], a1 = lv.nodes[nyl * lv.w + nxh];
+        const float2 a2 = lv.nodes[nyh * lv.w + nxl], a3 = lv.nodes[nyh * lv.w + nxh];
+        const float mn = fminf(fminf(a0.x, a1.x), fminf(a2.x, a3.x)), mx = fmaxf(fmaxf(a0.y, a1.y), fmaxf(a2.y, a3.y));
+        const bool safe = outside || (zl > mx) || (zh < mn);
+        if (safe) {
+            t = te;
+            if (!(te < tb)) return HF_BEAM_ALL_MISS;
+            if (++grow >= 2 && L < Ltop) { ++L; grow = 0; }
+        } else {
+            grow = 0;
+            if (--L < 1) break;
+        }
+    }
+    L_start = hf_imin(hf_imin(hf_imax(L + 1, 1), HF_START_LEVEL), Ltop);
+    return fmaxf(t - t * 3.814697265625e-06f, 0.f);
 }

@@ -409,3 +409,40 @@ def test_full_size_invariants(hf, oracle):
     ref = c.backward(cr_all, pc_all, _adj_np({k: v.cpu().numpy() for k, v in adj.items()}), literal=False)
     got = _np(g1).astype(np.float64)
     assert np.linalg.norm(got - ref) <= 1e-4 * np.linalg.norm(ref)
+
+
+# ---- bundled kernel (hf_intersect_beam_kernel): identical answers to the plain kernel and the oracle -------------
+def test_bundled_kernel_bit_identical(hf, oracle, monkeypatch):
+    """HF_B200_BUNDLES=1 routes ray_intersect / ray_intersect_preliminary through the bundle march. Camera rays (bundles form),
+    random rays (no bundles), ragged sizes, an active mask and a transformed shape: bit-identical to the plain kernel."""
+    from hfb200 import workloads as wl
+    dev = "cuda"
+    h = wl.fbm_heights(1024, octaves=8, seed=0xC3, device=dev)
+    tw = np.array([[0.9, 0.1, 0.0, 0.05], [-0.1, 0.9, 0.05, -0.02], [0.0, 0.02, 1.1, 0.01]], np.float32)
+    for to_world in (None, tw):
+        props = {"type": "heightfield", "heights": h, "max_height": 0.3}
+        if to_world is not None:
+            props["to_world"] = to_world
+        monkeypatch.setenv("HF_B200_BUNDLES", "0")
+        plain = hf.load_dict(dict(props))
+        monkeypatch.setenv("HF_B200_BUNDLES", "1")
+        bund = hf.load_dict(dict(props))
+        o, d = wl.config_rays("C3", device=dev, image=96, spp=64, tile=32)
+        rng = np.random.default_rng(5)
+        ro, rd = random_rays(rng, 50001)
+        o = torch.cat([o, torch.from_numpy(ro.T.copy()).to(dev)], 1)[:, :-7]      # ragged: not a multiple of 32
+        d = torch.cat([d, torch.from_numpy(rd.T.copy()).to(dev)], 1)[:, :-7]
+        n = o.shape[1]
+        active = torch.from_numpy((rng.uniform(size=n) < 0.95)).to(dev)
+        ray = hf.Ray3f(o, d)
+        for act in (None, active):
+            sa, pa = plain.ray_intersect(ray, return_prelim=True, active=act)
+            sb, pb = bund.ray_intersect(ray, return_prelim=True, active=act)
+            assert torch.equal(pa.t.view(torch.int32), pb.t.view(torch.int32))
+            assert torch.equal(pa.prim_index, pb.prim_index)
+            assert torch.equal(pa.prim_uv.view(torch.int32), pb.prim_uv.view(torch.int32))
+            assert torch.equal(sa.p.view(torch.int32), sb.p.view(torch.int32))
+            assert torch.equal(sa.n.view(torch.int32), sb.n.view(torch.int32))
+            pc = bund.ray_intersect_preliminary(ray, active=act)
+            assert torch.equal(pa.t.view(torch.int32), pc.t.view(torch.int32))
+        assert 0.3 < float(pa.is_valid().float().mean()) < 1.0

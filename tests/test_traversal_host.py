@@ -1,0 +1,119 @@
+"""The production walk (csrc/hf_traverse.cuh) instantiated on the HOST and checked bit-for-bit against the oracle's canonical DDA (which test_oracle.py pins to brute force):
+conservativeness of the warp-uniform hierarchical DDA and of the bundle march (hf_beam_enter) on random, adversarial
+and camera rays -- without a GPU. The GPU parity tests then pin the device build of the same header to the oracle."""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+from util import adversarial_rays, random_heights, random_rays
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.fixture(scope="module")
+def trav(oracle, tmp_path_factory):
+    so = str(tmp_path_factory.mktemp("trav") / "trav_host.so")
+    subprocess.check_call(["g++", "-O2", "-std=c++17", "-ffp-contract=off", "-fopenmp", "-fPIC", "-shared", "-o", so,
+                           os.path.join(ROOT, "tests", "trav_host.cpp"), "-L" + os.path.join(ROOT, "oracle", "_build"),
+                           "-lhf_oracle", "-Wl,-rpath," + os.path.join(ROOT, "oracle", "_build")])
+    O = oracle
+    L = C.CDLL(so)
+    L.trav_host_intersect.argtypes = [C.POINTER(O._Shape), C.POINTER(O._Rays), C.c_size_t, C.POINTER(O._Prelim), O._u32p, O._u32p, O._u32p]
+    L.trav_host_intersect_beam.argtypes = [C.POINTER(O._Shape), C.POINTER(O._Rays), C.c_size_t, C.POINTER(O._Prelim), O._u32p, O._u32p,
+                                           O._u32p, O._f32p]
+    return L
+
+
+def _run(L, O, hf, rays, beam):
+    out = O.Prelim(rays.n)
+    s, r, o = hf._shape(), rays.c(), out.c()
+    if beam:
+        te = np.zeros((rays.n + 31) // 32, np.float32)
+        L.trav_host_intersect_beam(C.byref(s), C.byref(r), rays.n, C.byref(o), None, None, None, te.ctypes.data_as(O._f32p))
+        return out, te
+    L.trav_host_intersect(C.byref(s), C.byref(r), rays.n, C.byref(o), None, None, None)
+    return out, None
+
+
+def _same(a, b):
+    return (a.t.view(np.uint32) == b.t.view(np.uint32)) & (a.prim_index == b.prim_index) & (a.u.view(np.uint32) == b.u.view(np.uint32)) & \
+           (a.v.view(np.uint32) == b.v.view(np.uint32))
+
+
+@pytest.mark.parametrize("H,W,kind", [(2, 2, "noise"), (3, 2, "noise"), (5, 7, "smooth"), (17, 17, "smooth"), (33, 20, "noise"),
+                                      (64, 65, "smooth"), (12, 12, "flat"), (300, 257, "smooth")])
+def test_walk_equals_canonical_dda(oracle, trav, H, W, kind):
+    O = oracle
+    rng = np.random.default_rng(H * 131 + W)
+    hf = O.OracleHeightfield(random_heights(rng, H, W, kind), 0.7)
+    n = 60000 if H * W > 5000 else 200000
+    o, d = random_rays(rng, n)
+    ao, ad = adversarial_rays(W, H, 0.7)
+    o, d = np.concatenate([o, ao]), np.concatenate([d, ad])
+    maxt = np.where(rng.uniform(size=o.shape[0]) < 0.15, rng.uniform(0.5, 4, o.shape[0]), np.inf).astype(np.float32)
+    r = O.Rays(o, d, maxt)
+    ref = hf.ray_intersect_preliminary(r)          # canonical DDA; test_oracle.py pins it to brute force away from ties
+    got, _ = _run(trav, O, hf, r, beam=False)
+    assert _same(ref, got).all()
+    got, _ = _run(trav, O, hf, r, beam=True)      # random origins: no bundles form, same path through the other entry
+    assert _same(ref, got).all()
+
+
+def _bundle_rays(rng, n_bundles, origin_fn, spread):
+    """n_bundles x 32 rays; every bundle has one origin and directions within `spread` of a random aim point."""
+    o = np.repeat(origin_fn(n_bundles), 32, axis=0)
+    aim = np.stack([rng.uniform(-1.2, 1.2, n_bundles), rng.uniform(-1.2, 1.2, n_bundles), rng.uniform(0.0, 0.6, n_bundles)], 1)
+    tgt = np.repeat(aim, 32, axis=0) + rng.uniform(-1, 1, (n_bundles * 32, 3)) * np.repeat(spread(n_bundles), 32, axis=0)[:, None]
+    d = tgt - o
+    d *= np.repeat(rng.uniform(0.2, 3.0, (n_bundles, 1)), 32, axis=0)
+    return o.astype(np.float32), d.astype(np.float32)
+
+
+@pytest.mark.parametrize("H,W,kind,mh", [(64, 65, "smooth", 0.7), (33, 20, "noise", 0.7), (257, 300, "smooth", 0.3), (12, 12, "flat", 1.0),
+                                          (2, 2, "noise", 1.0), (513, 513, "noise", 0.05)])
+def test_bundle_march_is_conservative(oracle, trav, H, W, kind, mh):
+    """Bundles from above, from below, from inside the box, grazing and wide: the bundled walk must give the canonical answer."""
+    O = oracle
+    rng = np.random.default_rng(H * 7 + W)
+    hf = O.OracleHeightfield(random_heights(rng, H, W, kind), mh)
+    nb = 1500 if H * W > 50000 else 4000
+    sets = [
+        (lambda k: np.stack([rng.uniform(-2, 2, k), rng.uniform(-2, 2, k), rng.uniform(0.8, 3, k)], 1), lambda k: rng.uniform(1e-4, 0.05, k)),   # above
+        (lambda k: np.stack([rng.uniform(-2, 2, k), rng.uniform(-2, 2, k), rng.uniform(-2, -0.1, k)], 1), lambda k: rng.uniform(1e-4, 0.05, k)),  # below
+        (lambda k: np.stack([rng.uniform(-1, 1, k), rng.uniform(-1, 1, k), rng.uniform(0, mh, k)], 1), lambda k: rng.uniform(1e-3, 0.3, k)),      # inside
+        (lambda k: np.stack([rng.uniform(-3, -1.2, k), rng.uniform(-1, 1, k), rng.uniform(0.3 * mh, 1.1 * mh, k)], 1), lambda k: rng.uniform(1e-4, 0.02, k)),  # grazing
+        (lambda k: np.stack([rng.uniform(-2, 2, k), rng.uniform(-2, 2, k), rng.uniform(0.5, 3, k)], 1), lambda k: rng.uniform(0.3, 1.5, k)),      # wide
+    ]
+    skipped = 0
+    for origin_fn, spread in sets:
+        o, d = _bundle_rays(rng, nb, origin_fn, spread)
+        maxt = np.where(rng.uniform(size=o.shape[0]) < 0.1, rng.uniform(0.5, 4, o.shape[0]), np.inf).astype(np.float32)
+        active = (rng.uniform(size=o.shape[0]) < 0.97).astype(np.uint8)
+        r = O.Rays(o, d, maxt, active)
+        ref = hf.ray_intersect_preliminary(r)
+        got, te = _run(trav, O, hf, r, beam=True)
+        bad = ~_same(ref, got)
+        assert not bad.any(), f"{int(bad.sum())} mismatches, first at ray {int(np.nonzero(bad)[0][0])}"
+        skipped += int((te > 0).sum())
+    assert skipped > 0 or H * W <= 4          # the march actually advanced some bundles
+
+
+def test_bundle_march_on_camera_rays(oracle, trav):
+    import torch
+    import hfb200
+    from hfb200 import workloads as wl
+    O = oracle
+    h = wl.fbm_heights(1024, octaves=8, seed=0xC3).numpy()
+    hf = O.OracleHeightfield(h, 0.3)
+    cam = wl.CONFIGS["C3"]["camera"]
+    pix = torch.arange(0, 1024 * 1024, 523, dtype=torch.int64)
+    o, d = wl.camera_rays(cam["origin"], cam["target"], cam["up"], cam["fov"], 1024, 1024, 64, seed=0, pixels=pix)
+    r = O.Rays(o.numpy().T, d.numpy().T)
+    ref = hf.ray_intersect_preliminary(r)
+    got, te = _run(trav, O, hf, r, beam=True)
+    assert _same(ref, got).all()
+    hitb = ref.valid().reshape(-1, 32).any(1)
+    assert (te[hitb] > 0).mean() > 0.9     # nearly every hit bundle skipped part of its way

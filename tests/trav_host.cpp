@@ -74,3 +74,85 @@ extern "C" int trav_host_intersect(const hfo_shape *s, const hfo_rays *r, size_t
     hfo_pyramid_free(p);
     return 0;
 }
+
+// Bundled variant: every 32 consecutive rays with a bit-identical origin form a bundle; hf_beam_enter gives the bundle's
+// entry parameter and each ray walks from there. beam_iters (nullable): uint32[n/32] iterations of the bundle march.
+extern "C" int trav_host_intersect_beam(const hfo_shape *s, const hfo_rays *r, size_t n, hfo_prelim *out,
+                                        uint32_t *iters, uint32_t *cands, uint32_t *beam_iters, float *t_enter_out) {
+    hfo_pyramid *p = hfo_pyramid_build(s);
+    const int Ltop = hfo_pyramid_levels(p);
+    std::vector<HfLevel> lvl(Ltop + 1);
+    lvl[0].nodes = nullptr; lvl[0].w = 0;
+    for (int l = 1; l <= Ltop; ++l) {
+        int w, h;
+        hfo_pyramid_level_dims(p, l, &w, &h);
+        lvl[l].nodes = reinterpret_cast<const float2 *>(hfo_pyramid_level_data(p, l));
+        lvl[l].w = w;
+    }
+    HfGrid G;
+    G.W = s->W; G.NX = s->W - 1; G.NY = s->H - 1; G.Ltop = Ltop; G.mh = s->max_height;
+    const float rw = 1.0f / (float) G.NX, rh = 1.0f / (float) G.NY;
+    G.x0 = (float) (-(s->W - 1)) * rw; G.y0 = (float) (-(s->H - 1)) * rh;
+    G.sgx = 0.5f * (float) G.NX; G.sgy = 0.5f * (float) G.NY;
+    G.heights = s->heights; G.lvl = lvl.data();
+    G.top_min = lvl[Ltop].nodes[0].x; G.top_max = lvl[Ltop].nodes[0].y;
+    const float *m = s->to_object;
+    auto xf = [&](size_t i, float o[3], float d[3]) {
+        const float ow[3] = { r->ox[i], r->oy[i], r->oz[i] }, dw[3] = { r->dx[i], r->dy[i], r->dz[i] };
+        for (int a = 0; a < 3; ++a) {
+            float v = m[4 * a + 3];
+            v = fmaf(m[4 * a + 0], ow[0], v); v = fmaf(m[4 * a + 1], ow[1], v); v = fmaf(m[4 * a + 2], ow[2], v);
+            o[a] = v;
+            float q = m[4 * a + 0] * dw[0];
+            q = fmaf(m[4 * a + 1], dw[1], q); q = fmaf(m[4 * a + 2], dw[2], q);
+            d[a] = q;
+        }
+    };
+    const long long ngroups = (long long) ((n + 31) / 32);
+    #pragma omp parallel for schedule(dynamic, 64)
+    for (long long g = 0; g < ngroups; ++g) {
+        const size_t i0 = (size_t) g * 32, i1 = i0 + 32 < n ? i0 + 32 : n;
+        // bundle bounds (what the kernel gets from warp shuffles)
+        bool same = true; int nact = 0;
+        HfBeam b; b.dxl = b.dyl = b.dzl = INFINITY; b.dxh = b.dyh = b.dzh = -INFINITY; b.ogx = b.ogy = b.oz = 0.f;
+        float o0[3] = { 0, 0, 0 };
+        for (size_t i = i0; i < i1; ++i) {
+            if (r->active && !r->active[i]) continue;
+            float o[3], d[3]; xf(i, o, d);
+            if (nact == 0) { o0[0] = o[0]; o0[1] = o[1]; o0[2] = o[2]; }
+            else if (memcmp(o, o0, sizeof(o0)) != 0) same = false;
+            const float dgx = d[0] * G.sgx, dgy = d[1] * G.sgy;
+            b.dxl = fminf(b.dxl, dgx); b.dxh = fmaxf(b.dxh, dgx); b.dyl = fminf(b.dyl, dgy); b.dyh = fmaxf(b.dyh, dgy);
+            b.dzl = fminf(b.dzl, d[2]); b.dzh = fmaxf(b.dzh, d[2]);
+            if (!(d[0] == d[0] && d[1] == d[1] && d[2] == d[2])) same = false;
+            ++nact;
+        }
+        float t_enter = 0.f; int L_start = HF_START_LEVEL; unsigned bit = 0;
+        if (same && nact > 1) {
+            b.ogx = (o0[0] - G.x0) * G.sgx; b.ogy = (o0[1] - G.y0) * G.sgy; b.oz = o0[2];
+            t_enter = hf_beam_enter(G, b, L_start, &bit);
+        }
+        if (beam_iters) beam_iters[g] = bit;
+        if (t_enter_out) t_enter_out[g] = t_enter;
+        for (size_t i = i0; i < i1; ++i) {
+            unsigned it = 0, nc = 0;
+            float bt = INFINITY, bu = 0.f, bv = 0.f; uint32_t bp = 0;
+            if (!r->active || r->active[i]) {
+                float o[3], d[3]; xf(i, o, d);
+                HfWalk w; HfCand c;
+                if (hf_walk_init(G, o[0], o[1], o[2], d[0], d[1], d[2], r->maxt[i], w, t_enter, L_start)) {
+                    while (hf_walk_next(G, w, c, &it)) {
+                        ++nc;
+                        float t, u, v; uint32_t prim;
+                        if (hfo_cell_intersect(s, c.cx, c.cy, o, d, r->maxt[i], &t, &u, &v, &prim)) { bt = t; bu = u; bv = v; bp = prim; break; }
+                    }
+                }
+            }
+            out->t[i] = bt; out->u[i] = bu; out->v[i] = bv; out->prim_index[i] = bp;
+            if (iters) iters[i] = it;
+            if (cands) cands[i] = nc;
+        }
+    }
+    hfo_pyramid_free(p);
+    return 0;
+}
