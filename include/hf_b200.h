@@ -172,6 +172,53 @@ int hf_comm_init(hf_ctx *ctx, int rank, int nranks, const uint8_t id[128]);
 int hf_comm_destroy(hf_ctx *ctx);
 int hf_allreduce_grad(hf_ctx *ctx, void *stream);                  /* ncclAllReduce(grad, fp32, sum) */
 
+/* ---- render step on the heightfield alone ----------------------------------------------
+ * The callers of the shape in the reference, restated for ONE heightfield lit by ONE directional emitter and seen by
+ * ONE perspective sensor, so that an inverse-rendering step runs without materialising rays or interaction records:
+ *   sensor      perspective pinhole, src/sensors/perspective.cpp:198-234 (origin = camera position, normalised direction,
+ *               maxt = +inf); sample index = pixel * spp + sample as in src/render/integrator.cpp:251-265; the sub-pixel
+ *               position comes from an integer hash of (seed, index) instead of the PCG32 sampler stream
+ *   emitter     directional, src/emitters/directional.cpp (irradiance E arriving along `direction`)
+ *   bsdf        Lambertian, src/bsdfs/diffuse.cpp: f * cos = albedo / pi * max(0, n . wo)
+ *   integrator  direct illumination of the first hit, src/integrators/direct.cpp:114-210; with shadow_rays != 0 the
+ *               emitter is tested for visibility with a ray spawned as in include/mitsuba/render/interaction.h:136-165
+ *   film        box reconstruction filter: a sample contributes to its own pixel only (src/render/imageblock.cpp:119-132
+ *               with a 0.5-radius box), pixel = mean of its spp samples
+ *   adjoint     PRB-style replay (src/python/python/ad/integrators/common.py:784-970): d(image) arrives per pixel, is
+ *               spread to the samples, and reaches the heights through the normal of the hit triangle (visibility and
+ *               the hit position are detached, as in prb_basic.py without reparameterisation)
+ * Images are single-channel fp32, row-major (height, width), indexed by pixel id y * width + x. `d_pixels` lists the
+ * pixel ids this context renders (image-tile shard of a rank); NULL = every pixel, npix = width * height. */
+typedef struct {
+    float origin[3];               /* world space */
+    float right[3], up[3], forward[3];   /* orthonormal camera frame, world space */
+    float tan_half_fov;            /* of the horizontal field of view */
+    uint32_t width, height, spp;
+    uint32_t seed;
+} hf_camera;
+
+typedef struct {
+    float direction[3];            /* unit vector FROM the surface TOWARDS the emitter, world space */
+    float irradiance;              /* E */
+    float albedo;                  /* Lambertian reflectance */
+    int32_t shadow_rays;           /* != 0: one visibility ray per shaded sample */
+} hf_light;
+
+/* the rays the render entry points generate, written out as an hf_rays-shaped SoA (index = k * spp + sample for the k-th
+ * listed pixel); lets a caller run the same batch through hf_ray_intersect / hf_backward */
+int hf_render_rays(hf_ctx *ctx, const hf_camera *cam, const uint32_t *d_pixels, size_t npix, const hf_rays *d_out, void *stream);
+/* primal image. d_prim (nullable): npix * spp hit triangles (0xffffffff = miss / unlit) for hf_render_backward */
+int hf_render_forward(hf_ctx *ctx, const hf_camera *cam, const hf_light *light, const uint32_t *d_pixels, size_t npix,
+                      float *d_image, uint32_t *d_prim, void *stream);
+/* d(loss)/d(heights) += J^T d_adj_image. d_prim from hf_render_forward of the SAME heights, or NULL to re-trace */
+int hf_render_backward(hf_ctx *ctx, const hf_camera *cam, const hf_light *light, const uint32_t *d_pixels, size_t npix,
+                       const float *d_adj_image, const uint32_t *d_prim, void *stream);
+/* forward + L2 loss against d_target + backward in ONE pass (a warp owns a pixel, so the pixel's adjoint
+ * 2 (I - T) / (width * height) is known before its samples leave the registers). Writes the pixels it rendered to
+ * d_image (nullable) and ADDS sum (I - T)^2 / (width * height) over them to *d_loss (nullable, device double). */
+int hf_render_step_l2(hf_ctx *ctx, const hf_camera *cam, const hf_light *light, const uint32_t *d_pixels, size_t npix,
+                      const float *d_target, float *d_image, double *d_loss, void *stream);
+
 /* ---- host-buffer entry points (the llvm_ad_rgb caller keeps its arrays in host memory) ---
  * rays / outputs / adjoints are HOST pointers (pinned memory gives full PCIe bandwidth; use
  * hf_host_alloc). The call stages chunks through device buffers, overlapping H2D, kernels and

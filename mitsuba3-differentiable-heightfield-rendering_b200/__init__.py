@@ -27,7 +27,8 @@ import numpy as np
 import torch
 
 __all__ = ["RayFlags", "Ray3f", "PreliminaryIntersection3f", "SurfaceInteraction3f", "Heightfield",
-           "load_dict", "traverse", "SceneParameters", "Adam", "lib_path", "HeightfieldError"]
+           "load_dict", "traverse", "SceneParameters", "Adam", "lib_path", "HeightfieldError", "perspective_camera",
+           "directional_light"]
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _LIB = os.environ.get("HF_B200_LIB") or os.path.join(_HERE, "lib", "libhf_b200.so")   # override: kernel experiments only
@@ -93,6 +94,15 @@ class _Adam(C.Structure):
                 ("mask_updates", C.c_int32)]
 
 
+class _Camera(C.Structure):
+    _fields_ = [("origin", C.c_float * 3), ("right", C.c_float * 3), ("up", C.c_float * 3), ("forward", C.c_float * 3),
+                ("tan_half_fov", C.c_float), ("width", C.c_uint32), ("height", C.c_uint32), ("spp", C.c_uint32), ("seed", C.c_uint32)]
+
+
+class _Light(C.Structure):
+    _fields_ = [("direction", C.c_float * 3), ("irradiance", C.c_float), ("albedo", C.c_float), ("shadow_rays", C.c_int32)]
+
+
 class _Stats(C.Structure):
     _fields_ = [(k, C.c_uint64) for k in ("rays", "nodes", "leaves", "hits")]
 
@@ -141,6 +151,10 @@ def _load():
         "hf_comm_init": [vp, C.c_int, C.c_int, C.POINTER(C.c_uint8)],
         "hf_comm_destroy": [vp],
         "hf_allreduce_grad": [vp, vp],
+        "hf_render_rays": [vp, C.POINTER(_Camera), vp, sz, C.POINTER(_Rays), vp],
+        "hf_render_forward": [vp, C.POINTER(_Camera), C.POINTER(_Light), vp, sz, vp, vp, vp],
+        "hf_render_backward": [vp, C.POINTER(_Camera), C.POINTER(_Light), vp, sz, vp, vp, vp],
+        "hf_render_step_l2": [vp, C.POINTER(_Camera), C.POINTER(_Light), vp, sz, vp, vp, vp, vp],
         "hf_host_alloc": [C.POINTER(vp), sz],
         "hf_host_free": [vp],
         "hf_ray_intersect_host": [vp, C.POINTER(_Rays), u32, C.POINTER(_Prelim), C.POINTER(_SI), sz],
@@ -505,6 +519,57 @@ class Heightfield:
         with torch.cuda.device(self.device):
             _check(_load().hf_allreduce_grad(self._ctx, _stream()))
 
+    # -- render step on the heightfield alone (sensor + direct illumination + film + adjoint) ------
+    def _pixels(self, cam, pixels):
+        if pixels is None:
+            return None, int(cam["width"]) * int(cam["height"])
+        t = torch.as_tensor(pixels, device=self.device).to(torch.int32).contiguous()     # uint32 bit pattern
+        return t, t.numel()
+
+    def render_rays(self, cam: dict, pixels=None) -> "Ray3f":
+        """The primary rays the render entry points generate (index = k * spp + sample for the k-th listed pixel)."""
+        c = _camera_struct(cam)
+        px, npix = self._pixels(cam, pixels)
+        n = npix * c.spp
+        ray = Ray3f(torch.empty((3, n), device=self.device), torch.empty((3, n), device=self.device),
+                    torch.empty(n, device=self.device), device=self.device)
+        r = ray._c()
+        with torch.cuda.device(self.device):
+            _check(_load().hf_render_rays(self._ctx, C.byref(c), _ptr(px), npix, C.byref(r), _stream()))
+        return ray
+
+    def render_forward(self, cam: dict, light: dict, pixels=None, image=None, return_prims=False):
+        """Primal image (height, width) fp32; pixels not listed keep their previous value (zeros for a fresh image)."""
+        c, l = _camera_struct(cam), _light_struct(light)
+        px, npix = self._pixels(cam, pixels)
+        if image is None:
+            image = torch.zeros((c.height, c.width), dtype=torch.float32, device=self.device)
+        prims = torch.empty(npix * c.spp, dtype=torch.int32, device=self.device) if return_prims else None
+        with torch.cuda.device(self.device):
+            _check(_load().hf_render_forward(self._ctx, C.byref(c), C.byref(l), _ptr(px), npix, _ptr(image), _ptr(prims), _stream()))
+        return (image, prims) if return_prims else image
+
+    def render_backward(self, cam: dict, light: dict, adj_image, pixels=None, prims=None):
+        """self.grad += J^T adj_image (ADIntegrator.render_backward, common.py:784-970, for this one shape)."""
+        c, l = _camera_struct(cam), _light_struct(light)
+        px, npix = self._pixels(cam, pixels)
+        adj = torch.as_tensor(adj_image, dtype=torch.float32, device=self.device).contiguous()
+        if adj.numel() != c.width * c.height:
+            raise HeightfieldError("adjoint image has the wrong size")
+        with torch.cuda.device(self.device):
+            _check(_load().hf_render_backward(self._ctx, C.byref(c), C.byref(l), _ptr(px), npix, _ptr(adj), _ptr(prims), _stream()))
+
+    def render_step_l2(self, cam: dict, light: dict, target, pixels=None, image=None, loss=None):
+        """Forward + L2 loss against `target` + backward in one kernel. `loss`: 1-element float64 device tensor that the
+        call ADDS mean-squared-error contributions to (or None)."""
+        c, l = _camera_struct(cam), _light_struct(light)
+        px, npix = self._pixels(cam, pixels)
+        if target.dtype != torch.float32 or not target.is_contiguous() or target.numel() != c.width * c.height:
+            raise HeightfieldError("target must be a contiguous fp32 (height, width) device tensor")
+        with torch.cuda.device(self.device):
+            _check(_load().hf_render_step_l2(self._ctx, C.byref(c), C.byref(l), _ptr(px), npix, _ptr(target), _ptr(image), _ptr(loss), _stream()))
+        return image
+
     # -- host-buffer path (llvm_ad_rgb keeps its arrays in host memory) ------------------------
     def forward_backward_host(self, h_rays: dict, h_adj: dict, h_si: dict, h_grad, n, ray_flags=RayFlags.All,
                               h_prelim: dict | None = None):
@@ -529,6 +594,46 @@ class Heightfield:
     def __repr__(self):
         return (f"Heightfield[\n  size = {self.W}x{self.H},\n  max_height = {self._max_height},\n"
                 f"  primitive_count = {self.primitive_count()},\n  flip_normals = {self.flip_normals}\n]")
+
+
+def perspective_camera(origin, target, up, fov, width, height, spp, seed=0) -> dict:
+    """`perspective` sensor with to_world = look_at(origin, target, up) and a horizontal field of view `fov` in degrees
+    (src/sensors/perspective.cpp:63-150): the orthonormal frame is computed in fp64 and rounded to fp32."""
+    o, t, u = (np.asarray(x, np.float64) for x in (origin, target, up))
+    f = t - o
+    f /= np.linalg.norm(f)
+    r = np.cross(f, u)
+    r /= np.linalg.norm(r)
+    upv = np.cross(r, f)
+    f32 = lambda v: [float(np.float32(x)) for x in v]
+    return {"origin": f32(o), "right": f32(r), "up": f32(upv), "forward": f32(f),
+            "tan_half_fov": float(np.float32(np.tan(np.radians(fov) * 0.5))), "width": int(width), "height": int(height),
+            "spp": int(spp), "seed": int(seed)}
+
+
+def directional_light(towards, irradiance=1.0, albedo=1.0, shadow_rays=False) -> dict:
+    """`directional` emitter seen from the surface (unit vector towards the emitter) + the `diffuse` BSDF's reflectance."""
+    d = np.asarray(towards, np.float64)
+    d /= np.linalg.norm(d)
+    return {"direction": [float(np.float32(x)) for x in d], "irradiance": float(irradiance), "albedo": float(albedo),
+            "shadow_rays": bool(shadow_rays)}
+
+
+def _camera_struct(cam: dict) -> _Camera:
+    c = _Camera()
+    for k in ("origin", "right", "up", "forward"):
+        getattr(c, k)[:] = [float(x) for x in cam[k]]
+    c.tan_half_fov = float(cam["tan_half_fov"])
+    c.width, c.height, c.spp, c.seed = int(cam["width"]), int(cam["height"]), int(cam["spp"]), int(cam.get("seed", 0))
+    return c
+
+
+def _light_struct(light: dict) -> _Light:
+    l = _Light()
+    l.direction[:] = [float(x) for x in light["direction"]]
+    l.irradiance, l.albedo = float(light.get("irradiance", 1.0)), float(light.get("albedo", 1.0))
+    l.shadow_rays = int(bool(light.get("shadow_rays", False)))
+    return l
 
 
 def comm_unique_id() -> bytes:

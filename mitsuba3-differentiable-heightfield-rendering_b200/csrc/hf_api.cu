@@ -555,6 +555,98 @@ extern "C" int hf_allreduce_grad(hf_ctx *c, void *stream) {
 }
 
 // ------------------------------------------------------------------------------------------
+// render step (sensor + direct illumination + film + adjoint on the heightfield alone)
+// ------------------------------------------------------------------------------------------
+static int check_camera(const hf_camera *cam, bool needs_stash) {
+    if (!cam) return fail(HF_ERR_INVALID, "null camera");
+    if (cam->width == 0 || cam->height == 0 || cam->spp == 0) return fail(HF_ERR_INVALID, "camera: width, height and spp must be positive");
+    if ((uint64_t) cam->width * cam->height > 0xffffffffull) return fail(HF_ERR_INVALID, "camera: pixel ids would overflow uint32");
+    if (!(cam->tan_half_fov > 0.f) || !isfinite(cam->tan_half_fov)) return fail(HF_ERR_INVALID, "camera: tan_half_fov must be positive and finite");
+    if (needs_stash && cam->spp > HF_RENDER_MAX_SPP_HOST)
+        return fail(HF_ERR_INVALID, "camera: spp = %u exceeds %d for the adjoint passes (split the samples over several seeds)", cam->spp, HF_RENDER_MAX_SPP_HOST);
+    // the bundle march relies on an orthonormal frame (|fwd + sx right + sy up| >= 1)
+    const float *r = cam->right, *up = cam->up, *f = cam->forward;
+    auto dot = [](const float *a, const float *b) { return (double) a[0] * b[0] + (double) a[1] * b[1] + (double) a[2] * b[2]; };
+    for (int k = 0; k < 3; ++k) if (!isfinite(cam->origin[k]) || !isfinite(r[k]) || !isfinite(up[k]) || !isfinite(f[k])) return fail(HF_ERR_INVALID, "camera: non-finite entry");
+    if (fabs(dot(r, r) - 1) > 1e-4 || fabs(dot(up, up) - 1) > 1e-4 || fabs(dot(f, f) - 1) > 1e-4 || fabs(dot(r, up)) > 1e-4 ||
+        fabs(dot(r, f)) > 1e-4 || fabs(dot(up, f)) > 1e-4)
+        return fail(HF_ERR_INVALID, "camera: right / up / forward must be orthonormal");
+    return HF_OK;
+}
+static int check_light(const hf_light *l) {
+    if (!l) return fail(HF_ERR_INVALID, "null light");
+    const double n2 = (double) l->direction[0] * l->direction[0] + (double) l->direction[1] * l->direction[1] + (double) l->direction[2] * l->direction[2];
+    if (!(fabs(n2 - 1) < 1e-4)) return fail(HF_ERR_INVALID, "light: direction must be a unit vector");
+    if (!isfinite(l->irradiance) || !isfinite(l->albedo)) return fail(HF_ERR_INVALID, "light: non-finite irradiance / albedo");
+    return HF_OK;
+}
+static int check_pixels(const hf_camera *cam, const uint32_t *d_pixels, size_t npix) {
+    const size_t all = (size_t) cam->width * cam->height;
+    if (!d_pixels && npix != all) return fail(HF_ERR_INVALID, "npix must be width * height when no pixel list is given");
+    if (npix > all) return fail(HF_ERR_INVALID, "more listed pixels than the image has");
+    return HF_OK;
+}
+
+extern "C" int hf_render_rays(hf_ctx *c, const hf_camera *cam, const uint32_t *d_pixels, size_t npix, const hf_rays *d_out, void *stream) {
+    CHECK_CTX(c);
+    int rc;
+    if ((rc = check_camera(cam, false)) || (rc = check_pixels(cam, d_pixels, npix))) return rc;
+    if (npix == 0) return HF_OK;
+    if ((rc = check_rays(d_out))) return rc;
+    CU(cudaSetDevice(c->device));
+    CU(hf_launch_render_rays(c->P, c->li, *cam, d_pixels, npix, *d_out, (cudaStream_t) stream));
+    return HF_OK;
+}
+
+extern "C" int hf_render_forward(hf_ctx *c, const hf_camera *cam, const hf_light *light, const uint32_t *d_pixels, size_t npix,
+                                 float *d_image, uint32_t *d_prim, void *stream) {
+    CHECK_CTX(c);
+    int rc;
+    if ((rc = check_camera(cam, false)) || (rc = check_light(light)) || (rc = check_pixels(cam, d_pixels, npix))) return rc;
+    if (npix == 0) return HF_OK;
+    if (!d_image) return fail(HF_ERR_INVALID, "null image");
+    NEED_ACCEL(c);
+    CU(cudaSetDevice(c->device));
+    CU(hf_launch_render(c->P, c->li, 0, *cam, *light, d_pixels, npix, d_image, d_prim, nullptr, nullptr, nullptr, nullptr,
+                        c->d_counters + 4, (cudaStream_t) stream));
+    return HF_OK;
+}
+
+extern "C" int hf_render_backward(hf_ctx *c, const hf_camera *cam, const hf_light *light, const uint32_t *d_pixels, size_t npix,
+                                  const float *d_adj_image, const uint32_t *d_prim, void *stream) {
+    CHECK_CTX(c);
+    int rc;
+    if ((rc = check_camera(cam, d_prim == nullptr)) || (rc = check_light(light)) || (rc = check_pixels(cam, d_pixels, npix))) return rc;
+    if (npix == 0) return HF_OK;
+    if (!d_adj_image) return fail(HF_ERR_INVALID, "null adjoint image");
+    if (!c->grad_enabled) return HF_OK;
+    CU(cudaSetDevice(c->device));
+    if (d_prim) {
+        if (!c->have_heights) return fail(HF_ERR_STATE, "heights were never set");
+        CU(hf_launch_render_backward_prim(c->P, c->li, *cam, *light, d_pixels, npix, d_adj_image, d_prim, c->d_grad, (cudaStream_t) stream));
+    } else {
+        NEED_ACCEL(c);
+        CU(hf_launch_render(c->P, c->li, 2, *cam, *light, d_pixels, npix, nullptr, nullptr, nullptr, d_adj_image, c->d_grad, nullptr,
+                            c->d_counters + 4, (cudaStream_t) stream));
+    }
+    return HF_OK;
+}
+
+extern "C" int hf_render_step_l2(hf_ctx *c, const hf_camera *cam, const hf_light *light, const uint32_t *d_pixels, size_t npix,
+                                 const float *d_target, float *d_image, double *d_loss, void *stream) {
+    CHECK_CTX(c);
+    int rc;
+    if ((rc = check_camera(cam, true)) || (rc = check_light(light)) || (rc = check_pixels(cam, d_pixels, npix))) return rc;
+    if (npix == 0) return HF_OK;
+    if (!d_target) return fail(HF_ERR_INVALID, "null target image");
+    NEED_ACCEL(c);
+    CU(cudaSetDevice(c->device));
+    CU(hf_launch_render(c->P, c->li, 1, *cam, *light, d_pixels, npix, d_image, nullptr, d_target, nullptr, c->d_grad, d_loss,
+                        c->d_counters + 4, (cudaStream_t) stream));
+    return HF_OK;
+}
+
+// ------------------------------------------------------------------------------------------
 // host-buffer entry points: chunked, double-buffered H2D -> kernels -> D2H
 // ------------------------------------------------------------------------------------------
 extern "C" int hf_host_alloc(void **out, size_t bytes) {

@@ -29,3 +29,14 @@ cudaError_t hf_launch_backward(const HfParams &P, const HfLaunchInfo &li, const 
 cudaError_t hf_launch_adam(float *p, const float *g, float *m, float *v, size_t n, float lr_t, float beta1,
                            float beta2, float omb1, float omb2, float eps, int mask_updates, int num_sms,
                            cudaStream_t s);
+
+// hf_render.cu: mode 0 = forward image (+ hit triangles), 1 = fused forward + L2 adjoint + backward, 2 = backward by re-tracing
+#define HF_RENDER_MAX_SPP_HOST 256
+cudaError_t hf_launch_render(const HfParams &P, const HfLaunchInfo &li, int mode, const hf_camera &cam, const hf_light &light,
+                             const uint32_t *d_pixels, size_t npix, float *d_image, uint32_t *d_prim, const float *d_target,
+                             const float *d_adj_image, float *d_grad, double *d_loss, unsigned long long *d_sched, cudaStream_t s);
+cudaError_t hf_launch_render_backward_prim(const HfParams &P, const HfLaunchInfo &li, const hf_camera &cam, const hf_light &light,
+                                           const uint32_t *d_pixels, size_t npix, const float *d_adj_image, const uint32_t *d_prim,
+                                           float *d_grad, cudaStream_t s);
+cudaError_t hf_launch_render_rays(const HfParams &P, const HfLaunchInfo &li, const hf_camera &cam, const uint32_t *d_pixels, size_t npix,
+                                  const hf_rays &out, cudaStream_t s);

@@ -1,0 +1,393 @@
+// hf_render.cu -- the render step on the heightfield alone (include/hf_b200.h, "render step" section; SURVEY.md 8(f)
+// rows 1-2): perspective pinhole rays generated in registers, the production walk (hf_traverse.cuh), Lambert shading
+// under one directional emitter (optionally with a visibility ray), box-filter pixel means, and the adjoint of all of it
+// with respect to the height texels -- without a ray, an intersection record or a surface interaction ever touching HBM.
+//
+// Work decomposition: a warp owns a tile of 32 listed pixels.
+//   phase B  lane j marches the bundle of pixel j (all sub-pixel positions of the pixel: the direction bounds are
+//            the four pixel corners, known analytically) through the pyramid -> entry parameter of the pixel;
+//   phase C  pixel by pixel, the 32 lanes trace the pixel's samples (spp / 32 rounds) from that entry parameter,
+//            shade them, and reduce the pixel mean with shuffles in a fixed order (deterministic image);
+//   epilogue the pixel's adjoint is known as soon as its mean is (L2 step) or is read from the adjoint image
+//            (backward); the samples' hit triangles wait in shared memory, every distinct triangle of a round gets
+//            ONE set of three red.global.add.f32 (match.any on the triangle id; all samples of a pixel carry the
+//            same adjoint, so a group's contribution is count x value).
+//
+// Arithmetic of the shape part is the reference's op order (hf_device.cuh); the sensor / shading part is this
+// file's own definition, restated op for op by the oracle (oracle/hf_oracle.c, hfo_render_*).
+// Compiled with -fmad=false like the rest: every fma below is explicit.
+#include <string.h>
+#include "hf_walk_common.cuh"
+
+#define HF_RENDER_MAX_SPP 256          // samples of one pixel whose hit triangles wait in shared memory
+#define HF_NO_PRIM 0xffffffffu
+
+struct HfRenderArgs {
+    hf_camera cam;
+    float lx, ly, lz;                  // unit vector towards the emitter, world space
+    float scale;                       // albedo / pi * irradiance
+    int shadow;
+    float inv_w, inv_h, tan_x, tan_y;  // 1/width, 1/height, tan(fov/2), tan(fov/2) * height / width
+    float inv_spp, inv_npix;           // 1/spp, 1/(width*height)
+    f3 o_obj;                          // camera position in object space
+    const uint32_t *pixels;            // nullable
+    size_t npix;
+};
+
+// ---- sampling ---------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t hf_hash32(uint32_t x) {       // lowbias32
+    x ^= x >> 16; x *= 0x7FEB352Du; x ^= x >> 15; x *= 0x846CA68Bu; x ^= x >> 16;
+    return x;
+}
+// U[0,1) with 24 bits from (seed, index, channel) -- same stream as workloads.hash_uniform
+__device__ __forceinline__ float hf_hash_uniform(uint32_t seed, uint32_t idx, uint32_t channel) {
+    const uint32_t h = hf_hash32(idx ^ hf_hash32(seed * 0x9E3779B1u + channel * 0x85EBCA6Bu));
+    return (float) (h >> 8) * (1.0f / 16777216.0f);
+}
+
+// Film-plane coordinates of a sub-pixel position -> un-normalised world direction fwd + sx right + sy up
+__device__ __forceinline__ f3 hf_film_dir(const HfRenderArgs &A, float fx, float fy) {
+    const float sx = fmaf(2.f, fx, -1.f) * A.tan_x;
+    const float sy = fmaf(-2.f, fy, 1.f) * A.tan_y;
+    return mk3(fmaf(sy, A.cam.up[0], fmaf(sx, A.cam.right[0], A.cam.forward[0])),
+               fmaf(sy, A.cam.up[1], fmaf(sx, A.cam.right[1], A.cam.forward[1])),
+               fmaf(sy, A.cam.up[2], fmaf(sx, A.cam.right[2], A.cam.forward[2])));
+}
+
+// perspective.cpp:212-231 for a pinhole without clipping planes: o = camera position, d = normalised direction
+__device__ __forceinline__ f3 hf_camera_dir(const HfRenderArgs &A, uint32_t pid, uint32_t s) {
+    const uint32_t x = pid % A.cam.width, y = pid / A.cam.width;
+    float jx = 0.5f, jy = 0.5f;
+    if (A.cam.spp > 1) {
+        const unsigned long long k = (unsigned long long) pid * A.cam.spp + s;
+        const uint32_t key = (uint32_t) k ^ ((uint32_t) (k >> 32) * 0x85EBCA6Bu);
+        jx = hf_hash_uniform(A.cam.seed, key, 0); jy = hf_hash_uniform(A.cam.seed, key, 1);
+    }
+    const float fx = ((float) x + jx) * A.inv_w, fy = ((float) y + jy) * A.inv_h;
+    return normalize3(hf_film_dir(A, fx, fy));
+}
+
+// ---- one sample: trace, shade -------------------------------------------------------------------------------------
+// Closest hit of the object-space ray (o, d) from parameter t_start on; fills the hit triangle's vertices.
+__device__ __forceinline__ bool hf_trace(const HfParams &P, const HfGrid &G, f3 o, f3 d, float maxt, float t_start, int L_start,
+                                         float &ht, float &hu, float &hv, uint32_t &hprim, f3 &p0, f3 &p1, f3 &p2) {
+    HfWalk w;
+    HfCand c;
+    bool hit = false;
+    if (hf_walk_init(G, o.x, o.y, o.z, d.x, d.y, d.z, maxt, w, t_start, L_start)) {
+        while (hf_walk_next(G, w, c)) {
+            if (cell_intersect(P, c.cx, c.cy, c.z00, c.z10, c.z01, c.z11, o, d, maxt, ht, hu, hv, hprim)) { hit = true; break; }
+        }
+    }
+    if (hit) {
+        const float x0 = vtx(c.cx, P.W, P.rw), x1 = vtx(c.cx + 1, P.W, P.rw);
+        const float y0 = vtx(c.cy, P.H, P.rh), y1 = vtx(c.cy + 1, P.H, P.rh);
+        p0 = mk3(x1, y0, c.z10);
+        if ((hprim & 1u) == 0u) { p1 = mk3(x0, y1, c.z01); p2 = mk3(x0, y0, c.z00); }
+        else { p1 = mk3(x1, y1, c.z11); p2 = mk3(x0, y1, c.z01); }
+    }
+    return hit;
+}
+
+// any hit (Shape::ray_test): the walk's first hit cell decides
+__device__ __forceinline__ bool hf_occluded(const HfParams &P, const HfGrid &G, f3 o, f3 d, float maxt) {
+    HfWalk w;
+    HfCand c;
+    float t, u, v; uint32_t prim;
+    if (hf_walk_init(G, o.x, o.y, o.z, d.x, d.y, d.z, maxt, w))
+        while (hf_walk_next(G, w, c))
+            if (cell_intersect(P, c.cx, c.cy, c.z00, c.z10, c.z01, c.z11, o, d, maxt, t, u, v, prim)) return true;
+    return false;
+}
+
+// World-space geometric normal of triangle (p0, p1, p2): mesh.cpp:757 then the normal transform of rectangle.cpp:281-286
+__device__ __forceinline__ f3 hf_world_normal(const HfParams &P, f3 p0, f3 p1, f3 p2) {
+    const f3 no = normalize3(cross3(sub3(p1, p0), sub3(p2, p0)));
+    f3 nw = normalize3(xform_normal(P.to_object, no));
+    if (P.flip_normals) nw = neg3(nw);
+    return nw;
+}
+
+// Radiance of one camera sample: direct illumination of the first hit (direct.cpp:114-210 with one directional emitter and a
+// Lambertian BSDF). Returns the value; `prim` = hit triangle when the sample is lit (its value depends on the heights
+// through the normal), HF_NO_PRIM otherwise.
+__device__ __forceinline__ float hf_shade_sample(const HfParams &P, const HfGrid &G, const HfRenderArgs &A, f3 dw, float t_start,
+                                                 int L_start, uint32_t &prim) {
+    prim = HF_NO_PRIM;
+    const f3 d = xform_vector(P.to_object, dw);
+    float ht, hu, hv; uint32_t hprim;
+    f3 p0, p1, p2;
+    if (!hf_trace(P, G, A.o_obj, d, HF_INF, t_start, L_start, ht, hu, hv, hprim, p0, p1, p2)) return 0.f;
+    const f3 nw = hf_world_normal(P, p0, p1, p2);
+    const f3 l = mk3(A.lx, A.ly, A.lz);
+    const float cosl = dot3(nw, l);
+    if (!(cosl > 0.f)) return 0.f;
+    if (A.shadow) {
+        // si.spawn_ray(l): interaction.h:136-165; p by the barycentric fma chain of mesh.cpp:748
+        const float b1 = hu, b2 = hv, b0 = 1.f - b1 - b2;
+        const f3 po = mk3(fmaf(p0.x, b0, fmaf(p1.x, b1, p2.x * b2)), fmaf(p0.y, b0, fmaf(p1.y, b1, p2.y * b2)),
+                          fmaf(p0.z, b0, fmaf(p1.z, b1, p2.z * b2)));
+        const f3 pw = xform_point(P.to_world, po);
+        float mag = (1.f + fmaxf(fmaxf(fabsf(pw.x), fabsf(pw.y)), fabsf(pw.z))) * 8.940696716308594e-05f;   // RayEpsilon = 1500 * 2^-24
+        mag = mulsign_(mag, cosl);
+        const f3 os = mk3(fmaf(mag, nw.x, pw.x), fmaf(mag, nw.y, pw.y), fmaf(mag, nw.z, pw.z));
+        if (hf_occluded(P, G, xform_point(P.to_object, os), xform_vector(P.to_object, l), 3.4028234663852886e+38f)) return 0.f;
+    }
+    prim = hprim;
+    return A.scale * cosl;
+}
+
+// d(value)/d(heights) of a lit sample on triangle `prim` for an upstream adjoint a_v of the sample value:
+// value = scale * dot(n_w, l), n_w = normalize(TO^T normalize(cross(e1, e2))). Returns the three texel indices / gradients.
+__device__ __forceinline__ void hf_shade_adjoint(const HfParams &P, const HfRenderArgs &A, uint32_t prim, float a_v,
+                                                 uint32_t &i0, uint32_t &i1, uint32_t &i2, float &g0, float &g1, float &g2) {
+    f3 p0, p1, p2;
+    cell_triangle(P, prim, p0, p1, p2, i0, i1, i2);
+    const f3 e1 = sub3(p1, p0), e2 = sub3(p2, p0);
+    const f3 c = cross3(e1, e2);
+    const float k = a_v * A.scale;
+    f3 a_nw = mk3(k * A.lx, k * A.ly, k * A.lz);
+    if (P.flip_normals) a_nw = neg3(a_nw);
+    const float inv_clen = rsqrtf(dot3(c, c));
+    const f3 no = mk3(c.x * inv_clen, c.y * inv_clen, c.z * inv_clen);
+    const f3 m = lin_T(P.to_object, no);
+    const float inv_mlen = rsqrtf(dot3(m, m));
+    const f3 nw = mk3(m.x * inv_mlen, m.y * inv_mlen, m.z * inv_mlen);
+    const float dn = dot3(nw, a_nw);
+    const f3 a_m = mk3((a_nw.x - nw.x * dn) * inv_mlen, (a_nw.y - nw.y * dn) * inv_mlen, (a_nw.z - nw.z * dn) * inv_mlen);
+    const f3 a_no = lin(P.to_object, a_m);
+    const float dno = dot3(no, a_no);
+    const f3 a_c = mk3((a_no.x - no.x * dno) * inv_clen, (a_no.y - no.y * dno) * inv_clen, (a_no.z - no.z * dno) * inv_clen);
+    const f3 a_e1 = cross3(e2, a_c), a_e2 = cross3(a_c, e1);
+    g0 = P.mh * -(a_e1.z + a_e2.z);
+    g1 = P.mh * a_e1.z;
+    g2 = P.mh * a_e2.z;
+}
+
+// Bundle of a pixel: every sub-pixel position of pixel (x, y). The un-normalised direction fwd + sx right + sy up is affine
+// in (sx, sy), so its object-space components are bounded by the four corners; the rays themselves use d = v / |v| with
+// |v| >= 1 for an orthonormal frame, i.e. they reach LESS far than o + s v for the same parameter s -- the bundle entry of the
+// un-normalised box is therefore valid for them (hf_render_entry backs it off by 2e-4 for frames that are orthonormal only
+// to rounding; hf_api.cu rejects anything worse).
+__device__ __forceinline__ HfBeam hf_pixel_bundle(const HfParams &P, const HfRenderArgs &A, uint32_t pid) {
+    const uint32_t x = pid % A.cam.width, y = pid / A.cam.width;
+    const float e = 1e-3f;                                   // 1/1000 pixel of slack around the jitter square
+    const float fx0 = ((float) x - e) * A.inv_w, fx1 = ((float) (x + 1) + e) * A.inv_w;
+    const float fy0 = ((float) y - e) * A.inv_h, fy1 = ((float) (y + 1) + e) * A.inv_h;
+    HfBeam B;
+    B.ogx = (A.o_obj.x - P.x0) * P.sgx; B.ogy = (A.o_obj.y - P.y0) * P.sgy; B.oz = A.o_obj.z;
+    B.dxl = B.dyl = B.dzl = HF_INF; B.dxh = B.dyh = B.dzh = -HF_INF;
+    #pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const f3 v = xform_vector(P.to_object, hf_film_dir(A, (k & 1) ? fx1 : fx0, (k & 2) ? fy1 : fy0));
+        const float gx = v.x * P.sgx, gy = v.y * P.sgy;
+        B.dxl = fminf(B.dxl, gx); B.dxh = fmaxf(B.dxh, gx);
+        B.dyl = fminf(B.dyl, gy); B.dyh = fmaxf(B.dyh, gy);
+        B.dzl = fminf(B.dzl, v.z); B.dzh = fmaxf(B.dzh, v.z);
+    }
+    return B;
+}
+
+// ---- the render kernel ----------------------------------------------------------------------------------------------
+enum { HF_RENDER_FWD = 0, HF_RENDER_STEP_L2 = 1, HF_RENDER_BWD = 2 };
+
+template <int MODE>
+__global__ void __launch_bounds__(HF_BLOCK, 3)
+hf_render_kernel(const __grid_constant__ HfParams P, const HfLaunchInfo li, const __grid_constant__ HfRenderArgs A,
+                 float *__restrict__ image, uint32_t *__restrict__ prim_out, const float *__restrict__ target,
+                 const float *__restrict__ adj_image, float *__restrict__ grad, double *__restrict__ loss,
+                 unsigned long long *__restrict__ sched) {
+    __shared__ uint32_t s_prim[HF_BLOCK / 32][HF_RENDER_MAX_SPP];
+    HfGrid G;
+    hf_stage_pyramid(P, li, G);
+
+    const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    const uint32_t spp = A.cam.spp;
+    const uint32_t rounds = (spp + 31u) >> 5;
+    const size_t ntiles = (A.npix + 31) / 32;
+    double loss_acc = 0.0;
+
+    for (;;) {
+        unsigned long long tile = 0;
+        if (lane == 0) tile = atomicAdd(sched, 1ull);
+        tile = __shfl_sync(FULL_MASK, tile, 0);
+        if (tile >= ntiles) break;
+        // ---- phase B: lane j marches the bundle of listed pixel 32 * tile + j
+        const size_t kq = (size_t) tile * 32 + lane;
+        const bool have = kq < A.npix;
+        const uint32_t my_pid = have ? (A.pixels ? __ldg(A.pixels + kq) : (uint32_t) kq) : 0u;
+        float t_enter = 0.f;
+        int L_start = HF_START_LEVEL;
+        if (have) {
+            const HfBeam B = hf_pixel_bundle(P, A, my_pid);
+            t_enter = hf_beam_enter(G, B, L_start);
+            t_enter -= t_enter * 2e-4f;
+        }
+        __syncwarp();
+        // ---- phase C: pixel by pixel
+        const unsigned npx = (unsigned) min((size_t) 32, A.npix - (size_t) tile * 32);
+        for (unsigned j = 0; j < npx; ++j) {
+            const uint32_t pid = __shfl_sync(FULL_MASK, my_pid, j);
+            const float ts = __shfl_sync(FULL_MASK, t_enter, j);
+            const int ls = __shfl_sync(FULL_MASK, L_start, j);
+            float acc = 0.f;
+            for (uint32_t r = 0; r < rounds; ++r) {
+                const uint32_t s = r * 32u + lane;
+                uint32_t prim = HF_NO_PRIM;
+                float v = 0.f;
+                if (s < spp) v = hf_shade_sample(P, G, A, hf_camera_dir(A, pid, s), ts, ls, prim);
+                acc += v;
+                s_prim[warp][(r * 32u + lane) & (HF_RENDER_MAX_SPP - 1)] = prim;
+                if (MODE == HF_RENDER_FWD && prim_out && s < spp)
+                    __stcs(prim_out + ((size_t) tile * 32 + j) * spp + s, prim);
+            }
+            // pixel mean: lane partials in sample order, then a butterfly -- the same order on every run
+            #pragma unroll
+            for (int sft = 16; sft > 0; sft >>= 1) acc += __shfl_xor_sync(FULL_MASK, acc, sft);
+            const float I = acc * A.inv_spp;
+            if (MODE == HF_RENDER_FWD) {
+                if (lane == 0) image[pid] = I;
+                continue;
+            }
+            float a_v;                                     // adjoint of ONE sample value of this pixel
+            if (MODE == HF_RENDER_STEP_L2) {
+                const float diff = I - __ldg(target + pid);
+                if (lane == 0) {
+                    if (image) image[pid] = I;
+                    loss_acc += (double) diff * (double) diff;
+                }
+                a_v = (2.f * diff * A.inv_npix) * A.inv_spp;
+            } else {
+                a_v = __ldg(adj_image + pid) * A.inv_spp;
+            }
+            __syncwarp();
+            if (a_v != 0.f) {
+                for (uint32_t r = 0; r < rounds; ++r) {
+                    const uint32_t prim = s_prim[warp][(r * 32u + lane) & (HF_RENDER_MAX_SPP - 1)];
+                    const bool lit = prim != HF_NO_PRIM;
+                    const unsigned act = __ballot_sync(FULL_MASK, lit);
+                    if (lit) {
+                        const unsigned peers = __match_any_sync(act, prim);
+                        uint32_t i0, i1, i2; float g0, g1, g2;
+                        hf_shade_adjoint(P, A, prim, a_v, i0, i1, i2, g0, g1, g2);
+                        if ((peers & ((1u << lane) - 1u)) == 0u) {            // lowest lane of the group
+                            const float cnt = (float) __popc(peers);
+                            atomicAdd(grad + i0, cnt * g0); atomicAdd(grad + i1, cnt * g1); atomicAdd(grad + i2, cnt * g2);
+                        }
+                    }
+                }
+            }
+            __syncwarp();
+        }
+    }
+    if (MODE == HF_RENDER_STEP_L2 && loss && lane == 0 && loss_acc != 0.0) atomicAdd(loss, loss_acc * (double) A.inv_npix);
+}
+
+// Backward from stored hit triangles (no re-trace): sample i = k * spp + s of listed pixel k
+__global__ void __launch_bounds__(HF_BLOCK)
+hf_render_backward_prim_kernel(const __grid_constant__ HfParams P, const __grid_constant__ HfRenderArgs A,
+                               const float *__restrict__ adj_image, const uint32_t *__restrict__ prim_in, float *__restrict__ grad) {
+    const size_t n = A.npix * (size_t) A.cam.spp;
+    const size_t ntiles = (n + HF_BLOCK - 1) / HF_BLOCK;
+    for (size_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        const size_t i = tile * HF_BLOCK + threadIdx.x;
+        uint32_t prim = HF_NO_PRIM;
+        float a_v = 0.f;
+        if (i < n) {
+            prim = __ldcs(prim_in + i);
+            const size_t k = i / A.cam.spp;
+            const uint32_t pid = A.pixels ? __ldg(A.pixels + k) : (uint32_t) k;
+            a_v = __ldg(adj_image + pid) * A.inv_spp;
+        }
+        const bool valid = prim != HF_NO_PRIM && a_v != 0.f;
+        uint32_t i0 = 0, i1 = 0, i2 = 0; float g0 = 0.f, g1 = 0.f, g2 = 0.f;
+        if (valid) hf_shade_adjoint(P, A, prim, a_v, i0, i1, i2, g0, g1, g2);
+        warp_aggregated_add(grad, i0, g0, valid);
+        warp_aggregated_add(grad, i1, g1, valid);
+        warp_aggregated_add(grad, i2, g2, valid);
+    }
+}
+
+// The generated rays as an SoA (hf_render_rays)
+__global__ void __launch_bounds__(HF_BLOCK)
+hf_render_rays_kernel(const __grid_constant__ HfRenderArgs A, float *ox, float *oy, float *oz, float *dx, float *dy, float *dz, float *maxt) {
+    const size_t n = A.npix * (size_t) A.cam.spp;
+    for (size_t i = (size_t) blockIdx.x * HF_BLOCK + threadIdx.x; i < n; i += (size_t) gridDim.x * HF_BLOCK) {
+        const size_t k = i / A.cam.spp;
+        const uint32_t s = (uint32_t) (i - k * A.cam.spp);
+        const uint32_t pid = A.pixels ? __ldg(A.pixels + k) : (uint32_t) k;
+        const f3 d = hf_camera_dir(A, pid, s);
+        ox[i] = A.cam.origin[0]; oy[i] = A.cam.origin[1]; oz[i] = A.cam.origin[2];
+        dx[i] = d.x; dy[i] = d.y; dz[i] = d.z; maxt[i] = HF_INF;
+    }
+}
+
+// ---- host side --------------------------------------------------------------------------------------------------------
+static HfRenderArgs hf_render_args(const HfParams &P, const hf_camera &cam, const hf_light *light, const uint32_t *d_pixels, size_t npix) {
+    HfRenderArgs A;
+    memset(&A, 0, sizeof(A));
+    A.cam = cam;
+    if (light) {
+        A.lx = light->direction[0]; A.ly = light->direction[1]; A.lz = light->direction[2];
+        A.scale = (float) ((double) light->albedo / 3.14159265358979323846 * (double) light->irradiance);
+        A.shadow = light->shadow_rays ? 1 : 0;
+    }
+    A.inv_w = 1.0f / (float) cam.width; A.inv_h = 1.0f / (float) cam.height;
+    A.tan_x = cam.tan_half_fov;
+    A.tan_y = cam.tan_half_fov * ((float) cam.height / (float) cam.width);
+    A.inv_spp = 1.0f / (float) cam.spp;
+    A.inv_npix = 1.0f / ((float) cam.width * (float) cam.height);
+    const float *m = P.to_object;                 // xform_point, same op order as the device
+    float r[3];
+    for (int a = 0; a < 3; ++a) {
+        float v = m[4 * a + 3];
+        v = fmaf(m[4 * a + 0], cam.origin[0], v); v = fmaf(m[4 * a + 1], cam.origin[1], v); v = fmaf(m[4 * a + 2], cam.origin[2], v);
+        r[a] = v;
+    }
+    A.o_obj.x = r[0]; A.o_obj.y = r[1]; A.o_obj.z = r[2];
+    A.pixels = d_pixels; A.npix = npix;
+    return A;
+}
+
+static int hf_render_grid(const HfLaunchInfo &li, size_t npix) {
+    const size_t ntiles = (npix + 31) / 32, ncta = (ntiles + HF_BLOCK / 32 - 1) / (HF_BLOCK / 32), cap = (size_t) li.num_sms * 3;
+    return (int) (ncta < cap ? (ncta ? ncta : 1) : cap);
+}
+
+cudaError_t hf_launch_render(const HfParams &P, const HfLaunchInfo &li, int mode, const hf_camera &cam, const hf_light &light,
+                             const uint32_t *d_pixels, size_t npix, float *d_image, uint32_t *d_prim, const float *d_target,
+                             const float *d_adj_image, float *d_grad, double *d_loss, unsigned long long *d_sched, cudaStream_t s) {
+    if (npix == 0) return cudaSuccess;
+    const HfRenderArgs A = hf_render_args(P, cam, &light, d_pixels, npix);
+    cudaError_t e = cudaMemsetAsync(d_sched, 0, sizeof(unsigned long long), s);
+    if (e != cudaSuccess) return e;
+    const size_t smem = (size_t) li.top_nodes * sizeof(float2);
+    const int grid = hf_render_grid(li, npix);
+    if (mode == HF_RENDER_FWD)
+        hf_render_kernel<HF_RENDER_FWD><<<grid, HF_BLOCK, smem, s>>>(P, li, A, d_image, d_prim, nullptr, nullptr, nullptr, nullptr, d_sched);
+    else if (mode == HF_RENDER_STEP_L2)
+        hf_render_kernel<HF_RENDER_STEP_L2><<<grid, HF_BLOCK, smem, s>>>(P, li, A, d_image, nullptr, d_target, nullptr, d_grad, d_loss, d_sched);
+    else
+        hf_render_kernel<HF_RENDER_BWD><<<grid, HF_BLOCK, smem, s>>>(P, li, A, nullptr, nullptr, nullptr, d_adj_image, d_grad, nullptr, d_sched);
+    return cudaGetLastError();
+}
+
+cudaError_t hf_launch_render_backward_prim(const HfParams &P, const HfLaunchInfo &li, const hf_camera &cam, const hf_light &light,
+                                           const uint32_t *d_pixels, size_t npix, const float *d_adj_image, const uint32_t *d_prim,
+                                           float *d_grad, cudaStream_t s) {
+    if (npix == 0) return cudaSuccess;
+    const HfRenderArgs A = hf_render_args(P, cam, &light, d_pixels, npix);
+    const size_t n = npix * (size_t) cam.spp, nt = (n + HF_BLOCK - 1) / HF_BLOCK, cap = (size_t) li.num_sms * 8;
+    hf_render_backward_prim_kernel<<<(int) (nt < cap ? nt : cap), HF_BLOCK, 0, s>>>(P, A, d_adj_image, d_prim, d_grad);
+    return cudaGetLastError();
+}
+
+cudaError_t hf_launch_render_rays(const HfParams &P, const HfLaunchInfo &li, const hf_camera &cam, const uint32_t *d_pixels, size_t npix,
+                                  const hf_rays &out, cudaStream_t s) {
+    if (npix == 0) return cudaSuccess;
+    const HfRenderArgs A = hf_render_args(P, cam, nullptr, d_pixels, npix);
+    const size_t n = npix * (size_t) cam.spp, nt = (n + HF_BLOCK - 1) / HF_BLOCK, cap = (size_t) li.num_sms * 8;
+    hf_render_rays_kernel<<<(int) (nt < cap ? nt : cap), HF_BLOCK, 0, s>>>(A, (float *) out.ox, (float *) out.oy, (float *) out.oz,
+                                                                          (float *) out.dx, (float *) out.dy, (float *) out.dz, (float *) out.maxt);
+    return cudaGetLastError();
+}

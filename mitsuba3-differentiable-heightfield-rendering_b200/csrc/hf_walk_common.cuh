@@ -1,0 +1,94 @@
+// hf_walk_common.cuh -- device helpers shared by the kernels that walk the pyramid (hf_kernels.cu, hf_render.cu):
+// mbarrier / bulk-copy PTX, the kernel prologue that stages the coarse pyramid levels in shared memory, and the
+// warp-aggregated atomic add of the gradient scatter.
+#pragma once
+#include "hf_kernels.h"
+#include "hf_traverse.cuh"
+
+#define HF_BLOCK 256
+#define FULL_MASK 0xffffffffu
+
+// ------------------------------------------------------------------------------------------
+// small PTX helpers: mbarrier + 1-D bulk copy (TMA engine, SASS UBLKCP) for pyramid staging
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t) __cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void *dst_smem, const void *src_gmem, uint32_t bytes, uint64_t *bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_u32(dst_smem)), "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint64_t *bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                 : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+    return ok != 0;
+}
+
+// Kernel prologue shared by the walk kernels: level table in shared memory, coarse levels staged by one bulk async copy.
+__device__ __forceinline__ void hf_stage_pyramid(const HfParams &P, const HfLaunchInfo &li, HfGrid &G) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    HfLevel *s_lvl = hf_s_lvl;                                                                // static __shared__ (hf_traverse.cuh)
+    float2 *s_nodes = reinterpret_cast<float2 *>(smem_raw);                                   // levels >= li.top_level_start
+    __shared__ __align__(8) uint64_t s_bar;
+
+    if (threadIdx.x == 0) {
+        mbar_init(&s_bar, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (threadIdx.x < HF_MAX_LEVELS) {
+        const int l = threadIdx.x;
+        HfLevel e;
+        e.nodes = (li.top_nodes > 0 && l >= li.top_level_start) ? (s_nodes + (P.lvl_off[l] - li.top_off)) : (P.pyr + P.lvl_off[l]);
+        e.w = P.lvl_w[l]; e.pad = 0;
+        s_lvl[l] = e;
+    }
+    __syncthreads();
+    if (li.top_nodes > 0) {
+        if (threadIdx.x == 0) {
+            const uint32_t bytes = (uint32_t) li.top_nodes * (uint32_t) sizeof(float2);
+            mbar_expect_tx(&s_bar, bytes);
+            bulk_g2s(s_nodes, P.pyr + li.top_off, bytes, &s_bar);
+        }
+        uint32_t spins = 0;
+        while (!mbar_try_wait(&s_bar, 0)) { if (++spins > (1u << 24)) __trap(); }
+    }
+
+    G.W = P.W; G.NX = P.NX; G.NY = P.NY; G.Ltop = P.Ltop; G.mh = P.mh;
+    G.x0 = P.x0; G.y0 = P.y0; G.sgx = P.sgx; G.sgy = P.sgy;
+    G.heights = P.heights; G.lvl = s_lvl;
+    {
+        const float2 top = s_lvl[P.Ltop].nodes[0];
+        G.top_min = top.x; G.top_max = top.y;
+    }
+
+}
+
+// One RED per distinct address per warp: match.any on the texel index, then a log-step segmented
+// reduction inside each peer group (cf. the reference JIT's reduce_add_f32,
+// ext/drjit/ext/drjit-core/src/cuda_eval.cpp:805-888, which walks its peers serially).
+__device__ __forceinline__ void warp_aggregated_add(float *__restrict__ grad, uint32_t idx, float val, bool valid) {
+    const unsigned act = __ballot_sync(FULL_MASK, valid);
+    if (!valid) return;
+    const unsigned lane = threadIdx.x & 31u;
+    unsigned peers = __match_any_sync(act, idx);
+    const bool leader = (peers & ((1u << lane) - 1u)) == 0u;
+    unsigned rel = __popc(peers & ((1u << lane) - 1u));        // my rank inside the group
+    peers &= (0xfffffffeu << lane);                            // peers above me
+    while (__any_sync(act, peers != 0u)) {
+        const int next = __ffs((int) peers);                   // 1-based lane of the next peer above, 0 = none
+        const float other = __shfl_sync(act, val, next ? next - 1 : (int) lane);
+        if (next) val += other;
+        // ranks that are odd retire: drop them from everybody's peer set
+        const unsigned retired = __ballot_sync(act, (rel & 1u) != 0u);
+        peers &= ~retired;
+        rel >>= 1;
+    }
+    if (leader) atomicAdd(grad + idx, val);
+}
+

@@ -804,6 +804,111 @@ void hfo_adam_step(float *p, const float *g, float *m, float *v, size_t n,
     }
 }
 
+/* ---------------------------------------------------------------------- */
+/* Render step on the heightfield alone:        */
+/* perspective pinhole (src/sensors/perspective.cpp:198-234), directional */
+/* emitter + Lambertian BSDF, direct illumination of the first hit        */
+/* (src/integrators/direct.cpp:114-210), optional visibility ray spawned  */
+/* as in include/mitsuba/render/interaction.h:136-165. The sensor and     */
+/* shading op order is the definition in DESIGN.md section 7.             */
+/* ---------------------------------------------------------------------- */
+static inline uint32_t hash32(uint32_t x) {
+    x ^= x >> 16; x *= 0x7FEB352Du; x ^= x >> 15; x *= 0x846CA68Bu; x ^= x >> 16;
+    return x;
+}
+static inline float hash_uniform(uint32_t seed, uint32_t idx, uint32_t channel) {
+    uint32_t h = hash32(idx ^ hash32(seed * 0x9E3779B1u + channel * 0x85EBCA6Bu));
+    return (float) (h >> 8) * (1.0f / 16777216.0f);
+}
+
+static void camera_dir(const hfo_camera *c, uint32_t pid, uint32_t s, float d[3]) {
+    const uint32_t x = pid % c->width, y = pid / c->width;
+    const float inv_w = 1.0f / (float) c->width, inv_h = 1.0f / (float) c->height;
+    const float tan_x = c->tan_half_fov, tan_y = c->tan_half_fov * ((float) c->height / (float) c->width);
+    float jx = 0.5f, jy = 0.5f;
+    if (c->spp > 1) {
+        const unsigned long long k = (unsigned long long) pid * c->spp + s;
+        const uint32_t key = (uint32_t) k ^ ((uint32_t) (k >> 32) * 0x85EBCA6Bu);
+        jx = hash_uniform(c->seed, key, 0); jy = hash_uniform(c->seed, key, 1);
+    }
+    const float fx = ((float) x + jx) * inv_w, fy = ((float) y + jy) * inv_h;
+    const float sx = fmaf(2.f, fx, -1.f) * tan_x, sy = fmaf(-2.f, fy, 1.f) * tan_y;
+    float v[3];
+    for (int a = 0; a < 3; ++a) v[a] = fmaf(sy, c->up[a], fmaf(sx, c->right[a], c->forward[a]));
+    normalize3(v, d);
+}
+
+void hfo_camera_rays(const hfo_camera *c, const uint32_t *pixels, size_t npix,
+                     float *ox, float *oy, float *oz, float *dx, float *dy, float *dz, float *maxt) {
+    #pragma omp parallel for schedule(static)
+    for (long long kk = 0; kk < (long long) npix; ++kk) {
+        const size_t k = (size_t) kk;
+        const uint32_t pid = pixels ? pixels[k] : (uint32_t) k;
+        for (uint32_t s = 0; s < c->spp; ++s) {
+            const size_t i = k * c->spp + s;
+            float d[3];
+            camera_dir(c, pid, s, d);
+            ox[i] = c->origin[0]; oy[i] = c->origin[1]; oz[i] = c->origin[2];
+            dx[i] = d[0]; dy[i] = d[1]; dz[i] = d[2]; maxt[i] = INFINITY;
+        }
+    }
+}
+
+/* Per-sample radiance (fp32, the kernel's op order) and the hit triangle of every LIT sample (0xffffffff otherwise).
+ * pi (nullable) receives the preliminary intersection of every sample. */
+void hfo_render_samples(const hfo_shape *sh, const hfo_pyramid *p, const hfo_camera *c, const hfo_light *l,
+                        const uint32_t *pixels, size_t npix, float *value, uint32_t *prim_out, hfo_prelim *pi) {
+    grid_t g = make_grid(sh);
+    const float scale = (float) ((double) l->albedo / 3.14159265358979323846 * (double) l->irradiance);
+    float o_obj[3], l_obj[3];
+    xform_point(sh->to_object, c->origin, o_obj);
+    xform_vector(sh->to_object, l->direction, l_obj);
+    #pragma omp parallel for schedule(dynamic, 16)
+    for (long long kk = 0; kk < (long long) npix; ++kk) {
+        const size_t k = (size_t) kk;
+        const uint32_t pid = pixels ? pixels[k] : (uint32_t) k;
+        for (uint32_t s = 0; s < c->spp; ++s) {
+            const size_t i = k * c->spp + s;
+            float dw[3], d[3], t = 0, u = 0, v = 0; uint32_t prim = 0;
+            camera_dir(c, pid, s, dw);
+            xform_vector(sh->to_object, dw, d);
+            const int hit = traverse(&g, p, o_obj, d, INFINITY, 0, &t, &u, &v, &prim, NULL, NULL);
+            if (pi) {
+                if (hit) { pi->t[i] = t; pi->u[i] = u; pi->v[i] = v; pi->prim_index[i] = prim; }
+                else write_miss(pi, i);
+            }
+            value[i] = 0.f; prim_out[i] = 0xffffffffu;
+            if (!hit) continue;
+            int cx, cy, kt, vi[3], vj[3];
+            float p0[3], p1[3], p2[3], e1[3], e2[3], cr[3], no[3], nt[3], nw[3];
+            decode_prim(&g, prim, &cx, &cy, &kt);
+            cell_triangle(&g, cx, cy, kt, p0, p1, p2, vi, vj);
+            for (int a = 0; a < 3; ++a) { e1[a] = p1[a] - p0[a]; e2[a] = p2[a] - p0[a]; }
+            cross3(e1, e2, cr);
+            normalize3(cr, no);
+            xform_normal(sh->to_object, no, nt);
+            normalize3(nt, nw);
+            if (sh->flip_normals) for (int a = 0; a < 3; ++a) nw[a] = -nw[a];
+            const float cosl = dot3(nw, l->direction);
+            if (!(cosl > 0.f)) continue;
+            if (l->shadow_rays) {
+                const float b1 = u, b2 = v, b0 = 1.f - b1 - b2;
+                float po[3], pw[3], os[3], oso[3];
+                for (int a = 0; a < 3; ++a) po[a] = fmaf(p0[a], b0, fmaf(p1[a], b1, p2[a] * b2));
+                xform_point(sh->to_world, po, pw);
+                float mag = (1.f + fmaxf(fmaxf(fabsf(pw[0]), fabsf(pw[1])), fabsf(pw[2]))) * 8.940696716308594e-05f;
+                mag = mulsign_(mag, cosl);
+                for (int a = 0; a < 3; ++a) os[a] = fmaf(mag, nw[a], pw[a]);
+                xform_point(sh->to_object, os, oso);
+                float t2, u2, v2; uint32_t prim2;
+                if (traverse(&g, p, oso, l_obj, 3.4028234663852886e+38f, 1, &t2, &u2, &v2, &prim2, NULL, NULL)) continue;
+            }
+            value[i] = scale * cosl;
+            prim_out[i] = prim;
+        }
+    }
+}
+
 void hfo_set_threads(int n) {
 #ifdef _OPENMP
     omp_set_num_threads(n);

@@ -137,6 +137,23 @@ void hfo_backward(const hfo_shape *s, const hfo_rays *r, const hfo_prelim *pi, c
 void hfo_adam_step(float *p, const float *g, float *m, float *v, size_t n,
                    float lr, float beta1, float beta2, float eps, int step_t, int mask_updates);
 
+/* -- render step on the heightfield alone (sensor + direct illumination) -------- */
+typedef struct {
+    float origin[3], right[3], up[3], forward[3];
+    float tan_half_fov;
+    uint32_t width, height, spp, seed;
+} hfo_camera;          /* perspective pinhole, src/sensors/perspective.cpp:198-234 */
+typedef struct {
+    float direction[3];    /* unit, towards the emitter */
+    float irradiance, albedo;
+    int32_t shadow_rays;
+} hfo_light;           /* src/emitters/directional.cpp + src/bsdfs/diffuse.cpp */
+
+void hfo_camera_rays(const hfo_camera *c, const uint32_t *pixels, size_t npix,
+                     float *ox, float *oy, float *oz, float *dx, float *dy, float *dz, float *maxt);
+void hfo_render_samples(const hfo_shape *s, const hfo_pyramid *p, const hfo_camera *c, const hfo_light *l,
+                        const uint32_t *pixels, size_t npix, float *value, uint32_t *prim_out, hfo_prelim *pi);
+
 void hfo_set_threads(int n);
 int  hfo_get_threads(void);
 

@@ -58,6 +58,15 @@ class _Adj(C.Structure):
     _fields_ = [(k, _f32p) for k in ADJ_FIELDS]
 
 
+class _Camera(C.Structure):
+    _fields_ = [("origin", C.c_float * 3), ("right", C.c_float * 3), ("up", C.c_float * 3), ("forward", C.c_float * 3),
+                ("tan_half_fov", C.c_float), ("width", C.c_uint32), ("height", C.c_uint32), ("spp", C.c_uint32), ("seed", C.c_uint32)]
+
+
+class _Light(C.Structure):
+    _fields_ = [("direction", C.c_float * 3), ("irradiance", C.c_float), ("albedo", C.c_float), ("shadow_rays", C.c_int32)]
+
+
 def build(force: bool = False) -> None:
     """Compile the oracle (and, where /root/reference exists, oracle/_ref)."""
     if force or not os.path.exists(_LIB_PATH) or \
@@ -102,6 +111,9 @@ def lib():
                                    C.c_uint32, C.c_size_t, _f64p, C.c_int]
         L.hfo_adam_step.argtypes = [_f32p, _f32p, _f32p, _f32p, C.c_size_t, C.c_float, C.c_float, C.c_float,
                                     C.c_float, C.c_int, C.c_int]
+        L.hfo_camera_rays.argtypes = [C.POINTER(_Camera), _u32p, C.c_size_t] + [_f32p] * 7
+        L.hfo_render_samples.argtypes = [C.POINTER(_Shape), C.c_void_p, C.POINTER(_Camera), C.POINTER(_Light), _u32p, C.c_size_t,
+                                         _f32p, _u32p, C.POINTER(_Prelim)]
         L.hfo_set_threads.argtypes = [C.c_int]
         L.hfo_get_threads.restype = C.c_int
         _lib = L
@@ -300,3 +312,77 @@ def set_threads(n):
 
 def get_threads():
     return lib().hfo_get_threads()
+
+
+# ---- render step on the heightfield alone -----------------------------------------------
+def make_camera(cam: dict) -> _Camera:
+    """cam: dict with origin/right/up/forward (3 floats each), tan_half_fov, width, height, spp, seed -- the fp32 values the
+    product's perspective_camera() helper produced (the oracle does not recompute the frame)."""
+    c = _Camera()
+    for k in ("origin", "right", "up", "forward"):
+        getattr(c, k)[:] = [float(x) for x in cam[k]]
+    c.tan_half_fov = float(cam["tan_half_fov"])
+    c.width, c.height, c.spp, c.seed = int(cam["width"]), int(cam["height"]), int(cam["spp"]), int(cam.get("seed", 0))
+    return c
+
+
+def make_light(light: dict) -> _Light:
+    l = _Light()
+    l.direction[:] = [float(x) for x in light["direction"]]
+    l.irradiance, l.albedo, l.shadow_rays = float(light.get("irradiance", 1.0)), float(light.get("albedo", 1.0)), int(bool(light.get("shadow_rays", False)))
+    return l
+
+
+def _pix(pixels):
+    if pixels is None:
+        return None, None
+    a = np.ascontiguousarray(pixels, np.uint32)
+    return a, a.ctypes.data_as(_u32p)
+
+
+def camera_rays(cam: dict, pixels=None) -> "Rays":
+    c = make_camera(cam)
+    a, ap = _pix(pixels)
+    npix = c.width * c.height if a is None else a.size
+    n = npix * c.spp
+    f = [np.empty(n, np.float32) for _ in range(7)]
+    lib().hfo_camera_rays(C.byref(c), ap, npix, *[_fp(x) for x in f])
+    return Rays.from_soa(*f)
+
+
+def render_samples(hf: "OracleHeightfield", cam: dict, light: dict, pixels=None):
+    """-> (value (npix, spp) fp32, lit-triangle ids (npix, spp) uint32, Prelim of every sample)"""
+    c, l = make_camera(cam), make_light(light)
+    a, ap = _pix(pixels)
+    npix = c.width * c.height if a is None else a.size
+    n = npix * c.spp
+    value, prim, pi = np.empty(n, np.float32), np.empty(n, np.uint32), Prelim(n)
+    s, pc = hf._shape(), pi.c()
+    lib().hfo_render_samples(C.byref(s), hf._pyramid(), C.byref(c), C.byref(l), ap, npix, _fp(value),
+                             prim.ctypes.data_as(_u32p), C.byref(pc))
+    return value.reshape(npix, c.spp), prim.reshape(npix, c.spp), pi
+
+
+def render_forward(hf, cam, light, pixels=None):
+    """Box-filter image in fp64, indexed by pixel id (zeros where not rendered), plus the per-sample data."""
+    value, prim, pi = render_samples(hf, cam, light, pixels)
+    img = np.zeros(int(cam["width"]) * int(cam["height"]), np.float64)
+    ids = np.arange(img.size) if pixels is None else np.asarray(pixels, np.int64)
+    img[ids] = value.astype(np.float64).mean(1)
+    return img, value, prim, pi
+
+
+def render_backward(hf, cam, light, adj_image, pixels=None, samples=None):
+    """d(loss)/d(heights) in fp64 for a per-pixel adjoint image: each lit sample passes adj / spp * scale * l to the adjoint of
+    its normal (hfo_backward), visibility and hit position detached."""
+    value, prim, pi = samples if samples is not None else render_samples(hf, cam, light, pixels)
+    npix, spp = value.shape
+    ids = np.arange(npix) if pixels is None else np.asarray(pixels, np.int64)
+    lit = (prim != 0xFFFFFFFF).reshape(-1)
+    scale = np.float32(float(light.get("albedo", 1.0)) / np.pi * float(light.get("irradiance", 1.0)))
+    a_v = (np.repeat(np.asarray(adj_image, np.float64)[ids], spp) / spp * float(scale)) * lit
+    rays = camera_rays(cam, pixels)
+    pi2 = Prelim(t=np.where(lit, pi.t, np.float32(np.inf)).astype(np.float32), u=pi.u, v=pi.v, prim_index=pi.prim_index)
+    ldir = [float(x) for x in light["direction"]]
+    adj = {"nx": (a_v * ldir[0]).astype(np.float32), "ny": (a_v * ldir[1]).astype(np.float32), "nz": (a_v * ldir[2]).astype(np.float32)}
+    return hf.backward(rays, pi2, adj, literal=False)
