@@ -291,6 +291,13 @@ def main_ours(a):
     params["heights"] = h           # restore the field for the legs below
     params.update()
 
+    # ---- the optimisation step of BASELINE.json configs[2] through the fused render entry:
+    #      zero_grad -> hf_render_step_l2 (in-register camera rays, direct illumination, box filter, L2 adjoint, backward)
+    #      [-> allreduce] -> Adam -> pyramid rebuild. No ray / interaction record touches HBM.
+    rs = run_render_step(a, shape, h, params, opt, rank, world, dev, timed, ev)
+    params["heights"] = h
+    params.update()
+
     # ---- traversal counters for the algorithmic byte model (outside every timed region) ----
     shape.stats(reset=True)
     shape.ray_intersect_preliminary(ray, counted=True, out=pi2)
@@ -339,6 +346,18 @@ def main_ours(a):
                    "full_step": "zero_grad + intersect/SI + backward + allreduce + Adam + pyramid rebuild",
                    "grad_abs_sum": grad_checksum, "mean_nodes_per_ray": n_node, "mean_leaves_per_ray": n_leaf},
     }
+    # SURVEY.md 8(d) "full step" byte model: rays x (B_trav + 16 + 12) + texels x (4 + 28 + 4 + 8/3) + pixels x 36
+    texels, pixels_img = float(a.heights) ** 2, float(a.image) ** 2
+    step_bytes = n_total * (b_trav + 28.0) + texels * (4 + 28 + 4 + 8.0 / 3.0) + pixels_img * 36.0
+    kern_bytes = n_local * (b_trav + 28.0) + (pixels_img / world) * 12.0
+    rs["roofline"] = {"bound": "hbm", "kernel": "hf_render_kernel<STEP_L2>", "kernel_ms": rs.pop("kernel_ms"),
+                      "achieved": kern_bytes / (rs["kernel_ms_"] * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
+                      "frac": kern_bytes / (rs["kernel_ms_"] * 1e-3) / 1e9 / peak,
+                      "model": f"rays x ({b_trav:.1f} B traversal + 16 B hit cell + 12 B gradient atomics) + 12 B per pixel"}
+    rs.pop("kernel_ms_")
+    rs["step_model_gbs"] = step_bytes / (rs["ms_per_step"] * 1e-3) / 1e9
+    rs["step_model_frac"] = rs["step_model_gbs"] / peak
+    line["extras"]["render_step"] = rs
     if e2e is not None:
         line["e2e"] = e2e
     if world == 1 and not a.no_cpu:
@@ -350,6 +369,70 @@ def main_ours(a):
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
+
+
+def run_render_step(a, shape, h, params, opt, rank, world, dev, timed, ev):
+    import hfb200
+    from hfb200 import workloads as wl
+    cam3 = wl.CONFIGS["C3"]["camera"]
+    cam = hfb200.perspective_camera(cam3["origin"], cam3["target"], cam3["up"], cam3["fov"], a.image, a.image, a.spp, seed=0)
+    light = hfb200.directional_light((0.3, 0.2, 1.0))
+    pix = None if world == 1 else wl.tile_pixels(a.image, a.image, a.tile, rank, world, device=dev).to(torch.int32)
+    # target image: the same scene over another fBm field (seed 0x7A); every rank renders the pixels it owns
+    tgt_shape = hfb200.load_dict({"type": "heightfield", "heights": wl.fbm_heights(a.heights, octaves=8, seed=0x7A, device=dev),
+                                  "max_height": 0.3}, device=dev)
+    target = tgt_shape.render_forward(cam, light, pix)
+    del tgt_shape
+    torch.cuda.empty_cache()
+    image = torch.zeros_like(target)
+    loss = torch.zeros(1, dtype=torch.float64, device=dev)
+    k_times = []
+
+    def step(record=False):
+        shape.zero_grad()
+        loss.zero_()
+        if record:
+            e0, e1 = ev(), ev()
+            e0.record()
+        shape.render_step_l2(cam, light, target, pix, image=image, loss=loss)
+        if record:
+            e1.record(); k_times.append((e0, e1))
+        if world > 1:
+            shape.allreduce_grad()
+        opt.step()
+        params.update()
+
+    def kernel_only(record=True):          # the fused kernel alone on the initial field (heights do not move)
+        shape.zero_grad()
+        e0, e1 = ev(), ev()
+        e0.record()
+        shape.render_step_l2(cam, light, target, pix, image=image, loss=loss)
+        e1.record()
+        if record:
+            k_times.append((e0, e1))
+
+    params["heights"] = h
+    params.update()
+    for _ in range(3):
+        kernel_only(False)
+    timed(kernel_only, a.steps)
+    kms = float(np.mean([x.elapsed_time(y) for x, y in k_times]))
+    # real optimisation steps from the initial state (the field roughens as Adam moves it, walks get longer)
+    opt.reset()
+    for _ in range(3):
+        step()
+    params["heights"] = h
+    params.update()
+    opt.reset()
+    step(); torch.cuda.synchronize(); loss0 = float(loss.item())
+    ms = timed(step, a.steps) / a.steps
+    torch.cuda.synchronize()
+    loss1 = float(loss.item())
+    n_total = a.image * a.image * a.spp
+    return {"what": "zero_grad + hf_render_step_l2 (camera rays, direct illumination, box filter, L2 adjoint, backward in ONE kernel) "
+                    "+ allreduce + Adam + pyramid rebuild", "ms_per_step": ms, "mrays": n_total / (ms * 1e-3) / 1e6,
+            "kernel_ms": kms, "kernel_ms_": kms, "kernel_mrays": n_total / world / (kms * 1e-3) / 1e6 * world,
+            "loss_first_step_local": loss0, f"loss_after_{a.steps + 1}_steps_local": loss1, "gpu_launches_per_step": 5}
 
 
 def run_e2e(a, shape, ray, adj, n_local, n_total, world, dev, timed):

@@ -3,7 +3,7 @@
 // under one directional emitter (optionally with a visibility ray), box-filter pixel means, and the adjoint of all of it
 // with respect to the height texels -- without a ray, an intersection record or a surface interaction ever touching HBM.
 //
-// Work decomposition: a warp owns a tile of 32 listed pixels.
+// Work decomposition: a warp owns a tile of HF_RENDER_TILE listed pixels, fetched from a global counter.
 //   phase B  lane j marches the bundle of pixel j (all sub-pixel positions of the pixel: the direction bounds are
 //            the four pixel corners, known analytically) through the pyramid -> entry parameter of the pixel;
 //   phase C  pixel by pixel, the 32 lanes trace the pixel's samples (spp / 32 rounds) from that entry parameter,
@@ -21,6 +21,9 @@
 
 #define HF_RENDER_MAX_SPP 256          // samples of one pixel whose hit triangles wait in shared memory
 #define HF_NO_PRIM 0xffffffffu
+#ifndef HF_RENDER_TILE
+#define HF_RENDER_TILE 4               // listed pixels per warp tile: small tiles keep the tail of the dynamic schedule short;
+#endif                                 // only HF_RENDER_TILE lanes march bundles in phase B (1 % of the instructions)
 
 struct HfRenderArgs {
     hf_camera cam;
@@ -164,16 +167,23 @@ __device__ __forceinline__ void hf_shade_adjoint(const HfParams &P, const HfRend
     g2 = P.mh * a_e2.z;
 }
 
-// Bundle of a pixel: every sub-pixel position of pixel (x, y). The un-normalised direction fwd + sx right + sy up is affine
-// in (sx, sy), so its object-space components are bounded by the four corners; the rays themselves use d = v / |v| with
-// |v| >= 1 for an orthonormal frame, i.e. they reach LESS far than o + s v for the same parameter s -- the bundle entry of the
-// un-normalised box is therefore valid for them (hf_render_entry backs it off by 2e-4 for frames that are orthonormal only
-// to rounding; hf_api.cu rejects anything worse).
-__device__ __forceinline__ HfBeam hf_pixel_bundle(const HfParams &P, const HfRenderArgs &A, uint32_t pid) {
+// Bundle of a pixel: every sub-pixel position of pixel (x, y). The un-normalised direction v = fwd + sx right + sy up is affine
+// in (sx, sy), so its object-space components are bounded by the four corners, and the march runs on o + s v. The rays
+// themselves use d = v / |v|: at parameter t they stand at s = t / |v|, so with |v| >= vmin over the pixel
+// (|v|^2 = 1 + sx^2 + sy^2 for an orthonormal frame) every ray is still inside the marched region at t = s_enter * vmin.
+// hf_api.cu rejects frames that are not orthonormal to 1e-4; the caller backs the result off by 2e-4 for that.
+__device__ __forceinline__ HfBeam hf_pixel_bundle(const HfParams &P, const HfRenderArgs &A, uint32_t pid, float &vmin) {
     const uint32_t x = pid % A.cam.width, y = pid / A.cam.width;
     const float e = 1e-3f;                                   // 1/1000 pixel of slack around the jitter square
     const float fx0 = ((float) x - e) * A.inv_w, fx1 = ((float) (x + 1) + e) * A.inv_w;
     const float fy0 = ((float) y - e) * A.inv_h, fy1 = ((float) (y + 1) + e) * A.inv_h;
+    {   // smallest |v| over the pixel
+        const float sxa = fmaf(2.f, fx0, -1.f) * A.tan_x, sxb = fmaf(2.f, fx1, -1.f) * A.tan_x;
+        const float sya = fmaf(-2.f, fy0, 1.f) * A.tan_y, syb = fmaf(-2.f, fy1, 1.f) * A.tan_y;
+        const float mx = (sxa <= 0.f && sxb >= 0.f) ? 0.f : fminf(sxa * sxa, sxb * sxb);
+        const float my = (sya >= 0.f && syb <= 0.f) ? 0.f : fminf(sya * sya, syb * syb);
+        vmin = sqrtf(1.f + mx + my);
+    }
     HfBeam B;
     B.ogx = (A.o_obj.x - P.x0) * P.sgx; B.ogy = (A.o_obj.y - P.y0) * P.sgy; B.oz = A.o_obj.z;
     B.dxl = B.dyl = B.dzl = HF_INF; B.dxh = B.dyh = B.dzh = -HF_INF;
@@ -204,7 +214,7 @@ hf_render_kernel(const __grid_constant__ HfParams P, const HfLaunchInfo li, cons
     const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
     const uint32_t spp = A.cam.spp;
     const uint32_t rounds = (spp + 31u) >> 5;
-    const size_t ntiles = (A.npix + 31) / 32;
+    const size_t ntiles = (A.npix + HF_RENDER_TILE - 1) / HF_RENDER_TILE;
     double loss_acc = 0.0;
 
     for (;;) {
@@ -213,19 +223,20 @@ hf_render_kernel(const __grid_constant__ HfParams P, const HfLaunchInfo li, cons
         tile = __shfl_sync(FULL_MASK, tile, 0);
         if (tile >= ntiles) break;
         // ---- phase B: lane j marches the bundle of listed pixel 32 * tile + j
-        const size_t kq = (size_t) tile * 32 + lane;
-        const bool have = kq < A.npix;
+        const size_t kq = (size_t) tile * HF_RENDER_TILE + lane;
+        const bool have = lane < HF_RENDER_TILE && kq < A.npix;
         const uint32_t my_pid = have ? (A.pixels ? __ldg(A.pixels + kq) : (uint32_t) kq) : 0u;
         float t_enter = 0.f;
         int L_start = HF_START_LEVEL;
         if (have) {
-            const HfBeam B = hf_pixel_bundle(P, A, my_pid);
+            float vmin;
+            const HfBeam B = hf_pixel_bundle(P, A, my_pid, vmin);
             t_enter = hf_beam_enter(G, B, L_start);
-            t_enter -= t_enter * 2e-4f;
+            if (t_enter < HF_BEAM_ALL_MISS) t_enter = t_enter * vmin * (1.f - 2e-4f);
         }
         __syncwarp();
         // ---- phase C: pixel by pixel
-        const unsigned npx = (unsigned) min((size_t) 32, A.npix - (size_t) tile * 32);
+        const unsigned npx = (unsigned) min((size_t) HF_RENDER_TILE, A.npix - (size_t) tile * HF_RENDER_TILE);
         for (unsigned j = 0; j < npx; ++j) {
             const uint32_t pid = __shfl_sync(FULL_MASK, my_pid, j);
             const float ts = __shfl_sync(FULL_MASK, t_enter, j);
@@ -239,7 +250,7 @@ hf_render_kernel(const __grid_constant__ HfParams P, const HfLaunchInfo li, cons
                 acc += v;
                 s_prim[warp][(r * 32u + lane) & (HF_RENDER_MAX_SPP - 1)] = prim;
                 if (MODE == HF_RENDER_FWD && prim_out && s < spp)
-                    __stcs(prim_out + ((size_t) tile * 32 + j) * spp + s, prim);
+                    __stcs(prim_out + ((size_t) tile * HF_RENDER_TILE + j) * spp + s, prim);
             }
             // pixel mean: lane partials in sample order, then a butterfly -- the same order on every run
             #pragma unroll
@@ -350,7 +361,7 @@ static HfRenderArgs hf_render_args(const HfParams &P, const hf_camera &cam, cons
 }
 
 static int hf_render_grid(const HfLaunchInfo &li, size_t npix) {
-    const size_t ntiles = (npix + 31) / 32, ncta = (ntiles + HF_BLOCK / 32 - 1) / (HF_BLOCK / 32), cap = (size_t) li.num_sms * 3;
+    const size_t ntiles = (npix + HF_RENDER_TILE - 1) / HF_RENDER_TILE, ncta = (ntiles + HF_BLOCK / 32 - 1) / (HF_BLOCK / 32), cap = (size_t) li.num_sms * 3;
     return (int) (ncta < cap ? (ncta ? ncta : 1) : cap);
 }
 
