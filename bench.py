@@ -49,6 +49,15 @@ def peaks():
         return 6650.0, "fallback (B200_PROFILING.md)"
 
 
+def measured_traffic(kernel, rays):
+    """dram bytes per launch from the committed ncu capture (profiles/traffic.json), scaled to this launch's ray count."""
+    try:
+        t = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))[kernel]
+        return float(t["dram_bytes"]) * rays / float(t["rays"])
+    except Exception:
+        return None
+
+
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
@@ -334,9 +343,10 @@ def main_ours(a):
                    "si_fields": "t,p,n,uv", "hit_fraction": hits},
         "clocks": clocks,
         "gpu_launches": 2 * a.steps,
-        "kernels_per_step": ["hf_intersect_kernel<FUSED_SI>", "hf_backward_kernel"],
-        "roofline": {"bound": "hbm", "kernel": "hf_intersect_kernel<FUSED_SI>", "achieved": ach_fwd, "peak": peak, "unit": "GB/s",
-                     "frac": ach_fwd / peak, "traffic": None, "peak_source": peak_src, "bytes_per_ray": bpr_fwd,
+        "kernels_per_step": ["hf_intersect_fast_kernel<FUSED_SI>", "hf_backward_kernel"],
+        "roofline": {"bound": "hbm", "kernel": "hf_intersect_fast_kernel<FUSED_SI>", "achieved": ach_fwd, "peak": peak, "unit": "GB/s",
+                     "frac": ach_fwd / peak, "traffic": measured_traffic("hf_intersect_fast_kernel<FUSED_SI>", n_local), "traffic_unit": "bytes per launch (ncu dram__bytes_read + write, profiles/traffic.json)",
+                     "algorithmic_bytes": n_local * bpr_fwd, "peak_source": peak_src, "bytes_per_ray": bpr_fwd,
                      "model": f"76 B I/O + 8 B x {n_node:.2f} nodes + 16 B x {n_leaf:.2f} leaves (canonical traversal, counted on this batch)",
                      "io_only_frac": n_local * B_IO_FWD / (ms_fwd * 1e-3) / 1e9 / peak, "kernel_ms": ms_fwd,
                      "backward": {"kernel": "hf_backward_kernel", "kernel_ms": ms_bwd, "achieved": ach_bwd, "frac": ach_bwd / peak,

@@ -17,6 +17,7 @@ $BCMD > gpurun_out/${tag}_plain.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -k regex:hf_ -c 60 --csv --log-file gpurun_out/${tag}_launches.csv $BCMD > gpurun_out/${tag}_ncu_l.log 2>&1
 echo "ncu launches rc=$?"
 $BCMD > gpurun_out/${tag}_plain2.log 2>&1 &&
-ncu --set full --clock-control none --import-source on -k regex:'hf_intersect_fast_kernel|hf_backward_kernel' -s 6 -c 2 -o gpurun_out/${tag}_prof -f $BCMD > gpurun_out/${tag}_ncu_f.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:'hf_intersect_fast_kernel|hf_backward_kernel|hf_render_kernel' -s 6 -c 4 -o gpurun_out/${tag}_prof -f $BCMD > gpurun_out/${tag}_ncu_f.log 2>&1
 echo "ncu full rc=$?"
+python tools/ncu_summary.py gpurun_out/${tag}_prof.ncu-rep > gpurun_out/${tag}_ncu_full_summary.txt 2>&1
 ls -la gpurun_out | tail -20
