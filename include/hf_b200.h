@@ -30,7 +30,7 @@
 extern "C" {
 #endif
 
-#define HF_B200_ABI_VERSION 1
+#define HF_B200_ABI_VERSION 2
 
 typedef enum {
     HF_OK = 0,
@@ -201,7 +201,10 @@ typedef struct {
     float direction[3];            /* unit vector FROM the surface TOWARDS the emitter, world space */
     float irradiance;              /* E */
     float albedo;                  /* Lambertian reflectance */
-    int32_t shadow_rays;           /* != 0: one visibility ray per shaded sample */
+    int32_t shadow_rays;           /* != 0: one visibility ray per shaded vertex */
+    int32_t max_depth;             /* 0 or 1: direct illumination of the first hit (direct.cpp); k in 2..4: path tracing with
+                                      k - 1 cosine-sampled diffuse bounces and emitter sampling at every vertex
+                                      (src/integrators/path.cpp:133-250); adjoint as in prb.py:98-254 (sampling detached) */
 } hf_light;
 
 /* the rays the render entry points generate, written out as an hf_rays-shaped SoA (index = k * spp + sample for the k-th

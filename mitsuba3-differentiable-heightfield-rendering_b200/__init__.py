@@ -100,7 +100,8 @@ class _Camera(C.Structure):
 
 
 class _Light(C.Structure):
-    _fields_ = [("direction", C.c_float * 3), ("irradiance", C.c_float), ("albedo", C.c_float), ("shadow_rays", C.c_int32)]
+    _fields_ = [("direction", C.c_float * 3), ("irradiance", C.c_float), ("albedo", C.c_float), ("shadow_rays", C.c_int32),
+                ("max_depth", C.c_int32)]
 
 
 class _Stats(C.Structure):
@@ -611,12 +612,12 @@ def perspective_camera(origin, target, up, fov, width, height, spp, seed=0) -> d
             "spp": int(spp), "seed": int(seed)}
 
 
-def directional_light(towards, irradiance=1.0, albedo=1.0, shadow_rays=False) -> dict:
+def directional_light(towards, irradiance=1.0, albedo=1.0, shadow_rays=False, max_depth=1) -> dict:
     """`directional` emitter seen from the surface (unit vector towards the emitter) + the `diffuse` BSDF's reflectance."""
     d = np.asarray(towards, np.float64)
     d /= np.linalg.norm(d)
     return {"direction": [float(np.float32(x)) for x in d], "irradiance": float(irradiance), "albedo": float(albedo),
-            "shadow_rays": bool(shadow_rays)}
+            "shadow_rays": bool(shadow_rays), "max_depth": int(max_depth)}
 
 
 def _camera_struct(cam: dict) -> _Camera:
@@ -633,6 +634,7 @@ def _light_struct(light: dict) -> _Light:
     l.direction[:] = [float(x) for x in light["direction"]]
     l.irradiance, l.albedo = float(light.get("irradiance", 1.0)), float(light.get("albedo", 1.0))
     l.shadow_rays = int(bool(light.get("shadow_rays", False)))
+    l.max_depth = int(light.get("max_depth", 1))
     return l
 
 

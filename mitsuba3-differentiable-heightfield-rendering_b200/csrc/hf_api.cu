@@ -105,6 +105,8 @@ struct hf_ctx {
     float *d_heights = nullptr, *d_grad = nullptr, *d_m = nullptr, *d_v = nullptr;
     float2 *d_pyr = nullptr;
     unsigned long long *d_counters = nullptr;
+    float *d_scratch = nullptr;       // two images (path-traced L2 step)
+    size_t scratch_bytes = 0;
     bool have_heights = false, accel_valid = false;
     int grad_enabled = 1;
     int adam_t = 0;
@@ -231,7 +233,7 @@ extern "C" int hf_destroy(hf_ctx *c) {
     cudaSetDevice(c->device);
     if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
     for (auto &s : c->slots) { if (s.slab) cudaFree(s.slab); if (s.stream) cudaStreamDestroy(s.stream); }
-    cudaFree(c->d_heights); cudaFree(c->d_grad); cudaFree(c->d_m); cudaFree(c->d_v); cudaFree(c->d_pyr); cudaFree(c->d_counters);
+    cudaFree(c->d_heights); cudaFree(c->d_grad); cudaFree(c->d_m); cudaFree(c->d_v); cudaFree(c->d_pyr); cudaFree(c->d_counters); cudaFree(c->d_scratch);
     delete c;
     return HF_OK;
 }
@@ -578,6 +580,7 @@ static int check_light(const hf_light *l) {
     const double n2 = (double) l->direction[0] * l->direction[0] + (double) l->direction[1] * l->direction[1] + (double) l->direction[2] * l->direction[2];
     if (!(fabs(n2 - 1) < 1e-4)) return fail(HF_ERR_INVALID, "light: direction must be a unit vector");
     if (!isfinite(l->irradiance) || !isfinite(l->albedo)) return fail(HF_ERR_INVALID, "light: non-finite irradiance / albedo");
+    if (l->max_depth < 0 || l->max_depth > HF_MAX_DEPTH_HOST) return fail(HF_ERR_INVALID, "light: max_depth must be in 0..%d", HF_MAX_DEPTH_HOST);
     return HF_OK;
 }
 static int check_pixels(const hf_camera *cam, const uint32_t *d_pixels, size_t npix) {
@@ -605,6 +608,7 @@ extern "C" int hf_render_forward(hf_ctx *c, const hf_camera *cam, const hf_light
     if ((rc = check_camera(cam, false)) || (rc = check_light(light)) || (rc = check_pixels(cam, d_pixels, npix))) return rc;
     if (npix == 0) return HF_OK;
     if (!d_image) return fail(HF_ERR_INVALID, "null image");
+    if (d_prim && light->max_depth > 1) return fail(HF_ERR_INVALID, "hit triangles are only stored for max_depth <= 1 (paths are replayed)");
     NEED_ACCEL(c);
     CU(cudaSetDevice(c->device));
     CU(hf_launch_render(c->P, c->li, 0, *cam, *light, d_pixels, npix, d_image, d_prim, nullptr, nullptr, nullptr, nullptr,
@@ -620,6 +624,7 @@ extern "C" int hf_render_backward(hf_ctx *c, const hf_camera *cam, const hf_ligh
     if (npix == 0) return HF_OK;
     if (!d_adj_image) return fail(HF_ERR_INVALID, "null adjoint image");
     if (!c->grad_enabled) return HF_OK;
+    if (d_prim && light->max_depth > 1) return fail(HF_ERR_INVALID, "hit triangles are only stored for max_depth <= 1 (paths are replayed)");
     CU(cudaSetDevice(c->device));
     if (d_prim) {
         if (!c->have_heights) return fail(HF_ERR_STATE, "heights were never set");
@@ -641,6 +646,24 @@ extern "C" int hf_render_step_l2(hf_ctx *c, const hf_camera *cam, const hf_light
     if (!d_target) return fail(HF_ERR_INVALID, "null target image");
     NEED_ACCEL(c);
     CU(cudaSetDevice(c->device));
+    if (light->max_depth > 1) {
+        // paths: forward image -> L2 adjoint image -> replayed adjoint (three launches; the path vertices do not fit the
+        // shared-memory stash of the one-kernel step)
+        const size_t img_bytes = (size_t) cam->width * cam->height * sizeof(float);
+        if (c->scratch_bytes < 2 * img_bytes) {
+            if (c->d_scratch) CU(cudaFree(c->d_scratch));
+            c->d_scratch = nullptr; c->scratch_bytes = 0;
+            CU(cudaMalloc(&c->d_scratch, 2 * img_bytes));
+            c->scratch_bytes = 2 * img_bytes;
+        }
+        float *img = d_image ? d_image : c->d_scratch, *adj = c->d_scratch + (size_t) cam->width * cam->height;
+        cudaStream_t st = (cudaStream_t) stream;
+        CU(hf_launch_render(c->P, c->li, 0, *cam, *light, d_pixels, npix, img, nullptr, nullptr, nullptr, nullptr, nullptr, c->d_counters + 4, st));
+        CU(hf_launch_l2_adjoint(c->P, c->li, *cam, d_pixels, npix, img, d_target, adj, d_loss, st));
+        if (c->grad_enabled)
+            CU(hf_launch_render(c->P, c->li, 2, *cam, *light, d_pixels, npix, nullptr, nullptr, nullptr, adj, c->d_grad, nullptr, c->d_counters + 4, st));
+        return HF_OK;
+    }
     CU(hf_launch_render(c->P, c->li, 1, *cam, *light, d_pixels, npix, d_image, nullptr, d_target, nullptr, c->d_grad, d_loss,
                         c->d_counters + 4, (cudaStream_t) stream));
     return HF_OK;

@@ -40,3 +40,6 @@ cudaError_t hf_launch_render_backward_prim(const HfParams &P, const HfLaunchInfo
                                            float *d_grad, cudaStream_t s);
 cudaError_t hf_launch_render_rays(const HfParams &P, const HfLaunchInfo &li, const hf_camera &cam, const uint32_t *d_pixels, size_t npix,
                                   const hf_rays &out, cudaStream_t s);
+cudaError_t hf_launch_l2_adjoint(const HfParams &P, const HfLaunchInfo &li, const hf_camera &cam, const uint32_t *d_pixels, size_t npix,
+                                 const float *d_image, const float *d_target, float *d_adj, double *d_loss, cudaStream_t s);
+#define HF_MAX_DEPTH_HOST 4

@@ -29,6 +29,8 @@ struct HfRenderArgs {
     hf_camera cam;
     float lx, ly, lz;                  // unit vector towards the emitter, world space
     float scale;                       // albedo / pi * irradiance
+    float albedo;
+    int max_depth;
     int shadow;
     float inv_w, inv_h, tan_x, tan_y;  // 1/width, 1/height, tan(fov/2), tan(fov/2) * height / width
     float inv_spp, inv_npix;           // 1/spp, 1/(width*height)
@@ -124,7 +126,8 @@ __device__ __forceinline__ float hf_shade_sample(const HfParams &P, const HfGrid
     const f3 nw = hf_world_normal(P, p0, p1, p2);
     const f3 l = mk3(A.lx, A.ly, A.lz);
     const float cosl = dot3(nw, l);
-    if (!(cosl > 0.f)) return 0.f;
+    // diffuse.cpp:127-139: the BSDF is one-sided, cos(theta_i) = dot(n, -d) and cos(theta_o) = dot(n, l) must both be positive
+    if (!(dot3(nw, neg3(dw)) > 0.f) || !(cosl > 0.f)) return 0.f;
     if (A.shadow) {
         // si.spawn_ray(l): interaction.h:136-165; p by the barycentric fma chain of mesh.cpp:748
         const float b1 = hu, b2 = hv, b0 = 1.f - b1 - b2;
@@ -165,6 +168,101 @@ __device__ __forceinline__ void hf_shade_adjoint(const HfParams &P, const HfRend
     g0 = P.mh * -(a_e1.z + a_e2.z);
     g1 = P.mh * a_e1.z;
     g2 = P.mh * a_e2.z;
+}
+
+// ---- path tracing on the heightfield alone ---------------------------------------------------------
+// src/integrators/path.cpp:133-250 for one Lambertian surface under one directional emitter: at every vertex emitter sampling
+// (direct term, optional visibility ray), then a cosine-weighted bounce (warp.h:54-90, 320-328 in the frame of
+// include/mitsuba/core/frame.h:24-41), throughput *= albedo. No emitter is ever hit by a BSDF sample (delta emitter), a ray
+// that leaves the heightfield ends the path. Adjoint as in src/python/python/ad/integrators/prb.py:98-254: the sampled
+// directions, hit positions and visibility are detached; the heights act through every vertex normal n_k, via the direct
+// term scale * dot(n_k, l) and via the BSDF value albedo / pi * dot(n_k, wo_k) over its detached pdf.
+#define HF_MAX_DEPTH 4
+
+struct HfVertex {               // what the adjoint needs of path vertex k
+    uint32_t prim;
+    float ld;                   // direct radiance leaving the vertex: scale * cos_l when lit, else 0
+    float lit;                  // 1 when lit
+    float wx, wy, wz, cwo;      // bounce direction (world) and dot(n, wo); cwo = 0 at the last vertex
+};
+
+// sin / cos of the concentric-map angle through double precision: the CPU oracle and the GPU then agree to the last bit of
+// the fp32 result (libm and CUDA fp32 sincos differ by an ulp, which would send a bounce to another triangle now and then)
+__device__ __forceinline__ void hf_sincos_exact(float phi, float &s, float &c) {
+    double sd, cd;
+    sincos((double) phi, &sd, &cd);
+    s = (float) sd; c = (float) cd;
+}
+
+// warp::square_to_cosine_hemisphere (warp.h:320-328) over square_to_uniform_disk_concentric (warp.h:54-90)
+__device__ __forceinline__ f3 hf_cosine_hemisphere(float u1, float u2) {
+    const float x = fmaf(2.f, u1, -1.f), y = fmaf(2.f, u2, -1.f);
+    const bool zero = (x == 0.f) && (y == 0.f), q13 = fabsf(x) < fabsf(y);
+    const float r = q13 ? y : x, rp = q13 ? x : y;
+    float phi = __fdiv_rn(0.25f * 3.14159265358979323846f * rp, r);
+    if (q13) phi = 0.5f * 3.14159265358979323846f - phi;
+    if (zero) phi = 0.f;
+    float sn, cs;
+    hf_sincos_exact(phi, sn, cs);
+    const float px = r * cs, py = r * sn;
+    const float z2 = 1.f - fmaf(py, py, px * px);
+    return mk3(px, py, __fsqrt_rn(fmaxf(z2, 0.f)));
+}
+
+// One camera sample through up to A.max_depth vertices. Returns the radiance; fills V[0..nv).
+__device__ __forceinline__ float hf_path_sample(const HfParams &P, const HfGrid &G, const HfRenderArgs &A, f3 dw, float t_start, int L_start,
+                                                uint32_t pid, uint32_t s, HfVertex *V, int &nv) {
+    const f3 l = mk3(A.lx, A.ly, A.lz);
+    const unsigned long long kk = (unsigned long long) pid * A.cam.spp + s;
+    const uint32_t key = (uint32_t) kk ^ ((uint32_t) (kk >> 32) * 0x85EBCA6Bu);
+    f3 o = A.o_obj, d = xform_vector(P.to_object, dw);
+    float maxt = HF_INF, beta = 1.f, L = 0.f;
+    nv = 0;
+    #pragma unroll 1
+    for (int k = 0; k < A.max_depth; ++k) {
+        float ht, hu, hv; uint32_t hprim;
+        f3 p0, p1, p2;
+        if (!hf_trace(P, G, o, d, maxt, k == 0 ? t_start : 0.f, k == 0 ? L_start : HF_START_LEVEL, ht, hu, hv, hprim, p0, p1, p2)) break;
+        const f3 nw = hf_world_normal(P, p0, p1, p2);
+        if (!(dot3(nw, neg3(dw)) > 0.f)) break;                      // back side: the one-sided BSDF is zero
+        const float cosl = dot3(nw, l);
+        bool lit = cosl > 0.f;
+        const float b1 = hu, b2 = hv, b0 = 1.f - b1 - b2;            // mesh.cpp:738-748
+        const f3 po = mk3(fmaf(p0.x, b0, fmaf(p1.x, b1, p2.x * b2)), fmaf(p0.y, b0, fmaf(p1.y, b1, p2.y * b2)),
+                          fmaf(p0.z, b0, fmaf(p1.z, b1, p2.z * b2)));
+        const f3 pw = xform_point(P.to_world, po);
+        const float mag0 = (1.f + fmaxf(fmaxf(fabsf(pw.x), fabsf(pw.y)), fabsf(pw.z))) * 8.940696716308594e-05f;
+        if (lit && A.shadow) {
+            const float mag = mulsign_(mag0, cosl);
+            const f3 os = mk3(fmaf(mag, nw.x, pw.x), fmaf(mag, nw.y, pw.y), fmaf(mag, nw.z, pw.z));
+            if (hf_occluded(P, G, xform_point(P.to_object, os), xform_vector(P.to_object, l), 3.4028234663852886e+38f)) lit = false;
+        }
+        HfVertex v;
+        v.prim = hprim; v.lit = lit ? 1.f : 0.f; v.ld = lit ? A.scale * cosl : 0.f;
+        v.wx = v.wy = v.wz = 0.f; v.cwo = 0.f;
+        L = fmaf(beta, v.ld, L);
+        bool go_on = k + 1 < A.max_depth;
+        f3 wo = mk3(0.f, 0.f, 0.f);
+        if (go_on) {
+            const float u1 = hf_hash_uniform(A.cam.seed, key, 2u + 2u * (uint32_t) k), u2 = hf_hash_uniform(A.cam.seed, key, 3u + 2u * (uint32_t) k);
+            const f3 loc = hf_cosine_hemisphere(u1, u2);
+            f3 fs, ft;
+            coordinate_system(nw, fs, ft);                           // Frame3f(n), frame.h:24-41
+            wo = mk3(fmaf(nw.x, loc.z, fmaf(ft.x, loc.y, fs.x * loc.x)), fmaf(nw.y, loc.z, fmaf(ft.y, loc.y, fs.y * loc.x)),
+                     fmaf(nw.z, loc.z, fmaf(ft.z, loc.y, fs.z * loc.x)));
+            const float cwo = dot3(nw, wo);
+            go_on = cwo > 0.f;
+            if (go_on) { v.wx = wo.x; v.wy = wo.y; v.wz = wo.z; v.cwo = cwo; }
+        }
+        V[nv++] = v;
+        if (!go_on) break;
+        beta = beta * A.albedo;
+        const float mag = mulsign_(mag0, v.cwo);                     // si.spawn_ray(wo), interaction.h:136-165
+        const f3 os = mk3(fmaf(mag, nw.x, pw.x), fmaf(mag, nw.y, pw.y), fmaf(mag, nw.z, pw.z));
+        o = xform_point(P.to_object, os); d = xform_vector(P.to_object, wo); dw = wo;
+        maxt = 3.4028234663852886e+38f;
+    }
+    return L;
 }
 
 // Bundle of a pixel: every sub-pixel position of pixel (x, y). The un-normalised direction v = fwd + sx right + sy up is affine
@@ -294,6 +392,122 @@ hf_render_kernel(const __grid_constant__ HfParams P, const HfLaunchInfo li, cons
     if (MODE == HF_RENDER_STEP_L2 && loss && lane == 0 && loss_acc != 0.0) atomicAdd(loss, loss_acc * (double) A.inv_npix);
 }
 
+// d/d(heights) of dot(a_nw, n_w(prim)) for an arbitrary world-space adjoint a_nw of the facet normal
+__device__ __forceinline__ void hf_normal_adjoint(const HfParams &P, uint32_t prim, f3 a_nw, uint32_t &i0, uint32_t &i1, uint32_t &i2,
+                                                  float &g0, float &g1, float &g2) {
+    f3 p0, p1, p2;
+    cell_triangle(P, prim, p0, p1, p2, i0, i1, i2);
+    const f3 e1 = sub3(p1, p0), e2 = sub3(p2, p0);
+    const f3 c = cross3(e1, e2);
+    if (P.flip_normals) a_nw = neg3(a_nw);
+    const float inv_clen = rsqrtf(dot3(c, c));
+    const f3 no = mk3(c.x * inv_clen, c.y * inv_clen, c.z * inv_clen);
+    const f3 m = lin_T(P.to_object, no);
+    const float inv_mlen = rsqrtf(dot3(m, m));
+    const f3 nw = mk3(m.x * inv_mlen, m.y * inv_mlen, m.z * inv_mlen);
+    const float dn = dot3(nw, a_nw);
+    const f3 a_m = mk3((a_nw.x - nw.x * dn) * inv_mlen, (a_nw.y - nw.y * dn) * inv_mlen, (a_nw.z - nw.z * dn) * inv_mlen);
+    const f3 a_no = lin(P.to_object, a_m);
+    const float dno = dot3(no, a_no);
+    const f3 a_c = mk3((a_no.x - no.x * dno) * inv_clen, (a_no.y - no.y * dno) * inv_clen, (a_no.z - no.z * dno) * inv_clen);
+    const f3 a_e1 = cross3(e2, a_c), a_e2 = cross3(a_c, e1);
+    g0 = P.mh * -(a_e1.z + a_e2.z);
+    g1 = P.mh * a_e1.z;
+    g2 = P.mh * a_e2.z;
+}
+
+// Path-traced image (BWD = false) or its adjoint by replay (BWD = true: the pixel adjoint is read from adj_image, every
+// vertex of every path scatters into grad). Same tiling as hf_render_kernel; only the primary segment uses the bundle entry.
+template <bool BWD>
+__global__ void __launch_bounds__(HF_BLOCK, 2)
+hf_render_path_kernel(const __grid_constant__ HfParams P, const HfLaunchInfo li, const __grid_constant__ HfRenderArgs A,
+                      float *__restrict__ image, const float *__restrict__ adj_image, float *__restrict__ grad,
+                      unsigned long long *__restrict__ sched) {
+    HfGrid G;
+    hf_stage_pyramid(P, li, G);
+    const unsigned lane = threadIdx.x & 31u;
+    const uint32_t spp = A.cam.spp, rounds = (spp + 31u) >> 5;
+    const size_t ntiles = (A.npix + HF_RENDER_TILE - 1) / HF_RENDER_TILE;
+    for (;;) {
+        unsigned long long tile = 0;
+        if (lane == 0) tile = atomicAdd(sched, 1ull);
+        tile = __shfl_sync(FULL_MASK, tile, 0);
+        if (tile >= ntiles) break;
+        const size_t kq = (size_t) tile * HF_RENDER_TILE + lane;
+        const bool have = lane < HF_RENDER_TILE && kq < A.npix;
+        const uint32_t my_pid = have ? (A.pixels ? __ldg(A.pixels + kq) : (uint32_t) kq) : 0u;
+        float t_enter = 0.f;
+        int L_start = HF_START_LEVEL;
+        if (have) {
+            float vmin;
+            const HfBeam B = hf_pixel_bundle(P, A, my_pid, vmin);
+            t_enter = hf_beam_enter(G, B, L_start);
+            if (t_enter < HF_BEAM_ALL_MISS) t_enter = t_enter * vmin * (1.f - 2e-4f);
+        }
+        __syncwarp();
+        const unsigned npx = (unsigned) min((size_t) HF_RENDER_TILE, A.npix - (size_t) tile * HF_RENDER_TILE);
+        for (unsigned j = 0; j < npx; ++j) {
+            const uint32_t pid = __shfl_sync(FULL_MASK, my_pid, j);
+            const float ts = __shfl_sync(FULL_MASK, t_enter, j);
+            const int ls = __shfl_sync(FULL_MASK, L_start, j);
+            const float a_v = BWD ? __ldg(adj_image + pid) * A.inv_spp : 0.f;
+            float acc = 0.f;
+            for (uint32_t r = 0; r < rounds; ++r) {
+                const uint32_t s = r * 32u + lane;
+                HfVertex V[HF_MAX_DEPTH];
+                int nv = 0;
+                if (s < spp) acc += hf_path_sample(P, G, A, hf_camera_dir(A, pid, s), ts, ls, pid, s, V, nv);
+                if (BWD) {
+                    // radiance arriving at vertex k from the later vertices, back to front: Lo_k = ld_k + albedo * Lo_{k+1}
+                    float lo_next[HF_MAX_DEPTH];
+                    float run = 0.f;
+                    for (int k = HF_MAX_DEPTH - 1; k >= 0; --k) {
+                        lo_next[k] = run;
+                        if (k < nv) run = fmaf(A.albedo, run, V[k].ld);
+                    }
+                    float beta = 1.f;
+                    for (int k = 0; k < HF_MAX_DEPTH; ++k) {            // uniform trip count: the scatter is a warp-wide operation
+                        const bool valid = (k < nv) && (a_v != 0.f);
+                        uint32_t i0 = 0, i1 = 0, i2 = 0; float g0 = 0.f, g1 = 0.f, g2 = 0.f;
+                        if (valid) {
+                            const HfVertex v = V[k];
+                            const float kd = a_v * beta * v.lit * A.scale;                                   // direct term
+                            const float kw = v.cwo > 0.f ? __fdividef(a_v * beta * A.albedo * lo_next[k], v.cwo) : 0.f;   // BSDF weight of the bounce
+                            hf_normal_adjoint(P, v.prim, mk3(kd * A.lx + kw * v.wx, kd * A.ly + kw * v.wy, kd * A.lz + kw * v.wz),
+                                              i0, i1, i2, g0, g1, g2);
+                        }
+                        warp_aggregated_add(grad, i0, g0, valid);
+                        warp_aggregated_add(grad, i1, g1, valid);
+                        warp_aggregated_add(grad, i2, g2, valid);
+                        beta *= A.albedo;
+                    }
+                }
+            }
+            if (!BWD) {
+                #pragma unroll
+                for (int sft = 16; sft > 0; sft >>= 1) acc += __shfl_xor_sync(FULL_MASK, acc, sft);
+                if (lane == 0) image[pid] = acc * A.inv_spp;
+            }
+        }
+    }
+}
+
+// adjoint image and loss of the L2 objective for the listed pixels: adj = 2 (I - T) / (W H), loss += sum (I - T)^2 / (W H)
+__global__ void __launch_bounds__(HF_BLOCK)
+hf_l2_adjoint_kernel(const __grid_constant__ HfRenderArgs A, const float *__restrict__ image, const float *__restrict__ target,
+                     float *__restrict__ adj, double *__restrict__ loss) {
+    double acc = 0.0;
+    for (size_t k = (size_t) blockIdx.x * HF_BLOCK + threadIdx.x; k < A.npix; k += (size_t) gridDim.x * HF_BLOCK) {
+        const uint32_t pid = A.pixels ? __ldg(A.pixels + k) : (uint32_t) k;
+        const float diff = image[pid] - target[pid];
+        adj[pid] = 2.f * diff * A.inv_npix;
+        acc += (double) diff * (double) diff;
+    }
+    #pragma unroll
+    for (int sft = 16; sft > 0; sft >>= 1) acc += __shfl_xor_sync(FULL_MASK, acc, sft);
+    if (loss && (threadIdx.x & 31) == 0 && acc != 0.0) atomicAdd(loss, acc * (double) A.inv_npix);
+}
+
 // Backward from stored hit triangles (no re-trace): sample i = k * spp + s of listed pixel k
 __global__ void __launch_bounds__(HF_BLOCK)
 hf_render_backward_prim_kernel(const __grid_constant__ HfParams P, const __grid_constant__ HfRenderArgs A,
@@ -342,6 +556,8 @@ static HfRenderArgs hf_render_args(const HfParams &P, const hf_camera &cam, cons
         A.lx = light->direction[0]; A.ly = light->direction[1]; A.lz = light->direction[2];
         A.scale = (float) ((double) light->albedo / 3.14159265358979323846 * (double) light->irradiance);
         A.shadow = light->shadow_rays ? 1 : 0;
+        A.albedo = light->albedo;
+        A.max_depth = light->max_depth < 1 ? 1 : light->max_depth;
     }
     A.inv_w = 1.0f / (float) cam.width; A.inv_h = 1.0f / (float) cam.height;
     A.tan_x = cam.tan_half_fov;
@@ -374,6 +590,16 @@ cudaError_t hf_launch_render(const HfParams &P, const HfLaunchInfo &li, int mode
     if (e != cudaSuccess) return e;
     const size_t smem = (size_t) li.top_nodes * sizeof(float2);
     const int grid = hf_render_grid(li, npix);
+    if (A.max_depth > 1) {                    // path tracing: forward image or replayed adjoint (the fused L2 step is composed by hf_api.cu)
+        const int pgrid = grid < li.num_sms * 2 ? grid : li.num_sms * 2;
+        if (mode == HF_RENDER_FWD)
+            hf_render_path_kernel<false><<<pgrid, HF_BLOCK, smem, s>>>(P, li, A, d_image, nullptr, nullptr, d_sched);
+        else if (mode == HF_RENDER_BWD)
+            hf_render_path_kernel<true><<<pgrid, HF_BLOCK, smem, s>>>(P, li, A, nullptr, d_adj_image, d_grad, d_sched);
+        else
+            return cudaErrorInvalidValue;
+        return cudaGetLastError();
+    }
     if (mode == HF_RENDER_FWD)
         hf_render_kernel<HF_RENDER_FWD><<<grid, HF_BLOCK, smem, s>>>(P, li, A, d_image, d_prim, nullptr, nullptr, nullptr, nullptr, d_sched);
     else if (mode == HF_RENDER_STEP_L2)
@@ -400,5 +626,14 @@ cudaError_t hf_launch_render_rays(const HfParams &P, const HfLaunchInfo &li, con
     const size_t n = npix * (size_t) cam.spp, nt = (n + HF_BLOCK - 1) / HF_BLOCK, cap = (size_t) li.num_sms * 8;
     hf_render_rays_kernel<<<(int) (nt < cap ? nt : cap), HF_BLOCK, 0, s>>>(A, (float *) out.ox, (float *) out.oy, (float *) out.oz,
                                                                           (float *) out.dx, (float *) out.dy, (float *) out.dz, (float *) out.maxt);
+    return cudaGetLastError();
+}
+
+cudaError_t hf_launch_l2_adjoint(const HfParams &P, const HfLaunchInfo &li, const hf_camera &cam, const uint32_t *d_pixels, size_t npix,
+                                 const float *d_image, const float *d_target, float *d_adj, double *d_loss, cudaStream_t s) {
+    if (npix == 0) return cudaSuccess;
+    const HfRenderArgs A = hf_render_args(P, cam, nullptr, d_pixels, npix);
+    const size_t nt = (npix + HF_BLOCK - 1) / HF_BLOCK, cap = (size_t) li.num_sms * 8;
+    hf_l2_adjoint_kernel<<<(int) (nt < cap ? nt : cap), HF_BLOCK, 0, s>>>(A, d_image, d_target, d_adj, d_loss);
     return cudaGetLastError();
 }

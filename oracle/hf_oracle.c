@@ -890,7 +890,8 @@ void hfo_render_samples(const hfo_shape *sh, const hfo_pyramid *p, const hfo_cam
             normalize3(nt, nw);
             if (sh->flip_normals) for (int a = 0; a < 3; ++a) nw[a] = -nw[a];
             const float cosl = dot3(nw, l->direction);
-            if (!(cosl > 0.f)) continue;
+            const float mdw[3] = { -dw[0], -dw[1], -dw[2] };
+            if (!(dot3(nw, mdw) > 0.f) || !(cosl > 0.f)) continue;      /* one-sided BSDF, src/bsdfs/diffuse.cpp:127-139 */
             if (l->shadow_rays) {
                 const float b1 = u, b2 = v, b0 = 1.f - b1 - b2;
                 float po[3], pw[3], os[3], oso[3];
@@ -905,6 +906,120 @@ void hfo_render_samples(const hfo_shape *sh, const hfo_pyramid *p, const hfo_cam
             }
             value[i] = scale * cosl;
             prim_out[i] = prim;
+        }
+    }
+}
+
+/* Path tracing on the heightfield alone: src/integrators/path.cpp:133-250 for one Lambertian surface
+ * under one directional emitter -- emitter sampling at every vertex, cosine-weighted bounce (include/mitsuba/core/warp.h:54-90,
+ * 320-328; frame of include/mitsuba/core/frame.h:24-41), throughput *= albedo. The primal arithmetic is fp32 in the kernel's
+ * op order. Per sample it returns the radiance, the triangle of every path vertex (0xffffffff past the end) and, in double,
+ * the vector g_k with d(radiance)/d(n_k) = g_k (src/python/python/ad/integrators/prb.py:98-254: sampled directions, hit
+ * positions and visibility detached): g_k = albedo^k (lit_k scale l + albedo Lo_{k+1} wo_k / dot(n_k, wo_k)). */
+#define HFO_MAX_DEPTH 4
+static void cosine_hemisphere(float u1, float u2, float out[3]) {
+    const float x = fmaf(2.f, u1, -1.f), y = fmaf(2.f, u2, -1.f);
+    const int zero = (x == 0.f) && (y == 0.f), q13 = fabsf(x) < fabsf(y);
+    const float r = q13 ? y : x, rp = q13 ? x : y;
+    float phi = (0.25f * 3.14159265358979323846f * rp) / r;
+    if (q13) phi = 0.5f * 3.14159265358979323846f - phi;
+    if (zero) phi = 0.f;
+    const float sn = (float) sin((double) phi), cs = (float) cos((double) phi);   /* through double: bit-identical to the GPU */
+    const float px = r * cs, py = r * sn;
+    const float z2 = 1.f - fmaf(py, py, px * px);
+    out[0] = px; out[1] = py; out[2] = sqrtf(fmaxf(z2, 0.f));
+}
+
+void hfo_render_path_samples(const hfo_shape *sh, const hfo_pyramid *p, const hfo_camera *c, const hfo_light *l,
+                             const uint32_t *pixels, size_t npix, float *value, uint32_t *vprim, double *vadj, double *vinfo) {
+    grid_t g = make_grid(sh);
+    const float scale = (float) ((double) l->albedo / 3.14159265358979323846 * (double) l->irradiance);
+    const int max_depth = l->max_depth < 1 ? 1 : (l->max_depth > HFO_MAX_DEPTH ? HFO_MAX_DEPTH : l->max_depth);
+    float o_cam[3], l_obj[3];
+    xform_point(sh->to_object, c->origin, o_cam);
+    xform_vector(sh->to_object, l->direction, l_obj);
+    #pragma omp parallel for schedule(dynamic, 16)
+    for (long long kk = 0; kk < (long long) npix; ++kk) {
+        const size_t kpx = (size_t) kk;
+        const uint32_t pid = pixels ? pixels[kpx] : (uint32_t) kpx;
+        for (uint32_t s = 0; s < c->spp; ++s) {
+            const size_t i = kpx * c->spp + s;
+            const unsigned long long kq = (unsigned long long) pid * c->spp + s;
+            const uint32_t key = (uint32_t) kq ^ ((uint32_t) (kq >> 32) * 0x85EBCA6Bu);
+            float dw[3], o[3], d[3], maxt = INFINITY, beta = 1.f, L = 0.f;
+            camera_dir(c, pid, s, dw);
+            memcpy(o, o_cam, sizeof(o));
+            xform_vector(sh->to_object, dw, d);
+            int nv = 0;
+            float ld[HFO_MAX_DEPTH], lit[HFO_MAX_DEPTH], wo_[HFO_MAX_DEPTH][3], cwo_[HFO_MAX_DEPTH];
+            for (int k = 0; k < HFO_MAX_DEPTH; ++k) { vprim[i * HFO_MAX_DEPTH + k] = 0xffffffffu; for (int a = 0; a < 3; ++a) vadj[(i * HFO_MAX_DEPTH + k) * 3 + a] = 0.0; }
+            for (int k = 0; k < max_depth; ++k) {
+                float t = 0, u = 0, v = 0; uint32_t prim = 0;
+                if (!traverse(&g, p, o, d, maxt, 0, &t, &u, &v, &prim, NULL, NULL)) break;
+                int cx, cy, kt, vi[3], vj[3];
+                float p0[3], p1[3], p2[3], e1[3], e2[3], cr[3], no[3], nt[3], nw[3];
+                decode_prim(&g, prim, &cx, &cy, &kt);
+                cell_triangle(&g, cx, cy, kt, p0, p1, p2, vi, vj);
+                for (int a = 0; a < 3; ++a) { e1[a] = p1[a] - p0[a]; e2[a] = p2[a] - p0[a]; }
+                cross3(e1, e2, cr); normalize3(cr, no); xform_normal(sh->to_object, no, nt); normalize3(nt, nw);
+                if (sh->flip_normals) for (int a = 0; a < 3; ++a) nw[a] = -nw[a];
+                const float mdw[3] = { -dw[0], -dw[1], -dw[2] };
+                if (!(dot3(nw, mdw) > 0.f)) break;
+                const float cosl = dot3(nw, l->direction);
+                int is_lit = cosl > 0.f;
+                const float b1 = u, b2 = v, b0 = 1.f - b1 - b2;
+                float po[3], pw[3], os[3], oso[3];
+                for (int a = 0; a < 3; ++a) po[a] = fmaf(p0[a], b0, fmaf(p1[a], b1, p2[a] * b2));
+                xform_point(sh->to_world, po, pw);
+                const float mag0 = (1.f + fmaxf(fmaxf(fabsf(pw[0]), fabsf(pw[1])), fabsf(pw[2]))) * 8.940696716308594e-05f;
+                if (is_lit && l->shadow_rays) {
+                    const float mag = mulsign_(mag0, cosl);
+                    for (int a = 0; a < 3; ++a) os[a] = fmaf(mag, nw[a], pw[a]);
+                    xform_point(sh->to_object, os, oso);
+                    float t2, u2, v2; uint32_t prim2;
+                    if (traverse(&g, p, oso, l_obj, 3.4028234663852886e+38f, 1, &t2, &u2, &v2, &prim2, NULL, NULL)) is_lit = 0;
+                }
+                ld[nv] = is_lit ? scale * cosl : 0.f; lit[nv] = is_lit ? 1.f : 0.f;
+                wo_[nv][0] = wo_[nv][1] = wo_[nv][2] = 0.f; cwo_[nv] = 0.f;
+                vprim[i * HFO_MAX_DEPTH + nv] = prim;
+                L = fmaf(beta, ld[nv], L);
+                int go_on = k + 1 < max_depth;
+                float wo[3] = { 0, 0, 0 };
+                if (go_on) {
+                    const float u1 = hash_uniform(c->seed, key, 2u + 2u * (uint32_t) k), u2 = hash_uniform(c->seed, key, 3u + 2u * (uint32_t) k);
+                    float loc[3], fs[3], ft[3];
+                    cosine_hemisphere(u1, u2, loc);
+                    coordinate_system(nw, fs, ft);
+                    for (int a = 0; a < 3; ++a) wo[a] = fmaf(nw[a], loc[2], fmaf(ft[a], loc[1], fs[a] * loc[0]));
+                    const float cwo = dot3(nw, wo);
+                    go_on = cwo > 0.f;
+                    if (go_on) { memcpy(wo_[nv], wo, sizeof(wo)); cwo_[nv] = cwo; }
+                }
+                ++nv;
+                if (!go_on) break;
+                beta = beta * l->albedo;
+                const float mag = mulsign_(mag0, cwo_[nv - 1]);
+                for (int a = 0; a < 3; ++a) os[a] = fmaf(mag, nw[a], pw[a]);
+                xform_point(sh->to_object, os, o);
+                xform_vector(sh->to_object, wo, d);
+                memcpy(dw, wo, sizeof(wo));
+                maxt = 3.4028234663852886e+38f;
+            }
+            value[i] = L;
+            double run = 0.0, lo_next[HFO_MAX_DEPTH];
+            for (int k = HFO_MAX_DEPTH - 1; k >= 0; --k) { lo_next[k] = run; if (k < nv) run = (double) ld[k] + (double) l->albedo * run; }
+            double bk = 1.0;
+            if (vinfo) for (int k = 0; k < HFO_MAX_DEPTH; ++k) {        /* lit, wo (3), dot(n, wo) of every vertex: what a test needs to rebuild L(normals) */
+                double *q = vinfo + (i * HFO_MAX_DEPTH + k) * 5;
+                q[0] = k < nv ? lit[k] : 0.0; q[1] = k < nv ? wo_[k][0] : 0.0; q[2] = k < nv ? wo_[k][1] : 0.0;
+                q[3] = k < nv ? wo_[k][2] : 0.0; q[4] = k < nv ? cwo_[k] : 0.0;
+            }
+            for (int k = 0; k < nv; ++k) {
+                const double kd = bk * (double) lit[k] * (double) scale;
+                const double kw = cwo_[k] > 0.f ? bk * (double) l->albedo * lo_next[k] / (double) cwo_[k] : 0.0;
+                for (int a = 0; a < 3; ++a) vadj[(i * HFO_MAX_DEPTH + k) * 3 + a] = kd * (double) l->direction[a] + kw * (double) wo_[k][a];
+                bk *= (double) l->albedo;
+            }
         }
     }
 }

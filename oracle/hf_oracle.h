@@ -147,12 +147,18 @@ typedef struct {
     float direction[3];    /* unit, towards the emitter */
     float irradiance, albedo;
     int32_t shadow_rays;
+    int32_t max_depth;     /* 0/1 direct illumination; 2..4 path tracing (src/integrators/path.cpp) */
 } hfo_light;           /* src/emitters/directional.cpp + src/bsdfs/diffuse.cpp */
 
 void hfo_camera_rays(const hfo_camera *c, const uint32_t *pixels, size_t npix,
                      float *ox, float *oy, float *oz, float *dx, float *dy, float *dz, float *maxt);
 void hfo_render_samples(const hfo_shape *s, const hfo_pyramid *p, const hfo_camera *c, const hfo_light *l,
                         const uint32_t *pixels, size_t npix, float *value, uint32_t *prim_out, hfo_prelim *pi);
+
+/* vprim: uint32[n][4], vadj: double[n][4][3] (d radiance / d n_k), n = npix * spp */
+void hfo_render_path_samples(const hfo_shape *s, const hfo_pyramid *p, const hfo_camera *c, const hfo_light *l,
+                             const uint32_t *pixels, size_t npix, float *value, uint32_t *vprim, double *vadj,
+                             double *vinfo /* nullable: double[n][4][5] = lit, wo.xyz, dot(n, wo) */);
 
 void hfo_set_threads(int n);
 int  hfo_get_threads(void);

@@ -64,7 +64,8 @@ class _Camera(C.Structure):
 
 
 class _Light(C.Structure):
-    _fields_ = [("direction", C.c_float * 3), ("irradiance", C.c_float), ("albedo", C.c_float), ("shadow_rays", C.c_int32)]
+    _fields_ = [("direction", C.c_float * 3), ("irradiance", C.c_float), ("albedo", C.c_float), ("shadow_rays", C.c_int32),
+                ("max_depth", C.c_int32)]
 
 
 def build(force: bool = False) -> None:
@@ -114,6 +115,8 @@ def lib():
         L.hfo_camera_rays.argtypes = [C.POINTER(_Camera), _u32p, C.c_size_t] + [_f32p] * 7
         L.hfo_render_samples.argtypes = [C.POINTER(_Shape), C.c_void_p, C.POINTER(_Camera), C.POINTER(_Light), _u32p, C.c_size_t,
                                          _f32p, _u32p, C.POINTER(_Prelim)]
+        L.hfo_render_path_samples.argtypes = [C.POINTER(_Shape), C.c_void_p, C.POINTER(_Camera), C.POINTER(_Light), _u32p, C.c_size_t,
+                                              _f32p, _u32p, _f64p, _f64p]
         L.hfo_set_threads.argtypes = [C.c_int]
         L.hfo_get_threads.restype = C.c_int
         _lib = L
@@ -330,6 +333,7 @@ def make_light(light: dict) -> _Light:
     l = _Light()
     l.direction[:] = [float(x) for x in light["direction"]]
     l.irradiance, l.albedo, l.shadow_rays = float(light.get("irradiance", 1.0)), float(light.get("albedo", 1.0)), int(bool(light.get("shadow_rays", False)))
+    l.max_depth = int(light.get("max_depth", 1))
     return l
 
 
@@ -386,3 +390,48 @@ def render_backward(hf, cam, light, adj_image, pixels=None, samples=None):
     ldir = [float(x) for x in light["direction"]]
     adj = {"nx": (a_v * ldir[0]).astype(np.float32), "ny": (a_v * ldir[1]).astype(np.float32), "nz": (a_v * ldir[2]).astype(np.float32)}
     return hf.backward(rays, pi2, adj, literal=False)
+
+
+def render_path_samples(hf, cam, light, pixels=None, info=None):
+    """Path tracing (light['max_depth'] in 2..4): -> (value (npix, spp) fp32, vertex triangles (npix*spp, 4) uint32,
+    d radiance / d n_k (npix*spp, 4, 3) float64)."""
+    c, l = make_camera(cam), make_light(light)
+    a, ap = _pix(pixels)
+    npix = c.width * c.height if a is None else a.size
+    n = npix * c.spp
+    value, vprim, vadj = np.empty(n, np.float32), np.empty((n, 4), np.uint32), np.empty((n, 4, 3), np.float64)
+    s = hf._shape()
+    lib().hfo_render_path_samples(C.byref(s), hf._pyramid(), C.byref(c), C.byref(l), ap, npix, _fp(value),
+                                  vprim.ctypes.data_as(_u32p), vadj.ctypes.data_as(_f64p),
+                                  info.ctypes.data_as(_f64p) if info is not None else None)
+    return value.reshape(npix, c.spp), vprim, vadj
+
+
+def render_path_forward(hf, cam, light, pixels=None):
+    value, vprim, vadj = render_path_samples(hf, cam, light, pixels)
+    img = np.zeros(int(cam["width"]) * int(cam["height"]), np.float64)
+    ids = np.arange(img.size) if pixels is None else np.asarray(pixels, np.int64)
+    img[ids] = value.astype(np.float64).mean(1)
+    return img, (value, vprim, vadj)
+
+
+def render_path_backward(hf, cam, light, adj_image, pixels=None, samples=None):
+    """fp64 gradient: every path vertex passes a_v * g_k to the adjoint of its facet normal (hfo_backward, n adjoint only)."""
+    value, vprim, vadj = samples if samples is not None else render_path_samples(hf, cam, light, pixels)
+    npix, spp = value.shape
+    n = npix * spp
+    ids = np.arange(npix) if pixels is None else np.asarray(pixels, np.int64)
+    a_v = np.repeat(np.asarray(adj_image, np.float64)[ids], spp) / spp
+    grad = np.zeros((hf.H, hf.W), np.float64)
+    dummy = Rays(np.tile(np.array([[0, 0, 5]], np.float32), (n, 1)), np.tile(np.array([[0, 0, -1]], np.float32), (n, 1)))
+    for k in range(4):
+        ok = vprim[:, k] != 0xFFFFFFFF
+        if not ok.any():
+            continue
+        pi = Prelim(t=np.where(ok, np.float32(1), np.float32(np.inf)).astype(np.float32), u=np.full(n, 0.3, np.float32),
+                    v=np.full(n, 0.3, np.float32), prim_index=np.where(ok, vprim[:, k], 0).astype(np.uint32))
+        a = a_v[:, None] * vadj[:, k, :] * ok[:, None]
+        # split the adjoint into fp32 head + tail so that the fp32 interface of hfo_backward loses nothing
+        for part in (a.astype(np.float32), (a - a.astype(np.float32).astype(np.float64)).astype(np.float32)):
+            hf.backward(dummy, pi, {"nx": part[:, 0].copy(), "ny": part[:, 1].copy(), "nz": part[:, 2].copy()}, literal=False, grad=grad)
+    return grad

@@ -54,7 +54,7 @@ def test_generated_rays_bit_exact(hf, oracle):
                                                 (100, True, "tw", False), (33, False, "tw", True), (256, False, None, False)])
 def test_forward_image_and_prims(hf, oracle, spp, shadow, xf, flip):
     g, c = _scene(hf, oracle, to_world=TW if xf else None, flip=flip, kind="noise" if shadow else "smooth", mh=0.5 if shadow else 0.3)
-    cam = _cam(hf, spp=spp)
+    cam = _cam(hf, spp=spp, origin=(0.3, -2.5, -1.8) if flip else (0.3, -2.5, 1.8))     # flipped normals face a camera below the sheet
     ldir = (0.6, 0.2, -0.5) if flip else (0.6, 0.2, 0.5)
     light = hf.directional_light(ldir, irradiance=3.0, albedo=0.8, shadow_rays=shadow)
     rng = np.random.default_rng(1)
@@ -139,7 +139,7 @@ def test_render_equals_the_shape_api_on_the_same_rays(hf, oracle):
     si, pi = g.ray_intersect(ray, return_prelim=True)
     l = torch.tensor(light["direction"], device=si.n.device)[:, None]
     cosl = (si.n * l).sum(0)
-    lit = pi.is_valid() & (cosl > 0)
+    lit = pi.is_valid() & (cosl > 0) & ((si.n * -ray.d).sum(0) > 0)          # one-sided Lambertian (diffuse.cpp:127-139)
     scale = np.float32(0.9 / np.pi * 1.5)
     value = torch.where(lit, float(scale) * cosl, torch.zeros_like(cosl))
     img_ref = value.reshape(-1, 32).double().mean(1)
@@ -170,3 +170,52 @@ def test_render_error_behaviour(hf, oracle):
         import ctypes as C
         c, l = hf._camera_struct(_cam(hf)), hf._light_struct(light)
         hf._check(hf._load().hf_render_forward(g._ctx, C.byref(c), C.byref(l), None, 5, C.c_void_p(target.data_ptr()), None, None))
+
+
+# ---- path tracing -------------------------------------------------------------------------------
+@pytest.mark.parametrize("depth,shadow,xf,spp", [(2, False, None, 16), (3, True, None, 32), (3, True, "tw", 40), (4, False, None, 8)])
+def test_path_forward_and_backward(hf, oracle, depth, shadow, xf, spp):
+    """Radiance per pixel within 1e-5 relative of the oracle (fp32 sums; the bounce directions go through the same double-precision
+    sincos on both sides), height gradient within 1e-4 relative L2 of the oracle's fp64 PRB adjoint."""
+    g, c = _scene(hf, oracle, to_world=TW if xf else None, kind="noise", mh=0.5)
+    cam = _cam(hf, spp=spp)
+    light = hf.directional_light((0.6, 0.2, 0.5), irradiance=2.0, albedo=0.8, shadow_rays=shadow, max_depth=depth)
+    rng = np.random.default_rng(9)
+    adj = rng.uniform(-1, 1, 48 * 40).astype(f32)
+    px = rng.permutation(48 * 40)[:901].astype(np.uint32)
+    for pixels in (None, px):
+        img = g.render_forward(cam, light, pixels)
+        ref_img, samples = oracle.render_path_forward(c, cam, light, pixels)
+        got = img.cpu().numpy().reshape(-1).astype(np.float64)
+        assert np.allclose(got, ref_img, rtol=1e-5, atol=1e-7)
+        value, vprim, _ = samples
+        assert (vprim[:, depth - 1] != 0xFFFFFFFF).sum() > 50                      # paths do reach the last vertex
+        d1, *_ = oracle.render_forward(c, cam, dict(light, max_depth=1), pixels)
+        assert ref_img.sum() > 1.02 * d1.sum()                                     # and the bounces carry light
+        ref = oracle.render_path_backward(c, cam, light, adj, pixels, samples=samples)
+        g.zero_grad(); g.render_backward(cam, light, torch.from_numpy(adj), pixels)
+        ga = g.grad.cpu().numpy().astype(np.float64)
+        assert np.linalg.norm(ga - ref) <= 1e-4 * np.linalg.norm(ref)
+
+
+def test_path_l2_step_and_errors(hf, oracle):
+    g, c = _scene(hf, oracle, kind="noise", mh=0.5)
+    cam = _cam(hf, spp=32)
+    light = hf.directional_light((0.6, 0.2, 0.5), albedo=0.8, shadow_rays=True, max_depth=3)
+    npix = 48 * 40
+    g2, _ = _scene(hf, oracle, kind="noise", mh=0.5, seed=12)
+    target = g2.render_forward(cam, light)
+    img = g.render_forward(cam, light)
+    adj = 2 * (img - target).reshape(-1) / npix
+    g.zero_grad(); g.render_backward(cam, light, adj)
+    want = g.grad.clone()
+    loss = torch.zeros(1, dtype=torch.float64, device=img.device)
+    img2 = torch.zeros_like(img)
+    g.zero_grad(); g.render_step_l2(cam, light, target, image=img2, loss=loss)
+    assert torch.equal(img2.view(torch.int32), img.view(torch.int32))
+    assert abs(float(loss) - float(((img - target).double() ** 2).mean())) <= 1e-9 + 1e-6 * float(loss)
+    assert float((g.grad - want).double().norm() / want.double().norm()) < 1e-5
+    with pytest.raises(hf.HeightfieldError, match="max_depth"):
+        g.render_forward(cam, dict(light, max_depth=7))
+    with pytest.raises(hf.HeightfieldError, match="replayed"):
+        g.render_forward(cam, light, return_prims=True)

@@ -45,7 +45,9 @@ def test_render_samples_agree_with_the_shape_level_oracle(oracle):
     assert np.array_equal(ref.t.view(np.uint32), pi.t.view(np.uint32)) and np.array_equal(ref.prim_index, pi.prim_index)
     si = hf.compute_surface_interaction(rays, ref)
     cosl = (np.stack([si["nx"], si["ny"], si["nz"]], 1).astype(np.float64) @ np.asarray(light["direction"], np.float64))
-    want = np.where(ref.valid() & (cosl > 0), 0.5 / np.pi * 2.0 * cosl, 0.0)
+    d64 = np.stack([rays.dx, rays.dy, rays.dz], 1).astype(np.float64)
+    front = (np.stack([si["nx"], si["ny"], si["nz"]], 1).astype(np.float64) * -d64).sum(1) > 0      # one-sided BSDF, diffuse.cpp:127-139
+    want = np.where(ref.valid() & (cosl > 0) & front, 0.5 / np.pi * 2.0 * cosl, 0.0)
     assert np.allclose(value.reshape(-1), want, rtol=2e-6, atol=1e-7)
     assert np.array_equal(prim.reshape(-1) != 0xFFFFFFFF, value.reshape(-1) > 0)
     # a visibility ray can only remove light, and it does on a rough field lit at a grazing angle
@@ -94,3 +96,66 @@ def test_render_backward_is_the_derivative_with_hit_triangles_held_fixed(oracle)
         hp, hm = h64.copy(), h64.copy(); hp[j, i] += e; hm[j, i] -= e
         fd = (objective(hp) - objective(hm)) / (2 * e)
         assert abs(fd - g[j, i]) <= 2e-4 * max(abs(fd), 1e-6), (fd, g[j, i])
+
+
+def test_path_depth1_is_direct_and_path_adjoint_matches_fd(oracle):
+    """max_depth = 1 reproduces the direct integrator; for max_depth = 3 the PRB adjoint equals central differences of the
+    radiance with the path geometry (triangles, bounce directions, visibility) held fixed -- prb.py's detached sampling."""
+    import hfb200
+    rng = np.random.default_rng(5)
+    h = random_heights(rng, 20, 18, "noise")
+    mh, W, H = 0.5, 18, 20
+    hf = oracle.OracleHeightfield(h, mh)
+    cam = _cam(spp=4, w=12, h=10)
+    l1 = hfb200.directional_light((0.5, 0.3, 0.6), irradiance=1.3, albedo=0.9, shadow_rays=True, max_depth=1)
+    img_d, *_ = oracle.render_forward(hf, cam, l1)
+    img_p, _ = oracle.render_path_forward(hf, cam, l1)
+    assert np.array_equal(img_d, img_p)
+    light = dict(l1, max_depth=3)
+    adj = rng.uniform(-1, 1, 12 * 10)
+    value, vprim, vadj = oracle.render_path_samples(hf, cam, light)
+    assert (vprim[:, 1] != 0xFFFFFFFF).sum() > 20 and (vprim[:, 2] != 0xFFFFFFFF).sum() > 5
+    g = oracle.render_path_backward(hf, cam, light, adj, samples=(value, vprim, vadj))
+    scale, alb = 0.9 / np.pi * 1.3, 0.9
+    ld = np.asarray(light["direction"], np.float64)
+
+    def normal(hh, prim):
+        cell, k = int(prim) >> 1, int(prim) & 1
+        cy, cx = divmod(cell, W - 1)
+        P = lambda ii, jj: np.array([(2 * ii - (W - 1)) / (W - 1), (2 * jj - (H - 1)) / (H - 1), mh * hh[jj, ii]])
+        p0 = P(cx + 1, cy)
+        p1, p2 = (P(cx, cy + 1), P(cx, cy)) if k == 0 else (P(cx + 1, cy + 1), P(cx, cy + 1))
+        n = np.cross(p1 - p0, p2 - p0)
+        return n / np.linalg.norm(n)
+
+    # radiance of the FIXED paths as an explicit fp64 function of the facet normals (detached: triangles, wo_k, visibility):
+    # L = sum_k alb^k lit_k scale (n_k . l) prod_{j<k} (n_j . wo_j) / (n_j . wo_j)_primal
+    info = np.zeros((vprim.shape[0], 4, 5))
+    oracle.render_path_samples(hf, cam, light, info=info)
+    h64 = h.astype(np.float64)
+    a_s = np.repeat(adj, 4) / 4
+    paths = [(i, [int(p) for p in vprim[i] if p != 0xFFFFFFFF]) for i in np.nonzero(vprim[:, 0] != 0xFFFFFFFF)[0]]
+
+    def objective(hh):
+        tot = 0.0
+        for i, verts in paths:
+            w, L = 1.0, 0.0
+            for k, p in enumerate(verts):
+                n = normal(hh, p)
+                lit, wo, cwo = info[i, k, 0], info[i, k, 1:4], info[i, k, 4]
+                L += w * (alb ** k) * lit * scale * float(n @ ld)
+                if cwo > 0:
+                    w *= float(n @ wo) / cwo
+            tot += a_s[i] * L
+        return tot
+
+    # the primal agrees with the kernel-order fp32 radiance
+    L0 = objective(h64)
+    assert abs(L0 - float((a_s * value.reshape(-1)).sum())) <= 1e-5 * abs(L0) + 1e-7
+    idx = np.argsort(-np.abs(g).reshape(-1))[:6]
+    for flat in idx:
+        j, i = divmod(int(flat), W)
+        e = 1e-5
+        hp, hm = h64.copy(), h64.copy(); hp[j, i] += e; hm[j, i] -= e
+        fd = (objective(hp) - objective(hm)) / (2 * e)
+        assert abs(fd - g[j, i]) <= 5e-4 * max(abs(fd), 1e-6), (fd, g[j, i])
