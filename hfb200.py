@@ -11,3 +11,4 @@ _pkg = importlib.import_module("mitsuba3-differentiable-heightfield-rendering_b2
 workloads = importlib.import_module("mitsuba3-differentiable-heightfield-rendering_b200.workloads")
 sys.modules[__name__] = _pkg
 _pkg.workloads = workloads
+_pkg.formats = importlib.import_module("mitsuba3-differentiable-heightfield-rendering_b200.formats")

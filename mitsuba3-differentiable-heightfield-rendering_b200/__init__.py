@@ -317,7 +317,8 @@ class Heightfield:
         self.device = dev
         h = props.pop("heights", None)
         if h is None:
-            h = np.load(props.pop("filename"))
+            from .formats import load_heights          # .npy / .pfm / .pgm (formats.py)
+            h = load_heights(props.pop("filename"))
         h = torch.as_tensor(h, dtype=torch.float32)
         if h.dim() == 3 and h.shape[2] == 1:      # (H, W, 1) tensors as in bitmap.cpp:259-263
             h = h[:, :, 0]
@@ -332,6 +333,8 @@ class Heightfield:
         self._max_height = float(props.pop("max_height", 1.0))
         self.flip_normals = bool(props.pop("flip_normals", False))
         to_object = props.pop("to_object", None)
+        props.pop("bsdf", None)            # children of the shape that this package does not model (shape.cpp:27-78)
+        props.pop("id", None)
         if props:
             raise HeightfieldError(f"heightfield: unreferenced properties {sorted(props)}")   # Properties::mark_queried semantics
 
