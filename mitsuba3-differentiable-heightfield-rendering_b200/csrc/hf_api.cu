@@ -17,6 +17,7 @@
 #include <vector>
 
 #include "hf_kernels.h"
+#include "hf_qpyr.h"
 
 // ------------------------------------------------------------------------------------------
 // errors
@@ -104,6 +105,8 @@ struct hf_ctx {
     size_t pyr_nodes = 0;
     float *d_heights = nullptr, *d_grad = nullptr, *d_m = nullptr, *d_v = nullptr;
     float2 *d_pyr = nullptr;
+    uint32_t *d_qpyr = nullptr;      // quantised pyramid (hf_qpyr.h)
+    size_t qpyr_nodes = 0;
     unsigned long long *d_counters = nullptr;
     float *d_scratch = nullptr;       // two images (path-traced L2 step)
     size_t scratch_bytes = 0;
@@ -162,6 +165,12 @@ static void layout_pyramid(hf_ctx *c) {
         off += cnt[l];
     }
     c->pyr_nodes = off;
+    {   // quantised, padded pyramid read by the production walk
+        const HfQLayout q = hf_qlayout(P.NX, P.NY);
+        P.QLtop = q.Ltop; P.xmask = q.Mx - 1; P.ymask = q.My - 1;
+        for (int l = 0; l < HF_MAX_LEVELS; ++l) P.qoff[l] = q.off[l];
+        c->qpyr_nodes = q.nodes;
+    }
     // levels >= Ls are staged in shared memory by the intersection kernel
     int Ls = L;
     size_t top = cnt[L];
@@ -218,12 +227,15 @@ extern "C" int hf_create(hf_ctx **out, const hf_desc *desc) {
     cudaError_t e2 = cudaMalloc(&c->d_grad, texels * sizeof(float));
     cudaError_t e3 = cudaMalloc(&c->d_pyr, c->pyr_nodes * sizeof(float2));
     cudaError_t e4 = cudaMalloc(&c->d_counters, 8 * sizeof(unsigned long long));
-    if (e1 || e2 || e3 || e4) { hf_destroy(c); return fail(HF_ERR_CUDA, "cudaMalloc failed for a %ux%u heightfield", c->W, c->H); }
+    if (c->qpyr_nodes >= (size_t(1) << 32)) { hf_destroy(c); return fail(HF_ERR_INVALID, "%ux%u heightfield: padded acceleration pyramid exceeds 2^32 nodes", c->W, c->H); }
+    cudaError_t e5 = cudaMalloc(&c->d_qpyr, c->qpyr_nodes * sizeof(uint32_t));
+    if (e1 || e2 || e3 || e4 || e5) { hf_destroy(c); return fail(HF_ERR_CUDA, "cudaMalloc failed for a %ux%u heightfield", c->W, c->H); }
     cudaMemset(c->d_grad, 0, texels * sizeof(float));
     cudaMemset(c->d_pyr, 0, c->pyr_nodes * sizeof(float2));
     cudaMemset(c->d_counters, 0, 8 * sizeof(unsigned long long));
     P.heights = c->d_heights;
     P.pyr = c->d_pyr;
+    P.qpyr = c->d_qpyr;
     *out = c;
     return HF_OK;
 }
@@ -233,7 +245,7 @@ extern "C" int hf_destroy(hf_ctx *c) {
     cudaSetDevice(c->device);
     if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
     for (auto &s : c->slots) { if (s.slab) cudaFree(s.slab); if (s.stream) cudaStreamDestroy(s.stream); }
-    cudaFree(c->d_heights); cudaFree(c->d_grad); cudaFree(c->d_m); cudaFree(c->d_v); cudaFree(c->d_pyr); cudaFree(c->d_counters); cudaFree(c->d_scratch);
+    cudaFree(c->d_heights); cudaFree(c->d_grad); cudaFree(c->d_m); cudaFree(c->d_v); cudaFree(c->d_pyr); cudaFree(c->d_qpyr); cudaFree(c->d_counters); cudaFree(c->d_scratch);
     delete c;
     return HF_OK;
 }
@@ -292,7 +304,7 @@ extern "C" int hf_parameters_changed(hf_ctx *c, void *stream) {
     CHECK_CTX(c);
     if (!c->have_heights) return fail(HF_ERR_STATE, "heights were never set");
     CU(cudaSetDevice(c->device));
-    CU(hf_launch_pyramid(c->P, c->d_pyr, (cudaStream_t) stream));
+    CU(hf_launch_pyramid(c->P, c->d_pyr, c->d_qpyr, (cudaStream_t) stream));
     c->accel_valid = true;
     return HF_OK;
 }

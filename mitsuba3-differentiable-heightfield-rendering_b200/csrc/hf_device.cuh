@@ -31,6 +31,10 @@ struct HfParams {
     const float2 *pyr;        // levels 1..Ltop, (min,max) of z = mh*h
     int lvl_off[HF_MAX_LEVELS];   // node offset of level l in pyr
     int lvl_w[HF_MAX_LEVELS];     // nodes per row at level l
+    // quantised, power-of-two padded pyramid with a level 0 (hf_qpyr.h): what the production walk reads
+    const uint32_t *qpyr;
+    uint32_t qoff[HF_MAX_LEVELS]; // node offset of level l in qpyr; pitch of level l = max((xmask + 1) >> l, 1)
+    int QLtop, xmask, ymask;      // top level; padded cell counts minus one
 };
 
 struct f3 { float x, y, z; };

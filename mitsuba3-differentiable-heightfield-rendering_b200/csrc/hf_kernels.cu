@@ -99,10 +99,84 @@ __global__ void __launch_bounds__(1024) hf_pyramid_top_kernel(const __grid_const
     }
 }
 
-cudaError_t hf_launch_pyramid(const HfParams &P, float2 *pyr, cudaStream_t s) {
+// ------------------------------------------------------------------------------------------
+// Quantised pyramid (hf_qpyr.h): what the production walk reads. Built right after the fp32 pyramid, whose top node
+// gives the global z range the 16-bit codes are spread over.
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ int hf_qpitch(const HfParams &P, int l) { int p = (P.xmask + 1) >> l; return p > 0 ? p : 1; }
+__device__ __forceinline__ int hf_qrows(const HfParams &P, int l) { int p = (P.ymask + 1) >> l; return p > 0 ? p : 1; }
+
+// levels 0, 1, 2: one thread per 4 x 4 block of cells
+__global__ void __launch_bounds__(256) hf_qpyramid_base_kernel(const __grid_constant__ HfParams P, uint32_t *__restrict__ qpyr) {
+    const int Mx = P.xmask + 1, My = P.ymask + 1;
+    const int bx = blockIdx.x * 16 + (threadIdx.x & 15), by = blockIdx.y * 16 + (threadIdx.x >> 4);
+    const int x0 = bx * 4, y0 = by * 4;
+    if (x0 >= Mx || y0 >= My) return;
+    const float2 top = P.pyr[P.lvl_off[P.Ltop]];
+    const HfQuant Q = hf_quant_make(top.x, top.y);
+    uint32_t l1[4] = { HF_Q_EMPTY, HF_Q_EMPTY, HF_Q_EMPTY, HF_Q_EMPTY };
+    #pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const int y = y0 + j;
+        uint32_t row[4];
+        #pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int x = x0 + i;
+            uint32_t q = HF_Q_EMPTY;
+            if (x < P.NX && y < P.NY) {
+                const float *r0 = P.heights + (size_t) y * P.W + x;
+                const float z00 = P.mh * __ldg(r0), z10 = P.mh * __ldg(r0 + 1), z01 = P.mh * __ldg(r0 + P.W), z11 = P.mh * __ldg(r0 + P.W + 1);
+                q = hf_quant_node(fminf(fminf(z00, z10), fminf(z01, z11)), fmaxf(fmaxf(z00, z10), fmaxf(z01, z11)), Q);
+            }
+            row[i] = q;
+            l1[(j >> 1) * 2 + (i >> 1)] = hf_quant_merge(l1[(j >> 1) * 2 + (i >> 1)], q);
+        }
+        if (y < My) {
+            uint32_t *dst = qpyr + P.qoff[0] + (size_t) y * Mx + x0;
+            if (x0 + 3 < Mx) *reinterpret_cast<uint4 *>(dst) = make_uint4(row[0], row[1], row[2], row[3]);   // Mx % 4 == 0 here
+            else { for (int i = 0; i < 4; ++i) if (x0 + i < Mx) dst[i] = row[i]; }
+        }
+    }
+    if (P.QLtop >= 1) {
+        const int p1 = hf_qpitch(P, 1), r1 = hf_qrows(P, 1);
+        #pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const int nx = 2 * bx + (k & 1), ny = 2 * by + (k >> 1);
+            if (nx < p1 && ny < r1) qpyr[P.qoff[1] + (size_t) ny * p1 + nx] = l1[k];
+        }
+    }
+    if (P.QLtop >= 2) {
+        const int p2 = hf_qpitch(P, 2), r2 = hf_qrows(P, 2);
+        if (bx < p2 && by < r2) qpyr[P.qoff[2] + (size_t) by * p2 + bx] = hf_quant_merge(hf_quant_merge(l1[0], l1[1]), hf_quant_merge(l1[2], l1[3]));
+    }
+}
+
+// level l >= 3 from level l - 1 (small: <= 1/64 of the cells)
+__global__ void __launch_bounds__(256) hf_qpyramid_level_kernel(const __grid_constant__ HfParams P, uint32_t *__restrict__ qpyr, const int l) {
+    const int pw = hf_qpitch(P, l), ph = hf_qrows(P, l), cw = hf_qpitch(P, l - 1), ch = hf_qrows(P, l - 1);
+    const int fx = cw / pw, fy = ch / ph;                    // 2, or 1 once the axis is down to one node
+    const uint32_t *src = qpyr + P.qoff[l - 1];
+    for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < pw * ph; idx += gridDim.x * blockDim.x) {
+        const int ny = idx / pw, nx = idx - ny * pw;
+        uint32_t q = HF_Q_EMPTY;
+        for (int dj = 0; dj < fy; ++dj)
+            for (int di = 0; di < fx; ++di) q = hf_quant_merge(q, src[(size_t) (ny * fy + dj) * cw + (nx * fx + di)]);
+        qpyr[P.qoff[l] + idx] = q;
+    }
+}
+
+cudaError_t hf_launch_pyramid(const HfParams &P, float2 *pyr, uint32_t *qpyr, cudaStream_t s) {
     dim3 grid((P.NX + PT - 1) / PT, (P.NY + PT - 1) / PT);
     hf_pyramid_tile_kernel<<<grid, 256, 0, s>>>(P, pyr);
     if (P.Ltop > PT_LEVELS) hf_pyramid_top_kernel<<<1, 1024, 0, s>>>(P, pyr);
+    const int Mx = P.xmask + 1, My = P.ymask + 1;
+    dim3 qgrid((Mx + 63) / 64, (My + 63) / 64);
+    hf_qpyramid_base_kernel<<<qgrid, 256, 0, s>>>(P, qpyr);
+    for (int l = 3; l <= P.QLtop; ++l) {
+        const long long nodes = (long long) ((Mx >> l) > 0 ? (Mx >> l) : 1) * ((My >> l) > 0 ? (My >> l) : 1);
+        const int blocks = (int) ((nodes + 255) / 256 < 1184 ? (nodes + 255) / 256 : 1184);
+        hf_qpyramid_level_kernel<<<blocks, 256, 0, s>>>(P, qpyr, l);
+    }
     return cudaGetLastError();
 }
 

@@ -17,7 +17,7 @@ struct HfLaunchInfo {
 
 enum HfIntersectMode { HF_MODE_PRELIM = 0, HF_MODE_FUSED_SI = 1, HF_MODE_TEST = 2, HF_MODE_COUNTED = 3 };
 
-cudaError_t hf_launch_pyramid(const HfParams &P, float2 *pyr, cudaStream_t s);
+cudaError_t hf_launch_pyramid(const HfParams &P, float2 *pyr, uint32_t *qpyr, cudaStream_t s);
 cudaError_t hf_launch_intersect(const HfParams &P, const HfLaunchInfo &li, int mode, const hf_rays &rays,
                                 const hf_prelim &prelim, const hf_si &si, uint8_t *d_hit, uint32_t flags,
                                 size_t n, unsigned long long *d_counters, cudaStream_t s);

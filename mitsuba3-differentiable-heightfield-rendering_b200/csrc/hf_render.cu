@@ -75,7 +75,8 @@ __device__ __forceinline__ f3 hf_camera_dir(const HfRenderArgs &A, uint32_t pid,
 // ---- one sample: trace, shade -------------------------------------------------------------------------------------
 // Closest hit of the object-space ray (o, d) from parameter t_start on; fills the hit triangle's vertices.
 __device__ __forceinline__ bool hf_trace(const HfParams &P, const HfGrid &G, f3 o, f3 d, float maxt, float t_start, int L_start,
-                                         float &ht, float &hu, float &hv, uint32_t &hprim, f3 &p0, f3 &p1, f3 &p2) {
+                                         float &ht, float &hu, float &hv, uint32_t &hprim, f3 &p0, f3 &p1, f3 &p2,
+                                         const unsigned conv = 0u) {
     HfWalk w;
     HfCand c;
     bool hit = false;
@@ -84,6 +85,9 @@ __device__ __forceinline__ bool hf_trace(const HfParams &P, const HfGrid &G, f3 
             if (cell_intersect(P, c.cx, c.cy, c.z00, c.z10, c.z01, c.z11, o, d, maxt, ht, hu, hv, hprim)) { hit = true; break; }
         }
     }
+    // conv = the lanes that entered together: without this barrier the lanes that hit in different primitive rounds run
+    // the shading below in separate groups of ~8 (profiles/r01_notes.md)
+    if (conv) __syncwarp(conv);
     if (hit) {
         const float x0 = vtx(c.cx, P.W, P.rw), x1 = vtx(c.cx + 1, P.W, P.rw);
         const float y0 = vtx(c.cy, P.H, P.rh), y1 = vtx(c.cy + 1, P.H, P.rh);
@@ -117,12 +121,12 @@ __device__ __forceinline__ f3 hf_world_normal(const HfParams &P, f3 p0, f3 p1, f
 // Lambertian BSDF). Returns the value; `prim` = hit triangle when the sample is lit (its value depends on the heights
 // through the normal), HF_NO_PRIM otherwise.
 __device__ __forceinline__ float hf_shade_sample(const HfParams &P, const HfGrid &G, const HfRenderArgs &A, f3 dw, float t_start,
-                                                 int L_start, uint32_t &prim) {
+                                                 int L_start, uint32_t &prim, const unsigned conv = 0u) {
     prim = HF_NO_PRIM;
     const f3 d = xform_vector(P.to_object, dw);
     float ht, hu, hv; uint32_t hprim;
     f3 p0, p1, p2;
-    if (!hf_trace(P, G, A.o_obj, d, HF_INF, t_start, L_start, ht, hu, hv, hprim, p0, p1, p2)) return 0.f;
+    if (!hf_trace(P, G, A.o_obj, d, HF_INF, t_start, L_start, ht, hu, hv, hprim, p0, p1, p2, conv)) return 0.f;
     const f3 nw = hf_world_normal(P, p0, p1, p2);
     const f3 l = mk3(A.lx, A.ly, A.lz);
     const float cosl = dot3(nw, l);
@@ -344,7 +348,8 @@ hf_render_kernel(const __grid_constant__ HfParams P, const HfLaunchInfo li, cons
                 const uint32_t s = r * 32u + lane;
                 uint32_t prim = HF_NO_PRIM;
                 float v = 0.f;
-                if (s < spp) v = hf_shade_sample(P, G, A, hf_camera_dir(A, pid, s), ts, ls, prim);
+                const unsigned conv = __ballot_sync(FULL_MASK, s < spp);
+                if (s < spp) v = hf_shade_sample(P, G, A, hf_camera_dir(A, pid, s), ts, ls, prim, conv);
                 acc += v;
                 s_prim[warp][(r * 32u + lane) & (HF_RENDER_MAX_SPP - 1)] = prim;
                 if (MODE == HF_RENDER_FWD && prim_out && s < spp)

@@ -1,10 +1,15 @@
 // hf_traverse.cuh -- the production traversal: warp-uniform hierarchical DDA over the min/max pyramid.
 //
-// Same geometry and the same position arithmetic as the canonical traversal that defines the byte model
-// (oracle/hf_oracle.c::traverse, mirrored on the device by traverse_canonical in hf_kernels.cu), so it inherits its
-// conservativeness; what changes is the control structure, which is what the SMs pay for:
+// Same geometry as the canonical traversal that defines the byte model (oracle/hf_oracle.c::traverse, mirrored on the
+// device by traverse_canonical in hf_kernels.cu); what changes is the control structure and the data it reads, which is
+// what the SMs pay for (the kernel is bound by instruction issue, profiles/r01_notes.md):
 //   * ONE loop body for "descend", "step" and "leaf": every lane of a warp executes the same instructions each
 //     iteration and updates its state through selects (the canonical form serialises three divergent paths);
+//   * the loop reads the QUANTISED, power-of-two padded pyramid of hf_qpyr.h, which has a level 0: one 4-byte load and
+//     the same decode at every level; the four texels of a cell are fetched only when the cell becomes a candidate;
+//   * the ray is walked in MIRRORED cell coordinates (ix' = Mx-1-ix when it travels towards -x, same for y) and in a
+//     FLIPPED z (z' = -z when it climbs): it then always moves towards +x', +y', -z', so the loop has no per-axis
+//     direction selects and no min/max of the two z end points;
 //   * the walk starts at level min(Ltop, HF_START_LEVEL) instead of the root (the root-side levels always overlap
 //     at the entry point), and after a step it may pop several levels at once (HF_POP_LEVELS) when the step crossed
 //     a coarse node boundary;
@@ -20,6 +25,7 @@
 #pragma once
 #include <math.h>
 #include <stdint.h>
+#include "hf_qpyr.h"
 
 #ifdef __CUDACC__
 #define HF_HD __device__ __forceinline__
@@ -50,9 +56,16 @@ struct __attribute__((aligned(16))) HfLevel {   // one pyramid level; `nodes` ma
     int pad;
 };
 
+struct __attribute__((aligned(16))) HfQLevel {  // one level of the quantised pyramid (global memory)
+    const uint32_t *nodes;     // row-major, (hi << 16) | lo codes
+    int pitch;                 // nodes per row (a power of two)
+    int pad;
+};
+
 #ifdef __CUDACC__
 #define HF_LVL_ENTRIES 26
 __shared__ HfLevel hf_s_lvl[HF_LVL_ENTRIES];      // filled by the kernel prologue
+__shared__ HfQLevel hf_s_qlvl[HF_LVL_ENTRIES];    // level 0..Ltop of the quantised pyramid
 #endif
 
 struct HfGrid {                // what the walk needs to know about the shape
@@ -62,19 +75,30 @@ struct HfGrid {                // what the walk needs to know about the shape
     const float *heights;      // (H, W)
     const HfLevel *lvl;        // [level 1..Ltop]; the table itself sits in shared memory on the device
     float top_min, top_max;    // root node
+    // quantised pyramid (hf_qpyr.h): what hf_walk_next reads
+    const HfQLevel *qlvl;      // [level 0..QLtop] (host build; the device reads hf_s_qlvl through qlvl_saddr)
+    uint32_t qlvl_saddr;       // shared-memory address of hf_s_qlvl (device)
+    int QLtop;                 // top level of the quantised pyramid (one node)
+    int xmask, ymask;          // Mx - 1, My - 1 (padded cell counts are powers of two)
+    float qs, zb;              // decode(c) = fmaf(float(c), qs, zb)
 };
 
-struct HfWalk {                // per-ray state, lives in registers
-    float ogx, ogy, dgx, dgy, oz, dz;
+struct HfWalk {                // per-ray state, lives in registers. x, y are MIRRORED grid units, z is FLIPPED (see top)
+    float ogx, ogy, dgx, dgy;  // dgx, dgy >= 0
+    float ogxl, ogyl;          // low parts of the mirrored origin: Mx - og is kept EXACTLY as ogx + ogxl (a rounded mirror image is a
+                               // different ray: next to a cell boundary a nearly axis-parallel ray would leave its row far too early)
+    float dz;                  // <= 0
     float idx, idy;            // 1/dg; after hf_walk_init: 0 when the component is zero ...
     float infx, infy;          // ... and +inf here (0 otherwise), so that t_exit = fma(b - og, id, inf) needs no select
-    float t1, epsz;
+    float t1;
     float t;                   // ray parameter at the entry of the current node
     float idz;                 // 1/dz (0 when dz == 0)
-    float zeps;                // +epsz for a descending ray (enters a node's z slab through its max), -epsz otherwise
+    float ozp, ozm;            // oz + epsz, oz - epsz: z(t) padded up / down by the walk's z slack
     float ogxb, ogyb;          // og backed off against the direction of travel: cells derived from t are never ahead of the ray
-    int ix, iy, L;
-    int sx, sy;                // 1 when the ray moves towards +x / +y
+    float qsf, zbf;            // decode constants of the quantised nodes, negated for a flipped ray
+    int ix, iy, L;             // mirrored cell, level
+    int xm, ym;                // mirror masks: real cell = (ix ^ xm, iy ^ ym)
+    uint32_t sel_lo;           // byte selector (prmt) of the node half that bounds z' from below
     bool alive;
 };
 
@@ -113,20 +137,19 @@ HF_HD bool hf_walk_init(const HfGrid &G, float ox, float oy, float oz, float dx,
     if (dx == 0.f && dy == 0.f && dz == 0.f) return false;
     if (!(maxt >= 0.f)) return false;
     const int NX = G.NX, NY = G.NY;
-    w.ogx = (ox - G.x0) * G.sgx; w.ogy = (oy - G.y0) * G.sgy;
-    w.dgx = dx * G.sgx; w.dgy = dy * G.sgy;
-    w.oz = oz; w.dz = dz;
-    w.idx = HF_RCP(w.dgx); w.idy = HF_RCP(w.dgy);           // correctly rounded on both sides (== 1.0f / x)
-    const float idz = HF_RCP(dz);
+    float ogx = (ox - G.x0) * G.sgx, ogy = (oy - G.y0) * G.sgy;
+    float dgx = dx * G.sgx, dgy = dy * G.sgy;
+    float idx = HF_RCP(dgx), idy = HF_RCP(dgy);             // correctly rounded on both sides (== 1.0f / x)
+    float idz = HF_RCP(dz);
     float t0 = 0.f, t1 = maxt;
-    if (w.dgx != 0.f) {
-        float a = (0.f - w.ogx) * w.idx, b = ((float) NX - w.ogx) * w.idx;
+    if (dgx != 0.f) {
+        float a = (0.f - ogx) * idx, b = ((float) NX - ogx) * idx;
         t0 = fmaxf(t0, fminf(a, b)); t1 = fminf(t1, fmaxf(a, b));
-    } else if (w.ogx < 0.f || w.ogx > (float) NX) return false;
-    if (w.dgy != 0.f) {
-        float a = (0.f - w.ogy) * w.idy, b = ((float) NY - w.ogy) * w.idy;
+    } else if (ogx < 0.f || ogx > (float) NX) return false;
+    if (dgy != 0.f) {
+        float a = (0.f - ogy) * idy, b = ((float) NY - ogy) * idy;
         t0 = fmaxf(t0, fminf(a, b)); t1 = fminf(t1, fmaxf(a, b));
-    } else if (w.ogy < 0.f || w.ogy > (float) NY) return false;
+    } else if (ogy < 0.f || ogy > (float) NY) return false;
     {
         const float pad = HF_TRAV_SLACK * fmaxf(fabsf(G.top_min), fabsf(G.top_max)) + HF_TRAV_SLACK * fabsf(oz);
         if (dz != 0.f) {
@@ -138,33 +161,62 @@ HF_HD bool hf_walk_init(const HfGrid &G, float ox, float oy, float oz, float dx,
     }
     if (!(t0 <= t1)) return false;
     w.t1 = t1;
-    w.epsz = HF_TRAV_SLACK * (fabsf(oz) + fabsf(t1 * dz));
-    w.sx = w.dgx > 0.f ? 1 : 0; w.sy = w.dgy > 0.f ? 1 : 0;
-    {   // 4 ulp of the largest grid coordinate the ray reaches: a cell derived from a ray parameter is never ahead of the true one
-        const float ex = 2.384185791015625e-07f * (fabsf(w.ogx) + fabsf(t1 * w.dgx));
-        const float ey = 2.384185791015625e-07f * (fabsf(w.ogy) + fabsf(t1 * w.dgy));
-        w.ogxb = w.ogx + (w.sx ? -ex : ex); w.ogyb = w.ogy + (w.sy ? -ey : ey);
-    }
-    if (t_start > t0) {            // nothing can be hit before t_start: enter the grid there, one cell back at most
+    const float epsz = HF_TRAV_SLACK * (fabsf(oz) + fabsf(t1 * dz));
+    // entry cell in REAL coordinates (same arithmetic as the canonical walk), then mirrored below
+    int ix, iy;
+    const bool late = t_start > t0;          // nothing can be hit before t_start: enter the grid there, one cell back at most
+    if (late) {
         if (!(t_start <= t1)) return false;
         t0 = t_start;
-        w.ix = hf_imin(hf_imax(hf_floor_sat(fmaf(t0, w.dgx, w.ogxb)), 0), NX - 1);
-        w.iy = hf_imin(hf_imax(hf_floor_sat(fmaf(t0, w.dgy, w.ogyb)), 0), NY - 1);
-        w.L = hf_imin(G.Ltop, L_start);
-    } else {
-        w.ix = hf_imin(hf_imax(hf_floor_sat(fmaf(t0, w.dgx, w.ogx)), 0), NX - 1);
-        w.iy = hf_imin(hf_imax(hf_floor_sat(fmaf(t0, w.dgy, w.ogy)), 0), NY - 1);
-        w.L = hf_imin(G.Ltop, HF_START_LEVEL);
     }
+    {   // 6 ulp of the largest grid coordinate the ray reaches (in either orientation): a cell derived from a ray parameter
+        // is never ahead of the true one; covers the one extra rounding of the mirrored origin
+        const float ex = 3.5762786865234375e-07f * ((float) (G.xmask + 1) + fabsf(ogx) + fabsf(t1 * dgx));
+        const float ey = 3.5762786865234375e-07f * ((float) (G.ymask + 1) + fabsf(ogy) + fabsf(t1 * dgy));
+        const float bx0 = late ? (dgx > 0.f ? ogx - ex : ogx + ex) : ogx, by0 = late ? (dgy > 0.f ? ogy - ey : ogy + ey) : ogy;
+        ix = hf_imin(hf_imax(hf_floor_sat(fmaf(t0, dgx, bx0)), 0), NX - 1);
+        iy = hf_imin(hf_imax(hf_floor_sat(fmaf(t0, dgy, by0)), 0), NY - 1);
+        // mirror: the walk only ever moves towards +x', +y'
+        const bool mx_ = dgx < 0.f, my_ = dgy < 0.f;
+        w.xm = mx_ ? G.xmask : 0; w.ym = my_ ? G.ymask : 0;
+        w.ogxl = 0.f; w.ogyl = 0.f;
+        if (mx_) {                           // two-sum: M + (-og) = s + e exactly
+            const float a = (float) (G.xmask + 1), b = -ogx, sm = a + b, bb = sm - a;
+            w.ogxl = (a - (sm - bb)) + (b - bb); ogx = sm; dgx = -dgx; idx = -idx;
+        }
+        if (my_) {
+            const float a = (float) (G.ymask + 1), b = -ogy, sm = a + b, bb = sm - a;
+            w.ogyl = (a - (sm - bb)) + (b - bb); ogy = sm; dgy = -dgy; idy = -idy;
+        }
+        w.ogx = ogx; w.ogy = ogy; w.dgx = dgx; w.dgy = dgy;
+        w.ogxb = ogx - ex; w.ogyb = ogy - ey;
+        w.ix = ix ^ w.xm; w.iy = iy ^ w.ym;
+    }
+    w.L = hf_imin(G.QLtop, late ? L_start : HF_START_LEVEL);
     w.t = t0;
-    w.idz = dz != 0.f ? idz : 0.f;
-    w.zeps = dz < 0.f ? w.epsz : -w.epsz;
+    {   // flip z for a climbing ray: the walk only ever moves towards -z'
+        const bool fz = dz > 0.f;
+        const float ozf = fz ? -oz : oz;
+        w.dz = fz ? -dz : dz;
+        w.idz = dz != 0.f ? (fz ? -idz : idz) : 0.f;
+        w.ozp = ozf + epsz; w.ozm = ozf - epsz;
+        w.qsf = fz ? -G.qs : G.qs; w.zbf = fz ? -G.zb : G.zb;
+        w.sel_lo = fz ? 0x4432u : 0x4410u;
+    }
     const float inf = INFINITY;
-    w.infx = w.dgx != 0.f ? 0.f : inf; w.infy = w.dgy != 0.f ? 0.f : inf;
-    if (w.dgx == 0.f) w.idx = 0.f;
-    if (w.dgy == 0.f) w.idy = 0.f;
+    w.infx = dgx != 0.f ? 0.f : inf; w.infy = dgy != 0.f ? 0.f : inf;
+    w.idx = dgx != 0.f ? idx : 0.f;
+    w.idy = dgy != 0.f ? idy : 0.f;
     w.alive = true;
     return true;
+}
+
+HF_HD uint32_t hf_prmt(uint32_t q, uint32_t sel) {      // __byte_perm(q, 0, sel) for the two selectors the walk uses
+#ifdef __CUDACC__
+    return __byte_perm(q, 0u, sel);
+#else
+    return ((sel & 0xffu) == 0x10u) ? (q & 0xffffu) : (q >> 16);
+#endif
 }
 
 // Advance the walk until a leaf cell overlaps the ray's z interval (returns true, cell in `c`, and the state is
@@ -176,81 +228,82 @@ HF_HD bool hf_walk_next(const HfGrid &G, HfWalk &w, HfCand &c
 #endif
 ) {
     if (!w.alive) return false;
-    const int NX = G.NX, NY = G.NY, Ltop = G.Ltop;
+    const int NX_ = G.NX, NY_ = G.NY;
+    const uint32_t sel_hi = w.sel_lo ^ 0x0022u;
     for (;;) {
 #ifndef __CUDACC__
         if (iters) ++*iters;
 #endif
         const int L = w.L, ix = w.ix, iy = w.iy;
-        const int nx = ix >> L, ny = iy >> L;
-        const int lox = nx << L, loy = ny << L, span = 1 << L;
-        const int bx = w.sx ? lox + span : lox, by = w.sy ? loy + span : loy;      // exit planes of this node
-        // (float(b) - og) * id, exactly as the canonical walk; the fma only adds +0 or +inf
-        const float tx = fmaf((float) bx - w.ogx, w.idx, w.infx);
-        const float ty = fmaf((float) by - w.ogy, w.idy, w.infy);
+        const int mask = (1 << L) - 1;
+        const int hx = ix | mask, hy = iy | mask;                 // last cell of this node on each axis
+        const int bx = hx + 1, by = hy + 1;                       // exit planes of this node
+        const float tx = fmaf(((float) bx - w.ogx) - w.ogxl, w.idx, w.infx); // the fma only adds +0 or +inf
+        const float ty = fmaf(((float) by - w.ogy) - w.ogyl, w.idy, w.infy);
         const float tmin = fminf(tx, ty);
         const bool last = !(tmin < w.t1);
         const float te = fminf(tmin, w.t1);
-        const float za = fmaf(w.t, w.dz, w.oz), zb = fmaf(te, w.dz, w.oz);
-        const float zlo = fminf(za, zb) - w.epsz, zhi = fmaxf(za, zb) + w.epsz;
+        // z' never increases along the ray: its padded range over [t, te] is [z'(te) - eps, z'(t) + eps]
+        const float zhi = fmaf(w.t, w.dz, w.ozp), zlo = fmaf(te, w.dz, w.ozm);
 
-        float mn, mx;
-        if (L > 0) {
+        uint32_t q;
+        {
 #ifdef __CUDACC__
-            const HfLevel lv = hf_s_lvl[L];           // the table is a __shared__ array: the address is L*16 + a constant
+            uint32_t p0, p1, pitch, pad_;
+            asm("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(p0), "=r"(p1), "=r"(pitch), "=r"(pad_) : "r"(G.qlvl_saddr + (uint32_t) L * 16u));
+            (void) pad_;
+            const uint32_t *nodes = reinterpret_cast<const uint32_t *>(((unsigned long long) p1 << 32) | (unsigned long long) p0);
+            q = HF_LDG(nodes + (unsigned) (((iy ^ w.ym) >> L) * (int) pitch + ((ix ^ w.xm) >> L)));
 #else
-            const HfLevel lv = G.lvl[L];
+            const HfQLevel lv = G.qlvl[L];
+            q = lv.nodes[(unsigned) (((iy ^ w.ym) >> L) * lv.pitch + ((ix ^ w.xm) >> L))];
 #endif
-            const float2 nd = lv.nodes[ny * lv.w + nx];
-            mn = nd.x; mx = nd.y;
-        } else {
-            const float *row0 = G.heights + (unsigned) (iy * G.W + ix);          // W*H < 2^32 (checked by hf_create)
-            c.z00 = G.mh * HF_LDG(row0); c.z10 = G.mh * HF_LDG(row0 + 1);
-            c.z01 = G.mh * HF_LDG(row0 + G.W); c.z11 = G.mh * HF_LDG(row0 + G.W + 1);
-            mn = fminf(fminf(c.z00, c.z10), fminf(c.z01, c.z11));
-            mx = fmaxf(fmaxf(c.z00, c.z10), fmaxf(c.z01, c.z11));
-            c.cx = ix; c.cy = iy;
         }
+        const float mn = fmaf((float) hf_prmt(q, w.sel_lo), w.qsf, w.zbf);
+        const float mx = fmaf((float) hf_prmt(q, sel_hi), w.qsf, w.zbf);
         const bool overlap = (zlo <= mx) && (zhi >= mn);
         const bool desc = overlap && (L > 0);
         const bool found = overlap && (L == 0);
 
-        // Descending lanes first clip their entry point to the node's z slab [mn, mx]: before the ray crosses
-        // zbnd it cannot touch anything inside this node, so the children in front of that point are skipped.
-        const float zbnd = (w.dz < 0.f ? mx : mn) + w.zeps;
-        float ts = (zbnd - w.oz) * w.idz;
-        ts -= fabsf(ts) * HF_TRAV_SLACK;                                  // never later than the true crossing
+        // Descending lanes first clip their entry point to the node's z slab: before the ray crosses mx + eps it
+        // cannot touch anything inside this node, so the children in front of that point are skipped.
+        float ts = (mx - w.ozm) * w.idz;
+        ts = fmaf(-fabsf(ts), HF_TRAV_SLACK, ts);                         // never later than the true crossing
         const float tc = fminf(fmaxf(w.t, ts), te);
         // tq: the parameter the next cell is derived from -- the clipped entry (descend) or the node's exit (step)
         const float tq = desc ? tc : te;
-        const bool stepx = tx <= ty, stepy = ty <= tx;
         const int qx = hf_floor_sat(fmaf(tq, w.dgx, w.ogxb)), qy = hf_floor_sat(fmaf(tq, w.dgy, w.ogyb));
-        const int hix = hf_imin(lox + span - 1, NX - 1), hiy = hf_imin(loy + span - 1, NY - 1);
         // position at tq, kept inside the node and monotone along the ray
-        const int rx = hf_imin(hf_imax(qx, w.sx ? ix : lox), w.sx ? hix : ix);
-        const int ry = hf_imin(hf_imax(qy, w.sy ? iy : loy), w.sy ? hiy : iy);
+        const int rx = hf_imin(hf_imax(qx, ix), hx), ry = hf_imin(hf_imax(qy, iy), hy);
         // a step leaves the node through the plane(s) reached first; a descent stays inside
-        const int nix = (stepx && !desc) ? (w.sx ? bx : bx - 1) : rx;
-        const int niy = (stepy && !desc) ? (w.sy ? by : by - 1) : ry;
-        const bool outside = ((unsigned) nix >= (unsigned) NX) || ((unsigned) niy >= (unsigned) NY);
+        const bool stepx = !desc && (tx <= ty), stepy = !desc && (ty <= tx);
+        const int nix = stepx ? bx : rx, niy = stepy ? by : ry;
+        const bool outside = ((unsigned) nix > (unsigned) G.xmask) || ((unsigned) niy > (unsigned) G.ymask);
         const unsigned m = (unsigned) ((nix ^ ix) | (niy ^ iy));
-#if HF_POP_LEVELS == 1
-        const int nL = ((m >> (L + 1)) != 0u && L < Ltop) ? L + 1 : L;                  // left the parent node: go up one level
-#else
-        const int b = hf_msb(m | 1u);                                                   // coarsest node boundary crossed
-        const int nL = hf_imin(hf_imin(hf_imax(b, L), L + HF_POP_LEVELS), Ltop);
-#endif
+        const bool up = m > (unsigned) (2 * mask + 1);                    // left the parent node: go up one level
 
 #if !defined(__CUDACC__) && defined(HF_WALK_HIST)
         { extern unsigned long long hf_walk_hist[3][32];
           _Pragma("omp atomic") hf_walk_hist[desc ? 0 : (found ? 2 : 1)][L]++; }
 #endif
-        w.L = desc ? hf_imax(L - HF_DESC_LEVELS, 0) : nL;
+        w.L = desc ? hf_imax(L - HF_DESC_LEVELS, 0) : (up ? L + 1 : L);
         w.ix = nix;
         w.iy = niy;
         w.t = tq;
         w.alive = desc ? true : !(last || outside);
-        if (found) return true;
+        if (found) {
+#ifdef __CUDACC__
+            asm volatile("");                                             // keep the guard below out of the loop body
+#endif
+            const int cx = ix ^ w.xm, cy = iy ^ w.ym;
+            if (cx < NX_ && cy < NY_) {                                   // padding cells hold HF_Q_EMPTY; belt and braces
+                const float *row0 = G.heights + (unsigned) (cy * G.W + cx);          // W*H < 2^32 (checked by hf_create)
+                c.z00 = G.mh * HF_LDG(row0); c.z10 = G.mh * HF_LDG(row0 + 1);
+                c.z01 = G.mh * HF_LDG(row0 + G.W); c.z11 = G.mh * HF_LDG(row0 + G.W + 1);
+                c.cx = cx; c.cy = cy;
+                return true;
+            }
+        }
         if (!w.alive) return false;
     }
 }

@@ -47,6 +47,10 @@ __device__ __forceinline__ void hf_stage_pyramid(const HfParams &P, const HfLaun
         e.nodes = (li.top_nodes > 0 && l >= li.top_level_start) ? (s_nodes + (P.lvl_off[l] - li.top_off)) : (P.pyr + P.lvl_off[l]);
         e.w = P.lvl_w[l]; e.pad = 0;
         s_lvl[l] = e;
+        HfQLevel qe;                                           // quantised pyramid: global memory at every level (L1 / L2 resident)
+        qe.nodes = P.qpyr + P.qoff[l];
+        qe.pitch = ((P.xmask + 1) >> l) > 0 ? ((P.xmask + 1) >> l) : 1; qe.pad = 0;
+        hf_s_qlvl[l] = qe;
     }
     __syncthreads();
     if (li.top_nodes > 0) {
@@ -65,7 +69,11 @@ __device__ __forceinline__ void hf_stage_pyramid(const HfParams &P, const HfLaun
     {
         const float2 top = s_lvl[P.Ltop].nodes[0];
         G.top_min = top.x; G.top_max = top.y;
+        const HfQuant Q = hf_quant_make(top.x, top.y);         // the same expression the builder used
+        G.qs = Q.qs; G.zb = Q.zb;
     }
+    G.qlvl = hf_s_qlvl; G.qlvl_saddr = smem_u32(hf_s_qlvl);
+    G.QLtop = P.QLtop; G.xmask = P.xmask; G.ymask = P.ymask;
 
 }
 

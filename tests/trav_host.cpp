@@ -16,6 +16,44 @@ extern "C" unsigned long long *trav_host_hist(void) { return &hf_walk_hist[0][0]
 #include "../mitsuba3-differentiable-heightfield-rendering_b200/csrc/hf_traverse.cuh"
 #include "../oracle/hf_oracle.h"
 
+
+// Quantised pyramid (csrc/hf_qpyr.h) built on the host with the very functions the device builder uses.
+struct HostQPyr {
+    std::vector<uint32_t> nodes;
+    std::vector<HfQLevel> lvl;
+    HfQLayout lay;
+    void build(const hfo_shape *s, float top_min, float top_max) {
+        const int NX = s->W - 1, NY = s->H - 1;
+        lay = hf_qlayout(NX, NY);
+        nodes.assign(lay.nodes, HF_Q_EMPTY);
+        const HfQuant Q = hf_quant_make(top_min, top_max);
+        for (int y = 0; y < NY; ++y)
+            for (int x = 0; x < NX; ++x) {
+                const float *r0 = s->heights + (size_t) y * s->W + x;
+                const float z00 = s->max_height * r0[0], z10 = s->max_height * r0[1], z01 = s->max_height * r0[s->W], z11 = s->max_height * r0[s->W + 1];
+                nodes[lay.off[0] + (size_t) y * lay.pitch[0] + x] =
+                    hf_quant_node(fminf(fminf(z00, z10), fminf(z01, z11)), fmaxf(fmaxf(z00, z10), fmaxf(z01, z11)), Q);
+            }
+        for (int l = 1; l <= lay.Ltop; ++l) {
+            const int fx = lay.pitch[l - 1] / lay.pitch[l], fy = lay.rows[l - 1] / lay.rows[l];
+            for (int ny = 0; ny < lay.rows[l]; ++ny)
+                for (int nx = 0; nx < lay.pitch[l]; ++nx) {
+                    uint32_t q = HF_Q_EMPTY;
+                    for (int dj = 0; dj < fy; ++dj)
+                        for (int di = 0; di < fx; ++di)
+                            q = hf_quant_merge(q, nodes[lay.off[l - 1] + (size_t) (ny * fy + dj) * lay.pitch[l - 1] + (nx * fx + di)]);
+                    nodes[lay.off[l] + (size_t) ny * lay.pitch[l] + nx] = q;
+                }
+        }
+        lvl.resize(lay.Ltop + 1);
+        for (int l = 0; l <= lay.Ltop; ++l) { lvl[l].nodes = nodes.data() + lay.off[l]; lvl[l].pitch = lay.pitch[l]; lvl[l].pad = 0; }
+    }
+    void attach(HfGrid &G, float top_min, float top_max) const {
+        const HfQuant Q = hf_quant_make(top_min, top_max);
+        G.qlvl = lvl.data(); G.qlvl_saddr = 0; G.QLtop = lay.Ltop; G.xmask = lay.Mx - 1; G.ymask = lay.My - 1; G.qs = Q.qs; G.zb = Q.zb;
+    }
+};
+
 // rounds (nullable): uint32[n][8], loop iterations spent in each call of hf_walk_next (candidate round)
 extern "C" int trav_host_intersect(const hfo_shape *s, const hfo_rays *r, size_t n, hfo_prelim *out,
                                    uint32_t *iters, uint32_t *cands, uint32_t *rounds) {
@@ -36,6 +74,7 @@ extern "C" int trav_host_intersect(const hfo_shape *s, const hfo_rays *r, size_t
     G.sgx = 0.5f * (float) G.NX; G.sgy = 0.5f * (float) G.NY;
     G.heights = s->heights; G.lvl = lvl.data();
     G.top_min = lvl[Ltop].nodes[0].x; G.top_max = lvl[Ltop].nodes[0].y;
+    HostQPyr qp; qp.build(s, G.top_min, G.top_max); qp.attach(G, G.top_min, G.top_max);
 
     #pragma omp parallel for schedule(dynamic, 1024)
     for (long long ii = 0; ii < (long long) n; ++ii) {
@@ -75,6 +114,9 @@ extern "C" int trav_host_intersect(const hfo_shape *s, const hfo_rays *r, size_t
     return 0;
 }
 
+static uint32_t *g_beam_rounds = nullptr;      // dev statistics: uint32[n][8] iterations per candidate round (bundled variant)
+extern "C" void trav_host_set_beam_rounds(uint32_t *p) { g_beam_rounds = p; }
+
 // Bundled variant: every 32 consecutive rays with a bit-identical origin form a bundle; hf_beam_enter gives the bundle's
 // entry parameter and each ray walks from there. beam_iters (nullable): uint32[n/32] iterations of the bundle march.
 extern "C" int trav_host_intersect_beam(const hfo_shape *s, const hfo_rays *r, size_t n, hfo_prelim *out,
@@ -96,6 +138,7 @@ extern "C" int trav_host_intersect_beam(const hfo_shape *s, const hfo_rays *r, s
     G.sgx = 0.5f * (float) G.NX; G.sgy = 0.5f * (float) G.NY;
     G.heights = s->heights; G.lvl = lvl.data();
     G.top_min = lvl[Ltop].nodes[0].x; G.top_max = lvl[Ltop].nodes[0].y;
+    HostQPyr qp; qp.build(s, G.top_min, G.top_max); qp.attach(G, G.top_min, G.top_max);
     const float *m = s->to_object;
     auto xf = [&](size_t i, float o[3], float d[3]) {
         const float ow[3] = { r->ox[i], r->oy[i], r->oz[i] }, dw[3] = { r->dx[i], r->dy[i], r->dz[i] };
@@ -141,7 +184,11 @@ extern "C" int trav_host_intersect_beam(const hfo_shape *s, const hfo_rays *r, s
                 float o[3], d[3]; xf(i, o, d);
                 HfWalk w; HfCand c;
                 if (hf_walk_init(G, o[0], o[1], o[2], d[0], d[1], d[2], r->maxt[i], w, t_enter, L_start)) {
-                    while (hf_walk_next(G, w, c, &it)) {
+                    for (;;) {
+                        const unsigned before = it;
+                        const bool more = hf_walk_next(G, w, c, &it);
+                        if (g_beam_rounds && nc < 8) g_beam_rounds[8 * i + nc] = it - before;
+                        if (!more) break;
                         ++nc;
                         float t, u, v; uint32_t prim;
                         if (hfo_cell_intersect(s, c.cx, c.cy, o, d, r->maxt[i], &t, &u, &v, &prim)) { bt = t; bu = u; bv = v; bp = prim; break; }
