@@ -86,6 +86,7 @@ static int nccl_load() {
 // ------------------------------------------------------------------------------------------
 // context
 // ------------------------------------------------------------------------------------------
+#define HF_SCHED_SLOTS 256            // every launch of a self-scheduling kernel gets its own counter (launches on different streams overlap)
 #define HF_TOP_NODE_CAP 1366          // (32^2 + 16^2 + ... + 1) rounded up to even: 10.9 KB of shared memory
 #define HF_HOST_CHUNK (size_t(1) << 21)
 #define HF_HOST_SLOTS 2
@@ -107,7 +108,8 @@ struct hf_ctx {
     float2 *d_pyr = nullptr;
     uint32_t *d_qpyr = nullptr;      // quantised pyramid (hf_qpyr.h)
     size_t qpyr_nodes = 0;
-    unsigned long long *d_counters = nullptr;
+    unsigned long long *d_counters = nullptr;     // [0..3] traversal statistics, [8..8+HF_SCHED_SLOTS) tile counters of the persistent kernels
+    unsigned sched_next = 0;
     float *d_scratch = nullptr;       // two images (path-traced L2 step)
     size_t scratch_bytes = 0;
     bool have_heights = false, accel_valid = false;
@@ -149,6 +151,8 @@ static int set_transform(hf_ctx *c, const float to_world[12], const float *to_ob
     for (int i = 0; i < 12; ++i) if (!isfinite(c->P.to_object[i])) return fail(HF_ERR_INVALID, "to_world is singular");
     return HF_OK;
 }
+
+static unsigned long long *next_sched(hf_ctx *c) { return c->d_counters + 8 + (c->sched_next++ % HF_SCHED_SLOTS); }
 
 static void layout_pyramid(hf_ctx *c) {
     HfParams &P = c->P;
@@ -226,13 +230,13 @@ extern "C" int hf_create(hf_ctx **out, const hf_desc *desc) {
     cudaError_t e1 = cudaMalloc(&c->d_heights, texels * sizeof(float));
     cudaError_t e2 = cudaMalloc(&c->d_grad, texels * sizeof(float));
     cudaError_t e3 = cudaMalloc(&c->d_pyr, c->pyr_nodes * sizeof(float2));
-    cudaError_t e4 = cudaMalloc(&c->d_counters, 8 * sizeof(unsigned long long));
+    cudaError_t e4 = cudaMalloc(&c->d_counters, (8 + HF_SCHED_SLOTS) * sizeof(unsigned long long));
     if (c->qpyr_nodes >= (size_t(1) << 32)) { hf_destroy(c); return fail(HF_ERR_INVALID, "%ux%u heightfield: padded acceleration pyramid exceeds 2^32 nodes", c->W, c->H); }
     cudaError_t e5 = cudaMalloc(&c->d_qpyr, c->qpyr_nodes * sizeof(uint32_t));
     if (e1 || e2 || e3 || e4 || e5) { hf_destroy(c); return fail(HF_ERR_CUDA, "cudaMalloc failed for a %ux%u heightfield", c->W, c->H); }
     cudaMemset(c->d_grad, 0, texels * sizeof(float));
     cudaMemset(c->d_pyr, 0, c->pyr_nodes * sizeof(float2));
-    cudaMemset(c->d_counters, 0, 8 * sizeof(unsigned long long));
+    cudaMemset(c->d_counters, 0, (8 + HF_SCHED_SLOTS) * sizeof(unsigned long long));
     P.heights = c->d_heights;
     P.pyr = c->d_pyr;
     P.qpyr = c->d_qpyr;
@@ -401,7 +405,7 @@ extern "C" int hf_ray_intersect_preliminary(hf_ctx *c, const hf_rays *rays, cons
     NEED_ACCEL(c);
     CU(cudaSetDevice(c->device));
     hf_si none; memset(&none, 0, sizeof(none));
-    CU(hf_launch_intersect(c->P, c->li, HF_MODE_PRELIM, *rays, *out, none, nullptr, 0, n, c->d_counters, (cudaStream_t) stream));
+    CU(hf_launch_intersect(c->P, c->li, HF_MODE_PRELIM, *rays, *out, none, nullptr, 0, n, c->d_counters, next_sched(c), (cudaStream_t) stream));
     return HF_OK;
 }
 
@@ -413,7 +417,7 @@ extern "C" int hf_ray_intersect_preliminary_counted(hf_ctx *c, const hf_rays *ra
     NEED_ACCEL(c);
     CU(cudaSetDevice(c->device));
     hf_si none; memset(&none, 0, sizeof(none));
-    CU(hf_launch_intersect(c->P, c->li, HF_MODE_COUNTED, *rays, *out, none, nullptr, 0, n, c->d_counters, (cudaStream_t) stream));
+    CU(hf_launch_intersect(c->P, c->li, HF_MODE_COUNTED, *rays, *out, none, nullptr, 0, n, c->d_counters, next_sched(c), (cudaStream_t) stream));
     return HF_OK;
 }
 
@@ -439,7 +443,7 @@ extern "C" int hf_ray_test(hf_ctx *c, const hf_rays *rays, uint8_t *d_hit, size_
     CU(cudaSetDevice(c->device));
     hf_si none; memset(&none, 0, sizeof(none));
     hf_prelim nop; memset(&nop, 0, sizeof(nop));
-    CU(hf_launch_intersect(c->P, c->li, HF_MODE_TEST, *rays, nop, none, d_hit, 0, n, c->d_counters, (cudaStream_t) stream));
+    CU(hf_launch_intersect(c->P, c->li, HF_MODE_TEST, *rays, nop, none, d_hit, 0, n, c->d_counters, next_sched(c), (cudaStream_t) stream));
     return HF_OK;
 }
 
@@ -475,7 +479,7 @@ extern "C" int hf_ray_intersect(hf_ctx *c, const hf_rays *rays, uint32_t flags, 
     CU(cudaSetDevice(c->device));
     hf_prelim nop; memset(&nop, 0, sizeof(nop));
     CU(hf_launch_intersect(c->P, c->li, HF_MODE_FUSED_SI, *rays, prelim_out ? *prelim_out : nop, *out, nullptr, flags, n,
-                           c->d_counters, (cudaStream_t) stream));
+                           c->d_counters, next_sched(c), (cudaStream_t) stream));
     return HF_OK;
 }
 
@@ -624,7 +628,7 @@ extern "C" int hf_render_forward(hf_ctx *c, const hf_camera *cam, const hf_light
     NEED_ACCEL(c);
     CU(cudaSetDevice(c->device));
     CU(hf_launch_render(c->P, c->li, 0, *cam, *light, d_pixels, npix, d_image, d_prim, nullptr, nullptr, nullptr, nullptr,
-                        c->d_counters + 4, (cudaStream_t) stream));
+                        next_sched(c), (cudaStream_t) stream));
     return HF_OK;
 }
 
@@ -644,7 +648,7 @@ extern "C" int hf_render_backward(hf_ctx *c, const hf_camera *cam, const hf_ligh
     } else {
         NEED_ACCEL(c);
         CU(hf_launch_render(c->P, c->li, 2, *cam, *light, d_pixels, npix, nullptr, nullptr, nullptr, d_adj_image, c->d_grad, nullptr,
-                            c->d_counters + 4, (cudaStream_t) stream));
+                            next_sched(c), (cudaStream_t) stream));
     }
     return HF_OK;
 }
@@ -670,14 +674,14 @@ extern "C" int hf_render_step_l2(hf_ctx *c, const hf_camera *cam, const hf_light
         }
         float *img = d_image ? d_image : c->d_scratch, *adj = c->d_scratch + (size_t) cam->width * cam->height;
         cudaStream_t st = (cudaStream_t) stream;
-        CU(hf_launch_render(c->P, c->li, 0, *cam, *light, d_pixels, npix, img, nullptr, nullptr, nullptr, nullptr, nullptr, c->d_counters + 4, st));
+        CU(hf_launch_render(c->P, c->li, 0, *cam, *light, d_pixels, npix, img, nullptr, nullptr, nullptr, nullptr, nullptr, next_sched(c), st));
         CU(hf_launch_l2_adjoint(c->P, c->li, *cam, d_pixels, npix, img, d_target, adj, d_loss, st));
         if (c->grad_enabled)
-            CU(hf_launch_render(c->P, c->li, 2, *cam, *light, d_pixels, npix, nullptr, nullptr, nullptr, adj, c->d_grad, nullptr, c->d_counters + 4, st));
+            CU(hf_launch_render(c->P, c->li, 2, *cam, *light, d_pixels, npix, nullptr, nullptr, nullptr, adj, c->d_grad, nullptr, next_sched(c), st));
         return HF_OK;
     }
     CU(hf_launch_render(c->P, c->li, 1, *cam, *light, d_pixels, npix, d_image, nullptr, d_target, nullptr, c->d_grad, d_loss,
-                        c->d_counters + 4, (cudaStream_t) stream));
+                        next_sched(c), (cudaStream_t) stream));
     return HF_OK;
 }
 
@@ -758,7 +762,7 @@ static int host_pipeline(hf_ctx *c, const hf_rays *hr, const hf_si_adj *hadj, ui
             }
         }
 
-        CU(hf_launch_intersect(c->P, c->li, HF_MODE_FUSED_SI, dr, dp, dsi, nullptr, flags, m, c->d_counters, s.stream));
+        CU(hf_launch_intersect(c->P, c->li, HF_MODE_FUSED_SI, dr, dp, dsi, nullptr, flags, m, c->d_counters, next_sched(c), s.stream));
         if (backward && c->grad_enabled)
             CU(hf_launch_backward(c->P, c->li, dr, dp, dadj, flags, c->d_grad, m, s.stream));
 

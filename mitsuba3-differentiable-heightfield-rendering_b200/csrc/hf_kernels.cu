@@ -9,6 +9,7 @@
 //   hf_adam_kernel           : src/python/python/ad/optimizers.py:263-302
 //
 // Compiled with -fmad=false: see hf_device.cuh.
+#include <stdlib.h>
 #include "hf_kernels.h"
 #include "hf_walk_common.cuh"
 
@@ -563,18 +564,32 @@ __device__ __forceinline__ void hf_process_ray(const HfParams &P, const HfGrid &
 #ifndef HF_MIN_CTAS
 #define HF_MIN_CTAS 4
 #endif
+#ifndef HF_FAST_GROUPS
+#define HF_FAST_GROUPS 4           // 32-ray groups a warp takes off the global counter at a time
+#endif
+// Persistent warps; each takes HF_FAST_GROUPS consecutive 32-ray groups at a time off one global counter: hit and miss regions of a
+// ray batch differ ~8x in cost per ray, and a static deal of tiles left the SMs idle 7 % of the kernel (profiles/r01_notes.md).
 template <int MODE>
 __global__ void __launch_bounds__(HF_BLOCK, HF_MIN_CTAS)
 hf_intersect_fast_kernel(const __grid_constant__ HfParams P, const HfLaunchInfo li, const hf_rays R, const hf_prelim O,
-                         const hf_si S, uint8_t *__restrict__ hit_out, const uint32_t flags, const size_t n) {
+                         const hf_si S, uint8_t *__restrict__ hit_out, const uint32_t flags, const size_t n,
+                         unsigned long long *__restrict__ sched) {
     HfGrid G;
     hf_stage_pyramid(P, li, G);
 
-    const size_t ntiles = (n + HF_BLOCK - 1) / HF_BLOCK;
-    for (size_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-        const size_t i = tile * HF_BLOCK + threadIdx.x;
-        if (i >= n) continue;
-        hf_process_ray<MODE>(P, G, R, O, S, hit_out, flags, i, 0.f, HF_START_LEVEL);
+    const unsigned lane = threadIdx.x & 31u;
+    const unsigned long long ngroups = (n + 31) / 32;
+    for (;;) {
+        unsigned long long g0 = 0;
+        if (lane == 0) g0 = atomicAdd(sched, (unsigned long long) HF_FAST_GROUPS);
+        g0 = __shfl_sync(FULL_MASK, g0, 0);
+        if (g0 >= ngroups) break;
+        #pragma unroll 1
+        for (unsigned g = 0; g < HF_FAST_GROUPS; ++g) {
+            const size_t i = (size_t) (g0 + g) * 32u + lane;
+            if (i < n) hf_process_ray<MODE>(P, G, R, O, S, hit_out, flags, i, 0.f, HF_START_LEVEL);
+            __syncwarp();
+        }
     }
 }
 
@@ -590,29 +605,42 @@ hf_intersect_fast_kernel(const __grid_constant__ HfParams P, const HfLaunchInfo 
 // Phase A reads the rays with default caching so that phase C finds them in L2; phase C streams (ld.cs / st.cs).
 // ------------------------------------------------------------------------------------------
 #define HF_WARP_TILE 1024
+#define HF_SMALL_GROUPS 4          // groups per tile in the closing phase of the schedule
+#ifndef HF_BEAM_EXACT_BOUNDS
+#define HF_BEAM_EXACT_BOUNDS 0
+#endif
+// Schedule: tiles come off one global counter. The first `nbig` tiles are 32 groups (1024 rays) wide, the remaining groups are
+// handed out HF_SMALL_GROUPS at a time: a 1024-ray tile is ~0.3 ms of one warp, and with only large tiles the SMs sat idle
+// 23 % of the kernel waiting for the last ones (profiles/r01_notes.md); the closing phase absorbs that imbalance.
 template <int MODE>
 __global__ void __launch_bounds__(HF_BLOCK, HF_MIN_CTAS)
 hf_intersect_beam_kernel(const __grid_constant__ HfParams P, const HfLaunchInfo li, const hf_rays R, const hf_prelim O,
                          const hf_si S, uint8_t *__restrict__ hit_out, const uint32_t flags, const size_t n,
-                         unsigned long long *__restrict__ sched) {
+                         const unsigned long long nbig, unsigned long long *__restrict__ sched) {
     HfGrid G;
     hf_stage_pyramid(P, li, G);
 
     const unsigned lane = threadIdx.x & 31u;
-    const size_t nwt = (n + HF_WARP_TILE - 1) / HF_WARP_TILE;
+    const unsigned long long ngroups = (n + 31) / 32;
     for (;;) {
-        // dynamic tile fetch: tiles differ several-fold in cost (hit / miss regions), a static deal leaves SMs idle at the end
         unsigned long long wt = 0;
         if (lane == 0) wt = atomicAdd(sched, 1ull);
         wt = __shfl_sync(FULL_MASK, wt, 0);
-        if (wt >= nwt) break;
-        const size_t base = (size_t) wt * HF_WARP_TILE;
+        unsigned long long g0;
+        unsigned ng;
+        if (wt < nbig) { g0 = wt * 32ull; ng = 32u; }
+        else {
+            g0 = nbig * 32ull + (wt - nbig) * HF_SMALL_GROUPS;
+            if (g0 >= ngroups) break;
+            ng = (unsigned) (ngroups - g0 < HF_SMALL_GROUPS ? ngroups - g0 : HF_SMALL_GROUPS);
+        }
+        const size_t base = (size_t) g0 * 32u;
         // ---- phase A: bundle bounds, lane g <- group g
         HfBeam B;
         B.ogx = B.ogy = B.oz = 0.f; B.dxl = B.dyl = B.dzl = 0.f; B.dxh = B.dyh = B.dzh = 0.f;
         bool bundle = false;
         #pragma unroll 2
-        for (unsigned g = 0; g < 32u; ++g) {
+        for (unsigned g = 0; g < ng; ++g) {
             const size_t i = base + (size_t) g * 32u + lane;
             bool valid = i < n;
             if (valid && R.active) valid = R.active[i] != 0;
@@ -623,12 +651,13 @@ hf_intersect_beam_kernel(const __grid_constant__ HfParams P, const HfLaunchInfo 
                 o = xform_point(P.to_object, ow); d = xform_vector(P.to_object, dw);
             }
             const unsigned vm = __ballot_sync(FULL_MASK, valid);
-            const int first = __ffs((int) vm) - 1;
-            const float ox0 = __shfl_sync(FULL_MASK, o.x, first & 31), oy0 = __shfl_sync(FULL_MASK, o.y, first & 31),
-                        oz0 = __shfl_sync(FULL_MASK, o.z, first & 31);
+            const int first = (__ffs((int) vm) - 1) & 31;
+            const float ox0 = __shfl_sync(FULL_MASK, o.x, first), oy0 = __shfl_sync(FULL_MASK, o.y, first),
+                        oz0 = __shfl_sync(FULL_MASK, o.z, first);
             const bool fin = (d.x == d.x) && (d.y == d.y) && (d.z == d.z);
             const bool same = __all_sync(FULL_MASK, !valid || (o.x == ox0 && o.y == oy0 && o.z == oz0 && fin));
             const float dgx = d.x * P.sgx, dgy = d.y * P.sgy;
+#if HF_BEAM_EXACT_BOUNDS
             float xl = valid ? dgx : HF_INF, xh = valid ? dgx : -HF_INF, yl = valid ? dgy : HF_INF, yh = valid ? dgy : -HF_INF;
             float zl = valid ? d.z : HF_INF, zh = valid ? d.z : -HF_INF;
             #pragma unroll
@@ -637,6 +666,16 @@ hf_intersect_beam_kernel(const __grid_constant__ HfParams P, const HfLaunchInfo 
                 yl = fminf(yl, __shfl_xor_sync(FULL_MASK, yl, sft)); yh = fmaxf(yh, __shfl_xor_sync(FULL_MASK, yh, sft));
                 zl = fminf(zl, __shfl_xor_sync(FULL_MASK, zl, sft)); zh = fmaxf(zh, __shfl_xor_sync(FULL_MASK, zh, sft));
             }
+#else
+            // centre (the first valid ray's direction) + radius: |delta| >= 0 orders like its bit pattern, so each radius is
+            // ONE integer warp reduction (REDUX) instead of ten shuffles; the box is at most twice the tight one per axis
+            const float cx = __shfl_sync(FULL_MASK, dgx, first), cy = __shfl_sync(FULL_MASK, dgy, first), cz = __shfl_sync(FULL_MASK, d.z, first);
+            const float ex_ = valid ? fmaxf(fabsf(dgx - cx), fabsf(dgy - cy)) : 0.f, ez_ = valid ? fabsf(d.z - cz) : 0.f;
+            float rxy = __uint_as_float(__reduce_max_sync(FULL_MASK, __float_as_uint(ex_)));
+            float rz = __uint_as_float(__reduce_max_sync(FULL_MASK, __float_as_uint(ez_)));
+            rxy = rxy * 1.0000005f + 1e-30f; rz = rz * 1.0000005f + 1e-30f;          // outward: the subtraction above rounded once
+            const float xl = cx - rxy, xh = cx + rxy, yl = cy - rxy, yh = cy + rxy, zl = cz - rz, zh = cz + rz;
+#endif
             if (lane == g) {
                 bundle = same && (__popc(vm) > 1);
                 B.ogx = (ox0 - P.x0) * P.sgx; B.ogy = (oy0 - P.y0) * P.sgy; B.oz = oz0;
@@ -649,7 +688,7 @@ hf_intersect_beam_kernel(const __grid_constant__ HfParams P, const HfLaunchInfo 
         if (bundle) t_enter = hf_beam_enter(G, B, L_start);
         __syncwarp();
         // ---- phase C: per-ray walks from the bundle entry
-        for (unsigned g = 0; g < 32u; ++g) {
+        for (unsigned g = 0; g < ng; ++g) {
             const float ts = __shfl_sync(FULL_MASK, t_enter, g);
             const int ls = __shfl_sync(FULL_MASK, L_start, g);
             const size_t i = base + (size_t) g * 32u + lane;
@@ -657,6 +696,18 @@ hf_intersect_beam_kernel(const __grid_constant__ HfParams P, const HfLaunchInfo 
             __syncwarp();
         }
     }
+}
+
+// L1 / shared-memory split: the walk kernels use a few KB of shared memory per CTA and live off L1 hits on pyramid nodes and
+// texels, so ask for the smallest shared carve-out that still fits the resident CTAs (HF_B200_CARVEOUT overrides, in percent).
+template <typename K>
+static void hf_prefer_l1(K kernel, size_t smem_per_cta, int ctas) {
+    int pct = (int) ((smem_per_cta + 2048) * (size_t) ctas * 100 / (228 * 1024)) + 1;
+    if (pct < 25) pct = 25;            // measured on C3: 25 % is the optimum, 10 % already costs resident CTAs (profiles/r01_notes.md)
+    if (const char *e = getenv("HF_B200_CARVEOUT")) pct = atoi(e);
+    if (pct < 0) return;
+    if (pct > 100) pct = 100;
+    cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
 }
 
 static inline int hf_grid_for(size_t n, int num_sms, int ctas_per_sm) {
@@ -667,7 +718,7 @@ static inline int hf_grid_for(size_t n, int num_sms, int ctas_per_sm) {
 
 cudaError_t hf_launch_intersect(const HfParams &P, const HfLaunchInfo &li, int mode, const hf_rays &rays,
                                 const hf_prelim &prelim, const hf_si &si, uint8_t *d_hit, uint32_t flags,
-                                size_t n, unsigned long long *d_counters, cudaStream_t s) {
+                                size_t n, unsigned long long *d_counters, unsigned long long *d_sched, cudaStream_t s) {
     if (n == 0) return cudaSuccess;
     const int grid = hf_grid_for(n, li.num_sms, 8);
     if (mode == HF_MODE_COUNTED) {
@@ -677,25 +728,43 @@ cudaError_t hf_launch_intersect(const HfParams &P, const HfLaunchInfo &li, int m
     }
     const size_t smem = (size_t) li.top_nodes * sizeof(float2);
     if (li.use_bundles && mode != HF_MODE_TEST) {
-        const size_t nwt = (n + HF_WARP_TILE - 1) / HF_WARP_TILE, nct = (nwt + HF_BLOCK / 32 - 1) / (HF_BLOCK / 32);
+        const unsigned long long ngroups = (n + 31) / 32;
+        const unsigned long long nbig = (ngroups - ngroups / 8) / 32;                 // the last eighth (at least) goes out in small tiles
+        const unsigned long long ntile = nbig + (ngroups - nbig * 32 + HF_SMALL_GROUPS - 1) / HF_SMALL_GROUPS;
+        const size_t nct = (size_t) ((ntile + HF_BLOCK / 32 - 1) / (HF_BLOCK / 32));
         const size_t cap = (size_t) li.num_sms * HF_MIN_CTAS;
         const int bgrid = (int) (nct < cap ? nct : cap);
-        unsigned long long *sched = d_counters + 4;
+        unsigned long long *sched = d_sched;
         cudaError_t e = cudaMemsetAsync(sched, 0, sizeof(unsigned long long), s);
         if (e != cudaSuccess) return e;
         if (mode == HF_MODE_PRELIM)
-            hf_intersect_beam_kernel<HF_MODE_PRELIM><<<bgrid, HF_BLOCK, smem, s>>>(P, li, rays, prelim, si, d_hit, flags, n, sched);
+            hf_intersect_beam_kernel<HF_MODE_PRELIM><<<bgrid, HF_BLOCK, smem, s>>>(P, li, rays, prelim, si, d_hit, flags, n, nbig, sched);
         else
-            hf_intersect_beam_kernel<HF_MODE_FUSED_SI><<<bgrid, HF_BLOCK, smem, s>>>(P, li, rays, prelim, si, d_hit, flags, n, sched);
+            hf_intersect_beam_kernel<HF_MODE_FUSED_SI><<<bgrid, HF_BLOCK, smem, s>>>(P, li, rays, prelim, si, d_hit, flags, n, nbig, sched);
         return cudaGetLastError();
     }
-    switch (mode) {
-        case HF_MODE_PRELIM:
-            hf_intersect_fast_kernel<HF_MODE_PRELIM><<<grid, HF_BLOCK, smem, s>>>(P, li, rays, prelim, si, d_hit, flags, n); break;
-        case HF_MODE_FUSED_SI:
-            hf_intersect_fast_kernel<HF_MODE_FUSED_SI><<<grid, HF_BLOCK, smem, s>>>(P, li, rays, prelim, si, d_hit, flags, n); break;
-        default:
-            hf_intersect_fast_kernel<HF_MODE_TEST><<<grid, HF_BLOCK, smem, s>>>(P, li, rays, prelim, si, d_hit, flags, n); break;
+    static bool carved = false;
+    if (!carved) {
+        carved = true;
+        hf_prefer_l1(hf_intersect_fast_kernel<HF_MODE_PRELIM>, smem + 1024, HF_MIN_CTAS);
+        hf_prefer_l1(hf_intersect_fast_kernel<HF_MODE_FUSED_SI>, smem + 1024, HF_MIN_CTAS);
+        hf_prefer_l1(hf_intersect_fast_kernel<HF_MODE_TEST>, smem + 1024, HF_MIN_CTAS);
+    }
+    {
+        const size_t nwt = ((n + 31) / 32 + HF_FAST_GROUPS - 1) / HF_FAST_GROUPS, nct = (nwt + HF_BLOCK / 32 - 1) / (HF_BLOCK / 32);
+        const size_t cap = (size_t) li.num_sms * HF_MIN_CTAS;
+        const int fgrid = (int) (nct < cap ? nct : cap);
+        unsigned long long *sched = d_sched;
+        cudaError_t e = cudaMemsetAsync(sched, 0, sizeof(unsigned long long), s);
+        if (e != cudaSuccess) return e;
+        switch (mode) {
+            case HF_MODE_PRELIM:
+                hf_intersect_fast_kernel<HF_MODE_PRELIM><<<fgrid, HF_BLOCK, smem, s>>>(P, li, rays, prelim, si, d_hit, flags, n, sched); break;
+            case HF_MODE_FUSED_SI:
+                hf_intersect_fast_kernel<HF_MODE_FUSED_SI><<<fgrid, HF_BLOCK, smem, s>>>(P, li, rays, prelim, si, d_hit, flags, n, sched); break;
+            default:
+                hf_intersect_fast_kernel<HF_MODE_TEST><<<fgrid, HF_BLOCK, smem, s>>>(P, li, rays, prelim, si, d_hit, flags, n, sched); break;
+        }
     }
     return cudaGetLastError();
 }

@@ -20,7 +20,7 @@ enum HfIntersectMode { HF_MODE_PRELIM = 0, HF_MODE_FUSED_SI = 1, HF_MODE_TEST = 
 cudaError_t hf_launch_pyramid(const HfParams &P, float2 *pyr, uint32_t *qpyr, cudaStream_t s);
 cudaError_t hf_launch_intersect(const HfParams &P, const HfLaunchInfo &li, int mode, const hf_rays &rays,
                                 const hf_prelim &prelim, const hf_si &si, uint8_t *d_hit, uint32_t flags,
-                                size_t n, unsigned long long *d_counters, cudaStream_t s);
+                                size_t n, unsigned long long *d_counters, unsigned long long *d_sched, cudaStream_t s);
 cudaError_t hf_launch_surface_interaction(const HfParams &P, const HfLaunchInfo &li, const hf_rays &rays,
                                           const hf_prelim &pi, uint32_t flags, const hf_si &si, size_t n,
                                           cudaStream_t s);

@@ -18,10 +18,10 @@ for r in rows:
         pass
 def region(f, l):
     if f.startswith("hf_traverse"):
-        if 178 <= l <= 256: return "walk loop"
-        if 86 <= l <= 104: return "walk int helpers"
-        if 106 <= l <= 168: return "walk init"
-        if l >= 280: return "beam march"
+        if 213 <= l <= 310: return "walk loop"
+        if 108 <= l <= 128: return "walk int helpers"
+        if 129 <= l <= 212: return "walk init"
+        if l >= 320: return "beam march"
     if f.startswith("hf_device"):
         if 100 <= l <= 156: return "cell_intersect/MT"
         return "hf_device other (vec, xform, rcp, rsqrt, vtx)"
