@@ -10,6 +10,7 @@
 //
 // Compiled with -fmad=false: see hf_device.cuh.
 #include <stdlib.h>
+#include <algorithm>
 #include "hf_kernels.h"
 #include "hf_walk_common.cuh"
 
@@ -564,6 +565,14 @@ __device__ __forceinline__ void hf_process_ray(const HfParams &P, const HfGrid &
 #ifndef HF_MIN_CTAS
 #define HF_MIN_CTAS 4
 #endif
+#ifdef HF_DEBUG_TIMING            // dev builds only (make VARIANT=_dbg EXTRA=-DHF_DEBUG_TIMING): per-warp timeline of the fast kernel
+__device__ unsigned long long hf_dbg[8192 * 6];
+extern "C" int hf_debug_read(unsigned long long *dst) { return (int) cudaMemcpyFromSymbol(dst, hf_dbg, sizeof(hf_dbg)); }
+__device__ __forceinline__ unsigned long long hf_gtime() { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
+#endif
+#ifndef HF_FAST_TAIL
+#define HF_FAST_TAIL 48
+#endif
 #ifndef HF_FAST_GROUPS
 #define HF_FAST_GROUPS 4           // 32-ray groups a warp takes off the global counter at a time
 #endif
@@ -573,19 +582,38 @@ template <int MODE>
 __global__ void __launch_bounds__(HF_BLOCK, HF_MIN_CTAS)
 hf_intersect_fast_kernel(const __grid_constant__ HfParams P, const HfLaunchInfo li, const hf_rays R, const hf_prelim O,
                          const hf_si S, uint8_t *__restrict__ hit_out, const uint32_t flags, const size_t n,
-                         unsigned long long *__restrict__ sched) {
+                         const unsigned long long nbig, unsigned long long *__restrict__ sched) {
     HfGrid G;
     hf_stage_pyramid(P, li, G);
 
     const unsigned lane = threadIdx.x & 31u;
     const unsigned long long ngroups = (n + 31) / 32;
+#ifdef HF_DEBUG_TIMING
+    const unsigned long long dbg_t0 = hf_gtime();
+    unsigned long long dbg_max = 0, dbg_arg = 0, dbg_n = 0, dbg_last = dbg_t0, dbg_prev_t = 0;
+#endif
     for (;;) {
-        unsigned long long g0 = 0;
-        if (lane == 0) g0 = atomicAdd(sched, (unsigned long long) HF_FAST_GROUPS);
-        g0 = __shfl_sync(FULL_MASK, g0, 0);
+        unsigned long long t = 0;
+        if (lane == 0) t = atomicAdd(sched, 1ull);
+        t = __shfl_sync(FULL_MASK, t, 0);
+#ifdef HF_DEBUG_TIMING
+        {
+            const unsigned long long now = hf_gtime();
+            if (dbg_n > 0 && now - dbg_last > dbg_max) { dbg_max = now - dbg_last; dbg_arg = dbg_prev_t; }
+            dbg_last = now; ++dbg_n; dbg_prev_t = t;
+            if (lane == 0) {
+                unsigned long long *d = hf_dbg + ((size_t) blockIdx.x * (HF_BLOCK / 32) + (threadIdx.x >> 5)) * 6;
+                d[0] = dbg_t0; d[1] = now; d[2] = dbg_n; d[3] = dbg_max; d[4] = dbg_arg; d[5] = t;
+            }
+        }
+#endif
+        // the first nbig fetches are HF_FAST_GROUPS groups wide (a warp that stays on neighbouring rays re-uses its L1 lines); the
+        // closing fetches are single groups, so that the warps finish within ~20 us of each other whatever the batch size
+        const unsigned long long g0 = t < nbig ? t * HF_FAST_GROUPS : nbig * HF_FAST_GROUPS + (t - nbig);
+        const unsigned ng = t < nbig ? (unsigned) HF_FAST_GROUPS : 1u;
         if (g0 >= ngroups) break;
         #pragma unroll 1
-        for (unsigned g = 0; g < HF_FAST_GROUPS; ++g) {
+        for (unsigned g = 0; g < ng; ++g) {
             const size_t i = (size_t) (g0 + g) * 32u + lane;
             if (i < n) hf_process_ray<MODE>(P, G, R, O, S, hit_out, flags, i, 0.f, HF_START_LEVEL);
             __syncwarp();
@@ -751,19 +779,25 @@ cudaError_t hf_launch_intersect(const HfParams &P, const HfLaunchInfo &li, int m
         hf_prefer_l1(hf_intersect_fast_kernel<HF_MODE_TEST>, smem + 1024, HF_MIN_CTAS);
     }
     {
-        const size_t nwt = ((n + 31) / 32 + HF_FAST_GROUPS - 1) / HF_FAST_GROUPS, nct = (nwt + HF_BLOCK / 32 - 1) / (HF_BLOCK / 32);
+        const size_t ngroups = (n + 31) / 32;
+        const size_t nwt = (ngroups + HF_FAST_GROUPS - 1) / HF_FAST_GROUPS, nct = (nwt + HF_BLOCK / 32 - 1) / (HF_BLOCK / 32);
         const size_t cap = (size_t) li.num_sms * HF_MIN_CTAS;
         const int fgrid = (int) (nct < cap ? nct : cap);
+        // closing phase: the last HF_FAST_TAIL groups per resident warp go out one at a time. A group whose rays skim down a slope
+        // (tens of candidate cells per ray) keeps its warp for ~100 us, four of them in one fetch for ~0.5 ms (profiles/r01_notes.md):
+        // the single-group phase has to last longer than that, i.e. ~48 groups of ~12 us per warp
+        const size_t tail = std::min(ngroups, (size_t) fgrid * (HF_BLOCK / 32) * HF_FAST_TAIL);
+        const unsigned long long nbig = (ngroups - tail) / HF_FAST_GROUPS;
         unsigned long long *sched = d_sched;
         cudaError_t e = cudaMemsetAsync(sched, 0, sizeof(unsigned long long), s);
         if (e != cudaSuccess) return e;
         switch (mode) {
             case HF_MODE_PRELIM:
-                hf_intersect_fast_kernel<HF_MODE_PRELIM><<<fgrid, HF_BLOCK, smem, s>>>(P, li, rays, prelim, si, d_hit, flags, n, sched); break;
+                hf_intersect_fast_kernel<HF_MODE_PRELIM><<<fgrid, HF_BLOCK, smem, s>>>(P, li, rays, prelim, si, d_hit, flags, n, nbig, sched); break;
             case HF_MODE_FUSED_SI:
-                hf_intersect_fast_kernel<HF_MODE_FUSED_SI><<<fgrid, HF_BLOCK, smem, s>>>(P, li, rays, prelim, si, d_hit, flags, n, sched); break;
+                hf_intersect_fast_kernel<HF_MODE_FUSED_SI><<<fgrid, HF_BLOCK, smem, s>>>(P, li, rays, prelim, si, d_hit, flags, n, nbig, sched); break;
             default:
-                hf_intersect_fast_kernel<HF_MODE_TEST><<<fgrid, HF_BLOCK, smem, s>>>(P, li, rays, prelim, si, d_hit, flags, n, sched); break;
+                hf_intersect_fast_kernel<HF_MODE_TEST><<<fgrid, HF_BLOCK, smem, s>>>(P, li, rays, prelim, si, d_hit, flags, n, nbig, sched); break;
         }
     }
     return cudaGetLastError();

@@ -25,6 +25,29 @@
 #define HF_RENDER_TILE 4               // listed pixels per warp tile: small tiles keep the tail of the dynamic schedule short;
 #endif                                 // only HF_RENDER_TILE lanes march bundles in phase B (1 % of the instructions)
 
+#ifndef HF_RENDER_TAIL
+#define HF_RENDER_TAIL 24              // pixels per resident warp that go out one at a time at the end (a pixel whose rays skim down a slope takes ~0.2 ms)
+#endif
+#define HF_SUB (32 / HF_RENDER_TILE)    // bundles marched per pixel in hf_render_kernel: a HF_SUB_X x HF_SUB_Y split of the jitter square
+#if HF_RENDER_TILE == 4
+#define HF_SUB_X 4
+#define HF_SUB_Y 2
+#elif HF_RENDER_TILE == 8
+#define HF_SUB_X 2
+#define HF_SUB_Y 2
+#elif HF_RENDER_TILE == 2
+#define HF_SUB_X 4
+#define HF_SUB_Y 4
+#elif HF_RENDER_TILE == 16
+#define HF_SUB_X 2
+#define HF_SUB_Y 1
+#elif HF_RENDER_TILE == 32
+#define HF_SUB_X 1
+#define HF_SUB_Y 1
+#else
+#error "HF_RENDER_TILE must be 2, 4, 8, 16 or 32"
+#endif
+
 struct HfRenderArgs {
     hf_camera cam;
     float lx, ly, lz;                  // unit vector towards the emitter, world space
@@ -60,16 +83,23 @@ __device__ __forceinline__ f3 hf_film_dir(const HfRenderArgs &A, float fx, float
 }
 
 // perspective.cpp:212-231 for a pinhole without clipping planes: o = camera position, d = normalised direction
-__device__ __forceinline__ f3 hf_camera_dir(const HfRenderArgs &A, uint32_t pid, uint32_t s) {
-    const uint32_t x = pid % A.cam.width, y = pid / A.cam.width;
-    float jx = 0.5f, jy = 0.5f;
+__device__ __forceinline__ void hf_camera_jitter(const HfRenderArgs &A, uint32_t pid, uint32_t s, float &jx, float &jy) {
+    jx = 0.5f; jy = 0.5f;
     if (A.cam.spp > 1) {
         const unsigned long long k = (unsigned long long) pid * A.cam.spp + s;
         const uint32_t key = (uint32_t) k ^ ((uint32_t) (k >> 32) * 0x85EBCA6Bu);
         jx = hf_hash_uniform(A.cam.seed, key, 0); jy = hf_hash_uniform(A.cam.seed, key, 1);
     }
+}
+__device__ __forceinline__ f3 hf_camera_dir_at(const HfRenderArgs &A, uint32_t pid, float jx, float jy) {
+    const uint32_t x = pid % A.cam.width, y = pid / A.cam.width;
     const float fx = ((float) x + jx) * A.inv_w, fy = ((float) y + jy) * A.inv_h;
     return normalize3(hf_film_dir(A, fx, fy));
+}
+__device__ __forceinline__ f3 hf_camera_dir(const HfRenderArgs &A, uint32_t pid, uint32_t s) {
+    float jx, jy;
+    hf_camera_jitter(A, pid, s, jx, jy);
+    return hf_camera_dir_at(A, pid, jx, jy);
 }
 
 // ---- one sample: trace, shade -------------------------------------------------------------------------------------
@@ -274,11 +304,13 @@ __device__ __forceinline__ float hf_path_sample(const HfParams &P, const HfGrid 
 // themselves use d = v / |v|: at parameter t they stand at s = t / |v|, so with |v| >= vmin over the pixel
 // (|v|^2 = 1 + sx^2 + sy^2 for an orthonormal frame) every ray is still inside the marched region at t = s_enter * vmin.
 // hf_api.cu rejects frames that are not orthonormal to 1e-4; the caller backs the result off by 2e-4 for that.
-__device__ __forceinline__ HfBeam hf_pixel_bundle(const HfParams &P, const HfRenderArgs &A, uint32_t pid, float &vmin) {
+// (a0, a1) x (b0, b1): the part of the pixel's jitter square the bundle covers (the whole square by default).
+__device__ __forceinline__ HfBeam hf_pixel_bundle(const HfParams &P, const HfRenderArgs &A, uint32_t pid, float &vmin,
+                                                  float a0 = 0.f, float a1 = 1.f, float b0 = 0.f, float b1 = 1.f) {
     const uint32_t x = pid % A.cam.width, y = pid / A.cam.width;
-    const float e = 1e-3f;                                   // 1/1000 pixel of slack around the jitter square
-    const float fx0 = ((float) x - e) * A.inv_w, fx1 = ((float) (x + 1) + e) * A.inv_w;
-    const float fy0 = ((float) y - e) * A.inv_h, fy1 = ((float) (y + 1) + e) * A.inv_h;
+    const float e = 1e-3f;                                   // 1/1000 pixel of slack around the jitter rectangle
+    const float fx0 = ((float) x + (a0 - e)) * A.inv_w, fx1 = ((float) x + (a1 + e)) * A.inv_w;
+    const float fy0 = ((float) y + (b0 - e)) * A.inv_h, fy1 = ((float) y + (b1 + e)) * A.inv_h;
     {   // smallest |v| over the pixel
         const float sxa = fmaf(2.f, fx0, -1.f) * A.tan_x, sxb = fmaf(2.f, fx1, -1.f) * A.tan_x;
         const float sya = fmaf(-2.f, fy0, 1.f) * A.tan_y, syb = fmaf(-2.f, fy1, 1.f) * A.tan_y;
@@ -316,44 +348,57 @@ hf_render_kernel(const __grid_constant__ HfParams P, const HfLaunchInfo li, cons
     const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
     const uint32_t spp = A.cam.spp;
     const uint32_t rounds = (spp + 31u) >> 5;
-    const size_t ntiles = (A.npix + HF_RENDER_TILE - 1) / HF_RENDER_TILE;
+    // closing phase of the schedule: the last HF_RENDER_TAIL pixels per resident warp go out one at a time, so that the warps
+    // finish within one pixel of each other whatever the size of the pixel list
+    const size_t tailpx = min(A.npix, (size_t) gridDim.x * (HF_BLOCK / 32) * HF_RENDER_TAIL);
+    const size_t nbig = (A.npix - tailpx) / HF_RENDER_TILE, rest0 = nbig * HF_RENDER_TILE;
     double loss_acc = 0.0;
 
     for (;;) {
         unsigned long long tile = 0;
         if (lane == 0) tile = atomicAdd(sched, 1ull);
         tile = __shfl_sync(FULL_MASK, tile, 0);
-        if (tile >= ntiles) break;
-        // ---- phase B: lane j marches the bundle of listed pixel 32 * tile + j
-        const size_t kq = (size_t) tile * HF_RENDER_TILE + lane;
-        const bool have = lane < HF_RENDER_TILE && kq < A.npix;
+        const size_t k0 = tile < nbig ? (size_t) tile * HF_RENDER_TILE : rest0 + (size_t) (tile - nbig);
+        const unsigned cap = tile < nbig ? (unsigned) HF_RENDER_TILE : 1u;
+        if (k0 >= A.npix) break;
+        // ---- phase B: all 32 lanes march: lane = pixel * HF_SUB + sub-rectangle of the pixel's jitter square (HF_SUB_X x HF_SUB_Y).
+        // A narrower bundle is marched further down the pyramid, so its samples start their own walks closer to the surface.
+        const size_t kq = k0 + lane / HF_SUB;
+        const bool have = lane / HF_SUB < cap && kq < A.npix;
         const uint32_t my_pid = have ? (A.pixels ? __ldg(A.pixels + kq) : (uint32_t) kq) : 0u;
         float t_enter = 0.f;
         int L_start = HF_START_LEVEL;
         if (have) {
+            const unsigned sub = lane % HF_SUB, sbx = sub % HF_SUB_X, sby = sub / HF_SUB_X;
             float vmin;
-            const HfBeam B = hf_pixel_bundle(P, A, my_pid, vmin);
+            const HfBeam B = hf_pixel_bundle(P, A, my_pid, vmin, (float) sbx * (1.f / HF_SUB_X), (float) (sbx + 1) * (1.f / HF_SUB_X),
+                                             (float) sby * (1.f / HF_SUB_Y), (float) (sby + 1) * (1.f / HF_SUB_Y));
             t_enter = hf_beam_enter(G, B, L_start);
             if (t_enter < HF_BEAM_ALL_MISS) t_enter = t_enter * vmin * (1.f - 2e-4f);
         }
         __syncwarp();
         // ---- phase C: pixel by pixel
-        const unsigned npx = (unsigned) min((size_t) HF_RENDER_TILE, A.npix - (size_t) tile * HF_RENDER_TILE);
+        const unsigned npx = (unsigned) min((size_t) cap, A.npix - k0);
         for (unsigned j = 0; j < npx; ++j) {
-            const uint32_t pid = __shfl_sync(FULL_MASK, my_pid, j);
-            const float ts = __shfl_sync(FULL_MASK, t_enter, j);
-            const int ls = __shfl_sync(FULL_MASK, L_start, j);
+            const uint32_t pid = __shfl_sync(FULL_MASK, my_pid, j * HF_SUB);
             float acc = 0.f;
             for (uint32_t r = 0; r < rounds; ++r) {
                 const uint32_t s = r * 32u + lane;
                 uint32_t prim = HF_NO_PRIM;
                 float v = 0.f;
+                float jx, jy;
+                hf_camera_jitter(A, pid, s < spp ? s : 0u, jx, jy);
+                // the sub-rectangle this sample's jitter falls into (jx, jy in [0, 1): the products are exact)
+                const unsigned src = j * HF_SUB + min((unsigned) (jy * (float) HF_SUB_Y), (unsigned) HF_SUB_Y - 1u) * HF_SUB_X
+                                     + min((unsigned) (jx * (float) HF_SUB_X), (unsigned) HF_SUB_X - 1u);
+                const float ts = __shfl_sync(FULL_MASK, t_enter, src);
+                const int ls = __shfl_sync(FULL_MASK, L_start, src);
                 const unsigned conv = __ballot_sync(FULL_MASK, s < spp);
-                if (s < spp) v = hf_shade_sample(P, G, A, hf_camera_dir(A, pid, s), ts, ls, prim, conv);
+                if (s < spp) v = hf_shade_sample(P, G, A, hf_camera_dir_at(A, pid, jx, jy), ts, ls, prim, conv);
                 acc += v;
                 s_prim[warp][(r * 32u + lane) & (HF_RENDER_MAX_SPP - 1)] = prim;
                 if (MODE == HF_RENDER_FWD && prim_out && s < spp)
-                    __stcs(prim_out + ((size_t) tile * HF_RENDER_TILE + j) * spp + s, prim);
+                    __stcs(prim_out + (k0 + j) * spp + s, prim);
             }
             // pixel mean: lane partials in sample order, then a butterfly -- the same order on every run
             #pragma unroll
