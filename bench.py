@@ -299,6 +299,7 @@ def main_ours(a):
 
     full_step()
     ms_full = timed(full_step, a.steps) / a.steps
+    ms_allreduce = timed(shape.allreduce_grad, 10) / 10 if world > 1 else 0.0     # the collective alone (64 MiB fp32 at C3)
     params["heights"] = h           # restore the field for the legs below
     params.update()
 
@@ -356,6 +357,7 @@ def main_ours(a):
         "extras": {"intersect_only_mrays": n_total / (ms_isect * 1e-3) / 1e6, "intersect_only_ms": ms_isect,
                    "full_step_mrays": n_total / (ms_full * 1e-3) / 1e6, "full_step_ms": ms_full,
                    "full_step": "zero_grad + intersect/SI + backward + allreduce + Adam + pyramid rebuild",
+                   "allreduce_ms": ms_allreduce,
                    "grad_abs_sum": grad_checksum, "mean_nodes_per_ray": n_node, "mean_leaves_per_ray": n_leaf},
     }
     # SURVEY.md 8(d) "full step" byte model: rays x (B_trav + 16 + 12) + texels x (4 + 28 + 4 + 8/3) + pixels x 36

@@ -168,6 +168,8 @@ int hf_adam_reset(hf_ctx *ctx, void *stream);
 
 /* one NCCL communicator per context; the unique id is created on rank 0 and shipped by the caller */
 int hf_comm_unique_id(uint8_t out_id[128]);
+/* With nranks > 1 hf_comm_init moves the gradient grid into NCCL-allocated, communicator-registered memory (in-switch reduction on
+   NVSwitch boxes): the pointer hf_grad() returns changes, fetch it again. HF_B200_NCCL_MEM=0 keeps the original buffer. */
 int hf_comm_init(hf_ctx *ctx, int rank, int nranks, const uint8_t id[128]);
 int hf_comm_destroy(hf_ctx *ctx);
 int hf_allreduce_grad(hf_ctx *ctx, void *stream);                  /* ncclAllReduce(grad, fp32, sum) */

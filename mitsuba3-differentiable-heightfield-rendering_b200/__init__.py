@@ -518,6 +518,10 @@ class Heightfield:
         buf = (C.c_uint8 * 128).from_buffer_copy(unique_id)
         with torch.cuda.device(self.device):
             _check(_load().hf_comm_init(self._ctx, rank, world_size, buf))
+            # hf_comm_init may move the gradient grid into NCCL-registered memory: wrap the pointer again
+            gp = C.c_void_p()
+            _check(_load().hf_grad(self._ctx, C.byref(gp)))
+            self.grad = torch.as_tensor(_DevView(gp.value, (self.H, self.W), self), device=self.device)
 
     def allreduce_grad(self):
         with torch.cuda.device(self.device):

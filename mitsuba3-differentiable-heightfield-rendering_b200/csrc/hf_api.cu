@@ -56,6 +56,11 @@ struct NcclApi {
     int (*CommDestroy)(hf_nccl_comm) = nullptr;
     int (*AllReduce)(const void *, void *, size_t, int, int, hf_nccl_comm, cudaStream_t) = nullptr;
     const char *(*GetErrorString)(int) = nullptr;
+    // optional (NCCL >= 2.19): buffers the switch can reduce in place (NVLS) need ncclMemAlloc + ncclCommRegister
+    int (*MemAlloc)(void **, size_t) = nullptr;
+    int (*MemFree)(void *) = nullptr;
+    int (*CommRegister)(hf_nccl_comm, void *, size_t, void **) = nullptr;
+    int (*CommDeregister)(hf_nccl_comm, void *) = nullptr;
 };
 static NcclApi g_nccl;
 
@@ -72,6 +77,10 @@ static int nccl_load() {
     a.CommDestroy = (int (*)(hf_nccl_comm)) dlsym(h, "ncclCommDestroy");
     a.AllReduce = (int (*)(const void *, void *, size_t, int, int, hf_nccl_comm, cudaStream_t)) dlsym(h, "ncclAllReduce");
     a.GetErrorString = (const char *(*) (int) ) dlsym(h, "ncclGetErrorString");
+    a.MemAlloc = (int (*)(void **, size_t)) dlsym(h, "ncclMemAlloc");
+    a.MemFree = (int (*)(void *)) dlsym(h, "ncclMemFree");
+    a.CommRegister = (int (*)(hf_nccl_comm, void *, size_t, void **)) dlsym(h, "ncclCommRegister");
+    a.CommDeregister = (int (*)(hf_nccl_comm, void *)) dlsym(h, "ncclCommDeregister");
     if (!a.GetUniqueId || !a.CommInitRank || !a.CommDestroy || !a.AllReduce || !a.GetErrorString)
         return fail(HF_ERR_NCCL, "libnccl is missing a required symbol");
     g_nccl = a;
@@ -105,6 +114,8 @@ struct hf_ctx {
     HfLaunchInfo li;
     size_t pyr_nodes = 0;
     float *d_heights = nullptr, *d_grad = nullptr, *d_m = nullptr, *d_v = nullptr;
+    bool grad_nccl = false;           // d_grad comes from ncclMemAlloc (hf_comm_init moved it there)
+    void *grad_reg = nullptr;         // ncclCommRegister handle of d_grad
     float2 *d_pyr = nullptr;
     uint32_t *d_qpyr = nullptr;      // quantised pyramid (hf_qpyr.h)
     size_t qpyr_nodes = 0;
@@ -247,7 +258,9 @@ extern "C" int hf_create(hf_ctx **out, const hf_desc *desc) {
 extern "C" int hf_destroy(hf_ctx *c) {
     if (!c) return HF_OK;
     cudaSetDevice(c->device);
+    if (c->comm && c->grad_reg && g_nccl.CommDeregister) g_nccl.CommDeregister(c->comm, c->grad_reg);
     if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
+    if (c->grad_nccl && g_nccl.MemFree) { g_nccl.MemFree(c->d_grad); c->d_grad = nullptr; }
     for (auto &s : c->slots) { if (s.slab) cudaFree(s.slab); if (s.stream) cudaStreamDestroy(s.stream); }
     cudaFree(c->d_heights); cudaFree(c->d_grad); cudaFree(c->d_m); cudaFree(c->d_v); cudaFree(c->d_pyr); cudaFree(c->d_qpyr); cudaFree(c->d_counters); cudaFree(c->d_scratch);
     delete c;
@@ -548,11 +561,31 @@ extern "C" int hf_comm_init(hf_ctx *c, int rank, int nranks, const uint8_t id_by
     int rc = nccl_load();
     if (rc) return rc;
     CU(cudaSetDevice(c->device));
-    if (c->comm) { g_nccl.CommDestroy(c->comm); c->comm = nullptr; }
+    if (c->comm) {
+        if (c->grad_reg && g_nccl.CommDeregister) g_nccl.CommDeregister(c->comm, c->grad_reg);
+        c->grad_reg = nullptr;
+        g_nccl.CommDestroy(c->comm); c->comm = nullptr;
+    }
     hf_nccl_uid id;
     memcpy(id.internal, id_bytes, 128);
     NC(g_nccl.CommInitRank(&c->comm, nranks, id, rank));
     c->nranks = nranks;
+    // The gradient grid is the one buffer that crosses NVLink every step. Move it into NCCL-allocated memory and register it with the
+    // communicator, so that on an NVSwitch box the allreduce can run in the switch on the user buffer (NVLS) instead of being staged
+    // through NCCL's own buffers. The pointer hf_grad() returns CHANGES here. HF_B200_NCCL_MEM=0 keeps the cudaMalloc buffer.
+    const char *e = getenv("HF_B200_NCCL_MEM");
+    if (nranks > 1 && !(e && e[0] == '0') && g_nccl.MemAlloc && g_nccl.MemFree && g_nccl.CommRegister) {
+        const size_t bytes = (size_t) c->W * c->H * sizeof(float);
+        if (!c->grad_nccl) {
+            void *nb = nullptr;
+            if (g_nccl.MemAlloc(&nb, bytes) == 0 && nb) {
+                CU(cudaMemcpy(nb, c->d_grad, bytes, cudaMemcpyDeviceToDevice));
+                cudaFree(c->d_grad);
+                c->d_grad = (float *) nb; c->grad_nccl = true;
+            } else cudaGetLastError();
+        }
+        if (c->grad_nccl && g_nccl.CommRegister(c->comm, c->d_grad, bytes, &c->grad_reg) != 0) c->grad_reg = nullptr;
+    }
     return HF_OK;
 }
 

@@ -108,12 +108,13 @@ __global__ void __launch_bounds__(1024) hf_pyramid_top_kernel(const __grid_const
 __device__ __forceinline__ int hf_qpitch(const HfParams &P, int l) { int p = (P.xmask + 1) >> l; return p > 0 ? p : 1; }
 __device__ __forceinline__ int hf_qrows(const HfParams &P, int l) { int p = (P.ymask + 1) >> l; return p > 0 ? p : 1; }
 
-// levels 0, 1, 2: one thread per 4 x 4 block of cells
+#define HF_QBASE_TOP 6             // the base kernel writes levels 0..6
+// levels 0, 1, 2: one thread per 4 x 4 block of cells; levels 3..6: reduced inside the CTA
 __global__ void __launch_bounds__(256) hf_qpyramid_base_kernel(const __grid_constant__ HfParams P, uint32_t *__restrict__ qpyr) {
     const int Mx = P.xmask + 1, My = P.ymask + 1;
     const int bx = blockIdx.x * 16 + (threadIdx.x & 15), by = blockIdx.y * 16 + (threadIdx.x >> 4);
     const int x0 = bx * 4, y0 = by * 4;
-    if (x0 >= Mx || y0 >= My) return;
+    __shared__ uint32_t s_q[256 + 64 + 16 + 4 + 1];
     const float2 top = P.pyr[P.lvl_off[P.Ltop]];
     const HfQuant Q = hf_quant_make(top.x, top.y);
     uint32_t l1[4] = { HF_Q_EMPTY, HF_Q_EMPTY, HF_Q_EMPTY, HF_Q_EMPTY };
@@ -133,7 +134,7 @@ __global__ void __launch_bounds__(256) hf_qpyramid_base_kernel(const __grid_cons
             row[i] = q;
             l1[(j >> 1) * 2 + (i >> 1)] = hf_quant_merge(l1[(j >> 1) * 2 + (i >> 1)], q);
         }
-        if (y < My) {
+        if (y < My && x0 < Mx) {
             uint32_t *dst = qpyr + P.qoff[0] + (size_t) y * Mx + x0;
             if (x0 + 3 < Mx) *reinterpret_cast<uint4 *>(dst) = make_uint4(row[0], row[1], row[2], row[3]);   // Mx % 4 == 0 here
             else { for (int i = 0; i < 4; ++i) if (x0 + i < Mx) dst[i] = row[i]; }
@@ -147,23 +148,45 @@ __global__ void __launch_bounds__(256) hf_qpyramid_base_kernel(const __grid_cons
             if (nx < p1 && ny < r1) qpyr[P.qoff[1] + (size_t) ny * p1 + nx] = l1[k];
         }
     }
+    const uint32_t l2 = hf_quant_merge(hf_quant_merge(l1[0], l1[1]), hf_quant_merge(l1[2], l1[3]));
     if (P.QLtop >= 2) {
         const int p2 = hf_qpitch(P, 2), r2 = hf_qrows(P, 2);
-        if (bx < p2 && by < r2) qpyr[P.qoff[2] + (size_t) by * p2 + bx] = hf_quant_merge(hf_quant_merge(l1[0], l1[1]), hf_quant_merge(l1[2], l1[3]));
+        if (bx < p2 && by < r2) qpyr[P.qoff[2] + (size_t) by * p2 + bx] = l2;
+    }
+    // levels 3..6 of this CTA's 64 x 64 cells through shared memory (16 x 16 level-2 nodes -> 8 x 8 -> 4 x 4 -> 2 x 2 -> 1)
+    s_q[threadIdx.x] = l2;
+    __syncthreads();
+    int src = 0, sdim = 16;
+    #pragma unroll
+    for (int l = 3; l <= HF_QBASE_TOP; ++l) {
+        const int dim = sdim >> 1, dst = src + sdim * sdim;
+        if ((int) threadIdx.x < dim * dim) {
+            const int ly = threadIdx.x / dim, lx = threadIdx.x - ly * dim;
+            const uint32_t q = hf_quant_merge(hf_quant_merge(s_q[src + (2 * ly) * sdim + 2 * lx], s_q[src + (2 * ly) * sdim + 2 * lx + 1]),
+                                              hf_quant_merge(s_q[src + (2 * ly + 1) * sdim + 2 * lx], s_q[src + (2 * ly + 1) * sdim + 2 * lx + 1]));
+            s_q[dst + threadIdx.x] = q;
+            const int nx = blockIdx.x * dim + lx, ny = blockIdx.y * dim + ly;
+            if (l <= P.QLtop && nx < hf_qpitch(P, l) && ny < hf_qrows(P, l)) qpyr[P.qoff[l] + (size_t) ny * hf_qpitch(P, l) + nx] = q;
+        }
+        __syncthreads();
+        src = dst; sdim = dim;
     }
 }
 
-// level l >= 3 from level l - 1 (small: <= 1/64 of the cells)
-__global__ void __launch_bounds__(256) hf_qpyramid_level_kernel(const __grid_constant__ HfParams P, uint32_t *__restrict__ qpyr, const int l) {
-    const int pw = hf_qpitch(P, l), ph = hf_qrows(P, l), cw = hf_qpitch(P, l - 1), ch = hf_qrows(P, l - 1);
-    const int fx = cw / pw, fy = ch / ph;                    // 2, or 1 once the axis is down to one node
-    const uint32_t *src = qpyr + P.qoff[l - 1];
-    for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < pw * ph; idx += gridDim.x * blockDim.x) {
-        const int ny = idx / pw, nx = idx - ny * pw;
-        uint32_t q = HF_Q_EMPTY;
-        for (int dj = 0; dj < fy; ++dj)
-            for (int di = 0; di < fx; ++di) q = hf_quant_merge(q, src[(size_t) (ny * fy + dj) * cw + (nx * fx + di)]);
-        qpyr[P.qoff[l] + idx] = q;
+// levels HF_QBASE_TOP + 1 .. QLtop: one CTA walks up through global memory (level 7 of a 16384^2 field has 128 x 128 nodes)
+__global__ void __launch_bounds__(1024) hf_qpyramid_top_kernel(const __grid_constant__ HfParams P, uint32_t *__restrict__ qpyr) {
+    for (int l = HF_QBASE_TOP + 1; l <= P.QLtop; ++l) {
+        const int pw = hf_qpitch(P, l), ph = hf_qrows(P, l), cw = hf_qpitch(P, l - 1), ch = hf_qrows(P, l - 1);
+        const int fx = cw / pw, fy = ch / ph;                    // 2, or 1 once the axis is down to one node
+        const uint32_t *src = qpyr + P.qoff[l - 1];
+        for (int idx = threadIdx.x; idx < pw * ph; idx += blockDim.x) {
+            const int ny = idx / pw, nx = idx - ny * pw;
+            uint32_t q = HF_Q_EMPTY;
+            for (int dj = 0; dj < fy; ++dj)
+                for (int di = 0; di < fx; ++di) q = hf_quant_merge(q, src[(size_t) (ny * fy + dj) * cw + (nx * fx + di)]);
+            qpyr[P.qoff[l] + idx] = q;
+        }
+        __syncthreads();
     }
 }
 
@@ -174,11 +197,7 @@ cudaError_t hf_launch_pyramid(const HfParams &P, float2 *pyr, uint32_t *qpyr, cu
     const int Mx = P.xmask + 1, My = P.ymask + 1;
     dim3 qgrid((Mx + 63) / 64, (My + 63) / 64);
     hf_qpyramid_base_kernel<<<qgrid, 256, 0, s>>>(P, qpyr);
-    for (int l = 3; l <= P.QLtop; ++l) {
-        const long long nodes = (long long) ((Mx >> l) > 0 ? (Mx >> l) : 1) * ((My >> l) > 0 ? (My >> l) : 1);
-        const int blocks = (int) ((nodes + 255) / 256 < 1184 ? (nodes + 255) / 256 : 1184);
-        hf_qpyramid_level_kernel<<<blocks, 256, 0, s>>>(P, qpyr, l);
-    }
+    if (P.QLtop > HF_QBASE_TOP) hf_qpyramid_top_kernel<<<1, 1024, 0, s>>>(P, qpyr);
     return cudaGetLastError();
 }
 
