@@ -277,7 +277,20 @@ def main_ours(a):
     if rank == 0:
         sampler.start()
         time.sleep(0.3)
-    ms_total = timed(lambda: step(True), a.steps)
+    timed(lambda: step(True), a.steps)              # eager pass: per-kernel CUDA events (roofline legs below)
+    # headline: the same step replayed from ONE CUDA graph (hfb200.capture): at N = 8 the step is ~1 ms of four launches and
+    # the host's launch calls would otherwise show up in it. Falls back to eager launches if capture is refused.
+    run_step, launch = (lambda: step(False)), "eager"
+    if os.environ.get("HF_BENCH_GRAPH", "1") != "0":
+        try:
+            run_step = hfb200.capture(lambda: step(False))
+            launch = "cuda-graph"
+        except Exception as exc:      # noqa: BLE001
+            print(f"bench.py: CUDA graph capture refused ({type(exc).__name__}: {exc}); eager launches", file=sys.stderr, flush=True)
+            torch.cuda.synchronize()
+    for _ in range(3):
+        run_step()
+    ms_total = timed(run_step, a.steps)
     clocks = sampler.stop() if rank == 0 else None
     ms_step = ms_total / a.steps
     value = n_total / (ms_step * 1e-3) / 1e6
@@ -340,7 +353,7 @@ def main_ours(a):
     line = {
         "metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": a.steps, "warmup": max(a.warmup, 3),
         "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": workload_name(a), "rays_per_step": n_total, "rays_per_gpu": n_local, "sharding": f"{a.tile}x{a.tile}-pixel image tiles, round-robin",
+        "config": {"workload": workload_name(a), "rays_per_step": n_total, "rays_per_gpu": n_local, "sharding": f"{a.tile}x{a.tile}-pixel image tiles, round-robin", "launch": launch,
                    "collective": "ncclAllReduce(grad 64 MiB fp32, sum) per step" if world > 1 else "none (1 GPU)",
                    "l2": "inputs exceed L2 (ray + adjoint + output SoA > 5 GB per step vs 126 MB L2); no explicit flush",
                    "si_fields": "t,p,n,uv", "hit_fraction": hits},

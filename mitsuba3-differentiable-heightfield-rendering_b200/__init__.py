@@ -178,6 +178,26 @@ def _stream():
     return C.c_void_p(torch.cuda.current_stream().cuda_stream)
 
 
+def capture(fn, warmup=1):
+    """Record the launches `fn` makes (every entry point here is asynchronous on the current stream, the NCCL allreduce included)
+    into one CUDA graph and return a callable that replays it: a step of a few ~1 ms kernels is otherwise bound by the host's
+    launch calls. `fn` must not allocate, synchronise or read results back; arguments are baked in (the buffers are re-used)."""
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        for _ in range(max(1, warmup)):
+            fn()
+    torch.cuda.current_stream().wait_stream(side)
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        fn()
+    def replay():
+        g.replay()
+    replay.graph = g              # keeps the graph (and its memory pool) alive as long as the callable
+    return replay
+
+
 def _ptr(t):
     return C.c_void_p(t.data_ptr()) if t is not None else None
 
