@@ -48,6 +48,10 @@ struct float2 { float x, y; };
 #define HF_DESC_LEVELS 2      // levels dropped per descent (the slab clip places the entry cell, so skipping a level is cheap)
 #endif
 
+#ifndef HF_EVEN_LEVELS
+#define HF_EVEN_LEVELS 1      // 1: the walk only visits even levels (descends and pops two levels at a time)
+#endif
+
 #define HF_TRAV_SLACK 9.5367431640625e-07f   // 2^-20, identical to HF_Z_SLACK / HFO_Z_SLACK
 
 struct __attribute__((aligned(16))) HfLevel {   // one pyramid level; `nodes` may point to global OR shared memory (generic address)
@@ -98,6 +102,7 @@ struct HfWalk {                // per-ray state, lives in registers. x, y are MI
     float qsf, zbf;            // decode constants of the quantised nodes, negated for a flipped ray
     int ix, iy, L;             // mirrored cell, level
     int xm, ym;                // mirror masks: real cell = (ix ^ xm, iy ^ ym)
+    int xlim, ylim;            // last real cell in mirrored coordinates: beyond it lies padding (or the end of the padded domain)
     uint32_t sel_lo;           // byte selector (prmt) of the node half that bounds z' from below
     bool alive;
 };
@@ -179,6 +184,7 @@ HF_HD bool hf_walk_init(const HfGrid &G, float ox, float oy, float oz, float dx,
         // mirror: the walk only ever moves towards +x', +y'
         const bool mx_ = dgx < 0.f, my_ = dgy < 0.f;
         w.xm = mx_ ? G.xmask : 0; w.ym = my_ ? G.ymask : 0;
+        w.xlim = mx_ ? G.xmask : NX - 1; w.ylim = my_ ? G.ymask : NY - 1;   // a mirrored ray has the padding behind it
         w.ogxl = 0.f; w.ogyl = 0.f;
         if (mx_) {                           // two-sum: M + (-og) = s + e exactly
             const float a = (float) (G.xmask + 1), b = -ogx, sm = a + b, bb = sm - a;
@@ -193,6 +199,9 @@ HF_HD bool hf_walk_init(const HfGrid &G, float ox, float oy, float oz, float dx,
         w.ix = ix ^ w.xm; w.iy = iy ^ w.ym;
     }
     w.L = hf_imin(G.QLtop, late ? L_start : HF_START_LEVEL);
+#if HF_EVEN_LEVELS
+    w.L &= ~1;
+#endif
     w.t = t0;
     {   // flip z for a climbing ray: the walk only ever moves towards -z'
         const bool fz = dz > 0.f;
@@ -228,7 +237,6 @@ HF_HD bool hf_walk_next(const HfGrid &G, HfWalk &w, HfCand &c
 #endif
 ) {
     if (!w.alive) return false;
-    const int NX_ = G.NX, NY_ = G.NY;
     const uint32_t sel_hi = w.sel_lo ^ 0x0022u;
     for (;;) {
 #ifndef __CUDACC__
@@ -278,31 +286,34 @@ HF_HD bool hf_walk_next(const HfGrid &G, HfWalk &w, HfCand &c
         // a step leaves the node through the plane(s) reached first; a descent stays inside
         const bool stepx = !desc && (tx <= ty), stepy = !desc && (ty <= tx);
         const int nix = stepx ? bx : rx, niy = stepy ? by : ry;
-        const bool outside = ((unsigned) nix > (unsigned) G.xmask) || ((unsigned) niy > (unsigned) G.ymask);
+        const bool outside = (nix > w.xlim) || (niy > w.ylim);            // never enters a padding cell (their nodes hold HF_Q_EMPTY)
         const unsigned m = (unsigned) ((nix ^ ix) | (niy ^ iy));
+#if HF_EVEN_LEVELS
+        const bool up = m > (unsigned) (4 * mask + 3);                    // left the grandparent node: go up two levels
+#else
         const bool up = m > (unsigned) (2 * mask + 1);                    // left the parent node: go up one level
+#endif
 
 #if !defined(__CUDACC__) && defined(HF_WALK_HIST)
         { extern unsigned long long hf_walk_hist[3][32];
           _Pragma("omp atomic") hf_walk_hist[desc ? 0 : (found ? 2 : 1)][L]++; }
 #endif
+#if HF_EVEN_LEVELS
+        w.L = desc ? L - 2 : (up ? L + 2 : L);                            // levels stay even: a 4 x 4-ary walk
+#else
         w.L = desc ? hf_imax(L - HF_DESC_LEVELS, 0) : (up ? L + 1 : L);
+#endif
         w.ix = nix;
         w.iy = niy;
         w.t = tq;
         w.alive = desc ? true : !(last || outside);
         if (found) {
-#ifdef __CUDACC__
-            asm volatile("");                                             // keep the guard below out of the loop body
-#endif
-            const int cx = ix ^ w.xm, cy = iy ^ w.ym;
-            if (cx < NX_ && cy < NY_) {                                   // padding cells hold HF_Q_EMPTY; belt and braces
-                const float *row0 = G.heights + (unsigned) (cy * G.W + cx);          // W*H < 2^32 (checked by hf_create)
-                c.z00 = G.mh * HF_LDG(row0); c.z10 = G.mh * HF_LDG(row0 + 1);
-                c.z01 = G.mh * HF_LDG(row0 + G.W); c.z11 = G.mh * HF_LDG(row0 + G.W + 1);
-                c.cx = cx; c.cy = cy;
-                return true;
-            }
+            const int cx = ix ^ w.xm, cy = iy ^ w.ym;                     // always a real cell: see `outside`
+            const float *row0 = G.heights + (unsigned) (cy * G.W + cx);   // W*H < 2^32 (checked by hf_create)
+            c.z00 = G.mh * HF_LDG(row0); c.z10 = G.mh * HF_LDG(row0 + 1);
+            c.z01 = G.mh * HF_LDG(row0 + G.W); c.z11 = G.mh * HF_LDG(row0 + G.W + 1);
+            c.cx = cx; c.cy = cy;
+            return true;
         }
         if (!w.alive) return false;
     }
