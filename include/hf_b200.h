@@ -142,6 +142,12 @@ int hf_size(hf_ctx *ctx, uint32_t *width, uint32_t *height);
  * pairs of z = max_height*h, row-major. levels/width/height/d_nodes are each nullable. */
 int hf_pyramid_level(hf_ctx *ctx, uint32_t level, uint32_t *levels, uint32_t *width, uint32_t *height,
                      const float **d_nodes);
+/* the quantised copy of that data which the production walk reads (csrc/hf_qpyr.h): level l in 0..levels (level 0 = one node per
+ * cell), padded to a power of two per axis: pitch x rows uint32 nodes, row-major, (hi << 16) | lo with
+ * decode(code) = fmaf(float(code), qs, zb) a lower (lo) / upper (hi) bound of the node's z range; padding nodes hold 0x0000FFFF.
+ * Synchronises (qs, zb derive from the root node on the device). Every output is nullable. */
+int hf_qpyramid_level(hf_ctx *ctx, uint32_t level, uint32_t *levels, uint32_t *pitch, uint32_t *rows, const uint32_t **d_nodes,
+                      float *qs, float *zb);
 
 /* shape.h:137-138 ray_intersect_preliminary */
 int hf_ray_intersect_preliminary(hf_ctx *ctx, const hf_rays *rays, const hf_prelim *out, size_t n, void *stream);

@@ -139,6 +139,7 @@ def _load():
         "hf_primitive_count": [vp, C.POINTER(u32)],
         "hf_size": [vp, C.POINTER(u32), C.POINTER(u32)],
         "hf_pyramid_level": [vp, u32, C.POINTER(u32), C.POINTER(u32), C.POINTER(u32), C.POINTER(vp)],
+        "hf_qpyramid_level": [vp, u32, C.POINTER(u32), C.POINTER(u32), C.POINTER(u32), C.POINTER(vp), C.POINTER(C.c_float), C.POINTER(C.c_float)],
         "hf_ray_intersect_preliminary": [vp, C.POINTER(_Rays), C.POINTER(_Prelim), sz, vp],
         "hf_ray_intersect_preliminary_counted": [vp, C.POINTER(_Rays), C.POINTER(_Prelim), sz, vp],
         "hf_stats_get": [vp, C.POINTER(_Stats), C.c_int],
@@ -452,6 +453,22 @@ class Heightfield:
             with torch.cuda.device(self.device):
                 out.append(torch.as_tensor(_DevView(ptr.value, (h.value, w.value, 2), self), device=self.device))
         return out
+
+    def qpyramid_levels(self):
+        """The quantised pyramid the production walk reads: ([(rows, pitch) int32 device tensors for levels 0..Ltop], qs, zb);
+        node = (hi << 16) | lo, bound = fma(code, qs, zb) (csrc/hf_qpyr.h). Zero-copy views."""
+        L = _load()
+        nl, qs, zb = C.c_uint32(), C.c_float(), C.c_float()
+        _check(L.hf_qpyramid_level(self._ctx, 0, C.byref(nl), None, None, None, C.byref(qs), C.byref(zb)))
+        out = []
+        for l in range(0, nl.value + 1):
+            p, r, ptr = C.c_uint32(), C.c_uint32(), C.c_void_p()
+            _check(L.hf_qpyramid_level(self._ctx, l, None, C.byref(p), C.byref(r), C.byref(ptr), None, None))
+            view = _DevView(ptr.value, (r.value, p.value), self)
+            view.__cuda_array_interface__["typestr"] = "<i4"
+            with torch.cuda.device(self.device):
+                out.append(torch.as_tensor(view, device=self.device))
+        return out, qs.value, zb.value
 
     def _mask(self, active, n):
         if active is None:

@@ -386,6 +386,30 @@ extern "C" int hf_size(hf_ctx *c, uint32_t *w, uint32_t *h) {
     return HF_OK;
 }
 
+extern "C" int hf_qpyramid_level(hf_ctx *c, uint32_t level, uint32_t *levels, uint32_t *pitch, uint32_t *rows, const uint32_t **d_nodes,
+                                 float *qs, float *zb) {
+    CHECK_CTX(c);
+    const HfParams &P = c->P;
+    if (levels) *levels = (uint32_t) P.QLtop;
+    if (level > (uint32_t) P.QLtop) {
+        if (pitch || rows || d_nodes) return fail(HF_ERR_INVALID, "quantised pyramid level %u out of range 0..%d", level, P.QLtop);
+    } else {
+        if (pitch) *pitch = (uint32_t) std::max((P.xmask + 1) >> level, 1);
+        if (rows) *rows = (uint32_t) std::max((P.ymask + 1) >> level, 1);
+        if (d_nodes) *d_nodes = c->d_qpyr + P.qoff[level];
+    }
+    if (qs || zb) {
+        NEED_ACCEL(c);
+        CU(cudaSetDevice(c->device));
+        float2 top;
+        CU(cudaMemcpy(&top, c->d_pyr + P.lvl_off[P.Ltop], sizeof(float2), cudaMemcpyDeviceToHost));
+        const HfQuant q = hf_quant_make(top.x, top.y);
+        if (qs) *qs = q.qs;
+        if (zb) *zb = q.zb;
+    }
+    return HF_OK;
+}
+
 extern "C" int hf_pyramid_level(hf_ctx *c, uint32_t level, uint32_t *levels, uint32_t *w, uint32_t *h, const float **d_nodes) {
     CHECK_CTX(c);
     const HfParams &P = c->P;

@@ -91,6 +91,68 @@ def test_pyramid_bit_exact(hf, oracle, H, W):
     assert g.primitive_count() == c.primitive_count() == 2 * (H - 1) * (W - 1)
 
 
+@pytest.mark.parametrize("H,W", [(2, 2), (3, 2), (5, 7), (17, 33), (64, 65), (100, 517), (700, 300)])
+def test_quantised_pyramid_is_conservative(hf, oracle, H, W):
+    """csrc/hf_qpyr.h: every node of the padded, quantised pyramid the walk reads decodes to bounds that contain the exact
+    (min, max) of its cells; padding nodes hold the empty code; the layout is the documented power-of-two one."""
+    rng = np.random.default_rng(H * 11 + W)
+    h = (rng.uniform(-1, 2, (H, W)) * rng.choice([1.0, 1e-3, 50.0])).astype(f32)
+    mh = -0.8
+    g, _ = _mk(hf, oracle, h, mh)
+    levels, qs, zb = g.qpyramid_levels()
+    NX, NY = W - 1, H - 1
+    Mx, My = 1 << int(np.ceil(np.log2(max(NX, 1)))), 1 << int(np.ceil(np.log2(max(NY, 1))))
+    assert len(levels) - 1 == max(int(np.log2(Mx)), int(np.log2(My)), 1)
+    z = (f32(mh) * h).astype(f32)
+    cmin = np.minimum(np.minimum(z[:-1, :-1], z[:-1, 1:]), np.minimum(z[1:, :-1], z[1:, 1:]))
+    cmax = np.maximum(np.maximum(z[:-1, :-1], z[:-1, 1:]), np.maximum(z[1:, :-1], z[1:, 1:]))
+    pmin = np.full((My, Mx), np.inf, f32); pmax = np.full((My, Mx), -np.inf, f32)
+    pmin[:NY, :NX] = cmin; pmax[:NY, :NX] = cmax
+    qs32, zb32 = f32(qs), f32(zb)
+    for l, t in enumerate(levels):
+        q = _np(t).view(np.uint32)
+        rows, pitch = max(My >> l, 1), max(Mx >> l, 1)
+        assert q.shape == (rows, pitch)
+        fy, fx = My // rows, Mx // pitch
+        emin = pmin.reshape(rows, fy, pitch, fx).min(axis=(1, 3)); emax = pmax.reshape(rows, fy, pitch, fx).max(axis=(1, 3))
+        lo = (q & 0xFFFF).astype(np.float64); hi = (q >> 16).astype(np.float64)
+        # fma(code, qs, zb) in fp32: the product code * qs is exact in fp64, one rounding to fp32 after the add
+        dlo = (lo * np.float64(qs32) + np.float64(zb32)).astype(f32); dhi = (hi * np.float64(qs32) + np.float64(zb32)).astype(f32)
+        real = np.isfinite(emin)
+        assert (q[~real] == 0x0000FFFF).all()
+        assert (dlo[real] <= emin[real]).all() and (dhi[real] >= emax[real]).all()
+        if l == 0:            # quantisation costs at most a few codes per bound
+            assert (emin[real] - dlo[real]).max() <= 4.5 * qs32 + 1e-30 and (dhi[real] - emax[real]).max() <= 4.5 * qs32 + 1e-30
+
+
+def test_capture_replays_the_step(hf, oracle):
+    """hfb200.capture: zero_grad + ray_intersect + backward recorded into one CUDA graph give the eager result on every replay."""
+    rng = np.random.default_rng(5)
+    h = random_heights(rng, 65, 65, "smooth")
+    g, _ = _mk(hf, oracle, h, 0.7)
+    o, d = random_rays(rng, 50000)
+    ray = hf.Ray3f(torch.from_numpy(o.T.copy()), torch.from_numpy(d.T.copy()))
+    n = o.shape[0]
+    adj = g.prepare_adjoints({"t": torch.ones(n), "n": torch.ones(3, n)}, n)
+    si = hf.SurfaceInteraction3f(n, g.device, g, ("t", "p", "n", "uv")); pi = hf.PreliminaryIntersection3f(n, g.device, g)
+
+    def step():
+        g.zero_grad()
+        g.ray_intersect(ray, out=(si, pi))
+        g.backward(ray, pi, adj)
+
+    step()
+    torch.cuda.synchronize()
+    ref_t, ref_g = _np(pi.t).copy(), _np(g.grad).astype(np.float64).copy()
+    replay = hf.capture(step)
+    for _ in range(3):
+        pi.t.zero_()
+        replay()
+        torch.cuda.synchronize()
+        assert np.array_equal(_np(pi.t).view(np.uint32), ref_t.view(np.uint32))
+        assert np.linalg.norm(_np(g.grad).astype(np.float64) - ref_g) <= 1e-5 * np.linalg.norm(ref_g)
+
+
 # ---- the reference's known answers, on the GPU ---------------------------------------------------------
 def test_test10_known_answers(hf, oracle):
     """src/render/tests/test_mesh.py:257-292 on the flat 2x2 field (== rectangle.obj)."""
