@@ -582,7 +582,7 @@ __device__ __forceinline__ void hf_process_ray(const HfParams &P, const HfGrid &
 }
 
 #ifndef HF_MIN_CTAS
-#define HF_MIN_CTAS 4
+#define HF_MIN_CTAS 3              // 80 registers, no spills: measured 3 % faster than 4 CTAs of 64 registers once the loop got shorter
 #endif
 #ifdef HF_DEBUG_TIMING            // dev builds only (make VARIANT=_dbg EXTRA=-DHF_DEBUG_TIMING): per-warp timeline of the fast kernel
 __device__ unsigned long long hf_dbg[8192 * 6];
