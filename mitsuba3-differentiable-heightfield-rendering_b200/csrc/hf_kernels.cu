@@ -412,6 +412,38 @@ __device__ __forceinline__ void write_si(const HfParams &P, const hf_si &S, size
     }
 }
 
+// The common request -- t, p, n, uv only (no dp_du / dp_dv, shading frame, wi, no FollowShape): same arithmetic as write_si for these
+// fields, without the 17 null tests and the partial-derivative code of the general writer (3-4 % of the fused kernel's instructions).
+__device__ __forceinline__ void write_si_lean(const HfParams &P, const hf_si &S, size_t i, float t, float b1, float b2, f3 p0, f3 p1, f3 p2) {
+    const float b0 = 1.f - b1 - b2;
+    const f3 dp0 = sub3(p1, p0), dp1 = sub3(p2, p0);
+    const f3 po = mk3(fmaf(p0.x, b0, fmaf(p1.x, b1, p2.x * b2)),
+                      fmaf(p0.y, b0, fmaf(p1.y, b1, p2.y * b2)),
+                      fmaf(p0.z, b0, fmaf(p1.z, b1, p2.z * b2)));
+    const f3 no = normalize3(cross3(dp0, dp1));
+    const f3 pw = xform_point(P.to_world, po);
+    f3 nw = normalize3(xform_normal(P.to_object, no));
+    const float u0x = tex(p0.x), u0y = tex(p0.y), u1x = tex(p1.x), u1y = tex(p1.y), u2x = tex(p2.x), u2y = tex(p2.y);
+    const float uvx = fmaf(u2x, b2, fmaf(u1x, b1, u0x * b0));
+    const float uvy = fmaf(u2y, b2, fmaf(u1y, b1, u0y * b0));
+    if (P.flip_normals) nw = neg3(nw);
+    STF(S.t, t);
+    STF(S.px, pw.x); STF(S.py, pw.y); STF(S.pz, pw.z);
+    STF(S.nx, nw.x); STF(S.ny, nw.y); STF(S.nz, nw.z);
+    STF(S.uvx, uvx); STF(S.uvy, uvy);
+}
+__device__ __forceinline__ void write_si_invalid_lean(const hf_si &S, size_t i) {
+    STF(S.t, HF_INF);
+    STF(S.px, 0.f); STF(S.py, 0.f); STF(S.pz, 0.f);
+    STF(S.nx, 0.f); STF(S.ny, 0.f); STF(S.nz, 0.f);
+    STF(S.uvx, 0.f); STF(S.uvy, 0.f);
+}
+static inline bool hf_si_is_lean(const hf_si &S, uint32_t flags) {
+    return !(flags & HF_RAY_FOLLOWSHAPE) && !S.dpdu_x && !S.dpdu_y && !S.dpdu_z && !S.dpdv_x && !S.dpdv_y && !S.dpdv_z &&
+           !S.shn_x && !S.shn_y && !S.shn_z && !S.shs_x && !S.shs_y && !S.shs_z && !S.sht_x && !S.sht_y && !S.sht_z &&
+           !S.wi_x && !S.wi_y && !S.wi_z;
+}
+
 // ------------------------------------------------------------------------------------------
 // Intersection kernel (persistent CTAs, one ray per thread per tile of HF_BLOCK rays)
 // ------------------------------------------------------------------------------------------
@@ -556,7 +588,7 @@ __device__ __forceinline__ void hf_process_ray(const HfParams &P, const HfGrid &
         __stcs(O.v + i, hit ? hv : 0.f);
         __stcs(O.prim_index + i, hit ? hprim : 0u);
     }
-    if (MODE == HF_MODE_FUSED_SI) {
+    if (MODE == HF_MODE_FUSED_SI || MODE == HF_MODE_FUSED_SI_LEAN) {
         if (hit) {
             // vertices of the hit triangle straight from the candidate-cell registers
             const float x0 = vtx(c.cx, P.W, P.rw), x1 = vtx(c.cx + 1, P.W, P.rw);
@@ -565,14 +597,20 @@ __device__ __forceinline__ void hf_process_ray(const HfParams &P, const HfGrid &
             f3 p1, p2;
             if ((hprim & 1u) == 0u) { p1 = mk3(x0, y1, c.z01); p2 = mk3(x0, y0, c.z00); }
             else { p1 = mk3(x1, y1, c.z11); p2 = mk3(x0, y1, c.z01); }
-            // the world-space ray is only needed by FollowShape and wi: re-read it (L2) instead of keeping six
-            // registers alive across the walk
-            f3 ow2 = mk3(0.f, 0.f, 0.f), dw2 = ow2;
-            if ((flags & HF_RAY_FOLLOWSHAPE) || S.wi_x || S.wi_y || S.wi_z) {
-                ow2 = mk3(__ldcs(R.ox + i), __ldcs(R.oy + i), __ldcs(R.oz + i));
-                dw2 = mk3(__ldcs(R.dx + i), __ldcs(R.dy + i), __ldcs(R.dz + i));
+            if (MODE == HF_MODE_FUSED_SI_LEAN) {
+                write_si_lean(P, S, i, ht, hu, hv, p0, p1, p2);
+            } else {
+                // the world-space ray is only needed by FollowShape and wi: re-read it (L2) instead of keeping six
+                // registers alive across the walk
+                f3 ow2 = mk3(0.f, 0.f, 0.f), dw2 = ow2;
+                if ((flags & HF_RAY_FOLLOWSHAPE) || S.wi_x || S.wi_y || S.wi_z) {
+                    ow2 = mk3(__ldcs(R.ox + i), __ldcs(R.oy + i), __ldcs(R.oz + i));
+                    dw2 = mk3(__ldcs(R.dx + i), __ldcs(R.dy + i), __ldcs(R.dz + i));
+                }
+                write_si(P, S, i, flags, ow2, dw2, ht, hu, hv, p0, p1, p2);
             }
-            write_si(P, S, i, flags, ow2, dw2, ht, hu, hv, p0, p1, p2);
+        } else if (MODE == HF_MODE_FUSED_SI_LEAN) {
+            write_si_invalid_lean(S, i);
         } else {
             f3 dw2 = mk3(0.f, 0.f, 0.f);
             if (S.wi_x || S.wi_y || S.wi_z) dw2 = mk3(__ldcs(R.dx + i), __ldcs(R.dy + i), __ldcs(R.dz + i));
@@ -774,6 +812,7 @@ cudaError_t hf_launch_intersect(const HfParams &P, const HfLaunchInfo &li, int m
         return cudaGetLastError();
     }
     const size_t smem = (size_t) li.top_nodes * sizeof(float2);
+    if (mode == HF_MODE_FUSED_SI && hf_si_is_lean(si, flags)) mode = HF_MODE_FUSED_SI_LEAN;
     if (li.use_bundles && mode != HF_MODE_TEST) {
         const unsigned long long ngroups = (n + 31) / 32;
         const unsigned long long nbig = (ngroups - ngroups / 8) / 32;                 // the last eighth (at least) goes out in small tiles
@@ -786,6 +825,8 @@ cudaError_t hf_launch_intersect(const HfParams &P, const HfLaunchInfo &li, int m
         if (e != cudaSuccess) return e;
         if (mode == HF_MODE_PRELIM)
             hf_intersect_beam_kernel<HF_MODE_PRELIM><<<bgrid, HF_BLOCK, smem, s>>>(P, li, rays, prelim, si, d_hit, flags, n, nbig, sched);
+        else if (mode == HF_MODE_FUSED_SI_LEAN)
+            hf_intersect_beam_kernel<HF_MODE_FUSED_SI_LEAN><<<bgrid, HF_BLOCK, smem, s>>>(P, li, rays, prelim, si, d_hit, flags, n, nbig, sched);
         else
             hf_intersect_beam_kernel<HF_MODE_FUSED_SI><<<bgrid, HF_BLOCK, smem, s>>>(P, li, rays, prelim, si, d_hit, flags, n, nbig, sched);
         return cudaGetLastError();
@@ -795,6 +836,7 @@ cudaError_t hf_launch_intersect(const HfParams &P, const HfLaunchInfo &li, int m
         carved = true;
         hf_prefer_l1(hf_intersect_fast_kernel<HF_MODE_PRELIM>, smem + 1024, HF_MIN_CTAS);
         hf_prefer_l1(hf_intersect_fast_kernel<HF_MODE_FUSED_SI>, smem + 1024, HF_MIN_CTAS);
+        hf_prefer_l1(hf_intersect_fast_kernel<HF_MODE_FUSED_SI_LEAN>, smem + 1024, HF_MIN_CTAS);
         hf_prefer_l1(hf_intersect_fast_kernel<HF_MODE_TEST>, smem + 1024, HF_MIN_CTAS);
     }
     {
@@ -813,6 +855,8 @@ cudaError_t hf_launch_intersect(const HfParams &P, const HfLaunchInfo &li, int m
         switch (mode) {
             case HF_MODE_PRELIM:
                 hf_intersect_fast_kernel<HF_MODE_PRELIM><<<fgrid, HF_BLOCK, smem, s>>>(P, li, rays, prelim, si, d_hit, flags, n, nbig, sched); break;
+            case HF_MODE_FUSED_SI_LEAN:
+                hf_intersect_fast_kernel<HF_MODE_FUSED_SI_LEAN><<<fgrid, HF_BLOCK, smem, s>>>(P, li, rays, prelim, si, d_hit, flags, n, nbig, sched); break;
             case HF_MODE_FUSED_SI:
                 hf_intersect_fast_kernel<HF_MODE_FUSED_SI><<<fgrid, HF_BLOCK, smem, s>>>(P, li, rays, prelim, si, d_hit, flags, n, nbig, sched); break;
             default:

@@ -15,7 +15,8 @@ struct HfLaunchInfo {
     int use_bundles;         // 1: bundled kernel (hf_intersect_beam_kernel), 0: plain per-ray kernel
 };
 
-enum HfIntersectMode { HF_MODE_PRELIM = 0, HF_MODE_FUSED_SI = 1, HF_MODE_TEST = 2, HF_MODE_COUNTED = 3 };
+enum HfIntersectMode { HF_MODE_PRELIM = 0, HF_MODE_FUSED_SI = 1, HF_MODE_TEST = 2, HF_MODE_COUNTED = 3,
+                       HF_MODE_FUSED_SI_LEAN = 4 };   // internal: FUSED_SI when only t, p, n, uv are requested (chosen by hf_launch_intersect)
 
 cudaError_t hf_launch_pyramid(const HfParams &P, float2 *pyr, uint32_t *qpyr, cudaStream_t s);
 cudaError_t hf_launch_intersect(const HfParams &P, const HfLaunchInfo &li, int mode, const hf_rays &rays,
