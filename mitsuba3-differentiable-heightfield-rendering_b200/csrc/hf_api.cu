@@ -97,8 +97,13 @@ static int nccl_load() {
 // ------------------------------------------------------------------------------------------
 #define HF_SCHED_SLOTS 256            // every launch of a self-scheduling kernel gets its own counter (launches on different streams overlap)
 #define HF_TOP_NODE_CAP 1366          // (32^2 + 16^2 + ... + 1) rounded up to even: 10.9 KB of shared memory
-#define HF_HOST_CHUNK (size_t(1) << 21)
+#ifndef HF_HOST_CHUNK_LOG2
+#define HF_HOST_CHUNK_LOG2 21
+#endif
+#define HF_HOST_CHUNK (size_t(1) << HF_HOST_CHUNK_LOG2)
+#ifndef HF_HOST_SLOTS
 #define HF_HOST_SLOTS 2
+#endif
 #define HF_SLAB_FLOATS 53             // rays 7 + prelim 4 + si 26 + adj 15 + active mask
 
 struct HostSlot {

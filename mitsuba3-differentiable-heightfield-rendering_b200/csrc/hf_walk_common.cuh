@@ -5,7 +5,9 @@
 #include "hf_kernels.h"
 #include "hf_traverse.cuh"
 
+#ifndef HF_BLOCK
 #define HF_BLOCK 256
+#endif
 #define FULL_MASK 0xffffffffu
 
 // ------------------------------------------------------------------------------------------
