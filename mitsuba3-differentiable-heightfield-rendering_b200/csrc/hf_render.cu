@@ -58,6 +58,7 @@ struct HfRenderArgs {
     float inv_w, inv_h, tan_x, tan_y;  // 1/width, 1/height, tan(fov/2), tan(fov/2) * height / width
     float inv_spp, inv_npix;           // 1/spp, 1/(width*height)
     f3 o_obj;                          // camera position in object space
+    uint32_t seed_h0, seed_h1;         // lowbias32(seed * 0x9E3779B1 + channel * 0x85EBCA6B) for the two jitter channels (same for every sample)
     const uint32_t *pixels;            // nullable
     size_t npix;
 };
@@ -88,11 +89,16 @@ __device__ __forceinline__ void hf_camera_jitter(const HfRenderArgs &A, uint32_t
     if (A.cam.spp > 1) {
         const unsigned long long k = (unsigned long long) pid * A.cam.spp + s;
         const uint32_t key = (uint32_t) k ^ ((uint32_t) (k >> 32) * 0x85EBCA6Bu);
-        jx = hf_hash_uniform(A.cam.seed, key, 0); jy = hf_hash_uniform(A.cam.seed, key, 1);
+        jx = (float) (hf_hash32(key ^ A.seed_h0) >> 8) * (1.0f / 16777216.0f);      // == hf_hash_uniform(seed, key, 0 / 1)
+        jy = (float) (hf_hash32(key ^ A.seed_h1) >> 8) * (1.0f / 16777216.0f);
     }
 }
 __device__ __forceinline__ f3 hf_camera_dir_at(const HfRenderArgs &A, uint32_t pid, float jx, float jy) {
     const uint32_t x = pid % A.cam.width, y = pid / A.cam.width;
+    const float fx = ((float) x + jx) * A.inv_w, fy = ((float) y + jy) * A.inv_h;
+    return normalize3(hf_film_dir(A, fx, fy));
+}
+__device__ __forceinline__ f3 hf_camera_dir_xy(const HfRenderArgs &A, uint32_t x, uint32_t y, float jx, float jy) {   // pixel (x, y) given
     const float fx = ((float) x + jx) * A.inv_w, fy = ((float) y + jy) * A.inv_h;
     return normalize3(hf_film_dir(A, fx, fy));
 }
@@ -381,6 +387,7 @@ hf_render_kernel(const __grid_constant__ HfParams P, const HfLaunchInfo li, cons
         const unsigned npx = (unsigned) min((size_t) cap, A.npix - k0);
         for (unsigned j = 0; j < npx; ++j) {
             const uint32_t pid = __shfl_sync(FULL_MASK, my_pid, j * HF_SUB);
+            const uint32_t px = pid % A.cam.width, py = pid / A.cam.width;       // once per pixel, not per sample
             float acc = 0.f;
             for (uint32_t r = 0; r < rounds; ++r) {
                 const uint32_t s = r * 32u + lane;
@@ -394,7 +401,7 @@ hf_render_kernel(const __grid_constant__ HfParams P, const HfLaunchInfo li, cons
                 const float ts = __shfl_sync(FULL_MASK, t_enter, src);
                 const int ls = __shfl_sync(FULL_MASK, L_start, src);
                 const unsigned conv = __ballot_sync(FULL_MASK, s < spp);
-                if (s < spp) v = hf_shade_sample(P, G, A, hf_camera_dir_at(A, pid, jx, jy), ts, ls, prim, conv);
+                if (s < spp) v = hf_shade_sample(P, G, A, hf_camera_dir_xy(A, px, py, jx, jy), ts, ls, prim, conv);
                 acc += v;
                 s_prim[warp][(r * 32u + lane) & (HF_RENDER_MAX_SPP - 1)] = prim;
                 if (MODE == HF_RENDER_FWD && prim_out && s < spp)
@@ -623,6 +630,9 @@ static HfRenderArgs hf_render_args(const HfParams &P, const hf_camera &cam, cons
     }
     A.o_obj.x = r[0]; A.o_obj.y = r[1]; A.o_obj.z = r[2];
     A.pixels = d_pixels; A.npix = npix;
+    auto lowbias32 = [](uint32_t x) { x ^= x >> 16; x *= 0x7FEB352Du; x ^= x >> 15; x *= 0x846CA68Bu; x ^= x >> 16; return x; };
+    A.seed_h0 = lowbias32(cam.seed * 0x9E3779B1u + 0u * 0x85EBCA6Bu);
+    A.seed_h1 = lowbias32(cam.seed * 0x9E3779B1u + 1u * 0x85EBCA6Bu);
     return A;
 }
 
