@@ -630,6 +630,9 @@ __device__ __forceinline__ unsigned long long hf_gtime() { unsigned long long t;
 #ifndef HF_FAST_TAIL
 #define HF_FAST_TAIL 48
 #endif
+#ifndef HF_FAST_MIDTAIL
+#define HF_FAST_MIDTAIL 48
+#endif
 #ifndef HF_FAST_GROUPS
 #define HF_FAST_GROUPS 4           // 32-ray groups a warp takes off the global counter at a time
 #endif
@@ -639,7 +642,7 @@ template <int MODE>
 __global__ void __launch_bounds__(HF_BLOCK, HF_MIN_CTAS)
 hf_intersect_fast_kernel(const __grid_constant__ HfParams P, const HfLaunchInfo li, const hf_rays R, const hf_prelim O,
                          const hf_si S, uint8_t *__restrict__ hit_out, const uint32_t flags, const size_t n,
-                         const unsigned long long nbig, unsigned long long *__restrict__ sched) {
+                         const unsigned long long nbig, const unsigned long long npair, unsigned long long *__restrict__ sched) {
     HfGrid G;
     hf_stage_pyramid(P, li, G);
 
@@ -664,10 +667,13 @@ hf_intersect_fast_kernel(const __grid_constant__ HfParams P, const HfLaunchInfo 
             }
         }
 #endif
-        // the first nbig fetches are HF_FAST_GROUPS groups wide (a warp that stays on neighbouring rays re-uses its L1 lines); the
-        // closing fetches are single groups, so that the warps finish within ~20 us of each other whatever the batch size
-        const unsigned long long g0 = t < nbig ? t * HF_FAST_GROUPS : nbig * HF_FAST_GROUPS + (t - nbig);
-        const unsigned ng = t < nbig ? (unsigned) HF_FAST_GROUPS : 1u;
+        // the first nbig fetches are HF_FAST_GROUPS groups wide (a warp that stays on neighbouring rays re-uses its L1 lines), the
+        // next npair fetches two groups, the closing ones a single group: every phase outlasts the slowest fetch of the one before
+        unsigned long long g0;
+        unsigned ng;
+        if (t < nbig) { g0 = t * HF_FAST_GROUPS; ng = (unsigned) HF_FAST_GROUPS; }
+        else if (t < nbig + npair) { g0 = nbig * HF_FAST_GROUPS + (t - nbig) * 2ull; ng = 2u; }
+        else { g0 = nbig * HF_FAST_GROUPS + npair * 2ull + (t - nbig - npair); ng = 1u; }
         if (g0 >= ngroups) break;
         #pragma unroll 1
         for (unsigned g = 0; g < ng; ++g) {
@@ -844,23 +850,28 @@ cudaError_t hf_launch_intersect(const HfParams &P, const HfLaunchInfo &li, int m
         const size_t nwt = (ngroups + HF_FAST_GROUPS - 1) / HF_FAST_GROUPS, nct = (nwt + HF_BLOCK / 32 - 1) / (HF_BLOCK / 32);
         const size_t cap = (size_t) li.num_sms * HF_MIN_CTAS;
         const int fgrid = (int) (nct < cap ? nct : cap);
-        // closing phase: the last HF_FAST_TAIL groups per resident warp go out one at a time. A group whose rays skim down a slope
-        // (tens of candidate cells per ray) keeps its warp for ~100 us, four of them in one fetch for ~0.5 ms (profiles/r01_notes.md):
-        // the single-group phase has to last longer than that, i.e. ~48 groups of ~12 us per warp
-        const size_t tail = std::min(ngroups, (size_t) fgrid * (HF_BLOCK / 32) * HF_FAST_TAIL);
-        const unsigned long long nbig = (ngroups - tail) / HF_FAST_GROUPS;
+        // Closing phases. A group whose rays skim down a slope (tens of candidate cells per ray) keeps its warp for ~100 us, and such
+        // groups are neighbours: a fetch of four lasts up to ~0.5 ms, of two ~0.25 ms (profiles/r01_notes.md). So the last
+        // HF_FAST_TAIL groups per resident warp (~12 us each: ~0.3 ms) go out one at a time, the HF_FAST_MIDTAIL groups per warp
+        // before them in pairs (single groups lose the L1 sharing between the two halves of a 64-spp pixel, so they are kept to
+        // what the pairs need), and only the rest in fetches of HF_FAST_GROUPS.
+        const size_t warps = (size_t) fgrid * (HF_BLOCK / 32);
+        const size_t tail = std::min(ngroups, warps * HF_FAST_TAIL);
+        const size_t mid = std::min(ngroups - tail, warps * HF_FAST_MIDTAIL);
+        const unsigned long long nbig = (ngroups - tail - mid) / HF_FAST_GROUPS;
+        const unsigned long long npair = (ngroups - tail - nbig * HF_FAST_GROUPS) / 2;
         unsigned long long *sched = d_sched;
         cudaError_t e = cudaMemsetAsync(sched, 0, sizeof(unsigned long long), s);
         if (e != cudaSuccess) return e;
         switch (mode) {
             case HF_MODE_PRELIM:
-                hf_intersect_fast_kernel<HF_MODE_PRELIM><<<fgrid, HF_BLOCK, smem, s>>>(P, li, rays, prelim, si, d_hit, flags, n, nbig, sched); break;
+                hf_intersect_fast_kernel<HF_MODE_PRELIM><<<fgrid, HF_BLOCK, smem, s>>>(P, li, rays, prelim, si, d_hit, flags, n, nbig, npair, sched); break;
             case HF_MODE_FUSED_SI_LEAN:
-                hf_intersect_fast_kernel<HF_MODE_FUSED_SI_LEAN><<<fgrid, HF_BLOCK, smem, s>>>(P, li, rays, prelim, si, d_hit, flags, n, nbig, sched); break;
+                hf_intersect_fast_kernel<HF_MODE_FUSED_SI_LEAN><<<fgrid, HF_BLOCK, smem, s>>>(P, li, rays, prelim, si, d_hit, flags, n, nbig, npair, sched); break;
             case HF_MODE_FUSED_SI:
-                hf_intersect_fast_kernel<HF_MODE_FUSED_SI><<<fgrid, HF_BLOCK, smem, s>>>(P, li, rays, prelim, si, d_hit, flags, n, nbig, sched); break;
+                hf_intersect_fast_kernel<HF_MODE_FUSED_SI><<<fgrid, HF_BLOCK, smem, s>>>(P, li, rays, prelim, si, d_hit, flags, n, nbig, npair, sched); break;
             default:
-                hf_intersect_fast_kernel<HF_MODE_TEST><<<fgrid, HF_BLOCK, smem, s>>>(P, li, rays, prelim, si, d_hit, flags, n, nbig, sched); break;
+                hf_intersect_fast_kernel<HF_MODE_TEST><<<fgrid, HF_BLOCK, smem, s>>>(P, li, rays, prelim, si, d_hit, flags, n, nbig, npair, sched); break;
         }
     }
     return cudaGetLastError();

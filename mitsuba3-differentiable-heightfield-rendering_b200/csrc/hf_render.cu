@@ -28,6 +28,9 @@
 #ifndef HF_RENDER_TAIL
 #define HF_RENDER_TAIL 24              // pixels per resident warp that go out one at a time at the end (a pixel whose rays skim down a slope takes ~0.2 ms)
 #endif
+#ifndef HF_RENDER_MIDTAIL
+#define HF_RENDER_MIDTAIL 24           // pixels per resident warp that go out in pairs before those
+#endif
 #define HF_SUB (32 / HF_RENDER_TILE)    // bundles marched per pixel in hf_render_kernel: a HF_SUB_X x HF_SUB_Y split of the jitter square
 #if HF_RENDER_TILE == 4
 #define HF_SUB_X 4
@@ -354,18 +357,25 @@ hf_render_kernel(const __grid_constant__ HfParams P, const HfLaunchInfo li, cons
     const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
     const uint32_t spp = A.cam.spp;
     const uint32_t rounds = (spp + 31u) >> 5;
-    // closing phase of the schedule: the last HF_RENDER_TAIL pixels per resident warp go out one at a time, so that the warps
-    // finish within one pixel of each other whatever the size of the pixel list
-    const size_t tailpx = min(A.npix, (size_t) gridDim.x * (HF_BLOCK / 32) * HF_RENDER_TAIL);
-    const size_t nbig = (A.npix - tailpx) / HF_RENDER_TILE, rest0 = nbig * HF_RENDER_TILE;
+    // closing phases of the schedule: the last HF_RENDER_TAIL pixels per resident warp go out one at a time and the
+    // HF_RENDER_MIDTAIL pixels per warp before them in pairs, so that every phase outlasts the slowest tile of the one before
+    // (a pixel whose rays skim down a slope takes ~0.2 ms, and such pixels are neighbours) whatever the size of the pixel list
+    const size_t nwarps = (size_t) gridDim.x * (HF_BLOCK / 32);
+    const size_t tailpx = min(A.npix, nwarps * HF_RENDER_TAIL);
+    const size_t midpx = min(A.npix - tailpx, nwarps * HF_RENDER_MIDTAIL);
+    const size_t nbig = (A.npix - tailpx - midpx) / HF_RENDER_TILE, rest0 = nbig * HF_RENDER_TILE;
+    const size_t npair = (A.npix - tailpx - rest0) / 2, rest1 = rest0 + npair * 2;
     double loss_acc = 0.0;
 
     for (;;) {
         unsigned long long tile = 0;
         if (lane == 0) tile = atomicAdd(sched, 1ull);
         tile = __shfl_sync(FULL_MASK, tile, 0);
-        const size_t k0 = tile < nbig ? (size_t) tile * HF_RENDER_TILE : rest0 + (size_t) (tile - nbig);
-        const unsigned cap = tile < nbig ? (unsigned) HF_RENDER_TILE : 1u;
+        size_t k0;
+        unsigned cap;
+        if (tile < nbig) { k0 = (size_t) tile * HF_RENDER_TILE; cap = (unsigned) HF_RENDER_TILE; }
+        else if (tile < nbig + npair) { k0 = rest0 + (size_t) (tile - nbig) * 2; cap = 2u; }
+        else { k0 = rest1 + (size_t) (tile - nbig - npair); cap = 1u; }
         if (k0 >= A.npix) break;
         // ---- phase B: all 32 lanes march: lane = pixel * HF_SUB + sub-rectangle of the pixel's jitter square (HF_SUB_X x HF_SUB_Y).
         // A narrower bundle is marched further down the pyramid, so its samples start their own walks closer to the surface.

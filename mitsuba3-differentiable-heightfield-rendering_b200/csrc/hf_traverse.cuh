@@ -178,7 +178,10 @@ HF_HD bool hf_walk_init(const HfGrid &G, float ox, float oy, float oz, float dx,
         // is never ahead of the true one; covers the one extra rounding of the mirrored origin
         const float ex = 3.5762786865234375e-07f * ((float) (G.xmask + 1) + fabsf(ogx) + fabsf(t1 * dgx));
         const float ey = 3.5762786865234375e-07f * ((float) (G.ymask + 1) + fabsf(ogy) + fabsf(t1 * dgy));
-        const float bx0 = late ? (dgx > 0.f ? ogx - ex : ogx + ex) : ogx, by0 = late ? (dgy > 0.f ? ogy - ey : ogy + ey) : ogy;
+        // (no back-off along an axis the ray does not move on: its cell there is exact, and a ray lying in a cell boundary
+        // plane keeps the side the walk from t = 0 is on)
+        const float bx0 = late && dgx != 0.f ? (dgx > 0.f ? ogx - ex : ogx + ex) : ogx;
+        const float by0 = late && dgy != 0.f ? (dgy > 0.f ? ogy - ey : ogy + ey) : ogy;
         ix = hf_imin(hf_imax(hf_floor_sat(fmaf(t0, dgx, bx0)), 0), NX - 1);
         iy = hf_imin(hf_imax(hf_floor_sat(fmaf(t0, dgy, by0)), 0), NY - 1);
         // mirror: the walk only ever moves towards +x', +y'

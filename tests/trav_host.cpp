@@ -16,6 +16,10 @@ extern "C" unsigned long long *trav_host_hist(void) { return &hf_walk_hist[0][0]
 #include "../mitsuba3-differentiable-heightfield-rendering_b200/csrc/hf_traverse.cuh"
 #include "../oracle/hf_oracle.h"
 
+#ifndef HF_HOST_ROUNDS
+#define HF_HOST_ROUNDS 8      // dev statistics: walk iterations recorded for the first HF_HOST_ROUNDS candidate rounds of a ray
+#endif
+
 
 // Quantised pyramid (csrc/hf_qpyr.h) built on the host with the very functions the device builder uses.
 struct HostQPyr {
@@ -98,7 +102,7 @@ extern "C" int trav_host_intersect(const hfo_shape *s, const hfo_rays *r, size_t
                 for (;;) {
                     const unsigned before = it;
                     const bool more = hf_walk_next(G, w, c, &it);
-                    if (rounds && nc < 8) rounds[8 * i + nc] = it - before;
+                    if (rounds && nc < HF_HOST_ROUNDS) rounds[HF_HOST_ROUNDS * i + nc] = it - before;
                     if (!more) break;
                     ++nc;
                     float t, u, v; uint32_t prim;
