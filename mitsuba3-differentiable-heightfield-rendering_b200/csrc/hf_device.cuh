@@ -162,6 +162,9 @@ __device__ __forceinline__ void cell_triangle(const HfParams &P, uint32_t prim, 
                                               uint32_t &i0, uint32_t &i1, uint32_t &i2) {
     uint32_t cell = prim >> 1, k = prim & 1u;
     uint32_t cy = cell / (uint32_t) P.NX, cx = cell - cy * (uint32_t) P.NX;
+#ifdef HF_DEBUG_BOUNDS
+    if (cy >= (uint32_t) P.NY) __trap();       // checked build: a primitive index that is not a triangle of this field
+#endif
     float x0 = vtx((int) cx, P.W, P.rw), x1 = vtx((int) cx + 1, P.W, P.rw);
     float y0 = vtx((int) cy, P.H, P.rh), y1 = vtx((int) cy + 1, P.H, P.rh);
     uint32_t b = cy * (uint32_t) P.W + cx;

@@ -223,6 +223,15 @@ HF_HD bool hf_walk_init(const HfGrid &G, float ox, float oy, float oz, float dx,
     return true;
 }
 
+#ifdef HF_DEBUG_BOUNDS
+#ifdef __CUDACC__
+#define HF_BOUNDS_FAIL() __trap()
+#else
+#include <stdlib.h>
+#define HF_BOUNDS_FAIL() abort()
+#endif
+#endif
+
 HF_HD uint32_t hf_prmt(uint32_t q, uint32_t sel) {      // __byte_perm(q, 0, sel) for the two selectors the walk uses
 #ifdef __CUDACC__
     return __byte_perm(q, 0u, sel);
@@ -257,6 +266,12 @@ HF_HD bool hf_walk_next(const HfGrid &G, HfWalk &w, HfCand &c
         // z' never increases along the ray: its padded range over [t, te] is [z'(te) - eps, z'(t) + eps]
         const float zhi = fmaf(w.t, w.dz, w.ozp), zlo = fmaf(te, w.dz, w.ozm);
 
+#ifdef HF_DEBUG_BOUNDS
+        // checked build (make VARIANT=_bounds EXTRA=-DHF_DEBUG_BOUNDS; tests/trav_host.cpp defines it too): every node and texel
+        // index the walk forms is tested against the layout before it is used (compute-sanitizer is not available on the GPU pool)
+        if (L < 0 || L > G.QLtop || ((ix ^ w.xm) >> L) < 0 || ((ix ^ w.xm) >> L) > (G.xmask >> L) ||
+            ((iy ^ w.ym) >> L) < 0 || ((iy ^ w.ym) >> L) > (G.ymask >> L)) HF_BOUNDS_FAIL();
+#endif
         uint32_t q;
         {
 #ifdef __CUDACC__
@@ -312,6 +327,9 @@ HF_HD bool hf_walk_next(const HfGrid &G, HfWalk &w, HfCand &c
         w.alive = desc ? true : !(last || outside);
         if (found) {
             const int cx = ix ^ w.xm, cy = iy ^ w.ym;                     // always a real cell: see `outside`
+#ifdef HF_DEBUG_BOUNDS
+            if (cx < 0 || cx >= G.NX || cy < 0 || cy >= G.NY) HF_BOUNDS_FAIL();
+#endif
             const float *row0 = G.heights + (unsigned) (cy * G.W + cx);   // W*H < 2^32 (checked by hf_create)
             c.z00 = G.mh * HF_LDG(row0); c.z10 = G.mh * HF_LDG(row0 + 1);
             c.z01 = G.mh * HF_LDG(row0 + G.W); c.z11 = G.mh * HF_LDG(row0 + G.W + 1);
@@ -410,6 +428,9 @@ HF_HD float hf_beam_enter(const HfGrid &G, const HfBeam &b, int &L_start
         const HfLevel lv = G.lvl[Lq];
 #endif
         const int nxl = cxl >> Lq, nxh = cxh >> Lq, nyl = cyl >> Lq, nyh = cyh >> Lq;
+#ifdef HF_DEBUG_BOUNDS
+        if (nxl < 0 || nxh >= lv.w || nyl < 0 || nyh > ((NY - 1) >> Lq) || nxh > ((NX - 1) >> Lq)) HF_BOUNDS_FAIL();
+#endif
         const float2 a0 = lv.nodes[nyl * lv.w + nxl], a1 = lv.nodes[nyl * lv.w + nxh];
         const float2 a2 = lv.nodes[nyh * lv.w + nxl], a3 = lv.nodes[nyh * lv.w + nxh];
         const float mn = fminf(fminf(a0.x, a1.x), fminf(a2.x, a3.x)), mx = fmaxf(fmaxf(a0.y, a1.y), fmaxf(a2.y, a3.y));

@@ -13,6 +13,7 @@
 unsigned long long hf_walk_hist[3][32];
 extern "C" unsigned long long *trav_host_hist(void) { return &hf_walk_hist[0][0]; }
 #endif
+#define HF_DEBUG_BOUNDS 1     // the host build always checks the node / texel indices the walk forms
 #include "../mitsuba3-differentiable-heightfield-rendering_b200/csrc/hf_traverse.cuh"
 #include "../oracle/hf_oracle.h"
 
