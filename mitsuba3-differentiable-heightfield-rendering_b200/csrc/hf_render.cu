@@ -3,11 +3,13 @@
 // under one directional emitter (optionally with a visibility ray), box-filter pixel means, and the adjoint of all of it
 // with respect to the height texels -- without a ray, an intersection record or a surface interaction ever touching HBM.
 //
-// Work decomposition: a warp owns a tile of HF_RENDER_TILE listed pixels, fetched from a global counter.
-//   phase B  lane j marches the bundle of pixel j (all sub-pixel positions of the pixel: the direction bounds are
-//            the four pixel corners, known analytically) through the pyramid -> entry parameter of the pixel;
-//   phase C  pixel by pixel, the 32 lanes trace the pixel's samples (spp / 32 rounds) from that entry parameter,
-//            shade them, and reduce the pixel mean with shuffles in a fixed order (deterministic image);
+// Work decomposition: a warp owns a tile of listed pixels, fetched from a global counter: HF_RENDER_TILE rounds of 32 rays, i.e.
+// HF_RENDER_TILE pixels at >= 32 spp and up to 32 pixels below (half and quarter tiles in the closing phases of the schedule).
+//   phase B  all 32 lanes march bundles through the pyramid: each pixel of the tile is split into 8 / 4 / 2 / 1 sub-rectangles of
+//            its jitter square (direction bounds = the corners of the sub-rectangle, known analytically) -> entry parameter
+//            and start level for the samples that fall into it;
+//   phase C  round by round, the 32 lanes trace 32 samples (of one pixel, or of 32 / seg pixels when spp < 32) from their entry
+//            parameters, shade them, and reduce each pixel's mean with shuffles in a fixed order (deterministic image);
 //   epilogue the pixel's adjoint is known as soon as its mean is (L2 step) or is read from the adjoint image
 //            (backward); the samples' hit triangles wait in shared memory, every distinct triangle of a round gets
 //            ONE set of three red.global.add.f32 (match.any on the triangle id; all samples of a pixel carry the
@@ -22,32 +24,16 @@
 #define HF_RENDER_MAX_SPP 256          // samples of one pixel whose hit triangles wait in shared memory
 #define HF_NO_PRIM 0xffffffffu
 #ifndef HF_RENDER_TILE
-#define HF_RENDER_TILE 4               // listed pixels per warp tile: small tiles keep the tail of the dynamic schedule short;
-#endif                                 // only HF_RENDER_TILE lanes march bundles in phase B (1 % of the instructions)
+#define HF_RENDER_TILE 4               // 32-ray rounds per warp tile: small tiles keep the tail of the dynamic schedule short
+#endif
 
 #ifndef HF_RENDER_TAIL
-#define HF_RENDER_TAIL 24              // pixels per resident warp that go out one at a time at the end (a pixel whose rays skim down a slope takes ~0.2 ms)
+#define HF_RENDER_TAIL 24              // quarter tiles per resident warp that go out one at a time at the end (a pixel whose rays skim down a slope takes ~0.2 ms)
 #endif
 #ifndef HF_RENDER_MIDTAIL
-#define HF_RENDER_MIDTAIL 24           // pixels per resident warp that go out in pairs before those
+#define HF_RENDER_MIDTAIL 24           // quarter tiles per resident warp that go out in pairs before those
 #endif
-#define HF_SUB (32 / HF_RENDER_TILE)    // bundles marched per pixel in hf_render_kernel: a HF_SUB_X x HF_SUB_Y split of the jitter square
-#if HF_RENDER_TILE == 4
-#define HF_SUB_X 4
-#define HF_SUB_Y 2
-#elif HF_RENDER_TILE == 8
-#define HF_SUB_X 2
-#define HF_SUB_Y 2
-#elif HF_RENDER_TILE == 2
-#define HF_SUB_X 4
-#define HF_SUB_Y 4
-#elif HF_RENDER_TILE == 16
-#define HF_SUB_X 2
-#define HF_SUB_Y 1
-#elif HF_RENDER_TILE == 32
-#define HF_SUB_X 1
-#define HF_SUB_Y 1
-#else
+#if HF_RENDER_TILE != 2 && HF_RENDER_TILE != 4 && HF_RENDER_TILE != 8 && HF_RENDER_TILE != 16 && HF_RENDER_TILE != 32
 #error "HF_RENDER_TILE must be 2, 4, 8, 16 or 32"
 #endif
 
@@ -357,14 +343,20 @@ hf_render_kernel(const __grid_constant__ HfParams P, const HfLaunchInfo li, cons
     const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
     const uint32_t spp = A.cam.spp;
     const uint32_t rounds = (spp + 31u) >> 5;
-    // closing phases of the schedule: the last HF_RENDER_TAIL pixels per resident warp go out one at a time and the
-    // HF_RENDER_MIDTAIL pixels per warp before them in pairs, so that every phase outlasts the slowest tile of the one before
+    uint32_t seg = 32u;                                    // lanes per pixel in a round, pixels per round (phase C)
+    while (seg > 1u && (seg >> 1) >= spp) seg >>= 1;
+    const uint32_t ppr = 32u / seg;
+    // Tile sizes in pixels: a full tile is HF_RENDER_TILE rounds of rays (HF_RENDER_TILE pixels at >= 32 spp, HF_RENDER_TILE * ppr below,
+    // 32 at most: one pixel per marching lane), the closing phases hand out half and quarter tiles.
+    const unsigned u4 = min((unsigned) HF_RENDER_TILE * ppr, 32u), u2 = max(u4 / 2u, 1u), u1 = max(u4 / 4u, 1u);
+    // closing phases of the schedule: the last HF_RENDER_TAIL quarter tiles per resident warp go out one at a time and the
+    // HF_RENDER_MIDTAIL quarter tiles per warp before them in pairs, so that every phase outlasts the slowest tile of the one before
     // (a pixel whose rays skim down a slope takes ~0.2 ms, and such pixels are neighbours) whatever the size of the pixel list
     const size_t nwarps = (size_t) gridDim.x * (HF_BLOCK / 32);
-    const size_t tailpx = min(A.npix, nwarps * HF_RENDER_TAIL);
-    const size_t midpx = min(A.npix - tailpx, nwarps * HF_RENDER_MIDTAIL);
-    const size_t nbig = (A.npix - tailpx - midpx) / HF_RENDER_TILE, rest0 = nbig * HF_RENDER_TILE;
-    const size_t npair = (A.npix - tailpx - rest0) / 2, rest1 = rest0 + npair * 2;
+    const size_t tailpx = min(A.npix, nwarps * HF_RENDER_TAIL * u1);
+    const size_t midpx = min(A.npix - tailpx, nwarps * HF_RENDER_MIDTAIL * u1);
+    const size_t nbig = (A.npix - tailpx - midpx) / u4, rest0 = nbig * u4;
+    const size_t npair = (A.npix - tailpx - rest0) / u2, rest1 = rest0 + npair * u2;
     double loss_acc = 0.0;
 
     for (;;) {
@@ -373,62 +365,76 @@ hf_render_kernel(const __grid_constant__ HfParams P, const HfLaunchInfo li, cons
         tile = __shfl_sync(FULL_MASK, tile, 0);
         size_t k0;
         unsigned cap;
-        if (tile < nbig) { k0 = (size_t) tile * HF_RENDER_TILE; cap = (unsigned) HF_RENDER_TILE; }
-        else if (tile < nbig + npair) { k0 = rest0 + (size_t) (tile - nbig) * 2; cap = 2u; }
-        else { k0 = rest1 + (size_t) (tile - nbig - npair); cap = 1u; }
+        if (tile < nbig) { k0 = (size_t) tile * u4; cap = u4; }
+        else if (tile < nbig + npair) { k0 = rest0 + (size_t) (tile - nbig) * u2; cap = u2; }
+        else { k0 = rest1 + (size_t) (tile - nbig - npair) * u1; cap = u1; }
         if (k0 >= A.npix) break;
-        // ---- phase B: all 32 lanes march: lane = pixel * HF_SUB + sub-rectangle of the pixel's jitter square (HF_SUB_X x HF_SUB_Y).
-        // A narrower bundle is marched further down the pyramid, so its samples start their own walks closer to the surface.
-        const size_t kq = k0 + lane / HF_SUB;
-        const bool have = lane / HF_SUB < cap && kq < A.npix;
+        // ---- phase B: all 32 lanes march: lane = pixel * nsub + sub-rectangle of the pixel's jitter square (sub_x x sub_y; 8 bundles
+        // per pixel when the tile has <= 4 pixels, 4 / 2 / 1 for 8 / 16 / 32 pixels). A narrower bundle is marched further down the
+        // pyramid, so its samples start their own walks closer to the surface.
+        const unsigned nsub = min(8u, 32u / cap), sub_x = nsub == 8u ? 4u : (nsub >= 2u ? 2u : 1u), sub_y = nsub / sub_x;
+        const float rsx = 1.f / (float) sub_x, rsy = 1.f / (float) sub_y;      // 1, 1/2, 1/4: exact
+        const size_t kq = k0 + lane / nsub;
+        const bool have = lane / nsub < cap && kq < A.npix;
         const uint32_t my_pid = have ? (A.pixels ? __ldg(A.pixels + kq) : (uint32_t) kq) : 0u;
         float t_enter = 0.f;
         int L_start = HF_START_LEVEL;
         if (have) {
-            const unsigned sub = lane % HF_SUB, sbx = sub % HF_SUB_X, sby = sub / HF_SUB_X;
+            const unsigned sub = lane % nsub, sbx = sub % sub_x, sby = sub / sub_x;
             float vmin;
-            const HfBeam B = hf_pixel_bundle(P, A, my_pid, vmin, (float) sbx * (1.f / HF_SUB_X), (float) (sbx + 1) * (1.f / HF_SUB_X),
-                                             (float) sby * (1.f / HF_SUB_Y), (float) (sby + 1) * (1.f / HF_SUB_Y));
+            const HfBeam B = hf_pixel_bundle(P, A, my_pid, vmin, (float) sbx * rsx, (float) (sbx + 1) * rsx, (float) sby * rsy, (float) (sby + 1) * rsy);
             t_enter = hf_beam_enter(G, B, L_start);
             if (t_enter < HF_BEAM_ALL_MISS) t_enter = t_enter * vmin * (1.f - 2e-4f);
         }
         __syncwarp();
-        // ---- phase C: pixel by pixel
+        // ---- phase C: pixel by pixel; below 32 spp several pixels share a round: `seg` lanes per pixel (spp rounded up to a power
+        // of two), 32 / seg pixels at a time, so that a 1 / 2 / 4 / 8 / 16 spp image still fills the warp
         const unsigned npx = (unsigned) min((size_t) cap, A.npix - k0);
-        for (unsigned j = 0; j < npx; ++j) {
-            const uint32_t pid = __shfl_sync(FULL_MASK, my_pid, j * HF_SUB);
+        for (unsigned j0 = 0; j0 < npx; j0 += ppr) {
+            const unsigned j = j0 + lane / seg;
+            const bool pix_ok = j < npx;
+            const unsigned jj = pix_ok ? j : j0;
+            const unsigned sl = lane & (seg - 1u);                               // this lane's sample slot within its pixel
+            const unsigned segmask = seg == 32u ? FULL_MASK : (((1u << seg) - 1u) << (lane & ~(seg - 1u)));
+            const uint32_t pid = __shfl_sync(FULL_MASK, my_pid, jj * nsub);
             const uint32_t px = pid % A.cam.width, py = pid / A.cam.width;       // once per pixel, not per sample
             float acc = 0.f;
             for (uint32_t r = 0; r < rounds; ++r) {
-                const uint32_t s = r * 32u + lane;
+                const uint32_t s = r * 32u + sl;
+                const bool on = pix_ok && s < spp;
                 uint32_t prim = HF_NO_PRIM;
                 float v = 0.f;
                 float jx, jy;
-                hf_camera_jitter(A, pid, s < spp ? s : 0u, jx, jy);
+                hf_camera_jitter(A, pid, on ? s : 0u, jx, jy);
                 // the sub-rectangle this sample's jitter falls into (jx, jy in [0, 1): the products are exact)
-                const unsigned src = j * HF_SUB + min((unsigned) (jy * (float) HF_SUB_Y), (unsigned) HF_SUB_Y - 1u) * HF_SUB_X
-                                     + min((unsigned) (jx * (float) HF_SUB_X), (unsigned) HF_SUB_X - 1u);
+                const unsigned src = jj * nsub + min((unsigned) (jy * (float) sub_y), sub_y - 1u) * sub_x
+                                     + min((unsigned) (jx * (float) sub_x), sub_x - 1u);
                 const float ts = __shfl_sync(FULL_MASK, t_enter, src);
                 const int ls = __shfl_sync(FULL_MASK, L_start, src);
-                const unsigned conv = __ballot_sync(FULL_MASK, s < spp);
-                if (s < spp) v = hf_shade_sample(P, G, A, hf_camera_dir_xy(A, px, py, jx, jy), ts, ls, prim, conv);
+                const unsigned conv = __ballot_sync(FULL_MASK, on);
+                if (on) v = hf_shade_sample(P, G, A, hf_camera_dir_xy(A, px, py, jx, jy), ts, ls, prim, conv);
                 acc += v;
                 s_prim[warp][(r * 32u + lane) & (HF_RENDER_MAX_SPP - 1)] = prim;
-                if (MODE == HF_RENDER_FWD && prim_out && s < spp)
+                if (MODE == HF_RENDER_FWD && prim_out && on)
                     __stcs(prim_out + (k0 + j) * spp + s, prim);
             }
-            // pixel mean: lane partials in sample order, then a butterfly -- the same order on every run
+            // pixel mean: lane partials in sample order, then a butterfly over the pixel's lanes -- the same order on every run,
+            // and the same sums as a 32-lane butterfly whose other lanes hold +0
             #pragma unroll
-            for (int sft = 16; sft > 0; sft >>= 1) acc += __shfl_xor_sync(FULL_MASK, acc, sft);
+            for (int sft = 16; sft > 0; sft >>= 1) {
+                const float other = __shfl_xor_sync(FULL_MASK, acc, sft);
+                if ((unsigned) sft < seg) acc += other;
+            }
             const float I = acc * A.inv_spp;
+            const bool lead = pix_ok && sl == 0u;                                // one lane per pixel reports it
             if (MODE == HF_RENDER_FWD) {
-                if (lane == 0) image[pid] = I;
+                if (lead) image[pid] = I;
                 continue;
             }
-            float a_v;                                     // adjoint of ONE sample value of this pixel
+            float a_v;                                     // adjoint of ONE sample value of this lane's pixel
             if (MODE == HF_RENDER_STEP_L2) {
                 const float diff = I - __ldg(target + pid);
-                if (lane == 0) {
+                if (lead) {
                     if (image) image[pid] = I;
                     loss_acc += (double) diff * (double) diff;
                 }
@@ -436,14 +442,15 @@ hf_render_kernel(const __grid_constant__ HfParams P, const HfLaunchInfo li, cons
             } else {
                 a_v = __ldg(adj_image + pid) * A.inv_spp;
             }
+            if (!pix_ok) a_v = 0.f;
             __syncwarp();
-            if (a_v != 0.f) {
+            if (__any_sync(FULL_MASK, a_v != 0.f)) {
                 for (uint32_t r = 0; r < rounds; ++r) {
                     const uint32_t prim = s_prim[warp][(r * 32u + lane) & (HF_RENDER_MAX_SPP - 1)];
-                    const bool lit = prim != HF_NO_PRIM;
+                    const bool lit = prim != HF_NO_PRIM && a_v != 0.f;
                     const unsigned act = __ballot_sync(FULL_MASK, lit);
                     if (lit) {
-                        const unsigned peers = __match_any_sync(act, prim);
+                        const unsigned peers = __match_any_sync(act, prim) & segmask;     // same facet AND same pixel (same a_v)
                         uint32_t i0, i1, i2; float g0, g1, g2;
                         hf_shade_adjoint(P, A, prim, a_v, i0, i1, i2, g0, g1, g2);
                         if ((peers & ((1u << lane) - 1u)) == 0u) {            // lowest lane of the group
@@ -456,7 +463,7 @@ hf_render_kernel(const __grid_constant__ HfParams P, const HfLaunchInfo li, cons
             __syncwarp();
         }
     }
-    if (MODE == HF_RENDER_STEP_L2 && loss && lane == 0 && loss_acc != 0.0) atomicAdd(loss, loss_acc * (double) A.inv_npix);
+    if (MODE == HF_RENDER_STEP_L2 && loss && loss_acc != 0.0) atomicAdd(loss, loss_acc * (double) A.inv_npix);
 }
 
 // d/d(heights) of dot(a_nw, n_w(prim)) for an arbitrary world-space adjoint a_nw of the facet normal

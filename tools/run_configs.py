@@ -107,11 +107,12 @@ def main():
         shape_modes("C4 16384^2 fBm (1 GiB), grazing camera, 2048^2 x 8 spp primary", shape, o, d, a.reps)
         del o, d
         cam = hfb200.perspective_camera(cam0["origin"], cam0["target"], cam0["up"], cam0["fov"], 2048, 2048, 8, seed=4)
-        light = hfb200.directional_light((0.3, 0.2, 1.0), shadow_rays=True)
         img = torch.zeros((2048, 2048), device=dev)
-        ms = timed(lambda: shape.render_forward(cam, light, image=img), a.reps)
-        print(json.dumps({"case": "C4 render_forward with shadow rays (depth 1)", "primary_rays": 2048 * 2048 * 8, "render_forward_ms": ms,
-                          "primary_mrays": 2048 * 2048 * 8 / ms / 1e3}), flush=True)
+        for shadow in (False, True):
+            light = hfb200.directional_light((0.3, 0.2, 1.0), shadow_rays=shadow)
+            ms = timed(lambda: shape.render_forward(cam, light, image=img), a.reps)
+            print(json.dumps({"case": "C4 render_forward" + (" with shadow rays (depth 1)" if shadow else ", primary rays only"),
+                              "primary_rays": 2048 * 2048 * 8, "render_forward_ms": ms, "primary_mrays": 2048 * 2048 * 8 / ms / 1e3}), flush=True)
         del shape, img
         torch.cuda.empty_cache()
 
