@@ -501,14 +501,18 @@ hf_render_path_kernel(const __grid_constant__ HfParams P, const HfLaunchInfo li,
     hf_stage_pyramid(P, li, G);
     const unsigned lane = threadIdx.x & 31u;
     const uint32_t spp = A.cam.spp, rounds = (spp + 31u) >> 5;
-    const size_t ntiles = (A.npix + HF_RENDER_TILE - 1) / HF_RENDER_TILE;
+    uint32_t seg = 32u;                                    // as in hf_render_kernel: lanes per pixel, pixels per round, pixels per tile
+    while (seg > 1u && (seg >> 1) >= spp) seg >>= 1;
+    const uint32_t ppr = 32u / seg;
+    const unsigned T = min((unsigned) HF_RENDER_TILE * ppr, 32u);
+    const size_t ntiles = (A.npix + T - 1) / T;
     for (;;) {
         unsigned long long tile = 0;
         if (lane == 0) tile = atomicAdd(sched, 1ull);
         tile = __shfl_sync(FULL_MASK, tile, 0);
         if (tile >= ntiles) break;
-        const size_t kq = (size_t) tile * HF_RENDER_TILE + lane;
-        const bool have = lane < HF_RENDER_TILE && kq < A.npix;
+        const size_t kq = (size_t) tile * T + lane;
+        const bool have = lane < T && kq < A.npix;
         const uint32_t my_pid = have ? (A.pixels ? __ldg(A.pixels + kq) : (uint32_t) kq) : 0u;
         float t_enter = 0.f;
         int L_start = HF_START_LEVEL;
@@ -519,18 +523,21 @@ hf_render_path_kernel(const __grid_constant__ HfParams P, const HfLaunchInfo li,
             if (t_enter < HF_BEAM_ALL_MISS) t_enter = t_enter * vmin * (1.f - 2e-4f);
         }
         __syncwarp();
-        const unsigned npx = (unsigned) min((size_t) HF_RENDER_TILE, A.npix - (size_t) tile * HF_RENDER_TILE);
-        for (unsigned j = 0; j < npx; ++j) {
-            const uint32_t pid = __shfl_sync(FULL_MASK, my_pid, j);
-            const float ts = __shfl_sync(FULL_MASK, t_enter, j);
-            const int ls = __shfl_sync(FULL_MASK, L_start, j);
-            const float a_v = BWD ? __ldg(adj_image + pid) * A.inv_spp : 0.f;
+        const unsigned npx = (unsigned) min((size_t) T, A.npix - (size_t) tile * T);
+        for (unsigned j0 = 0; j0 < npx; j0 += ppr) {
+            const unsigned j = j0 + lane / seg;
+            const bool pix_ok = j < npx;
+            const unsigned jj = pix_ok ? j : j0;
+            const uint32_t pid = __shfl_sync(FULL_MASK, my_pid, jj);
+            const float ts = __shfl_sync(FULL_MASK, t_enter, jj);
+            const int ls = __shfl_sync(FULL_MASK, L_start, jj);
+            const float a_v = BWD && pix_ok ? __ldg(adj_image + pid) * A.inv_spp : 0.f;
             float acc = 0.f;
             for (uint32_t r = 0; r < rounds; ++r) {
-                const uint32_t s = r * 32u + lane;
+                const uint32_t s = r * 32u + (lane & (seg - 1u));
                 HfVertex V[HF_MAX_DEPTH];
                 int nv = 0;
-                if (s < spp) acc += hf_path_sample(P, G, A, hf_camera_dir(A, pid, s), ts, ls, pid, s, V, nv);
+                if (pix_ok && s < spp) acc += hf_path_sample(P, G, A, hf_camera_dir(A, pid, s), ts, ls, pid, s, V, nv);
                 if (BWD) {
                     // radiance arriving at vertex k from the later vertices, back to front: Lo_k = ld_k + albedo * Lo_{k+1}
                     float lo_next[HF_MAX_DEPTH];
@@ -559,8 +566,11 @@ hf_render_path_kernel(const __grid_constant__ HfParams P, const HfLaunchInfo li,
             }
             if (!BWD) {
                 #pragma unroll
-                for (int sft = 16; sft > 0; sft >>= 1) acc += __shfl_xor_sync(FULL_MASK, acc, sft);
-                if (lane == 0) image[pid] = acc * A.inv_spp;
+                for (int sft = 16; sft > 0; sft >>= 1) {
+                    const float other = __shfl_xor_sync(FULL_MASK, acc, sft);
+                    if ((unsigned) sft < seg) acc += other;
+                }
+                if (pix_ok && (lane & (seg - 1u)) == 0u) image[pid] = acc * A.inv_spp;
             }
         }
     }

@@ -51,7 +51,8 @@ def test_generated_rays_bit_exact(hf, oracle):
 
 
 @pytest.mark.parametrize("spp,shadow,xf,flip", [(1, False, None, False), (16, False, None, False), (64, True, None, False),
-                                                (100, True, "tw", False), (33, False, "tw", True), (256, False, None, False)])
+                                                (100, True, "tw", False), (33, False, "tw", True), (256, False, None, False),
+                                                (5, True, "tw", False), (12, False, None, False), (8, True, None, True)])
 def test_forward_image_and_prims(hf, oracle, spp, shadow, xf, flip):
     g, c = _scene(hf, oracle, to_world=TW if xf else None, flip=flip, kind="noise" if shadow else "smooth", mh=0.5 if shadow else 0.3)
     cam = _cam(hf, spp=spp, origin=(0.3, -2.5, -1.8) if flip else (0.3, -2.5, 1.8))     # flipped normals face a camera below the sheet
@@ -71,7 +72,7 @@ def test_forward_image_and_prims(hf, oracle, spp, shadow, xf, flip):
             assert (p2 != 0xFFFFFFFF).sum() > (rprim != 0xFFFFFFFF).sum()
 
 
-@pytest.mark.parametrize("spp,shadow,xf", [(16, False, None), (64, True, "tw"), (40, False, "tw")])
+@pytest.mark.parametrize("spp,shadow,xf", [(16, False, None), (64, True, "tw"), (40, False, "tw"), (12, True, None), (2, False, "tw")])
 def test_backward_matches_oracle_fp64(hf, oracle, spp, shadow, xf):
     g, c = _scene(hf, oracle, to_world=TW if xf else None)
     cam = _cam(hf, spp=spp)
@@ -96,9 +97,10 @@ def test_backward_matches_oracle_fp64(hf, oracle, spp, shadow, xf):
         assert np.allclose(ga[big], ref[big], rtol=2e-3) and np.allclose(gb[big], ref[big], rtol=2e-3)
 
 
-def test_fused_l2_step_equals_forward_loss_backward(hf, oracle):
+@pytest.mark.parametrize("spp", [64, 8, 3])          # below 32 spp several pixels share a warp round
+def test_fused_l2_step_equals_forward_loss_backward(hf, oracle, spp):
     g, c = _scene(hf, oracle)
-    cam = _cam(hf, spp=64)
+    cam = _cam(hf, spp=spp)
     light = hf.directional_light((0.6, 0.2, 0.5))
     npix = 48 * 40
     g2, _ = _scene(hf, oracle, seed=11)                      # another field renders the target
@@ -173,7 +175,8 @@ def test_render_error_behaviour(hf, oracle):
 
 
 # ---- path tracing -------------------------------------------------------------------------------
-@pytest.mark.parametrize("depth,shadow,xf,spp", [(2, False, None, 16), (3, True, None, 32), (3, True, "tw", 40), (4, False, None, 8)])
+@pytest.mark.parametrize("depth,shadow,xf,spp", [(2, False, None, 16), (3, True, None, 32), (3, True, "tw", 40), (4, False, None, 8),
+                                                 (2, True, None, 12), (3, False, "tw", 1)])
 def test_path_forward_and_backward(hf, oracle, depth, shadow, xf, spp):
     """Radiance per pixel within 1e-5 relative of the oracle (fp32 sums; the bounce directions go through the same double-precision
     sincos on both sides), height gradient within 1e-4 relative L2 of the oracle's fp64 PRB adjoint."""
