@@ -123,12 +123,15 @@ __device__ __forceinline__ bool hf_trace(const HfParams &P, const HfGrid &G, f3 
     return hit;
 }
 
+#ifndef HF_SHADOW_START_LEVEL
+#define HF_SHADOW_START_LEVEL 2        // visibility rays start ON the surface: every level above overlaps at the origin anyway
+#endif
 // any hit (Shape::ray_test): the walk's first hit cell decides
 __device__ __forceinline__ bool hf_occluded(const HfParams &P, const HfGrid &G, f3 o, f3 d, float maxt) {
     HfWalk w;
     HfCand c;
     float t, u, v; uint32_t prim;
-    if (hf_walk_init(G, o.x, o.y, o.z, d.x, d.y, d.z, maxt, w))
+    if (hf_walk_init(G, o.x, o.y, o.z, d.x, d.y, d.z, maxt, w, 0.f, HF_SHADOW_START_LEVEL, true))
         while (hf_walk_next(G, w, c))
             if (cell_intersect(P, c.cx, c.cy, c.z00, c.z10, c.z01, c.z11, o, d, maxt, t, u, v, prim)) return true;
     return false;

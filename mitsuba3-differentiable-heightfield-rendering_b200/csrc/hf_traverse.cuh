@@ -137,7 +137,7 @@ HF_HD int hf_msb(unsigned v) {                     // index of the highest set b
 // t_start / L_start: the walk may begin at a ray parameter > 0 and at a finer level when the caller knows that the ray
 // cannot touch the surface before t_start (hf_beam_enter below); t_start = 0, L_start = HF_START_LEVEL is the plain walk.
 HF_HD bool hf_walk_init(const HfGrid &G, float ox, float oy, float oz, float dx, float dy, float dz, float maxt, HfWalk &w,
-                        float t_start = 0.f, int L_start = HF_START_LEVEL) {
+                        float t_start = 0.f, int L_start = HF_START_LEVEL, bool force_level = false) {
     w.alive = false;
     if (dx == 0.f && dy == 0.f && dz == 0.f) return false;
     if (!(maxt >= 0.f)) return false;
@@ -201,7 +201,8 @@ HF_HD bool hf_walk_init(const HfGrid &G, float ox, float oy, float oz, float dx,
         w.ogxb = ogx - ex; w.ogyb = ogy - ey;
         w.ix = ix ^ w.xm; w.iy = iy ^ w.ym;
     }
-    w.L = hf_imin(G.QLtop, late ? L_start : HF_START_LEVEL);
+    // force_level: the caller knows the ray starts next to the surface (a visibility ray leaving a hit point): start low and climb
+    w.L = hf_imin(G.QLtop, (late || force_level) ? L_start : HF_START_LEVEL);
 #if HF_EVEN_LEVELS
     w.L &= ~1;
 #endif
