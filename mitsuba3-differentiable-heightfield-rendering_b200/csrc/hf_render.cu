@@ -333,7 +333,8 @@ __device__ __forceinline__ HfBeam hf_pixel_bundle(const HfParams &P, const HfRen
 // ---- the render kernel ----------------------------------------------------------------------------------------------
 enum { HF_RENDER_FWD = 0, HF_RENDER_STEP_L2 = 1, HF_RENDER_BWD = 2 };
 
-template <int MODE>
+// LOW: the image has fewer than 32 spp (several pixels per round, tiles of up to 32 pixels); otherwise the packing is constant-folded
+template <int MODE, bool LOW>
 __global__ void __launch_bounds__(HF_BLOCK, 3)
 hf_render_kernel(const __grid_constant__ HfParams P, const HfLaunchInfo li, const __grid_constant__ HfRenderArgs A,
                  float *__restrict__ image, uint32_t *__restrict__ prim_out, const float *__restrict__ target,
@@ -347,7 +348,7 @@ hf_render_kernel(const __grid_constant__ HfParams P, const HfLaunchInfo li, cons
     const uint32_t spp = A.cam.spp;
     const uint32_t rounds = (spp + 31u) >> 5;
     uint32_t seg = 32u;                                    // lanes per pixel in a round, pixels per round (phase C)
-    while (seg > 1u && (seg >> 1) >= spp) seg >>= 1;
+    if (LOW) while (seg > 1u && (seg >> 1) >= spp) seg >>= 1;
     const uint32_t ppr = 32u / seg;
     // Tile sizes in pixels: a full tile is HF_RENDER_TILE rounds of rays (HF_RENDER_TILE pixels at >= 32 spp, HF_RENDER_TILE * ppr below,
     // 32 at most: one pixel per marching lane), the closing phases hand out half and quarter tiles.
@@ -375,7 +376,7 @@ hf_render_kernel(const __grid_constant__ HfParams P, const HfLaunchInfo li, cons
         // ---- phase B: all 32 lanes march: lane = pixel * nsub + sub-rectangle of the pixel's jitter square (sub_x x sub_y; 8 bundles
         // per pixel when the tile has <= 4 pixels, 4 / 2 / 1 for 8 / 16 / 32 pixels). A narrower bundle is marched further down the
         // pyramid, so its samples start their own walks closer to the surface.
-        const unsigned nsub = min(8u, 32u / cap), sub_x = nsub == 8u ? 4u : (nsub >= 2u ? 2u : 1u), sub_y = nsub / sub_x;
+        const unsigned nsub = LOW ? min(8u, 32u / cap) : 8u, sub_x = nsub == 8u ? 4u : (nsub >= 2u ? 2u : 1u), sub_y = nsub / sub_x;
         const float rsx = 1.f / (float) sub_x, rsy = 1.f / (float) sub_y;      // 1, 1/2, 1/4: exact
         const size_t kq = k0 + lane / nsub;
         const bool have = lane / nsub < cap && kq < A.npix;
@@ -690,12 +691,17 @@ cudaError_t hf_launch_render(const HfParams &P, const HfLaunchInfo &li, int mode
             return cudaErrorInvalidValue;
         return cudaGetLastError();
     }
-    if (mode == HF_RENDER_FWD)
-        hf_render_kernel<HF_RENDER_FWD><<<grid, HF_BLOCK, smem, s>>>(P, li, A, d_image, d_prim, nullptr, nullptr, nullptr, nullptr, d_sched);
-    else if (mode == HF_RENDER_STEP_L2)
-        hf_render_kernel<HF_RENDER_STEP_L2><<<grid, HF_BLOCK, smem, s>>>(P, li, A, d_image, nullptr, d_target, nullptr, d_grad, d_loss, d_sched);
-    else
-        hf_render_kernel<HF_RENDER_BWD><<<grid, HF_BLOCK, smem, s>>>(P, li, A, nullptr, nullptr, nullptr, d_adj_image, d_grad, nullptr, d_sched);
+    const bool low = cam.spp < 32u;
+    if (mode == HF_RENDER_FWD) {
+        if (low) hf_render_kernel<HF_RENDER_FWD, true><<<grid, HF_BLOCK, smem, s>>>(P, li, A, d_image, d_prim, nullptr, nullptr, nullptr, nullptr, d_sched);
+        else hf_render_kernel<HF_RENDER_FWD, false><<<grid, HF_BLOCK, smem, s>>>(P, li, A, d_image, d_prim, nullptr, nullptr, nullptr, nullptr, d_sched);
+    } else if (mode == HF_RENDER_STEP_L2) {
+        if (low) hf_render_kernel<HF_RENDER_STEP_L2, true><<<grid, HF_BLOCK, smem, s>>>(P, li, A, d_image, nullptr, d_target, nullptr, d_grad, d_loss, d_sched);
+        else hf_render_kernel<HF_RENDER_STEP_L2, false><<<grid, HF_BLOCK, smem, s>>>(P, li, A, d_image, nullptr, d_target, nullptr, d_grad, d_loss, d_sched);
+    } else {
+        if (low) hf_render_kernel<HF_RENDER_BWD, true><<<grid, HF_BLOCK, smem, s>>>(P, li, A, nullptr, nullptr, nullptr, d_adj_image, d_grad, nullptr, d_sched);
+        else hf_render_kernel<HF_RENDER_BWD, false><<<grid, HF_BLOCK, smem, s>>>(P, li, A, nullptr, nullptr, nullptr, d_adj_image, d_grad, nullptr, d_sched);
+    }
     return cudaGetLastError();
 }
 
