@@ -28,13 +28,14 @@
 #define HF_Q_EMPTY 0x0000FFFFu          // lo = 65535, hi = 0
 #define HF_Q_MAX_LEVELS 26
 
-struct HfQuant { float zb, qs; };
+struct HfQuant { float zb, qs, rqs; };   // rqs = 1 / qs: the encoder's first guess (the verify loops below make it exact)
 
 HF_QHD HfQuant hf_quant_make(float top_min, float top_max) {
     HfQuant q;
     float qs = (top_max - top_min) * (1.0f / 65280.0f);       // 255 codes of headroom split below / above the range
     if (!(qs > 1e-30f) || !(qs < 1e30f)) qs = 1e-30f;         // flat (or degenerate) field: every code decodes to ~top_min
     q.qs = qs;
+    q.rqs = 1.0f / qs;
     q.zb = top_min - 128.0f * qs;
     return q;
 }
@@ -42,13 +43,13 @@ HF_QHD HfQuant hf_quant_make(float top_min, float top_max) {
 HF_QHD float hf_quant_decode(uint32_t code, float qs, float zb) { return fmaf((float) code, qs, zb); }
 
 HF_QHD uint32_t hf_quant_lo(float mn, HfQuant q) {            // largest convenient code with decode(code) <= mn
-    float f = floorf((mn - q.zb) / q.qs) - 1.0f;
+    float f = floorf((mn - q.zb) * q.rqs) - 1.0f;
     int c = !(f > 0.f) ? 0 : (f > 65535.f ? 65535 : (int) f);
     while (c > 0 && !(hf_quant_decode((uint32_t) c, q.qs, q.zb) <= mn)) --c;
     return (uint32_t) c;
 }
 HF_QHD uint32_t hf_quant_hi(float mx, HfQuant q) {            // smallest convenient code with decode(code) >= mx
-    float f = ceilf((mx - q.zb) / q.qs) + 1.0f;
+    float f = ceilf((mx - q.zb) * q.rqs) + 1.0f;
     int c = !(f > 0.f) ? 0 : (f > 65535.f ? 65535 : (int) f);
     while (c < 65535 && !(hf_quant_decode((uint32_t) c, q.qs, q.zb) >= mx)) ++c;
     return (uint32_t) c;
