@@ -141,7 +141,7 @@ def cpu_sample(a, heights_np, n_sample):
     stride = max(1, npix // want_pix)
     pix = torch.arange(0, npix, stride, dtype=torch.int64)[:want_pix]
     o, d = wl.camera_rays(cam["origin"], cam["target"], cam["up"], cam["fov"], a.image, a.image, a.spp, seed=0, pixels=pix)
-    adj = wl.hashed_adjoints(o.shape[1], seed=1)
+    adj = wl.hashed_adjoints(o.shape[1], seed=1, ids=wl.global_ray_ids(pix, a.spp))
     return o, d, adj
 
 
@@ -194,6 +194,46 @@ def main_reference(a):
 # ---------------------------------------------------------------------------------------------------------
 # GPU arm
 # ---------------------------------------------------------------------------------------------------------
+def sharded_gradient_check(rank, world, dev, tile):
+    """N-rank path against the 1-rank path on a reduced configuration (512^2 heights, 256^2 image x 16 spp), inside the run: every
+    rank traces its image tiles, the grids are summed by hf_allreduce_grad over the SAME communicator kind the timed step uses, and
+    rank 0 compares with the grid it gets by tracing all rays alone. Returns the relative L2 difference (rank 0) or None."""
+    import torch.distributed as dist
+    import hfb200
+    from hfb200 import workloads as wl
+    hs, img, spp = 512, 256, 16
+    cam = wl.CONFIGS["C3"]["camera"]
+    h = wl.fbm_heights(hs, octaves=6, seed=0xC3, device=dev)
+
+    def grad_of(shape, pix):
+        o, d = wl.camera_rays(cam["origin"], cam["target"], cam["up"], cam["fov"], img, img, spp, seed=0, device=dev, pixels=pix)
+        ray = hfb200.Ray3f(o, d)
+        adj = wl.hashed_adjoints(o.shape[1], seed=1, device=dev, ids=wl.global_ray_ids(pix, spp))
+        si, pi = shape.ray_intersect(ray, return_prelim=True, fields=("t", "p", "n", "uv"))
+        shape.zero_grad()
+        shape.backward(ray, pi, adj)
+
+    sh = hfb200.load_dict({"type": "heightfield", "heights": h, "max_height": 0.3}, device=dev)
+    ids = [None] * world
+    dist.all_gather_object(ids, hfb200.comm_unique_id() if rank == 0 else None)
+    sh.comm_init(rank, world, ids[0])
+    grad_of(sh, wl.tile_pixels(img, img, tile, rank, world, device=dev))
+    sh.allreduce_grad()
+    torch.cuda.synchronize()
+    g_n = sh.grad.double().clone()
+    out = None
+    if rank == 0:
+        one = hfb200.load_dict({"type": "heightfield", "heights": h, "max_height": 0.3}, device=dev)
+        grad_of(one, torch.arange(img * img, dtype=torch.int64, device=dev))
+        torch.cuda.synchronize()
+        g_1 = one.grad.double()
+        out = float((g_n - g_1).norm() / g_1.norm())
+        del one
+    del sh
+    dist.barrier()
+    return out
+
+
 def main_ours(a):
     import torch.distributed as dist
     import hfb200
@@ -221,7 +261,9 @@ def main_ours(a):
     n_local = o.shape[1]
     n_total = a.image * a.image * a.spp if shard_of <= 1 else n_local
     ray = hfb200.Ray3f(o, d)
-    adj = wl.hashed_adjoints(n_local, seed=1 + rank, device=dev)
+    # adjoints keyed by the GLOBAL ray id (pixel * spp + sample): every N solves the same problem, so the gradient grids (and their
+    # checksums in `extras`) of the 1 / 2 / 4 / 8-GPU runs are comparable
+    adj = wl.hashed_adjoints(n_local, seed=1, device=dev, ids=wl.global_ray_ids(pix, a.spp))
     adj_c = shape.prepare_adjoints(adj, n_local)
     fields = ("t", "p", "n", "uv")
     si = hfb200.SurfaceInteraction3f(n_local, dev, shape, fields)
@@ -233,6 +275,8 @@ def main_ours(a):
         ids = [None] * world
         dist.all_gather_object(ids, hfb200.comm_unique_id() if rank == 0 else None)
         shape.comm_init(rank, world, ids[0])
+
+    shard_check = sharded_gradient_check(rank, world, dev, a.tile) if world > 1 else None
 
     ev = lambda: torch.cuda.Event(enable_timing=True)
     k_fwd, k_bwd = [], []
@@ -385,6 +429,8 @@ def main_ours(a):
                    "full_step_mrays": n_total / (ms_full * 1e-3) / 1e6, "full_step_ms": ms_full,
                    "full_step": "zero_grad + intersect/SI + backward + allreduce + Adam + pyramid rebuild",
                    "allreduce_ms": ms_allreduce,
+                   "grad_rel_l2_vs_single_rank": shard_check,
+                   "grad_rel_l2_vs_single_rank_what": "N-rank tile shards + hf_allreduce_grad vs one rank tracing every ray, 512^2 heights, 256^2 x 16 spp, in this run",
                    "grad_abs_sum": grad_checksum, "mean_nodes_per_ray": n_node, "mean_leaves_per_ray": n_leaf},
     }
     # SURVEY.md 8(d) "full step" byte model: rays x (B_trav + 16 + 12) + texels x (4 + 28 + 4 + 8/3) + pixels x 36

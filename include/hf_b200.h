@@ -30,7 +30,7 @@
 extern "C" {
 #endif
 
-#define HF_B200_ABI_VERSION 2
+#define HF_B200_ABI_VERSION 3
 
 typedef enum {
     HF_OK = 0,
@@ -101,9 +101,10 @@ typedef struct {
     const float *dpdv_x, *dpdv_y, *dpdv_z;
 } hf_si_adj;
 
-/* src/python/python/ad/optimizers.py:263-302 */
+/* src/python/python/ad/optimizers.py:263-302. The hyper-parameters are doubles because they are Python floats there:
+ * (1 - beta) and the bias correction are evaluated in double before they become fp32 (0.001f, not 1 - 0.999f). */
 typedef struct {
-    float lr, beta1, beta2, epsilon;
+    double lr, beta1, beta2, epsilon;
     int32_t mask_updates;
 } hf_adam;
 

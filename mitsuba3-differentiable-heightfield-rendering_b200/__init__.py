@@ -90,7 +90,7 @@ class _Adj(C.Structure):
 
 
 class _Adam(C.Structure):
-    _fields_ = [("lr", C.c_float), ("beta1", C.c_float), ("beta2", C.c_float), ("epsilon", C.c_float),
+    _fields_ = [("lr", C.c_double), ("beta1", C.c_double), ("beta2", C.c_double), ("epsilon", C.c_double),
                 ("mask_updates", C.c_int32)]
 
 

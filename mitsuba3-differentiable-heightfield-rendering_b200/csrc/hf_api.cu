@@ -95,20 +95,36 @@ static int nccl_load() {
 // ------------------------------------------------------------------------------------------
 // context
 // ------------------------------------------------------------------------------------------
-#define HF_SCHED_SLOTS 256            // every launch of a self-scheduling kernel gets its own counter (launches on different streams overlap)
+#define HF_SCHED_SLOTS 256            // every eager launch of a self-scheduling kernel gets its own counter (launches on different streams overlap)
+#define HF_SCHED_CAPTURE_SLOTS 1024   // launches recorded into a CUDA graph get a counter of their own for good: a graph bakes the pointer in
+                                      // and may replay beside eager launches long after the eager ring has wrapped around
 #define HF_TOP_NODE_CAP 1366          // (32^2 + 16^2 + ... + 1) rounded up to even: 10.9 KB of shared memory
 #ifndef HF_HOST_CHUNK_LOG2
 #define HF_HOST_CHUNK_LOG2 21
 #endif
 #define HF_HOST_CHUNK (size_t(1) << HF_HOST_CHUNK_LOG2)
 #ifndef HF_HOST_SLOTS
-#define HF_HOST_SLOTS 2
+#define HF_HOST_SLOTS 3
 #endif
-#define HF_SLAB_FLOATS 53             // rays 7 + prelim 4 + si 26 + adj 15 + active mask
+// staging slab of one chunk, in fields of HF_HOST_CHUNK floats: rays | prelim | surface interaction | adjoints | active mask.
+// The field counts are DERIVED from the ABI structs, so a field added to hf_si / hf_si_adj cannot be left without a slot.
+#define RAY_NFIELDS 7
+#define PRE_NFIELDS 4
+#define SI_NFIELDS ((int) (sizeof(hf_si) / sizeof(float *)))
+#define ADJ_NFIELDS ((int) (sizeof(hf_si_adj) / sizeof(const float *)))
+static_assert(sizeof(hf_si) == 27 * sizeof(float *), "hf_si: 27 float* members (t, p3, n3, uv2, dpdu3, dpdv3, shn3, shs3, sht3, wi3)");
+static_assert(sizeof(hf_si_adj) == 15 * sizeof(const float *), "hf_si_adj: 15 members");
+static_assert(sizeof(hf_prelim) == PRE_NFIELDS * sizeof(void *), "hf_prelim: 4 members");
+#define SLAB_RAY 0
+#define SLAB_PRE (SLAB_RAY + RAY_NFIELDS)
+#define SLAB_SI (SLAB_PRE + PRE_NFIELDS)
+#define SLAB_ADJ (SLAB_SI + SI_NFIELDS)
+#define SLAB_ACTIVE (SLAB_ADJ + ADJ_NFIELDS)
+#define HF_SLAB_FLOATS (SLAB_ACTIVE + 1)
 
 struct HostSlot {
-    cudaStream_t stream = nullptr;
     float *slab = nullptr;            // HF_HOST_CHUNK * HF_SLAB_FLOATS floats
+    cudaEvent_t in_done = nullptr, k_done = nullptr, out_done = nullptr;   // H2D landed / kernels finished / D2H landed
 };
 
 struct hf_ctx {
@@ -125,15 +141,18 @@ struct hf_ctx {
     uint32_t *d_qpyr = nullptr;      // quantised pyramid (hf_qpyr.h)
     size_t qpyr_nodes = 0;
     unsigned long long *d_counters = nullptr;     // [0..3] traversal statistics, [8..8+HF_SCHED_SLOTS) tile counters of the persistent kernels
-    unsigned sched_next = 0;
+    unsigned sched_next = 0, sched_capture_next = 0;
     float *d_scratch = nullptr;       // two images (path-traced L2 step)
     size_t scratch_bytes = 0;
     bool have_heights = false, accel_valid = false;
     int grad_enabled = 1;
     int adam_t = 0;
     hf_nccl_comm comm = nullptr;
-    int nranks = 1;
+    int nranks = 1, rank = 0;
     HostSlot slots[HF_HOST_SLOTS];
+    cudaStream_t s_in = nullptr, s_k = nullptr, s_out = nullptr;   // host pipeline: one stream per copy engine + one for the kernels
+    cudaEvent_t ev_entry = nullptr;
+    cudaEvent_t ev_accel = nullptr;   // recorded behind the last pyramid build (hf_bbox waits for it instead of the whole device)
     bool slots_ready = false;
 };
 
@@ -168,7 +187,21 @@ static int set_transform(hf_ctx *c, const float to_world[12], const float *to_ob
     return HF_OK;
 }
 
-static unsigned long long *next_sched(hf_ctx *c) { return c->d_counters + 8 + (c->sched_next++ % HF_SCHED_SLOTS); }
+// Tile counter of one launch of a self-scheduling (persistent) kernel; the launcher zeroes it in stream order. Eager launches take
+// the next slot of a ring (two launches that overlap on different streams are never 256 launches apart). A launch that is being
+// RECORDED into a CUDA graph gets a slot from a pool that is never handed out again: the graph keeps the pointer for its lifetime
+// and may replay at any time beside eager launches of the same context.
+static unsigned long long *next_sched(hf_ctx *c, cudaStream_t s) {
+    cudaStreamCaptureStatus st = cudaStreamCaptureStatusNone;
+    if (cudaStreamIsCapturing(s, &st) != cudaSuccess) { cudaGetLastError(); st = cudaStreamCaptureStatusNone; }
+    if (st == cudaStreamCaptureStatusActive) {
+        if (c->sched_capture_next >= HF_SCHED_CAPTURE_SLOTS) return nullptr;
+        return c->d_counters + 8 + HF_SCHED_SLOTS + c->sched_capture_next++;
+    }
+    return c->d_counters + 8 + (c->sched_next++ % HF_SCHED_SLOTS);
+}
+#define SCHED(c, s) ({ unsigned long long *p_ = next_sched((c), (cudaStream_t) (s)); \
+    if (!p_) return fail(HF_ERR_STATE, "this context has recorded more than %d self-scheduling launches into CUDA graphs", HF_SCHED_CAPTURE_SLOTS); p_; })
 
 static void layout_pyramid(hf_ctx *c) {
     HfParams &P = c->P;
@@ -199,6 +232,19 @@ static void layout_pyramid(hf_ctx *c) {
     c->li.top_nodes = (int) top;
     c->li.top_off = P.lvl_off[Ls];
     c->li.num_sms = c->num_sms;
+    {   // coarse even levels of the quantised pyramid that fit the shared-memory budget of a walk kernel, finest first
+        const HfQLayout q = hf_qlayout(P.NX, P.NY);
+        int lo = (q.Ltop & ~1) + 2;
+        size_t bytes = 0;
+        for (int l = q.Ltop & ~1; l >= 0; l -= 2) {
+            const size_t b = (((size_t) q.pitch[l] * q.rows[l] + 3) & ~size_t(3)) * sizeof(uint32_t);
+            if (bytes + b > HF_QSTAGE_CAP) break;
+            bytes += b; lo = l;
+        }
+        const char *e = getenv("HF_B200_QSTAGE");
+        if (!HF_STAGE_Q || (e && e[0] == '0')) { lo = q.Ltop + 2; bytes = 0; }
+        c->li.q_stage_level = lo; c->li.q_stage_bytes = (int) bytes;
+    }
     {   // HF_B200_BUNDLES=1 selects the bundled kernel (hf_intersect_beam_kernel). Measured on C3 (profiles/): it removes 40 % of
         // the walk's instructions but pays them back in the shuffle reductions that find the bundle bounds of a generic ray
         // array, so the plain kernel stays the default for ray-array entry points; the fused render step, which knows its
@@ -238,6 +284,7 @@ extern "C" int hf_create(hf_ctx **out, const hf_desc *desc) {
     P.rw = 1.0f / (float) P.NX; P.rh = 1.0f / (float) P.NY;
     P.x0 = (float) (-(P.W - 1)) * P.rw; P.y0 = (float) (-(P.H - 1)) * P.rh;
     P.sgx = 0.5f * (float) P.NX; P.sgy = 0.5f * (float) P.NY;
+    { const HfDivMagic dm = hf_divmagic((uint32_t) P.NX); P.nx_magic = dm.m; P.nx_shift = dm.s; }
     int rc = set_transform(c, desc->to_world, desc->has_to_object ? desc->to_object : nullptr);
     if (rc) { delete c; return rc; }
     layout_pyramid(c);
@@ -246,13 +293,13 @@ extern "C" int hf_create(hf_ctx **out, const hf_desc *desc) {
     cudaError_t e1 = cudaMalloc(&c->d_heights, texels * sizeof(float));
     cudaError_t e2 = cudaMalloc(&c->d_grad, texels * sizeof(float));
     cudaError_t e3 = cudaMalloc(&c->d_pyr, c->pyr_nodes * sizeof(float2));
-    cudaError_t e4 = cudaMalloc(&c->d_counters, (8 + HF_SCHED_SLOTS) * sizeof(unsigned long long));
+    cudaError_t e4 = cudaMalloc(&c->d_counters, (8 + HF_SCHED_SLOTS + HF_SCHED_CAPTURE_SLOTS) * sizeof(unsigned long long));
     if (c->qpyr_nodes >= (size_t(1) << 32)) { hf_destroy(c); return fail(HF_ERR_INVALID, "%ux%u heightfield: padded acceleration pyramid exceeds 2^32 nodes", c->W, c->H); }
     cudaError_t e5 = cudaMalloc(&c->d_qpyr, c->qpyr_nodes * sizeof(uint32_t));
     if (e1 || e2 || e3 || e4 || e5) { hf_destroy(c); return fail(HF_ERR_CUDA, "cudaMalloc failed for a %ux%u heightfield", c->W, c->H); }
     cudaMemset(c->d_grad, 0, texels * sizeof(float));
     cudaMemset(c->d_pyr, 0, c->pyr_nodes * sizeof(float2));
-    cudaMemset(c->d_counters, 0, (8 + HF_SCHED_SLOTS) * sizeof(unsigned long long));
+    cudaMemset(c->d_counters, 0, (8 + HF_SCHED_SLOTS + HF_SCHED_CAPTURE_SLOTS) * sizeof(unsigned long long));
     P.heights = c->d_heights;
     P.pyr = c->d_pyr;
     P.qpyr = c->d_qpyr;
@@ -266,7 +313,17 @@ extern "C" int hf_destroy(hf_ctx *c) {
     if (c->comm && c->grad_reg && g_nccl.CommDeregister) g_nccl.CommDeregister(c->comm, c->grad_reg);
     if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
     if (c->grad_nccl && g_nccl.MemFree) { g_nccl.MemFree(c->d_grad); c->d_grad = nullptr; }
-    for (auto &s : c->slots) { if (s.slab) cudaFree(s.slab); if (s.stream) cudaStreamDestroy(s.stream); }
+    for (auto &s : c->slots) {
+        if (s.slab) cudaFree(s.slab);
+        if (s.in_done) cudaEventDestroy(s.in_done);
+        if (s.k_done) cudaEventDestroy(s.k_done);
+        if (s.out_done) cudaEventDestroy(s.out_done);
+    }
+    if (c->ev_entry) cudaEventDestroy(c->ev_entry);
+    if (c->ev_accel) cudaEventDestroy(c->ev_accel);
+    if (c->s_in) cudaStreamDestroy(c->s_in);
+    if (c->s_k) cudaStreamDestroy(c->s_k);
+    if (c->s_out) cudaStreamDestroy(c->s_out);
     cudaFree(c->d_heights); cudaFree(c->d_grad); cudaFree(c->d_m); cudaFree(c->d_v); cudaFree(c->d_pyr); cudaFree(c->d_qpyr); cudaFree(c->d_counters); cudaFree(c->d_scratch);
     delete c;
     return HF_OK;
@@ -327,6 +384,8 @@ extern "C" int hf_parameters_changed(hf_ctx *c, void *stream) {
     if (!c->have_heights) return fail(HF_ERR_STATE, "heights were never set");
     CU(cudaSetDevice(c->device));
     CU(hf_launch_pyramid(c->P, c->d_pyr, c->d_qpyr, (cudaStream_t) stream));
+    if (!c->ev_accel) CU(cudaEventCreateWithFlags(&c->ev_accel, cudaEventDisableTiming));
+    CU(cudaEventRecord(c->ev_accel, (cudaStream_t) stream));
     c->accel_valid = true;
     return HF_OK;
 }
@@ -363,7 +422,7 @@ extern "C" int hf_bbox(hf_ctx *c, float out[6]) {
     NEED_ACCEL(c);
     CU(cudaSetDevice(c->device));
     float2 top;
-    CU(cudaDeviceSynchronize());
+    CU(cudaEventSynchronize(c->ev_accel));      // the pyramid build this bbox derives from (whatever stream it ran on)
     CU(cudaMemcpy(&top, c->d_pyr + c->P.lvl_off[c->P.Ltop], sizeof(float2), cudaMemcpyDeviceToHost));
     const HfParams &P = c->P;
     float lo[3] = { P.x0, P.y0, top.x };
@@ -407,6 +466,7 @@ extern "C" int hf_qpyramid_level(hf_ctx *c, uint32_t level, uint32_t *levels, ui
         NEED_ACCEL(c);
         CU(cudaSetDevice(c->device));
         float2 top;
+        CU(cudaEventSynchronize(c->ev_accel));
         CU(cudaMemcpy(&top, c->d_pyr + P.lvl_off[P.Ltop], sizeof(float2), cudaMemcpyDeviceToHost));
         const HfQuant q = hf_quant_make(top.x, top.y);
         if (qs) *qs = q.qs;
@@ -447,7 +507,7 @@ extern "C" int hf_ray_intersect_preliminary(hf_ctx *c, const hf_rays *rays, cons
     NEED_ACCEL(c);
     CU(cudaSetDevice(c->device));
     hf_si none; memset(&none, 0, sizeof(none));
-    CU(hf_launch_intersect(c->P, c->li, HF_MODE_PRELIM, *rays, *out, none, nullptr, 0, n, c->d_counters, next_sched(c), (cudaStream_t) stream));
+    CU(hf_launch_intersect(c->P, c->li, HF_MODE_PRELIM, *rays, *out, none, nullptr, 0, n, c->d_counters, SCHED(c, stream), (cudaStream_t) stream));
     return HF_OK;
 }
 
@@ -459,7 +519,7 @@ extern "C" int hf_ray_intersect_preliminary_counted(hf_ctx *c, const hf_rays *ra
     NEED_ACCEL(c);
     CU(cudaSetDevice(c->device));
     hf_si none; memset(&none, 0, sizeof(none));
-    CU(hf_launch_intersect(c->P, c->li, HF_MODE_COUNTED, *rays, *out, none, nullptr, 0, n, c->d_counters, next_sched(c), (cudaStream_t) stream));
+    CU(hf_launch_intersect(c->P, c->li, HF_MODE_COUNTED, *rays, *out, none, nullptr, 0, n, c->d_counters, SCHED(c, stream), (cudaStream_t) stream));
     return HF_OK;
 }
 
@@ -485,7 +545,7 @@ extern "C" int hf_ray_test(hf_ctx *c, const hf_rays *rays, uint8_t *d_hit, size_
     CU(cudaSetDevice(c->device));
     hf_si none; memset(&none, 0, sizeof(none));
     hf_prelim nop; memset(&nop, 0, sizeof(nop));
-    CU(hf_launch_intersect(c->P, c->li, HF_MODE_TEST, *rays, nop, none, d_hit, 0, n, c->d_counters, next_sched(c), (cudaStream_t) stream));
+    CU(hf_launch_intersect(c->P, c->li, HF_MODE_TEST, *rays, nop, none, d_hit, 0, n, c->d_counters, SCHED(c, stream), (cudaStream_t) stream));
     return HF_OK;
 }
 
@@ -521,7 +581,7 @@ extern "C" int hf_ray_intersect(hf_ctx *c, const hf_rays *rays, uint32_t flags, 
     CU(cudaSetDevice(c->device));
     hf_prelim nop; memset(&nop, 0, sizeof(nop));
     CU(hf_launch_intersect(c->P, c->li, HF_MODE_FUSED_SI, *rays, prelim_out ? *prelim_out : nop, *out, nullptr, flags, n,
-                           c->d_counters, next_sched(c), (cudaStream_t) stream));
+                           c->d_counters, SCHED(c, stream), (cudaStream_t) stream));
     return HF_OK;
 }
 
@@ -558,18 +618,19 @@ extern "C" int hf_adam_step(hf_ctx *c, const hf_adam *cfg, void *stream) {
     CHECK_CTX(c);
     if (!cfg) return fail(HF_ERR_INVALID, "null Adam configuration");
     // optimizers.py:243-244
-    if (!(cfg->beta1 >= 0.f && cfg->beta1 < 1.f && cfg->beta2 >= 0.f && cfg->beta2 < 1.f && cfg->lr > 0.f && cfg->epsilon > 0.f))
+    if (!(cfg->beta1 >= 0. && cfg->beta1 < 1. && cfg->beta2 >= 0. && cfg->beta2 < 1. && cfg->lr > 0. && cfg->epsilon > 0.))
         return fail(HF_ERR_INVALID, "Adam: need 0 <= beta < 1, lr > 0, epsilon > 0");
     if (!c->have_heights) return fail(HF_ERR_STATE, "heights were never set");
     if (!c->d_m || !c->d_v) { int rc = hf_adam_reset(c, stream); if (rc) return rc; }
     CU(cudaSetDevice(c->device));
     c->adam_t += 1;
-    // optimizers.py:266-269: lr_scale in Python doubles, then an opaque fp32
-    const double b1 = (double) cfg->beta1, b2 = (double) cfg->beta2;
+    // optimizers.py:266-279. The hyper-parameters are Python floats (doubles) there: lr_scale and (1 - beta) are evaluated in double
+    // and only then become fp32 literals of the traced expression; lr is an opaque fp32 (lr_v) multiplied by the fp32 lr_scale.
+    const double b1 = cfg->beta1, b2 = cfg->beta2;
     const float lr_scale = (float) (sqrt(1.0 - pow(b2, c->adam_t)) / (1.0 - pow(b1, c->adam_t)));
-    const float lr_t = cfg->lr * lr_scale;
-    CU(hf_launch_adam(c->d_heights, c->d_grad, c->d_m, c->d_v, (size_t) c->W * c->H, lr_t, cfg->beta1, cfg->beta2,
-                      (float) (1.0 - b1), (float) (1.0 - b2), cfg->epsilon, cfg->mask_updates, c->num_sms, (cudaStream_t) stream));
+    const float lr_t = (float) cfg->lr * lr_scale;
+    CU(hf_launch_adam(c->d_heights, c->d_grad, c->d_m, c->d_v, (size_t) c->W * c->H, lr_t, (float) b1, (float) b2,
+                      (float) (1.0 - b1), (float) (1.0 - b2), (float) cfg->epsilon, cfg->mask_updates, c->num_sms, (cudaStream_t) stream));
     c->accel_valid = false;       // heights moved: the caller runs hf_parameters_changed (SceneParameters.update)
     return HF_OK;
 }
@@ -598,7 +659,7 @@ extern "C" int hf_comm_init(hf_ctx *c, int rank, int nranks, const uint8_t id_by
     hf_nccl_uid id;
     memcpy(id.internal, id_bytes, 128);
     NC(g_nccl.CommInitRank(&c->comm, nranks, id, rank));
-    c->nranks = nranks;
+    c->nranks = nranks; c->rank = rank;
     // The gradient grid is the one buffer that crosses NVLink every step. Move it into NCCL-allocated memory and register it with the
     // communicator, so that on an NVSwitch box the allreduce can run in the switch on the user buffer (NVLS) instead of being staged
     // through NCCL's own buffers. The pointer hf_grad() returns CHANGES here. HF_B200_NCCL_MEM=0 keeps the cudaMalloc buffer.
@@ -620,8 +681,14 @@ extern "C" int hf_comm_init(hf_ctx *c, int rank, int nranks, const uint8_t id_by
 
 extern "C" int hf_comm_destroy(hf_ctx *c) {
     CHECK_CTX(c);
-    if (c->comm) { NC(g_nccl.CommDestroy(c->comm)); c->comm = nullptr; }
-    c->nranks = 1;
+    if (c->comm) {
+        // the registration handle belongs to the communicator: drop it first (the buffer itself stays in ncclMemAlloc memory and is
+        // registered again by the next hf_comm_init)
+        if (c->grad_reg && g_nccl.CommDeregister) g_nccl.CommDeregister(c->comm, c->grad_reg);
+        c->grad_reg = nullptr;
+        NC(g_nccl.CommDestroy(c->comm)); c->comm = nullptr;
+    }
+    c->nranks = 1; c->rank = 0;
     return HF_OK;
 }
 
@@ -690,7 +757,7 @@ extern "C" int hf_render_forward(hf_ctx *c, const hf_camera *cam, const hf_light
     NEED_ACCEL(c);
     CU(cudaSetDevice(c->device));
     CU(hf_launch_render(c->P, c->li, 0, *cam, *light, d_pixels, npix, d_image, d_prim, nullptr, nullptr, nullptr, nullptr,
-                        next_sched(c), (cudaStream_t) stream));
+                        SCHED(c, stream), (cudaStream_t) stream));
     return HF_OK;
 }
 
@@ -710,7 +777,7 @@ extern "C" int hf_render_backward(hf_ctx *c, const hf_camera *cam, const hf_ligh
     } else {
         NEED_ACCEL(c);
         CU(hf_launch_render(c->P, c->li, 2, *cam, *light, d_pixels, npix, nullptr, nullptr, nullptr, d_adj_image, c->d_grad, nullptr,
-                            next_sched(c), (cudaStream_t) stream));
+                            SCHED(c, stream), (cudaStream_t) stream));
     }
     return HF_OK;
 }
@@ -736,14 +803,14 @@ extern "C" int hf_render_step_l2(hf_ctx *c, const hf_camera *cam, const hf_light
         }
         float *img = d_image ? d_image : c->d_scratch, *adj = c->d_scratch + (size_t) cam->width * cam->height;
         cudaStream_t st = (cudaStream_t) stream;
-        CU(hf_launch_render(c->P, c->li, 0, *cam, *light, d_pixels, npix, img, nullptr, nullptr, nullptr, nullptr, nullptr, next_sched(c), st));
+        CU(hf_launch_render(c->P, c->li, 0, *cam, *light, d_pixels, npix, img, nullptr, nullptr, nullptr, nullptr, nullptr, SCHED(c, st), st));
         CU(hf_launch_l2_adjoint(c->P, c->li, *cam, d_pixels, npix, img, d_target, adj, d_loss, st));
         if (c->grad_enabled)
-            CU(hf_launch_render(c->P, c->li, 2, *cam, *light, d_pixels, npix, nullptr, nullptr, nullptr, adj, c->d_grad, nullptr, next_sched(c), st));
+            CU(hf_launch_render(c->P, c->li, 2, *cam, *light, d_pixels, npix, nullptr, nullptr, nullptr, adj, c->d_grad, nullptr, SCHED(c, st), st));
         return HF_OK;
     }
     CU(hf_launch_render(c->P, c->li, 1, *cam, *light, d_pixels, npix, d_image, nullptr, d_target, nullptr, c->d_grad, d_loss,
-                        next_sched(c), (cudaStream_t) stream));
+                        SCHED(c, stream), (cudaStream_t) stream));
     return HF_OK;
 }
 
@@ -762,83 +829,108 @@ extern "C" int hf_host_free(void *p) {
 
 static int ensure_slots(hf_ctx *c) {
     if (c->slots_ready) return HF_OK;
+    CU(cudaStreamCreateWithFlags(&c->s_in, cudaStreamNonBlocking));
+    CU(cudaStreamCreateWithFlags(&c->s_k, cudaStreamNonBlocking));
+    CU(cudaStreamCreateWithFlags(&c->s_out, cudaStreamNonBlocking));
+    CU(cudaEventCreateWithFlags(&c->ev_entry, cudaEventDisableTiming));
     for (auto &s : c->slots) {
-        CU(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
         CU(cudaMalloc(&s.slab, HF_HOST_CHUNK * HF_SLAB_FLOATS * sizeof(float)));
+        CU(cudaEventCreateWithFlags(&s.in_done, cudaEventDisableTiming));
+        CU(cudaEventCreateWithFlags(&s.k_done, cudaEventDisableTiming));
+        CU(cudaEventCreateWithFlags(&s.out_done, cudaEventDisableTiming));
     }
     c->slots_ready = true;
     return HF_OK;
 }
 
-#define SI_NFIELDS 26
-#define ADJ_NFIELDS 15
-
+// Chunks of HF_HOST_CHUNK rays flow through HF_HOST_SLOTS device slabs on THREE streams, one per engine: all host->device copies
+// on s_in, all kernels on s_k, all device->host copies on s_out, chained per slab by events (in_done -> kernels -> k_done -> D2H ->
+// out_done -> the slab's next H2D). Both copy engines and the SMs are busy at the same time, and the step is bound by the larger
+// of the two PCIe directions (the reference's host-array caller: src/render/scene_embree.inl:261-326).
 static int host_pipeline(hf_ctx *c, const hf_rays *hr, const hf_si_adj *hadj, uint32_t flags, const hf_prelim *hpre,
                          const hf_si *hsi, float *h_grad_out, size_t n, bool backward) {
     int rc;
     if (n == 0 && !h_grad_out) return HF_OK;
     if (n > 0 && ((rc = check_rays(hr)) || (rc = check_flags(flags)))) return rc;
     if (n > 0 && hpre && (rc = check_prelim(hpre))) return rc;
-    if (backward && !hadj) return fail(HF_ERR_INVALID, "null adjoints");
-    NEED_ACCEL(c);
+    if (n > 0 && backward && !hadj) return fail(HF_ERR_INVALID, "null adjoints");
+    if (n > 0) NEED_ACCEL(c);
     CU(cudaSetDevice(c->device));
     if ((rc = ensure_slots(c))) return rc;
-    // order after whatever the caller queued on the legacy stream (heights upload, pyramid build)
-    CU(cudaDeviceSynchronize());
+    // order after whatever the caller queued on the legacy default stream (heights upload, pyramid build, zero_grad): an event
+    // there, waited for by the pipeline's streams -- no device-wide synchronisation
+    CU(cudaEventRecord(c->ev_entry, (cudaStream_t) 0));
+    CU(cudaStreamWaitEvent(c->s_in, c->ev_entry, 0));
+    CU(cudaStreamWaitEvent(c->s_k, c->ev_entry, 0));
+    CU(cudaStreamWaitEvent(c->s_out, c->ev_entry, 0));
 
-    float *const *hsi_f = reinterpret_cast<float *const *>(hsi);
-    const float *const *hadj_f = reinterpret_cast<const float *const *>(hadj);
-    const float *hray_f[7] = { hr->ox, hr->oy, hr->oz, hr->dx, hr->dy, hr->dz, hr->maxt };
+    if (n > 0) {
+        float *const *hsi_f = reinterpret_cast<float *const *>(hsi);
+        const float *const *hadj_f = reinterpret_cast<const float *const *>(hadj);
+        const float *hray_f[RAY_NFIELDS] = { hr->ox, hr->oy, hr->oz, hr->dx, hr->dy, hr->dz, hr->maxt };
+        float *const *hpre_f = reinterpret_cast<float *const *>(hpre);
 
-    size_t chunk_idx = 0;
-    for (size_t base = 0; base < n; base += HF_HOST_CHUNK, ++chunk_idx) {
-        const size_t m = std::min(HF_HOST_CHUNK, n - base);
-        HostSlot &s = c->slots[chunk_idx % HF_HOST_SLOTS];
-        float *slab = s.slab;
-        auto field = [&](int k) { return slab + (size_t) k * HF_HOST_CHUNK; };
+        size_t chunk_idx = 0;
+        for (size_t base = 0; base < n; base += HF_HOST_CHUNK, ++chunk_idx) {
+            const size_t m = std::min(HF_HOST_CHUNK, n - base);
+            HostSlot &s = c->slots[chunk_idx % HF_HOST_SLOTS];
+            float *slab = s.slab;
+            auto field = [&](int k) { return slab + (size_t) k * HF_HOST_CHUNK; };
 
-        hf_rays dr; memset(&dr, 0, sizeof(dr));
-        const float **drf = reinterpret_cast<const float **>(&dr);
-        for (int k = 0; k < 7; ++k) {
-            CU(cudaMemcpyAsync(field(k), hray_f[k] + base, m * sizeof(float), cudaMemcpyHostToDevice, s.stream));
-            drf[k] = field(k);
-        }
-        if (hr->active) {
-            uint8_t *da = reinterpret_cast<uint8_t *>(field(52));
-            CU(cudaMemcpyAsync(da, hr->active + base, m, cudaMemcpyHostToDevice, s.stream));
-            dr.active = da;
-        }
-        hf_prelim dp;
-        dp.t = field(7); dp.u = field(8); dp.v = field(9); dp.prim_index = reinterpret_cast<uint32_t *>(field(10));
-        hf_si dsi; memset(&dsi, 0, sizeof(dsi));
-        float **dsif = reinterpret_cast<float **>(&dsi);
-        if (hsi) for (int k = 0; k < SI_NFIELDS; ++k) if (hsi_f[k]) dsif[k] = field(11 + k);
-        hf_si_adj dadj; memset(&dadj, 0, sizeof(dadj));
-        const float **dadjf = reinterpret_cast<const float **>(&dadj);
-        if (backward) {
-            int slot = 37;
-            for (int k = 0; k < ADJ_NFIELDS; ++k) if (hadj_f[k]) {
-                CU(cudaMemcpyAsync(field(slot), hadj_f[k] + base, m * sizeof(float), cudaMemcpyHostToDevice, s.stream));
-                dadjf[k] = field(slot);
-                ++slot;
+            // ---- host -> device (waits until the slab's previous results have left)
+            if (chunk_idx >= HF_HOST_SLOTS) CU(cudaStreamWaitEvent(c->s_in, s.out_done, 0));
+            hf_rays dr; memset(&dr, 0, sizeof(dr));
+            const float **drf = reinterpret_cast<const float **>(&dr);
+            for (int k = 0; k < RAY_NFIELDS; ++k) {
+                CU(cudaMemcpyAsync(field(SLAB_RAY + k), hray_f[k] + base, m * sizeof(float), cudaMemcpyHostToDevice, c->s_in));
+                drf[k] = field(SLAB_RAY + k);
             }
-        }
+            if (hr->active) {
+                uint8_t *da = reinterpret_cast<uint8_t *>(field(SLAB_ACTIVE));
+                CU(cudaMemcpyAsync(da, hr->active + base, m, cudaMemcpyHostToDevice, c->s_in));
+                dr.active = da;
+            }
+            hf_si_adj dadj; memset(&dadj, 0, sizeof(dadj));
+            const float **dadjf = reinterpret_cast<const float **>(&dadj);
+            if (backward) {
+                for (int k = 0; k < ADJ_NFIELDS; ++k) if (hadj_f[k]) {
+                    CU(cudaMemcpyAsync(field(SLAB_ADJ + k), hadj_f[k] + base, m * sizeof(float), cudaMemcpyHostToDevice, c->s_in));
+                    dadjf[k] = field(SLAB_ADJ + k);
+                }
+            }
+            CU(cudaEventRecord(s.in_done, c->s_in));
 
-        CU(hf_launch_intersect(c->P, c->li, HF_MODE_FUSED_SI, dr, dp, dsi, nullptr, flags, m, c->d_counters, next_sched(c), s.stream));
-        if (backward && c->grad_enabled)
-            CU(hf_launch_backward(c->P, c->li, dr, dp, dadj, flags, c->d_grad, m, s.stream));
+            // ---- kernels
+            hf_prelim dp;
+            float **dpf = reinterpret_cast<float **>(&dp);
+            for (int k = 0; k < PRE_NFIELDS; ++k) dpf[k] = field(SLAB_PRE + k);
+            hf_si dsi; memset(&dsi, 0, sizeof(dsi));
+            float **dsif = reinterpret_cast<float **>(&dsi);
+            if (hsi) for (int k = 0; k < SI_NFIELDS; ++k) if (hsi_f[k]) dsif[k] = field(SLAB_SI + k);
+            CU(cudaStreamWaitEvent(c->s_k, s.in_done, 0));
+            CU(hf_launch_intersect(c->P, c->li, HF_MODE_FUSED_SI, dr, dp, dsi, nullptr, flags, m, c->d_counters, SCHED(c, c->s_k), c->s_k));
+            if (backward && c->grad_enabled)
+                CU(hf_launch_backward(c->P, c->li, dr, dp, dadj, flags, c->d_grad, m, c->s_k));
+            CU(cudaEventRecord(s.k_done, c->s_k));
 
-        if (hpre) {
-            CU(cudaMemcpyAsync(hpre->t + base, dp.t, m * sizeof(float), cudaMemcpyDeviceToHost, s.stream));
-            CU(cudaMemcpyAsync(hpre->u + base, dp.u, m * sizeof(float), cudaMemcpyDeviceToHost, s.stream));
-            CU(cudaMemcpyAsync(hpre->v + base, dp.v, m * sizeof(float), cudaMemcpyDeviceToHost, s.stream));
-            CU(cudaMemcpyAsync(hpre->prim_index + base, dp.prim_index, m * sizeof(uint32_t), cudaMemcpyDeviceToHost, s.stream));
+            // ---- device -> host
+            CU(cudaStreamWaitEvent(c->s_out, s.k_done, 0));
+            if (hpre) for (int k = 0; k < PRE_NFIELDS; ++k)
+                CU(cudaMemcpyAsync(hpre_f[k] + base, dpf[k], m * sizeof(float), cudaMemcpyDeviceToHost, c->s_out));
+            if (hsi) for (int k = 0; k < SI_NFIELDS; ++k) if (hsi_f[k])
+                CU(cudaMemcpyAsync(hsi_f[k] + base, dsif[k], m * sizeof(float), cudaMemcpyDeviceToHost, c->s_out));
+            CU(cudaEventRecord(s.out_done, c->s_out));
         }
-        if (hsi) for (int k = 0; k < SI_NFIELDS; ++k) if (hsi_f[k])
-            CU(cudaMemcpyAsync(hsi_f[k] + base, dsif[k], m * sizeof(float), cudaMemcpyDeviceToHost, s.stream));
     }
-    for (auto &s : c->slots) CU(cudaStreamSynchronize(s.stream));
-    if (h_grad_out) CU(cudaMemcpy(h_grad_out, c->d_grad, (size_t) c->W * c->H * sizeof(float), cudaMemcpyDeviceToHost));
+    if (h_grad_out) {
+        // the gradient grid is complete when the last kernel has finished: s_out waits for s_k, then copies
+        CU(cudaEventRecord(c->ev_entry, c->s_k));
+        CU(cudaStreamWaitEvent(c->s_out, c->ev_entry, 0));
+        CU(cudaMemcpyAsync(h_grad_out, c->d_grad, (size_t) c->W * c->H * sizeof(float), cudaMemcpyDeviceToHost, c->s_out));
+    }
+    CU(cudaStreamSynchronize(c->s_in));
+    CU(cudaStreamSynchronize(c->s_k));
+    CU(cudaStreamSynchronize(c->s_out));
     return HF_OK;
 }
 

@@ -10,6 +10,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include "hf_divmagic.h"
 
 #define HF_MAX_LEVELS 26
 #define HF_INF __int_as_float(0x7f800000)
@@ -35,6 +36,8 @@ struct HfParams {
     const uint32_t *qpyr;
     uint32_t qoff[HF_MAX_LEVELS]; // node offset of level l in qpyr; pitch of level l = max((xmask + 1) >> l, 1)
     int QLtop, xmask, ymask;      // top level; padded cell counts minus one
+    uint32_t nx_magic;            // cell / NX without a divide (hf_divmagic.h); prim_index < 2^31 is checked by hf_create
+    int32_t nx_shift;
 };
 
 struct f3 { float x, y, z; };
@@ -161,7 +164,7 @@ __device__ __forceinline__ bool cell_intersect(const HfParams &P, int cx, int cy
 __device__ __forceinline__ void cell_triangle(const HfParams &P, uint32_t prim, f3 &p0, f3 &p1, f3 &p2,
                                               uint32_t &i0, uint32_t &i1, uint32_t &i2) {
     uint32_t cell = prim >> 1, k = prim & 1u;
-    uint32_t cy = cell / (uint32_t) P.NX, cx = cell - cy * (uint32_t) P.NX;
+    uint32_t cy = hf_divide(cell, P.nx_magic, P.nx_shift), cx = cell - cy * (uint32_t) P.NX;
 #ifdef HF_DEBUG_BOUNDS
     if (cy >= (uint32_t) P.NY) __trap();       // checked build: a primitive index that is not a triangle of this field
 #endif

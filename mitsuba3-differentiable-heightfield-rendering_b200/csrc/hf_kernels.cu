@@ -5,7 +5,7 @@
 //   hf_intersect_kernel      : hierarchical DDA + two Moeller-Trumbore triangles per cell
 //        (Shape::ray_intersect_preliminary / ray_test / ray_intersect, shape.h:137-197)
 //   hf_si_kernel             : Shape::compute_surface_interaction (+ finalize), shape.h:179-183
-//   hf_backward_kernel       : reverse mode w.r.t. the hit cell's texels, warp-aggregated atomics
+//   (hf_backward_kernel lives in hf_backward.cu: reverse mode w.r.t. the hit cell's texels, warp-aggregated atomics)
 //   hf_adam_kernel           : src/python/python/ad/optimizers.py:263-302
 //
 // Compiled with -fmad=false: see hf_device.cuh.
@@ -644,7 +644,7 @@ hf_intersect_fast_kernel(const __grid_constant__ HfParams P, const HfLaunchInfo 
                          const hf_si S, uint8_t *__restrict__ hit_out, const uint32_t flags, const size_t n,
                          const unsigned long long nbig, const unsigned long long npair, unsigned long long *__restrict__ sched) {
     HfGrid G;
-    hf_stage_pyramid(P, li, G);
+    hf_stage_pyramid<false>(P, li, G);       // no bundle march here: only the quantised coarse levels are staged
 
     const unsigned lane = threadIdx.x & 31u;
     const unsigned long long ngroups = (n + 31) / 32;
@@ -709,7 +709,7 @@ hf_intersect_beam_kernel(const __grid_constant__ HfParams P, const HfLaunchInfo 
                          const hf_si S, uint8_t *__restrict__ hit_out, const uint32_t flags, const size_t n,
                          const unsigned long long nbig, unsigned long long *__restrict__ sched) {
     HfGrid G;
-    hf_stage_pyramid(P, li, G);
+    hf_stage_pyramid<true>(P, li, G);
 
     const unsigned lane = threadIdx.x & 31u;
     const unsigned long long ngroups = (n + 31) / 32;
@@ -817,9 +817,9 @@ cudaError_t hf_launch_intersect(const HfParams &P, const HfLaunchInfo &li, int m
         hf_intersect_kernel<HF_MODE_COUNTED><<<grid, HF_BLOCK, smem, s>>>(P, li, rays, prelim, si, d_hit, flags, n, d_counters);
         return cudaGetLastError();
     }
-    const size_t smem = (size_t) li.top_nodes * sizeof(float2);
     if (mode == HF_MODE_FUSED_SI && hf_si_is_lean(si, flags)) mode = HF_MODE_FUSED_SI_LEAN;
     if (li.use_bundles && mode != HF_MODE_TEST) {
+        const size_t smem = hf_walk_smem(li, true);
         const unsigned long long ngroups = (n + 31) / 32;
         const unsigned long long nbig = (ngroups - ngroups / 8) / 32;                 // the last eighth (at least) goes out in small tiles
         const unsigned long long ntile = nbig + (ngroups - nbig * 32 + HF_SMALL_GROUPS - 1) / HF_SMALL_GROUPS;
@@ -837,7 +837,11 @@ cudaError_t hf_launch_intersect(const HfParams &P, const HfLaunchInfo &li, int m
             hf_intersect_beam_kernel<HF_MODE_FUSED_SI><<<bgrid, HF_BLOCK, smem, s>>>(P, li, rays, prelim, si, d_hit, flags, n, nbig, sched);
         return cudaGetLastError();
     }
-    static bool carved = false;
+    static bool carved_dev[64] = { false };     // function attributes are per device: one process may drive several GPUs
+    int dev_ = 0;
+    cudaGetDevice(&dev_);
+    bool &carved = carved_dev[dev_ & 63];
+    const size_t smem = hf_walk_smem(li, false);
     if (!carved) {
         carved = true;
         hf_prefer_l1(hf_intersect_fast_kernel<HF_MODE_PRELIM>, smem + 1024, HF_MIN_CTAS);
@@ -901,116 +905,6 @@ cudaError_t hf_launch_surface_interaction(const HfParams &P, const HfLaunchInfo 
                                           const hf_prelim &pi, uint32_t flags, const hf_si &si, size_t n, cudaStream_t s) {
     if (n == 0) return cudaSuccess;
     hf_si_kernel<<<hf_grid_for(n, li.num_sms, 8), HF_BLOCK, 0, s>>>(P, rays, pi, flags, si, n);
-    return cudaGetLastError();
-}
-
-// ------------------------------------------------------------------------------------------
-// Backward: adjoint of (t, p, n, uv, dp_du, dp_dv) w.r.t. the three texels of the hit triangle,
-// closed form (the hit stays on the ray: p = o + t d), accumulated with warp-aggregated atomics.
-// ------------------------------------------------------------------------------------------
-
-__global__ void __launch_bounds__(HF_BLOCK)
-hf_backward_kernel(const __grid_constant__ HfParams P, const hf_rays R, const hf_prelim PI, const hf_si_adj A,
-                   const uint32_t flags, float *__restrict__ grad, const size_t n) {
-    const size_t ntiles = (n + HF_BLOCK - 1) / HF_BLOCK;
-    for (size_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-        const size_t i = tile * HF_BLOCK + threadIdx.x;
-        bool valid = i < n;
-        float t = HF_INF;
-        if (valid) {
-            t = __ldcs(PI.t + i);
-            valid = (t != HF_INF) && (R.active ? (R.active[i] != 0) : true);
-        }
-        uint32_t i0 = 0, i1 = 0, i2 = 0;
-        float g0 = 0.f, g1 = 0.f, g2 = 0.f;
-        if (valid) {
-            const f3 ow = mk3(__ldcs(R.ox + i), __ldcs(R.oy + i), __ldcs(R.oz + i));
-            const f3 dw = mk3(__ldcs(R.dx + i), __ldcs(R.dy + i), __ldcs(R.dz + i));
-            const f3 o = xform_point(P.to_object, ow), d = xform_vector(P.to_object, dw);
-            const float u = __ldcs(PI.u + i), v = __ldcs(PI.v + i);
-            const uint32_t prim = __ldcs(PI.prim_index + i);
-            f3 p0, p1, p2;
-            cell_triangle(P, prim, p0, p1, p2, i0, i1, i2);
-            const f3 e1 = sub3(p1, p0), e2 = sub3(p2, p0);
-            const f3 c = cross3(e1, e2);
-
-            #define LDA(ptr) ((ptr) ? __ldcs((ptr) + i) : 0.f)
-            const float a_t = LDA(A.t);
-            const f3 a_pw = mk3(LDA(A.px), LDA(A.py), LDA(A.pz));
-            f3 a_nw = mk3(LDA(A.nx), LDA(A.ny), LDA(A.nz));
-            const float a_uvx = LDA(A.uvx), a_uvy = LDA(A.uvy);
-            const f3 a_duw = mk3(LDA(A.dpdu_x), LDA(A.dpdu_y), LDA(A.dpdu_z));
-            const f3 a_dvw = mk3(LDA(A.dpdv_x), LDA(A.dpdv_y), LDA(A.dpdv_z));
-            #undef LDA
-            if (P.flip_normals) a_nw = neg3(a_nw);
-
-            f3 a_p = lin_T(P.to_world, a_pw);
-            const f3 a_du = lin_T(P.to_world, a_duw), a_dv = lin_T(P.to_world, a_dvw);
-
-            // n_w = normalize(TO^T normalize(c))
-            const float inv_clen = rsqrtf(dot3(c, c));
-            const f3 no = mk3(c.x * inv_clen, c.y * inv_clen, c.z * inv_clen);
-            const f3 m = lin_T(P.to_object, no);
-            const float inv_mlen = rsqrtf(dot3(m, m));
-            const f3 nw = mk3(m.x * inv_mlen, m.y * inv_mlen, m.z * inv_mlen);
-            const float dn = dot3(nw, a_nw);
-            const f3 a_m = mk3((a_nw.x - nw.x * dn) * inv_mlen, (a_nw.y - nw.y * dn) * inv_mlen, (a_nw.z - nw.z * dn) * inv_mlen);
-            const f3 a_no = lin(P.to_object, a_m);
-            const float dno = dot3(no, a_no);
-            const f3 a_c = mk3((a_no.x - no.x * dno) * inv_clen, (a_no.y - no.y * dno) * inv_clen, (a_no.z - no.z * dno) * inv_clen);
-            f3 a_e1 = cross3(e2, a_c), a_e2 = cross3(a_c, e1);
-
-            const float u0x = tex(p0.x), u0y = tex(p0.y), u1x = tex(p1.x), u1y = tex(p1.y), u2x = tex(p2.x), u2y = tex(p2.y);
-            const float d0x = u1x - u0x, d0y = u1y - u0y, d1x = u2x - u0x, d1y = u2y - u0y;
-            if (flags & HF_RAY_DPDUV) {
-                const float det = d0x * d1y - d0y * d1x;
-                if (det != 0.f) {
-                    const float r = 1.0f / det;
-                    const float k11 = d1y * r, k12 = -d1x * r, k21 = -d0y * r, k22 = d0x * r;
-                    a_e1 = mk3(a_e1.x + a_du.x * k11 + a_dv.x * k12, a_e1.y + a_du.y * k11 + a_dv.y * k12, a_e1.z + a_du.z * k11 + a_dv.z * k12);
-                    a_e2 = mk3(a_e2.x + a_du.x * k21 + a_dv.x * k22, a_e2.y + a_du.y * k21 + a_dv.y * k22, a_e2.z + a_du.z * k21 + a_dv.z * k22);
-                }
-            }
-
-            const float b1 = u, b2 = v, b0 = 1.f - u - v;
-            float wz;       // z component of the adjoint that is distributed with the barycentrics
-            if (flags & HF_RAY_FOLLOWSHAPE) {
-                // mesh.cpp:728-729, 751-752: barycentrics detached, t = sqrt(|p-o|^2/|d|^2)
-                const f3 po = mk3(p0.x * b0 + p1.x * b1 + p2.x * b2, p0.y * b0 + p1.y * b1 + p2.y * b2, p0.z * b0 + p1.z * b1 + p2.z * b2);
-                const f3 pw = xform_point(P.to_world, po);
-                const f3 rel = sub3(pw, ow);
-                const float dd = dot3(dw, dw);
-                const float tt = sqrtf(dot3(rel, rel) / dd);
-                if (tt > 0.f) {
-                    const float k = a_t / (tt * dd);
-                    const f3 extra = lin_T(P.to_world, mk3(rel.x * k, rel.y * k, rel.z * k));
-                    a_p = mk3(a_p.x + extra.x, a_p.y + extra.y, a_p.z + extra.z);
-                }
-                wz = a_p.z;
-            } else {
-                const float a_tt = a_t + dot3(d, a_p);
-                const float a_u = d0x * a_uvx + d0y * a_uvy;
-                const float a_v = d1x * a_uvx + d1y * a_uvy;
-                const f3 pvec = cross3(d, e2);
-                const float det = dot3(e1, pvec);
-                const f3 de1 = cross3(d, e1);
-                wz = (-a_tt * c.z - a_u * pvec.z + a_v * de1.z) / det;
-            }
-            g0 = P.mh * (wz * b0 - (a_e1.z + a_e2.z));
-            g1 = P.mh * (wz * b1 + a_e1.z);
-            g2 = P.mh * (wz * b2 + a_e2.z);
-        }
-        // whole warp participates (inactive lanes pass valid = false)
-        warp_aggregated_add(grad, i0, g0, valid);
-        warp_aggregated_add(grad, i1, g1, valid);
-        warp_aggregated_add(grad, i2, g2, valid);
-    }
-}
-
-cudaError_t hf_launch_backward(const HfParams &P, const HfLaunchInfo &li, const hf_rays &rays, const hf_prelim &pi,
-                               const hf_si_adj &adj, uint32_t flags, float *grad, size_t n, cudaStream_t s) {
-    if (n == 0 || (flags & HF_RAY_DETACHSHAPE)) return cudaSuccess;   // mesh.cpp:713-717
-    hf_backward_kernel<<<hf_grid_for(n, li.num_sms, 8), HF_BLOCK, 0, s>>>(P, rays, pi, adj, flags, grad, n);
     return cudaGetLastError();
 }
 

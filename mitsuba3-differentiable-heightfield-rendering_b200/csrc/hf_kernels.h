@@ -13,7 +13,16 @@ struct HfLaunchInfo {
     int top_nodes;           // node count of levels Ls..Ltop (padded to even)
     int top_off;             // node offset of level Ls
     int use_bundles;         // 1: bundled kernel (hf_intersect_beam_kernel), 0: plain per-ray kernel
+    // quantised pyramid: the coarse EVEN levels >= q_stage_level (the levels every walk starts from) are staged in shared memory
+    int q_stage_level;       // lowest staged level (even), > QLtop: nothing staged
+    int q_stage_bytes;       // shared memory they take (each level padded to 16 bytes)
 };
+#ifndef HF_STAGE_Q
+#define HF_STAGE_Q 1
+#endif
+#ifndef HF_QSTAGE_CAP
+#define HF_QSTAGE_CAP 17536  // bytes per CTA: levels 6, 8, 10, 12 of a 4096^2 field (16 KB + 1 KB + 64 B + 16 B); 16384^2 stages 8..14
+#endif
 
 enum HfIntersectMode { HF_MODE_PRELIM = 0, HF_MODE_FUSED_SI = 1, HF_MODE_TEST = 2, HF_MODE_COUNTED = 3,
                        HF_MODE_FUSED_SI_LEAN = 4 };   // internal: FUSED_SI when only t, p, n, uv are requested (chosen by hf_launch_intersect)

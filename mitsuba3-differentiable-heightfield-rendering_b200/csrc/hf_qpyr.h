@@ -33,7 +33,10 @@ struct HfQuant { float zb, qs, rqs; };   // rqs = 1 / qs: the encoder's first gu
 HF_QHD HfQuant hf_quant_make(float top_min, float top_max) {
     HfQuant q;
     float qs = (top_max - top_min) * (1.0f / 65280.0f);       // 255 codes of headroom split below / above the range
-    if (!(qs > 1e-30f) || !(qs < 1e30f)) qs = 1e-30f;         // flat (or degenerate) field: every code decodes to ~top_min
+    // flat (or degenerate) field: every code decodes to ~top_min. The floor is one fp32 ulp of the field's own magnitude (finer codes
+    // resolve nothing) and keeps 1 / qs, which the walk multiplies ray heights by (hf_traverse.cuh, HF_CODE_SPACE), far from overflow
+    const float qmin = fmaxf(5.9604644775390625e-08f * fmaxf(fabsf(top_min), fabsf(top_max)), 1e-20f);
+    if (!(qs > qmin) || !(qs < 1e30f)) qs = qmin;
     q.qs = qs;
     q.rqs = 1.0f / qs;
     q.zb = top_min - 128.0f * qs;

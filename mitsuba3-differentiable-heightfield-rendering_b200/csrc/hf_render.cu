@@ -342,7 +342,7 @@ hf_render_kernel(const __grid_constant__ HfParams P, const HfLaunchInfo li, cons
                  unsigned long long *__restrict__ sched) {
     __shared__ uint32_t s_prim[HF_BLOCK / 32][HF_RENDER_MAX_SPP];
     HfGrid G;
-    hf_stage_pyramid(P, li, G);
+    hf_stage_pyramid<true>(P, li, G);
 
     const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
     const uint32_t spp = A.cam.spp;
@@ -502,7 +502,7 @@ hf_render_path_kernel(const __grid_constant__ HfParams P, const HfLaunchInfo li,
                       float *__restrict__ image, const float *__restrict__ adj_image, float *__restrict__ grad,
                       unsigned long long *__restrict__ sched) {
     HfGrid G;
-    hf_stage_pyramid(P, li, G);
+    hf_stage_pyramid<true>(P, li, G);
     const unsigned lane = threadIdx.x & 31u;
     const uint32_t spp = A.cam.spp, rounds = (spp + 31u) >> 5;
     uint32_t seg = 32u;                                    // as in hf_render_kernel: lanes per pixel, pixels per round, pixels per tile
@@ -679,7 +679,7 @@ cudaError_t hf_launch_render(const HfParams &P, const HfLaunchInfo &li, int mode
     const HfRenderArgs A = hf_render_args(P, cam, &light, d_pixels, npix);
     cudaError_t e = cudaMemsetAsync(d_sched, 0, sizeof(unsigned long long), s);
     if (e != cudaSuccess) return e;
-    const size_t smem = (size_t) li.top_nodes * sizeof(float2);
+    const size_t smem = hf_walk_smem(li, true);
     const int grid = hf_render_grid(li, npix);
     if (A.max_depth > 1) {                    // path tracing: forward image or replayed adjoint (the fused L2 step is composed by hf_api.cu)
         const int pgrid = grid < li.num_sms * 2 ? grid : li.num_sms * 2;

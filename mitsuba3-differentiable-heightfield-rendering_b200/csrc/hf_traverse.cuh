@@ -25,8 +25,12 @@
 #pragma once
 #include <math.h>
 #include <stdint.h>
+#include <string.h>
 #include "hf_qpyr.h"
 
+#ifndef HF_STAGE_Q
+#define HF_STAGE_Q 1
+#endif
 #ifdef __CUDACC__
 #define HF_HD __device__ __forceinline__
 #define HF_LDG(p) __ldg(p)
@@ -54,13 +58,23 @@ struct float2 { float x, y; };
 
 #define HF_TRAV_SLACK 9.5367431640625e-07f   // 2^-20, identical to HF_Z_SLACK / HFO_Z_SLACK
 
+// HF_CODE_SPACE = 1: the walk compares the ray's z interval with the node's 16-bit bounds IN CODE UNITS instead of decoding the two
+// bounds to object-space floats at every node. z'(t) is carried as  M + (z - zb) / qs  with M = 2^23 (sign-flipped for a climbing
+// ray), and a code c becomes the float M + c by ONE byte permute that puts the code into the mantissa of 0x4B000000 (the classic
+// int -> float magic number; 0xCB000000 for the flipped sign): per node 2 PRMT + 2 FSETP instead of 2 PRMT + 2 I2F + 2 FFMA + 2 FSETP,
+// and nothing left on the conversion (XU) pipe. Conservative: one extra code of slack pays for the integer rounding at M (below).
+#ifndef HF_CODE_SPACE
+#define HF_CODE_SPACE 1
+#endif
+#define HF_CODE_MAGIC 8388608.0f             // 2^23: float(M + c) has the bit pattern 0x4B000000 | c for 0 <= c < 2^23
+
 struct __attribute__((aligned(16))) HfLevel {   // one pyramid level; `nodes` may point to global OR shared memory (generic address)
     const float2 *nodes;       // row-major (min,max) of z = max_height*h
     int w;                     // nodes per row
     int pad;
 };
 
-struct __attribute__((aligned(16))) HfQLevel {  // one level of the quantised pyramid (global memory)
+struct __attribute__((aligned(16))) HfQLevel {  // one level of the quantised pyramid; `nodes` is a generic address (staged coarse levels: shared memory)
     const uint32_t *nodes;     // row-major, (hi << 16) | lo codes
     int pitch;                 // nodes per row (a power of two)
     int pad;
@@ -85,21 +99,26 @@ struct HfGrid {                // what the walk needs to know about the shape
     int QLtop;                 // top level of the quantised pyramid (one node)
     int xmask, ymask;          // Mx - 1, My - 1 (padded cell counts are powers of two)
     float qs, zb;              // decode(c) = fmaf(float(c), qs, zb)
+    float rqs;                 // 1 / qs (HfQuant::rqs)
 };
 
 struct HfWalk {                // per-ray state, lives in registers. x, y are MIRRORED grid units, z is FLIPPED (see top)
     float ogx, ogy, dgx, dgy;  // dgx, dgy >= 0
     float ogxl, ogyl;          // low parts of the mirrored origin: Mx - og is kept EXACTLY as ogx + ogxl (a rounded mirror image is a
                                // different ray: next to a cell boundary a nearly axis-parallel ray would leave its row far too early)
-    float dz;                  // <= 0
+    float dz;                  // <= 0  (HF_CODE_SPACE: in code units per unit of t)
     float idx, idy;            // 1/dg; after hf_walk_init: 0 when the component is zero ...
     float infx, infy;          // ... and +inf here (0 otherwise), so that t_exit = fma(b - og, id, inf) needs no select
     float t1;
     float t;                   // ray parameter at the entry of the current node
     float idz;                 // 1/dz (0 when dz == 0)
-    float ozp, ozm;            // oz + epsz, oz - epsz: z(t) padded up / down by the walk's z slack
+    float ozp, ozm;            // oz + epsz, oz - epsz: z(t) padded up / down by the walk's z slack (HF_CODE_SPACE: code units, offset by +-M)
     float ogxb, ogyb;          // og backed off against the direction of travel: cells derived from t are never ahead of the ray
+#if HF_CODE_SPACE
+    uint32_t kmagic;           // 0x4B000000 (M + code) or 0xCB000000 (-(M + code), flipped ray): upper bytes of a node bound as a float
+#else
     float qsf, zbf;            // decode constants of the quantised nodes, negated for a flipped ray
+#endif
     int ix, iy, L;             // mirrored cell, level
     int xm, ym;                // mirror masks: real cell = (ix ^ xm, iy ^ ym)
     int xlim, ylim;            // last real cell in mirrored coordinates: beyond it lies padding (or the end of the padded domain)
@@ -188,16 +207,18 @@ HF_HD bool hf_walk_init(const HfGrid &G, float ox, float oy, float oz, float dx,
         const bool mx_ = dgx < 0.f, my_ = dgy < 0.f;
         w.xm = mx_ ? G.xmask : 0; w.ym = my_ ? G.ymask : 0;
         w.xlim = mx_ ? G.xmask : NX - 1; w.ylim = my_ ? G.ymask : NY - 1;   // a mirrored ray has the padding behind it
-        w.ogxl = 0.f; w.ogyl = 0.f;
+        float ogxl = 0.f, ogyl = 0.f;        // low parts of the mirrored origin: Mx - og is kept EXACTLY as ogx + ogxl (a rounded mirror image
+                                             // is a different ray: next to a cell boundary a nearly axis-parallel ray would leave its row far too early)
         if (mx_) {                           // two-sum: M + (-og) = s + e exactly
             const float a = (float) (G.xmask + 1), b = -ogx, sm = a + b, bb = sm - a;
-            w.ogxl = (a - (sm - bb)) + (b - bb); ogx = sm; dgx = -dgx; idx = -idx;
+            ogxl = (a - (sm - bb)) + (b - bb); ogx = sm; dgx = -dgx; idx = -idx;
         }
         if (my_) {
             const float a = (float) (G.ymask + 1), b = -ogy, sm = a + b, bb = sm - a;
-            w.ogyl = (a - (sm - bb)) + (b - bb); ogy = sm; dgy = -dgy; idy = -idy;
+            ogyl = (a - (sm - bb)) + (b - bb); ogy = sm; dgy = -dgy; idy = -idy;
         }
-        w.ogx = ogx; w.ogy = ogy; w.dgx = dgx; w.dgy = dgy;
+        w.dgx = dgx; w.dgy = dgy;
+        w.ogx = ogx; w.ogy = ogy; w.ogxl = ogxl; w.ogyl = ogyl;
         w.ogxb = ogx - ex; w.ogyb = ogy - ey;
         w.ix = ix ^ w.xm; w.iy = iy ^ w.ym;
     }
@@ -209,12 +230,32 @@ HF_HD bool hf_walk_init(const HfGrid &G, float ox, float oy, float oz, float dx,
     w.t = t0;
     {   // flip z for a climbing ray: the walk only ever moves towards -z'
         const bool fz = dz > 0.f;
+#if HF_CODE_SPACE
+        // code units: zc = (z - zb) * rqs. What must hold for every node the walk prunes: the padded interval [zlo, zhi] contains the
+        // true z range of the ray over [t, te] as measured against the bounds the ENCODER guaranteed in fp32 (decode(lo) <= min,
+        // decode(hi) >= max with decode = fmaf(code, qs, zb)). Slack, in codes:
+        //   * the object-space slack of the float walk, scaled: 2^-20 (|oz - zb| + |t1 dz|) rqs  (rounding of z(t), of t, of rqs);
+        //   * the rounding of decode itself, which the float compare shared with the encoder and this one does not: 2^-23 |z|max rqs;
+        //   * 1.25: the offset M makes the two roundings (of oz' +- eps + M, and of the fma per node) integer roundings, 0.5 each.
+        const float rqs = G.rqs;
+        const float oc = (oz - G.zb) * rqs, dzc = dz * rqs;
+        const float epsc = HF_TRAV_SLACK * (fabsf(oc) + fabsf(t1 * dzc)) +
+                           1.1920928955078125e-07f * fmaxf(fabsf(G.top_min), fabsf(G.top_max)) * rqs + 1.25f;
+        const float ocf = fz ? -oc : oc, sM = fz ? -HF_CODE_MAGIC : HF_CODE_MAGIC;
+        w.dz = fz ? -dzc : dzc;
+        w.idz = dz != 0.f ? (fz ? -idz : idz) * G.qs : 0.f;
+        w.ozp = (ocf + epsc) + sM; w.ozm = (ocf - epsc) + sM;
+        w.kmagic = fz ? 0xCB000000u : 0x4B000000u;
+        w.sel_lo = fz ? 0x7632u : 0x7610u;       // the node half that bounds z' from below: lo codes, or the hi codes of a flipped ray
+        (void) epsz;
+#else
         const float ozf = fz ? -oz : oz;
         w.dz = fz ? -dz : dz;
         w.idz = dz != 0.f ? (fz ? -idz : idz) : 0.f;
         w.ozp = ozf + epsz; w.ozm = ozf - epsz;
         w.qsf = fz ? -G.qs : G.qs; w.zbf = fz ? -G.zb : G.zb;
         w.sel_lo = fz ? 0x4432u : 0x4410u;
+#endif
     }
     const float inf = INFINITY;
     w.infx = dgx != 0.f ? 0.f : inf; w.infy = dgy != 0.f ? 0.f : inf;
@@ -233,11 +274,19 @@ HF_HD bool hf_walk_init(const HfGrid &G, float ox, float oy, float oz, float dx,
 #endif
 #endif
 
-HF_HD uint32_t hf_prmt(uint32_t q, uint32_t sel) {      // __byte_perm(q, 0, sel) for the two selectors the walk uses
+HF_HD uint32_t hf_prmt(uint32_t q, uint32_t k, uint32_t sel) {      // __byte_perm(q, k, sel) for the selectors the walk uses
 #ifdef __CUDACC__
-    return __byte_perm(q, 0u, sel);
+    return __byte_perm(q, k, sel);
 #else
-    return ((sel & 0xffu) == 0x10u) ? (q & 0xffffu) : (q >> 16);
+    const uint32_t half = ((sel & 0xffu) == 0x10u) ? (q & 0xffffu) : (q >> 16);
+    return (sel & 0xff00u) == 0x7600u ? ((k & 0xffff0000u) | half) : half;      // 0x76xx: upper two bytes from k
+#endif
+}
+HF_HD float hf_bits_float(uint32_t b) {
+#ifdef __CUDACC__
+    return __uint_as_float(b);
+#else
+    float f; memcpy(&f, &b, 4); return f;
 #endif
 }
 
@@ -259,6 +308,8 @@ HF_HD bool hf_walk_next(const HfGrid &G, HfWalk &w, HfCand &c
         const int mask = (1 << L) - 1;
         const int hx = ix | mask, hy = iy | mask;                 // last cell of this node on each axis
         const int bx = hx + 1, by = hy + 1;                       // exit planes of this node
+        // (NOT fma(float(b), id, -og * id): for a nearly axis-parallel ray id is huge and the two products cancel catastrophically;
+        // the subtraction below is exact next to the ray -- tests/test_traversal_host.py::test_walk_under_an_affine_transform)
         const float tx = fmaf(((float) bx - w.ogx) - w.ogxl, w.idx, w.infx); // the fma only adds +0 or +inf
         const float ty = fmaf(((float) by - w.ogy) - w.ogyl, w.idy, w.infy);
         const float tmin = fminf(tx, ty);
@@ -276,18 +327,27 @@ HF_HD bool hf_walk_next(const HfGrid &G, HfWalk &w, HfCand &c
         uint32_t q;
         {
 #ifdef __CUDACC__
-            uint32_t p0, p1, pitch, pad_;
+            uint32_t p0, p1, pitch, pad_ = 0u;
             asm("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(p0), "=r"(p1), "=r"(pitch), "=r"(pad_) : "r"(G.qlvl_saddr + (uint32_t) L * 16u));
             (void) pad_;
             const uint32_t *nodes = reinterpret_cast<const uint32_t *>(((unsigned long long) p1 << 32) | (unsigned long long) p0);
+#if HF_STAGE_Q
+            q = nodes[(unsigned) (((iy ^ w.ym) >> L) * (int) pitch + ((ix ^ w.xm) >> L))];       // generic: shared (staged coarse levels) or global
+#else
             q = HF_LDG(nodes + (unsigned) (((iy ^ w.ym) >> L) * (int) pitch + ((ix ^ w.xm) >> L)));
+#endif
 #else
             const HfQLevel lv = G.qlvl[L];
             q = lv.nodes[(unsigned) (((iy ^ w.ym) >> L) * lv.pitch + ((ix ^ w.xm) >> L))];
 #endif
         }
-        const float mn = fmaf((float) hf_prmt(q, w.sel_lo), w.qsf, w.zbf);
-        const float mx = fmaf((float) hf_prmt(q, sel_hi), w.qsf, w.zbf);
+#if HF_CODE_SPACE
+        const float mn = hf_bits_float(hf_prmt(q, w.kmagic, w.sel_lo));     // +-(M + code): no conversion, no decode
+        const float mx = hf_bits_float(hf_prmt(q, w.kmagic, sel_hi));
+#else
+        const float mn = fmaf((float) hf_prmt(q, 0u, w.sel_lo), w.qsf, w.zbf);
+        const float mx = fmaf((float) hf_prmt(q, 0u, sel_hi), w.qsf, w.zbf);
+#endif
         const bool overlap = (zlo <= mx) && (zhi >= mn);
         const bool desc = overlap && (L > 0);
         const bool found = overlap && (L == 0);

@@ -32,34 +32,58 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t *bar, uint32_t parity) {
     return ok != 0;
 }
 
-// Kernel prologue shared by the walk kernels: level table in shared memory, coarse levels staged by one bulk async copy.
+// Kernel prologue shared by the walk kernels: level tables in shared memory; the coarse levels are staged next to them by bulk
+// async copies (TMA engine, SASS UBLKCP) that complete on one mbarrier:
+//   * WANT_FP32: levels >= li.top_level_start of the fp32 pyramid (read by the bundle march, hf_beam_enter);
+//   * the coarse EVEN levels >= li.q_stage_level of the quantised pyramid (read by every walk: each ray starts at level
+//     min(QLtop, HF_START_LEVEL) and descends two levels at a time, so its first descents are shared-memory loads).
+// Both level tables hold GENERIC pointers: the walk reads a node with one load whether its level lives in shared or global memory.
+// Dynamic shared memory: [fp32 nodes: li.top_nodes * 8 bytes if WANT_FP32][quantised levels: li.q_stage_bytes].
+template <bool WANT_FP32>
 __device__ __forceinline__ void hf_stage_pyramid(const HfParams &P, const HfLaunchInfo &li, HfGrid &G) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     HfLevel *s_lvl = hf_s_lvl;                                                                // static __shared__ (hf_traverse.cuh)
+    const bool fp32_staged = WANT_FP32 && li.top_nodes > 0;
     float2 *s_nodes = reinterpret_cast<float2 *>(smem_raw);                                   // levels >= li.top_level_start
+    uint32_t *s_q = reinterpret_cast<uint32_t *>(smem_raw + (fp32_staged ? (size_t) li.top_nodes * sizeof(float2) : 0));
     __shared__ __align__(8) uint64_t s_bar;
+    __shared__ uint32_t s_qoff[HF_MAX_LEVELS];             // byte offset of a staged level inside s_q
 
     if (threadIdx.x == 0) {
         mbar_init(&s_bar, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        uint32_t o = 0;
+        for (int l = li.q_stage_level; l <= P.QLtop; l += 2) {
+            s_qoff[l] = o;
+            const uint32_t pitch = ((P.xmask + 1) >> l) > 0 ? ((P.xmask + 1) >> l) : 1, rows = ((P.ymask + 1) >> l) > 0 ? ((P.ymask + 1) >> l) : 1;
+            o += ((pitch * rows + 3u) & ~3u) * 4u;
+        }
     }
+    __syncthreads();
     if (threadIdx.x < HF_MAX_LEVELS) {
         const int l = threadIdx.x;
         HfLevel e;
-        e.nodes = (li.top_nodes > 0 && l >= li.top_level_start) ? (s_nodes + (P.lvl_off[l] - li.top_off)) : (P.pyr + P.lvl_off[l]);
+        e.nodes = (fp32_staged && l >= li.top_level_start) ? (s_nodes + (P.lvl_off[l] - li.top_off)) : (P.pyr + P.lvl_off[l]);
         e.w = P.lvl_w[l]; e.pad = 0;
         s_lvl[l] = e;
-        HfQLevel qe;                                           // quantised pyramid: global memory at every level (L1 / L2 resident)
-        qe.nodes = P.qpyr + P.qoff[l];
+        HfQLevel qe;
+        const bool staged = HF_STAGE_Q && l >= li.q_stage_level && l <= P.QLtop && !(l & 1);
+        qe.nodes = staged ? reinterpret_cast<const uint32_t *>(reinterpret_cast<const unsigned char *>(s_q) + s_qoff[l]) : (P.qpyr + P.qoff[l]);
         qe.pitch = ((P.xmask + 1) >> l) > 0 ? ((P.xmask + 1) >> l) : 1; qe.pad = 0;
         hf_s_qlvl[l] = qe;
     }
     __syncthreads();
-    if (li.top_nodes > 0) {
+    const uint32_t fp32_bytes = fp32_staged ? (uint32_t) li.top_nodes * (uint32_t) sizeof(float2) : 0u;
+    const uint32_t q_bytes = HF_STAGE_Q ? (uint32_t) li.q_stage_bytes : 0u;
+    if (fp32_bytes + q_bytes > 0u) {
         if (threadIdx.x == 0) {
-            const uint32_t bytes = (uint32_t) li.top_nodes * (uint32_t) sizeof(float2);
-            mbar_expect_tx(&s_bar, bytes);
-            bulk_g2s(s_nodes, P.pyr + li.top_off, bytes, &s_bar);
+            mbar_expect_tx(&s_bar, fp32_bytes + q_bytes);
+            if (fp32_bytes) bulk_g2s(s_nodes, P.pyr + li.top_off, fp32_bytes, &s_bar);
+            if (q_bytes)
+                for (int l = li.q_stage_level; l <= P.QLtop; l += 2) {
+                    const uint32_t pitch = ((P.xmask + 1) >> l) > 0 ? ((P.xmask + 1) >> l) : 1, rows = ((P.ymask + 1) >> l) > 0 ? ((P.ymask + 1) >> l) : 1;
+                    bulk_g2s(reinterpret_cast<unsigned char *>(s_q) + s_qoff[l], P.qpyr + P.qoff[l], ((pitch * rows + 3u) & ~3u) * 4u, &s_bar);
+                }
         }
         uint32_t spins = 0;
         while (!mbar_try_wait(&s_bar, 0)) { if (++spins > (1u << 24)) __trap(); }
@@ -72,11 +96,14 @@ __device__ __forceinline__ void hf_stage_pyramid(const HfParams &P, const HfLaun
         const float2 top = s_lvl[P.Ltop].nodes[0];
         G.top_min = top.x; G.top_max = top.y;
         const HfQuant Q = hf_quant_make(top.x, top.y);         // the same expression the builder used
-        G.qs = Q.qs; G.zb = Q.zb;
+        G.qs = Q.qs; G.zb = Q.zb; G.rqs = Q.rqs;
     }
     G.qlvl = hf_s_qlvl; G.qlvl_saddr = smem_u32(hf_s_qlvl);
     G.QLtop = P.QLtop; G.xmask = P.xmask; G.ymask = P.ymask;
-
+}
+// dynamic shared memory a walk kernel needs
+static inline size_t hf_walk_smem(const HfLaunchInfo &li, bool want_fp32) {
+    return (want_fp32 ? (size_t) li.top_nodes * sizeof(float2) : 0) + (HF_STAGE_Q ? (size_t) li.q_stage_bytes : 0);
 }
 
 // One RED per distinct address per warp: match.any on the texel index, then a log-step segmented

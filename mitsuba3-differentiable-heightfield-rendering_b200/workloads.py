@@ -138,9 +138,17 @@ def hemisphere_rays(n, seed=5, radius=3.0, device="cpu"):
     return o.contiguous(), d.contiguous()
 
 
-def hashed_adjoints(n, seed=1, device="cpu"):
-    """Upstream adjoints dt, dp, dn, duv ~ U[-1,1] from hash(seed, ray, channel)."""
-    idx = torch.arange(n, dtype=torch.int64, device=device)
+def global_ray_ids(pixels, spp):
+    """Ray id = pixel * spp + sample (src/render/integrator.cpp:251-265) for a list of pixel ids, in the order camera_rays emits them."""
+    pixels = pixels.to(torch.int64)
+    return pixels.repeat_interleave(spp) * spp + torch.arange(spp, dtype=torch.int64, device=pixels.device).repeat(pixels.numel())
+
+
+def hashed_adjoints(n, seed=1, device="cpu", ids=None):
+    """Upstream adjoints dt, dp, dn, duv ~ U[-1,1] from hash(seed, ray, channel). `ids`: the GLOBAL id of every
+    ray (global_ray_ids) -- a shard of an image then sees exactly the adjoints the single-rank run gives those rays."""
+    idx = torch.arange(n, dtype=torch.int64, device=device) if ids is None else ids.to(device=device, dtype=torch.int64)
+    assert idx.numel() == n
     ch = lambda c: 2 * hash_uniform(seed, idx, c) - 1
     return {"t": ch(0), "p": torch.stack([ch(1), ch(2), ch(3)]), "n": torch.stack([ch(4), ch(5), ch(6)]),
             "uv": torch.stack([ch(7), ch(8)])}

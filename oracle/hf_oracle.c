@@ -783,11 +783,12 @@ void hfo_backward(const hfo_shape *s, const hfo_rays *r, const hfo_prelim *pi, c
 /* ---------------------------------------------------------------------- */
 
 void hfo_adam_step(float *p, const float *g, float *m, float *v, size_t n,
-                   float lr, float beta1, float beta2, float eps, int step_t, int mask_updates) {
-    /* lr_scale is evaluated in Python doubles, then made an opaque fp32 (optimizers.py:266-269) */
-    const double b1d = (double) beta1, b2d = (double) beta2;
+                   double lr_d, double b1d, double b2d, double eps_d, int step_t, int mask_updates) {
+    /* The hyper-parameters are Python floats (doubles) in optimizers.py: lr_scale (266-269) and (1 - beta) (281-282) are evaluated
+       in double and only then become fp32 literals of the traced expression; lr is an opaque fp32 (lr_v). */
     const float lr_scale = (float) (sqrt(1.0 - pow(b2d, step_t)) / (1.0 - pow(b1d, step_t)));
-    const float lr_t = lr * lr_scale;
+    const float lr_t = (float) lr_d * lr_scale;
+    const float beta1 = (float) b1d, beta2 = (float) b2d, eps = (float) eps_d;
     const float omb1 = (float) (1.0 - b1d), omb2 = (float) (1.0 - b2d);
     #pragma omp parallel for schedule(static)
     for (long long ii = 0; ii < (long long) n; ++ii) {

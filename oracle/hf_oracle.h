@@ -135,7 +135,7 @@ void hfo_backward(const hfo_shape *s, const hfo_rays *r, const hfo_prelim *pi, c
 
 /* src/python/python/ad/optimizers.py:263-302 (fp32, Dr.Jit LLVM lowering) */
 void hfo_adam_step(float *p, const float *g, float *m, float *v, size_t n,
-                   float lr, float beta1, float beta2, float eps, int step_t, int mask_updates);
+                   double lr, double beta1, double beta2, double eps, int step_t, int mask_updates);
 
 /* -- render step on the heightfield alone (sensor + direct illumination) -------- */
 typedef struct {

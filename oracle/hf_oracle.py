@@ -110,8 +110,8 @@ def lib():
                                               C.c_uint32, C.c_size_t, C.POINTER(_SI)]
         L.hfo_backward.argtypes = [C.POINTER(_Shape), C.POINTER(_Rays), C.POINTER(_Prelim), C.POINTER(_Adj),
                                    C.c_uint32, C.c_size_t, _f64p, C.c_int]
-        L.hfo_adam_step.argtypes = [_f32p, _f32p, _f32p, _f32p, C.c_size_t, C.c_float, C.c_float, C.c_float,
-                                    C.c_float, C.c_int, C.c_int]
+        L.hfo_adam_step.argtypes = [_f32p, _f32p, _f32p, _f32p, C.c_size_t, C.c_double, C.c_double, C.c_double,
+                                    C.c_double, C.c_int, C.c_int]
         L.hfo_camera_rays.argtypes = [C.POINTER(_Camera), _u32p, C.c_size_t] + [_f32p] * 7
         L.hfo_render_samples.argtypes = [C.POINTER(_Shape), C.c_void_p, C.POINTER(_Camera), C.POINTER(_Light), _u32p, C.c_size_t,
                                          _f32p, _u32p, C.POINTER(_Prelim)]

@@ -1,0 +1,118 @@
+"""The multi-GPU product path on real devices: hf_comm_init -> hf_ray_intersect -> hf_backward -> hf_allreduce_grad on disjoint
+image-tile shards, through the C ABI, one process per GPU. The reference has nothing here, so the
+check is self-consistency + the oracle: the all-reduced gradient grid of N ranks equals the single-rank grid (1e-4 relative L2, the
+north star's gradient tolerance; fp32 atomics make both sides order-dependent) and the oracle's fp64 gradient of the full batch.
+Skipped with the reason visible when the box has a single GPU (tests/test_sharding.py covers the host logic over gloo on CPU)."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _ngpu():
+    try:
+        return torch.cuda.device_count() if torch.cuda.is_available() else 0
+    except Exception:
+        return 0
+
+
+def _worker(rank, world, port, out_dir):
+    import torch.distributed as dist
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)          # plumbing only: ships the NCCL unique id
+    import hfb200
+    from hfb200 import workloads as wl
+    torch.cuda.set_device(rank)
+    dev = torch.device("cuda", rank)
+    hs, img, spp, tile = 256, 128, 8, 16
+    cam = wl.CONFIGS["C1"]["camera"]
+    h = wl.sine_heights(hs, device=dev)
+
+    def trace(shape, pix):
+        o, d = wl.camera_rays(cam["origin"], cam["target"], cam["up"], cam["fov"], img, img, spp, seed=3, device=dev, pixels=pix)
+        ray = hfb200.Ray3f(o, d, device=dev)
+        adj = wl.hashed_adjoints(o.shape[1], seed=1, device=dev, ids=wl.global_ray_ids(pix, spp))
+        si, pi = shape.ray_intersect(ray, return_prelim=True, fields=("t", "p", "n", "uv"))
+        shape.backward(ray, pi, adj)
+
+    def new_id():
+        ids = [hfb200.comm_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(ids, src=0)
+        return ids[0]
+
+    shape = hfb200.load_dict({"type": "heightfield", "heights": h, "max_height": 0.25}, device=dev)
+    ptr_before = shape.grad.data_ptr()
+    shape.comm_init(rank, world, new_id())
+    ptr_after = shape.grad.data_ptr()
+    moved = ptr_after != ptr_before                        # the grid moves into ncclMemAlloc memory when NCCL offers it
+    my_pix = wl.tile_pixels(img, img, tile, rank, world, device=dev)
+
+    results = {}
+    for attempt in ("first communicator", "second hf_comm_init on the same context", "after hf_comm_destroy"):
+        if attempt.startswith("second"):
+            shape.comm_init(rank, world, new_id())
+        elif attempt.startswith("after"):
+            from hfb200 import _load, _check
+            _check(_load().hf_comm_destroy(shape._ctx))
+            shape.comm_init(rank, world, new_id())
+        assert shape.grad.data_ptr() == ptr_after, "the gradient grid must stay where the first hf_comm_init put it"
+        shape.zero_grad()
+        trace(shape, my_pix)
+        torch.cuda.synchronize()
+        local = shape.grad.double().clone()                # hf_grad()'s NEW pointer must be the buffer the backward kernel wrote
+        assert float(local.abs().sum()) > 0, "backward did not land in the buffer hf_grad() returns after hf_comm_init"
+        shape.allreduce_grad()
+        torch.cuda.synchronize()
+        results[attempt] = shape.grad.double().cpu()
+        # every rank holds the same bits after the allreduce (replicas stay identical)
+        mine = shape.grad.clone().cpu()
+        gathered = [None] * world
+        dist.all_gather_object(gathered, mine.numpy().tobytes())
+        assert all(g == gathered[0] for g in gathered), "ranks disagree on the all-reduced gradient"
+        # and the sum of the per-rank grids is what came out
+        parts = [None] * world
+        dist.all_gather_object(parts, local.cpu().numpy())
+        total = np.sum(parts, axis=0)
+        assert np.linalg.norm(results[attempt].numpy() - total) <= 1e-5 * np.linalg.norm(total)
+
+    if rank == 0:
+        one = hfb200.load_dict({"type": "heightfield", "heights": h, "max_height": 0.25}, device=dev)
+        all_pix = torch.arange(img * img, dtype=torch.int64, device=dev)
+        one.zero_grad()
+        trace(one, all_pix)
+        torch.cuda.synchronize()
+        g1 = one.grad.double().cpu().numpy()
+        for k, g in results.items():
+            err = np.linalg.norm(g.numpy() - g1) / np.linalg.norm(g1)
+            assert err < 1e-4, f"{k}: all-reduced gradient differs from the single-rank gradient by {err:.2e}"
+        # the oracle on the whole batch (fp64 accumulation)
+        from oracle import hf_oracle as O
+        o, d = wl.camera_rays(cam["origin"], cam["target"], cam["up"], cam["fov"], img, img, spp, seed=3, pixels=all_pix.cpu())
+        adj = wl.hashed_adjoints(o.shape[1], seed=1, ids=wl.global_ray_ids(all_pix.cpu(), spp))
+        ref = O.OracleHeightfield(h.cpu().numpy(), 0.25)
+        r = O.Rays(o.numpy().T, d.numpy().T)
+        a = {"t": adj["t"].numpy(), "px": adj["p"][0].numpy(), "py": adj["p"][1].numpy(), "pz": adj["p"][2].numpy(),
+             "nx": adj["n"][0].numpy(), "ny": adj["n"][1].numpy(), "nz": adj["n"][2].numpy(),
+             "uvx": adj["uv"][0].numpy(), "uvy": adj["uv"][1].numpy()}
+        rg = ref.backward(r, ref.ray_intersect_preliminary(r), a, literal=False)
+        err = np.linalg.norm(results["first communicator"].numpy() - rg) / np.linalg.norm(rg)
+        assert err < 1e-4, f"all-reduced gradient vs oracle fp64: {err:.2e}"
+        with open(os.path.join(out_dir, "ok"), "w") as f:
+            f.write(f"moved={moved} err_vs_oracle={err:.3e}\n")
+    dist.barrier()
+    del shape
+    dist.destroy_process_group()
+
+
+@pytest.mark.skipif(_ngpu() < 2, reason=f"needs >= 2 GPUs on one box (found {_ngpu()}); host logic is covered by tests/test_sharding.py over gloo")
+def test_allreduced_gradient_equals_single_rank_gradient(tmp_path):
+    import torch.multiprocessing as mp
+    world = 2
+    port = 29700 + (os.getpid() % 2000)
+    mp.spawn(_worker, args=(world, port, str(tmp_path)), nprocs=world, join=True)
+    assert os.path.exists(tmp_path / "ok")
+    print(open(tmp_path / "ok").read())

@@ -428,6 +428,56 @@ def test_host_api_matches_device_api(hf, oracle):
     assert _same_bits(hp["t"].numpy()[idx], pc.t).all()
 
 
+def test_host_api_every_si_field_and_empty_batch(hf, oracle):
+    """hf_ray_intersect_host / hf_forward_backward_host with ALL 27 surface-interaction members requested (the staging slab is
+    derived from sizeof(hf_si): wi_z used to be left without a slot), compared bit for bit with the device API; then the n == 0 call
+    that only reads the gradient grid back (null rays allowed)."""
+    import hfb200
+    from hfb200 import workloads as wl
+    rng = np.random.default_rng(33)
+    H, W = 90, 120
+    g, c = _mk(hf, oracle, random_heights(rng, H, W), 0.5, to_world=AFFINE)
+    n = 70001
+    o, d = wl.hemisphere_rays(n, seed=9)
+    ray = hf.Ray3f(o, d)
+    si, pi = g.ray_intersect(ray, return_prelim=True)                  # every field
+    want = _si_dict(si)
+    pin = lambda x: x.contiguous().pin_memory()
+    hr = {"ox": pin(o[0]), "oy": pin(o[1]), "oz": pin(o[2]), "dx": pin(d[0]), "dy": pin(d[1]), "dz": pin(d[2]),
+          "maxt": pin(torch.full((n,), float("inf")))}
+    hs = {k: torch.full((n,), float("nan")).pin_memory() for k in hfb200.SI_FIELDS}
+    hp = {"t": torch.empty(n).pin_memory(), "u": torch.empty(n).pin_memory(), "v": torch.empty(n).pin_memory(),
+          "prim_index": torch.empty(n, dtype=torch.int32).pin_memory()}
+    torch.cuda.synchronize()
+    g.ray_intersect_host(hr, hs, n, h_prelim=hp)
+    assert len(hfb200.SI_FIELDS) == 27
+    for k in hfb200.SI_FIELDS:
+        assert not torch.isnan(hs[k]).any(), f"host API left {k} unwritten"
+        assert _same_bits(hs[k].numpy(), want[k]).all(), k
+    assert torch.equal(hp["prim_index"], pi.prim_index.cpu())
+    # forward + backward through the host entry with every field as well
+    adj = wl.hashed_adjoints(n, seed=4)
+    ha = {"t": pin(adj["t"]), "px": pin(adj["p"][0]), "py": pin(adj["p"][1]), "pz": pin(adj["p"][2]),
+          "nx": pin(adj["n"][0]), "ny": pin(adj["n"][1]), "nz": pin(adj["n"][2]), "uvx": pin(adj["uv"][0]), "uvy": pin(adj["uv"][1])}
+    g.zero_grad(); g.backward(ray, pi, adj)
+    torch.cuda.synchronize()
+    grad_dev = g.grad.clone().cpu()
+    for k in hs:
+        hs[k].fill_(float("nan"))
+    hg = torch.empty(H, W).pin_memory()
+    g.zero_grad()
+    torch.cuda.synchronize()
+    g.forward_backward_host(hr, ha, hs, hg, n, h_prelim=hp)
+    for k in hfb200.SI_FIELDS:
+        assert _same_bits(hs[k].numpy(), want[k]).all(), k
+    assert torch.allclose(hg, grad_dev, rtol=1e-4, atol=1e-5 * float(grad_dev.abs().max()))
+    # n == 0: nothing to trace, the call only copies the gradient grid out (rays may be null)
+    hg2 = torch.zeros(H, W).pin_memory()
+    g.forward_backward_host({}, {}, {}, hg2, 0)
+    assert torch.equal(hg2, hg)
+    g.forward_backward_host({}, {}, {}, None, 0)                         # and the fully empty call is a no-op
+
+
 # ---- full-size properties (sizes the oracle cannot finish: size-independent invariants) -------------------------
 def test_full_size_invariants(hf, oracle):
     """4096^2 heights (BASELINE.json C3 field), 4 M primary rays: p = o + t d, hits inside the bbox, ray_test ==

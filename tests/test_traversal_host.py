@@ -174,3 +174,59 @@ def test_bundle_march_on_camera_rays(oracle, trav):
     assert _same(ref, got).all()
     hitb = ref.valid().reshape(-1, 32).any(1)
     assert (te[hitb] > 0).mean() > 0.9     # nearly every hit bundle skipped part of its way
+
+
+@pytest.mark.parametrize("case", ["offset", "flat0", "flat_high", "negative", "tiny", "far_origin", "steep"])
+def test_walk_code_space_extremes(oracle, trav, case):
+    """The walk compares z in CODE units (hf_traverse.cuh, HF_CODE_SPACE): fields whose z range is tiny next to their magnitude, flat
+    fields (degenerate code step), negative max_height, denormal-small heights, ray origins far outside the code range. The closest
+    hit must still be the canonical one, bit for bit."""
+    O = oracle
+    rng = np.random.default_rng(hash(case) % 1000 + 5)
+    H, W, mh = 40, 33, 0.7
+    h = random_heights(rng, H, W, "smooth")
+    if case == "offset":
+        h, mh = (0.9999 + 1e-4 * h).astype(np.float32), 100.0          # z in [99.99, 100]: range / magnitude = 1e-4
+    elif case == "flat0":
+        h = np.zeros((H, W), np.float32)
+    elif case == "flat_high":
+        h, mh = np.full((H, W), 1.0, np.float32), 1000.0
+    elif case == "negative":
+        mh = -0.7
+    elif case == "tiny":
+        h = (h * 1e-30).astype(np.float32)
+    elif case == "steep":
+        h = rng.uniform(0, 1, (H, W)).astype(np.float32); mh = 50.0
+    hf = O.OracleHeightfield(h, mh)
+    zc = float(np.mean(h) * mh)
+    n = 60000
+    o, d = random_rays(rng, n)
+    o[:, 2] = o[:, 2] * (abs(mh) if case in ("steep",) else 1.0) + (zc if case in ("offset", "flat_high") else 0.0)
+    tgt = np.stack([rng.uniform(-1.1, 1.1, n), rng.uniform(-1.1, 1.1, n), zc + rng.uniform(-0.3, 0.3, n) * (abs(mh) if case == "steep" else 1.0)], 1)
+    if case == "far_origin":
+        o = (o * np.float32([1, 1, 3e4])).astype(np.float32)              # |z| up to 1e5: 10^10 codes away
+    d = (tgt - o).astype(np.float32)
+    ao, ad = adversarial_rays(W, H, mh)
+    ao[:, 2] += np.float32(zc if case in ("offset", "flat_high") else 0.0)
+    o, d = np.concatenate([o.astype(np.float32), ao]), np.concatenate([d, ad])
+    r = O.Rays(o, d, np.full(o.shape[0], np.inf, np.float32))
+    ref = hf.ray_intersect_preliminary(r)
+    got, _ = _run(trav, O, hf, r, beam=False)
+    assert ref.valid().sum() > 1000
+    assert _same(ref, got).all()
+
+
+def test_prim_index_division_by_multiplication(tmp_path):
+    """csrc/hf_divmagic.h: floor(n / d) == (n * m) >> (31 + l) for every 31-bit numerator; checked on the divisors heightfields
+    produce (W - 1) and on the numerators around every multiple of d."""
+    src = tmp_path / "dm.cpp"
+    src.write_text('#include "%s"\n#include <stdio.h>\nint main(){ unsigned ds[] = {1,2,3,4,5,7,15,16,17,63,255,256,1023,4095,4096,8191,16383,16384,65535,'
+                   '1000003,8388606,8388607}; unsigned long long bad = 0, tot = 0; for (unsigned d : ds) { HfDivMagic m = hf_divmagic(d);'
+                   ' for (unsigned long long q = 0; q * d < 0x7fffffffull; q += (0x7fffffffull / d) / 4099 + 1) for (long long e = -2; e <= 2; ++e) {'
+                   ' long long n = (long long) (q * d) + e; if (n < 0 || n > 0x7fffffffll) continue; ++tot; if (hf_divide((unsigned) n, m.m, m.s) != (unsigned) n / d) ++bad; }'
+                   ' for (unsigned long long n = 0x7fffffffull - 70000; n <= 0x7fffffffull; ++n) { ++tot; if (hf_divide((unsigned) n, m.m, m.s) != (unsigned) n / d) ++bad; } }'
+                   ' printf("%%llu %%llu\\n", bad, tot); return bad != 0; }\n' % os.path.join(ROOT, "mitsuba3-differentiable-heightfield-rendering_b200", "csrc", "hf_divmagic.h"))
+    exe = str(tmp_path / "dm")
+    subprocess.check_call(["g++", "-O2", "-std=c++17", "-o", exe, str(src)])
+    out = subprocess.check_output([exe]).decode().split()
+    assert out[0] == "0" and int(out[1]) > 1000000

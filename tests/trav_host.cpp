@@ -55,7 +55,7 @@ struct HostQPyr {
     }
     void attach(HfGrid &G, float top_min, float top_max) const {
         const HfQuant Q = hf_quant_make(top_min, top_max);
-        G.qlvl = lvl.data(); G.qlvl_saddr = 0; G.QLtop = lay.Ltop; G.xmask = lay.Mx - 1; G.ymask = lay.My - 1; G.qs = Q.qs; G.zb = Q.zb;
+        G.qlvl = lvl.data(); G.qlvl_saddr = 0; G.QLtop = lay.Ltop; G.xmask = lay.Mx - 1; G.ymask = lay.My - 1; G.qs = Q.qs; G.zb = Q.zb; G.rqs = Q.rqs;
     }
 };
 
