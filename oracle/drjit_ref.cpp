@@ -20,6 +20,7 @@
 #include <drjit/array.h>
 #include <drjit/packet.h>
 #include <cmath>
+#include <cstddef>
 #include <cstdint>
 
 namespace dr = drjit;
@@ -80,6 +81,37 @@ void ref_transform_vector(const float *m, const float *v_, float *out) {
     r = dr::fmadd(col1, FP(v_[1]), r);
     r = dr::fmadd(col2, FP(v_[2]), r);
     for (int i = 0; i < 3; ++i) out[i] = r[i][0];
+}
+
+// Whole-heightfield brute force THROUGH the arithmetic above: the mesh of DESIGN.md section 2 (vertex
+// P(i,j) = (X(i), Y(j), max_height h[j W + i]), cell (cx,cy) -> triangle 0 = (p10, p01, p00), triangle 1 = (p10, p11, p01), the
+// "procedural mesh" pattern of src/shapes/cube.cpp:106-163) is enumerated triangle by triangle, the ray is taken to object space by
+// transform_affine (src/shapes/rectangle.cpp:206-214, t preserved) and every triangle goes through the Moeller-Trumbore sequence of
+// include/mitsuba/render/mesh.h:357-380 in Dr.Jit arrays. Closest hit, tie: smaller prim_index. This ties hit mask / prim_index /
+// t / uv of whole heightfields to reference-compiled code rather than to the C restatement (the heightfield LAYOUT stays this
+// repo's definition: the plugin is absent from the snapshot).
+void ref_heightfield_brute_force(const float *h, int W, int H, float max_height, const float *to_object,
+                                 const float *o_, const float *d_, const float *maxt, size_t n,
+                                 float *t_out, float *u_out, float *v_out, uint32_t *prim_out) {
+    const float rw = 1.0f / (float) (W - 1), rh = 1.0f / (float) (H - 1);
+    for (size_t r = 0; r < n; ++r) {
+        float oo[3], dd[3];
+        ref_transform_affine_point(to_object, o_ + 3 * r, oo);
+        ref_transform_vector(to_object, d_ + 3 * r, dd);
+        float best = INFINITY, bu = 0.f, bv = 0.f; uint32_t bp = 0;
+        for (int cy = 0; cy < H - 1; ++cy)
+            for (int cx = 0; cx < W - 1; ++cx) {
+                const float x0 = (float) (2 * cx - (W - 1)) * rw, x1 = (float) (2 * (cx + 1) - (W - 1)) * rw;
+                const float y0 = (float) (2 * cy - (H - 1)) * rh, y1 = (float) (2 * (cy + 1) - (H - 1)) * rh;
+                const float p00[3] = { x0, y0, max_height * h[(size_t) cy * W + cx] }, p10[3] = { x1, y0, max_height * h[(size_t) cy * W + cx + 1] };
+                const float p01[3] = { x0, y1, max_height * h[(size_t) (cy + 1) * W + cx] }, p11[3] = { x1, y1, max_height * h[(size_t) (cy + 1) * W + cx + 1] };
+                float t, u, v;
+                const uint32_t base = 2u * ((uint32_t) cy * (uint32_t) (W - 1) + (uint32_t) cx);
+                if (ref_moeller_trumbore(oo, dd, maxt[r], p10, p01, p00, &t, &u, &v) && t < best) { best = t; bu = u; bv = v; bp = base; }
+                if (ref_moeller_trumbore(oo, dd, maxt[r], p10, p11, p01, &t, &u, &v) && t < best) { best = t; bu = u; bv = v; bp = base + 1u; }
+            }
+        t_out[r] = best; u_out[r] = bu; v_out[r] = bv; prim_out[r] = bp;
+    }
 }
 
 }  // extern "C"

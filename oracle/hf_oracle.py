@@ -136,12 +136,29 @@ def ref_lib():
         R.ref_interpolate_and_normal.argtypes = [_f32p, _f32p, _f32p, C.c_float, C.c_float, _f32p, _f32p]
         R.ref_transform_affine_point.argtypes = [_f32p, _f32p, _f32p]
         R.ref_transform_vector.argtypes = [_f32p, _f32p, _f32p]
+        if hasattr(R, "ref_heightfield_brute_force"):
+            R.ref_heightfield_brute_force.argtypes = [_f32p, C.c_int, C.c_int, C.c_float, _f32p, _f32p, _f32p, _f32p, C.c_size_t,
+                                                      _f32p, _f32p, _f32p, _u32p]
         _ref = R
     return _ref
 
 
 def _fp(a):
     return a.ctypes.data_as(_f32p) if a is not None else None
+
+
+def ref_heightfield_brute_force(heights, max_height, to_object, o, d, maxt):
+    """Closest hit of every ray over ALL triangles of the heightfield, evaluated by the reference's own Dr.Jit header arithmetic
+    (oracle/drjit_ref.cpp). heights (H, W); to_object 12 floats; o, d (N, 3); returns (t, u, v, prim_index)."""
+    R = ref_lib()
+    assert R is not None and hasattr(R, "ref_heightfield_brute_force"), "oracle/_ref is not built (needs /root/reference)"
+    h = _f32(heights); oo = _f32(o); dd = _f32(d); mt = _f32(maxt); to = _f32(np.asarray(to_object).reshape(-1)[:12])
+    n = oo.shape[0]
+    t, u, v = np.empty(n, np.float32), np.empty(n, np.float32), np.empty(n, np.float32)
+    prim = np.empty(n, np.uint32)
+    R.ref_heightfield_brute_force(_fp(h), h.shape[1], h.shape[0], float(max_height), _fp(to), _fp(oo), _fp(dd), _fp(mt), n,
+                                  _fp(t), _fp(u), _fp(v), prim.ctypes.data_as(_u32p))
+    return t, u, v, prim
 
 
 def _f32(a):

@@ -78,3 +78,40 @@ def test_product_package_never_imports_the_oracle():
                 s = open(os.path.join(dirpath, f)).read()
                 bad = re.findall(r"#include[^\n]*oracle|^\s*(?:from|import)\s+oracle|libhf_oracle|oracle/_build|oracle/_ref|hfo_[a-z_]+\s*\(", s, flags=re.M)
                 assert not bad, (f, bad)
+
+
+# ---- the C++ host class (include/hf_heightfield.hpp) ---------------------------------------------------------------------------
+def test_cpp_host_class_compiles_standalone_and_mirrors_the_shape_virtuals(tmp_path):
+    """The header needs nothing but hf_b200.h (no CUDA headers) and declares the Shape methods the plugin provides, in the
+    reference's order (include/mitsuba/render/shape.h:137-197, 253, 432, 533-550)."""
+    import subprocess
+    src = tmp_path / "tu.cpp"
+    src.write_text('#include "hf_heightfield.hpp"\nint main() { return sizeof(hf::Heightfield) > 0 ? 0 : 1; }\n')
+    subprocess.check_call(["g++", "-std=c++17", "-fsyntax-only", "-Wall", "-Wextra", "-Werror", "-I" + os.path.join(ROOT, "include"), str(src)])
+    hpp = open(os.path.join(ROOT, "include", "hf_heightfield.hpp")).read()
+    body = hpp[hpp.index("class Heightfield {"):]
+    order = ["ray_intersect_preliminary(", "ray_test(", "compute_surface_interaction(", "ray_intersect(", "bbox()", "primitive_count()",
+             "void traverse(", "void parameters_changed(", "parameters_grad_enabled()"]
+    pos = [body.index(" " + m if not m.startswith("void") else m) for m in order]
+    assert pos == sorted(pos), "methods are not in the order of the reference's Shape interface"
+
+
+def test_cpp_smoke_binary_is_built(lib):
+    import __graft_entry__
+    exe = os.path.join(ROOT, "tests", "cpp", "abi_smoke")
+    if not os.path.exists(exe):
+        __graft_entry__.build_cpp_smoke()
+    assert os.access(exe, os.X_OK)
+
+
+@pytest.mark.gpu
+def test_cpp_host_class_on_the_gpu(lib):
+    """tests/cpp/abi_smoke.cpp: hf::Heightfield from plain C++ -- the reference's known answers (test_mesh.py test10 / test16) on the
+    flat 2x2 field, bbox / traverse / parameters_changed, exceptions with the reference's messages."""
+    import subprocess
+    import __graft_entry__
+    exe = os.path.join(ROOT, "tests", "cpp", "abi_smoke")
+    if not os.path.exists(exe):
+        __graft_entry__.build_cpp_smoke()
+    r = subprocess.run([exe], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0 and "abi_smoke ok" in r.stdout, r.stdout + r.stderr

@@ -154,6 +154,33 @@ def test_capture_replays_the_step(hf, oracle):
 
 
 # ---- the reference's known answers, on the GPU ---------------------------------------------------------
+def test_gpu_matches_drjit_heightfield_golden(hf, oracle):
+    """DIRECT link GPU <-> reference-compiled arithmetic: tests/golden/drjit_heightfield.npz holds whole-heightfield closest hits
+    evaluated by the reference's own Dr.Jit headers over every triangle (oracle/make_golden_heightfield.py). The CUDA walk must give
+    the same mask / prim_index / t / u / v bit for bit away from cell-edge ties. (The per-triangle vectors of drjit_triangle.npz are
+    arbitrary triangles, which no heightfield cell can express: that link is transitive, through the oracle.)"""
+    import os
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "drjit_heightfield.npz"))
+    for name in ("a", "b", "c"):
+        c = {k[len(name) + 1:]: g[k] for k in g.files if k.startswith(name + "_")}
+        shape = hf.load_dict({"type": "heightfield", "heights": torch.from_numpy(c["h"]), "max_height": float(c["mh"]),
+                              "to_world": c["to_world"], "to_object": c["to_object"]})
+        ray = hf.Ray3f(torch.from_numpy(c["o"].T.copy()), torch.from_numpy(c["d"].T.copy()), torch.from_numpy(c["maxt"]))
+        pi = shape.ray_intersect_preliminary(ray)
+        t, u, v = _np(pi.t), _np(pi.prim_uv[0]), _np(pi.prim_uv[1])
+        prim = _np(pi.prim_index).view(np.uint32)
+        rv, gv = np.isfinite(c["t"]), np.isfinite(t)
+        diff = (rv != gv) | (gv & ((prim != c["prim"]) | ~_same_bits(t, c["t"]) | ~_same_bits(u, c["u"]) | ~_same_bits(v, c["v"])))
+        edge = lambda uu, vv: np.minimum.reduce([np.abs(uu), np.abs(vv), np.abs(1 - uu - vv)])
+        near = (rv & (edge(c["u"], c["v"]) < 1e-5)) | (gv & (edge(u, v) < 1e-5))
+        with np.errstate(invalid="ignore"):
+            t_tie = rv & gv & (np.abs(c["t"] - t) <= 4 * np.spacing(np.abs(c["t"])))
+        bad = diff & ~near & ~t_tie
+        assert bad.sum() == 0, f"case {name}: {int(bad.sum())} rays differ from the reference arithmetic away from ties"
+        assert diff[:2500].mean() < 2e-3 and gv.sum() > 1000
+        assert np.array_equal(_np(shape.ray_test(ray)), gv)
+
+
 def test_test10_known_answers(hf, oracle):
     """src/render/tests/test_mesh.py:257-292 on the flat 2x2 field (== rectangle.obj)."""
     g, _ = _mk(hf, oracle, np.zeros((2, 2), f32))
