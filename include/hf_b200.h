@@ -110,6 +110,7 @@ typedef struct {
 
 typedef struct {
     uint64_t rays, nodes, leaves, hits;   /* accumulated by the *_counted intersect entry */
+    uint64_t segments;                    /* ray segments (camera, bounce, visibility) traced by the path-tracing render entries (max_depth > 1) */
 } hf_stats;
 
 /* ---- life cycle ---------------------------------------------------------------------- */
@@ -243,6 +244,13 @@ int hf_ray_intersect_host(hf_ctx *ctx, const hf_rays *h_rays, uint32_t ray_flags
  * the context's device grad grid and, when h_grad_out != NULL, copied out (height*width floats). */
 int hf_forward_backward_host(hf_ctx *ctx, const hf_rays *h_rays, const hf_si_adj *h_adj, uint32_t ray_flags,
                              const hf_prelim *h_prelim_out, const hf_si *h_out, float *h_grad_out, size_t n);
+
+/* the optimisation step (hf_render_step_l2) for a caller whose arrays live in host memory: h_heights (nullable: keep the device copy;
+ * otherwise uploaded and the acceleration data rebuilt), the target image and the pixel list (nullable = every pixel) go in; the image
+ * (nullable; pixels not rendered are 0), the gradient grid d(loss)/d(heights) (nullable; height*width floats) and the loss (nullable)
+ * come out. Zeroes the gradient grid first. Returns after everything has landed. */
+int hf_render_step_l2_host(hf_ctx *ctx, const hf_camera *cam, const hf_light *light, const uint32_t *h_pixels, size_t npix,
+                           const float *h_heights, const float *h_target, float *h_image_out, float *h_grad_out, double *h_loss_out);
 
 #ifdef __cplusplus
 }

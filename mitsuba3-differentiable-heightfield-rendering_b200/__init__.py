@@ -105,7 +105,7 @@ class _Light(C.Structure):
 
 
 class _Stats(C.Structure):
-    _fields_ = [(k, C.c_uint64) for k in ("rays", "nodes", "leaves", "hits")]
+    _fields_ = [(k, C.c_uint64) for k in ("rays", "nodes", "leaves", "hits", "segments")]
 
 
 _lib = None
@@ -161,6 +161,7 @@ def _load():
         "hf_host_free": [vp],
         "hf_ray_intersect_host": [vp, C.POINTER(_Rays), u32, C.POINTER(_Prelim), C.POINTER(_SI), sz],
         "hf_forward_backward_host": [vp, C.POINTER(_Rays), C.POINTER(_Adj), u32, C.POINTER(_Prelim), C.POINTER(_SI), vp, sz],
+        "hf_render_step_l2_host": [vp, C.POINTER(_Camera), C.POINTER(_Light), vp, sz, vp, vp, vp, vp, C.POINTER(C.c_double)],
     }
     for name, args in sig.items():
         fn = getattr(L, name)
@@ -539,7 +540,7 @@ class Heightfield:
     def stats(self, reset=True):
         s = _Stats()
         _check(_load().hf_stats_get(self._ctx, C.byref(s), int(reset)))
-        return {"rays": s.rays, "nodes": s.nodes, "leaves": s.leaves, "hits": s.hits}
+        return {"rays": s.rays, "nodes": s.nodes, "leaves": s.leaves, "hits": s.hits, "segments": s.segments}
 
     # -- optimiser / multi-GPU --------------------------------------------------------------
     def adam_step(self, lr, beta_1=0.9, beta_2=0.999, epsilon=1e-8, mask_updates=False):
@@ -635,6 +636,17 @@ class Heightfield:
         with torch.cuda.device(self.device):
             _check(_load().hf_ray_intersect_host(self._ctx, C.byref(r), int(ray_flags),
                                                  C.byref(p) if p is not None else None, C.byref(s), n))
+
+    def render_step_l2_host(self, cam: dict, light: dict, h_target, h_heights=None, h_image=None, h_grad=None, h_pixels=None):
+        """The optimisation step with HOST tensors (pinned for full PCIe speed): heights (optional) + target in, image / gradient
+        grid (optional) + loss out. Returns the loss (float)."""
+        c, l = _camera_struct(cam), _light_struct(light)
+        npix = c.width * c.height if h_pixels is None else h_pixels.numel()
+        loss = C.c_double(0.0)
+        with torch.cuda.device(self.device):
+            _check(_load().hf_render_step_l2_host(self._ctx, C.byref(c), C.byref(l), _ptr(h_pixels), npix, _ptr(h_heights), _ptr(h_target),
+                                                  _ptr(h_image), _ptr(h_grad), C.byref(loss)))
+        return loss.value
 
     def __repr__(self):
         return (f"Heightfield[\n  size = {self.W}x{self.H},\n  max_height = {self._max_height},\n"

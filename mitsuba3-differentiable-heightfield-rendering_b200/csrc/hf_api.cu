@@ -98,6 +98,7 @@ static int nccl_load() {
 #define HF_SCHED_SLOTS 256            // every eager launch of a self-scheduling kernel gets its own counter (launches on different streams overlap)
 #define HF_SCHED_CAPTURE_SLOTS 1024   // launches recorded into a CUDA graph get a counter of their own for good: a graph bakes the pointer in
                                       // and may replay beside eager launches long after the eager ring has wrapped around
+#define HF_ADAM_TABLE 65536            // bias corrections tabulated per (beta1, beta2); 0.999^65535 ~ 3e-29: converged long before the end
 #define HF_TOP_NODE_CAP 1366          // (32^2 + 16^2 + ... + 1) rounded up to even: 10.9 KB of shared memory
 #ifndef HF_HOST_CHUNK_LOG2
 #define HF_HOST_CHUNK_LOG2 21
@@ -146,14 +147,23 @@ struct hf_ctx {
     size_t scratch_bytes = 0;
     bool have_heights = false, accel_valid = false;
     int grad_enabled = 1;
-    int adam_t = 0;
+    // Adam: step counter + lr_t on the device (graph replays advance t), bias-correction table per (beta1, beta2)
+    int *d_adam_t = nullptr;
+    float *d_adam_lr_t = nullptr, *d_adam_table = nullptr;
+    double tab_b1 = -1.0, tab_b2 = -1.0;
     hf_nccl_comm comm = nullptr;
     int nranks = 1, rank = 0;
     HostSlot slots[HF_HOST_SLOTS];
     cudaStream_t s_in = nullptr, s_k = nullptr, s_out = nullptr;   // host pipeline: one stream per copy engine + one for the kernels
     cudaEvent_t ev_entry = nullptr;
     cudaEvent_t ev_accel = nullptr;   // recorded behind the last pyramid build (hf_bbox waits for it instead of the whole device)
+    bool accel_event_ok = false;
     bool slots_ready = false;
+    // host-buffer render step: device copies of the caller's target / image / pixel list, and the loss
+    float *d_hs_target = nullptr, *d_hs_image = nullptr;
+    uint32_t *d_hs_pixels = nullptr;
+    double *d_hs_loss = nullptr;
+    size_t hs_img_elems = 0, hs_pix_elems = 0;
 };
 
 static void invert_affine(const float m[12], float out[12]) {
@@ -303,6 +313,7 @@ extern "C" int hf_create(hf_ctx **out, const hf_desc *desc) {
     P.heights = c->d_heights;
     P.pyr = c->d_pyr;
     P.qpyr = c->d_qpyr;
+    c->li.seg_counter = c->d_counters + 4;
     *out = c;
     return HF_OK;
 }
@@ -325,6 +336,8 @@ extern "C" int hf_destroy(hf_ctx *c) {
     if (c->s_k) cudaStreamDestroy(c->s_k);
     if (c->s_out) cudaStreamDestroy(c->s_out);
     cudaFree(c->d_heights); cudaFree(c->d_grad); cudaFree(c->d_m); cudaFree(c->d_v); cudaFree(c->d_pyr); cudaFree(c->d_qpyr); cudaFree(c->d_counters); cudaFree(c->d_scratch);
+    cudaFree(c->d_adam_t); cudaFree(c->d_adam_lr_t); cudaFree(c->d_adam_table);
+    cudaFree(c->d_hs_target); cudaFree(c->d_hs_image); cudaFree(c->d_hs_pixels); cudaFree(c->d_hs_loss);
     delete c;
     return HF_OK;
 }
@@ -385,7 +398,12 @@ extern "C" int hf_parameters_changed(hf_ctx *c, void *stream) {
     CU(cudaSetDevice(c->device));
     CU(hf_launch_pyramid(c->P, c->d_pyr, c->d_qpyr, (cudaStream_t) stream));
     if (!c->ev_accel) CU(cudaEventCreateWithFlags(&c->ev_accel, cudaEventDisableTiming));
-    CU(cudaEventRecord(c->ev_accel, (cudaStream_t) stream));
+    {   // an event recorded inside a stream capture cannot be waited for from the host: hf_bbox then synchronises the device instead
+        cudaStreamCaptureStatus st = cudaStreamCaptureStatusNone;
+        if (cudaStreamIsCapturing((cudaStream_t) stream, &st) != cudaSuccess) { cudaGetLastError(); st = cudaStreamCaptureStatusNone; }
+        c->accel_event_ok = (st != cudaStreamCaptureStatusActive);
+        if (c->accel_event_ok) CU(cudaEventRecord(c->ev_accel, (cudaStream_t) stream));
+    }
     c->accel_valid = true;
     return HF_OK;
 }
@@ -422,7 +440,8 @@ extern "C" int hf_bbox(hf_ctx *c, float out[6]) {
     NEED_ACCEL(c);
     CU(cudaSetDevice(c->device));
     float2 top;
-    CU(cudaEventSynchronize(c->ev_accel));      // the pyramid build this bbox derives from (whatever stream it ran on)
+    if (c->accel_event_ok) CU(cudaEventSynchronize(c->ev_accel));      // the pyramid build this bbox derives from (whatever stream it ran on)
+    else CU(cudaDeviceSynchronize());
     CU(cudaMemcpy(&top, c->d_pyr + c->P.lvl_off[c->P.Ltop], sizeof(float2), cudaMemcpyDeviceToHost));
     const HfParams &P = c->P;
     float lo[3] = { P.x0, P.y0, top.x };
@@ -466,7 +485,8 @@ extern "C" int hf_qpyramid_level(hf_ctx *c, uint32_t level, uint32_t *levels, ui
         NEED_ACCEL(c);
         CU(cudaSetDevice(c->device));
         float2 top;
-        CU(cudaEventSynchronize(c->ev_accel));
+        if (c->accel_event_ok) CU(cudaEventSynchronize(c->ev_accel));
+        else CU(cudaDeviceSynchronize());
         CU(cudaMemcpy(&top, c->d_pyr + P.lvl_off[P.Ltop], sizeof(float2), cudaMemcpyDeviceToHost));
         const HfQuant q = hf_quant_make(top.x, top.y);
         if (qs) *qs = q.qs;
@@ -527,10 +547,10 @@ extern "C" int hf_stats_get(hf_ctx *c, hf_stats *out, int reset) {
     CHECK_CTX(c);
     if (!out) return fail(HF_ERR_INVALID, "null out pointer");
     CU(cudaSetDevice(c->device));
-    unsigned long long h[4];
+    unsigned long long h[5];
     CU(cudaDeviceSynchronize());
     CU(cudaMemcpy(h, c->d_counters, sizeof(h), cudaMemcpyDeviceToHost));
-    out->rays = h[0]; out->nodes = h[1]; out->leaves = h[2]; out->hits = h[3];
+    out->rays = h[0]; out->nodes = h[1]; out->leaves = h[2]; out->hits = h[3]; out->segments = h[4];
     if (reset) CU(cudaMemset(c->d_counters, 0, sizeof(h)));
     return HF_OK;
 }
@@ -608,9 +628,10 @@ extern "C" int hf_adam_reset(hf_ctx *c, void *stream) {
     const size_t bytes = (size_t) c->W * c->H * sizeof(float);
     if (!c->d_m) { CU(cudaMalloc(&c->d_m, bytes)); }
     if (!c->d_v) { CU(cudaMalloc(&c->d_v, bytes)); }
+    if (!c->d_adam_t) { CU(cudaMalloc(&c->d_adam_t, sizeof(int))); CU(cudaMalloc(&c->d_adam_lr_t, sizeof(float))); }
     CU(cudaMemsetAsync(c->d_m, 0, bytes, (cudaStream_t) stream));
     CU(cudaMemsetAsync(c->d_v, 0, bytes, (cudaStream_t) stream));
-    c->adam_t = 0;
+    CU(cudaMemsetAsync(c->d_adam_t, 0, sizeof(int), (cudaStream_t) stream));
     return HF_OK;
 }
 
@@ -623,14 +644,25 @@ extern "C" int hf_adam_step(hf_ctx *c, const hf_adam *cfg, void *stream) {
     if (!c->have_heights) return fail(HF_ERR_STATE, "heights were never set");
     if (!c->d_m || !c->d_v) { int rc = hf_adam_reset(c, stream); if (rc) return rc; }
     CU(cudaSetDevice(c->device));
-    c->adam_t += 1;
     // optimizers.py:266-279. The hyper-parameters are Python floats (doubles) there: lr_scale and (1 - beta) are evaluated in double
     // and only then become fp32 literals of the traced expression; lr is an opaque fp32 (lr_v) multiplied by the fp32 lr_scale.
     const double b1 = cfg->beta1, b2 = cfg->beta2;
-    const float lr_scale = (float) (sqrt(1.0 - pow(b2, c->adam_t)) / (1.0 - pow(b1, c->adam_t)));
-    const float lr_t = (float) cfg->lr * lr_scale;
-    CU(hf_launch_adam(c->d_heights, c->d_grad, c->d_m, c->d_v, (size_t) c->W * c->H, lr_t, (float) b1, (float) b2,
-                      (float) (1.0 - b1), (float) (1.0 - b2), (float) cfg->epsilon, cfg->mask_updates, c->num_sms, (cudaStream_t) stream));
+    if (!c->d_adam_table || c->tab_b1 != b1 || c->tab_b2 != b2) {
+        // lr_scale(t) = sqrt(1 - beta2^t) / (1 - beta1^t) for t = 1 .. HF_ADAM_TABLE - 1, in double, rounded once (entry 0 unused)
+        cudaStreamCaptureStatus st = cudaStreamCaptureStatusNone;
+        if (cudaStreamIsCapturing((cudaStream_t) stream, &st) == cudaSuccess && st == cudaStreamCaptureStatusActive)
+            return fail(HF_ERR_STATE, "Adam: run one eager hf_adam_step with these betas before capturing it into a CUDA graph");
+        std::vector<float> tab(HF_ADAM_TABLE);
+        tab[0] = 1.f;
+        for (int t = 1; t < HF_ADAM_TABLE; ++t) tab[t] = (float) (sqrt(1.0 - pow(b2, t)) / (1.0 - pow(b1, t)));
+        if (!c->d_adam_table) CU(cudaMalloc(&c->d_adam_table, HF_ADAM_TABLE * sizeof(float)));
+        CU(cudaStreamSynchronize((cudaStream_t) stream));
+        CU(cudaMemcpy(c->d_adam_table, tab.data(), HF_ADAM_TABLE * sizeof(float), cudaMemcpyHostToDevice));
+        c->tab_b1 = b1; c->tab_b2 = b2;
+    }
+    CU(hf_launch_adam(c->d_heights, c->d_grad, c->d_m, c->d_v, (size_t) c->W * c->H, c->d_adam_t, c->d_adam_lr_t, c->d_adam_table,
+                      HF_ADAM_TABLE, (float) cfg->lr, (float) b1, (float) b2, (float) (1.0 - b1), (float) (1.0 - b2), (float) cfg->epsilon,
+                      cfg->mask_updates, c->num_sms, (cudaStream_t) stream));
     c->accel_valid = false;       // heights moved: the caller runs hf_parameters_changed (SceneParameters.update)
     return HF_OK;
 }
@@ -931,6 +963,55 @@ static int host_pipeline(hf_ctx *c, const hf_rays *hr, const hf_si_adj *hadj, ui
     CU(cudaStreamSynchronize(c->s_in));
     CU(cudaStreamSynchronize(c->s_k));
     CU(cudaStreamSynchronize(c->s_out));
+    return HF_OK;
+}
+
+// The optimisation step of BASELINE.json configs[2] for a caller whose arrays live in HOST memory: what crosses PCIe is the parameter
+// (heights, optional), the target image and the pixel list on the way in, and the image / gradient grid / loss on the way out --
+// no ray or interaction record exists anywhere. Everything runs on the pipeline's kernel stream, ordered after the legacy stream.
+extern "C" int hf_render_step_l2_host(hf_ctx *c, const hf_camera *cam, const hf_light *light, const uint32_t *h_pixels, size_t npix,
+                                      const float *h_heights, const float *h_target, float *h_image_out, float *h_grad_out,
+                                      double *h_loss_out) {
+    CHECK_CTX(c);
+    int rc;
+    if ((rc = check_camera(cam, true)) || (rc = check_light(light))) return rc;
+    const size_t img = (size_t) cam->width * cam->height;
+    if (!h_pixels && npix != img) return fail(HF_ERR_INVALID, "npix must be width * height when no pixel list is given");
+    if (npix > img) return fail(HF_ERR_INVALID, "more listed pixels than the image has");
+    if (!h_target) return fail(HF_ERR_INVALID, "null target image");
+    CU(cudaSetDevice(c->device));
+    if ((rc = ensure_slots(c))) return rc;
+    if (c->hs_img_elems < img) {
+        cudaFree(c->d_hs_target); cudaFree(c->d_hs_image); c->d_hs_target = c->d_hs_image = nullptr; c->hs_img_elems = 0;
+        CU(cudaMalloc(&c->d_hs_target, img * sizeof(float)));
+        CU(cudaMalloc(&c->d_hs_image, img * sizeof(float)));
+        c->hs_img_elems = img;
+    }
+    if (h_pixels && c->hs_pix_elems < npix) {
+        cudaFree(c->d_hs_pixels); c->d_hs_pixels = nullptr; c->hs_pix_elems = 0;
+        CU(cudaMalloc(&c->d_hs_pixels, npix * sizeof(uint32_t)));
+        c->hs_pix_elems = npix;
+    }
+    if (!c->d_hs_loss) CU(cudaMalloc(&c->d_hs_loss, sizeof(double)));
+    cudaStream_t st = c->s_k;
+    CU(cudaEventRecord(c->ev_entry, (cudaStream_t) 0));
+    CU(cudaStreamWaitEvent(st, c->ev_entry, 0));
+    if (h_heights) {
+        CU(cudaMemcpyAsync(c->d_heights, h_heights, (size_t) c->W * c->H * sizeof(float), cudaMemcpyHostToDevice, st));
+        c->have_heights = true;
+        if ((rc = hf_parameters_changed(c, st))) return rc;
+    }
+    NEED_ACCEL(c);
+    CU(cudaMemcpyAsync(c->d_hs_target, h_target, img * sizeof(float), cudaMemcpyHostToDevice, st));
+    if (h_pixels) CU(cudaMemcpyAsync(c->d_hs_pixels, h_pixels, npix * sizeof(uint32_t), cudaMemcpyHostToDevice, st));
+    CU(cudaMemsetAsync(c->d_grad, 0, (size_t) c->W * c->H * sizeof(float), st));
+    CU(cudaMemsetAsync(c->d_hs_loss, 0, sizeof(double), st));
+    if (h_image_out && npix != img) CU(cudaMemsetAsync(c->d_hs_image, 0, img * sizeof(float), st));
+    if (npix > 0 && (rc = hf_render_step_l2(c, cam, light, h_pixels ? c->d_hs_pixels : nullptr, npix, c->d_hs_target, c->d_hs_image, c->d_hs_loss, st))) return rc;
+    if (h_image_out) CU(cudaMemcpyAsync(h_image_out, c->d_hs_image, img * sizeof(float), cudaMemcpyDeviceToHost, st));
+    if (h_loss_out) CU(cudaMemcpyAsync(h_loss_out, c->d_hs_loss, sizeof(double), cudaMemcpyDeviceToHost, st));
+    if (h_grad_out) CU(cudaMemcpyAsync(h_grad_out, c->d_grad, (size_t) c->W * c->H * sizeof(float), cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
     return HF_OK;
 }
 

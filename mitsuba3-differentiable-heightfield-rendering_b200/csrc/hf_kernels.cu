@@ -860,8 +860,10 @@ cudaError_t hf_launch_intersect(const HfParams &P, const HfLaunchInfo &li, int m
         // before them in pairs (single groups lose the L1 sharing between the two halves of a 64-spp pixel, so they are kept to
         // what the pairs need), and only the rest in fetches of HF_FAST_GROUPS.
         const size_t warps = (size_t) fgrid * (HF_BLOCK / 32);
-        const size_t tail = std::min(ngroups, warps * HF_FAST_TAIL);
-        const size_t mid = std::min(ngroups - tail, warps * HF_FAST_MIDTAIL);
+        static const int env_tail = getenv("HF_B200_TAIL") ? atoi(getenv("HF_B200_TAIL")) : -1;          // dev knobs: groups per resident warp
+        static const int env_mid = getenv("HF_B200_MIDTAIL") ? atoi(getenv("HF_B200_MIDTAIL")) : -1;
+        const size_t tail = std::min(ngroups, warps * (size_t) (env_tail >= 0 ? env_tail : HF_FAST_TAIL));
+        const size_t mid = std::min(ngroups - tail, warps * (size_t) (env_mid >= 0 ? env_mid : HF_FAST_MIDTAIL));
         const unsigned long long nbig = (ngroups - tail - mid) / HF_FAST_GROUPS;
         const unsigned long long npair = (ngroups - tail - nbig * HF_FAST_GROUPS) / 2;
         unsigned long long *sched = d_sched;
@@ -923,10 +925,21 @@ __device__ __forceinline__ void adam_one(float &p, float g, float &m, float &v, 
     p = p - step;
 }
 
+// Step counter and bias correction live on the DEVICE, so that a CUDA graph which captured an optimisation step replays a correct Adam
+// (t advances with every replay): one thread bumps t and looks lr_scale(t) up in a table the host filled once per (beta1, beta2) with
+// the reference's double-precision expression (optimizers.py:266-269), then lr_t = lr * lr_scale in fp32 as there.
+__global__ void hf_adam_prep_kernel(int *__restrict__ t, float *__restrict__ lr_t, const float *__restrict__ scale_table, const int table_len,
+                                    const float lr) {
+    const int step = min(*t + 1, table_len - 1);          // beyond the table the bias correction has long converged
+    *t = step;
+    *lr_t = lr * scale_table[step];
+}
+
 __global__ void __launch_bounds__(256)
 hf_adam_kernel(float *__restrict__ p, const float *__restrict__ g, float *__restrict__ m, float *__restrict__ v,
-               const size_t n, const float lr_t, const float b1, const float b2, const float omb1, const float omb2,
+               const size_t n, const float *__restrict__ lr_t_ptr, const float b1, const float b2, const float omb1, const float omb2,
                const float eps, const int mask) {
+    const float lr_t = __ldg(lr_t_ptr);
     const size_t n4 = n / 4;
     float4 *p4 = reinterpret_cast<float4 *>(p), *m4 = reinterpret_cast<float4 *>(m), *v4 = reinterpret_cast<float4 *>(v);
     const float4 *g4 = reinterpret_cast<const float4 *>(g);
@@ -945,12 +958,14 @@ hf_adam_kernel(float *__restrict__ p, const float *__restrict__ g, float *__rest
     }
 }
 
-cudaError_t hf_launch_adam(float *p, const float *g, float *m, float *v, size_t n, float lr_t, float beta1,
-                           float beta2, float omb1, float omb2, float eps, int mask_updates, int num_sms, cudaStream_t s) {
+cudaError_t hf_launch_adam(float *p, const float *g, float *m, float *v, size_t n, int *d_t, float *d_lr_t, const float *d_scale_table,
+                           int table_len, float lr, float beta1, float beta2, float omb1, float omb2, float eps, int mask_updates,
+                           int num_sms, cudaStream_t s) {
     if (n == 0) return cudaSuccess;
+    hf_adam_prep_kernel<<<1, 1, 0, s>>>(d_t, d_lr_t, d_scale_table, table_len, lr);
     size_t blocks = (n / 4 + 255) / 256;
     size_t cap = (size_t) num_sms * 8;
     int grid = (int) (blocks < cap ? (blocks ? blocks : 1) : cap);
-    hf_adam_kernel<<<grid, 256, 0, s>>>(p, g, m, v, n, lr_t, beta1, beta2, omb1, omb2, eps, mask_updates);
+    hf_adam_kernel<<<grid, 256, 0, s>>>(p, g, m, v, n, d_lr_t, beta1, beta2, omb1, omb2, eps, mask_updates);
     return cudaGetLastError();
 }

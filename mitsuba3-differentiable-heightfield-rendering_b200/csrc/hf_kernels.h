@@ -16,6 +16,7 @@ struct HfLaunchInfo {
     // quantised pyramid: the coarse EVEN levels >= q_stage_level (the levels every walk starts from) are staged in shared memory
     int q_stage_level;       // lowest staged level (even), > QLtop: nothing staged
     int q_stage_bytes;       // shared memory they take (each level padded to 16 bytes)
+    unsigned long long *seg_counter;   // ray segments traced by the path kernels (camera, bounce and visibility rays): hf_stats.segments
 };
 #ifndef HF_STAGE_Q
 #define HF_STAGE_Q 1
@@ -36,9 +37,9 @@ cudaError_t hf_launch_surface_interaction(const HfParams &P, const HfLaunchInfo 
                                           cudaStream_t s);
 cudaError_t hf_launch_backward(const HfParams &P, const HfLaunchInfo &li, const hf_rays &rays, const hf_prelim &pi,
                                const hf_si_adj &adj, uint32_t flags, float *grad, size_t n, cudaStream_t s);
-cudaError_t hf_launch_adam(float *p, const float *g, float *m, float *v, size_t n, float lr_t, float beta1,
-                           float beta2, float omb1, float omb2, float eps, int mask_updates, int num_sms,
-                           cudaStream_t s);
+cudaError_t hf_launch_adam(float *p, const float *g, float *m, float *v, size_t n, int *d_t, float *d_lr_t, const float *d_scale_table,
+                           int table_len, float lr, float beta1, float beta2, float omb1, float omb2, float eps, int mask_updates,
+                           int num_sms, cudaStream_t s);
 
 // hf_render.cu: mode 0 = forward image (+ hit triangles), 1 = fused forward + L2 adjoint + backward, 2 = backward by re-tracing
 #define HF_RENDER_MAX_SPP_HOST 256

@@ -243,7 +243,7 @@ __device__ __forceinline__ f3 hf_cosine_hemisphere(float u1, float u2) {
 
 // One camera sample through up to A.max_depth vertices. Returns the radiance; fills V[0..nv).
 __device__ __forceinline__ float hf_path_sample(const HfParams &P, const HfGrid &G, const HfRenderArgs &A, f3 dw, float t_start, int L_start,
-                                                uint32_t pid, uint32_t s, HfVertex *V, int &nv) {
+                                                uint32_t pid, uint32_t s, HfVertex *V, int &nv, unsigned &nseg) {
     const f3 l = mk3(A.lx, A.ly, A.lz);
     const unsigned long long kk = (unsigned long long) pid * A.cam.spp + s;
     const uint32_t key = (uint32_t) kk ^ ((uint32_t) (kk >> 32) * 0x85EBCA6Bu);
@@ -254,6 +254,7 @@ __device__ __forceinline__ float hf_path_sample(const HfParams &P, const HfGrid 
     for (int k = 0; k < A.max_depth; ++k) {
         float ht, hu, hv; uint32_t hprim;
         f3 p0, p1, p2;
+        ++nseg;
         if (!hf_trace(P, G, o, d, maxt, k == 0 ? t_start : 0.f, k == 0 ? L_start : HF_START_LEVEL, ht, hu, hv, hprim, p0, p1, p2)) break;
         const f3 nw = hf_world_normal(P, p0, p1, p2);
         if (!(dot3(nw, neg3(dw)) > 0.f)) break;                      // back side: the one-sided BSDF is zero
@@ -267,6 +268,7 @@ __device__ __forceinline__ float hf_path_sample(const HfParams &P, const HfGrid 
         if (lit && A.shadow) {
             const float mag = mulsign_(mag0, cosl);
             const f3 os = mk3(fmaf(mag, nw.x, pw.x), fmaf(mag, nw.y, pw.y), fmaf(mag, nw.z, pw.z));
+            ++nseg;
             if (hf_occluded(P, G, xform_point(P.to_object, os), xform_vector(P.to_object, l), 3.4028234663852886e+38f)) lit = false;
         }
         HfVertex v;
@@ -510,11 +512,16 @@ hf_render_path_kernel(const __grid_constant__ HfParams P, const HfLaunchInfo li,
     const uint32_t ppr = 32u / seg;
     const unsigned T = min((unsigned) HF_RENDER_TILE * ppr, 32u);
     const size_t ntiles = (A.npix + T - 1) / T;
+    unsigned nseg = 0;                                     // ray segments this thread traced (statistics: hf_stats.segments)
     for (;;) {
         unsigned long long tile = 0;
         if (lane == 0) tile = atomicAdd(sched, 1ull);
         tile = __shfl_sync(FULL_MASK, tile, 0);
-        if (tile >= ntiles) break;
+        if (tile >= ntiles) {
+            nseg = __reduce_add_sync(FULL_MASK, nseg);
+            if (lane == 0 && li.seg_counter && nseg) atomicAdd(li.seg_counter, (unsigned long long) nseg);
+            break;
+        }
         const size_t kq = (size_t) tile * T + lane;
         const bool have = lane < T && kq < A.npix;
         const uint32_t my_pid = have ? (A.pixels ? __ldg(A.pixels + kq) : (uint32_t) kq) : 0u;
@@ -541,7 +548,7 @@ hf_render_path_kernel(const __grid_constant__ HfParams P, const HfLaunchInfo li,
                 const uint32_t s = r * 32u + (lane & (seg - 1u));
                 HfVertex V[HF_MAX_DEPTH];
                 int nv = 0;
-                if (pix_ok && s < spp) acc += hf_path_sample(P, G, A, hf_camera_dir(A, pid, s), ts, ls, pid, s, V, nv);
+                if (pix_ok && s < spp) acc += hf_path_sample(P, G, A, hf_camera_dir(A, pid, s), ts, ls, pid, s, V, nv, nseg);
                 if (BWD) {
                     // radiance arriving at vertex k from the later vertices, back to front: Lo_k = ld_k + albedo * Lo_{k+1}
                     float lo_next[HF_MAX_DEPTH];

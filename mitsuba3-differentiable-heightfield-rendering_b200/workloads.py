@@ -124,9 +124,10 @@ def tile_pixels(width, height, tile, rank, world, device="cpu"):
     return (y * width + x)[ok]
 
 
-def hemisphere_rays(n, seed=5, radius=3.0, device="cpu"):
-    """C5: origin uniform on the upper hemisphere of `radius`, target uniform on [-1,1]^2 x {0}."""
-    idx = torch.arange(n, dtype=torch.int64, device=device)
+def hemisphere_rays(n, seed=5, radius=3.0, device="cpu", start=0):
+    """C5: origin uniform on the upper hemisphere of `radius`, target uniform on [-1,1]^2 x {0}. Rays start .. start + n - 1 of the
+    stream (a chunk of a larger batch sees the same rays as the whole batch would)."""
+    idx = torch.arange(start, start + n, dtype=torch.int64, device=device)
     u1, u2 = hash_uniform(seed, idx, 0), hash_uniform(seed, idx, 1)
     z = u1
     r = torch.sqrt(torch.clamp(1 - z * z, min=0))

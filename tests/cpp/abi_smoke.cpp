@@ -17,7 +17,7 @@
 #define EXPECT(cond) do { if (!(cond)) { std::fprintf(stderr, "abi_smoke: %s:%d: expectation failed: %s\n", __FILE__, __LINE__, #cond); std::exit(1); } } while (0)
 #define CU(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { std::fprintf(stderr, "abi_smoke: %s: %s\n", #call, cudaGetErrorString(e_)); std::exit(1); } } while (0)
 
-static bool close(float a, float b, float tol = 1e-5f) { return std::fabs(a - b) <= tol; }
+static bool close(float a, float b, float tol = 3e-5f) { return std::fabs(a - b) <= tol; }
 
 template <typename T> struct DevBuf {
     T *p = nullptr; size_t n = 0;

@@ -222,3 +222,30 @@ def test_path_l2_step_and_errors(hf, oracle):
         g.render_forward(cam, dict(light, max_depth=7))
     with pytest.raises(hf.HeightfieldError, match="replayed"):
         g.render_forward(cam, light, return_prims=True)
+
+
+def test_host_render_step_matches_device_step(hf, oracle):
+    """hf_render_step_l2_host: heights + target + pixel list from HOST memory in, image / gradient grid / loss out -- the same bits
+    as the device entry point on the same inputs, with and without a new set of heights."""
+    g, _ = _scene(hf, oracle)
+    g2, _ = _scene(hf, oracle, seed=11)
+    cam = _cam(hf, spp=64)
+    light = hf.directional_light((0.6, 0.2, 0.5), shadow_rays=True)
+    target = g2.render_forward(cam, light)
+    npix = 48 * 40
+    rng = np.random.default_rng(6)
+    for pixels in (None, rng.permutation(npix)[:999].astype(np.int32)):
+        loss = torch.zeros(1, dtype=torch.float64, device="cuda")
+        img = torch.zeros_like(target)
+        g.zero_grad(); g.render_step_l2(cam, light, target, pixels, image=img, loss=loss)
+        torch.cuda.synchronize()
+        want_grad, want_img, want_loss = g.grad.clone().cpu(), img.cpu(), float(loss)
+        h_t = target.cpu().pin_memory()
+        h_img = torch.full((40, 48), -1.0).pin_memory(); h_grad = torch.empty(g.H, g.W).pin_memory()
+        h_h = g.heights.cpu().pin_memory()
+        h_px = None if pixels is None else torch.from_numpy(pixels).pin_memory()
+        for heights_in in (None, h_h):
+            got_loss = g.render_step_l2_host(cam, light, h_t, h_heights=heights_in, h_image=h_img, h_grad=h_grad, h_pixels=h_px)
+            assert torch.equal(h_img.view(torch.int32), want_img.view(torch.int32))
+            assert abs(got_loss - want_loss) <= 1e-12 + 1e-9 * abs(want_loss)
+            assert float((h_grad - want_grad).double().norm() / want_grad.double().norm()) < 1e-5
