@@ -351,8 +351,61 @@ def main_ours(a):
     for _ in range(3):
         run_step()
     ms_total = timed(run_step, a.steps)
-    clocks = sampler.stop() if rank == 0 else None
     ms_step = ms_total / a.steps
+    ms_allreduce = timed(shape.allreduce_grad, 10) / 10 if world > 1 else 0.0     # the collective alone (64 MiB fp32 at C3)
+    collective = "none (1 GPU)" if world == 1 else "ncclAllReduce(grad 64 MiB fp32, sum) per step"
+    peer = None
+    state = {"peer": False}
+    if world > 1 and os.environ.get("HF_BENCH_COLLECTIVE", "auto") != "nccl":
+        # The fused alternative (include/hf_b200.h "multi-GPU over peer memory"): every gradient scatter goes to the rank that owns the
+        # texel, over NVLink, inside the backward kernel; what is left of the collective is an all-gather by peer stores. Verified in
+        # this run against the NCCL step above on the full batch before it may become the headline.
+        try:
+            run_step(); torch.cuda.synchronize()
+            g_nccl = shape.grad.clone()
+            handles = [None] * world
+            dist.all_gather_object(handles, shape.peer_export())
+            shape.peer_attach(rank, world, handles)
+
+            def step_peer():
+                cur = torch.cuda.current_stream()
+                zside.wait_stream(cur)
+                with torch.cuda.stream(zside):              # own slab cleared + cross-GPU barrier beside the forward kernel
+                    shape.peer_zero_grad()
+                    shape.peer_barrier()
+                shape.ray_intersect(ray, out=(si, pi))
+                cur.wait_stream(zside)
+                shape.backward(ray, pi, adj_c)              # red.global.add.f32 to the owner's grid (local or over NVLink)
+                shape.peer_barrier()
+                shape.peer_gather_grad()                    # own (fully reduced) slab -> every rank's grid
+                shape.peer_barrier()
+            step_peer(); torch.cuda.synchronize()
+            rel = (shape.grad.double() - g_nccl.double()).norm() / g_nccl.double().norm()
+            if world > 1:
+                dist.all_reduce(rel, op=dist.ReduceOp.MAX)
+            del g_nccl
+            run_peer, peer_launch = step_peer, "eager"
+            if os.environ.get("HF_BENCH_GRAPH", "1") != "0":
+                run_peer = hfb200.capture(step_peer); peer_launch = "cuda-graph"
+            for _ in range(3):
+                run_peer()
+            ms_peer = timed(run_peer, a.steps) / a.steps
+            gather_ms = timed(lambda: (shape.peer_gather_grad(), shape.peer_barrier()), 10) / 10
+            peer = {"ms_per_step": ms_peer, "mrays": n_total / (ms_peer * 1e-3) / 1e6, "launch": peer_launch, "grad_rel_l2_vs_nccl_step": float(rel),
+                    "gather_and_barrier_ms": gather_ms,
+                    "what": "zero own slab + barrier (beside the forward kernel) -> intersect/SI -> backward scattering to the texels' owners over NVLink -> barrier -> "
+                            "all-gather of the reduced slabs by peer stores -> barrier"}
+            state["peer"] = True
+        except Exception as exc:      # noqa: BLE001
+            print(f"bench.py: peer-memory path unavailable ({type(exc).__name__}: {exc}); NCCL allreduce only", file=sys.stderr, flush=True)
+            peer = None
+    nccl_step = {"ms_per_step": ms_step, "mrays": n_total / (ms_step * 1e-3) / 1e6, "launch": launch, "allreduce_ms": ms_allreduce,
+                 "what": "zero_grad -> intersect/SI -> backward -> ONE ncclAllReduce(grad, fp32, sum) on NCCL-registered memory"}
+    if peer is not None and peer["grad_rel_l2_vs_nccl_step"] < 1e-4 and peer["ms_per_step"] < ms_step and os.environ.get("HF_BENCH_COLLECTIVE", "auto") != "nccl-headline":
+        ms_step, launch = peer["ms_per_step"], peer["launch"]
+        collective = ("peer scatter: gradient atomics go to the texel's owner over NVLink inside the backward kernel (reduce-scatter), all-gather by peer stores; "
+                      "the single-ncclAllReduce step is timed beside it (extras.nccl_allreduce_step)")
+    clocks = sampler.stop() if rank == 0 else None
     value = n_total / (ms_step * 1e-3) / 1e6
     ms_fwd = float(np.mean([x.elapsed_time(y) for x, y in k_fwd]))
     ms_bwd = float(np.mean([x.elapsed_time(y) for x, y in k_bwd]))
@@ -366,8 +419,21 @@ def main_ours(a):
     opt = hfb200.Adam(lr=1e-3, params=params)
 
     def full_step():
-        step()
-        opt.step()
+        if state["peer"]:                               # sharded Adam fused with the all-gather of the heights
+            cur = torch.cuda.current_stream()
+            zside.wait_stream(cur)
+            with torch.cuda.stream(zside):
+                shape.peer_zero_grad()
+                shape.peer_barrier()
+            shape.ray_intersect(ray, out=(si, pi))
+            cur.wait_stream(zside)
+            shape.backward(ray, pi, adj_c)
+            shape.peer_barrier()
+            opt.step(peer=True)
+            shape.peer_barrier()
+        else:
+            step()
+            opt.step()
         params.update()
 
     full_step()                                     # eager once: builds the Adam bias-correction table for these betas
@@ -381,15 +447,17 @@ def main_ours(a):
             torch.cuda.synchronize()
     for _ in range(2):
         run_full()
+    params["heights"] = h           # every timed run starts from the initial field (Adam roughens it step by step: walks get longer)
+    params.update()
+    opt.reset()
     ms_full = timed(run_full, a.steps) / a.steps
-    ms_allreduce = timed(shape.allreduce_grad, 10) / 10 if world > 1 else 0.0     # the collective alone (64 MiB fp32 at C3)
     params["heights"] = h           # restore the field for the legs below
     params.update()
 
     # ---- the optimisation step of BASELINE.json configs[2] through the fused render entry:
     #      zero_grad -> hf_render_step_l2 (in-register camera rays, direct illumination, box filter, L2 adjoint, backward)
     #      [-> allreduce] -> Adam -> pyramid rebuild. No ray / interaction record touches HBM.
-    rs = run_render_step(a, shape, h, params, opt, rank, world, dev, timed, ev)      # (its e2e legs run at N = 1 only)
+    rs = run_render_step(a, shape, h, params, opt, rank, world, dev, timed, ev, state["peer"])      # (its e2e legs run at N = 1 only)
     params["heights"] = h
     params.update()
 
@@ -407,6 +475,9 @@ def main_ours(a):
 
     # ---- e2e: host buffers through hf_forward_backward_host ----
     e2e = None
+    if state["peer"]:
+        shape.peer_detach()             # the host-buffer leg below sums with NCCL (its kernels must scatter locally again)
+        state["peer"] = False
     if not a.no_e2e:
         e2e = run_e2e(a, shape, ray, adj, n_local, n_total, world, dev, timed)
 
@@ -428,7 +499,7 @@ def main_ours(a):
         "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": workload_name(a), "rays_per_step": n_total, "rays_per_gpu": n_local, "sharding": f"{a.tile}x{a.tile}-pixel image tiles, round-robin", "launch": launch,
                    "zero_grad": "on a second stream beside the forward kernel" if overlap_zero else "in stream order",
-                   "collective": "ncclAllReduce(grad 64 MiB fp32, sum) per step" if world > 1 else "none (1 GPU)",
+                   "collective": collective,
                    "l2": "inputs exceed L2 (ray + adjoint + output SoA > 5 GB per step vs 126 MB L2); no explicit flush",
                    "si_fields": "t,p,n,uv", "hit_fraction": hits},
         "clocks": clocks,
@@ -451,7 +522,7 @@ def main_ours(a):
         "extras": {"intersect_only_mrays": n_total / (ms_isect * 1e-3) / 1e6, "intersect_only_ms": ms_isect,
                    "full_step_mrays": n_total / (ms_full * 1e-3) / 1e6, "full_step_ms": ms_full,
                    "full_step": "zero_grad + intersect/SI + backward + allreduce + Adam + pyramid rebuild", "full_step_launch": full_launch,
-                   "allreduce_ms": ms_allreduce,
+                   "allreduce_ms": ms_allreduce, "nccl_allreduce_step": nccl_step if world > 1 else None, "peer_scatter_step": peer,
                    "grad_rel_l2_vs_single_rank": shard_check,
                    "grad_rel_l2_vs_single_rank_what": "N-rank tile shards + hf_allreduce_grad vs one rank tracing every ray, 512^2 heights, 256^2 x 16 spp, in this run",
                    "grad_abs_sum": grad_checksum, "mean_nodes_per_ray": n_node, "mean_leaves_per_ray": n_leaf},
@@ -481,7 +552,7 @@ def main_ours(a):
         dist.destroy_process_group()
 
 
-def run_render_step(a, shape, h, params, opt, rank, world, dev, timed, ev):
+def run_render_step(a, shape, h, params, opt, rank, world, dev, timed, ev, peer=False):
     import hfb200
     from hfb200 import workloads as wl
     cam3 = wl.CONFIGS["C3"]["camera"]
@@ -501,7 +572,10 @@ def run_render_step(a, shape, h, params, opt, rank, world, dev, timed, ev):
     k_times = []
 
     def step(record=False):
-        shape.zero_grad()
+        if peer:
+            shape.peer_zero_grad(); shape.peer_barrier()
+        else:
+            shape.zero_grad()
         loss.zero_()
         if record:
             e0, e1 = ev(), ev()
@@ -509,13 +583,19 @@ def run_render_step(a, shape, h, params, opt, rank, world, dev, timed, ev):
         shape.render_step_l2(cam, light, target, pix, image=image, loss=loss)
         if record:
             e1.record(); k_times.append((e0, e1))
-        if world > 1:
-            shape.allreduce_grad()
-        opt.step()
+        if peer:                                # the kernel scattered to the owners: sharded Adam + all-gather of the heights by peer stores
+            shape.peer_barrier(); opt.step(peer=True); shape.peer_barrier()
+        else:
+            if world > 1:
+                shape.allreduce_grad()
+            opt.step()
         params.update()
 
     def kernel_only(record=True):          # the fused kernel alone on the initial field (heights do not move)
-        shape.zero_grad()
+        if peer:
+            shape.peer_zero_grad(); shape.peer_barrier()
+        else:
+            shape.zero_grad()
         e0, e1 = ev(), ev()
         e0.record()
         shape.render_step_l2(cam, light, target, pix, image=image, loss=loss)
@@ -550,8 +630,9 @@ def run_render_step(a, shape, h, params, opt, rank, world, dev, timed, ev):
     torch.cuda.synchronize()
     loss1 = float(loss.item())
     n_total = a.image * a.image * a.spp
-    out = {"what": "zero_grad + hf_render_step_l2 (camera rays, direct illumination, box filter, L2 adjoint, backward in ONE kernel) "
-                   "+ allreduce + Adam + pyramid rebuild", "ms_per_step": ms, "mrays": n_total / (ms * 1e-3) / 1e6, "launch": launch,
+    out = {"what": "zero_grad + hf_render_step_l2 (camera rays, direct illumination, box filter, L2 adjoint, backward in ONE kernel) + " +
+                   ("barrier + sharded Adam storing the heights into every rank's grid over NVLink + barrier" if peer else "allreduce + Adam") + " + pyramid rebuild",
+           "collective": "peer scatter (gradient atomics to the owner inside the kernel)" if peer else ("ncclAllReduce" if world > 1 else "none"), "ms_per_step": ms, "mrays": n_total / (ms * 1e-3) / 1e6, "launch": launch,
            "kernel_ms": kms, "kernel_ms_": kms, "kernel_mrays": n_total / world / (kms * 1e-3) / 1e6 * world,
            "loss_first_step_local": loss0, "loss_last_step_local": loss1, "gpu_launches_per_step": 6}
     if world == 1 and not a.no_e2e:

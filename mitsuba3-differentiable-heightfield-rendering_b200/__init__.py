@@ -162,6 +162,13 @@ def _load():
         "hf_ray_intersect_host": [vp, C.POINTER(_Rays), u32, C.POINTER(_Prelim), C.POINTER(_SI), sz],
         "hf_forward_backward_host": [vp, C.POINTER(_Rays), C.POINTER(_Adj), u32, C.POINTER(_Prelim), C.POINTER(_SI), vp, sz],
         "hf_render_step_l2_host": [vp, C.POINTER(_Camera), C.POINTER(_Light), vp, sz, vp, vp, vp, vp, C.POINTER(C.c_double)],
+        "hf_peer_export": [vp, C.POINTER(C.c_uint8)],
+        "hf_peer_attach": [vp, C.c_int, C.c_int, C.POINTER(C.c_uint8)],
+        "hf_peer_detach": [vp],
+        "hf_peer_barrier": [vp, vp],
+        "hf_peer_zero_grad": [vp, vp],
+        "hf_peer_gather_grad": [vp, vp],
+        "hf_peer_adam_step": [vp, C.POINTER(_Adam), vp],
     }
     for name, args in sig.items():
         fn = getattr(L, name)
@@ -565,6 +572,54 @@ class Heightfield:
         with torch.cuda.device(self.device):
             _check(_load().hf_allreduce_grad(self._ctx, _stream()))
 
+    # -- multi-GPU over peer memory: scatters go to the texel's owner over NVLink (include/hf_b200.h "multi-GPU over peer memory") --
+    PEER_HANDLE_BYTES = 192
+
+    def _rewrap_grad(self):
+        gp = C.c_void_p()
+        _check(_load().hf_grad(self._ctx, C.byref(gp)))
+        self.grad = torch.as_tensor(_DevView(gp.value, (self.H, self.W), self), device=self.device)
+
+    def peer_export(self) -> bytes:
+        """CUDA IPC handles of this rank's gradient grid, heights and barrier counter; ship them to every rank."""
+        buf = (C.c_uint8 * self.PEER_HANDLE_BYTES)()
+        with torch.cuda.device(self.device):
+            _check(_load().hf_peer_export(self._ctx, buf))
+            self._rewrap_grad()                # the grid leaves NCCL-registered memory if hf_comm_init had put it there
+        return bytes(buf)
+
+    def peer_attach(self, rank, world_size, handles):
+        """handles: the peer_export() bytes of ranks 0 .. world_size - 1, in rank order."""
+        blob = b"".join(handles)
+        if len(blob) != world_size * self.PEER_HANDLE_BYTES:
+            raise HeightfieldError("peer_attach: need one 192-byte handle block per rank")
+        buf = (C.c_uint8 * len(blob)).from_buffer_copy(blob)
+        with torch.cuda.device(self.device):
+            _check(_load().hf_peer_attach(self._ctx, rank, world_size, buf))
+        self.peer_world = world_size
+
+    def peer_detach(self):
+        with torch.cuda.device(self.device):
+            _check(_load().hf_peer_detach(self._ctx))
+        self.peer_world = 1
+
+    def peer_barrier(self):
+        with torch.cuda.device(self.device):
+            _check(_load().hf_peer_barrier(self._ctx, _stream()))
+
+    def peer_zero_grad(self):
+        with torch.cuda.device(self.device):
+            _check(_load().hf_peer_zero_grad(self._ctx, _stream()))
+
+    def peer_gather_grad(self):
+        with torch.cuda.device(self.device):
+            _check(_load().hf_peer_gather_grad(self._ctx, _stream()))
+
+    def peer_adam_step(self, lr, beta_1=0.9, beta_2=0.999, epsilon=1e-8, mask_updates=False):
+        cfg = _Adam(lr, beta_1, beta_2, epsilon, int(mask_updates))
+        with torch.cuda.device(self.device):
+            _check(_load().hf_peer_adam_step(self._ctx, C.byref(cfg), _stream()))
+
     # -- render step on the heightfield alone (sensor + direct illumination + film + adjoint) ------
     def _pixels(self, cam, pixels):
         if pixels is None:
@@ -763,9 +818,14 @@ class Adam:
         if params is not None:
             params._shape.adam_reset()
 
-    def step(self):
+    def step(self, peer=False):
+        """peer=True (after Heightfield.peer_attach): Adam on this rank's slab of the grid, updated heights stored into every rank's
+        height grid; the caller puts a peer_barrier() between this and params.update()."""
         s = self.params._shape
-        s.adam_step(self.lr, self.beta_1, self.beta_2, self.epsilon, self.mask_updates)
+        if peer:
+            s.peer_adam_step(self.lr, self.beta_1, self.beta_2, self.epsilon, self.mask_updates)
+        else:
+            s.adam_step(self.lr, self.beta_1, self.beta_2, self.epsilon, self.mask_updates)
         self.params.set_dirty(self.params._prefix + "heights")
 
     def reset(self, key=None):

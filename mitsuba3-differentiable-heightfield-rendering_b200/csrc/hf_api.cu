@@ -159,6 +159,14 @@ struct hf_ctx {
     cudaEvent_t ev_accel = nullptr;   // recorded behind the last pyramid build (hf_bbox waits for it instead of the whole device)
     bool accel_event_ok = false;
     bool slots_ready = false;
+    // multi-GPU over peer memory (hf_peer_attach): mapped grids of the other ranks, the device-side tables of those pointers, the barrier state
+    int peer_n = 1, peer_rank = 0;
+    size_t slab_elems = 0;
+    float *peer_grad[HF_MAX_PEERS] = { nullptr }, *peer_heights[HF_MAX_PEERS] = { nullptr };
+    unsigned *peer_counter[HF_MAX_PEERS] = { nullptr };
+    float **d_peer_grad_tab = nullptr, **d_peer_heights_tab = nullptr;
+    unsigned **d_peer_counter_tab = nullptr;
+    unsigned *d_xcounter = nullptr;       // [0] = this rank's barrier counter (peers add to it), [64] = the epoch (local)
     // host-buffer render step: device copies of the caller's target / image / pixel list, and the loss
     float *d_hs_target = nullptr, *d_hs_image = nullptr;
     uint32_t *d_hs_pixels = nullptr;
@@ -264,6 +272,8 @@ static void layout_pyramid(hf_ctx *c) {
     }
 }
 
+static void peer_release_fwd(hf_ctx *c);
+
 extern "C" int hf_create(hf_ctx **out, const hf_desc *desc) {
     if (!out || !desc) return fail(HF_ERR_INVALID, "null argument");
     *out = nullptr;
@@ -321,6 +331,8 @@ extern "C" int hf_create(hf_ctx **out, const hf_desc *desc) {
 extern "C" int hf_destroy(hf_ctx *c) {
     if (!c) return HF_OK;
     cudaSetDevice(c->device);
+    cudaDeviceSynchronize();
+    peer_release_fwd(c);
     if (c->comm && c->grad_reg && g_nccl.CommDeregister) g_nccl.CommDeregister(c->comm, c->grad_reg);
     if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
     if (c->grad_nccl && g_nccl.MemFree) { g_nccl.MemFree(c->d_grad); c->d_grad = nullptr; }
@@ -635,6 +647,22 @@ extern "C" int hf_adam_reset(hf_ctx *c, void *stream) {
     return HF_OK;
 }
 
+// lr_scale(t) = sqrt(1 - beta2^t) / (1 - beta1^t) for t = 1 .. HF_ADAM_TABLE - 1, in double, rounded once (entry 0 unused)
+static int ensure_adam_table(hf_ctx *c, double b1, double b2, void *stream) {
+    if (c->d_adam_table && c->tab_b1 == b1 && c->tab_b2 == b2) return HF_OK;
+    cudaStreamCaptureStatus st = cudaStreamCaptureStatusNone;
+    if (cudaStreamIsCapturing((cudaStream_t) stream, &st) == cudaSuccess && st == cudaStreamCaptureStatusActive)
+        return fail(HF_ERR_STATE, "Adam: run one eager hf_adam_step with these betas before capturing it into a CUDA graph");
+    std::vector<float> tab(HF_ADAM_TABLE);
+    tab[0] = 1.f;
+    for (int t = 1; t < HF_ADAM_TABLE; ++t) tab[t] = (float) (sqrt(1.0 - pow(b2, t)) / (1.0 - pow(b1, t)));
+    if (!c->d_adam_table) CU(cudaMalloc(&c->d_adam_table, HF_ADAM_TABLE * sizeof(float)));
+    CU(cudaStreamSynchronize((cudaStream_t) stream));
+    CU(cudaMemcpy(c->d_adam_table, tab.data(), HF_ADAM_TABLE * sizeof(float), cudaMemcpyHostToDevice));
+    c->tab_b1 = b1; c->tab_b2 = b2;
+    return HF_OK;
+}
+
 extern "C" int hf_adam_step(hf_ctx *c, const hf_adam *cfg, void *stream) {
     CHECK_CTX(c);
     if (!cfg) return fail(HF_ERR_INVALID, "null Adam configuration");
@@ -647,19 +675,7 @@ extern "C" int hf_adam_step(hf_ctx *c, const hf_adam *cfg, void *stream) {
     // optimizers.py:266-279. The hyper-parameters are Python floats (doubles) there: lr_scale and (1 - beta) are evaluated in double
     // and only then become fp32 literals of the traced expression; lr is an opaque fp32 (lr_v) multiplied by the fp32 lr_scale.
     const double b1 = cfg->beta1, b2 = cfg->beta2;
-    if (!c->d_adam_table || c->tab_b1 != b1 || c->tab_b2 != b2) {
-        // lr_scale(t) = sqrt(1 - beta2^t) / (1 - beta1^t) for t = 1 .. HF_ADAM_TABLE - 1, in double, rounded once (entry 0 unused)
-        cudaStreamCaptureStatus st = cudaStreamCaptureStatusNone;
-        if (cudaStreamIsCapturing((cudaStream_t) stream, &st) == cudaSuccess && st == cudaStreamCaptureStatusActive)
-            return fail(HF_ERR_STATE, "Adam: run one eager hf_adam_step with these betas before capturing it into a CUDA graph");
-        std::vector<float> tab(HF_ADAM_TABLE);
-        tab[0] = 1.f;
-        for (int t = 1; t < HF_ADAM_TABLE; ++t) tab[t] = (float) (sqrt(1.0 - pow(b2, t)) / (1.0 - pow(b1, t)));
-        if (!c->d_adam_table) CU(cudaMalloc(&c->d_adam_table, HF_ADAM_TABLE * sizeof(float)));
-        CU(cudaStreamSynchronize((cudaStream_t) stream));
-        CU(cudaMemcpy(c->d_adam_table, tab.data(), HF_ADAM_TABLE * sizeof(float), cudaMemcpyHostToDevice));
-        c->tab_b1 = b1; c->tab_b2 = b2;
-    }
+    { int rc = ensure_adam_table(c, b1, b2, stream); if (rc) return rc; }
     CU(hf_launch_adam(c->d_heights, c->d_grad, c->d_m, c->d_v, (size_t) c->W * c->H, c->d_adam_t, c->d_adam_lr_t, c->d_adam_table,
                       HF_ADAM_TABLE, (float) cfg->lr, (float) b1, (float) b2, (float) (1.0 - b1), (float) (1.0 - b2), (float) cfg->epsilon,
                       cfg->mask_updates, c->num_sms, (cudaStream_t) stream));
@@ -730,6 +746,168 @@ extern "C" int hf_allreduce_grad(hf_ctx *c, void *stream) {
     CU(cudaSetDevice(c->device));
     // ncclFloat32 = 7, ncclSum = 0
     NC(g_nccl.AllReduce(c->d_grad, c->d_grad, (size_t) c->W * c->H, 7, 0, c->comm, (cudaStream_t) stream));
+    return HF_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// Multi-GPU over peer memory: the gradient's reduce-scatter happens INSIDE the scatter kernels (every red.global.add.f32 goes to the
+// rank that owns the texel, over NVLink), the all-gather is a store kernel (gradient) or is fused into the sharded Adam (heights).
+// One process per GPU: the grids are shared with CUDA IPC handles the caller ships between the ranks (like the NCCL unique id).
+// ------------------------------------------------------------------------------------------
+// HF_PEER_HANDLE_BYTES (include/hf_b200.h): three cudaIpcMemHandle_t -- gradient grid, heights, barrier counter
+static_assert(sizeof(cudaIpcMemHandle_t) == 64, "cudaIpcMemHandle_t is 64 bytes");
+
+static void peer_release(hf_ctx *c);
+static void peer_release_fwd(hf_ctx *c) {
+    peer_release(c);
+    cudaFree(c->d_peer_grad_tab); cudaFree(c->d_peer_heights_tab); cudaFree(c->d_peer_counter_tab); cudaFree(c->d_xcounter);
+    c->d_peer_grad_tab = nullptr; c->d_peer_heights_tab = nullptr; c->d_peer_counter_tab = nullptr; c->d_xcounter = nullptr;
+}
+static void peer_release(hf_ctx *c) {
+    for (int r = 0; r < HF_MAX_PEERS; ++r) {
+        if (r != c->peer_rank || c->peer_n <= 1) {
+            if (c->peer_grad[r] && c->peer_grad[r] != c->d_grad) cudaIpcCloseMemHandle(c->peer_grad[r]);
+            if (c->peer_heights[r] && c->peer_heights[r] != c->d_heights) cudaIpcCloseMemHandle(c->peer_heights[r]);
+            if (c->peer_counter[r] && c->peer_counter[r] != c->d_xcounter) cudaIpcCloseMemHandle(c->peer_counter[r]);
+        }
+        c->peer_grad[r] = nullptr; c->peer_heights[r] = nullptr; c->peer_counter[r] = nullptr;
+    }
+    c->peer_n = 1; c->peer_rank = 0; c->slab_elems = 0;
+    c->P.peer_n = 1;
+    for (int r = 0; r < HF_MAX_PEERS; ++r) c->P.grad_peer[r] = nullptr;
+}
+
+extern "C" int hf_peer_export(hf_ctx *c, uint8_t out[HF_PEER_HANDLE_BYTES]) {
+    CHECK_CTX(c);
+    if (!out) return fail(HF_ERR_INVALID, "null handle buffer");
+    CU(cudaSetDevice(c->device));
+    if (c->grad_nccl) {
+        // CUDA IPC exports cudaMalloc memory only: bring the gradient grid back from ncclMemAlloc memory (hf_grad() changes again)
+        const size_t bytes = (size_t) c->W * c->H * sizeof(float);
+        float *nb = nullptr;
+        CU(cudaMalloc(&nb, bytes));
+        CU(cudaMemcpy(nb, c->d_grad, bytes, cudaMemcpyDeviceToDevice));
+        if (c->comm && c->grad_reg && g_nccl.CommDeregister) g_nccl.CommDeregister(c->comm, c->grad_reg);
+        c->grad_reg = nullptr;
+        if (g_nccl.MemFree) g_nccl.MemFree(c->d_grad);
+        c->d_grad = nb; c->grad_nccl = false;
+    }
+    if (!c->d_xcounter) {
+        CU(cudaMalloc(&c->d_xcounter, size_t(2) << 20));            // an allocation of its own (IPC maps whole allocations)
+        CU(cudaMemset(c->d_xcounter, 0, size_t(2) << 20));
+    }
+    cudaIpcMemHandle_t h[3];
+    CU(cudaIpcGetMemHandle(&h[0], c->d_grad));
+    CU(cudaIpcGetMemHandle(&h[1], c->d_heights));
+    CU(cudaIpcGetMemHandle(&h[2], c->d_xcounter));
+    memcpy(out, h, sizeof(h));
+    return HF_OK;
+}
+
+extern "C" int hf_peer_attach(hf_ctx *c, int rank, int nranks, const uint8_t *all_handles) {
+    CHECK_CTX(c);
+    if (!all_handles || nranks < 1 || nranks > HF_MAX_PEERS || rank < 0 || rank >= nranks)
+        return fail(HF_ERR_INVALID, "hf_peer_attach: need 1 <= nranks <= %d, 0 <= rank < nranks and the handles of every rank", HF_MAX_PEERS);
+    if (!c->d_xcounter) return fail(HF_ERR_STATE, "hf_peer_attach: call hf_peer_export on this context first");
+    CU(cudaSetDevice(c->device));
+    CU(cudaDeviceSynchronize());
+    peer_release(c);
+    c->peer_rank = rank;
+    for (int r = 0; r < nranks; ++r) {
+        if (r == rank) { c->peer_grad[r] = c->d_grad; c->peer_heights[r] = c->d_heights; c->peer_counter[r] = c->d_xcounter; continue; }
+        cudaIpcMemHandle_t h[3];
+        memcpy(h, all_handles + (size_t) r * HF_PEER_HANDLE_BYTES, sizeof(h));
+        void *pg = nullptr, *ph = nullptr, *pc = nullptr;
+        cudaError_t e1 = cudaIpcOpenMemHandle(&pg, h[0], cudaIpcMemLazyEnablePeerAccess);
+        cudaError_t e2 = e1 == cudaSuccess ? cudaIpcOpenMemHandle(&ph, h[1], cudaIpcMemLazyEnablePeerAccess) : e1;
+        cudaError_t e3 = e2 == cudaSuccess ? cudaIpcOpenMemHandle(&pc, h[2], cudaIpcMemLazyEnablePeerAccess) : e2;
+        if (e3 != cudaSuccess) {
+            cudaGetLastError();
+            if (pg) cudaIpcCloseMemHandle(pg);
+            if (ph) cudaIpcCloseMemHandle(ph);
+            c->peer_n = r;                         // release what was opened so far
+            peer_release(c);
+            return fail(HF_ERR_CUDA, "hf_peer_attach: cannot map rank %d's grids over CUDA IPC (%s); is peer access between the GPUs available?", r, cudaGetErrorString(e3));
+        }
+        c->peer_grad[r] = (float *) pg; c->peer_heights[r] = (float *) ph; c->peer_counter[r] = (unsigned *) pc;
+    }
+    c->peer_n = nranks;
+    const size_t total = (size_t) c->W * c->H;
+    c->slab_elems = (((total + nranks - 1) / nranks) + 1023) & ~size_t(1023);
+    if (!c->d_peer_grad_tab) {
+        CU(cudaMalloc(&c->d_peer_grad_tab, HF_MAX_PEERS * sizeof(float *)));
+        CU(cudaMalloc(&c->d_peer_heights_tab, HF_MAX_PEERS * sizeof(float *)));
+        CU(cudaMalloc(&c->d_peer_counter_tab, HF_MAX_PEERS * sizeof(unsigned *)));
+    }
+    CU(cudaMemcpy(c->d_peer_grad_tab, c->peer_grad, HF_MAX_PEERS * sizeof(float *), cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(c->d_peer_heights_tab, c->peer_heights, HF_MAX_PEERS * sizeof(float *), cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(c->d_peer_counter_tab, c->peer_counter, HF_MAX_PEERS * sizeof(unsigned *), cudaMemcpyHostToDevice));
+    const HfDivMagic dm = hf_divmagic((uint32_t) c->slab_elems);
+    c->P.slab_magic = dm.m; c->P.slab_shift = dm.s; c->P.peer_n = nranks;
+    for (int r = 0; r < HF_MAX_PEERS; ++r) c->P.grad_peer[r] = r < nranks ? c->peer_grad[r] : nullptr;
+    return HF_OK;
+}
+
+extern "C" int hf_peer_detach(hf_ctx *c) {
+    CHECK_CTX(c);
+    CU(cudaSetDevice(c->device));
+    CU(cudaDeviceSynchronize());
+    peer_release(c);
+    return HF_OK;
+}
+
+#define NEED_PEERS(c) do { if ((c)->peer_n <= 1) return fail(HF_ERR_STATE, "hf_peer_attach was not called (or with a single rank)"); } while (0)
+static inline void peer_slab(const hf_ctx *c, size_t &lo, size_t &hi) {
+    const size_t total = (size_t) c->W * c->H;
+    lo = std::min(total, (size_t) c->peer_rank * c->slab_elems);
+    hi = std::min(total, lo + c->slab_elems);
+}
+
+extern "C" int hf_peer_barrier(hf_ctx *c, void *stream) {
+    CHECK_CTX(c);
+    NEED_PEERS(c);
+    CU(cudaSetDevice(c->device));
+    CU(hf_launch_peer_barrier(c->d_peer_counter_tab, c->d_xcounter, c->d_xcounter + 64, c->peer_n, (cudaStream_t) stream));
+    return HF_OK;
+}
+
+extern "C" int hf_peer_zero_grad(hf_ctx *c, void *stream) {
+    CHECK_CTX(c);
+    NEED_PEERS(c);
+    CU(cudaSetDevice(c->device));
+    size_t lo, hi;
+    peer_slab(c, lo, hi);
+    if (hi > lo) CU(cudaMemsetAsync(c->d_grad + lo, 0, (hi - lo) * sizeof(float), (cudaStream_t) stream));
+    return HF_OK;
+}
+
+extern "C" int hf_peer_gather_grad(hf_ctx *c, void *stream) {
+    CHECK_CTX(c);
+    NEED_PEERS(c);
+    CU(cudaSetDevice(c->device));
+    size_t lo, hi;
+    peer_slab(c, lo, hi);
+    CU(hf_launch_peer_push(c->d_grad, c->d_peer_grad_tab, c->peer_n, c->peer_rank, lo, hi, c->num_sms, (cudaStream_t) stream));
+    return HF_OK;
+}
+
+extern "C" int hf_peer_adam_step(hf_ctx *c, const hf_adam *cfg, void *stream) {
+    CHECK_CTX(c);
+    NEED_PEERS(c);
+    if (!cfg) return fail(HF_ERR_INVALID, "null Adam configuration");
+    if (!(cfg->beta1 >= 0. && cfg->beta1 < 1. && cfg->beta2 >= 0. && cfg->beta2 < 1. && cfg->lr > 0. && cfg->epsilon > 0.))
+        return fail(HF_ERR_INVALID, "Adam: need 0 <= beta < 1, lr > 0, epsilon > 0");
+    if (!c->have_heights) return fail(HF_ERR_STATE, "heights were never set");
+    if (!c->d_m || !c->d_v) { int rc = hf_adam_reset(c, stream); if (rc) return rc; }
+    CU(cudaSetDevice(c->device));
+    const double b1 = cfg->beta1, b2 = cfg->beta2;
+    { int rc = ensure_adam_table(c, b1, b2, stream); if (rc) return rc; }
+    size_t lo, hi;
+    peer_slab(c, lo, hi);
+    CU(hf_launch_peer_adam(c->d_heights, c->d_grad, c->d_m, c->d_v, c->d_peer_heights_tab, c->peer_n, c->peer_rank, lo, hi, c->d_adam_t, c->d_adam_lr_t,
+                           c->d_adam_table, HF_ADAM_TABLE, (float) cfg->lr, (float) b1, (float) b2, (float) (1.0 - b1), (float) (1.0 - b2),
+                           (float) cfg->epsilon, cfg->mask_updates, c->num_sms, (cudaStream_t) stream));
+    c->accel_valid = false;       // heights moved (on every rank, once the peers' stores have landed: hf_peer_barrier, then hf_parameters_changed)
     return HF_OK;
 }
 

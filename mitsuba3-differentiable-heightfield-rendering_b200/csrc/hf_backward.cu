@@ -136,8 +136,11 @@ hf_backward_kernel(const __grid_constant__ HfParams P, const hf_rays R, const hf
             float a_e1z = e2.x * a_c.y - e2.y * a_c.x;          // (e2 x a_c).z
             float a_e2z = a_c.x * e1.y - a_c.y * e1.x;          // (a_c x e1).z
 
-            // vertex texcoords differ by constants: d0 = uv(p1) - uv(p0), d1 = uv(p2) - uv(p0)
-            const float d0x = 0.5f * e1.x, d0y = 0.5f * e1.y, d1x = 0.5f * e2.x, d1y = 0.5f * e2.y;
+            // d0 = uv(p1) - uv(p0), d1 = uv(p2) - uv(p0) from the fp32 vertex texcoords fmadd(x, 0.5, 0.5) the forward pass interpolates
+            // (src/shapes/rectangle.cpp:312-313). NOT 0.5 * e: the rounded texcoords are the function being differentiated, and their
+            // differences deviate from the exact half-edge by up to 1e-5 relative -- far above the 1e-4 per-texel tolerance once the
+            // texel sums cancel.
+            const float d0x = tex(p1.x) - tex(p0.x), d0y = tex(p1.y) - tex(p0.y), d1x = tex(p2.x) - tex(p0.x), d1y = tex(p2.y) - tex(p0.y);
             if (GENERAL && (flags & HF_RAY_DPDUV)) {            // mesh.cpp:778-789
                 const f3 a_du = bw_lin_T<IDENT>(TW, mk3(LDA(A.dpdu_x), LDA(A.dpdu_y), LDA(A.dpdu_z)));
                 const f3 a_dv = bw_lin_T<IDENT>(TW, mk3(LDA(A.dpdv_x), LDA(A.dpdv_y), LDA(A.dpdv_z)));
@@ -192,7 +195,7 @@ hf_backward_kernel(const __grid_constant__ HfParams P, const hf_rays R, const hf
                 g2 += __shfl_xor_sync(FULL_MASK, g2, s);
             }
             if (lane == (unsigned) (__ffs((int) act) - 1)) {
-                atomicAdd(grad + i0, g0); atomicAdd(grad + i1, g1); atomicAdd(grad + i2, g2);
+                hf_grad_add(P, grad, i0, g0); hf_grad_add(P, grad, i1, g1); hf_grad_add(P, grad, i2, g2);
             }
         } else if (valid) {
             unsigned peers = __match_any_sync(act, prim);
@@ -208,7 +211,7 @@ hf_backward_kernel(const __grid_constant__ HfParams P, const hf_rays R, const hf
                 peers &= ~retired;
                 rel >>= 1;
             }
-            if (leader) { atomicAdd(grad + i0, g0); atomicAdd(grad + i1, g1); atomicAdd(grad + i2, g2); }
+            if (leader) { hf_grad_add(P, grad, i0, g0); hf_grad_add(P, grad, i1, g1); hf_grad_add(P, grad, i2, g2); }
         }
     }
 }

@@ -13,6 +13,7 @@
 #include "hf_divmagic.h"
 
 #define HF_MAX_LEVELS 26
+#define HF_MAX_PEERS 8            // GPUs of one NVSwitch box
 #define HF_INF __int_as_float(0x7f800000)
 
 // 2^-20: relative slack on the ray's z interval during traversal (never culls a node that
@@ -38,7 +39,21 @@ struct HfParams {
     int QLtop, xmask, ymask;      // top level; padded cell counts minus one
     uint32_t nx_magic;            // cell / NX without a divide (hf_divmagic.h); prim_index < 2^31 is checked by hf_create
     int32_t nx_shift;
+    // Multi-GPU peer scatter (hf_peer_attach): the gradient grid is cut into peer_n slabs of slab_elems texels,
+    // slab r is OWNED by rank r, and grad_peer[r] is rank r's grid mapped into this process over NVLink (CUDA IPC). A scatter then
+    // goes straight to the owner (red.global.add.f32 on peer memory): the reduce-scatter of the gradient happens inside the kernels
+    // that produce it, texel by texel, instead of a 64 MiB collective behind them. peer_n <= 1: the local grid only.
+    float *grad_peer[HF_MAX_PEERS];
+    uint32_t slab_magic;
+    int32_t slab_shift;
+    int32_t peer_n;
 };
+
+// gradient scatter of one value: the texel's owner takes it (see HfParams::grad_peer)
+__device__ __forceinline__ void hf_grad_add(const HfParams &P, float *__restrict__ grad, uint32_t idx, float val) {
+    if (P.peer_n > 1) grad = P.grad_peer[hf_divide(idx, P.slab_magic, P.slab_shift)];
+    atomicAdd(grad + idx, val);
+}
 
 struct f3 { float x, y, z; };
 __device__ __forceinline__ f3 mk3(float x, float y, float z) { f3 r; r.x = x; r.y = y; r.z = z; return r; }

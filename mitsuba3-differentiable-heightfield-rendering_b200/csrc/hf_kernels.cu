@@ -958,6 +958,95 @@ hf_adam_kernel(float *__restrict__ p, const float *__restrict__ g, float *__rest
     }
 }
 
+// ------------------------------------------------------------------------------------------
+// Multi-GPU over peer memory (hf_peer_attach): the pieces that are not a scatter
+// ------------------------------------------------------------------------------------------
+// Cross-GPU barrier of one NVSwitch box, entirely on the device (it lives in the stream and in CUDA graphs like any kernel): every
+// rank adds 1 to a counter in EVERY rank's memory (red.add at system scope over NVLink), then spins until its own counter has seen
+// all ranks for this epoch. The counters only grow (epoch e ends at e * nranks), so there is nothing to reset. The system fences
+// order it against the kernels before (their peer writes / atomics) and after it in the stream.
+__global__ void hf_peer_barrier_kernel(unsigned *const *__restrict__ peer_counter, unsigned *__restrict__ my_counter, unsigned *__restrict__ my_epoch,
+                                       const int nranks) {
+    __threadfence_system();
+    __shared__ unsigned s_target;
+    if (threadIdx.x == 0) { const unsigned e = *my_epoch + 1u; *my_epoch = e; s_target = e * (unsigned) nranks; }
+    __syncthreads();
+    if ((int) threadIdx.x < nranks) atomicAdd_system(peer_counter[threadIdx.x], 1u);
+    if (threadIdx.x == 0) {
+        volatile unsigned *c = my_counter;
+        unsigned long long spins = 0;
+        while ((int) (*c - s_target) < 0) { if (++spins > (1ull << 34)) __trap(); }      // a missing rank: fail loudly instead of hanging the box
+    }
+    __syncthreads();
+    __threadfence_system();
+}
+
+// all-gather by peer stores: this rank's slab [lo, hi) of `local` goes to the same offsets of every other rank's buffer
+__global__ void __launch_bounds__(256)
+hf_peer_push_kernel(const float *__restrict__ local, float *const *__restrict__ peers, const int nranks, const int rank, const size_t lo, const size_t hi) {
+    const size_t n4 = (hi - lo) / 4;                      // slabs are multiples of 1024 texels, buffers 256-byte aligned
+    const float4 *src = reinterpret_cast<const float4 *>(local + lo);
+    for (size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (size_t) gridDim.x * blockDim.x) {
+        const float4 v = src[i];
+        for (int r = 0; r < nranks; ++r)
+            if (r != rank) __stcs(reinterpret_cast<float4 *>(peers[r] + lo) + i, v);
+    }
+    for (size_t i = lo + n4 * 4 + (size_t) blockIdx.x * blockDim.x + threadIdx.x; i < hi; i += (size_t) gridDim.x * blockDim.x)
+        for (int r = 0; r < nranks; ++r)
+            if (r != rank) peers[r][i] = local[i];
+}
+
+// Sharded Adam fused with the all-gather of the parameter: this rank updates the texels of ITS slab (whose gradient the scatter
+// kernels have already summed into this rank's grid) and stores every updated height into all ranks' height grids over NVLink.
+__global__ void __launch_bounds__(256)
+hf_peer_adam_kernel(float *__restrict__ p, const float *__restrict__ g, float *__restrict__ m, float *__restrict__ v, float *const *__restrict__ peer_heights,
+                    const int nranks, const int rank, const size_t lo, const size_t hi, const float *__restrict__ lr_t_ptr, const float b1, const float b2,
+                    const float omb1, const float omb2, const float eps, const int mask) {
+    const float lr_t = __ldg(lr_t_ptr);
+    const size_t n4 = (hi - lo) / 4;
+    float4 *p4 = reinterpret_cast<float4 *>(p + lo), *m4 = reinterpret_cast<float4 *>(m + lo), *v4 = reinterpret_cast<float4 *>(v + lo);
+    const float4 *g4 = reinterpret_cast<const float4 *>(g + lo);
+    for (size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (size_t) gridDim.x * blockDim.x) {
+        float4 pp = p4[i], gg = g4[i], mm = m4[i], vv = v4[i];
+        adam_one(pp.x, gg.x, mm.x, vv.x, lr_t, b1, b2, omb1, omb2, eps, mask);
+        adam_one(pp.y, gg.y, mm.y, vv.y, lr_t, b1, b2, omb1, omb2, eps, mask);
+        adam_one(pp.z, gg.z, mm.z, vv.z, lr_t, b1, b2, omb1, omb2, eps, mask);
+        adam_one(pp.w, gg.w, mm.w, vv.w, lr_t, b1, b2, omb1, omb2, eps, mask);
+        p4[i] = pp; m4[i] = mm; v4[i] = vv;
+        for (int r = 0; r < nranks; ++r)
+            if (r != rank) __stcs(reinterpret_cast<float4 *>(peer_heights[r] + lo) + i, pp);
+    }
+    for (size_t i = lo + n4 * 4 + (size_t) blockIdx.x * blockDim.x + threadIdx.x; i < hi; i += (size_t) gridDim.x * blockDim.x) {
+        float pp = p[i], mm = m[i], vv = v[i];
+        adam_one(pp, g[i], mm, vv, lr_t, b1, b2, omb1, omb2, eps, mask);
+        p[i] = pp; m[i] = mm; v[i] = vv;
+        for (int r = 0; r < nranks; ++r)
+            if (r != rank) peer_heights[r][i] = pp;
+    }
+}
+
+cudaError_t hf_launch_peer_barrier(unsigned *const *d_peer_counter, unsigned *d_my_counter, unsigned *d_my_epoch, int nranks, cudaStream_t s) {
+    hf_peer_barrier_kernel<<<1, 32, 0, s>>>(d_peer_counter, d_my_counter, d_my_epoch, nranks);
+    return cudaGetLastError();
+}
+cudaError_t hf_launch_peer_push(const float *local, float *const *d_peers, int nranks, int rank, size_t lo, size_t hi, int num_sms, cudaStream_t s) {
+    if (hi <= lo) return cudaSuccess;
+    const size_t blocks = ((hi - lo) / 4 + 255) / 256, cap = (size_t) num_sms * 4;
+    hf_peer_push_kernel<<<(int) (blocks < cap ? (blocks ? blocks : 1) : cap), 256, 0, s>>>(local, d_peers, nranks, rank, lo, hi);
+    return cudaGetLastError();
+}
+cudaError_t hf_launch_peer_adam(float *p, const float *g, float *m, float *v, float *const *d_peer_heights, int nranks, int rank, size_t lo, size_t hi,
+                                int *d_t, float *d_lr_t, const float *d_scale_table, int table_len, float lr, float beta1, float beta2, float omb1,
+                                float omb2, float eps, int mask_updates, int num_sms, cudaStream_t s) {
+    hf_adam_prep_kernel<<<1, 1, 0, s>>>(d_t, d_lr_t, d_scale_table, table_len, lr);
+    if (hi > lo) {
+        const size_t blocks = ((hi - lo) / 4 + 255) / 256, cap = (size_t) num_sms * 4;
+        hf_peer_adam_kernel<<<(int) (blocks < cap ? (blocks ? blocks : 1) : cap), 256, 0, s>>>(p, g, m, v, d_peer_heights, nranks, rank, lo, hi, d_lr_t, beta1,
+                                                                                            beta2, omb1, omb2, eps, mask_updates);
+    }
+    return cudaGetLastError();
+}
+
 cudaError_t hf_launch_adam(float *p, const float *g, float *m, float *v, size_t n, int *d_t, float *d_lr_t, const float *d_scale_table,
                            int table_len, float lr, float beta1, float beta2, float omb1, float omb2, float eps, int mask_updates,
                            int num_sms, cudaStream_t s) {

@@ -41,6 +41,13 @@ cudaError_t hf_launch_adam(float *p, const float *g, float *m, float *v, size_t 
                            int table_len, float lr, float beta1, float beta2, float omb1, float omb2, float eps, int mask_updates,
                            int num_sms, cudaStream_t s);
 
+// multi-GPU over peer memory (hf_peer_attach)
+cudaError_t hf_launch_peer_barrier(unsigned *const *d_peer_counter, unsigned *d_my_counter, unsigned *d_my_epoch, int nranks, cudaStream_t s);
+cudaError_t hf_launch_peer_push(const float *local, float *const *d_peers, int nranks, int rank, size_t lo, size_t hi, int num_sms, cudaStream_t s);
+cudaError_t hf_launch_peer_adam(float *p, const float *g, float *m, float *v, float *const *d_peer_heights, int nranks, int rank, size_t lo, size_t hi,
+                                int *d_t, float *d_lr_t, const float *d_scale_table, int table_len, float lr, float beta1, float beta2, float omb1,
+                                float omb2, float eps, int mask_updates, int num_sms, cudaStream_t s);
+
 // hf_render.cu: mode 0 = forward image (+ hit triangles), 1 = fused forward + L2 adjoint + backward, 2 = backward by re-tracing
 #define HF_RENDER_MAX_SPP_HOST 256
 cudaError_t hf_launch_render(const HfParams &P, const HfLaunchInfo &li, int mode, const hf_camera &cam, const hf_light &light,

@@ -19,6 +19,7 @@
 // file's own definition, restated op for op by the oracle (oracle/hf_oracle.c, hfo_render_*).
 // Compiled with -fmad=false like the rest: every fma below is explicit.
 #include <string.h>
+#include <stdlib.h>
 #include "hf_walk_common.cuh"
 
 #define HF_RENDER_MAX_SPP 256          // samples of one pixel whose hit triangles wait in shared memory
@@ -50,6 +51,7 @@ struct HfRenderArgs {
     uint32_t seed_h0, seed_h1;         // lowbias32(seed * 0x9E3779B1 + channel * 0x85EBCA6B) for the two jitter channels (same for every sample)
     const uint32_t *pixels;            // nullable
     size_t npix;
+    int tail, midtail;                 // closing phases of the schedule: quarter tiles per resident warp (HF_RENDER_TAIL / _MIDTAIL)
 };
 
 // ---- sampling ---------------------------------------------------------------------------------------------------
@@ -359,8 +361,8 @@ hf_render_kernel(const __grid_constant__ HfParams P, const HfLaunchInfo li, cons
     // HF_RENDER_MIDTAIL quarter tiles per warp before them in pairs, so that every phase outlasts the slowest tile of the one before
     // (a pixel whose rays skim down a slope takes ~0.2 ms, and such pixels are neighbours) whatever the size of the pixel list
     const size_t nwarps = (size_t) gridDim.x * (HF_BLOCK / 32);
-    const size_t tailpx = min(A.npix, nwarps * HF_RENDER_TAIL * u1);
-    const size_t midpx = min(A.npix - tailpx, nwarps * HF_RENDER_MIDTAIL * u1);
+    const size_t tailpx = min(A.npix, nwarps * (size_t) A.tail * u1);
+    const size_t midpx = min(A.npix - tailpx, nwarps * (size_t) A.midtail * u1);
     const size_t nbig = (A.npix - tailpx - midpx) / u4, rest0 = nbig * u4;
     const size_t npair = (A.npix - tailpx - rest0) / u2, rest1 = rest0 + npair * u2;
     double loss_acc = 0.0;
@@ -461,7 +463,7 @@ hf_render_kernel(const __grid_constant__ HfParams P, const HfLaunchInfo li, cons
                         hf_shade_adjoint(P, A, prim, a_v, i0, i1, i2, g0, g1, g2);
                         if ((peers & ((1u << lane) - 1u)) == 0u) {            // lowest lane of the group
                             const float cnt = (float) __popc(peers);
-                            atomicAdd(grad + i0, cnt * g0); atomicAdd(grad + i1, cnt * g1); atomicAdd(grad + i2, cnt * g2);
+                            hf_grad_add(P, grad, i0, cnt * g0); hf_grad_add(P, grad, i1, cnt * g1); hf_grad_add(P, grad, i2, cnt * g2);
                         }
                     }
                 }
@@ -568,9 +570,9 @@ hf_render_path_kernel(const __grid_constant__ HfParams P, const HfLaunchInfo li,
                             hf_normal_adjoint(P, v.prim, mk3(kd * A.lx + kw * v.wx, kd * A.ly + kw * v.wy, kd * A.lz + kw * v.wz),
                                               i0, i1, i2, g0, g1, g2);
                         }
-                        warp_aggregated_add(grad, i0, g0, valid);
-                        warp_aggregated_add(grad, i1, g1, valid);
-                        warp_aggregated_add(grad, i2, g2, valid);
+                        warp_aggregated_add(P, grad, i0, g0, valid);
+                        warp_aggregated_add(P, grad, i1, g1, valid);
+                        warp_aggregated_add(P, grad, i2, g2, valid);
                         beta *= A.albedo;
                     }
                 }
@@ -622,9 +624,9 @@ hf_render_backward_prim_kernel(const __grid_constant__ HfParams P, const __grid_
         const bool valid = prim != HF_NO_PRIM && a_v != 0.f;
         uint32_t i0 = 0, i1 = 0, i2 = 0; float g0 = 0.f, g1 = 0.f, g2 = 0.f;
         if (valid) hf_shade_adjoint(P, A, prim, a_v, i0, i1, i2, g0, g1, g2);
-        warp_aggregated_add(grad, i0, g0, valid);
-        warp_aggregated_add(grad, i1, g1, valid);
-        warp_aggregated_add(grad, i2, g2, valid);
+        warp_aggregated_add(P, grad, i0, g0, valid);
+        warp_aggregated_add(P, grad, i1, g1, valid);
+        warp_aggregated_add(P, grad, i2, g2, valid);
     }
 }
 
@@ -668,6 +670,9 @@ static HfRenderArgs hf_render_args(const HfParams &P, const hf_camera &cam, cons
     }
     A.o_obj.x = r[0]; A.o_obj.y = r[1]; A.o_obj.z = r[2];
     A.pixels = d_pixels; A.npix = npix;
+    static const int env_tail = getenv("HF_B200_RTAIL") ? atoi(getenv("HF_B200_RTAIL")) : -1;          // dev knobs
+    static const int env_mid = getenv("HF_B200_RMIDTAIL") ? atoi(getenv("HF_B200_RMIDTAIL")) : -1;
+    A.tail = env_tail >= 0 ? env_tail : HF_RENDER_TAIL; A.midtail = env_mid >= 0 ? env_mid : HF_RENDER_MIDTAIL;
     auto lowbias32 = [](uint32_t x) { x ^= x >> 16; x *= 0x7FEB352Du; x ^= x >> 15; x *= 0x846CA68Bu; x ^= x >> 16; return x; };
     A.seed_h0 = lowbias32(cam.seed * 0x9E3779B1u + 0u * 0x85EBCA6Bu);
     A.seed_h1 = lowbias32(cam.seed * 0x9E3779B1u + 1u * 0x85EBCA6Bu);

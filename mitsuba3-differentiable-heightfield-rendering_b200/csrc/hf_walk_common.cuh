@@ -109,7 +109,7 @@ static inline size_t hf_walk_smem(const HfLaunchInfo &li, bool want_fp32) {
 // One RED per distinct address per warp: match.any on the texel index, then a log-step segmented
 // reduction inside each peer group (cf. the reference JIT's reduce_add_f32,
 // ext/drjit/ext/drjit-core/src/cuda_eval.cpp:805-888, which walks its peers serially).
-__device__ __forceinline__ void warp_aggregated_add(float *__restrict__ grad, uint32_t idx, float val, bool valid) {
+__device__ __forceinline__ void warp_aggregated_add(const HfParams &P, float *__restrict__ grad, uint32_t idx, float val, bool valid) {
     const unsigned act = __ballot_sync(FULL_MASK, valid);
     if (!valid) return;
     const unsigned lane = threadIdx.x & 31u;
@@ -126,6 +126,6 @@ __device__ __forceinline__ void warp_aggregated_add(float *__restrict__ grad, ui
         peers &= ~retired;
         rel >>= 1;
     }
-    if (leader) atomicAdd(grad + idx, val);
+    if (leader) hf_grad_add(P, grad, idx, val);
 }
 

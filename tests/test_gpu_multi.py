@@ -116,3 +116,108 @@ def test_allreduced_gradient_equals_single_rank_gradient(tmp_path):
     mp.spawn(_worker, args=(world, port, str(tmp_path)), nprocs=world, join=True)
     assert os.path.exists(tmp_path / "ok")
     print(open(tmp_path / "ok").read())
+
+
+def _peer_worker(rank, world, port, out_dir):
+    import torch.distributed as dist
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    import hfb200
+    from hfb200 import workloads as wl
+    torch.cuda.set_device(rank)
+    dev = torch.device("cuda", rank)
+    hs, img, spp, tile = 300, 128, 8, 16                      # 90 000 texels: slabs are not a power of two, the last one is short
+    cam = wl.CONFIGS["C1"]["camera"]
+    h = wl.fbm_heights(hs, octaves=5, seed=0xC1, device=dev)
+
+    def trace(shape, pix):
+        o, d = wl.camera_rays(cam["origin"], cam["target"], cam["up"], cam["fov"], img, img, spp, seed=3, device=dev, pixels=pix)
+        ray = hfb200.Ray3f(o, d, device=dev)
+        adj = wl.hashed_adjoints(o.shape[1], seed=1, device=dev, ids=wl.global_ray_ids(pix, spp))
+        si, pi = shape.ray_intersect(ray, return_prelim=True, fields=("t", "p", "n", "uv"))
+        shape.backward(ray, pi, adj)
+
+    def everyone_agrees(t, what):
+        got = [None] * world
+        dist.all_gather_object(got, t.detach().cpu().numpy().tobytes())
+        assert all(g == got[0] for g in got), f"ranks disagree on {what}"
+
+    shape = hfb200.load_dict({"type": "heightfield", "heights": h, "max_height": 0.25}, device=dev)
+    handles = [None] * world
+    dist.all_gather_object(handles, shape.peer_export())
+    shape.peer_attach(rank, world, handles)
+    my_pix = wl.tile_pixels(img, img, tile, rank, world, device=dev)
+    all_pix = torch.arange(img * img, dtype=torch.int64, device=dev)
+
+    # single-rank references (a second, unattached context on this GPU)
+    one = hfb200.load_dict({"type": "heightfield", "heights": h, "max_height": 0.25}, device=dev)
+    one.zero_grad(); trace(one, all_pix); torch.cuda.synchronize()
+    g1 = one.grad.double().clone()
+
+    # ---- (1) scatter to the owners + gather == the single-rank gradient, identical bits on every rank
+    def peer_step():
+        shape.peer_zero_grad(); shape.peer_barrier()
+        trace(shape, my_pix)
+        shape.peer_barrier(); shape.peer_gather_grad(); shape.peer_barrier()
+    for attempt in range(3):                                   # the counters only grow: repeated steps must keep working
+        peer_step()
+        torch.cuda.synchronize()
+        err = float((shape.grad.double() - g1).norm() / g1.norm())
+        assert err < 1e-4, f"peer scatter + gather vs single rank: {err:.2e} (attempt {attempt})"
+        everyone_agrees(shape.grad, "the gathered gradient")
+
+    # ---- (2) the same step replayed from a CUDA graph (the barrier is a kernel)
+    replay = hfb200.capture(peer_step)
+    for _ in range(2):
+        replay()
+    torch.cuda.synchronize()
+    assert float((shape.grad.double() - g1).norm() / g1.norm()) < 1e-4
+    everyone_agrees(shape.grad, "the gathered gradient after a graph replay")
+
+    # ---- (3) the fused render step scatters to the owners as well
+    camr = hfb200.perspective_camera(cam["origin"], cam["target"], cam["up"], cam["fov"], img, img, 16, seed=5)
+    light = hfb200.directional_light((0.3, 0.2, 1.0))
+    target = torch.zeros(img, img, device=dev)
+    one.zero_grad(); one.render_step_l2(camr, light, target); torch.cuda.synchronize()
+    gr = one.grad.double().clone()
+    shape.peer_zero_grad(); shape.peer_barrier()
+    shape.render_step_l2(camr, light, target, my_pix.to(torch.int32))
+    shape.peer_barrier(); shape.peer_gather_grad(); shape.peer_barrier()
+    torch.cuda.synchronize()
+    assert float((shape.grad.double() - gr).norm() / gr.norm()) < 1e-4
+
+    # ---- (4) sharded Adam fused with the all-gather of the heights: every rank ends with the single-rank Adam's field
+    params1, paramsN = hfb200.traverse(one), hfb200.traverse(shape)
+    opt1, optN = hfb200.Adam(lr=1e-2, params=params1), hfb200.Adam(lr=1e-2, params=paramsN)
+    for it in range(3):
+        one.zero_grad(); trace(one, all_pix); opt1.step(); params1.update()
+        shape.peer_zero_grad(); shape.peer_barrier()
+        trace(shape, my_pix)
+        shape.peer_barrier(); optN.step(peer=True); shape.peer_barrier(); paramsN.update()
+        torch.cuda.synchronize()
+        # Adam's first steps move a texel by ~lr whatever the gradient's size: compare where the gradient is well above its rounding noise
+        big = g1.abs() > 1e-3 * g1.abs().max()
+        assert float((shape.heights - one.heights).abs()[big].max()) < 1e-5
+        everyone_agrees(shape.heights, "the heights after the sharded Adam step")
+        assert np.allclose(shape.bbox(), one.bbox(), atol=1e-5)
+    shape.peer_detach()
+    shape.zero_grad(); trace(shape, my_pix); torch.cuda.synchronize()        # detached: a plain local context again
+    assert float(shape.grad.abs().sum()) > 0
+    if rank == 0:
+        with open(os.path.join(out_dir, "ok_peer"), "w") as f:
+            f.write("ok\n")
+    dist.barrier()
+    del shape, one
+    dist.destroy_process_group()
+
+
+@pytest.mark.skipif(_ngpu() < 2, reason=f"needs >= 2 GPUs on one box (found {_ngpu()})")
+def test_peer_scatter_equals_single_rank(tmp_path):
+    """include/hf_b200.h "multi-GPU over peer memory": gradient scatters go to the texel's owner over NVLink, the gather is a store
+    kernel, Adam is sharded and fused with the all-gather of the heights. Against one rank tracing every ray."""
+    import torch.multiprocessing as mp
+    world = 2
+    port = 29900 + (os.getpid() % 2000)
+    mp.spawn(_peer_worker, args=(world, port, str(tmp_path)), nprocs=world, join=True)
+    assert os.path.exists(tmp_path / "ok_peer")
