@@ -370,15 +370,12 @@ def main_ours(a):
             def step_peer():
                 cur = torch.cuda.current_stream()
                 zside.wait_stream(cur)
-                with torch.cuda.stream(zside):              # own slab cleared + cross-GPU barrier beside the forward kernel
+                with torch.cuda.stream(zside):              # gradient grid cleared beside the forward kernel
                     shape.peer_zero_grad()
-                    shape.peer_barrier()
                 shape.ray_intersect(ray, out=(si, pi))
                 cur.wait_stream(zside)
-                shape.backward(ray, pi, adj_c)              # red.global.add.f32 to the owner's grid (local or over NVLink)
-                shape.peer_barrier()
-                shape.peer_gather_grad()                    # own (fully reduced) slab -> every rank's grid
-                shape.peer_barrier()
+                shape.backward(ray, pi, adj_c)
+                shape.peer_reduce_grad()                    # partial slabs -> owners (peer stores) | barrier | owner sums, stores the sum to every rank | barrier
             step_peer(); torch.cuda.synchronize()
             rel = (shape.grad.double() - g_nccl.double()).norm() / g_nccl.double().norm()
             if world > 1:
@@ -390,11 +387,17 @@ def main_ours(a):
             for _ in range(3):
                 run_peer()
             ms_peer = timed(run_peer, a.steps) / a.steps
-            gather_ms = timed(lambda: (shape.peer_gather_grad(), shape.peer_barrier()), 10) / 10
+            reduce_ms = timed(shape.peer_reduce_grad, 10) / 10
             peer = {"ms_per_step": ms_peer, "mrays": n_total / (ms_peer * 1e-3) / 1e6, "launch": peer_launch, "grad_rel_l2_vs_nccl_step": float(rel),
-                    "gather_and_barrier_ms": gather_ms,
-                    "what": "zero own slab + barrier (beside the forward kernel) -> intersect/SI -> backward scattering to the texels' owners over NVLink -> barrier -> "
-                            "all-gather of the reduced slabs by peer stores -> barrier"}
+                    "reduce_ms": reduce_ms,
+                    "what": "zero_grad (beside the forward kernel) -> intersect/SI -> backward -> hf_peer_reduce_grad: partial slabs stored into their owners' "
+                            "staging areas over NVLink, barrier kernel, owners sum in rank order and store the sum into every rank's grid, barrier kernel"}
+            if os.environ.get("HF_BENCH_PEER_ATOMICS", "0") == "1":        # the rejected variant, for the record: scatters go to the owner with remote atomics
+                shape.peer_set_mode(0)
+                for _ in range(3):
+                    step_peer()
+                peer["remote_atomics_ms_per_step"] = timed(step_peer, a.steps) / a.steps
+                shape.peer_set_mode(1)
             state["peer"] = True
         except Exception as exc:      # noqa: BLE001
             print(f"bench.py: peer-memory path unavailable ({type(exc).__name__}: {exc}); NCCL allreduce only", file=sys.stderr, flush=True)
@@ -403,7 +406,7 @@ def main_ours(a):
                  "what": "zero_grad -> intersect/SI -> backward -> ONE ncclAllReduce(grad, fp32, sum) on NCCL-registered memory"}
     if peer is not None and peer["grad_rel_l2_vs_nccl_step"] < 1e-4 and peer["ms_per_step"] < ms_step and os.environ.get("HF_BENCH_COLLECTIVE", "auto") != "nccl-headline":
         ms_step, launch = peer["ms_per_step"], peer["launch"]
-        collective = ("peer scatter: gradient atomics go to the texel's owner over NVLink inside the backward kernel (reduce-scatter), all-gather by peer stores; "
+        collective = ("reduce-scatter + all-gather written as two kernels over peer memory (NVLink stores into IPC-mapped grids, device-side barriers); "
                       "the single-ncclAllReduce step is timed beside it (extras.nccl_allreduce_step)")
     clocks = sampler.stop() if rank == 0 else None
     value = n_total / (ms_step * 1e-3) / 1e6
@@ -419,18 +422,15 @@ def main_ours(a):
     opt = hfb200.Adam(lr=1e-3, params=params)
 
     def full_step():
-        if state["peer"]:                               # sharded Adam fused with the all-gather of the heights
+        if state["peer"]:                               # reduce-scatter -> sharded Adam -> all-gather of the heights, over peer memory
             cur = torch.cuda.current_stream()
             zside.wait_stream(cur)
             with torch.cuda.stream(zside):
                 shape.peer_zero_grad()
-                shape.peer_barrier()
             shape.ray_intersect(ray, out=(si, pi))
             cur.wait_stream(zside)
             shape.backward(ray, pi, adj_c)
-            shape.peer_barrier()
             opt.step(peer=True)
-            shape.peer_barrier()
         else:
             step()
             opt.step()
@@ -573,7 +573,7 @@ def run_render_step(a, shape, h, params, opt, rank, world, dev, timed, ev, peer=
 
     def step(record=False):
         if peer:
-            shape.peer_zero_grad(); shape.peer_barrier()
+            shape.peer_zero_grad()
         else:
             shape.zero_grad()
         loss.zero_()
@@ -583,8 +583,8 @@ def run_render_step(a, shape, h, params, opt, rank, world, dev, timed, ev, peer=
         shape.render_step_l2(cam, light, target, pix, image=image, loss=loss)
         if record:
             e1.record(); k_times.append((e0, e1))
-        if peer:                                # the kernel scattered to the owners: sharded Adam + all-gather of the heights by peer stores
-            shape.peer_barrier(); opt.step(peer=True); shape.peer_barrier()
+        if peer:                                # reduce-scatter by peer stores -> sharded Adam -> heights stored into every rank's grid
+            opt.step(peer=True)
         else:
             if world > 1:
                 shape.allreduce_grad()
@@ -593,7 +593,7 @@ def run_render_step(a, shape, h, params, opt, rank, world, dev, timed, ev, peer=
 
     def kernel_only(record=True):          # the fused kernel alone on the initial field (heights do not move)
         if peer:
-            shape.peer_zero_grad(); shape.peer_barrier()
+            shape.peer_zero_grad()
         else:
             shape.zero_grad()
         e0, e1 = ev(), ev()
@@ -631,8 +631,8 @@ def run_render_step(a, shape, h, params, opt, rank, world, dev, timed, ev, peer=
     loss1 = float(loss.item())
     n_total = a.image * a.image * a.spp
     out = {"what": "zero_grad + hf_render_step_l2 (camera rays, direct illumination, box filter, L2 adjoint, backward in ONE kernel) + " +
-                   ("barrier + sharded Adam storing the heights into every rank's grid over NVLink + barrier" if peer else "allreduce + Adam") + " + pyramid rebuild",
-           "collective": "peer scatter (gradient atomics to the owner inside the kernel)" if peer else ("ncclAllReduce" if world > 1 else "none"), "ms_per_step": ms, "mrays": n_total / (ms * 1e-3) / 1e6, "launch": launch,
+                   ("reduce-scatter by peer stores + sharded Adam storing the heights into every rank's grid over NVLink" if peer else "allreduce + Adam") + " + pyramid rebuild",
+           "collective": "peer memory: reduce-scatter -> sharded Adam -> all-gather of the heights" if peer else ("ncclAllReduce" if world > 1 else "none"), "ms_per_step": ms, "mrays": n_total / (ms * 1e-3) / 1e6, "launch": launch,
            "kernel_ms": kms, "kernel_ms_": kms, "kernel_mrays": n_total / world / (kms * 1e-3) / 1e6 * world,
            "loss_first_step_local": loss0, "loss_last_step_local": loss1, "gpu_launches_per_step": 6}
     if world == 1 and not a.no_e2e:

@@ -183,25 +183,31 @@ int hf_comm_destroy(hf_ctx *ctx);
 int hf_allreduce_grad(hf_ctx *ctx, void *stream);                  /* ncclAllReduce(grad, fp32, sum) */
 
 /* ---- multi-GPU over peer memory (one NVSwitch box, one process per GPU) -----------------------------------------------------
- * The fused alternative to "scatter locally, then allreduce 64 MiB": the gradient grid is cut into nranks slabs, rank r OWNS slab r,
- * and every scatter of every kernel (hf_backward, the render entries) goes straight to the owner's grid with red.global.add.f32
- * over NVLink -- the reduce-scatter happens inside the kernels that produce the gradient, a few bytes per distinct texel per warp.
- * What remains of the collective is an all-gather: hf_peer_gather_grad (stores of the own slab into every rank's grid), or, for an
- * optimisation step, hf_peer_adam_step (Adam on the own slab, updated heights stored into every rank's height grid).
- *   set-up   every rank: hf_peer_export -> 192 bytes; ship them (like the NCCL id); every rank: hf_peer_attach(rank, nranks, all)
- *   a step   hf_peer_zero_grad (own slab) -> hf_peer_barrier -> forward / backward / render entries -> hf_peer_barrier ->
- *            hf_peer_gather_grad | hf_peer_adam_step -> hf_peer_barrier [-> hf_parameters_changed]
- * hf_peer_barrier is a kernel (a cross-GPU barrier through counters in peer memory): it lives in streams and CUDA graphs. While
- * attached, hf_zero_grad must not be used (it would clear contributions of the peers). hf_peer_export moves the gradient grid out of
- * NCCL-registered memory if hf_comm_init put it there (CUDA IPC shares cudaMalloc memory): fetch hf_grad() again. */
-#define HF_PEER_HANDLE_BYTES 192
+ * The fused alternative to "scatter, then ONE ncclAllReduce of the grid": the ranks map each other's grids (CUDA IPC over NVLink),
+ * the grid is cut into nranks slabs, rank r OWNS slab r, and the collective is written as kernels of this library:
+ *   mode 1 (default)  every kernel scatters into its LOCAL grid as on one GPU; hf_peer_reduce_grad then (A) stores each partial slab
+ *                     into its owner's staging area (peer stores at link rate), (barrier), (B) the owner sums the partials in rank
+ *                     order and stores the sum into EVERY rank's grid -- reduce-scatter and all-gather in two kernels; with
+ *                     hf_peer_adam_step kernel B applies Adam to the slab instead and stores the updated HEIGHTS into every rank's
+ *                     height grid (reduce-scatter -> sharded Adam -> all-gather, the gradient never travels back).
+ *   mode 0            every scatter of every kernel goes straight to the owner's grid with red.global.add.f32 over NVLink (the
+ *                     reduce-scatter happens inside the producing kernel); measured SLOWER than mode 1 and than NCCL: remote atomics
+ *                     reach ~2 G/s (profiles/r02_notes.md). Kept for the record and the tests.
+ *   set-up   every rank: hf_peer_export -> 256 bytes; ship them (like the NCCL id); every rank: hf_peer_attach(rank, nranks, all)
+ *   a step   hf_peer_zero_grad -> forward / backward / render entries -> hf_peer_reduce_grad | hf_peer_adam_step [-> hf_parameters_changed]
+ * All of it is stream-ordered and capturable: the cross-GPU barrier is a kernel (counters in peer memory; hf_peer_barrier exports it).
+ * While attached use hf_peer_zero_grad, not hf_zero_grad. hf_peer_export moves the gradient grid out of NCCL-registered memory if
+ * hf_comm_init put it there (CUDA IPC shares cudaMalloc memory): fetch hf_grad() again. Results: every rank ends with bit-identical
+ * grids (one owner sums in a fixed order and everybody receives its stores). */
+#define HF_PEER_HANDLE_BYTES 256
 int hf_peer_export(hf_ctx *ctx, uint8_t out_handles[HF_PEER_HANDLE_BYTES]);
 int hf_peer_attach(hf_ctx *ctx, int rank, int nranks, const uint8_t *all_handles /* nranks x HF_PEER_HANDLE_BYTES, rank-major */);
+int hf_peer_set_mode(hf_ctx *ctx, int mode);
 int hf_peer_detach(hf_ctx *ctx);
 int hf_peer_barrier(hf_ctx *ctx, void *stream);
 int hf_peer_zero_grad(hf_ctx *ctx, void *stream);
-int hf_peer_gather_grad(hf_ctx *ctx, void *stream);
-int hf_peer_adam_step(hf_ctx *ctx, const hf_adam *cfg, void *stream);
+int hf_peer_reduce_grad(hf_ctx *ctx, void *stream);                 /* afterwards every rank's gradient grid holds the sum over ranks */
+int hf_peer_adam_step(hf_ctx *ctx, const hf_adam *cfg, void *stream); /* afterwards every rank's heights hold the Adam update of the summed gradient */
 
 /* ---- render step on the heightfield alone ----------------------------------------------
  * The callers of the shape in the reference, restated for ONE heightfield lit by ONE directional emitter and seen by

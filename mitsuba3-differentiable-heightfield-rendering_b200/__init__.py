@@ -167,7 +167,8 @@ def _load():
         "hf_peer_detach": [vp],
         "hf_peer_barrier": [vp, vp],
         "hf_peer_zero_grad": [vp, vp],
-        "hf_peer_gather_grad": [vp, vp],
+        "hf_peer_reduce_grad": [vp, vp],
+        "hf_peer_set_mode": [vp, C.c_int],
         "hf_peer_adam_step": [vp, C.POINTER(_Adam), vp],
     }
     for name, args in sig.items():
@@ -573,7 +574,7 @@ class Heightfield:
             _check(_load().hf_allreduce_grad(self._ctx, _stream()))
 
     # -- multi-GPU over peer memory: scatters go to the texel's owner over NVLink (include/hf_b200.h "multi-GPU over peer memory") --
-    PEER_HANDLE_BYTES = 192
+    PEER_HANDLE_BYTES = 256
 
     def _rewrap_grad(self):
         gp = C.c_void_p()
@@ -592,7 +593,7 @@ class Heightfield:
         """handles: the peer_export() bytes of ranks 0 .. world_size - 1, in rank order."""
         blob = b"".join(handles)
         if len(blob) != world_size * self.PEER_HANDLE_BYTES:
-            raise HeightfieldError("peer_attach: need one 192-byte handle block per rank")
+            raise HeightfieldError("peer_attach: need one 256-byte handle block per rank")
         buf = (C.c_uint8 * len(blob)).from_buffer_copy(blob)
         with torch.cuda.device(self.device):
             _check(_load().hf_peer_attach(self._ctx, rank, world_size, buf))
@@ -611,9 +612,14 @@ class Heightfield:
         with torch.cuda.device(self.device):
             _check(_load().hf_peer_zero_grad(self._ctx, _stream()))
 
-    def peer_gather_grad(self):
+    def peer_reduce_grad(self):
+        """After the scatter kernels: every rank's gradient grid holds the sum over ranks (bit-identical everywhere)."""
         with torch.cuda.device(self.device):
-            _check(_load().hf_peer_gather_grad(self._ctx, _stream()))
+            _check(_load().hf_peer_reduce_grad(self._ctx, _stream()))
+
+    def peer_set_mode(self, mode):
+        """1 (default): local scatter + reduce-scatter by peer stores; 0: scatters go to the owner with remote atomics."""
+        _check(_load().hf_peer_set_mode(self._ctx, int(mode)))
 
     def peer_adam_step(self, lr, beta_1=0.9, beta_2=0.999, epsilon=1e-8, mask_updates=False):
         cfg = _Adam(lr, beta_1, beta_2, epsilon, int(mask_updates))
@@ -819,8 +825,8 @@ class Adam:
             params._shape.adam_reset()
 
     def step(self, peer=False):
-        """peer=True (after Heightfield.peer_attach): Adam on this rank's slab of the grid, updated heights stored into every rank's
-        height grid; the caller puts a peer_barrier() between this and params.update()."""
+        """peer=True (after Heightfield.peer_attach): reduce-scatter of the gradient, Adam on this rank's slab, updated heights stored
+        into every rank's height grid (barriers included); params.update() next."""
         s = self.params._shape
         if peer:
             s.peer_adam_step(self.lr, self.beta_1, self.beta_2, self.epsilon, self.mask_updates)

@@ -167,6 +167,10 @@ struct hf_ctx {
     float **d_peer_grad_tab = nullptr, **d_peer_heights_tab = nullptr;
     unsigned **d_peer_counter_tab = nullptr;
     unsigned *d_xcounter = nullptr;       // [0] = this rank's barrier counter (peers add to it), [64] = the epoch (local)
+    int peer_mode = 1;                    // 1: scatter locally, reduce-scatter by peer stores (default); 0: scatter to the owner with remote atomics
+    float *d_stage = nullptr;             // staging area of this rank: slot r = rank r's partial sums for MY slab
+    float *peer_stage[HF_MAX_PEERS] = { nullptr };
+    float **d_peer_stage_tab = nullptr;
     // host-buffer render step: device copies of the caller's target / image / pixel list, and the loss
     float *d_hs_target = nullptr, *d_hs_image = nullptr;
     uint32_t *d_hs_pixels = nullptr;
@@ -761,7 +765,9 @@ static void peer_release(hf_ctx *c);
 static void peer_release_fwd(hf_ctx *c) {
     peer_release(c);
     cudaFree(c->d_peer_grad_tab); cudaFree(c->d_peer_heights_tab); cudaFree(c->d_peer_counter_tab); cudaFree(c->d_xcounter);
+    cudaFree(c->d_peer_stage_tab); cudaFree(c->d_stage);
     c->d_peer_grad_tab = nullptr; c->d_peer_heights_tab = nullptr; c->d_peer_counter_tab = nullptr; c->d_xcounter = nullptr;
+    c->d_peer_stage_tab = nullptr; c->d_stage = nullptr;
 }
 static void peer_release(hf_ctx *c) {
     for (int r = 0; r < HF_MAX_PEERS; ++r) {
@@ -769,8 +775,9 @@ static void peer_release(hf_ctx *c) {
             if (c->peer_grad[r] && c->peer_grad[r] != c->d_grad) cudaIpcCloseMemHandle(c->peer_grad[r]);
             if (c->peer_heights[r] && c->peer_heights[r] != c->d_heights) cudaIpcCloseMemHandle(c->peer_heights[r]);
             if (c->peer_counter[r] && c->peer_counter[r] != c->d_xcounter) cudaIpcCloseMemHandle(c->peer_counter[r]);
+            if (c->peer_stage[r] && c->peer_stage[r] != c->d_stage) cudaIpcCloseMemHandle(c->peer_stage[r]);
         }
-        c->peer_grad[r] = nullptr; c->peer_heights[r] = nullptr; c->peer_counter[r] = nullptr;
+        c->peer_grad[r] = nullptr; c->peer_heights[r] = nullptr; c->peer_counter[r] = nullptr; c->peer_stage[r] = nullptr;
     }
     c->peer_n = 1; c->peer_rank = 0; c->slab_elems = 0;
     c->P.peer_n = 1;
@@ -796,10 +803,15 @@ extern "C" int hf_peer_export(hf_ctx *c, uint8_t out[HF_PEER_HANDLE_BYTES]) {
         CU(cudaMalloc(&c->d_xcounter, size_t(2) << 20));            // an allocation of its own (IPC maps whole allocations)
         CU(cudaMemset(c->d_xcounter, 0, size_t(2) << 20));
     }
-    cudaIpcMemHandle_t h[3];
+    if (!c->d_stage) {                                              // one slab per sender, whatever the number of ranks will be
+        const size_t elems = (size_t) c->W * c->H + (size_t) HF_MAX_PEERS * 2048;
+        CU(cudaMalloc(&c->d_stage, std::max(elems * sizeof(float), size_t(2) << 20)));
+    }
+    cudaIpcMemHandle_t h[4];
     CU(cudaIpcGetMemHandle(&h[0], c->d_grad));
     CU(cudaIpcGetMemHandle(&h[1], c->d_heights));
     CU(cudaIpcGetMemHandle(&h[2], c->d_xcounter));
+    CU(cudaIpcGetMemHandle(&h[3], c->d_stage));
     memcpy(out, h, sizeof(h));
     return HF_OK;
 }
@@ -814,22 +826,24 @@ extern "C" int hf_peer_attach(hf_ctx *c, int rank, int nranks, const uint8_t *al
     peer_release(c);
     c->peer_rank = rank;
     for (int r = 0; r < nranks; ++r) {
-        if (r == rank) { c->peer_grad[r] = c->d_grad; c->peer_heights[r] = c->d_heights; c->peer_counter[r] = c->d_xcounter; continue; }
-        cudaIpcMemHandle_t h[3];
+        if (r == rank) { c->peer_grad[r] = c->d_grad; c->peer_heights[r] = c->d_heights; c->peer_counter[r] = c->d_xcounter; c->peer_stage[r] = c->d_stage; continue; }
+        cudaIpcMemHandle_t h[4];
         memcpy(h, all_handles + (size_t) r * HF_PEER_HANDLE_BYTES, sizeof(h));
-        void *pg = nullptr, *ph = nullptr, *pc = nullptr;
+        void *pg = nullptr, *ph = nullptr, *pc = nullptr, *ps = nullptr;
         cudaError_t e1 = cudaIpcOpenMemHandle(&pg, h[0], cudaIpcMemLazyEnablePeerAccess);
         cudaError_t e2 = e1 == cudaSuccess ? cudaIpcOpenMemHandle(&ph, h[1], cudaIpcMemLazyEnablePeerAccess) : e1;
         cudaError_t e3 = e2 == cudaSuccess ? cudaIpcOpenMemHandle(&pc, h[2], cudaIpcMemLazyEnablePeerAccess) : e2;
+        if (e3 == cudaSuccess) e3 = cudaIpcOpenMemHandle(&ps, h[3], cudaIpcMemLazyEnablePeerAccess);
         if (e3 != cudaSuccess) {
             cudaGetLastError();
             if (pg) cudaIpcCloseMemHandle(pg);
             if (ph) cudaIpcCloseMemHandle(ph);
+            if (pc) cudaIpcCloseMemHandle(pc);
             c->peer_n = r;                         // release what was opened so far
             peer_release(c);
             return fail(HF_ERR_CUDA, "hf_peer_attach: cannot map rank %d's grids over CUDA IPC (%s); is peer access between the GPUs available?", r, cudaGetErrorString(e3));
         }
-        c->peer_grad[r] = (float *) pg; c->peer_heights[r] = (float *) ph; c->peer_counter[r] = (unsigned *) pc;
+        c->peer_grad[r] = (float *) pg; c->peer_heights[r] = (float *) ph; c->peer_counter[r] = (unsigned *) pc; c->peer_stage[r] = (float *) ps;
     }
     c->peer_n = nranks;
     const size_t total = (size_t) c->W * c->H;
@@ -838,13 +852,24 @@ extern "C" int hf_peer_attach(hf_ctx *c, int rank, int nranks, const uint8_t *al
         CU(cudaMalloc(&c->d_peer_grad_tab, HF_MAX_PEERS * sizeof(float *)));
         CU(cudaMalloc(&c->d_peer_heights_tab, HF_MAX_PEERS * sizeof(float *)));
         CU(cudaMalloc(&c->d_peer_counter_tab, HF_MAX_PEERS * sizeof(unsigned *)));
+        CU(cudaMalloc(&c->d_peer_stage_tab, HF_MAX_PEERS * sizeof(float *)));
     }
+    CU(cudaMemcpy(c->d_peer_stage_tab, c->peer_stage, HF_MAX_PEERS * sizeof(float *), cudaMemcpyHostToDevice));
     CU(cudaMemcpy(c->d_peer_grad_tab, c->peer_grad, HF_MAX_PEERS * sizeof(float *), cudaMemcpyHostToDevice));
     CU(cudaMemcpy(c->d_peer_heights_tab, c->peer_heights, HF_MAX_PEERS * sizeof(float *), cudaMemcpyHostToDevice));
     CU(cudaMemcpy(c->d_peer_counter_tab, c->peer_counter, HF_MAX_PEERS * sizeof(unsigned *), cudaMemcpyHostToDevice));
     const HfDivMagic dm = hf_divmagic((uint32_t) c->slab_elems);
-    c->P.slab_magic = dm.m; c->P.slab_shift = dm.s; c->P.peer_n = nranks;
+    c->P.slab_magic = dm.m; c->P.slab_shift = dm.s;
     for (int r = 0; r < HF_MAX_PEERS; ++r) c->P.grad_peer[r] = r < nranks ? c->peer_grad[r] : nullptr;
+    c->P.peer_n = c->peer_mode == 0 ? nranks : 1;         // mode 1: the kernels scatter into the local grid
+    return HF_OK;
+}
+
+extern "C" int hf_peer_set_mode(hf_ctx *c, int mode) {
+    CHECK_CTX(c);
+    if (mode != 0 && mode != 1) return fail(HF_ERR_INVALID, "hf_peer_set_mode: 0 (remote atomics to the owner) or 1 (local scatter + reduce-scatter by peer stores)");
+    c->peer_mode = mode;
+    if (c->peer_n > 1) c->P.peer_n = mode == 0 ? c->peer_n : 1;
     return HF_OK;
 }
 
@@ -870,25 +895,62 @@ extern "C" int hf_peer_barrier(hf_ctx *c, void *stream) {
     CU(hf_launch_peer_barrier(c->d_peer_counter_tab, c->d_xcounter, c->d_xcounter + 64, c->peer_n, (cudaStream_t) stream));
     return HF_OK;
 }
+static int peer_barrier(hf_ctx *c, cudaStream_t st);
+
+static int peer_barrier(hf_ctx *c, cudaStream_t st) {
+    CU(hf_launch_peer_barrier(c->d_peer_counter_tab, c->d_xcounter, c->d_xcounter + 64, c->peer_n, st));
+    return HF_OK;
+}
 
 extern "C" int hf_peer_zero_grad(hf_ctx *c, void *stream) {
     CHECK_CTX(c);
     NEED_PEERS(c);
     CU(cudaSetDevice(c->device));
-    size_t lo, hi;
+    cudaStream_t st = (cudaStream_t) stream;
+    if (c->peer_mode == 1) {              // every rank scatters into its own (whole) grid
+        CU(cudaMemsetAsync(c->d_grad, 0, (size_t) c->W * c->H * sizeof(float), st));
+        return HF_OK;
+    }
+    size_t lo, hi;                        // remote atomics: the owner clears its slab, and nobody may scatter before every slab is clear
     peer_slab(c, lo, hi);
-    if (hi > lo) CU(cudaMemsetAsync(c->d_grad + lo, 0, (hi - lo) * sizeof(float), (cudaStream_t) stream));
-    return HF_OK;
+    if (hi > lo) CU(cudaMemsetAsync(c->d_grad + lo, 0, (hi - lo) * sizeof(float), st));
+    return peer_barrier(c, st);
 }
 
-extern "C" int hf_peer_gather_grad(hf_ctx *c, void *stream) {
+static int peer_reduce(hf_ctx *c, const hf_adam *cfg, cudaStream_t st) {
+    size_t lo, hi;
+    peer_slab(c, lo, hi);
+    const size_t total = (size_t) c->W * c->H;
+    int rc;
+    const bool adam = cfg != nullptr;
+    const double b1 = adam ? cfg->beta1 : 0.0, b2 = adam ? cfg->beta2 : 0.0;
+    if (c->peer_mode == 1) {
+        // A: partial slabs to their owners' staging areas (stores at link rate); barrier; B: the owner sums the partials in rank order
+        // and stores the sum (or, with Adam, the updated heights) into every rank's grid -- reduction and all-gather in one pass
+        CU(hf_launch_peer_send_partials(c->d_grad, c->d_peer_stage_tab, c->peer_n, c->peer_rank, c->slab_elems, total, c->num_sms, st));
+        if ((rc = peer_barrier(c, st))) return rc;
+        CU(hf_launch_peer_reduce_gather(c->d_grad, c->d_stage, adam ? c->d_peer_heights_tab : c->d_peer_grad_tab, c->peer_n, c->peer_rank, lo, hi, c->slab_elems,
+                                        adam, c->d_heights, c->d_m, c->d_v, c->d_adam_t, c->d_adam_lr_t, c->d_adam_table, HF_ADAM_TABLE,
+                                        adam ? (float) cfg->lr : 0.f, (float) b1, (float) b2, (float) (1.0 - b1), (float) (1.0 - b2),
+                                        adam ? (float) cfg->epsilon : 0.f, adam ? cfg->mask_updates : 0, c->num_sms, st));
+    } else {
+        // the scatter kernels already summed every contribution into the owner's slab: wait for all of them, then all-gather by stores
+        if ((rc = peer_barrier(c, st))) return rc;
+        if (adam)
+            CU(hf_launch_peer_adam(c->d_heights, c->d_grad, c->d_m, c->d_v, c->d_peer_heights_tab, c->peer_n, c->peer_rank, lo, hi, c->d_adam_t, c->d_adam_lr_t,
+                                   c->d_adam_table, HF_ADAM_TABLE, (float) cfg->lr, (float) b1, (float) b2, (float) (1.0 - b1), (float) (1.0 - b2),
+                                   (float) cfg->epsilon, cfg->mask_updates, c->num_sms, st));
+        else
+            CU(hf_launch_peer_push(c->d_grad, c->d_peer_grad_tab, c->peer_n, c->peer_rank, lo, hi, c->num_sms, st));
+    }
+    return peer_barrier(c, st);           // every rank's stores have landed: the grids (heights) are complete and identical everywhere
+}
+
+extern "C" int hf_peer_reduce_grad(hf_ctx *c, void *stream) {
     CHECK_CTX(c);
     NEED_PEERS(c);
     CU(cudaSetDevice(c->device));
-    size_t lo, hi;
-    peer_slab(c, lo, hi);
-    CU(hf_launch_peer_push(c->d_grad, c->d_peer_grad_tab, c->peer_n, c->peer_rank, lo, hi, c->num_sms, (cudaStream_t) stream));
-    return HF_OK;
+    return peer_reduce(c, nullptr, (cudaStream_t) stream);
 }
 
 extern "C" int hf_peer_adam_step(hf_ctx *c, const hf_adam *cfg, void *stream) {
@@ -900,15 +962,10 @@ extern "C" int hf_peer_adam_step(hf_ctx *c, const hf_adam *cfg, void *stream) {
     if (!c->have_heights) return fail(HF_ERR_STATE, "heights were never set");
     if (!c->d_m || !c->d_v) { int rc = hf_adam_reset(c, stream); if (rc) return rc; }
     CU(cudaSetDevice(c->device));
-    const double b1 = cfg->beta1, b2 = cfg->beta2;
-    { int rc = ensure_adam_table(c, b1, b2, stream); if (rc) return rc; }
-    size_t lo, hi;
-    peer_slab(c, lo, hi);
-    CU(hf_launch_peer_adam(c->d_heights, c->d_grad, c->d_m, c->d_v, c->d_peer_heights_tab, c->peer_n, c->peer_rank, lo, hi, c->d_adam_t, c->d_adam_lr_t,
-                           c->d_adam_table, HF_ADAM_TABLE, (float) cfg->lr, (float) b1, (float) b2, (float) (1.0 - b1), (float) (1.0 - b2),
-                           (float) cfg->epsilon, cfg->mask_updates, c->num_sms, (cudaStream_t) stream));
-    c->accel_valid = false;       // heights moved (on every rank, once the peers' stores have landed: hf_peer_barrier, then hf_parameters_changed)
-    return HF_OK;
+    { int rc = ensure_adam_table(c, cfg->beta1, cfg->beta2, stream); if (rc) return rc; }
+    int rc = peer_reduce(c, cfg, (cudaStream_t) stream);
+    c->accel_valid = false;       // heights moved on every rank: hf_parameters_changed next
+    return rc;
 }
 
 // ------------------------------------------------------------------------------------------

@@ -48,8 +48,14 @@ __device__ __forceinline__ f3 bw_lin(const float *m, f3 x) {        // M x
 }
 
 // GENERAL: FollowShape and / or adjoints of dp_du, dp_dv are present. IDENT: to_world is the identity (the plugin's default).
+// The kernel is bound by memory latency (ncu: 0.9 eligible warps per cycle, DRAM 38 %), so what matters is how many of a ray's ~20
+// independent loads are in flight together: with the default register budget (40) ptxas serialises them to save registers and the
+// kernel time swings by 40 % with unrelated changes of the arithmetic. HF_BWD_MIN_CTAS resident CTAs per SM = the register budget.
+#ifndef HF_BWD_MIN_CTAS
+#define HF_BWD_MIN_CTAS 3              // measured (C3, ms): 3 -> 0.647, 4 -> 0.679, 5 -> 0.721, 6 -> 0.706
+#endif
 template <bool GENERAL, bool IDENT>
-__global__ void __launch_bounds__(HF_BLOCK)
+__global__ void __launch_bounds__(HF_BLOCK, HF_BWD_MIN_CTAS)
 hf_backward_kernel(const __grid_constant__ HfParams P, const hf_rays R, const hf_prelim PI, const hf_si_adj A,
                    const uint32_t flags, float *__restrict__ grad, const size_t n) {
     const unsigned lane = threadIdx.x & 31u;
@@ -87,17 +93,10 @@ hf_backward_kernel(const __grid_constant__ HfParams P, const hf_rays R, const hf
         if (!valid) prim = 0u;
         float g0 = 0.f, g1 = 0.f, g2 = 0.f;
         if (valid) {
-            f3 ow = mk3(0.f, 0.f, 0.f);
-            if (GENERAL) ow = mk3(__ldcs(R.ox + i), __ldcs(R.oy + i), __ldcs(R.oz + i));     // only FollowShape reads the origin
-            const f3 dw = mk3(__ldcs(R.dx + i), __ldcs(R.dy + i), __ldcs(R.dz + i));
-            const float u = __ldcs(PI.u + i), v = __ldcs(PI.v + i);
-            #define LDA(ptr) ((ptr) ? __ldcs((ptr) + i) : 0.f)
-            const float a_t = LDA(A.t);
-            const f3 a_pw = mk3(LDA(A.px), LDA(A.py), LDA(A.pz));
-            const f3 a_nw = mk3(flip * LDA(A.nx), flip * LDA(A.ny), flip * LDA(A.nz));      // mesh.cpp:837-840
-            const float a_uvx = LDA(A.uvx), a_uvy = LDA(A.uvy);
-
-            // the hit triangle from prim_index: triangle 0 = (p10, p01, p00), triangle 1 = (p10, p11, p01)
+            // Every load of the ray first, in program order (asm volatile keeps ptxas from sinking them behind the arithmetic to save
+            // registers): ~20 independent requests in flight per thread is what hides the DRAM latency this kernel is bound by.
+            #define LDS_CS(dst, ptr) asm volatile("ld.global.cs.f32 %0, [%1];" : "=f"(dst) : "l"((ptr) + i))
+            #define LDA(dst, ptr) do { dst = 0.f; if (ptr) LDS_CS(dst, ptr); } while (0)
             const uint32_t cell = prim >> 1, k = prim & 1u;
             const uint32_t cy = hf_divide(cell, P.nx_magic, P.nx_shift), cx = cell - cy * (uint32_t) P.NX;
 #ifdef HF_DEBUG_BOUNDS
@@ -108,7 +107,28 @@ hf_backward_kernel(const __grid_constant__ HfParams P, const hf_rays R, const hf
             i0 = b + 1u;
             i1 = b + (uint32_t) P.W + k;
             i2 = k ? b + (uint32_t) P.W : b;
-            const float z0 = P.mh * __ldg(h + i0), z1 = P.mh * __ldg(h + i1), z2 = P.mh * __ldg(h + i2);
+            float h0, h1, h2;
+            asm volatile("ld.global.nc.f32 %0, [%1];" : "=f"(h0) : "l"(h + i0));
+            asm volatile("ld.global.nc.f32 %0, [%1];" : "=f"(h1) : "l"(h + i1));
+            asm volatile("ld.global.nc.f32 %0, [%1];" : "=f"(h2) : "l"(h + i2));
+            f3 dw, ow = mk3(0.f, 0.f, 0.f);
+            LDS_CS(dw.x, R.dx); LDS_CS(dw.y, R.dy); LDS_CS(dw.z, R.dz);
+            float u, v;
+            LDS_CS(u, PI.u); LDS_CS(v, PI.v);
+            float a_t, apx, apy, apz, anx, any_, anz, a_uvx, a_uvy;
+            LDA(a_t, A.t); LDA(apx, A.px); LDA(apy, A.py); LDA(apz, A.pz); LDA(anx, A.nx); LDA(any_, A.ny); LDA(anz, A.nz); LDA(a_uvx, A.uvx); LDA(a_uvy, A.uvy);
+            float adu[3] = { 0.f, 0.f, 0.f }, adv[3] = { 0.f, 0.f, 0.f };
+            if (GENERAL) {                                      // only FollowShape reads the origin; dp_du / dp_dv adjoints are rare
+                LDS_CS(ow.x, R.ox); LDS_CS(ow.y, R.oy); LDS_CS(ow.z, R.oz);
+                LDA(adu[0], A.dpdu_x); LDA(adu[1], A.dpdu_y); LDA(adu[2], A.dpdu_z); LDA(adv[0], A.dpdv_x); LDA(adv[1], A.dpdv_y); LDA(adv[2], A.dpdv_z);
+            }
+            #undef LDA
+            #undef LDS_CS
+            const f3 a_pw = mk3(apx, apy, apz);
+            const f3 a_nw = mk3(flip * anx, flip * any_, flip * anz);      // mesh.cpp:837-840
+
+            // the hit triangle from prim_index: triangle 0 = (p10, p01, p00), triangle 1 = (p10, p11, p01)
+            const float z0 = P.mh * h0, z1 = P.mh * h1, z2 = P.mh * h2;
             const float x0 = vtx((int) cx, P.W, P.rw), x1 = vtx((int) cx + 1, P.W, P.rw);
             const float y0 = vtx((int) cy, P.H, P.rh), y1 = vtx((int) cy + 1, P.H, P.rh);
             const f3 p0 = mk3(x1, y0, z0);
@@ -140,10 +160,14 @@ hf_backward_kernel(const __grid_constant__ HfParams P, const hf_rays R, const hf
             // (src/shapes/rectangle.cpp:312-313). NOT 0.5 * e: the rounded texcoords are the function being differentiated, and their
             // differences deviate from the exact half-edge by up to 1e-5 relative -- far above the 1e-4 per-texel tolerance once the
             // texel sums cancel.
+#ifdef HF_BWD_HALF_EDGE          // dev builds only: the form that fails the per-texel tolerance, to measure what the exact form costs
+            const float d0x = 0.5f * e1.x, d0y = 0.5f * e1.y, d1x = 0.5f * e2.x, d1y = 0.5f * e2.y;
+#else
             const float d0x = tex(p1.x) - tex(p0.x), d0y = tex(p1.y) - tex(p0.y), d1x = tex(p2.x) - tex(p0.x), d1y = tex(p2.y) - tex(p0.y);
+#endif
             if (GENERAL && (flags & HF_RAY_DPDUV)) {            // mesh.cpp:778-789
-                const f3 a_du = bw_lin_T<IDENT>(TW, mk3(LDA(A.dpdu_x), LDA(A.dpdu_y), LDA(A.dpdu_z)));
-                const f3 a_dv = bw_lin_T<IDENT>(TW, mk3(LDA(A.dpdv_x), LDA(A.dpdv_y), LDA(A.dpdv_z)));
+                const f3 a_du = bw_lin_T<IDENT>(TW, mk3(adu[0], adu[1], adu[2]));
+                const f3 a_dv = bw_lin_T<IDENT>(TW, mk3(adv[0], adv[1], adv[2]));
                 const float det = d0x * d1y - d0y * d1x;
                 if (det != 0.f) {
                     const float r = 1.0f / det;
@@ -151,8 +175,6 @@ hf_backward_kernel(const __grid_constant__ HfParams P, const hf_rays R, const hf
                     a_e2z += (a_dv.z * d0x - a_du.z * d0y) * r;
                 }
             }
-            #undef LDA
-
             f3 a_p = bw_lin_T<IDENT>(TW, a_pw);
             const float b1 = u, b2 = v, b0 = 1.f - u - v;
             float wz;       // z component of the adjoint that is distributed with the barycentrics

@@ -51,7 +51,9 @@ struct HfParams {
 
 // gradient scatter of one value: the texel's owner takes it (see HfParams::grad_peer)
 __device__ __forceinline__ void hf_grad_add(const HfParams &P, float *__restrict__ grad, uint32_t idx, float val) {
+#ifndef HF_NO_PEER_ATOMICS          // dev builds: measure what the owner lookup costs the single-GPU kernels
     if (P.peer_n > 1) grad = P.grad_peer[hf_divide(idx, P.slab_magic, P.slab_shift)];
+#endif
     atomicAdd(grad + idx, val);
 }
 

@@ -1025,6 +1025,70 @@ hf_peer_adam_kernel(float *__restrict__ p, const float *__restrict__ g, float *_
     }
 }
 
+// ---- reduce-scatter by peer STORES (the default peer mode; remote atomics reach only ~2 G/s over NVLink, stores run at link rate) ----
+// A. every rank stores the part of its LOCAL gradient grid that belongs to rank r into rank r's staging area (slot = sender)
+__global__ void __launch_bounds__(256)
+hf_peer_send_partials_kernel(const float *__restrict__ local, float *const *__restrict__ peer_stage, const int nranks, const int rank,
+                             const size_t slab, const size_t total) {
+    const size_t slab4 = slab / 4;                              // slabs are multiples of 1024 texels
+    const size_t work = slab4 * (size_t) (nranks - 1);
+    for (size_t w = (size_t) blockIdx.x * blockDim.x + threadIdx.x; w < work; w += (size_t) gridDim.x * blockDim.x) {
+        const int k = (int) (w / slab4);
+        const size_t i = w - (size_t) k * slab4;
+        const int r = k < rank ? k : k + 1;                     // the k-th OTHER rank
+        const size_t src = (size_t) r * slab + 4 * i;
+        if (src >= total) continue;
+        float4 v;
+        if (src + 4 <= total) v = *reinterpret_cast<const float4 *>(local + src);
+        else { v.x = local[src]; v.y = src + 1 < total ? local[src + 1] : 0.f; v.z = src + 2 < total ? local[src + 2] : 0.f; v.w = 0.f; }
+        __stcs(reinterpret_cast<float4 *>(peer_stage[r] + (size_t) rank * slab) + i, v);
+    }
+}
+
+// B. the owner sums the partial slabs in rank order (own grid in place of its own slot) and stores the sum into every rank's grid:
+// reduction and all-gather in one pass. ADAM: the sum feeds the Adam update of the slab instead, and the HEIGHTS go to every rank.
+template <bool ADAM>
+__global__ void __launch_bounds__(256)
+hf_peer_reduce_gather_kernel(float *__restrict__ local_grad, const float *__restrict__ my_stage, float *const *__restrict__ peer_out, const int nranks,
+                             const int rank, const size_t lo, const size_t hi, const size_t slab, float *__restrict__ p, float *__restrict__ m,
+                             float *__restrict__ v, const float *__restrict__ lr_t_ptr, const float b1, const float b2, const float omb1, const float omb2,
+                             const float eps, const int mask) {
+    const float lr_t = ADAM ? __ldg(lr_t_ptr) : 0.f;
+    for (size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x; lo + i < hi; i += (size_t) gridDim.x * blockDim.x) {
+        float g = 0.f;
+        for (int r = 0; r < nranks; ++r) g += (r == rank) ? local_grad[lo + i] : __ldcs(my_stage + (size_t) r * slab + i);
+        local_grad[lo + i] = g;
+        float outv = g;
+        if (ADAM) {
+            float pp = p[lo + i], mm = m[lo + i], vv = v[lo + i];
+            adam_one(pp, g, mm, vv, lr_t, b1, b2, omb1, omb2, eps, mask);
+            p[lo + i] = pp; m[lo + i] = mm; v[lo + i] = vv;
+            outv = pp;
+        }
+        for (int r = 0; r < nranks; ++r)
+            if (r != rank) __stcs(peer_out[r] + lo + i, outv);
+    }
+}
+
+cudaError_t hf_launch_peer_send_partials(const float *local, float *const *d_peer_stage, int nranks, int rank, size_t slab, size_t total, int num_sms, cudaStream_t s) {
+    if (nranks < 2) return cudaSuccess;
+    const size_t work = slab / 4 * (size_t) (nranks - 1), blocks = (work + 255) / 256, cap = (size_t) num_sms * 8;
+    hf_peer_send_partials_kernel<<<(int) (blocks < cap ? (blocks ? blocks : 1) : cap), 256, 0, s>>>(local, d_peer_stage, nranks, rank, slab, total);
+    return cudaGetLastError();
+}
+cudaError_t hf_launch_peer_reduce_gather(float *local_grad, const float *my_stage, float *const *d_peer_out, int nranks, int rank, size_t lo, size_t hi, size_t slab,
+                                         bool adam, float *p, float *m, float *v, int *d_t, float *d_lr_t, const float *d_scale_table, int table_len, float lr,
+                                         float beta1, float beta2, float omb1, float omb2, float eps, int mask_updates, int num_sms, cudaStream_t s) {
+    if (adam) hf_adam_prep_kernel<<<1, 1, 0, s>>>(d_t, d_lr_t, d_scale_table, table_len, lr);
+    if (hi > lo) {
+        const size_t blocks = (hi - lo + 255) / 256, cap = (size_t) num_sms * 8;
+        const int grid = (int) (blocks < cap ? (blocks ? blocks : 1) : cap);
+        if (adam) hf_peer_reduce_gather_kernel<true><<<grid, 256, 0, s>>>(local_grad, my_stage, d_peer_out, nranks, rank, lo, hi, slab, p, m, v, d_lr_t, beta1, beta2, omb1, omb2, eps, mask_updates);
+        else hf_peer_reduce_gather_kernel<false><<<grid, 256, 0, s>>>(local_grad, my_stage, d_peer_out, nranks, rank, lo, hi, slab, nullptr, nullptr, nullptr, nullptr, 0.f, 0.f, 0.f, 0.f, 0.f, 0);
+    }
+    return cudaGetLastError();
+}
+
 cudaError_t hf_launch_peer_barrier(unsigned *const *d_peer_counter, unsigned *d_my_counter, unsigned *d_my_epoch, int nranks, cudaStream_t s) {
     hf_peer_barrier_kernel<<<1, 32, 0, s>>>(d_peer_counter, d_my_counter, d_my_epoch, nranks);
     return cudaGetLastError();
