@@ -387,7 +387,10 @@ def main_ours(a):
             for _ in range(3):
                 run_peer()
             ms_peer = timed(run_peer, a.steps) / a.steps
+            torch.cuda.synchronize()
+            state["checksum"] = float(shape.grad.double().abs().sum().item())     # (the leg below re-reduces the reduced grid: timing only)
             reduce_ms = timed(shape.peer_reduce_grad, 10) / 10
+            run_peer()
             peer = {"ms_per_step": ms_peer, "mrays": n_total / (ms_peer * 1e-3) / 1e6, "launch": peer_launch, "grad_rel_l2_vs_nccl_step": float(rel),
                     "reduce_ms": reduce_ms,
                     "what": "zero_grad (beside the forward kernel) -> intersect/SI -> backward -> hf_peer_reduce_grad: partial slabs stored into their owners' "
@@ -412,7 +415,13 @@ def main_ours(a):
     value = n_total / (ms_step * 1e-3) / 1e6
     ms_fwd = float(np.mean([x.elapsed_time(y) for x, y in k_fwd]))
     ms_bwd = float(np.mean([x.elapsed_time(y) for x, y in k_bwd]))
-    grad_checksum = float(shape.grad.double().abs().sum().item())
+    grad_checksum = state.get("checksum") or float(shape.grad.double().abs().sum().item())
+    # how evenly the image tiles spread the work: the step ends with a collective, i.e. with the slowest rank
+    kt = torch.tensor([ms_fwd, ms_bwd], dtype=torch.float64, device=dev)
+    kt_min, kt_max = kt.clone(), kt.clone()
+    if world > 1:
+        dist.all_reduce(kt_min, op=dist.ReduceOp.MIN); dist.all_reduce(kt_max, op=dist.ReduceOp.MAX)
+    rank_spread = {"fwd_ms_min": float(kt_min[0]), "fwd_ms_max": float(kt_max[0]), "bwd_ms_min": float(kt_min[1]), "bwd_ms_max": float(kt_max[1])}
     hits = float(pi.is_valid().float().mean().item())
 
     # ---- secondary modes (extras; not the headline) ----
@@ -523,6 +532,7 @@ def main_ours(a):
                    "full_step_mrays": n_total / (ms_full * 1e-3) / 1e6, "full_step_ms": ms_full,
                    "full_step": "zero_grad + intersect/SI + backward + allreduce + Adam + pyramid rebuild", "full_step_launch": full_launch,
                    "allreduce_ms": ms_allreduce, "nccl_allreduce_step": nccl_step if world > 1 else None, "peer_scatter_step": peer,
+                   "kernel_ms_over_ranks": rank_spread,
                    "grad_rel_l2_vs_single_rank": shard_check,
                    "grad_rel_l2_vs_single_rank_what": "N-rank tile shards + hf_allreduce_grad vs one rank tracing every ray, 512^2 heights, 256^2 x 16 spp, in this run",
                    "grad_abs_sum": grad_checksum, "mean_nodes_per_ray": n_node, "mean_leaves_per_ray": n_leaf},

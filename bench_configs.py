@@ -325,6 +325,7 @@ def run_c5(a, sampler_cls):
             ids = [None] * world
             dist.all_gather_object(ids, hfb200.comm_unique_id() if rank == 0 else None)
             shape.comm_init(rank, world, ids[0])
+            shape.zero_grad(); shape.allreduce_grad(); torch.cuda.synchronize()      # communicator set-up (lazy in NCCL) outside every timed region
         nmax = min(chunk, max(counts))
         si = hfb200.SurfaceInteraction3f(nmax, dev, shape, fields)
         pi = hfb200.PreliminaryIntersection3f(nmax, dev, shape)
@@ -350,6 +351,7 @@ def run_c5(a, sampler_cls):
                 del o, d, ray, adj
             ms_ar = 0.0
             if world > 1:
+                barrier()                                      # every rank has finished its chunks: time the collective alone
                 ms_ar = timed(shape.allreduce_grad, 1)
             t = torch.tensor([ms_i, ms_fb, hits], dtype=torch.float64, device=dev)
             if world > 1:

@@ -553,12 +553,9 @@ hf_intersect_kernel(const __grid_constant__ HfParams P, const HfLaunchInfo li, c
 // One ray through the production walk: load, transform, walk + per-cell primitive, store (+ fused surface interaction).
 // t_start / L_start come from the bundle march (hf_beam_enter) or are 0 / HF_START_LEVEL.
 template <int MODE>
-__device__ __forceinline__ void hf_process_ray(const HfParams &P, const HfGrid &G, const hf_rays &R, const hf_prelim &O,
-                                               const hf_si &S, uint8_t *__restrict__ hit_out, const uint32_t flags,
-                                               const size_t i, const float t_start, const int L_start) {
-    const f3 ow = mk3(__ldcs(R.ox + i), __ldcs(R.oy + i), __ldcs(R.oz + i));
-    const f3 dw = mk3(__ldcs(R.dx + i), __ldcs(R.dy + i), __ldcs(R.dz + i));
-    const float maxt = __ldcs(R.maxt + i);
+__device__ __forceinline__ void hf_process_loaded(const HfParams &P, const HfGrid &G, const hf_rays &R, const hf_prelim &O,
+                                                  const hf_si &S, uint8_t *__restrict__ hit_out, const uint32_t flags,
+                                                  const size_t i, const f3 ow, const f3 dw, const float maxt, const float t_start, const int L_start) {
     const bool active = R.active ? (R.active[i] != 0) : true;
 
     bool hit = false;
@@ -619,6 +616,16 @@ __device__ __forceinline__ void hf_process_ray(const HfParams &P, const HfGrid &
     }
 }
 
+template <int MODE>
+__device__ __forceinline__ void hf_process_ray(const HfParams &P, const HfGrid &G, const hf_rays &R, const hf_prelim &O,
+                                               const hf_si &S, uint8_t *__restrict__ hit_out, const uint32_t flags,
+                                               const size_t i, const float t_start, const int L_start) {
+    const f3 ow = mk3(__ldcs(R.ox + i), __ldcs(R.oy + i), __ldcs(R.oz + i));
+    const f3 dw = mk3(__ldcs(R.dx + i), __ldcs(R.dy + i), __ldcs(R.dz + i));
+    const float maxt = __ldcs(R.maxt + i);
+    hf_process_loaded<MODE>(P, G, R, O, S, hit_out, flags, i, ow, dw, maxt, t_start, L_start);
+}
+
 #ifndef HF_MIN_CTAS
 #define HF_MIN_CTAS 3              // 80 registers, no spills: measured 3 % faster than 4 CTAs of 64 registers once the loop got shorter
 #endif
@@ -636,6 +643,9 @@ __device__ __forceinline__ unsigned long long hf_gtime() { unsigned long long t;
 #ifndef HF_FAST_GROUPS
 #define HF_FAST_GROUPS 4           // 32-ray groups a warp takes off the global counter at a time
 #endif
+// (Tried in round 2 and removed: copying the next group's rays into shared memory with cp.async while the current group is walked, and
+// taking the next fetch index one group early. 3.93 vs 3.81 ms at C3 with the carve-out adjusted: the other 23 warps of the SM already
+// cover those waits, the copies and the extra warp synchronisations only add instructions. profiles/r02_notes.md)
 // Persistent warps; each takes HF_FAST_GROUPS consecutive 32-ray groups at a time off one global counter: hit and miss regions of a
 // ray batch differ ~8x in cost per ray, and a static deal of tiles left the SMs idle 7 % of the kernel (profiles/r01_notes.md).
 template <int MODE>
@@ -844,10 +854,11 @@ cudaError_t hf_launch_intersect(const HfParams &P, const HfLaunchInfo &li, int m
     const size_t smem = hf_walk_smem(li, false);
     if (!carved) {
         carved = true;
-        hf_prefer_l1(hf_intersect_fast_kernel<HF_MODE_PRELIM>, smem + 1024, HF_MIN_CTAS);
-        hf_prefer_l1(hf_intersect_fast_kernel<HF_MODE_FUSED_SI>, smem + 1024, HF_MIN_CTAS);
-        hf_prefer_l1(hf_intersect_fast_kernel<HF_MODE_FUSED_SI_LEAN>, smem + 1024, HF_MIN_CTAS);
-        hf_prefer_l1(hf_intersect_fast_kernel<HF_MODE_TEST>, smem + 1024, HF_MIN_CTAS);
+        const size_t stat = 1024;                   // static shared memory of the kernel (level tables, barrier)
+        hf_prefer_l1(hf_intersect_fast_kernel<HF_MODE_PRELIM>, smem + stat, HF_MIN_CTAS);
+        hf_prefer_l1(hf_intersect_fast_kernel<HF_MODE_FUSED_SI>, smem + stat, HF_MIN_CTAS);
+        hf_prefer_l1(hf_intersect_fast_kernel<HF_MODE_FUSED_SI_LEAN>, smem + stat, HF_MIN_CTAS);
+        hf_prefer_l1(hf_intersect_fast_kernel<HF_MODE_TEST>, smem + stat, HF_MIN_CTAS);
     }
     {
         const size_t ngroups = (n + 31) / 32;
