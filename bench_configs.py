@@ -321,6 +321,7 @@ def run_c5(a, sampler_cls):
         h = wl.fbm_heights(hs, octaves=8, seed=0xC5, device=dev)
         shape = hfb200.load_dict({"type": "heightfield", "heights": h, "max_height": 0.3}, device=dev)
         del h
+        shape.set_ray_coherence(os.environ.get("HF_C5_COHERENT", "0") == "1")      # hemisphere rays: unrelated -> the lane-pool kernel
         if world > 1:
             ids = [None] * world
             dist.all_gather_object(ids, hfb200.comm_unique_id() if rank == 0 else None)
@@ -393,10 +394,11 @@ def run_c5(a, sampler_cls):
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": "C5: ray-count sweep " + "/".join(f"2^{int(np.log2(n))}" for n in counts) + " rays x heightfield sizes " + "/".join(map(str, sizes)) +
                                    " (fBm seed 0xC5), intersect-only and fwd+bwd, hemisphere origins (radius 3, seed 5)",
+                       "ray_coherence_hint": "coherent (lock-step kernel)" if os.environ.get("HF_C5_COHERENT", "0") == "1" else "incoherent (hf_set_ray_coherence(0): lane-pool kernel)",
                        "chunk": chunk, "sharding": "chunks of <= 2^26 rays dealt round-robin; gradient grids summed by one allreduce per cell",
                        "l2": "every chunk's ray / result / adjoint SoA (>= 180 MB at 2^20 rays) exceeds L2 from 2^22 rays on; the 2^20 cells fit and say so by their rates"},
             "clocks": clocks, "gpu_launches": sum(3 * c["chunks"] for c in cells),
-            "roofline": {"bound": "hbm", "kernel": "hf_intersect_fast_kernel<FUSED_SI> + hf_backward_kernel (whole fwd+bwd cell)", "achieved": head[0]["fwd_bwd_frac"] * peak, "peak": peak,
+            "roofline": {"bound": "hbm", "kernel": "hf_intersect_pool_kernel<FUSED_SI> + hf_backward_kernel (whole fwd+bwd cell)", "achieved": head[0]["fwd_bwd_frac"] * peak, "peak": peak,
                          "unit": "GB/s", "frac": head[0]["fwd_bwd_frac"], "peak_source": peak_src, "traffic": None,
                          "model": "rays x (76 B fwd I/O + 8 B x nodes + 16 B x leaves [canonical traversal counted on 2^20 rays of the size] + 108 B per hit / 4 B per miss of the backward pass); "
                                   f"headline cell: {head[0]['heights']}^2 x {head[0]['rays']} rays"},

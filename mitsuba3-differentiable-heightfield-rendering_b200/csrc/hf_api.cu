@@ -273,6 +273,7 @@ static void layout_pyramid(hf_ctx *c) {
         // bundles analytically, always marches them.
         const char *e = getenv("HF_B200_BUNDLES");
         c->li.use_bundles = (e && e[0] == '1') ? 1 : 0;
+        c->li.incoherent = 0;
     }
 }
 
@@ -421,6 +422,12 @@ extern "C" int hf_parameters_changed(hf_ctx *c, void *stream) {
         if (c->accel_event_ok) CU(cudaEventRecord(c->ev_accel, (cudaStream_t) stream));
     }
     c->accel_valid = true;
+    return HF_OK;
+}
+
+extern "C" int hf_set_ray_coherence(hf_ctx *c, int coherent) {
+    CHECK_CTX(c);
+    c->li.incoherent = coherent ? 0 : 1;
     return HF_OK;
 }
 

@@ -552,29 +552,12 @@ hf_intersect_kernel(const __grid_constant__ HfParams P, const HfLaunchInfo li, c
 // ------------------------------------------------------------------------------------------
 // One ray through the production walk: load, transform, walk + per-cell primitive, store (+ fused surface interaction).
 // t_start / L_start come from the bundle march (hf_beam_enter) or are 0 / HF_START_LEVEL.
+// The result of one ray: preliminary record and (fused modes) the surface interaction of the hit triangle, whose vertices come from
+// the candidate cell `c` the walk left in registers.
 template <int MODE>
-__device__ __forceinline__ void hf_process_loaded(const HfParams &P, const HfGrid &G, const hf_rays &R, const hf_prelim &O,
-                                                  const hf_si &S, uint8_t *__restrict__ hit_out, const uint32_t flags,
-                                                  const size_t i, const f3 ow, const f3 dw, const float maxt, const float t_start, const int L_start) {
-    const bool active = R.active ? (R.active[i] != 0) : true;
-
-    bool hit = false;
-    HfCand c;
-    float ht = HF_INF, hu = 0.f, hv = 0.f;
-    uint32_t hprim = 0u;
-    if (active) {
-        // Transform::transform_affine(ray), src/shapes/rectangle.cpp:206-214: t is preserved
-        const f3 o = xform_point(P.to_object, ow), d = xform_vector(P.to_object, dw);
-        HfWalk w;
-        if (hf_walk_init(G, o.x, o.y, o.z, d.x, d.y, d.z, maxt, w, t_start, L_start)) {
-            // lanes leave hf_walk_next at different iterations and reconverge here, so the per-cell primitive
-            // runs for all candidate lanes of the warp together
-            while (hf_walk_next(G, w, c)) {
-                if (cell_intersect(P, c.cx, c.cy, c.z00, c.z10, c.z01, c.z11, o, d, maxt, ht, hu, hv, hprim)) { hit = true; break; }
-            }
-        }
-    }
-
+__device__ __forceinline__ void hf_store_result(const HfParams &P, const hf_rays &R, const hf_prelim &O, const hf_si &S, uint8_t *__restrict__ hit_out,
+                                                const uint32_t flags, const size_t i, const bool hit, const float ht, const float hu, const float hv,
+                                                const uint32_t hprim, const HfCand &c) {
     if (MODE == HF_MODE_TEST) {
         hit_out[i] = hit ? 1 : 0;
         return;
@@ -614,6 +597,32 @@ __device__ __forceinline__ void hf_process_loaded(const HfParams &P, const HfGri
             write_si_invalid(S, i, dw2);
         }
     }
+}
+
+template <int MODE>
+__device__ __forceinline__ void hf_process_loaded(const HfParams &P, const HfGrid &G, const hf_rays &R, const hf_prelim &O,
+                                                  const hf_si &S, uint8_t *__restrict__ hit_out, const uint32_t flags,
+                                                  const size_t i, const f3 ow, const f3 dw, const float maxt, const float t_start, const int L_start) {
+    const bool active = R.active ? (R.active[i] != 0) : true;
+
+    bool hit = false;
+    HfCand c;
+    float ht = HF_INF, hu = 0.f, hv = 0.f;
+    uint32_t hprim = 0u;
+    if (active) {
+        // Transform::transform_affine(ray), src/shapes/rectangle.cpp:206-214: t is preserved
+        const f3 o = xform_point(P.to_object, ow), d = xform_vector(P.to_object, dw);
+        HfWalk w;
+        if (hf_walk_init(G, o.x, o.y, o.z, d.x, d.y, d.z, maxt, w, t_start, L_start)) {
+            // lanes leave hf_walk_next at different iterations and reconverge here, so the per-cell primitive
+            // runs for all candidate lanes of the warp together
+            while (hf_walk_next(G, w, c)) {
+                if (cell_intersect(P, c.cx, c.cy, c.z00, c.z10, c.z01, c.z11, o, d, maxt, ht, hu, hv, hprim)) { hit = true; break; }
+            }
+        }
+    }
+
+    hf_store_result<MODE>(P, R, O, S, hit_out, flags, i, hit, ht, hu, hv, hprim, c);
 }
 
 template <int MODE>
@@ -692,6 +701,160 @@ hf_intersect_fast_kernel(const __grid_constant__ HfParams P, const HfLaunchInfo 
             __syncwarp();
         }
     }
+}
+
+// ------------------------------------------------------------------------------------------
+// Lane-pool intersection kernel for INCOHERENT ray batches (hf_set_ray_coherence(ctx, 0); the reference's Scene::ray_intersect takes
+// the same hint as its `coherent` argument, src/render/scene.cpp:141-150).
+//
+// In the kernel above a warp takes 32 consecutive rays and walks them in lock step until the last one is finished: fine for the
+// samples of one pixel, wasteful when the 32 rays have nothing to do with each other (C5: origins on a hemisphere) -- a warp then
+// needs 51 lock-step iterations for rays that need 17 each (tools/sim_pool.py). Here every LANE owns its own ray and takes the next
+// ray of the warp's pool as soon as its own is finished ("persistent while-while"):
+//   refill   idle lanes take consecutive rays of the pool (coalesced loads), transform them and set up their walks;
+//   walk     up to HF_POOL_ROUND iterations of hf_walk_iter for the lanes that are searching (a cap: lanes that hold a candidate must
+//            not wait for the slowest searcher);
+//   test     the per-cell primitive for the lanes that hold a candidate;
+//   retire   finished rays drop a 13-word record (ray id, hit, cell) into a per-warp shared-memory queue and the lane is idle again;
+//            when 32 records are queued the WHOLE warp turns them into surface interactions and stores them, one record per lane --
+//            so the expensive output code runs at 32 lanes, not at the two or three that happen to finish together.
+// Results are bit-identical to the kernel above (same walk, same primitive, same surface-interaction code). Measured (profiles/r02_notes.md):
+// the instruction model promised -38 %; on a B200 the kernel is 5-18 % faster than the lock-step kernel for intersect-only hemisphere rays
+// and about equal with the fused surface interaction -- large fields make incoherent rays latency-bound, and this kernel's per-lane state
+// costs the registers that resident warps would need.
+// ------------------------------------------------------------------------------------------
+#ifndef HF_POOL_ROUND
+#define HF_POOL_ROUND 8
+#endif
+#ifndef HF_POOL_RAYS
+#define HF_POOL_RAYS 256           // rays a warp takes off the global counter at a time
+#endif
+#ifndef HF_POOL_REFILL
+#define HF_POOL_REFILL 8           // refill as soon as this many lanes are idle (or nobody is working)
+#endif
+#define HF_POOL_REC 13             // words per queued result: ray id (2), hit, t, u, v, prim_index, cell (2), its four corner heights
+
+#ifndef HF_POOL_MIN_CTAS
+#define HF_POOL_MIN_CTAS 4         // 64 registers (192 bytes of spills): incoherent batches on large fields are latency-bound, resident warps beat
+#endif                             // registers -- C5, 2^24 rays, intersect-only Grays/s at 512^2 / 4096^2 / 16384^2: 2 CTAs 5.8 / 3.1 / 2.2, 3: 7.1 / 4.1 / 2.9,
+                                   // 4: 7.5 / 4.6 / 3.3, 5: 6.5 / 3.9 / 2.8, 6: 5.4 / 3.2 / 2.3; the lock-step kernel: 6.3 / 4.4 / 3.1
+template <int MODE>
+__global__ void __launch_bounds__(HF_BLOCK, HF_POOL_MIN_CTAS)
+hf_intersect_pool_kernel(const __grid_constant__ HfParams P, const HfLaunchInfo li, const hf_rays R, const hf_prelim O,
+                         const hf_si S, uint8_t *__restrict__ hit_out, const uint32_t flags, const size_t n,
+                         unsigned long long *__restrict__ sched) {
+    HfGrid G;
+    hf_stage_pyramid<false>(P, li, G);
+    __shared__ uint32_t s_rec[HF_BLOCK / 32][HF_POOL_REC][32];
+    const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    const unsigned lt = (1u << lane) - 1u;
+    uint32_t (*rec)[32] = s_rec[warp];
+
+    // per-lane state
+    bool busy = false, have_cand = false, done = false, hit = false;
+    size_t ri = 0;
+    f3 o = mk3(0.f, 0.f, 0.f), d = o;
+    float maxt = 0.f, ht = HF_INF, hu = 0.f, hv = 0.f;
+    uint32_t hprim = 0u;
+    HfWalk w;
+    w.alive = false;
+    HfCand c;
+    c.cx = c.cy = 0; c.z00 = c.z10 = c.z01 = c.z11 = 0.f;
+    // per-warp state (uniform)
+    size_t pnext = 0, pend = 0;
+    bool more = true;
+    unsigned queued = 0;
+
+    auto flush = [&]() {                                    // the whole warp: one queued record per lane -> results in memory
+        __syncwarp();
+        if (lane < queued) {
+            const size_t i = ((size_t) rec[1][lane] << 32) | rec[0][lane];
+            const bool h = rec[2][lane] != 0u;
+            HfCand cc;
+            cc.cx = (int) rec[7][lane]; cc.cy = (int) rec[8][lane];
+            cc.z00 = __uint_as_float(rec[9][lane]); cc.z10 = __uint_as_float(rec[10][lane]);
+            cc.z01 = __uint_as_float(rec[11][lane]); cc.z11 = __uint_as_float(rec[12][lane]);
+            hf_store_result<MODE>(P, R, O, S, hit_out, flags, i, h, __uint_as_float(rec[3][lane]), __uint_as_float(rec[4][lane]),
+                                  __uint_as_float(rec[5][lane]), rec[6][lane], cc);
+        }
+        __syncwarp();
+        queued = 0;
+    };
+
+    for (;;) {
+        // ---- refill
+        const unsigned idle = __ballot_sync(FULL_MASK, !busy);
+        const unsigned working = __ballot_sync(FULL_MASK, busy && !done);
+        if (idle && more && ((unsigned) __popc(idle) >= HF_POOL_REFILL || working == 0u)) {
+            if (pnext >= pend) {
+                unsigned long long t = 0;
+                if (lane == 0) t = atomicAdd(sched, 1ull);
+                t = __shfl_sync(FULL_MASK, t, 0);
+                pnext = (size_t) t * HF_POOL_RAYS;
+                pend = pnext + HF_POOL_RAYS < n ? pnext + HF_POOL_RAYS : n;
+                if (pnext >= n) { more = false; pnext = pend = 0; }
+            }
+            if (more) {
+                const size_t mine = pnext + __popc(idle & lt);
+                if (!busy && mine < pend) {
+                    ri = mine; busy = true; have_cand = false; done = false; hit = false;
+                    ht = HF_INF; hu = 0.f; hv = 0.f; hprim = 0u;
+                    const f3 ow = mk3(__ldcs(R.ox + ri), __ldcs(R.oy + ri), __ldcs(R.oz + ri));
+                    const f3 dw = mk3(__ldcs(R.dx + ri), __ldcs(R.dy + ri), __ldcs(R.dz + ri));
+                    maxt = __ldcs(R.maxt + ri);
+                    const bool active = R.active ? (R.active[ri] != 0) : true;
+                    o = xform_point(P.to_object, ow); d = xform_vector(P.to_object, dw);     // transform_affine: t is preserved
+                    w.alive = false;
+                    if (!active || !hf_walk_init(G, o.x, o.y, o.z, d.x, d.y, d.z, maxt, w)) done = true;
+                }
+                const size_t adv = pnext + __popc(idle);
+                pnext = adv < pend ? adv : pend;
+            }
+        }
+        if (!more && __ballot_sync(FULL_MASK, busy) == 0u) break;
+
+        // ---- walk: at most HF_POOL_ROUND lock-step iterations, searching lanes only
+        #pragma unroll 1
+        for (int it = 0; it < HF_POOL_ROUND; ++it) {
+            const bool search = busy && !done && !have_cand;
+            if (!__any_sync(FULL_MASK, search)) break;
+            if (search) {
+                if (!w.alive) done = true;
+                else {
+                    const int st = hf_walk_iter(G, w, c);
+                    if (st == 1) have_cand = true;
+                    else if (st == 2) done = true;
+                }
+            }
+        }
+        // ---- per-cell primitive for the lanes that hold a candidate
+        if (__any_sync(FULL_MASK, have_cand)) {
+            if (have_cand) {
+                have_cand = false;
+                if (cell_intersect(P, c.cx, c.cy, c.z00, c.z10, c.z01, c.z11, o, d, maxt, ht, hu, hv, hprim)) { hit = true; done = true; }
+                else if (!w.alive) done = true;
+            }
+        }
+        // ---- retire: finished rays queue their record; a full queue is turned into results by the whole warp
+        for (;;) {
+            const unsigned fin = __ballot_sync(FULL_MASK, busy && done);
+            if (fin == 0u) break;
+            const unsigned slot = queued + __popc(fin & lt);
+            if (busy && done && slot < 32u) {
+                rec[0][slot] = (uint32_t) ri; rec[1][slot] = (uint32_t) ((unsigned long long) ri >> 32);
+                rec[2][slot] = hit ? 1u : 0u;
+                rec[3][slot] = __float_as_uint(ht); rec[4][slot] = __float_as_uint(hu); rec[5][slot] = __float_as_uint(hv); rec[6][slot] = hprim;
+                rec[7][slot] = (uint32_t) c.cx; rec[8][slot] = (uint32_t) c.cy;
+                rec[9][slot] = __float_as_uint(c.z00); rec[10][slot] = __float_as_uint(c.z10); rec[11][slot] = __float_as_uint(c.z01);
+                rec[12][slot] = __float_as_uint(c.z11);
+                busy = false; done = false;
+            }
+            const unsigned total = queued + __popc(fin);
+            queued = total < 32u ? total : 32u;
+            if (queued == 32u) flush();
+        }
+    }
+    if (queued) flush();
 }
 
 // ------------------------------------------------------------------------------------------
@@ -845,6 +1008,25 @@ cudaError_t hf_launch_intersect(const HfParams &P, const HfLaunchInfo &li, int m
             hf_intersect_beam_kernel<HF_MODE_FUSED_SI_LEAN><<<bgrid, HF_BLOCK, smem, s>>>(P, li, rays, prelim, si, d_hit, flags, n, nbig, sched);
         else
             hf_intersect_beam_kernel<HF_MODE_FUSED_SI><<<bgrid, HF_BLOCK, smem, s>>>(P, li, rays, prelim, si, d_hit, flags, n, nbig, sched);
+        return cudaGetLastError();
+    }
+    if (li.incoherent) {
+        // every lane on its own ray (hf_intersect_pool_kernel): 2 CTAs per SM, pools of HF_POOL_RAYS rays off the global counter
+        const size_t smem = hf_walk_smem(li, false);
+        const size_t npools = (n + HF_POOL_RAYS - 1) / HF_POOL_RAYS, nct = (npools + HF_BLOCK / 32 - 1) / (HF_BLOCK / 32), cap = (size_t) li.num_sms * HF_POOL_MIN_CTAS;
+        const int pgrid = (int) (nct < cap ? nct : cap);
+        cudaError_t e = cudaMemsetAsync(d_sched, 0, sizeof(unsigned long long), s);
+        if (e != cudaSuccess) return e;
+        switch (mode) {
+            case HF_MODE_PRELIM:
+                hf_intersect_pool_kernel<HF_MODE_PRELIM><<<pgrid, HF_BLOCK, smem, s>>>(P, li, rays, prelim, si, d_hit, flags, n, d_sched); break;
+            case HF_MODE_FUSED_SI_LEAN:
+                hf_intersect_pool_kernel<HF_MODE_FUSED_SI_LEAN><<<pgrid, HF_BLOCK, smem, s>>>(P, li, rays, prelim, si, d_hit, flags, n, d_sched); break;
+            case HF_MODE_FUSED_SI:
+                hf_intersect_pool_kernel<HF_MODE_FUSED_SI><<<pgrid, HF_BLOCK, smem, s>>>(P, li, rays, prelim, si, d_hit, flags, n, d_sched); break;
+            default:
+                hf_intersect_pool_kernel<HF_MODE_TEST><<<pgrid, HF_BLOCK, smem, s>>>(P, li, rays, prelim, si, d_hit, flags, n, d_sched); break;
+        }
         return cudaGetLastError();
     }
     static bool carved_dev[64] = { false };     // function attributes are per device: one process may drive several GPUs

@@ -13,6 +13,7 @@ struct HfLaunchInfo {
     int top_nodes;           // node count of levels Ls..Ltop (padded to even)
     int top_off;             // node offset of level Ls
     int use_bundles;         // 1: bundled kernel (hf_intersect_beam_kernel), 0: plain per-ray kernel
+    int incoherent;          // 1: the batch's rays are unrelated (hf_set_ray_coherence): lane-pool kernel (hf_intersect_pool_kernel)
     // quantised pyramid: the coarse EVEN levels >= q_stage_level (the levels every walk starts from) are staged in shared memory
     int q_stage_level;       // lowest staged level (even), > QLtop: nothing staged
     int q_stage_bytes;       // shared memory they take (each level padded to 16 bytes)

@@ -290,6 +290,107 @@ HF_HD float hf_bits_float(uint32_t b) {
 #endif
 }
 
+// ONE iteration of the walk (the loop body of hf_walk_next): 0 = keep going, 1 = a leaf cell overlaps the ray's z interval (cell and
+// texels in `c`; the state has already moved past that cell, so a failed primitive test simply continues), 2 = the ray is finished.
+// Kernels that keep every lane of a warp on its own ray (hf_intersect_pool_kernel) call this directly.
+HF_HD int hf_walk_iter(const HfGrid &G, HfWalk &w, HfCand &c) {
+    const uint32_t sel_hi = w.sel_lo ^ 0x0022u;
+    const int L = w.L, ix = w.ix, iy = w.iy;
+    const int mask = (1 << L) - 1;
+    const int hx = ix | mask, hy = iy | mask;                 // last cell of this node on each axis
+    const int bx = hx + 1, by = hy + 1;                       // exit planes of this node
+    // (NOT fma(float(b), id, -og * id): for a nearly axis-parallel ray id is huge and the two products cancel catastrophically;
+    // the subtraction below is exact next to the ray -- tests/test_traversal_host.py::test_walk_under_an_affine_transform)
+    const float tx = fmaf(((float) bx - w.ogx) - w.ogxl, w.idx, w.infx); // the fma only adds +0 or +inf
+    const float ty = fmaf(((float) by - w.ogy) - w.ogyl, w.idy, w.infy);
+    const float tmin = fminf(tx, ty);
+    const bool last = !(tmin < w.t1);
+    const float te = fminf(tmin, w.t1);
+    // z' never increases along the ray: its padded range over [t, te] is [z'(te) - eps, z'(t) + eps]
+    const float zhi = fmaf(w.t, w.dz, w.ozp), zlo = fmaf(te, w.dz, w.ozm);
+
+#ifdef HF_DEBUG_BOUNDS
+    // checked build (make VARIANT=_bounds EXTRA=-DHF_DEBUG_BOUNDS; tests/trav_host.cpp defines it too): every node and texel
+    // index the walk forms is tested against the layout before it is used (compute-sanitizer is not available on the GPU pool)
+    if (L < 0 || L > G.QLtop || ((ix ^ w.xm) >> L) < 0 || ((ix ^ w.xm) >> L) > (G.xmask >> L) ||
+        ((iy ^ w.ym) >> L) < 0 || ((iy ^ w.ym) >> L) > (G.ymask >> L)) HF_BOUNDS_FAIL();
+#endif
+    uint32_t q;
+    {
+#ifdef __CUDACC__
+        uint32_t p0, p1, pitch, pad_ = 0u;
+        asm("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(p0), "=r"(p1), "=r"(pitch), "=r"(pad_) : "r"(G.qlvl_saddr + (uint32_t) L * 16u));
+        (void) pad_;
+        const uint32_t *nodes = reinterpret_cast<const uint32_t *>(((unsigned long long) p1 << 32) | (unsigned long long) p0);
+#if HF_STAGE_Q
+        q = nodes[(unsigned) (((iy ^ w.ym) >> L) * (int) pitch + ((ix ^ w.xm) >> L))];       // generic: shared (staged coarse levels) or global
+#else
+        q = HF_LDG(nodes + (unsigned) (((iy ^ w.ym) >> L) * (int) pitch + ((ix ^ w.xm) >> L)));
+#endif
+#else
+        const HfQLevel lv = G.qlvl[L];
+        q = lv.nodes[(unsigned) (((iy ^ w.ym) >> L) * lv.pitch + ((ix ^ w.xm) >> L))];
+#endif
+    }
+#if HF_CODE_SPACE
+    const float mn = hf_bits_float(hf_prmt(q, w.kmagic, w.sel_lo));     // +-(M + code): no conversion, no decode
+    const float mx = hf_bits_float(hf_prmt(q, w.kmagic, sel_hi));
+#else
+    const float mn = fmaf((float) hf_prmt(q, 0u, w.sel_lo), w.qsf, w.zbf);
+    const float mx = fmaf((float) hf_prmt(q, 0u, sel_hi), w.qsf, w.zbf);
+#endif
+    const bool overlap = (zlo <= mx) && (zhi >= mn);
+    const bool desc = overlap && (L > 0);
+    const bool found = overlap && (L == 0);
+
+    // Descending lanes first clip their entry point to the node's z slab: before the ray crosses mx + eps it
+    // cannot touch anything inside this node, so the children in front of that point are skipped.
+    float ts = (mx - w.ozm) * w.idz;
+    ts = fmaf(-fabsf(ts), HF_TRAV_SLACK, ts);                         // never later than the true crossing
+    const float tc = fminf(fmaxf(w.t, ts), te);
+    // tq: the parameter the next cell is derived from -- the clipped entry (descend) or the node's exit (step)
+    const float tq = desc ? tc : te;
+    const int qx = hf_floor_sat(fmaf(tq, w.dgx, w.ogxb)), qy = hf_floor_sat(fmaf(tq, w.dgy, w.ogyb));
+    // position at tq, kept inside the node and monotone along the ray
+    const int rx = hf_imin(hf_imax(qx, ix), hx), ry = hf_imin(hf_imax(qy, iy), hy);
+    // a step leaves the node through the plane(s) reached first; a descent stays inside
+    const bool stepx = !desc && (tx <= ty), stepy = !desc && (ty <= tx);
+    const int nix = stepx ? bx : rx, niy = stepy ? by : ry;
+    const bool outside = (nix > w.xlim) || (niy > w.ylim);            // never enters a padding cell (their nodes hold HF_Q_EMPTY)
+    const unsigned m = (unsigned) ((nix ^ ix) | (niy ^ iy));
+#if HF_EVEN_LEVELS
+    const bool up = m > (unsigned) (4 * mask + 3);                    // left the grandparent node: go up two levels
+#else
+    const bool up = m > (unsigned) (2 * mask + 1);                    // left the parent node: go up one level
+#endif
+
+#if !defined(__CUDACC__) && defined(HF_WALK_HIST)
+    { extern unsigned long long hf_walk_hist[3][32];
+      _Pragma("omp atomic") hf_walk_hist[desc ? 0 : (found ? 2 : 1)][L]++; }
+#endif
+#if HF_EVEN_LEVELS
+    w.L = desc ? L - 2 : (up ? L + 2 : L);                            // levels stay even: a 4 x 4-ary walk
+#else
+    w.L = desc ? hf_imax(L - HF_DESC_LEVELS, 0) : (up ? L + 1 : L);
+#endif
+    w.ix = nix;
+    w.iy = niy;
+    w.t = tq;
+    w.alive = desc ? true : !(last || outside);
+    if (found) {
+        const int cx = ix ^ w.xm, cy = iy ^ w.ym;                     // always a real cell: see `outside`
+#ifdef HF_DEBUG_BOUNDS
+        if (cx < 0 || cx >= G.NX || cy < 0 || cy >= G.NY) HF_BOUNDS_FAIL();
+#endif
+        const float *row0 = G.heights + (unsigned) (cy * G.W + cx);   // W*H < 2^32 (checked by hf_create)
+        c.z00 = G.mh * HF_LDG(row0); c.z10 = G.mh * HF_LDG(row0 + 1);
+        c.z01 = G.mh * HF_LDG(row0 + G.W); c.z11 = G.mh * HF_LDG(row0 + G.W + 1);
+        c.cx = cx; c.cy = cy;
+        return 1;
+    }
+    return w.alive ? 0 : 2;
+}
+
 // Advance the walk until a leaf cell overlaps the ray's z interval (returns true, cell in `c`, and the state is
 // already moved past that cell so that a failed primitive test simply calls again) or the ray is finished (false).
 // `iters` (host statistics only) counts loop iterations.
@@ -299,105 +400,13 @@ HF_HD bool hf_walk_next(const HfGrid &G, HfWalk &w, HfCand &c
 #endif
 ) {
     if (!w.alive) return false;
-    const uint32_t sel_hi = w.sel_lo ^ 0x0022u;
     for (;;) {
 #ifndef __CUDACC__
         if (iters) ++*iters;
 #endif
-        const int L = w.L, ix = w.ix, iy = w.iy;
-        const int mask = (1 << L) - 1;
-        const int hx = ix | mask, hy = iy | mask;                 // last cell of this node on each axis
-        const int bx = hx + 1, by = hy + 1;                       // exit planes of this node
-        // (NOT fma(float(b), id, -og * id): for a nearly axis-parallel ray id is huge and the two products cancel catastrophically;
-        // the subtraction below is exact next to the ray -- tests/test_traversal_host.py::test_walk_under_an_affine_transform)
-        const float tx = fmaf(((float) bx - w.ogx) - w.ogxl, w.idx, w.infx); // the fma only adds +0 or +inf
-        const float ty = fmaf(((float) by - w.ogy) - w.ogyl, w.idy, w.infy);
-        const float tmin = fminf(tx, ty);
-        const bool last = !(tmin < w.t1);
-        const float te = fminf(tmin, w.t1);
-        // z' never increases along the ray: its padded range over [t, te] is [z'(te) - eps, z'(t) + eps]
-        const float zhi = fmaf(w.t, w.dz, w.ozp), zlo = fmaf(te, w.dz, w.ozm);
-
-#ifdef HF_DEBUG_BOUNDS
-        // checked build (make VARIANT=_bounds EXTRA=-DHF_DEBUG_BOUNDS; tests/trav_host.cpp defines it too): every node and texel
-        // index the walk forms is tested against the layout before it is used (compute-sanitizer is not available on the GPU pool)
-        if (L < 0 || L > G.QLtop || ((ix ^ w.xm) >> L) < 0 || ((ix ^ w.xm) >> L) > (G.xmask >> L) ||
-            ((iy ^ w.ym) >> L) < 0 || ((iy ^ w.ym) >> L) > (G.ymask >> L)) HF_BOUNDS_FAIL();
-#endif
-        uint32_t q;
-        {
-#ifdef __CUDACC__
-            uint32_t p0, p1, pitch, pad_ = 0u;
-            asm("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(p0), "=r"(p1), "=r"(pitch), "=r"(pad_) : "r"(G.qlvl_saddr + (uint32_t) L * 16u));
-            (void) pad_;
-            const uint32_t *nodes = reinterpret_cast<const uint32_t *>(((unsigned long long) p1 << 32) | (unsigned long long) p0);
-#if HF_STAGE_Q
-            q = nodes[(unsigned) (((iy ^ w.ym) >> L) * (int) pitch + ((ix ^ w.xm) >> L))];       // generic: shared (staged coarse levels) or global
-#else
-            q = HF_LDG(nodes + (unsigned) (((iy ^ w.ym) >> L) * (int) pitch + ((ix ^ w.xm) >> L)));
-#endif
-#else
-            const HfQLevel lv = G.qlvl[L];
-            q = lv.nodes[(unsigned) (((iy ^ w.ym) >> L) * lv.pitch + ((ix ^ w.xm) >> L))];
-#endif
-        }
-#if HF_CODE_SPACE
-        const float mn = hf_bits_float(hf_prmt(q, w.kmagic, w.sel_lo));     // +-(M + code): no conversion, no decode
-        const float mx = hf_bits_float(hf_prmt(q, w.kmagic, sel_hi));
-#else
-        const float mn = fmaf((float) hf_prmt(q, 0u, w.sel_lo), w.qsf, w.zbf);
-        const float mx = fmaf((float) hf_prmt(q, 0u, sel_hi), w.qsf, w.zbf);
-#endif
-        const bool overlap = (zlo <= mx) && (zhi >= mn);
-        const bool desc = overlap && (L > 0);
-        const bool found = overlap && (L == 0);
-
-        // Descending lanes first clip their entry point to the node's z slab: before the ray crosses mx + eps it
-        // cannot touch anything inside this node, so the children in front of that point are skipped.
-        float ts = (mx - w.ozm) * w.idz;
-        ts = fmaf(-fabsf(ts), HF_TRAV_SLACK, ts);                         // never later than the true crossing
-        const float tc = fminf(fmaxf(w.t, ts), te);
-        // tq: the parameter the next cell is derived from -- the clipped entry (descend) or the node's exit (step)
-        const float tq = desc ? tc : te;
-        const int qx = hf_floor_sat(fmaf(tq, w.dgx, w.ogxb)), qy = hf_floor_sat(fmaf(tq, w.dgy, w.ogyb));
-        // position at tq, kept inside the node and monotone along the ray
-        const int rx = hf_imin(hf_imax(qx, ix), hx), ry = hf_imin(hf_imax(qy, iy), hy);
-        // a step leaves the node through the plane(s) reached first; a descent stays inside
-        const bool stepx = !desc && (tx <= ty), stepy = !desc && (ty <= tx);
-        const int nix = stepx ? bx : rx, niy = stepy ? by : ry;
-        const bool outside = (nix > w.xlim) || (niy > w.ylim);            // never enters a padding cell (their nodes hold HF_Q_EMPTY)
-        const unsigned m = (unsigned) ((nix ^ ix) | (niy ^ iy));
-#if HF_EVEN_LEVELS
-        const bool up = m > (unsigned) (4 * mask + 3);                    // left the grandparent node: go up two levels
-#else
-        const bool up = m > (unsigned) (2 * mask + 1);                    // left the parent node: go up one level
-#endif
-
-#if !defined(__CUDACC__) && defined(HF_WALK_HIST)
-        { extern unsigned long long hf_walk_hist[3][32];
-          _Pragma("omp atomic") hf_walk_hist[desc ? 0 : (found ? 2 : 1)][L]++; }
-#endif
-#if HF_EVEN_LEVELS
-        w.L = desc ? L - 2 : (up ? L + 2 : L);                            // levels stay even: a 4 x 4-ary walk
-#else
-        w.L = desc ? hf_imax(L - HF_DESC_LEVELS, 0) : (up ? L + 1 : L);
-#endif
-        w.ix = nix;
-        w.iy = niy;
-        w.t = tq;
-        w.alive = desc ? true : !(last || outside);
-        if (found) {
-            const int cx = ix ^ w.xm, cy = iy ^ w.ym;                     // always a real cell: see `outside`
-#ifdef HF_DEBUG_BOUNDS
-            if (cx < 0 || cx >= G.NX || cy < 0 || cy >= G.NY) HF_BOUNDS_FAIL();
-#endif
-            const float *row0 = G.heights + (unsigned) (cy * G.W + cx);   // W*H < 2^32 (checked by hf_create)
-            c.z00 = G.mh * HF_LDG(row0); c.z10 = G.mh * HF_LDG(row0 + 1);
-            c.z01 = G.mh * HF_LDG(row0 + G.W); c.z11 = G.mh * HF_LDG(row0 + G.W + 1);
-            c.cx = cx; c.cy = cy;
-            return true;
-        }
-        if (!w.alive) return false;
+        const int st = hf_walk_iter(G, w, c);
+        if (st == 1) return true;
+        if (st == 2) return false;
     }
 }
 

@@ -585,3 +585,54 @@ def test_bundled_kernel_bit_identical(hf, oracle, monkeypatch):
             pc = bund.ray_intersect_preliminary(ray, active=act)
             assert torch.equal(pa.t.view(torch.int32), pc.t.view(torch.int32))
         assert 0.3 < float(pa.is_valid().float().mean()) < 1.0
+
+
+# ---- lane-pool kernel for incoherent batches (hf_set_ray_coherence(0)): identical answers to the lock-step kernel and the oracle ----
+@pytest.mark.parametrize("H,W,xf,n", [(64, 65, None, 100003), (200, 150, "affine", 70001), (5, 7, None, 33), (1024, 1024, None, 1 << 20)])
+def test_pool_kernel_bit_identical(hf, oracle, H, W, xf, n):
+    """Every lane of a warp on its own ray, refilled from a pool, results queued in shared memory and written by the whole warp: the
+    same bits as the 32-rays-in-lock-step kernel for the preliminary record, every surface-interaction field and ray_test -- on random
+    incoherent rays, ragged sizes (pools, queues and the tail), an active mask, finite maxt and a transformed shape."""
+    from hfb200 import workloads as wl
+    rng = np.random.default_rng(H * 7 + W + n)
+    h = random_heights(rng, H, W, "smooth") if H < 1000 else wl.fbm_heights(H, octaves=8, seed=0xC5).numpy()
+    tw = AFFINE if xf else None
+    g, c = _mk(hf, oracle, h, 0.4, to_world=tw)
+    if H < 1000:
+        o, d = random_rays(rng, n)
+        ao, ad = adversarial_rays(W, H, 0.4)
+        o, d = np.concatenate([o, ao]), np.concatenate([d, ad])
+    else:
+        ot, dt = wl.hemisphere_rays(n, seed=5)
+        o, d = ot.numpy().T.copy(), dt.numpy().T.copy()
+    if tw is not None:
+        o = (o @ tw[:, :3].T + tw[:, 3]).astype(f32); d = (d @ tw[:, :3].T).astype(f32)
+    m = o.shape[0]
+    maxt = np.where(rng.uniform(size=m) < 0.15, rng.uniform(0.5, 4, m), np.inf).astype(f32)
+    active = rng.uniform(size=m) < 0.9
+    ray, cr = _rays(hf, oracle, o, d, maxt, active)
+    act_t = torch.from_numpy(active)
+    want_si, want_pi = g.ray_intersect(ray, active=act_t, return_prelim=True)
+    want_hit = g.ray_test(ray, active=act_t)
+    want_lean = g.ray_intersect(ray, active=act_t, fields=("t", "p", "n", "uv"))
+    g.set_ray_coherence(False)
+    try:
+        si, pi = g.ray_intersect(ray, active=act_t, return_prelim=True)
+        pi2 = g.ray_intersect_preliminary(ray, active=act_t)
+        hitp = g.ray_test(ray, active=act_t)
+        lean = g.ray_intersect(ray, active=act_t, fields=("t", "p", "n", "uv"))
+    finally:
+        g.set_ray_coherence(True)
+    for a, b in ((pi.t, want_pi.t), (pi.prim_uv, want_pi.prim_uv), (pi2.t, want_pi.t), (pi2.prim_uv, want_pi.prim_uv)):
+        assert _same_bits(_np(a), _np(b)).all()
+    assert torch.equal(pi.prim_index, want_pi.prim_index) and torch.equal(pi2.prim_index, want_pi.prim_index)
+    assert torch.equal(hitp, want_hit)
+    ws, gs = _si_dict(want_si), _si_dict(si)
+    for k in ws:
+        assert _same_bits(gs[k], ws[k]).all(), k
+    for k in ("t", "p", "n", "uv"):
+        assert _same_bits(_np(getattr(lean, k)), _np(getattr(want_lean, k))).all(), k
+    assert 0.05 < float(want_pi.is_valid().float().mean()) < 1.0
+    if m <= 200000:                                   # and the oracle, on the smaller cases
+        pc = c.ray_intersect_preliminary(cr)
+        assert _same_bits(_np(pi.t), pc.t).all()
