@@ -259,7 +259,8 @@ def main_ours(a):
     cam = wl.CONFIGS["C3"]["camera"]
     # dev knob: HF_BENCH_SHARD_OF=N on ONE GPU times the rays rank 0 of an N-GPU run would get (kernel scaling without the box)
     shard_of = int(os.environ.get("HF_BENCH_SHARD_OF", "0")) if world == 1 else 0
-    pix = wl.tile_pixels(a.image, a.image, a.tile, rank, shard_of if shard_of > 1 else world, device=dev)
+    shard_rank = int(os.environ.get("HF_BENCH_SHARD_RANK", "0")) if shard_of > 1 else rank       # ... or of any other rank of that run
+    pix = wl.tile_pixels(a.image, a.image, a.tile, shard_rank, shard_of if shard_of > 1 else world, device=dev)
     o, d = wl.camera_rays(cam["origin"], cam["target"], cam["up"], cam["fov"], a.image, a.image, a.spp, seed=0, device=dev, pixels=pix)
     n_local = o.shape[1]
     n_total = a.image * a.image * a.spp if shard_of <= 1 else n_local
@@ -569,8 +570,9 @@ def run_render_step(a, shape, h, params, opt, rank, world, dev, timed, ev, peer=
     cam = hfb200.perspective_camera(cam3["origin"], cam3["target"], cam3["up"], cam3["fov"], a.image, a.image, a.spp, seed=0)
     light = hfb200.directional_light((0.3, 0.2, 1.0))
     shard_of = int(os.environ.get("HF_BENCH_SHARD_OF", "0")) if world == 1 else 0      # dev knob, see main_ours
+    shard_rank = int(os.environ.get("HF_BENCH_SHARD_RANK", "0")) if shard_of > 1 else rank
     pix = None if world == 1 and shard_of <= 1 else \
-        wl.tile_pixels(a.image, a.image, a.tile, rank, shard_of if shard_of > 1 else world, device=dev).to(torch.int32)
+        wl.tile_pixels(a.image, a.image, a.tile, shard_rank, shard_of if shard_of > 1 else world, device=dev).to(torch.int32)
     # target image: the same scene over another fBm field (seed 0x7A); every rank renders the pixels it owns
     tgt_shape = hfb200.load_dict({"type": "heightfield", "heights": wl.fbm_heights(a.heights, octaves=8, seed=0x7A, device=dev),
                                   "max_height": 0.3}, device=dev)

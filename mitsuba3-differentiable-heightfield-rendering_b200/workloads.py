@@ -110,12 +110,16 @@ def camera_rays(origin, target, up, fov_deg, width, height, spp, seed=0, device=
     return o, d.contiguous()
 
 
-def tile_pixels(width, height, tile, rank, world, device="cpu"):
-    """Image tiles (tile x tile pixels) dealt round-robin to ranks; pixels of a rank ordered
-    tile by tile, row-major inside a tile."""
+def tile_pixels(width, height, tile, rank, world, device="cpu", skew=3):
+    """Image tiles (tile x tile pixels) dealt round-robin to ranks; pixels of a rank ordered tile by tile, row-major
+    inside a tile. The deal runs over a SKEWED tile order -- row r of tiles is rotated by skew * r columns -- because a plain
+    row-major deal gives rank k the same tile COLUMNS in every row whenever the tiles per row divide by the number of ranks (32 tiles
+    per row, 8 ranks: vertical stripes), and the cost of a pixel depends on its column: measured at 8 ranks on C3, the slowest rank
+    was 18 % behind the fastest (profiles/r02_notes.md). Counts per rank still differ by at most one tile."""
     tx, ty = (width + tile - 1) // tile, (height + tile - 1) // tile
-    tiles = torch.arange(rank, tx * ty, world, dtype=torch.int64, device=device)
-    t_x, t_y = tiles % tx, tiles // tx
+    slots = torch.arange(rank, tx * ty, world, dtype=torch.int64, device=device)       # positions in the skewed order
+    t_y = slots // tx
+    t_x = (slots % tx - skew * t_y) % tx                                                # slot (r, c) holds tile column (c - skew r) mod tx
     loc = torch.arange(tile * tile, dtype=torch.int64, device=device)
     lx, ly = loc % tile, loc // tile
     x = (t_x[:, None] * tile + lx[None, :]).reshape(-1)
