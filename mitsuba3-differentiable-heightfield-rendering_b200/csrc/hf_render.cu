@@ -501,7 +501,10 @@ __device__ __forceinline__ void hf_normal_adjoint(const HfParams &P, uint32_t pr
 // Path-traced image (BWD = false) or its adjoint by replay (BWD = true: the pixel adjoint is read from adj_image, every
 // vertex of every path scatters into grad). Same tiling as hf_render_kernel; only the primary segment uses the bundle entry.
 template <bool BWD>
-__global__ void __launch_bounds__(HF_BLOCK, 2)
+#ifndef HF_PATH_MIN_CTAS
+#define HF_PATH_MIN_CTAS 3             // 80 registers (68 bytes of spills): the walk waits on L2 at 10 of 32 lanes, resident warps pay -- C4 step 38.9 (2) / 35.7 (3) / 37.2 ms (4)
+#endif
+__global__ void __launch_bounds__(HF_BLOCK, HF_PATH_MIN_CTAS)
 hf_render_path_kernel(const __grid_constant__ HfParams P, const HfLaunchInfo li, const __grid_constant__ HfRenderArgs A,
                       float *__restrict__ image, const float *__restrict__ adj_image, float *__restrict__ grad,
                       unsigned long long *__restrict__ sched) {
@@ -694,7 +697,7 @@ cudaError_t hf_launch_render(const HfParams &P, const HfLaunchInfo &li, int mode
     const size_t smem = hf_walk_smem(li, true);
     const int grid = hf_render_grid(li, npix);
     if (A.max_depth > 1) {                    // path tracing: forward image or replayed adjoint (the fused L2 step is composed by hf_api.cu)
-        const int pgrid = grid < li.num_sms * 2 ? grid : li.num_sms * 2;
+        const int pgrid = grid < li.num_sms * HF_PATH_MIN_CTAS ? grid : li.num_sms * HF_PATH_MIN_CTAS;
         if (mode == HF_RENDER_FWD)
             hf_render_path_kernel<false><<<pgrid, HF_BLOCK, smem, s>>>(P, li, A, d_image, nullptr, nullptr, d_sched);
         else if (mode == HF_RENDER_BWD)
