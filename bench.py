@@ -528,7 +528,7 @@ def main_ours(a):
                                   "bytes_per_ray": bpr_bwd, "model": f"hit {B_BWD_HIT} B (ray 28, prelim 16, adjoints 36, atomics 12, cell re-fetch 16) x {hits:.3f} + miss {B_BWD_MISS} B",
                                   "traffic": tr_bwd, "dram_gbs": (tr_bwd / (ms_bwd * 1e-3) / 1e9) if tr_bwd else None,
                                   "dram_frac": (tr_bwd / (ms_bwd * 1e-3) / 1e9 / peak) if tr_bwd else None,
-                                  "limiter": "latency (dependent loads): ncu issue slots 43 %, DRAM 38 %, 0.9 eligible warps per cycle"}},
+                                  "limiter": "memory latency, then HBM: ncu issue slots 64 %, DRAM throughput 51 %, 1.6 eligible warps per cycle (profiles/r02_ncu_full_summary.txt)"}},
         "extras": {"intersect_only_mrays": n_total / (ms_isect * 1e-3) / 1e6, "intersect_only_ms": ms_isect,
                    "full_step_mrays": n_total / (ms_full * 1e-3) / 1e6, "full_step_ms": ms_full,
                    "full_step": "zero_grad + intersect/SI + backward + allreduce + Adam + pyramid rebuild", "full_step_launch": full_launch,

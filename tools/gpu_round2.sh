@@ -11,7 +11,7 @@ timeout 900 python bench.py --steps 10 --warmup 3 > gpurun_out/${tag}_bench.json
 timeout 600 python bench.py --config C4 --heights 2048 --image 512 --steps 3 --no-cpu > gpurun_out/${tag}_c4_small.json 2> gpurun_out/${tag}_c4_small.err; echo "c4 small rc=$?"; tail -3 gpurun_out/${tag}_c4_small.err
 timeout 1200 python bench.py --config C4 --steps 5 > gpurun_out/${tag}_c4.json 2> gpurun_out/${tag}_c4.err; echo "c4 rc=$?"; cat gpurun_out/${tag}_c4.json; tail -3 gpurun_out/${tag}_c4.err
 timeout 1500 python bench.py --config C5 > gpurun_out/${tag}_c5.json 2> gpurun_out/${tag}_c5.err; echo "c5 rc=$?"; cut -c1-1500 gpurun_out/${tag}_c5.json; tail -3 gpurun_out/${tag}_c5.err
-for tm in "48 48" "24 24" "16 32" "32 64" "8 16" "12 12"; do set -- $tm
+for tm in; do set -- $tm
   HF_BENCH_SHARD_OF=8 HF_B200_TAIL=$1 HF_B200_MIDTAIL=$2 python bench.py --steps 10 --warmup 3 --no-e2e --no-cpu 2>/dev/null | python -c "
 import sys, json
 for line in sys.stdin:
