@@ -810,9 +810,13 @@ extern "C" int hf_peer_export(hf_ctx *c, uint8_t out[HF_PEER_HANDLE_BYTES]) {
         CU(cudaMalloc(&c->d_xcounter, size_t(2) << 20));            // an allocation of its own (IPC maps whole allocations)
         CU(cudaMemset(c->d_xcounter, 0, size_t(2) << 20));
     }
-    if (!c->d_stage) {                                              // one slab per sender, whatever the number of ranks will be
-        const size_t elems = (size_t) c->W * c->H + (size_t) HF_MAX_PEERS * 2048;
-        CU(cudaMalloc(&c->d_stage, std::max(elems * sizeof(float), size_t(2) << 20)));
+    {                                                               // one slab per sender, whatever the number of ranks will be
+        const size_t bytes = std::max(((size_t) c->W * c->H + (size_t) HF_MAX_PEERS * 2048) * sizeof(float), size_t(2) << 20);
+        if (!c->d_stage) CU(cudaMalloc(&c->d_stage, bytes));
+        // all-zero before anybody can reach it: the senders skip the zero lines of their partial sums, and the owner clears what it has
+        // read, so the area is all-zero again after every reduction
+        CU(cudaMemset(c->d_stage, 0, bytes));
+        CU(cudaDeviceSynchronize());                                // ... and finished before the handle leaves this process
     }
     cudaIpcMemHandle_t h[4];
     CU(cudaIpcGetMemHandle(&h[0], c->d_grad));

@@ -1219,37 +1219,74 @@ hf_peer_adam_kernel(float *__restrict__ p, const float *__restrict__ g, float *_
 }
 
 // ---- reduce-scatter by peer STORES (the default peer mode; remote atomics reach only ~2 G/s over NVLink, stores run at link rate) ----
-// A. every rank stores the part of its LOCAL gradient grid that belongs to rank r into rank r's staging area (slot = sender)
+// A. every rank stores the part of its LOCAL gradient grid that belongs to rank r into rank r's staging area (slot = sender).
+// A rank's rays come from its image tiles, so its grid is zero over most of the terrain: 128-byte lines that hold only zeros are
+// NOT sent. The staging areas are all-zero whenever no reduction is in flight (cleared at export; kernel B clears what it read).
 __global__ void __launch_bounds__(256)
 hf_peer_send_partials_kernel(const float *__restrict__ local, float *const *__restrict__ peer_stage, const int nranks, const int rank,
                              const size_t slab, const size_t total) {
-    const size_t slab4 = slab / 4;                              // slabs are multiples of 1024 texels
-    const size_t work = slab4 * (size_t) (nranks - 1);
+    const size_t slab4 = slab / 4;                              // slabs are multiples of 1024 texels: `work` is a multiple of the CTA size,
+    const size_t work = slab4 * (size_t) (nranks - 1);          // so the trip count is uniform over a CTA and the ballot below is safe
+    const unsigned group = 0xffu << (threadIdx.x & 24u);        // the 8 lanes of one 128-byte line
     for (size_t w = (size_t) blockIdx.x * blockDim.x + threadIdx.x; w < work; w += (size_t) gridDim.x * blockDim.x) {
         const int k = (int) (w / slab4);
         const size_t i = w - (size_t) k * slab4;
         const int r = k < rank ? k : k + 1;                     // the k-th OTHER rank
         const size_t src = (size_t) r * slab + 4 * i;
-        if (src >= total) continue;
-        float4 v;
+        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
         if (src + 4 <= total) v = *reinterpret_cast<const float4 *>(local + src);
-        else { v.x = local[src]; v.y = src + 1 < total ? local[src + 1] : 0.f; v.z = src + 2 < total ? local[src + 2] : 0.f; v.w = 0.f; }
-        __stcs(reinterpret_cast<float4 *>(peer_stage[r] + (size_t) rank * slab) + i, v);
+        else if (src < total) { v.x = local[src]; v.y = src + 1 < total ? local[src + 1] : 0.f; v.z = src + 2 < total ? local[src + 2] : 0.f; }
+        const bool nz = v.x != 0.f || v.y != 0.f || v.z != 0.f || v.w != 0.f;              // (NaN != 0: a poisoned grid travels)
+        if (__ballot_sync(0xffffffffu, nz) & group) __stcs(reinterpret_cast<float4 *>(peer_stage[r] + (size_t) rank * slab) + i, v);
     }
 }
 
 // B. the owner sums the partial slabs in rank order (own grid in place of its own slot) and stores the sum into every rank's grid:
 // reduction and all-gather in one pass. ADAM: the sum feeds the Adam update of the slab instead, and the HEIGHTS go to every rank.
+// Every staged value that was not zero is cleared behind the read, which is what lets kernel A skip zero lines next time.
 template <bool ADAM>
 __global__ void __launch_bounds__(256)
-hf_peer_reduce_gather_kernel(float *__restrict__ local_grad, const float *__restrict__ my_stage, float *const *__restrict__ peer_out, const int nranks,
+hf_peer_reduce_gather_kernel(float *__restrict__ local_grad, float *__restrict__ my_stage, float *const *__restrict__ peer_out, const int nranks,
                              const int rank, const size_t lo, const size_t hi, const size_t slab, float *__restrict__ p, float *__restrict__ m,
                              float *__restrict__ v, const float *__restrict__ lr_t_ptr, const float b1, const float b2, const float omb1, const float omb2,
                              const float eps, const int mask) {
     const float lr_t = ADAM ? __ldg(lr_t_ptr) : 0.f;
-    for (size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x; lo + i < hi; i += (size_t) gridDim.x * blockDim.x) {
+    const size_t n4 = (hi - lo) / 4;                            // lo and the slots are multiples of 1024 texels, the buffers 256-byte aligned
+    for (size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (size_t) gridDim.x * blockDim.x) {
+        float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int r = 0; r < nranks; ++r) {
+            float4 a;
+            if (r == rank) a = reinterpret_cast<const float4 *>(local_grad + lo)[i];
+            else {
+                float4 *slot = reinterpret_cast<float4 *>(my_stage + (size_t) r * slab) + i;
+                a = __ldcs(slot);
+                if (a.x != 0.f || a.y != 0.f || a.z != 0.f || a.w != 0.f) __stcs(slot, make_float4(0.f, 0.f, 0.f, 0.f));
+            }
+            g.x += a.x; g.y += a.y; g.z += a.z; g.w += a.w;
+        }
+        reinterpret_cast<float4 *>(local_grad + lo)[i] = g;
+        float4 outv = g;
+        if (ADAM) {
+            float4 pp = reinterpret_cast<float4 *>(p + lo)[i], mm = reinterpret_cast<float4 *>(m + lo)[i], vv = reinterpret_cast<float4 *>(v + lo)[i];
+            adam_one(pp.x, g.x, mm.x, vv.x, lr_t, b1, b2, omb1, omb2, eps, mask);
+            adam_one(pp.y, g.y, mm.y, vv.y, lr_t, b1, b2, omb1, omb2, eps, mask);
+            adam_one(pp.z, g.z, mm.z, vv.z, lr_t, b1, b2, omb1, omb2, eps, mask);
+            adam_one(pp.w, g.w, mm.w, vv.w, lr_t, b1, b2, omb1, omb2, eps, mask);
+            reinterpret_cast<float4 *>(p + lo)[i] = pp; reinterpret_cast<float4 *>(m + lo)[i] = mm; reinterpret_cast<float4 *>(v + lo)[i] = vv;
+            outv = pp;
+        }
+        for (int r = 0; r < nranks; ++r)
+            if (r != rank) __stcs(reinterpret_cast<float4 *>(peer_out[r] + lo) + i, outv);
+    }
+    for (size_t i = 4 * n4 + (size_t) blockIdx.x * blockDim.x + threadIdx.x; lo + i < hi; i += (size_t) gridDim.x * blockDim.x) {      // W*H % 4 texels
         float g = 0.f;
-        for (int r = 0; r < nranks; ++r) g += (r == rank) ? local_grad[lo + i] : __ldcs(my_stage + (size_t) r * slab + i);
+        for (int r = 0; r < nranks; ++r) {
+            if (r == rank) { g += local_grad[lo + i]; continue; }
+            float *slot = my_stage + (size_t) r * slab + i;
+            const float a = __ldcs(slot);
+            if (a != 0.f) *slot = 0.f;
+            g += a;
+        }
         local_grad[lo + i] = g;
         float outv = g;
         if (ADAM) {
@@ -1269,12 +1306,12 @@ cudaError_t hf_launch_peer_send_partials(const float *local, float *const *d_pee
     hf_peer_send_partials_kernel<<<(int) (blocks < cap ? (blocks ? blocks : 1) : cap), 256, 0, s>>>(local, d_peer_stage, nranks, rank, slab, total);
     return cudaGetLastError();
 }
-cudaError_t hf_launch_peer_reduce_gather(float *local_grad, const float *my_stage, float *const *d_peer_out, int nranks, int rank, size_t lo, size_t hi, size_t slab,
+cudaError_t hf_launch_peer_reduce_gather(float *local_grad, float *my_stage, float *const *d_peer_out, int nranks, int rank, size_t lo, size_t hi, size_t slab,
                                          bool adam, float *p, float *m, float *v, int *d_t, float *d_lr_t, const float *d_scale_table, int table_len, float lr,
                                          float beta1, float beta2, float omb1, float omb2, float eps, int mask_updates, int num_sms, cudaStream_t s) {
     if (adam) hf_adam_prep_kernel<<<1, 1, 0, s>>>(d_t, d_lr_t, d_scale_table, table_len, lr);
     if (hi > lo) {
-        const size_t blocks = (hi - lo + 255) / 256, cap = (size_t) num_sms * 8;
+        const size_t blocks = ((hi - lo + 3) / 4 + 255) / 256, cap = (size_t) num_sms * 8;
         const int grid = (int) (blocks < cap ? (blocks ? blocks : 1) : cap);
         if (adam) hf_peer_reduce_gather_kernel<true><<<grid, 256, 0, s>>>(local_grad, my_stage, d_peer_out, nranks, rank, lo, hi, slab, p, m, v, d_lr_t, beta1, beta2, omb1, omb2, eps, mask_updates);
         else hf_peer_reduce_gather_kernel<false><<<grid, 256, 0, s>>>(local_grad, my_stage, d_peer_out, nranks, rank, lo, hi, slab, nullptr, nullptr, nullptr, nullptr, 0.f, 0.f, 0.f, 0.f, 0.f, 0);

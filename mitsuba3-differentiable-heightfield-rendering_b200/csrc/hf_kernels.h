@@ -50,7 +50,7 @@ cudaError_t hf_launch_peer_adam(float *p, const float *g, float *m, float *v, fl
                                 float omb2, float eps, int mask_updates, int num_sms, cudaStream_t s);
 
 cudaError_t hf_launch_peer_send_partials(const float *local, float *const *d_peer_stage, int nranks, int rank, size_t slab, size_t total, int num_sms, cudaStream_t s);
-cudaError_t hf_launch_peer_reduce_gather(float *local_grad, const float *my_stage, float *const *d_peer_out, int nranks, int rank, size_t lo, size_t hi, size_t slab,
+cudaError_t hf_launch_peer_reduce_gather(float *local_grad, float *my_stage, float *const *d_peer_out, int nranks, int rank, size_t lo, size_t hi, size_t slab,
                                          bool adam, float *p, float *m, float *v, int *d_t, float *d_lr_t, const float *d_scale_table, int table_len, float lr,
                                          float beta1, float beta2, float omb1, float omb2, float eps, int mask_updates, int num_sms, cudaStream_t s);
 

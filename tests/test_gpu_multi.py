@@ -135,7 +135,8 @@ def _peer_worker(rank, world, port, out_dir):
     from hfb200 import workloads as wl
     torch.cuda.set_device(rank)
     dev = torch.device("cuda", rank)
-    hs, img, spp, tile = 300, 128, 8, 16                      # 90 000 texels: slabs are not a power of two, the last one is short
+    hs, img, spp, tile = 301, 128, 8, 16                      # 90 601 texels: slabs are not a power of two, the last one is short and
+                                                              # ends in the middle of a float4
     cam = wl.CONFIGS["C1"]["camera"]
     h = wl.fbm_heights(hs, octaves=5, seed=0xC1, device=dev)
 
@@ -178,9 +179,11 @@ def _peer_worker(rank, world, port, out_dir):
     gr = one.grad.double().clone()
     my_pix32 = my_pix.to(torch.int32)
 
-    def peer_step():
+    other_pix = wl.tile_pixels(img, img, tile, (rank + 1) % world, world, device=dev)
+
+    def peer_step(pix=my_pix):
         shape.peer_zero_grad()
-        trace(shape, my_pix)
+        trace(shape, pix)
         shape.peer_reduce_grad()
 
     for mode in (1, 0):      # 1: local scatter + reduce-scatter by peer stores (default); 0: scatters go to the owner with remote atomics
@@ -192,6 +195,13 @@ def _peer_worker(rank, world, port, out_dir):
             err = float((shape.grad.double() - g1).norm() / g1.norm())
             assert err < 1e-4, f"mode {mode}: peer reduction vs single rank: {err:.2e} (attempt {attempt})"
             everyone_agrees(shape.grad, f"the reduced gradient (mode {mode})")
+        # ---- (1b) the ranks swap their tiles: lines of a partial grid that were sent last time are zero now and are NOT sent (mode 1),
+        # so the owner must have cleared its staging area behind the previous reduction
+        peer_step(other_pix)
+        torch.cuda.synchronize()
+        err = float((shape.grad.double() - g1).norm() / g1.norm())
+        assert err < 1e-4, f"mode {mode}: peer reduction after the ranks swapped tiles: {err:.2e}"
+        everyone_agrees(shape.grad, f"the reduced gradient after a tile swap (mode {mode})")
         # ---- (2) the same step replayed from a CUDA graph (barriers are kernels)
         replay = hfb200.capture(peer_step)
         for _ in range(2):
