@@ -256,6 +256,10 @@ def main_ours(a):
     # ---- workload (synthetic, identical on every rank; rays sharded by image tile) ----
     h = wl.fbm_heights(a.heights, octaves=8, seed=0xC3, device=dev)
     shape = hfb200.load_dict({"type": "heightfield", "heights": h, "max_height": 0.3}, device=dev)
+    # the step traces the same rays every iteration, as an optimisation does: the launches learn which 32-ray groups are far above the
+    # mean and start with those (include/hf_b200.h hf_set_adaptive_schedule; HF_BENCH_ADAPTIVE=0: the fixed schedule of round 1)
+    adaptive = os.environ.get("HF_BENCH_ADAPTIVE", "1") != "0"
+    shape.set_adaptive_schedule(adaptive)
     cam = wl.CONFIGS["C3"]["camera"]
     # dev knob: HF_BENCH_SHARD_OF=N on ONE GPU times the rays rank 0 of an N-GPU run would get (kernel scaling without the box)
     shard_of = int(os.environ.get("HF_BENCH_SHARD_OF", "0")) if world == 1 else 0
@@ -353,6 +357,7 @@ def main_ours(a):
         run_step()
     ms_total = timed(run_step, a.steps)
     ms_step = ms_total / a.steps
+    sched_info = shape.adaptive_schedule_info()
     ms_allreduce = timed(shape.allreduce_grad, 10) / 10 if world > 1 else 0.0     # the collective alone (64 MiB fp32 at C3)
     collective = "none (1 GPU)" if world == 1 else "ncclAllReduce(grad 64 MiB fp32, sum) per step"
     peer = None
@@ -511,10 +516,11 @@ def main_ours(a):
                    "zero_grad": "on a second stream beside the forward kernel" if overlap_zero else "in stream order",
                    "collective": collective,
                    "l2": "inputs exceed L2 (ray + adjoint + output SoA > 5 GB per step vs 126 MB L2); no explicit flush",
-                   "si_fields": "t,p,n,uv", "hit_fraction": hits},
+                   "si_fields": "t,p,n,uv", "hit_fraction": hits,
+                   "schedule": "adaptive (groups far above the mean cost of the previous launch go first)" if adaptive else "fixed"},
         "clocks": clocks,
-        "gpu_launches": 2 * a.steps,
-        "kernels_per_step": ["hf_intersect_fast_kernel<FUSED_SI>", "hf_backward_kernel"],
+        "gpu_launches": (3 if adaptive else 2) * a.steps,
+        "kernels_per_step": ["hf_intersect_fast_kernel<FUSED_SI>"] + (["hf_pick_heavy_kernel"] if adaptive else []) + ["hf_backward_kernel"],
         "roofline": {"bound": "hbm", "kernel": "hf_intersect_fast_kernel<FUSED_SI>", "achieved": ach_fwd, "peak": peak, "unit": "GB/s",
                      "frac": ach_fwd / peak, "traffic": tr_fwd, "traffic_unit": "bytes per launch (ncu dram__bytes_read + write, profiles/traffic.json)",
                      "what_frac_means": "ALGORITHMIC bytes of SURVEY.md 8(d) per second over the measured HBM copy bandwidth -- the contract's figure, NOT DRAM utilisation: "
@@ -536,7 +542,8 @@ def main_ours(a):
                    "kernel_ms_over_ranks": rank_spread,
                    "grad_rel_l2_vs_single_rank": shard_check,
                    "grad_rel_l2_vs_single_rank_what": "N-rank tile shards + hf_allreduce_grad vs one rank tracing every ray, 512^2 heights, 256^2 x 16 spp, in this run",
-                   "grad_abs_sum": grad_checksum, "mean_nodes_per_ray": n_node, "mean_leaves_per_ray": n_leaf},
+                   "grad_abs_sum": grad_checksum, "mean_nodes_per_ray": n_node, "mean_leaves_per_ray": n_leaf,
+                   "adaptive_schedule": dict(zip(("listed_groups", "groups"), sched_info)) if adaptive else None},
     }
     # SURVEY.md 8(d) "full step" byte model: rays x (B_trav + 16 + 12) + texels x (4 + 28 + 4 + 8/3) + pixels x 36
     texels, pixels_img = float(a.heights) ** 2, float(a.image) ** 2

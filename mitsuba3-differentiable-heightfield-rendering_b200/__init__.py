@@ -136,6 +136,8 @@ def _load():
         "hf_parameters_grad_enabled": [vp, C.POINTER(C.c_int)],
         "hf_set_grad_enabled": [vp, C.c_int],
         "hf_set_ray_coherence": [vp, C.c_int],
+        "hf_set_adaptive_schedule": [vp, C.c_int],
+        "hf_adaptive_schedule_info": [vp, C.POINTER(u32), C.POINTER(u32)],
         "hf_bbox": [vp, _f32p],
         "hf_primitive_count": [vp, C.POINTER(u32)],
         "hf_size": [vp, C.POINTER(u32), C.POINTER(u32)],
@@ -440,6 +442,17 @@ class Heightfield:
         """The `coherent` hint of Scene::ray_intersect (src/render/scene.cpp:141-150) for the ray-array entry points: False = the
         rays of a batch are unrelated (every lane of a warp keeps its own ray); results are bit-identical either way."""
         _check(_load().hf_set_ray_coherence(self._ctx, int(bool(coherent))))
+
+    def set_adaptive_schedule(self, on=True):
+        """include/hf_b200.h hf_set_adaptive_schedule: large coherent batches of the same size (the rays of an optimisation's iterations)
+        start with the 32-ray groups the previous launch found far more expensive than the mean. Results do not depend on it."""
+        _check(_load().hf_set_adaptive_schedule(self._ctx, int(bool(on))))
+
+    def adaptive_schedule_info(self):
+        """(listed, groups): how many of the last large batch's 32-ray groups the next launch will start with"""
+        a, b = C.c_uint32(0), C.c_uint32(0)
+        _check(_load().hf_adaptive_schedule_info(self._ctx, C.byref(a), C.byref(b)))
+        return int(a.value), int(b.value)
 
     def zero_grad(self):
         with torch.cuda.device(self.device):

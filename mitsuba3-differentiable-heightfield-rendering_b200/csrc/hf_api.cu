@@ -171,6 +171,14 @@ struct hf_ctx {
     float *d_stage = nullptr;             // staging area of this rank: slot r = rank r's partial sums for MY slab
     float *peer_stage[HF_MAX_PEERS] = { nullptr };
     float **d_peer_stage_tab = nullptr;
+    // adaptive schedule of the per-ray kernel (hf_set_adaptive_schedule): cost per 32-ray group of the last launch, the heavy list made from it
+    int adaptive = 0;
+    size_t as_cap = 0, as_groups = 0;     // groups the buffers hold / groups of the batch the list was made from
+    uint16_t *d_as_cost = nullptr;
+    unsigned *d_as_list = nullptr, *d_as_n = nullptr;
+    uint32_t *d_as_bits = nullptr;
+    unsigned long long *d_as_sum = nullptr;
+    std::vector<void *> as_retired;       // outgrown buffers: CUDA graphs recorded earlier may still hold them
     // host-buffer render step: device copies of the caller's target / image / pixel list, and the loss
     float *d_hs_target = nullptr, *d_hs_image = nullptr;
     uint32_t *d_hs_pixels = nullptr;
@@ -224,6 +232,51 @@ static unsigned long long *next_sched(hf_ctx *c, cudaStream_t s) {
 }
 #define SCHED(c, s) ({ unsigned long long *p_ = next_sched((c), (cudaStream_t) (s)); \
     if (!p_) return fail(HF_ERR_STATE, "this context has recorded more than %d self-scheduling launches into CUDA graphs", HF_SCHED_CAPTURE_SLOTS); p_; })
+
+// Launch info of one per-ray launch over n rays: c->li plus, when the adaptive schedule is on and the batch is large, its buffers.
+// A batch of another size than the last one starts without a list (and makes the next one); while a CUDA graph is being recorded
+// nothing may be allocated or reset behind the stream's back, so such a launch simply runs the plain schedule.
+#define HF_AS_MIN_GROUPS 16384u
+#define HF_AS_MAX_GROUPS_PER_WARP 320    // of the 24 resident warps per SM
+#define HF_AS_LIST_CAP 4096u
+static HfLaunchInfo launch_info_for(hf_ctx *c, size_t n, cudaStream_t s) {
+    HfLaunchInfo li = c->li;
+    const size_t ngroups = (n + 31) / 32;
+    if (!c->adaptive || li.incoherent || li.use_bundles || ngroups < HF_AS_MIN_GROUPS) return li;
+    // The closing phase of a launch weighs ~1 / (groups per resident warp); keeping the books costs the kernel ~1 % whatever its
+    // length. Measured on C3 (profiles/r02_notes.md): 1/8 of the batch (74 groups per warp) -11 %, 1/4 -5 %, 1/2 (295) -1.5 %, the
+    // whole batch (590) +1 %. So: only launches short enough for the end to matter.
+    static const int env_gpw = getenv("HF_B200_AS_MAX_GPW") ? atoi(getenv("HF_B200_AS_MAX_GPW")) : HF_AS_MAX_GROUPS_PER_WARP;     // dev knob
+    if (ngroups > (size_t) c->num_sms * 24 * (size_t) (env_gpw > 0 ? env_gpw : HF_AS_MAX_GROUPS_PER_WARP) || ngroups >= (size_t(1) << 31)) return li;
+    cudaStreamCaptureStatus st = cudaStreamCaptureStatusNone;
+    if (cudaStreamIsCapturing(s, &st) != cudaSuccess) { cudaGetLastError(); st = cudaStreamCaptureStatusNone; }
+    const bool capturing = st == cudaStreamCaptureStatusActive;
+    if (ngroups > c->as_cap) {
+        if (capturing) return li;
+        const size_t cap = (ngroups + 1023) & ~size_t(1023);
+        uint16_t *cost = nullptr; unsigned *list = nullptr; uint32_t *bits = nullptr;
+        if (cudaMalloc(&cost, cap * sizeof(uint16_t)) != cudaSuccess || cudaMalloc(&bits, cap / 32 * sizeof(uint32_t)) != cudaSuccess ||
+            cudaMalloc(&list, (HF_AS_LIST_CAP + 4) * sizeof(unsigned)) != cudaSuccess) {
+            cudaGetLastError(); cudaFree(cost); cudaFree(bits); cudaFree(list);
+            return li;                                   // a schedule hint must not fail a launch
+        }
+        if (c->d_as_cost) { c->as_retired.push_back(c->d_as_cost); c->as_retired.push_back(c->d_as_bits); c->as_retired.push_back(c->d_as_list); }
+        c->d_as_cost = cost; c->d_as_bits = bits; c->d_as_list = list;
+        c->d_as_n = list + HF_AS_LIST_CAP;               // the count and the cost sum live behind the list
+        c->d_as_sum = reinterpret_cast<unsigned long long *>(list + HF_AS_LIST_CAP + 2);
+        c->as_cap = cap; c->as_groups = 0;
+    }
+    if (c->as_groups != ngroups) {
+        if (capturing) return li;
+        if (cudaMemsetAsync(c->d_as_n, 0, sizeof(unsigned), s) != cudaSuccess) { cudaGetLastError(); return li; }
+        c->as_groups = ngroups;
+    }
+    li.grp_cost = c->d_as_cost; li.cost_sum = c->d_as_sum; li.heavy_n = c->d_as_n; li.heavy_list = c->d_as_list; li.heavy_bits = c->d_as_bits;
+    li.heavy_cap = HF_AS_LIST_CAP; li.heavy_words = (unsigned) (c->as_cap / 32);
+    li.heavy_shift = 0;
+    while (((ngroups - 1) >> li.heavy_shift) >= 8192) li.heavy_shift++;
+    return li;
+}
 
 static void layout_pyramid(hf_ctx *c) {
     HfParams &P = c->P;
@@ -352,6 +405,8 @@ extern "C" int hf_destroy(hf_ctx *c) {
     if (c->s_in) cudaStreamDestroy(c->s_in);
     if (c->s_k) cudaStreamDestroy(c->s_k);
     if (c->s_out) cudaStreamDestroy(c->s_out);
+    cudaFree(c->d_as_cost); cudaFree(c->d_as_bits); cudaFree(c->d_as_list);
+    for (void *p : c->as_retired) cudaFree(p);
     cudaFree(c->d_heights); cudaFree(c->d_grad); cudaFree(c->d_m); cudaFree(c->d_v); cudaFree(c->d_pyr); cudaFree(c->d_qpyr); cudaFree(c->d_counters); cudaFree(c->d_scratch);
     cudaFree(c->d_adam_t); cudaFree(c->d_adam_lr_t); cudaFree(c->d_adam_table);
     cudaFree(c->d_hs_target); cudaFree(c->d_hs_image); cudaFree(c->d_hs_pixels); cudaFree(c->d_hs_loss);
@@ -428,6 +483,27 @@ extern "C" int hf_parameters_changed(hf_ctx *c, void *stream) {
 extern "C" int hf_set_ray_coherence(hf_ctx *c, int coherent) {
     CHECK_CTX(c);
     c->li.incoherent = coherent ? 0 : 1;
+    return HF_OK;
+}
+
+extern "C" int hf_set_adaptive_schedule(hf_ctx *c, int on) {
+    CHECK_CTX(c);
+    c->adaptive = on ? 1 : 0;
+    c->as_groups = 0;                 // whatever was learnt is forgotten: the next large batch starts a new list
+    return HF_OK;
+}
+
+extern "C" int hf_adaptive_schedule_info(hf_ctx *c, uint32_t *listed, uint32_t *groups) {
+    CHECK_CTX(c);
+    unsigned n = 0;
+    if (c->adaptive && c->d_as_n && c->as_groups) {
+        CU(cudaSetDevice(c->device));
+        CU(cudaDeviceSynchronize());
+        CU(cudaMemcpy(&n, c->d_as_n, sizeof(n), cudaMemcpyDeviceToHost));
+        if (n > HF_AS_LIST_CAP) n = HF_AS_LIST_CAP;
+    }
+    if (listed) *listed = n;
+    if (groups) *groups = c->adaptive ? (uint32_t) c->as_groups : 0u;
     return HF_OK;
 }
 
@@ -550,7 +626,8 @@ extern "C" int hf_ray_intersect_preliminary(hf_ctx *c, const hf_rays *rays, cons
     NEED_ACCEL(c);
     CU(cudaSetDevice(c->device));
     hf_si none; memset(&none, 0, sizeof(none));
-    CU(hf_launch_intersect(c->P, c->li, HF_MODE_PRELIM, *rays, *out, none, nullptr, 0, n, c->d_counters, SCHED(c, stream), (cudaStream_t) stream));
+    CU(hf_launch_intersect(c->P, launch_info_for(c, n, (cudaStream_t) stream), HF_MODE_PRELIM, *rays, *out, none, nullptr, 0, n, c->d_counters, SCHED(c, stream),
+                           (cudaStream_t) stream));
     return HF_OK;
 }
 
@@ -623,7 +700,7 @@ extern "C" int hf_ray_intersect(hf_ctx *c, const hf_rays *rays, uint32_t flags, 
     NEED_ACCEL(c);
     CU(cudaSetDevice(c->device));
     hf_prelim nop; memset(&nop, 0, sizeof(nop));
-    CU(hf_launch_intersect(c->P, c->li, HF_MODE_FUSED_SI, *rays, prelim_out ? *prelim_out : nop, *out, nullptr, flags, n,
+    CU(hf_launch_intersect(c->P, launch_info_for(c, n, (cudaStream_t) stream), HF_MODE_FUSED_SI, *rays, prelim_out ? *prelim_out : nop, *out, nullptr, flags, n,
                            c->d_counters, SCHED(c, stream), (cudaStream_t) stream));
     return HF_OK;
 }

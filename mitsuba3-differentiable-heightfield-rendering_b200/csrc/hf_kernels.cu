@@ -649,6 +649,12 @@ __device__ __forceinline__ unsigned long long hf_gtime() { unsigned long long t;
 #ifndef HF_FAST_MIDTAIL
 #define HF_FAST_MIDTAIL 48
 #endif
+#ifndef HF_HEAVY_FACTOR
+#define HF_HEAVY_FACTOR 8          // adaptive schedule: a group is "heavy" above this many times the mean cost of a group ...
+#endif
+#ifndef HF_HEAVY_SPAN
+#define HF_HEAVY_SPAN 16           // ... and above 1/16 of the time a resident warp is busy in the launch
+#endif
 #ifndef HF_FAST_GROUPS
 #define HF_FAST_GROUPS 4           // 32-ray groups a warp takes off the global counter at a time
 #endif
@@ -657,13 +663,32 @@ __device__ __forceinline__ unsigned long long hf_gtime() { unsigned long long t;
 // cover those waits, the copies and the extra warp synchronisations only add instructions. profiles/r02_notes.md)
 // Persistent warps; each takes HF_FAST_GROUPS consecutive 32-ray groups at a time off one global counter: hit and miss regions of a
 // ray batch differ ~8x in cost per ray, and a static deal of tiles left the SMs idle 7 % of the kernel (profiles/r01_notes.md).
-template <int MODE>
+template <int MODE, bool ADAPT>
 __global__ void __launch_bounds__(HF_BLOCK, HF_MIN_CTAS)
 hf_intersect_fast_kernel(const __grid_constant__ HfParams P, const HfLaunchInfo li, const hf_rays R, const hf_prelim O,
                          const hf_si S, uint8_t *__restrict__ hit_out, const uint32_t flags, const size_t n,
                          const unsigned long long nbig, const unsigned long long npair, unsigned long long *__restrict__ sched) {
     HfGrid G;
-    hf_stage_pyramid<false>(P, li, G);       // no bundle march here: only the quantised coarse levels are staged
+    // ADAPT (hf_set_adaptive_schedule): the groups the previous launch found far more expensive than the rest go out first, one per
+    // fetch, and are skipped when their turn comes in the natural order -- a 100 us group that starts at t = 0 costs nothing, one
+    // that starts 10 us before the end of a 0.5 ms kernel costs 18 % (profiles/r02_notes.md). The list and the bitmap are written
+    // together by one kernel (hf_pick_heavy_kernel), so a group is processed exactly once whatever they hold; any schedule gives
+    // the same results. Its state lives in shared memory: the walk below has no register to spare.
+    __shared__ unsigned s_nheavy, s_c0[HF_BLOCK / 32];       // (costs in units of 64 cycles: 32 bits last 140 s)
+    // ... and a coarse copy of the bitmap (one bit per 2^heavy_shift groups, 8192 bits): the exact bit is a global load on every
+    // group's critical path (~550 cycles per group, 4 % of the kernel when measured); with the coarse bit clear it is not needed
+    __shared__ uint32_t s_coarse[256];
+    if (ADAPT) {
+        const unsigned nheavy = min(*li.heavy_n, li.heavy_cap);
+        if (threadIdx.x == 0) s_nheavy = nheavy;
+        s_coarse[threadIdx.x & 255u] = 0u;
+        __syncthreads();
+        for (unsigned k = threadIdx.x; k < nheavy; k += HF_BLOCK) {
+            const unsigned b = (li.heavy_list[k] >> li.heavy_shift) & 8191u;
+            atomicOr(&s_coarse[b >> 5], 1u << (b & 31u));
+        }
+    }
+    hf_stage_pyramid<false>(P, li, G);       // no bundle march here: only the quantised coarse levels are staged (ends with a CTA barrier)
 
     const unsigned lane = threadIdx.x & 31u;
     const unsigned long long ngroups = (n + 31) / 32;
@@ -671,6 +696,53 @@ hf_intersect_fast_kernel(const __grid_constant__ HfParams P, const HfLaunchInfo 
     const unsigned long long dbg_t0 = hf_gtime();
     unsigned long long dbg_max = 0, dbg_arg = 0, dbg_n = 0, dbg_last = dbg_t0, dbg_prev_t = 0;
 #endif
+    if (ADAPT) {
+        // 32-bit group ids (< 2^31: bit 31 of g0 marks a fetch from the list) and the clock in shared memory: the walk below has no
+        // register to spare (one more live value and the compiler recomputes loop invariants inside the leaf loop). A group's cost
+        // is the time since the warp finished the group before it -- one clock read per group -- and the sum of all costs is
+        // the time the warps were busy.
+        const unsigned ng32 = (unsigned) ngroups, nbig32 = (unsigned) nbig, npair32 = (unsigned) npair;
+        if (lane == 0) s_c0[threadIdx.x >> 5] = (unsigned) clock();
+        const unsigned c_begin = s_c0[threadIdx.x >> 5];
+        for (;;) {
+            unsigned t = 0;
+            if (lane == 0) t = (unsigned) atomicAdd(sched, 1ull);
+            t = __shfl_sync(FULL_MASK, t, 0);
+            const unsigned nheavy = s_nheavy;
+            unsigned g0, ng;
+            if (t < nheavy) {
+                g0 = li.heavy_list[t]; ng = g0 < ng32 ? 1u : 0u;       // (an id beyond the batch: a list made for a larger batch of this context)
+                g0 |= 0x80000000u;
+            } else {
+                t -= nheavy;
+                if (t < nbig32) { g0 = t * HF_FAST_GROUPS; ng = (unsigned) HF_FAST_GROUPS; }
+                else if (t < nbig32 + npair32) { g0 = nbig32 * HF_FAST_GROUPS + (t - nbig32) * 2u; ng = 2u; }
+                else { g0 = nbig32 * HF_FAST_GROUPS + npair32 * 2u + (t - nbig32 - npair32); ng = 1u; }
+                if (g0 >= ng32) break;
+                ng = min(ng, ng32 - g0);
+                if (nheavy == 0u) g0 |= 0x80000000u;                     // no list: nothing to skip
+            }
+            #pragma unroll 1
+            for (unsigned g = 0; g < ng; ++g) {
+                const unsigned gid = (g0 & 0x7fffffffu) + g;
+                if (!(g0 >> 31)) {
+                    const unsigned b = (gid >> li.heavy_shift) & 8191u;
+                    if (((s_coarse[b >> 5] >> (b & 31u)) & 1u) && ((li.heavy_bits[gid >> 5] >> (gid & 31u)) & 1u)) continue;      // it went out first
+                }
+                const size_t i = (size_t) gid * 32u + lane;
+                if (i < n) hf_process_ray<MODE>(P, G, R, O, S, hit_out, flags, i, 0.f, HF_START_LEVEL);
+                __syncwarp();
+#ifndef HF_AS_NO_RECORD          // (dev: what the consuming half of the schedule costs on its own)
+                if (lane == 0) {
+                    const unsigned now = (unsigned) clock();
+                    li.grp_cost[gid] = (uint16_t) min((now - s_c0[threadIdx.x >> 5]) >> 6, 65535u);
+                    s_c0[threadIdx.x >> 5] = now;
+                }
+#endif
+            }
+        }
+        if (lane == 0) atomicAdd(li.cost_sum, (unsigned long long) (((unsigned) clock() - c_begin) >> 6));
+    } else
     for (;;) {
         unsigned long long t = 0;
         if (lane == 0) t = atomicAdd(sched, 1ull);
@@ -700,6 +772,30 @@ hf_intersect_fast_kernel(const __grid_constant__ HfParams P, const HfLaunchInfo 
             if (i < n) hf_process_ray<MODE>(P, G, R, O, S, hit_out, flags, i, 0.f, HF_START_LEVEL);
             __syncwarp();
         }
+    }
+}
+
+// The list for the next launch: groups that cost more than `factor` times the mean AND more than 1 / HF_HEAVY_SPAN of what a resident
+// warp spent in the whole launch (only groups that can hold up the end of the kernel are worth taking out of their neighbourhood: a
+// listed group loses the L1 lines it shares with the groups next to it), at most `cap` of them. The bitmap is rewritten as a whole
+// (nwords words, zeros beyond the batch) so that it always matches the list.
+__global__ void __launch_bounds__(256)
+hf_pick_heavy_kernel(const uint16_t *__restrict__ cost, const unsigned ngroups, const unsigned long long *__restrict__ cost_sum,
+                     unsigned *__restrict__ heavy_n, unsigned *__restrict__ heavy_list, uint32_t *__restrict__ heavy_bits,
+                     const unsigned nwords, const unsigned cap, const unsigned factor, const unsigned span, const unsigned resident_warps) {
+    const unsigned long long sum = *cost_sum;
+    const unsigned long long by_mean = sum / (ngroups ? ngroups : 1u) * factor, by_span = sum / resident_warps / span;
+    const unsigned thresh = (unsigned) min((unsigned long long) 65534u, max(by_mean, by_span));
+    const unsigned lane = threadIdx.x & 31u;
+    for (unsigned w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; w < nwords; w += (gridDim.x * blockDim.x) >> 5) {
+        const unsigned g = w * 32u + lane;
+        bool h = g < ngroups && cost[g] > thresh;
+        if (h) {
+            const unsigned slot = atomicAdd(heavy_n, 1u);
+            if (slot < cap) heavy_list[slot] = g; else h = false;
+        }
+        const unsigned bits = __ballot_sync(FULL_MASK, h);
+        if (lane == 0) heavy_bits[w] = bits;
     }
 }
 
@@ -1036,11 +1132,15 @@ cudaError_t hf_launch_intersect(const HfParams &P, const HfLaunchInfo &li, int m
     const size_t smem = hf_walk_smem(li, false);
     if (!carved) {
         carved = true;
-        const size_t stat = 1024;                   // static shared memory of the kernel (level tables, barrier)
-        hf_prefer_l1(hf_intersect_fast_kernel<HF_MODE_PRELIM>, smem + stat, HF_MIN_CTAS);
-        hf_prefer_l1(hf_intersect_fast_kernel<HF_MODE_FUSED_SI>, smem + stat, HF_MIN_CTAS);
-        hf_prefer_l1(hf_intersect_fast_kernel<HF_MODE_FUSED_SI_LEAN>, smem + stat, HF_MIN_CTAS);
-        hf_prefer_l1(hf_intersect_fast_kernel<HF_MODE_TEST>, smem + stat, HF_MIN_CTAS);
+        const size_t stat = 1024;                   // static shared memory of the kernel (level tables, barrier; adaptive schedule: + 1 KB coarse bitmap, 2112 bytes in all)
+        hf_prefer_l1(hf_intersect_fast_kernel<HF_MODE_PRELIM, false>, smem + stat, HF_MIN_CTAS);
+        hf_prefer_l1(hf_intersect_fast_kernel<HF_MODE_PRELIM, true>, smem + stat, HF_MIN_CTAS);
+        hf_prefer_l1(hf_intersect_fast_kernel<HF_MODE_FUSED_SI, false>, smem + stat, HF_MIN_CTAS);
+        hf_prefer_l1(hf_intersect_fast_kernel<HF_MODE_FUSED_SI, true>, smem + stat, HF_MIN_CTAS);
+        hf_prefer_l1(hf_intersect_fast_kernel<HF_MODE_FUSED_SI_LEAN, false>, smem + stat, HF_MIN_CTAS);
+        hf_prefer_l1(hf_intersect_fast_kernel<HF_MODE_FUSED_SI_LEAN, true>, smem + stat, HF_MIN_CTAS);
+        hf_prefer_l1(hf_intersect_fast_kernel<HF_MODE_TEST, false>, smem + stat, HF_MIN_CTAS);
+        hf_prefer_l1(hf_intersect_fast_kernel<HF_MODE_TEST, true>, smem + stat, HF_MIN_CTAS);
     }
     {
         const size_t ngroups = (n + 31) / 32;
@@ -1055,22 +1155,37 @@ cudaError_t hf_launch_intersect(const HfParams &P, const HfLaunchInfo &li, int m
         const size_t warps = (size_t) fgrid * (HF_BLOCK / 32);
         static const int env_tail = getenv("HF_B200_TAIL") ? atoi(getenv("HF_B200_TAIL")) : -1;          // dev knobs: groups per resident warp
         static const int env_mid = getenv("HF_B200_MIDTAIL") ? atoi(getenv("HF_B200_MIDTAIL")) : -1;
-        const size_t tail = std::min(ngroups, warps * (size_t) (env_tail >= 0 ? env_tail : HF_FAST_TAIL));
-        const size_t mid = std::min(ngroups - tail, warps * (size_t) (env_mid >= 0 ? env_mid : HF_FAST_MIDTAIL));
+        // (with the adaptive schedule the ~100 us groups are no longer waiting in these phases: half as long is enough -- 1/8 of C3:
+        // 0.529 -> 0.521 ms; 12 / 12 and 4 / 8 are slower again)
+        const bool adapt = li.grp_cost && li.heavy_n && li.heavy_list && li.heavy_bits && li.cost_sum;
+        const size_t tail = std::min(ngroups, warps * (size_t) (env_tail >= 0 ? env_tail : adapt ? HF_FAST_TAIL / 2 : HF_FAST_TAIL));
+        const size_t mid = std::min(ngroups - tail, warps * (size_t) (env_mid >= 0 ? env_mid : adapt ? HF_FAST_MIDTAIL / 2 : HF_FAST_MIDTAIL));
         const unsigned long long nbig = (ngroups - tail - mid) / HF_FAST_GROUPS;
         const unsigned long long npair = (ngroups - tail - nbig * HF_FAST_GROUPS) / 2;
         unsigned long long *sched = d_sched;
         cudaError_t e = cudaMemsetAsync(sched, 0, sizeof(unsigned long long), s);
         if (e != cudaSuccess) return e;
+        if (adapt && (e = cudaMemsetAsync(li.cost_sum, 0, sizeof(unsigned long long), s)) != cudaSuccess) return e;
+        static const bool env_plain = getenv("HF_B200_AS_PLAIN_KERNEL") != nullptr;      // dev: the list is made but the plain kernel runs
+#define HF_FAST_LAUNCH(M) do { \
+            if (adapt && !env_plain) hf_intersect_fast_kernel<M, true><<<fgrid, HF_BLOCK, smem, s>>>(P, li, rays, prelim, si, d_hit, flags, n, nbig, npair, sched); \
+            else hf_intersect_fast_kernel<M, false><<<fgrid, HF_BLOCK, smem, s>>>(P, li, rays, prelim, si, d_hit, flags, n, nbig, npair, sched); } while (0)
         switch (mode) {
-            case HF_MODE_PRELIM:
-                hf_intersect_fast_kernel<HF_MODE_PRELIM><<<fgrid, HF_BLOCK, smem, s>>>(P, li, rays, prelim, si, d_hit, flags, n, nbig, npair, sched); break;
-            case HF_MODE_FUSED_SI_LEAN:
-                hf_intersect_fast_kernel<HF_MODE_FUSED_SI_LEAN><<<fgrid, HF_BLOCK, smem, s>>>(P, li, rays, prelim, si, d_hit, flags, n, nbig, npair, sched); break;
-            case HF_MODE_FUSED_SI:
-                hf_intersect_fast_kernel<HF_MODE_FUSED_SI><<<fgrid, HF_BLOCK, smem, s>>>(P, li, rays, prelim, si, d_hit, flags, n, nbig, npair, sched); break;
-            default:
-                hf_intersect_fast_kernel<HF_MODE_TEST><<<fgrid, HF_BLOCK, smem, s>>>(P, li, rays, prelim, si, d_hit, flags, n, nbig, npair, sched); break;
+            case HF_MODE_PRELIM: HF_FAST_LAUNCH(HF_MODE_PRELIM); break;
+            case HF_MODE_FUSED_SI_LEAN: HF_FAST_LAUNCH(HF_MODE_FUSED_SI_LEAN); break;
+            case HF_MODE_FUSED_SI: HF_FAST_LAUNCH(HF_MODE_FUSED_SI); break;
+            default: HF_FAST_LAUNCH(HF_MODE_TEST); break;
+        }
+#undef HF_FAST_LAUNCH
+        if (adapt) {                                 // the list for the next launch over a batch of this size
+            static const int env_factor = getenv("HF_B200_HEAVY_FACTOR") ? atoi(getenv("HF_B200_HEAVY_FACTOR")) : HF_HEAVY_FACTOR;    // dev knobs
+            static const int env_span = getenv("HF_B200_HEAVY_SPAN") ? atoi(getenv("HF_B200_HEAVY_SPAN")) : HF_HEAVY_SPAN;
+            if ((e = cudaMemsetAsync(li.heavy_n, 0, sizeof(unsigned), s)) != cudaSuccess) return e;
+            const unsigned blocks = (li.heavy_words * 32u + 255u) / 256u, capb = (unsigned) li.num_sms * 8u;
+            hf_pick_heavy_kernel<<<blocks < capb ? (blocks ? blocks : 1u) : capb, 256, 0, s>>>(li.grp_cost, (unsigned) ngroups, li.cost_sum, li.heavy_n, li.heavy_list,
+                                                                                              li.heavy_bits, li.heavy_words, li.heavy_cap,
+                                                                                              (unsigned) (env_factor > 0 ? env_factor : HF_HEAVY_FACTOR),
+                                                                                              (unsigned) (env_span > 0 ? env_span : HF_HEAVY_SPAN), (unsigned) warps);
         }
     }
     return cudaGetLastError();

@@ -18,6 +18,15 @@ struct HfLaunchInfo {
     int q_stage_level;       // lowest staged level (even), > QLtop: nothing staged
     int q_stage_bytes;       // shared memory they take (each level padded to 16 bytes)
     unsigned long long *seg_counter;   // ray segments traced by the path kernels (camera, bounce and visibility rays): hf_stats.segments
+    // Adaptive schedule of the per-ray kernel (hf_set_adaptive_schedule): every launch records what each 32-ray group cost, a small
+    // kernel behind it lists the groups far above the mean, and the NEXT launch over a batch of the same size starts with those.
+    // All null / 0 when the launch is not part of it.
+    uint16_t *grp_cost;                // out: cycles / 64 (saturating) of every group of this launch
+    unsigned long long *cost_sum;      // out: their sum
+    unsigned *heavy_n;                 // in: groups listed by the previous launch (a device scalar: graph replays follow it)
+    unsigned *heavy_list;              // in: their ids; out (pick kernel): the list for the next launch
+    uint32_t *heavy_bits;              // in: one bit per group, set for the listed ones (always rewritten as a whole, heavy_words words)
+    unsigned heavy_cap, heavy_words, heavy_shift;   // heavy_shift: (groups of the batch) >> heavy_shift <= 8192 (the kernel's coarse bitmap)
 };
 #ifndef HF_STAGE_Q
 #define HF_STAGE_Q 1

@@ -636,3 +636,61 @@ def test_pool_kernel_bit_identical(hf, oracle, H, W, xf, n):
     if m <= 200000:                                   # and the oracle, on the smaller cases
         pc = c.ray_intersect_preliminary(cr)
         assert _same_bits(_np(pi.t), pc.t).all()
+
+
+# ---- adaptive schedule (hf_set_adaptive_schedule): the order in which 32-ray groups are handed out must not show in any result ----
+def test_adaptive_schedule_bit_identical(hf):
+    """Launch k + 1 starts with the groups launch k found far above the mean cost and skips them in the natural order: every ray is
+    traced exactly once whatever the list holds -- plain launches, a CUDA graph replay, a smaller and a larger batch in between
+    (lists made for another batch size), the preliminary entry point, and with the hint switched off again."""
+    from hfb200 import workloads as wl
+    dev = torch.device("cuda", 0)
+    h = wl.fbm_heights(1024, octaves=8, seed=0xC2, device=dev)
+    g = hf.load_dict({"type": "heightfield", "heights": h, "max_height": 0.3}, device=dev)
+    cam = wl.CONFIGS["C3"]["camera"]                      # grazing enough for slope-skimming groups
+
+    def batch(img, spp):
+        o, d = wl.camera_rays(cam["origin"], cam["target"], cam["up"], cam["fov"], img, img, spp, seed=2, device=dev)
+        return hf.Ray3f(o, d, device=dev)
+
+    ray, small, large = batch(256, 16), batch(192, 16), batch(320, 16)         # 2^20 rays (32768 groups), 18432 and 51200 groups
+    want = {id(r): g.ray_intersect(r, return_prelim=True) for r in (ray, small, large)}
+
+    def same(r, got):
+        (wsi, wpi), (si, pi) = want[id(r)], got
+        assert torch.equal(pi.prim_index, wpi.prim_index)
+        assert torch.equal(pi.t.view(torch.int32), wpi.t.view(torch.int32)) and torch.equal(pi.prim_uv.view(torch.int32), wpi.prim_uv.view(torch.int32))
+        ws, gs = _si_dict(wsi), _si_dict(si)
+        for k in ws:
+            assert _same_bits(gs[k], ws[k]).all(), k
+
+    g.set_adaptive_schedule(True)
+    assert g.adaptive_schedule_info() == (0, 0)
+    listed = []
+    for _ in range(3):
+        same(ray, g.ray_intersect(ray, return_prelim=True))
+        listed.append(g.adaptive_schedule_info())
+    assert all(grp == 32768 for _, grp in listed) and listed[-1][0] > 0, listed        # something was learnt ...
+    assert listed[-1][0] < 32768 // 8, listed                                           # ... and it is a short list
+    pi = g.ray_intersect_preliminary(ray)
+    assert torch.equal(pi.prim_index, want[id(ray)][1].prim_index) and torch.equal(pi.t.view(torch.int32), want[id(ray)][1].t.view(torch.int32))
+    # a CUDA graph of the launch (the list is read and rewritten on the device: replays keep learning)
+    si_g = hf.SurfaceInteraction3f(len(ray), dev, g, ("t", "p", "n", "uv"))
+    pi_g = hf.PreliminaryIntersection3f(len(ray), dev, g)
+    replay = hf.capture(lambda: g.ray_intersect(ray, out=(si_g, pi_g)))
+    for _ in range(3):
+        si_g.t.fill_(-1); pi_g.prim_index.zero_()
+        replay()
+        torch.cuda.synchronize()
+        assert torch.equal(pi_g.prim_index, want[id(ray)][1].prim_index)
+        assert torch.equal(si_g.t.view(torch.int32), want[id(ray)][0].t.view(torch.int32))
+        assert torch.equal(si_g.n.view(torch.int32), want[id(ray)][0].n.view(torch.int32))
+    # other batch sizes in between: the list of the last batch does not fit them (ids beyond a smaller batch, a larger buffer needed)
+    for r in (small, ray, large, ray, small, small, large, large, ray):
+        same(r, g.ray_intersect(r, return_prelim=True))
+    replay()                                                  # recorded against the buffers that `large` has outgrown: still exact
+    torch.cuda.synchronize()
+    assert torch.equal(pi_g.prim_index, want[id(ray)][1].prim_index)
+    g.set_adaptive_schedule(False)
+    same(ray, g.ray_intersect(ray, return_prelim=True))
+    assert g.adaptive_schedule_info() == (0, 0)
