@@ -357,7 +357,7 @@ def main_ours(a):
         run_step()
     ms_total = timed(run_step, a.steps)
     ms_step = ms_total / a.steps
-    sched_info = shape.adaptive_schedule_info()
+    sched_info = shape.adaptive_schedule_info("rays")
     ms_allreduce = timed(shape.allreduce_grad, 10) / 10 if world > 1 else 0.0     # the collective alone (64 MiB fp32 at C3)
     collective = "none (1 GPU)" if world == 1 else "ncclAllReduce(grad 64 MiB fp32, sum) per step"
     peer = None
@@ -653,7 +653,8 @@ def run_render_step(a, shape, h, params, opt, rank, world, dev, timed, ev, peer=
                    ("reduce-scatter by peer stores + sharded Adam storing the heights into every rank's grid over NVLink" if peer else "allreduce + Adam") + " + pyramid rebuild",
            "collective": "peer memory: reduce-scatter -> sharded Adam -> all-gather of the heights" if peer else ("ncclAllReduce" if world > 1 else "none"), "ms_per_step": ms, "mrays": n_total / (ms * 1e-3) / 1e6, "launch": launch,
            "kernel_ms": kms, "kernel_ms_": kms, "kernel_mrays": n_total / world / (kms * 1e-3) / 1e6 * world,
-           "loss_first_step_local": loss0, "loss_last_step_local": loss1, "gpu_launches_per_step": 6}
+           "loss_first_step_local": loss0, "loss_last_step_local": loss1, "gpu_launches_per_step": 6,
+           "adaptive_schedule": dict(zip(("listed_pixels", "pixels"), shape.adaptive_schedule_info("pixels")))}
     if world == 1 and not a.no_e2e:
         out["e2e"] = run_render_e2e(a, shape, h, params, opt, cam, light, target, dev, timed, ms)
     return out

@@ -157,16 +157,18 @@ int hf_qpyramid_level(hf_ctx *ctx, uint32_t level, uint32_t *levels, uint32_t *p
  * its own ray and refills from a pool (5-18 % on intersect-only hemisphere rays, measured). Results are bit-identical either way. */
 int hf_set_ray_coherence(hf_ctx *ctx, int coherent);
 
-/* Adaptive schedule for hf_ray_intersect / hf_ray_intersect_preliminary on coherent batches of >= 2^19 rays (off by default). An
- * optimisation traces (nearly) the same rays every iteration: each launch records what every 32-ray group cost, and the next launch
- * over a batch of the same size hands out the groups far above the mean FIRST (rays that skim down a slope keep a warp ~50x longer
- * than the mean; at the end of a kernel such a group leaves the rest of the GPU idle). Results do not depend on the schedule. The
- * launches of a context that use it must be ordered with respect to each other (one stream, or one CUDA graph), like the
- * launches that scatter into its gradient grid. No reference counterpart (Dr.Jit sizes its launches per kernel,
- * ext/drjit/ext/drjit-core/src/cuda_eval.cpp). */
+/* Adaptive schedule (off by default) for the self-scheduling kernels behind hf_ray_intersect / hf_ray_intersect_preliminary (coherent
+ * batches, unit of work = a group of 32 rays) and behind the render steps below (unit = a pixel with >= 32 samples). An optimisation
+ * traces (nearly) the same rays every iteration: each launch records what every unit cost, and the next launch over a batch of the same
+ * size hands out the units far above the mean FIRST (rays that skim down a slope keep a warp ~50x longer than the mean; at the end of
+ * a kernel such a unit leaves the rest of the GPU idle). Only launches of 2^14 units or more and short enough for their end to matter
+ * (<= 320 units per resident warp) take part. Results do not depend on the schedule. The launches of a context that use it
+ * must be ordered with respect to each other (one stream, or one CUDA graph), like the launches that scatter into its gradient grid.
+ * No reference counterpart (Dr.Jit sizes its launches per kernel, ext/drjit/ext/drjit-core/src/cuda_eval.cpp). */
 int hf_set_adaptive_schedule(hf_ctx *ctx, int on);
-/* what the last such launch left for the next one: `listed` of its `groups` 32-ray groups go first (0 / 0: nothing learnt yet). Synchronises. */
-int hf_adaptive_schedule_info(hf_ctx *ctx, uint32_t *listed, uint32_t *groups);
+/* what the last such launch left for the next one: `listed` of its `units` go first (0 / 0: nothing learnt yet). kind 0: ray batches,
+ * kind 1: the pixel lists of the render steps. Synchronises. */
+int hf_adaptive_schedule_info(hf_ctx *ctx, int kind, uint32_t *listed, uint32_t *units);
 
 /* shape.h:137-138 ray_intersect_preliminary */
 int hf_ray_intersect_preliminary(hf_ctx *ctx, const hf_rays *rays, const hf_prelim *out, size_t n, void *stream);

@@ -137,7 +137,7 @@ def _load():
         "hf_set_grad_enabled": [vp, C.c_int],
         "hf_set_ray_coherence": [vp, C.c_int],
         "hf_set_adaptive_schedule": [vp, C.c_int],
-        "hf_adaptive_schedule_info": [vp, C.POINTER(u32), C.POINTER(u32)],
+        "hf_adaptive_schedule_info": [vp, C.c_int, C.POINTER(u32), C.POINTER(u32)],
         "hf_bbox": [vp, _f32p],
         "hf_primitive_count": [vp, C.POINTER(u32)],
         "hf_size": [vp, C.POINTER(u32), C.POINTER(u32)],
@@ -444,14 +444,15 @@ class Heightfield:
         _check(_load().hf_set_ray_coherence(self._ctx, int(bool(coherent))))
 
     def set_adaptive_schedule(self, on=True):
-        """include/hf_b200.h hf_set_adaptive_schedule: large coherent batches of the same size (the rays of an optimisation's iterations)
-        start with the 32-ray groups the previous launch found far more expensive than the mean. Results do not depend on it."""
+        """include/hf_b200.h hf_set_adaptive_schedule: launches over batches of the same size (the rays or pixels of an optimisation's
+        iterations) start with the units of work the previous launch found far more expensive than the mean. Results do not depend on it."""
         _check(_load().hf_set_adaptive_schedule(self._ctx, int(bool(on))))
 
-    def adaptive_schedule_info(self):
-        """(listed, groups): how many of the last large batch's 32-ray groups the next launch will start with"""
+    def adaptive_schedule_info(self, kind="rays"):
+        """(listed, units): how many of the last launch's units of work (kind "rays": 32-ray groups of a ray batch; "pixels": pixels of a
+        render step) the next launch will start with"""
         a, b = C.c_uint32(0), C.c_uint32(0)
-        _check(_load().hf_adaptive_schedule_info(self._ctx, C.byref(a), C.byref(b)))
+        _check(_load().hf_adaptive_schedule_info(self._ctx, {"rays": 0, "pixels": 1}[kind], C.byref(a), C.byref(b)))
         return int(a.value), int(b.value)
 
     def zero_grad(self):

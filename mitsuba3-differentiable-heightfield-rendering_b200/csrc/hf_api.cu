@@ -123,6 +123,21 @@ static_assert(sizeof(hf_prelim) == PRE_NFIELDS * sizeof(void *), "hf_prelim: 4 m
 #define SLAB_ACTIVE (SLAB_ADJ + ADJ_NFIELDS)
 #define HF_SLAB_FLOATS (SLAB_ACTIVE + 1)
 
+// adaptive schedule of one kind of launch (hf_set_adaptive_schedule): cost per unit of work of the last launch, the heavy list made from it
+struct HfAdaptive {
+    size_t cap = 0, units = 0;            // units the buffers hold / units of the batch the list was made from
+    uint16_t *d_cost = nullptr;
+    unsigned *d_list = nullptr, *d_n = nullptr;
+    uint32_t *d_bits = nullptr;
+    unsigned long long *d_sum = nullptr;
+    std::vector<void *> retired;          // outgrown buffers: CUDA graphs recorded earlier may still hold them
+    void release() {
+        cudaFree(d_cost); cudaFree(d_bits); cudaFree(d_list);
+        for (void *p : retired) cudaFree(p);
+        retired.clear(); d_cost = nullptr; d_bits = nullptr; d_list = nullptr; d_n = nullptr; d_sum = nullptr; cap = units = 0;
+    }
+};
+
 struct HostSlot {
     float *slab = nullptr;            // HF_HOST_CHUNK * HF_SLAB_FLOATS floats
     cudaEvent_t in_done = nullptr, k_done = nullptr, out_done = nullptr;   // H2D landed / kernels finished / D2H landed
@@ -173,12 +188,7 @@ struct hf_ctx {
     float **d_peer_stage_tab = nullptr;
     // adaptive schedule of the per-ray kernel (hf_set_adaptive_schedule): cost per 32-ray group of the last launch, the heavy list made from it
     int adaptive = 0;
-    size_t as_cap = 0, as_groups = 0;     // groups the buffers hold / groups of the batch the list was made from
-    uint16_t *d_as_cost = nullptr;
-    unsigned *d_as_list = nullptr, *d_as_n = nullptr;
-    uint32_t *d_as_bits = nullptr;
-    unsigned long long *d_as_sum = nullptr;
-    std::vector<void *> as_retired;       // outgrown buffers: CUDA graphs recorded earlier may still hold them
+    HfAdaptive as_rays, as_pixels;        // units = 32-ray groups of a ray batch / pixels of a pixel list (render step)
     // host-buffer render step: device copies of the caller's target / image / pixel list, and the loss
     float *d_hs_target = nullptr, *d_hs_image = nullptr;
     uint32_t *d_hs_pixels = nullptr;
@@ -233,50 +243,52 @@ static unsigned long long *next_sched(hf_ctx *c, cudaStream_t s) {
 #define SCHED(c, s) ({ unsigned long long *p_ = next_sched((c), (cudaStream_t) (s)); \
     if (!p_) return fail(HF_ERR_STATE, "this context has recorded more than %d self-scheduling launches into CUDA graphs", HF_SCHED_CAPTURE_SLOTS); p_; })
 
-// Launch info of one per-ray launch over n rays: c->li plus, when the adaptive schedule is on and the batch is large, its buffers.
-// A batch of another size than the last one starts without a list (and makes the next one); while a CUDA graph is being recorded
-// nothing may be allocated or reset behind the stream's back, so such a launch simply runs the plain schedule.
-#define HF_AS_MIN_GROUPS 16384u
-#define HF_AS_MAX_GROUPS_PER_WARP 320    // of the 24 resident warps per SM
+// Launch info of one self-scheduling launch over `units` units of work (32-ray groups, pixels): c->li plus, when the adaptive schedule
+// is on and the launch is of the right size, its buffers. A batch of another size than the last one starts without a list (and
+// makes the next one); while a CUDA graph is being recorded nothing may be allocated or reset behind the stream's back, so such a
+// launch simply runs the plain schedule.
+#define HF_AS_MIN_UNITS 16384u
 #define HF_AS_LIST_CAP 4096u
-static HfLaunchInfo launch_info_for(hf_ctx *c, size_t n, cudaStream_t s) {
+#define HF_AS_MAX_UNITS_PER_WARP 320     // of the 24 resident warps per SM
+static HfLaunchInfo adaptive_launch_info(hf_ctx *c, HfAdaptive &A, size_t units, cudaStream_t s) {
     HfLaunchInfo li = c->li;
-    const size_t ngroups = (n + 31) / 32;
-    if (!c->adaptive || li.incoherent || li.use_bundles || ngroups < HF_AS_MIN_GROUPS) return li;
-    // The closing phase of a launch weighs ~1 / (groups per resident warp); keeping the books costs the kernel ~1 % whatever its
-    // length. Measured on C3 (profiles/r02_notes.md): 1/8 of the batch (74 groups per warp) -11 %, 1/4 -5 %, 1/2 (295) -1.5 %, the
+    if (!c->adaptive || li.incoherent || li.use_bundles || units < HF_AS_MIN_UNITS) return li;
+    // The closing phase of a launch weighs ~1 / (units per resident warp); keeping the books costs the kernel ~1 % whatever its
+    // length. Measured on C3 (profiles/r02_notes.md): 1/8 of the ray batch (74 groups per warp) -11 %, 1/4 -5 %, 1/2 (295) -1.5 %, the
     // whole batch (590) +1 %. So: only launches short enough for the end to matter.
-    static const int env_gpw = getenv("HF_B200_AS_MAX_GPW") ? atoi(getenv("HF_B200_AS_MAX_GPW")) : HF_AS_MAX_GROUPS_PER_WARP;     // dev knob
-    if (ngroups > (size_t) c->num_sms * 24 * (size_t) (env_gpw > 0 ? env_gpw : HF_AS_MAX_GROUPS_PER_WARP) || ngroups >= (size_t(1) << 31)) return li;
+    static const int env_upw = getenv("HF_B200_AS_MAX_UPW") ? atoi(getenv("HF_B200_AS_MAX_UPW")) : HF_AS_MAX_UNITS_PER_WARP;     // dev knob
+    if (units > (size_t) c->num_sms * 24 * (size_t) (env_upw > 0 ? env_upw : HF_AS_MAX_UNITS_PER_WARP) || units >= (size_t(1) << 31)) return li;
     cudaStreamCaptureStatus st = cudaStreamCaptureStatusNone;
     if (cudaStreamIsCapturing(s, &st) != cudaSuccess) { cudaGetLastError(); st = cudaStreamCaptureStatusNone; }
     const bool capturing = st == cudaStreamCaptureStatusActive;
-    if (ngroups > c->as_cap) {
+    if (units > A.cap) {
         if (capturing) return li;
-        const size_t cap = (ngroups + 1023) & ~size_t(1023);
+        const size_t cap = (units + 1023) & ~size_t(1023);
         uint16_t *cost = nullptr; unsigned *list = nullptr; uint32_t *bits = nullptr;
         if (cudaMalloc(&cost, cap * sizeof(uint16_t)) != cudaSuccess || cudaMalloc(&bits, cap / 32 * sizeof(uint32_t)) != cudaSuccess ||
             cudaMalloc(&list, (HF_AS_LIST_CAP + 4) * sizeof(unsigned)) != cudaSuccess) {
             cudaGetLastError(); cudaFree(cost); cudaFree(bits); cudaFree(list);
             return li;                                   // a schedule hint must not fail a launch
         }
-        if (c->d_as_cost) { c->as_retired.push_back(c->d_as_cost); c->as_retired.push_back(c->d_as_bits); c->as_retired.push_back(c->d_as_list); }
-        c->d_as_cost = cost; c->d_as_bits = bits; c->d_as_list = list;
-        c->d_as_n = list + HF_AS_LIST_CAP;               // the count and the cost sum live behind the list
-        c->d_as_sum = reinterpret_cast<unsigned long long *>(list + HF_AS_LIST_CAP + 2);
-        c->as_cap = cap; c->as_groups = 0;
+        if (A.d_cost) { A.retired.push_back(A.d_cost); A.retired.push_back(A.d_bits); A.retired.push_back(A.d_list); }
+        A.d_cost = cost; A.d_bits = bits; A.d_list = list;
+        A.d_n = list + HF_AS_LIST_CAP;                   // the count and the cost sum live behind the list
+        A.d_sum = reinterpret_cast<unsigned long long *>(list + HF_AS_LIST_CAP + 2);
+        A.cap = cap; A.units = 0;
     }
-    if (c->as_groups != ngroups) {
+    if (A.units != units) {
         if (capturing) return li;
-        if (cudaMemsetAsync(c->d_as_n, 0, sizeof(unsigned), s) != cudaSuccess) { cudaGetLastError(); return li; }
-        c->as_groups = ngroups;
+        if (cudaMemsetAsync(A.d_n, 0, sizeof(unsigned), s) != cudaSuccess) { cudaGetLastError(); return li; }
+        A.units = units;
     }
-    li.grp_cost = c->d_as_cost; li.cost_sum = c->d_as_sum; li.heavy_n = c->d_as_n; li.heavy_list = c->d_as_list; li.heavy_bits = c->d_as_bits;
-    li.heavy_cap = HF_AS_LIST_CAP; li.heavy_words = (unsigned) (c->as_cap / 32);
+    li.grp_cost = A.d_cost; li.cost_sum = A.d_sum; li.heavy_n = A.d_n; li.heavy_list = A.d_list; li.heavy_bits = A.d_bits;
+    li.heavy_cap = HF_AS_LIST_CAP; li.heavy_words = (unsigned) (A.cap / 32);
     li.heavy_shift = 0;
-    while (((ngroups - 1) >> li.heavy_shift) >= 8192) li.heavy_shift++;
+    while (((units - 1) >> li.heavy_shift) >= 8192) li.heavy_shift++;
     return li;
 }
+static inline HfLaunchInfo launch_info_for(hf_ctx *c, size_t n, cudaStream_t s) { return adaptive_launch_info(c, c->as_rays, (n + 31) / 32, s); }
+static inline HfLaunchInfo launch_info_for_pixels(hf_ctx *c, size_t npix, cudaStream_t s) { return adaptive_launch_info(c, c->as_pixels, npix, s); }
 
 static void layout_pyramid(hf_ctx *c) {
     HfParams &P = c->P;
@@ -405,8 +417,7 @@ extern "C" int hf_destroy(hf_ctx *c) {
     if (c->s_in) cudaStreamDestroy(c->s_in);
     if (c->s_k) cudaStreamDestroy(c->s_k);
     if (c->s_out) cudaStreamDestroy(c->s_out);
-    cudaFree(c->d_as_cost); cudaFree(c->d_as_bits); cudaFree(c->d_as_list);
-    for (void *p : c->as_retired) cudaFree(p);
+    c->as_rays.release(); c->as_pixels.release();
     cudaFree(c->d_heights); cudaFree(c->d_grad); cudaFree(c->d_m); cudaFree(c->d_v); cudaFree(c->d_pyr); cudaFree(c->d_qpyr); cudaFree(c->d_counters); cudaFree(c->d_scratch);
     cudaFree(c->d_adam_t); cudaFree(c->d_adam_lr_t); cudaFree(c->d_adam_table);
     cudaFree(c->d_hs_target); cudaFree(c->d_hs_image); cudaFree(c->d_hs_pixels); cudaFree(c->d_hs_loss);
@@ -489,21 +500,23 @@ extern "C" int hf_set_ray_coherence(hf_ctx *c, int coherent) {
 extern "C" int hf_set_adaptive_schedule(hf_ctx *c, int on) {
     CHECK_CTX(c);
     c->adaptive = on ? 1 : 0;
-    c->as_groups = 0;                 // whatever was learnt is forgotten: the next large batch starts a new list
+    c->as_rays.units = c->as_pixels.units = 0;       // whatever was learnt is forgotten: the next launches start new lists
     return HF_OK;
 }
 
-extern "C" int hf_adaptive_schedule_info(hf_ctx *c, uint32_t *listed, uint32_t *groups) {
+extern "C" int hf_adaptive_schedule_info(hf_ctx *c, int kind, uint32_t *listed, uint32_t *groups) {
     CHECK_CTX(c);
+    if (kind != 0 && kind != 1) return fail(HF_ERR_INVALID, "hf_adaptive_schedule_info: kind 0 (ray batches) or 1 (pixel lists of the render step)");
     unsigned n = 0;
-    if (c->adaptive && c->d_as_n && c->as_groups) {
+    const HfAdaptive &A = kind == 1 ? c->as_pixels : c->as_rays;
+    if (c->adaptive && A.d_n && A.units) {
         CU(cudaSetDevice(c->device));
         CU(cudaDeviceSynchronize());
-        CU(cudaMemcpy(&n, c->d_as_n, sizeof(n), cudaMemcpyDeviceToHost));
+        CU(cudaMemcpy(&n, A.d_n, sizeof(n), cudaMemcpyDeviceToHost));
         if (n > HF_AS_LIST_CAP) n = HF_AS_LIST_CAP;
     }
     if (listed) *listed = n;
-    if (groups) *groups = c->adaptive ? (uint32_t) c->as_groups : 0u;
+    if (groups) *groups = c->adaptive ? (uint32_t) A.units : 0u;
     return HF_OK;
 }
 
@@ -1111,7 +1124,7 @@ extern "C" int hf_render_forward(hf_ctx *c, const hf_camera *cam, const hf_light
     if (d_prim && light->max_depth > 1) return fail(HF_ERR_INVALID, "hit triangles are only stored for max_depth <= 1 (paths are replayed)");
     NEED_ACCEL(c);
     CU(cudaSetDevice(c->device));
-    CU(hf_launch_render(c->P, c->li, 0, *cam, *light, d_pixels, npix, d_image, d_prim, nullptr, nullptr, nullptr, nullptr,
+    CU(hf_launch_render(c->P, launch_info_for_pixels(c, npix, (cudaStream_t) stream), 0, *cam, *light, d_pixels, npix, d_image, d_prim, nullptr, nullptr, nullptr, nullptr,
                         SCHED(c, stream), (cudaStream_t) stream));
     return HF_OK;
 }
@@ -1131,7 +1144,7 @@ extern "C" int hf_render_backward(hf_ctx *c, const hf_camera *cam, const hf_ligh
         CU(hf_launch_render_backward_prim(c->P, c->li, *cam, *light, d_pixels, npix, d_adj_image, d_prim, c->d_grad, (cudaStream_t) stream));
     } else {
         NEED_ACCEL(c);
-        CU(hf_launch_render(c->P, c->li, 2, *cam, *light, d_pixels, npix, nullptr, nullptr, nullptr, d_adj_image, c->d_grad, nullptr,
+        CU(hf_launch_render(c->P, launch_info_for_pixels(c, npix, (cudaStream_t) stream), 2, *cam, *light, d_pixels, npix, nullptr, nullptr, nullptr, d_adj_image, c->d_grad, nullptr,
                             SCHED(c, stream), (cudaStream_t) stream));
     }
     return HF_OK;
@@ -1164,7 +1177,7 @@ extern "C" int hf_render_step_l2(hf_ctx *c, const hf_camera *cam, const hf_light
             CU(hf_launch_render(c->P, c->li, 2, *cam, *light, d_pixels, npix, nullptr, nullptr, nullptr, adj, c->d_grad, nullptr, SCHED(c, st), st));
         return HF_OK;
     }
-    CU(hf_launch_render(c->P, c->li, 1, *cam, *light, d_pixels, npix, d_image, nullptr, d_target, nullptr, c->d_grad, d_loss,
+    CU(hf_launch_render(c->P, launch_info_for_pixels(c, npix, (cudaStream_t) stream), 1, *cam, *light, d_pixels, npix, d_image, nullptr, d_target, nullptr, c->d_grad, d_loss,
                         SCHED(c, stream), (cudaStream_t) stream));
     return HF_OK;
 }

@@ -1076,6 +1076,18 @@ static inline int hf_grid_for(size_t n, int num_sms, int ctas_per_sm) {
     return (int) (ntiles < cap ? (ntiles ? ntiles : 1) : cap);
 }
 
+cudaError_t hf_launch_pick_heavy(const HfLaunchInfo &li, unsigned units, unsigned resident_warps, cudaStream_t s) {
+    static const int env_factor = getenv("HF_B200_HEAVY_FACTOR") ? atoi(getenv("HF_B200_HEAVY_FACTOR")) : HF_HEAVY_FACTOR;    // dev knobs
+    static const int env_span = getenv("HF_B200_HEAVY_SPAN") ? atoi(getenv("HF_B200_HEAVY_SPAN")) : HF_HEAVY_SPAN;
+    cudaError_t e = cudaMemsetAsync(li.heavy_n, 0, sizeof(unsigned), s);
+    if (e != cudaSuccess) return e;
+    const unsigned blocks = (li.heavy_words * 32u + 255u) / 256u, capb = (unsigned) li.num_sms * 8u;
+    hf_pick_heavy_kernel<<<blocks < capb ? (blocks ? blocks : 1u) : capb, 256, 0, s>>>(li.grp_cost, units, li.cost_sum, li.heavy_n, li.heavy_list, li.heavy_bits,
+                                                                                      li.heavy_words, li.heavy_cap, (unsigned) (env_factor > 0 ? env_factor : HF_HEAVY_FACTOR),
+                                                                                      (unsigned) (env_span > 0 ? env_span : HF_HEAVY_SPAN), resident_warps ? resident_warps : 1u);
+    return cudaGetLastError();
+}
+
 cudaError_t hf_launch_intersect(const HfParams &P, const HfLaunchInfo &li, int mode, const hf_rays &rays,
                                 const hf_prelim &prelim, const hf_si &si, uint8_t *d_hit, uint32_t flags,
                                 size_t n, unsigned long long *d_counters, unsigned long long *d_sched, cudaStream_t s) {
@@ -1178,14 +1190,8 @@ cudaError_t hf_launch_intersect(const HfParams &P, const HfLaunchInfo &li, int m
         }
 #undef HF_FAST_LAUNCH
         if (adapt) {                                 // the list for the next launch over a batch of this size
-            static const int env_factor = getenv("HF_B200_HEAVY_FACTOR") ? atoi(getenv("HF_B200_HEAVY_FACTOR")) : HF_HEAVY_FACTOR;    // dev knobs
-            static const int env_span = getenv("HF_B200_HEAVY_SPAN") ? atoi(getenv("HF_B200_HEAVY_SPAN")) : HF_HEAVY_SPAN;
-            if ((e = cudaMemsetAsync(li.heavy_n, 0, sizeof(unsigned), s)) != cudaSuccess) return e;
-            const unsigned blocks = (li.heavy_words * 32u + 255u) / 256u, capb = (unsigned) li.num_sms * 8u;
-            hf_pick_heavy_kernel<<<blocks < capb ? (blocks ? blocks : 1u) : capb, 256, 0, s>>>(li.grp_cost, (unsigned) ngroups, li.cost_sum, li.heavy_n, li.heavy_list,
-                                                                                              li.heavy_bits, li.heavy_words, li.heavy_cap,
-                                                                                              (unsigned) (env_factor > 0 ? env_factor : HF_HEAVY_FACTOR),
-                                                                                              (unsigned) (env_span > 0 ? env_span : HF_HEAVY_SPAN), (unsigned) warps);
+            if ((e = cudaGetLastError()) != cudaSuccess) return e;
+            return hf_launch_pick_heavy(li, (unsigned) ngroups, (unsigned) warps, s);
         }
     }
     return cudaGetLastError();

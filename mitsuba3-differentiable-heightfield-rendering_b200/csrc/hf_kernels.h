@@ -38,6 +38,8 @@ struct HfLaunchInfo {
 enum HfIntersectMode { HF_MODE_PRELIM = 0, HF_MODE_FUSED_SI = 1, HF_MODE_TEST = 2, HF_MODE_COUNTED = 3,
                        HF_MODE_FUSED_SI_LEAN = 4 };   // internal: FUSED_SI when only t, p, n, uv are requested (chosen by hf_launch_intersect)
 
+// adaptive schedule: the heavy list for the next launch from the unit costs this launch has recorded (li.grp_cost etc. must be set)
+cudaError_t hf_launch_pick_heavy(const HfLaunchInfo &li, unsigned units, unsigned resident_warps, cudaStream_t s);
 cudaError_t hf_launch_pyramid(const HfParams &P, float2 *pyr, uint32_t *qpyr, cudaStream_t s);
 cudaError_t hf_launch_intersect(const HfParams &P, const HfLaunchInfo &li, int mode, const hf_rays &rays,
                                 const hf_prelim &prelim, const hf_si &si, uint8_t *d_hit, uint32_t flags,

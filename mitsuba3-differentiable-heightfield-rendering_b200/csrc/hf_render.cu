@@ -338,15 +338,31 @@ __device__ __forceinline__ HfBeam hf_pixel_bundle(const HfParams &P, const HfRen
 enum { HF_RENDER_FWD = 0, HF_RENDER_STEP_L2 = 1, HF_RENDER_BWD = 2 };
 
 // LOW: the image has fewer than 32 spp (several pixels per round, tiles of up to 32 pixels); otherwise the packing is constant-folded
-template <int MODE, bool LOW>
+// ADAPT (>= 32 spp only; hf_set_adaptive_schedule, see hf_intersect_fast_kernel): the pixels the previous launch found far more
+// expensive than the rest go out first, one per fetch, and are skipped when their turn comes in the natural order.
+template <int MODE, bool LOW, bool ADAPT>
 __global__ void __launch_bounds__(HF_BLOCK, 3)
 hf_render_kernel(const __grid_constant__ HfParams P, const HfLaunchInfo li, const __grid_constant__ HfRenderArgs A,
                  float *__restrict__ image, uint32_t *__restrict__ prim_out, const float *__restrict__ target,
                  const float *__restrict__ adj_image, float *__restrict__ grad, double *__restrict__ loss,
                  unsigned long long *__restrict__ sched) {
+    static_assert(!(ADAPT && LOW), "the adaptive schedule's unit is one pixel per round");
     __shared__ uint32_t s_prim[HF_BLOCK / 32][HF_RENDER_MAX_SPP];
+    __shared__ unsigned s_nheavy, s_c0[HF_BLOCK / 32], s_begin[HF_BLOCK / 32], s_skip[HF_BLOCK / 32];
+    __shared__ uint32_t s_coarse[256];          // one bit per 2^heavy_shift pixel positions: clear = no listed pixel there, no global lookup
+    unsigned nheavy = 0u;
+    if (ADAPT) {
+        nheavy = min(*li.heavy_n, li.heavy_cap);
+        s_coarse[threadIdx.x & 255u] = 0u;
+        __syncthreads();
+        for (unsigned k = threadIdx.x; k < nheavy; k += HF_BLOCK) {
+            const unsigned b = (li.heavy_list[k] >> li.heavy_shift) & 8191u;
+            atomicOr(&s_coarse[b >> 5], 1u << (b & 31u));
+        }
+        if (threadIdx.x == 0) s_nheavy = nheavy;
+    }
     HfGrid G;
-    hf_stage_pyramid<true>(P, li, G);
+    hf_stage_pyramid<true>(P, li, G);           // (ends with a CTA barrier)
 
     const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
     const uint32_t spp = A.cam.spp;
@@ -366,6 +382,7 @@ hf_render_kernel(const __grid_constant__ HfParams P, const HfLaunchInfo li, cons
     const size_t nbig = (A.npix - tailpx - midpx) / u4, rest0 = nbig * u4;
     const size_t npair = (A.npix - tailpx - rest0) / u2, rest1 = rest0 + npair * u2;
     double loss_acc = 0.0;
+    if (ADAPT && lane == 0) s_c0[warp] = s_begin[warp] = (unsigned) clock();
 
     for (;;) {
         unsigned long long tile = 0;
@@ -373,17 +390,34 @@ hf_render_kernel(const __grid_constant__ HfParams P, const HfLaunchInfo li, cons
         tile = __shfl_sync(FULL_MASK, tile, 0);
         size_t k0;
         unsigned cap;
-        if (tile < nbig) { k0 = (size_t) tile * u4; cap = u4; }
-        else if (tile < nbig + npair) { k0 = rest0 + (size_t) (tile - nbig) * u2; cap = u2; }
-        else { k0 = rest1 + (size_t) (tile - nbig - npair) * u1; cap = u1; }
-        if (k0 >= A.npix) break;
+        if (ADAPT && lane == 0) s_skip[warp] = 0u;         // pixels of this tile that went out first (bit j); (the shuffle above has gathered the warp)
+        if (ADAPT && tile < s_nheavy) {
+            k0 = li.heavy_list[tile]; cap = 1u;
+            if (k0 >= A.npix) continue;         // a list made for a longer pixel list of this context
+        } else {
+            if (ADAPT) tile -= s_nheavy;
+            if (tile < nbig) { k0 = (size_t) tile * u4; cap = u4; }
+            else if (tile < nbig + npair) { k0 = rest0 + (size_t) (tile - nbig) * u2; cap = u2; }
+            else { k0 = rest1 + (size_t) (tile - nbig - npair) * u1; cap = u1; }
+            if (k0 >= A.npix) break;
+            if (ADAPT && s_nheavy) {
+                unsigned skip = 0u;
+                for (unsigned j = 0; j < cap; ++j) {
+                    const unsigned k = (unsigned) k0 + j, b = (k >> li.heavy_shift) & 8191u;
+                    if (k < A.npix && ((s_coarse[b >> 5] >> (b & 31u)) & 1u) && ((li.heavy_bits[k >> 5] >> (k & 31u)) & 1u)) skip |= 1u << j;
+                }
+                if (skip == (1u << cap) - 1u) continue;
+                if (lane == 0) s_skip[warp] = skip;
+            }
+        }
+        if (ADAPT) __syncwarp();
         // ---- phase B: all 32 lanes march: lane = pixel * nsub + sub-rectangle of the pixel's jitter square (sub_x x sub_y; 8 bundles
         // per pixel when the tile has <= 4 pixels, 4 / 2 / 1 for 8 / 16 / 32 pixels). A narrower bundle is marched further down the
         // pyramid, so its samples start their own walks closer to the surface.
         const unsigned nsub = LOW ? min(8u, 32u / cap) : 8u, sub_x = nsub == 8u ? 4u : (nsub >= 2u ? 2u : 1u), sub_y = nsub / sub_x;
         const float rsx = 1.f / (float) sub_x, rsy = 1.f / (float) sub_y;      // 1, 1/2, 1/4: exact
         const size_t kq = k0 + lane / nsub;
-        const bool have = lane / nsub < cap && kq < A.npix;
+        const bool have = lane / nsub < cap && kq < A.npix && !(ADAPT && ((s_skip[warp] >> (lane / nsub)) & 1u));
         const uint32_t my_pid = have ? (A.pixels ? __ldg(A.pixels + kq) : (uint32_t) kq) : 0u;
         float t_enter = 0.f;
         int L_start = HF_START_LEVEL;
@@ -399,6 +433,7 @@ hf_render_kernel(const __grid_constant__ HfParams P, const HfLaunchInfo li, cons
         // of two), 32 / seg pixels at a time, so that a 1 / 2 / 4 / 8 / 16 spp image still fills the warp
         const unsigned npx = (unsigned) min((size_t) cap, A.npix - k0);
         for (unsigned j0 = 0; j0 < npx; j0 += ppr) {
+            if (ADAPT && ((s_skip[warp] >> j0) & 1u)) continue;
             const unsigned j = j0 + lane / seg;
             const bool pix_ok = j < npx;
             const unsigned jj = pix_ok ? j : j0;
@@ -437,6 +472,11 @@ hf_render_kernel(const __grid_constant__ HfParams P, const HfLaunchInfo li, cons
             const bool lead = pix_ok && sl == 0u;                                // one lane per pixel reports it
             if (MODE == HF_RENDER_FWD) {
                 if (lead) image[pid] = I;
+                if (ADAPT && lane == 0) {
+                    const unsigned now = (unsigned) clock();
+                    li.grp_cost[k0 + j0] = (uint16_t) min((now - s_c0[warp]) >> 6, 65535u);
+                    s_c0[warp] = now;
+                }
                 continue;
             }
             float a_v;                                     // adjoint of ONE sample value of this lane's pixel
@@ -469,8 +509,14 @@ hf_render_kernel(const __grid_constant__ HfParams P, const HfLaunchInfo li, cons
                 }
             }
             __syncwarp();
+            if (ADAPT && lane == 0) {            // the pixel's cost: the time since this warp finished the pixel before it
+                const unsigned now = (unsigned) clock();
+                li.grp_cost[k0 + j0] = (uint16_t) min((now - s_c0[warp]) >> 6, 65535u);
+                s_c0[warp] = now;
+            }
         }
     }
+    if (ADAPT && lane == 0) atomicAdd(li.cost_sum, (unsigned long long) (((unsigned) clock() - s_begin[warp]) >> 6));
     if (MODE == HF_RENDER_STEP_L2 && loss && loss_acc != 0.0) atomicAdd(loss, loss_acc * (double) A.inv_npix);
 }
 
@@ -691,7 +737,7 @@ cudaError_t hf_launch_render(const HfParams &P, const HfLaunchInfo &li, int mode
                              const uint32_t *d_pixels, size_t npix, float *d_image, uint32_t *d_prim, const float *d_target,
                              const float *d_adj_image, float *d_grad, double *d_loss, unsigned long long *d_sched, cudaStream_t s) {
     if (npix == 0) return cudaSuccess;
-    const HfRenderArgs A = hf_render_args(P, cam, &light, d_pixels, npix);
+    HfRenderArgs A = hf_render_args(P, cam, &light, d_pixels, npix);
     cudaError_t e = cudaMemsetAsync(d_sched, 0, sizeof(unsigned long long), s);
     if (e != cudaSuccess) return e;
     const size_t smem = hf_walk_smem(li, true);
@@ -707,17 +753,25 @@ cudaError_t hf_launch_render(const HfParams &P, const HfLaunchInfo &li, int mode
         return cudaGetLastError();
     }
     const bool low = cam.spp < 32u;
-    if (mode == HF_RENDER_FWD) {
-        if (low) hf_render_kernel<HF_RENDER_FWD, true><<<grid, HF_BLOCK, smem, s>>>(P, li, A, d_image, d_prim, nullptr, nullptr, nullptr, nullptr, d_sched);
-        else hf_render_kernel<HF_RENDER_FWD, false><<<grid, HF_BLOCK, smem, s>>>(P, li, A, d_image, d_prim, nullptr, nullptr, nullptr, nullptr, d_sched);
-    } else if (mode == HF_RENDER_STEP_L2) {
-        if (low) hf_render_kernel<HF_RENDER_STEP_L2, true><<<grid, HF_BLOCK, smem, s>>>(P, li, A, d_image, nullptr, d_target, nullptr, d_grad, d_loss, d_sched);
-        else hf_render_kernel<HF_RENDER_STEP_L2, false><<<grid, HF_BLOCK, smem, s>>>(P, li, A, d_image, nullptr, d_target, nullptr, d_grad, d_loss, d_sched);
-    } else {
-        if (low) hf_render_kernel<HF_RENDER_BWD, true><<<grid, HF_BLOCK, smem, s>>>(P, li, A, nullptr, nullptr, nullptr, d_adj_image, d_grad, nullptr, d_sched);
-        else hf_render_kernel<HF_RENDER_BWD, false><<<grid, HF_BLOCK, smem, s>>>(P, li, A, nullptr, nullptr, nullptr, d_adj_image, d_grad, nullptr, d_sched);
+    const bool adapt = !low && li.grp_cost && li.heavy_n && li.heavy_list && li.heavy_bits && li.cost_sum;
+    if (adapt && (e = cudaMemsetAsync(li.cost_sum, 0, sizeof(unsigned long long), s)) != cudaSuccess) return e;
+    if (adapt) {
+        // the ~0.2 ms pixels are no longer waiting in the closing phases: a quarter / half of their length is enough, and more pixels
+        // go out in tiles of four (1/8 of C3 on one GPU: kernel 0.70 -> 0.64 ms; 2 / 6 and 12 / 12 are slower again)
+        if (!getenv("HF_B200_RTAIL")) A.tail = HF_RENDER_TAIL / 4;
+        if (!getenv("HF_B200_RMIDTAIL")) A.midtail = HF_RENDER_MIDTAIL / 2;
     }
-    return cudaGetLastError();
+#define HF_RENDER_LAUNCH(M, ...) do { \
+        if (low) hf_render_kernel<M, true, false><<<grid, HF_BLOCK, smem, s>>>(P, li, A, __VA_ARGS__, d_sched); \
+        else if (adapt) hf_render_kernel<M, false, true><<<grid, HF_BLOCK, smem, s>>>(P, li, A, __VA_ARGS__, d_sched); \
+        else hf_render_kernel<M, false, false><<<grid, HF_BLOCK, smem, s>>>(P, li, A, __VA_ARGS__, d_sched); } while (0)
+    if (mode == HF_RENDER_FWD) HF_RENDER_LAUNCH(HF_RENDER_FWD, d_image, d_prim, nullptr, nullptr, nullptr, nullptr);
+    else if (mode == HF_RENDER_STEP_L2) HF_RENDER_LAUNCH(HF_RENDER_STEP_L2, d_image, nullptr, d_target, nullptr, d_grad, d_loss);
+    else HF_RENDER_LAUNCH(HF_RENDER_BWD, nullptr, nullptr, nullptr, d_adj_image, d_grad, nullptr);
+#undef HF_RENDER_LAUNCH
+    if ((e = cudaGetLastError()) != cudaSuccess) return e;
+    if (adapt) e = hf_launch_pick_heavy(li, (unsigned) npix, (unsigned) grid * (HF_BLOCK / 32), s);       // the list for the next launch over a list of this length
+    return e;
 }
 
 cudaError_t hf_launch_render_backward_prim(const HfParams &P, const HfLaunchInfo &li, const hf_camera &cam, const hf_light &light,

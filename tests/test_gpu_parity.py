@@ -665,11 +665,11 @@ def test_adaptive_schedule_bit_identical(hf):
             assert _same_bits(gs[k], ws[k]).all(), k
 
     g.set_adaptive_schedule(True)
-    assert g.adaptive_schedule_info() == (0, 0)
+    assert g.adaptive_schedule_info("rays") == (0, 0)
     listed = []
     for _ in range(3):
         same(ray, g.ray_intersect(ray, return_prelim=True))
-        listed.append(g.adaptive_schedule_info())
+        listed.append(g.adaptive_schedule_info("rays"))
     assert all(grp == 32768 for _, grp in listed) and listed[-1][0] > 0, listed        # something was learnt ...
     assert listed[-1][0] < 32768 // 8, listed                                           # ... and it is a short list
     pi = g.ray_intersect_preliminary(ray)
@@ -693,4 +693,4 @@ def test_adaptive_schedule_bit_identical(hf):
     assert torch.equal(pi_g.prim_index, want[id(ray)][1].prim_index)
     g.set_adaptive_schedule(False)
     same(ray, g.ray_intersect(ray, return_prelim=True))
-    assert g.adaptive_schedule_info() == (0, 0)
+    assert g.adaptive_schedule_info("rays") == (0, 0)

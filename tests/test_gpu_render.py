@@ -249,3 +249,42 @@ def test_host_render_step_matches_device_step(hf, oracle):
             assert torch.equal(h_img.view(torch.int32), want_img.view(torch.int32))
             assert abs(got_loss - want_loss) <= 1e-12 + 1e-9 * abs(want_loss)
             assert float((h_grad - want_grad).double().norm() / want_grad.double().norm()) < 1e-5
+
+
+def test_render_step_under_the_adaptive_schedule(hf):
+    """hf_set_adaptive_schedule for pixel lists (unit of work = a pixel with >= 32 samples): forward image and hit triangles identical, the
+    fused L2 step's image identical and its gradient equal up to the order of the atomic additions, launch after launch (the list
+    of expensive pixels changes between them) and through a pixel list."""
+    from hfb200 import workloads as wl
+    dev = torch.device("cuda", 0)
+    h = wl.fbm_heights(1024, octaves=8, seed=0xC2, device=dev)
+    g = hf.load_dict({"type": "heightfield", "heights": h, "max_height": 0.3}, device=dev)
+    c3 = wl.CONFIGS["C3"]["camera"]
+    cam = hf.perspective_camera(c3["origin"], c3["target"], c3["up"], c3["fov"], 320, 256, 64, seed=4)       # 81920 pixels
+    light = hf.directional_light((0.3, 0.2, 1.0), shadow_rays=True)
+    target = torch.zeros(256, 320, device=dev)
+    rng = np.random.default_rng(9)
+    some = rng.permutation(320 * 256)[:60000].astype(np.int32)
+
+    def step(pixels):
+        img = torch.full((256, 320), -1.0, device=dev)
+        loss = torch.zeros(1, dtype=torch.float64, device=dev)
+        g.zero_grad(); g.render_step_l2(cam, light, target, pixels, image=img, loss=loss)
+        torch.cuda.synchronize()
+        return img.clone(), g.grad.double().clone(), float(loss)
+
+    want = {k: step(p) for k, p in (("all", None), ("some", some))}
+    want_img, want_prim = g.render_forward(cam, light, return_prims=True)
+    g.set_adaptive_schedule(True)
+    for it in range(3):
+        for k, p in (("all", None), ("all", None), ("some", some), ("all", None)):
+            img, grad, loss = step(p)
+            assert torch.equal(img.view(torch.int32), want[k][0].view(torch.int32)), (it, k)
+            assert float((grad - want[k][1]).norm() / want[k][1].norm()) < 1e-5
+            assert abs(loss - want[k][2]) <= 1e-9 * abs(want[k][2])
+        got_img, got_prim = g.render_forward(cam, light, return_prims=True)
+        assert torch.equal(got_img.view(torch.int32), want_img.view(torch.int32)) and torch.equal(got_prim, want_prim)
+    listed, units = g.adaptive_schedule_info("pixels")
+    print("adaptive schedule, pixels:", listed, "of", units)
+    assert units == 320 * 256 and listed < units // 4, (listed, units)
+    g.set_adaptive_schedule(False)

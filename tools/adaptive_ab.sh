@@ -6,7 +6,7 @@ show='
 import sys, json
 for line in sys.stdin:
     if line.startswith("{"):
-        d = json.loads(line); print(sys.argv[1], "fwd %.4f bwd %.4f step %.4f isect %.4f sched %s" % (d["roofline"]["kernel_ms"], d["roofline"]["backward"]["kernel_ms"], d["ms_per_step"], d["extras"]["intersect_only_ms"], d["extras"].get("adaptive_schedule")))
+        d = json.loads(line); print(sys.argv[1], "fwd %.4f bwd %.4f step %.4f isect %.4f sched %s" % (d["roofline"]["kernel_ms"], d["roofline"]["backward"]["kernel_ms"], d["ms_per_step"], d["extras"]["intersect_only_ms"], d["extras"].get("adaptive_schedule")), "| render step %.4f kernel %.4f %s" % (d["extras"]["render_step"]["ms_per_step"], d["extras"]["render_step"]["roofline"]["kernel_ms"], d["extras"]["render_step"].get("adaptive_schedule")))
 '
 run() {   # label, env...
   label=$1; shift
