@@ -7,7 +7,7 @@
 Metric (BASELINE.json): Mrays/s for forward + backward (intersection + surface interaction, then the adjoint
 w.r.t. the height texels) on the C3 workload: 4096^2 fBm heights, 1024^2 image x 64 spp = 67,108,864 primary rays
 per step. A step = zero_grad -> hf_ray_intersect (fused preliminary + surface interaction) -> hf_backward
-[-> one NCCL allreduce of the gradient grid when N > 1]. Rays are sharded by 32x32-pixel image tile across ranks, so
+[-> one NCCL allreduce of the gradient grid when N > 1]. Rays are sharded by 16x16-pixel image tile across ranks, so
 total work is fixed as N grows ("strong" scaling, as BASELINE.json configs[2] states: one step at 1/2/4/8 B200).
 
 `value`   : device-resident inputs, CUDA-event timed, max over ranks.
@@ -112,7 +112,7 @@ def parse_args():
     ap.add_argument("--heights", type=int, default=4096, help="heightfield side (C3: 4096)")
     ap.add_argument("--image", type=int, default=1024, help="image side (C3: 1024)")
     ap.add_argument("--spp", type=int, default=64)
-    ap.add_argument("--tile", type=int, default=32)
+    ap.add_argument("--tile", type=int, default=16, help="image tile (pixels per side) of the deal over ranks; 16: the eight shards of C3 differ by 3.5 %% in kernel time, 32: 5.7 %%, 64: 16 %%")
     ap.add_argument("--cpu-sample", type=int, default=1 << 23, help="rays in the bounded CPU sample")
     ap.add_argument("--config", default="C3", choices=["C3", "C4", "C5"],
                     help="C3 (default): the headline metric of BASELINE.json; C4 / C5: configs[3] / configs[4] as the file states them (bench_configs.py)")

@@ -1374,16 +1374,21 @@ hf_peer_reduce_gather_kernel(float *__restrict__ local_grad, float *__restrict__
     const float lr_t = ADAM ? __ldg(lr_t_ptr) : 0.f;
     const size_t n4 = (hi - lo) / 4;                            // lo and the slots are multiples of 1024 texels, the buffers 256-byte aligned
     for (size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (size_t) gridDim.x * blockDim.x) {
+        // all partials first (independent loads: one memory latency, not nranks of them), then the clearing stores, then the sum in rank order
+        float4 a[HF_MAX_PEERS];
+        #pragma unroll
+        for (int r = 0; r < HF_MAX_PEERS; ++r) {
+            a[r] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (r < nranks) a[r] = r == rank ? reinterpret_cast<const float4 *>(local_grad + lo)[i] : __ldcs(reinterpret_cast<const float4 *>(my_stage + (size_t) r * slab) + i);
+        }
         float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
-        for (int r = 0; r < nranks; ++r) {
-            float4 a;
-            if (r == rank) a = reinterpret_cast<const float4 *>(local_grad + lo)[i];
-            else {
-                float4 *slot = reinterpret_cast<float4 *>(my_stage + (size_t) r * slab) + i;
-                a = __ldcs(slot);
-                if (a.x != 0.f || a.y != 0.f || a.z != 0.f || a.w != 0.f) __stcs(slot, make_float4(0.f, 0.f, 0.f, 0.f));
+        #pragma unroll
+        for (int r = 0; r < HF_MAX_PEERS; ++r) {
+            if (r < nranks) {
+                if (r != rank && (a[r].x != 0.f || a[r].y != 0.f || a[r].z != 0.f || a[r].w != 0.f))
+                    __stcs(reinterpret_cast<float4 *>(my_stage + (size_t) r * slab) + i, make_float4(0.f, 0.f, 0.f, 0.f));
+                g.x += a[r].x; g.y += a[r].y; g.z += a[r].z; g.w += a[r].w;
             }
-            g.x += a.x; g.y += a.y; g.z += a.z; g.w += a.w;
         }
         reinterpret_cast<float4 *>(local_grad + lo)[i] = g;
         float4 outv = g;
