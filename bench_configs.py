@@ -171,10 +171,54 @@ def run_c4(a, sampler_cls):
     params.update()
     opt.reset()
     ms_step = timed(run_step, a.steps) / a.steps
-    clocks = sampler.stop() if rank == 0 else None
     torch.cuda.synchronize()
     loss1 = float(loss.item())
     grad_checksum = float(shape.grad.double().abs().sum().item())
+    collective = f"ncclAllReduce(grad {hs * hs * 4 / 2**20:.0f} MiB fp32, sum) per step, Adam replicated" if world > 1 else "none (1 GPU)"
+    nccl_step, peer = {"ms_per_step": ms_step, "launch": launch}, None
+    if world > 1 and os.environ.get("HF_BENCH_COLLECTIVE", "auto") != "nccl":
+        # the same step over peer memory (include/hf_b200.h): partial gradient slabs to their owners by NVLink stores (zero lines are not
+        # sent), the owner sums them, applies Adam to ITS slab and stores the new heights into every rank's grid. Checked against
+        # the NCCL step on the first step from the same field before it may become the headline.
+        try:
+            def one_step(fn):
+                params["heights"] = h; params.update(); opt.reset()
+                fn(); torch.cuda.synchronize()
+                return shape.heights.clone(), shape.grad.clone()
+            h_nccl, g_nccl = one_step(step)
+            handles = [None] * world
+            dist.all_gather_object(handles, shape.peer_export())
+            shape.peer_attach(rank, world, handles)
+
+            def step_peer():
+                shape.peer_zero_grad()
+                loss.zero_()
+                shape.render_step_l2(cam, light, target, pix, image=image, loss=loss)
+                opt.step(peer=True)                      # reduce-scatter -> sharded Adam -> all-gather of the heights
+                params.update()
+            h_peer, _ = one_step(step_peer)
+            big = g_nccl.abs() > 1e-3 * g_nccl.abs().max()       # Adam's first step moves a texel by lr whatever the gradient's size: compare
+            dev_h = (h_peer - h_nccl).abs()[big].max() if bool(big.any()) else torch.zeros((), device=dev)      # where it is above rounding noise
+            dist.all_reduce(dev_h, op=dist.ReduceOp.MAX)
+            del h_nccl, g_nccl, h_peer, big
+            run_peer, peer_launch = step_peer, "eager"
+            if os.environ.get("HF_BENCH_GRAPH", "1") != "0":
+                run_peer = hfb200.capture(step_peer); peer_launch = "cuda-graph"
+            for _ in range(2):
+                run_peer()
+            params["heights"] = h; params.update(); opt.reset()
+            ms_peer = timed(run_peer, a.steps) / a.steps
+            peer = {"ms_per_step": ms_peer, "launch": peer_launch, "heights_max_abs_diff_vs_nccl_step": float(dev_h), "lr": 1e-4,
+                    "what": "zero_grad -> path-traced L2 step -> hf_peer_adam_step (partial slabs to their owners over NVLink, owner sums + Adam on its slab, "
+                            "new heights stored into every rank's grid) -> pyramid rebuild"}
+            if float(dev_h) < 1e-5 and ms_peer < ms_step:
+                ms_step, launch = ms_peer, peer_launch
+                collective = ("reduce-scatter -> sharded Adam -> all-gather of the heights as kernels over peer memory (hf_peer_adam_step); "
+                              "the ncclAllReduce + replicated Adam step is timed beside it (extras.nccl_allreduce_step)")
+        except Exception as exc:      # noqa: BLE001
+            print(f"bench.py: peer-memory path unavailable ({type(exc).__name__}: {exc}); NCCL allreduce only", file=sys.stderr, flush=True)
+            peer = None
+    clocks = sampler.stop() if rank == 0 else None
 
     # traversal counters of the PRIMARY rays (canonical traversal, counting kernel) on a 1/64 pixel sample: B_trav per segment of the model
     sub = torch.arange(0, img * img, 64, dtype=torch.int32, device=dev) if pix is None else pix[::64].contiguous()
@@ -223,7 +267,7 @@ def run_c4(a, sampler_cls):
         "config": {"workload": c4_workload(a), "rays_per_step": n_total, "segments_per_step": seg_total * 2,
                    "segments_what": "camera + bounce + visibility segments, traced once by the forward kernel and once more by the replayed adjoint",
                    "sharding": f"{a.tile}x{a.tile}-pixel image tiles, round-robin", "launch": launch,
-                   "collective": f"ncclAllReduce(grad {hs * hs * 4 / 2**20:.0f} MiB fp32, sum) per step" if world > 1 else "none (1 GPU)",
+                   "collective": collective,
                    "l2": f"heights {hs * hs * 4 / 2**30:.2f} GiB + quantised pyramid {hs * hs * 4 * 4 / 3 / 2**30:.2f} GiB exceed the 126 MB L2; no explicit flush",
                    "hit_fraction_primary": hit_frac},
         "clocks": clocks, "gpu_launches": 6 * a.steps,
@@ -237,6 +281,7 @@ def run_c4(a, sampler_cls):
                                   "achieved": (seg_local * (b_trav + 16.0 + 12.0)) / (ms_bwd * 1e-3) / 1e9,
                                   "frac": (seg_local * (b_trav + 16.0 + 12.0)) / (ms_bwd * 1e-3) / 1e9 / peak}},
         "extras": {"forward_kernel_ms": ms_fwd, "adjoint_kernel_ms": ms_bwd, "allreduce_ms": ms_allreduce, "adam_and_rebuild_ms": ms_adam,
+                   "nccl_allreduce_step": nccl_step if world > 1 else None, "peer_adam_step": peer,
                    "loss_first_step_local": loss0, "loss_last_step_local": loss1, "grad_abs_sum": grad_checksum,
                    "mean_nodes_per_primary_ray": n_node, "mean_leaves_per_primary_ray": n_leaf},
     }

@@ -818,6 +818,7 @@ extern "C" int hf_comm_init(hf_ctx *c, int rank, int nranks, const uint8_t id_by
         if (!c->grad_nccl) {
             void *nb = nullptr;
             if (g_nccl.MemAlloc(&nb, bytes) == 0 && nb) {
+                CU(cudaDeviceSynchronize());           // (scatters into the old grid on other streams)
                 CU(cudaMemcpy(nb, c->d_grad, bytes, cudaMemcpyDeviceToDevice));
                 cudaFree(c->d_grad);
                 c->d_grad = (float *) nb; c->grad_nccl = true;
@@ -887,8 +888,11 @@ extern "C" int hf_peer_export(hf_ctx *c, uint8_t out[HF_PEER_HANDLE_BYTES]) {
     CU(cudaSetDevice(c->device));
     if (c->grad_nccl) {
         // CUDA IPC exports cudaMalloc memory only: bring the gradient grid back from ncclMemAlloc memory (hf_grad() changes again)
+        // Everything that still uses the old grid (on any stream: torch's streams do not wait for the legacy stream) must be done
+        // first: ncclMemFree unmaps at once, unlike cudaFree. (A 1 GiB clone of the grid was still running here at C4.)
         const size_t bytes = (size_t) c->W * c->H * sizeof(float);
         float *nb = nullptr;
+        CU(cudaDeviceSynchronize());
         CU(cudaMalloc(&nb, bytes));
         CU(cudaMemcpy(nb, c->d_grad, bytes, cudaMemcpyDeviceToDevice));
         if (c->comm && c->grad_reg && g_nccl.CommDeregister) g_nccl.CommDeregister(c->comm, c->grad_reg);
