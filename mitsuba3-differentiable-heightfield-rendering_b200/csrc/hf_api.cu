@@ -888,13 +888,14 @@ extern "C" int hf_peer_export(hf_ctx *c, uint8_t out[HF_PEER_HANDLE_BYTES]) {
     CU(cudaSetDevice(c->device));
     if (c->grad_nccl) {
         // CUDA IPC exports cudaMalloc memory only: bring the gradient grid back from ncclMemAlloc memory (hf_grad() changes again)
-        // Everything that still uses the old grid (on any stream: torch's streams do not wait for the legacy stream) must be done
-        // first: ncclMemFree unmaps at once, unlike cudaFree. (A 1 GiB clone of the grid was still running here at C4.)
+        // Everything that still uses the old grid (on any stream: non-blocking streams do not wait for the legacy stream) must be done
+        // before the copy, and the copy before the free: ncclMemFree unmaps at once, unlike cudaFree (found at C4: a 1 GiB grid).
         const size_t bytes = (size_t) c->W * c->H * sizeof(float);
         float *nb = nullptr;
         CU(cudaDeviceSynchronize());
         CU(cudaMalloc(&nb, bytes));
         CU(cudaMemcpy(nb, c->d_grad, bytes, cudaMemcpyDeviceToDevice));
+        CU(cudaDeviceSynchronize());               // (a device-to-device cudaMemcpy returns before the copy has finished)
         if (c->comm && c->grad_reg && g_nccl.CommDeregister) g_nccl.CommDeregister(c->comm, c->grad_reg);
         c->grad_reg = nullptr;
         if (g_nccl.MemFree) g_nccl.MemFree(c->d_grad);
