@@ -219,6 +219,12 @@ public:
     bool parameters_grad_enabled() const { int e = 0; check(hf_parameters_grad_enabled(m_ctx, &e)); return e != 0; }
     void set_grad_enabled(bool e) { check(hf_set_grad_enabled(m_ctx, e ? 1 : 0)); }
 
+    /// the `coherent` argument of Scene::ray_intersect (src/render/scene.cpp:141-150) for the ray-array entry points
+    void set_ray_coherence(bool coherent) { check(hf_set_ray_coherence(m_ctx, coherent ? 1 : 0)); }
+    /// launches over the same rays / pixels, iteration after iteration, start with the units of work the previous one found far more
+    /// expensive than the rest (no reference counterpart; results do not depend on it)
+    void set_adaptive_schedule(bool on) { check(hf_set_adaptive_schedule(m_ctx, on ? 1 : 0)); }
+
     //! @}
     // =============================================================
     //! @{ \name Reverse mode (what the reference's AD tape does for this shape) and the optimiser
