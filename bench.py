@@ -358,6 +358,7 @@ def main_ours(a):
     ms_total = timed(run_step, a.steps)
     ms_step = ms_total / a.steps
     sched_info = shape.adaptive_schedule_info("rays")
+    adaptive_used = adaptive and sched_info[1] > 0          # (the library takes batches of <= 320 groups per resident warp only)
     ms_allreduce = timed(shape.allreduce_grad, 10) / 10 if world > 1 else 0.0     # the collective alone (64 MiB fp32 at C3)
     collective = "none (1 GPU)" if world == 1 else "ncclAllReduce(grad 64 MiB fp32, sum) per step"
     peer = None
@@ -415,6 +416,7 @@ def main_ours(a):
                  "what": "zero_grad -> intersect/SI -> backward -> ONE ncclAllReduce(grad, fp32, sum) on NCCL-registered memory"}
     if peer is not None and peer["grad_rel_l2_vs_nccl_step"] < 1e-4 and peer["ms_per_step"] < ms_step and os.environ.get("HF_BENCH_COLLECTIVE", "auto") != "nccl-headline":
         ms_step, launch = peer["ms_per_step"], peer["launch"]
+        state["peer_headline"] = True
         collective = ("reduce-scatter + all-gather written as two kernels over peer memory (NVLink stores into IPC-mapped grids, device-side barriers); "
                       "the single-ncclAllReduce step is timed beside it (extras.nccl_allreduce_step)")
     clocks = sampler.stop() if rank == 0 else None
@@ -517,10 +519,12 @@ def main_ours(a):
                    "collective": collective,
                    "l2": "inputs exceed L2 (ray + adjoint + output SoA > 5 GB per step vs 126 MB L2); no explicit flush",
                    "si_fields": "t,p,n,uv", "hit_fraction": hits,
-                   "schedule": "adaptive (groups far above the mean cost of the previous launch go first)" if adaptive else "fixed"},
+                   "schedule": "adaptive (groups far above the mean cost of the previous launch go first)" if adaptive_used else
+                               ("fixed (adaptive schedule enabled; the library keeps the fixed one above 320 groups per resident warp)" if adaptive else "fixed")},
         "clocks": clocks,
-        "gpu_launches": (3 if adaptive else 2) * a.steps,
-        "kernels_per_step": ["hf_intersect_fast_kernel<FUSED_SI>"] + (["hf_pick_heavy_kernel"] if adaptive else []) + ["hf_backward_kernel"],
+        "gpu_launches": ((3 if adaptive_used else 2) + (4 if state.get("peer_headline") else 0)) * a.steps,
+        "kernels_per_step": ["hf_intersect_fast_kernel<FUSED_SI>"] + (["hf_pick_heavy_kernel"] if adaptive_used else []) + ["hf_backward_kernel"]
+                            + (["hf_peer_send_partials_kernel", "hf_peer_barrier_kernel", "hf_peer_reduce_gather_kernel", "hf_peer_barrier_kernel"] if state.get("peer_headline") else []),
         "roofline": {"bound": "hbm", "kernel": "hf_intersect_fast_kernel<FUSED_SI>", "achieved": ach_fwd, "peak": peak, "unit": "GB/s",
                      "frac": ach_fwd / peak, "traffic": tr_fwd, "traffic_unit": "bytes per launch (ncu dram__bytes_read + write, profiles/traffic.json)",
                      "what_frac_means": "ALGORITHMIC bytes of SURVEY.md 8(d) per second over the measured HBM copy bandwidth -- the contract's figure, NOT DRAM utilisation: "
