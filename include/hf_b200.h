@@ -185,6 +185,27 @@ int hf_ray_intersect(hf_ctx *ctx, const hf_rays *rays, uint32_t ray_flags, const
 int hf_backward(hf_ctx *ctx, const hf_rays *rays, const hf_prelim *pi, const hf_si_adj *adj, uint32_t ray_flags,
                 size_t n, void *stream);
 
+/* hf_ray_intersect_preliminary without a context and without any device allocation. No counterpart in the reference (there every
+ * array, the acceleration structures included, comes out of Dr.Jit's allocator); added for callers that cannot go to the CUDA allocator:
+ * a plugin whose host application has given the device-memory budget to its own pool and forbids a foreign cudaMalloc, a loop with a
+ * latency bound that cannot take cudaMalloc's device-wide synchronisation, a process whose memory was partitioned up front. hf_create
+ * is out of reach for them (it allocates the grids), so this call takes the description, the caller's own DEVICE copy of the heights
+ * (row-major (height, width), read only), the rays and the result arrays, and keeps the acceleration data of the walk in a fixed
+ * array inside the library image: HF_STATIC_SCRATCH_BYTES (9 MiB) of device memory on every GPU this entry point has run on, held
+ * until the process exits. Limit: the pyramids of the field must fit that array -- every field up to 1025 x 1025 texels does; a
+ * larger one is refused with HF_ERR_INVALID and a message that names both sizes (use a context then). Results are bit-identical to
+ * hf_ray_intersect_preliminary on a context with the same description and heights.
+ *   - Each call clears its part of the array and rebuilds the pyramids from d_heights, in order on `stream`, before the walk: the
+ *     heights may change between calls, and nothing carries over from one call to the next.
+ *   - The array is one per GPU for the whole process. Calls that can overlap on the GPU (two streams with no event between them,
+ *     two host threads) race on it; the caller serialises them.
+ *   - The first call that targets a device looks up the array's device address and loads the kernels; make it before any stream
+ *     capture begins. desc->device selects the GPU (it is made current).
+ *   - It calls no cudaMalloc / cudaFree and no allocating library routine; the only memory it writes is the array and `out`. */
+#define HF_STATIC_SCRATCH_BYTES ((size_t) 9 << 20)
+int hf_ray_intersect_preliminary_static(const hf_desc *desc, const float *d_heights, const hf_rays *rays, const hf_prelim *out,
+                                        size_t n, void *stream);
+
 /* same as hf_ray_intersect_preliminary, also accumulating traversal counters (slower) */
 int hf_ray_intersect_preliminary_counted(hf_ctx *ctx, const hf_rays *rays, const hf_prelim *out, size_t n, void *stream);
 int hf_stats_get(hf_ctx *ctx, hf_stats *out, int reset);

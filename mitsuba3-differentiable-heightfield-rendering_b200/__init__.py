@@ -145,6 +145,7 @@ def _load():
         "hf_qpyramid_level": [vp, u32, C.POINTER(u32), C.POINTER(u32), C.POINTER(u32), C.POINTER(vp), C.POINTER(C.c_float), C.POINTER(C.c_float)],
         "hf_ray_intersect_preliminary": [vp, C.POINTER(_Rays), C.POINTER(_Prelim), sz, vp],
         "hf_ray_intersect_preliminary_counted": [vp, C.POINTER(_Rays), C.POINTER(_Prelim), sz, vp],
+        "hf_ray_intersect_preliminary_static": [C.POINTER(_Desc), vp, C.POINTER(_Rays), C.POINTER(_Prelim), sz, vp],
         "hf_stats_get": [vp, C.POINTER(_Stats), C.c_int],
         "hf_ray_test": [vp, C.POINTER(_Rays), vp, sz, vp],
         "hf_compute_surface_interaction": [vp, C.POINTER(_Rays), C.POINTER(_Prelim), u32, C.POINTER(_SI), sz, vp],
@@ -732,6 +733,38 @@ class Heightfield:
     def __repr__(self):
         return (f"Heightfield[\n  size = {self.W}x{self.H},\n  max_height = {self._max_height},\n"
                 f"  primitive_count = {self.primitive_count()},\n  flip_normals = {self.flip_normals}\n]")
+
+
+STATIC_SCRATCH_BYTES = 9 << 20
+
+
+def ray_intersect_preliminary_static(heights, ray: Ray3f, max_height=1.0, to_world=None, flip_normals=False, active=None, out=None):
+    """`Heightfield.ray_intersect_preliminary` for a caller that may not allocate device memory: no shape object, no context.
+
+    `heights` is the caller's own (H, W) float32 CUDA tensor; the library reads it in place and keeps its acceleration data in a
+    fixed 9 MiB array that is part of the loaded library (include/hf_b200.h, hf_ray_intersect_preliminary_static), so the C call
+    itself allocates nothing. Fields whose pyramids do not fit (beyond 1025 x 1025 texels) raise HeightfieldError. Pass `out`
+    (a PreliminaryIntersection3f made ahead of time) to keep this wrapper from allocating the result through torch as well. Calls
+    share the array: keep them on one stream, or order them with events. Same results, bit for bit, as the shape's method."""
+    if not (isinstance(heights, torch.Tensor) and heights.is_cuda and heights.dtype == torch.float32 and heights.dim() == 2
+            and heights.is_contiguous()):
+        raise HeightfieldError("ray_intersect_preliminary_static: `heights` must be a contiguous (H, W) float32 CUDA tensor")
+    L = _load()
+    d = _Desc()
+    d.height, d.width, d.max_height = int(heights.shape[0]), int(heights.shape[1]), float(max_height)
+    tw = np.eye(4, dtype=np.float32) if to_world is None else np.asarray(
+        to_world.cpu() if isinstance(to_world, torch.Tensor) else to_world, dtype=np.float32)
+    d.to_world[:] = tw.reshape(-1)[:12].tolist()
+    d.flip_normals, d.device = int(bool(flip_normals)), heights.device.index or 0
+    n = len(ray)
+    pi = out if out is not None else PreliminaryIntersection3f(n, heights.device)
+    m = None
+    if active is not None:
+        m = torch.as_tensor(active, device=heights.device).to(torch.uint8).contiguous()
+    with torch.cuda.device(heights.device):
+        r, p = ray._c(m), pi._c()
+        _check(L.hf_ray_intersect_preliminary_static(C.byref(d), _ptr(heights), C.byref(r), C.byref(p), n, _stream()))
+    return pi
 
 
 def perspective_camera(origin, target, up, fov, width, height, spp, seed=0) -> dict:

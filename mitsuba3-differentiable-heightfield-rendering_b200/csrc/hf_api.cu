@@ -1367,3 +1367,120 @@ extern "C" int hf_forward_backward_host(hf_ctx *c, const hf_rays *h_rays, const 
     CHECK_CTX(c);
     return host_pipeline(c, h_rays, h_adj, flags, h_prelim_out, h_out, h_grad_out, n, true);
 }
+
+// ------------------------------------------------------------------------------------------
+// hf_ray_intersect_preliminary_static: the preliminary intersection for callers that must not allocate device memory
+// ------------------------------------------------------------------------------------------
+// Who needs this. A context (hf_create) owns cudaMalloc'ed grids, so it is of no use to code that is not allowed to reach the CUDA
+// allocator at all: a plugin inside a host application that has handed the whole device-memory budget to its own pool (Dr.Jit's
+// caching allocator in Mitsuba is one) and treats a foreign cudaMalloc as a bug; a frame / control loop with a latency bound, where
+// cudaMalloc's device-wide synchronisation is not tolerable; a process whose memory is partitioned ahead of time (MPS limits,
+// several tenants on one GPU) and that may not grow. For them the acceleration data of the walk (the fp32 min/max pyramid, the
+// quantised pyramid and the work counter of the self-scheduling kernel) lives in the array below, which is part of the library image:
+// the driver places it when the module is loaded on a GPU and it stays there until the process ends, on every GPU that runs this
+// entry point. The caller supplies the heights, the rays and the result arrays; nothing is allocated or freed here, neither by
+// CUDA nor by any library on top of it (the few bytes of host heap the layout helper takes are the only allocation of any kind).
+//
+// HF_STATIC_SCRATCH_BYTES bounds the field: whatever needs more is rejected with HF_ERR_INVALID before any device work. 9 MiB hold
+// every field of up to 1025 x 1025 texels (1024 x 1024 cells: 2.7 MiB fp32 pyramid + 5.4 MiB quantised pyramid) and any other shape
+// whose padded pyramids fit (the quantised one pads each axis to a power of two).
+//
+// `g_static_scratch` is a device symbol. In host code the name is only a handle for the runtime (its host-side shadow), never a
+// device address, so the launchers get the pointer cudaGetSymbolAddress returns; it is looked up once per device, with that device
+// current, on the first call that targets the device. That first call also loads the module and is best made before any stream
+// capture begins.
+//
+// The array is shared by every call in the process and keeps what the previous call left in it. Each call therefore clears the part
+// it uses (in stream order) and rebuilds both pyramids from the caller's heights before it walks them. Two calls that may run on
+// the GPU at the same time (different streams without an event between them, different host threads) would build and read the same
+// bytes: they race, and the caller has to serialise them.
+#include <mutex>
+#define HF_STATIC_MAX_DEVICES 64
+static __device__ __align__(256) unsigned char g_static_scratch[HF_STATIC_SCRATCH_BYTES];
+
+struct HfStaticDevice { unsigned char *base = nullptr; int num_sms = 0; };
+static HfStaticDevice g_static_dev[HF_STATIC_MAX_DEVICES];
+
+// once per device, with that device current
+static int static_scratch_for(int device, HfStaticDevice *out) {
+    static std::mutex mu;
+    std::lock_guard<std::mutex> lock(mu);
+    HfStaticDevice &d = g_static_dev[device];
+    int rc = HF_OK;
+    if (!d.base) {
+        void *p = nullptr;
+        int sms = 0;
+        cudaError_t e = cudaGetSymbolAddress(&p, g_static_scratch);
+        if (e == cudaSuccess) e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+        if (e != cudaSuccess || !p || sms <= 0) rc = fail(HF_ERR_CUDA, "static scratch of device %d: %s", device, e != cudaSuccess ? cudaGetErrorString(e) : "no address");
+        else { d.num_sms = sms; d.base = static_cast<unsigned char *>(p); }
+    }
+    *out = d;
+    return rc;
+}
+
+extern "C" int hf_ray_intersect_preliminary_static(const hf_desc *desc, const float *d_heights, const hf_rays *rays, const hf_prelim *out,
+                                                   size_t n, void *stream) {
+    if (!desc) return fail(HF_ERR_INVALID, "null heightfield description");
+    if (desc->width < 2 || desc->height < 2) return fail(HF_ERR_INVALID, "heightfield needs at least 2x2 texels (got %ux%u)", desc->width, desc->height);
+    if (desc->width > (1u << 23) || desc->height > (1u << 23)) return fail(HF_ERR_INVALID, "heightfield side exceeds 2^23 texels");
+    if (!isfinite(desc->max_height)) return fail(HF_ERR_INVALID, "max_height is not finite");
+    if (!d_heights) return fail(HF_ERR_INVALID, "null heights");
+
+    // the same description -> parameter block -> pyramid layout as hf_create, in a context object that lives on this stack frame and
+    // owns nothing (its device pointers are the caller's heights and slices of the static array)
+    hf_ctx c{};
+    HfParams &P = c.P;
+    memset(&P, 0, sizeof(P));
+    c.W = desc->width; c.H = desc->height;
+    P.W = (int) desc->width; P.H = (int) desc->height; P.NX = P.W - 1; P.NY = P.H - 1;
+    P.flip_normals = desc->flip_normals ? 1 : 0;
+    P.mh = desc->max_height;
+    P.rw = 1.0f / (float) P.NX; P.rh = 1.0f / (float) P.NY;
+    P.x0 = (float) (-(P.W - 1)) * P.rw; P.y0 = (float) (-(P.H - 1)) * P.rh;
+    P.sgx = 0.5f * (float) P.NX; P.sgy = 0.5f * (float) P.NY;
+    { const HfDivMagic dm = hf_divmagic((uint32_t) P.NX); P.nx_magic = dm.m; P.nx_shift = dm.s; }
+    int rc = set_transform(&c, desc->to_world, desc->has_to_object ? desc->to_object : nullptr);
+    if (rc) return rc;
+
+    // the size check comes before the layout is even formed for fields that are far too large (2^23 x 2^23 texels)
+    if ((uint64_t) (desc->width - 1) * (desc->height - 1) > HF_STATIC_SCRATCH_BYTES / sizeof(uint32_t))
+        return fail(HF_ERR_INVALID, "%ux%u heightfield is beyond the static scratch of %zu bytes (any field up to 1025x1025 texels fits); use hf_create",
+                    desc->width, desc->height, HF_STATIC_SCRATCH_BYTES);
+    layout_pyramid(&c);
+    const size_t counter_bytes = 256;                                              // [0..7] statistics block, [8] the work counter
+    const size_t pyr_bytes = (c.pyr_nodes * sizeof(float2) + 255) & ~size_t(255);
+    const size_t qpyr_bytes = (c.qpyr_nodes * sizeof(uint32_t) + 255) & ~size_t(255);
+    const size_t need = counter_bytes + pyr_bytes + qpyr_bytes;
+    if (need > HF_STATIC_SCRATCH_BYTES)
+        return fail(HF_ERR_INVALID, "%ux%u heightfield needs %zu bytes of acceleration data, the static scratch holds %zu (any field up to 1025x1025 texels fits); use hf_create",
+                    desc->width, desc->height, need, HF_STATIC_SCRATCH_BYTES);
+    if (n == 0) return HF_OK;      // empty batch: nothing to do, pointers may be null
+    if ((rc = check_rays(rays)) || (rc = check_prelim(out))) return rc;
+
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0) return fail(HF_ERR_CUDA, "no CUDA device available (%s); this library has no CPU path", e != cudaSuccess ? cudaGetErrorString(e) : "count = 0");
+    if (desc->device < 0 || desc->device >= ndev || desc->device >= HF_STATIC_MAX_DEVICES) return fail(HF_ERR_INVALID, "device ordinal %d out of range", desc->device);
+    CU(cudaSetDevice(desc->device));
+    HfStaticDevice dev;
+    if ((rc = static_scratch_for(desc->device, &dev))) return rc;
+
+    unsigned long long *counters = reinterpret_cast<unsigned long long *>(dev.base);
+    float2 *pyr = reinterpret_cast<float2 *>(dev.base + counter_bytes);
+    uint32_t *qpyr = reinterpret_cast<uint32_t *>(dev.base + counter_bytes + pyr_bytes);
+    c.device = desc->device;
+    c.num_sms = dev.num_sms;
+    c.li.num_sms = dev.num_sms;
+    c.li.seg_counter = counters + 4;
+    P.heights = d_heights;
+    P.pyr = pyr;
+    P.qpyr = qpyr;
+
+    const cudaStream_t st = (cudaStream_t) stream;
+    CU(cudaMemsetAsync(dev.base, 0, need, st));                // the previous call's counters and nodes
+    CU(hf_launch_pyramid(P, pyr, qpyr, st));
+    hf_si none; memset(&none, 0, sizeof(none));
+    CU(hf_launch_intersect(P, c.li, HF_MODE_PRELIM, *rays, *out, none, nullptr, 0, n, counters, counters + 8, st));
+    return HF_OK;
+}
