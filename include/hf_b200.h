@@ -302,7 +302,13 @@ int hf_render_step_l2(hf_ctx *ctx, const hf_camera *cam, const hf_light *light, 
 /* ---- host-buffer entry points (the llvm_ad_rgb caller keeps its arrays in host memory) ---
  * rays / outputs / adjoints are HOST pointers (pinned memory gives full PCIe bandwidth; use
  * hf_host_alloc). The call stages chunks through device buffers, overlapping H2D, kernels and
- * D2H on internal streams, and returns after everything has landed. */
+ * D2H on internal streams, and returns after everything has landed.
+ * Ordering contract: the internal streams are non-blocking. These entry points start behind (1) everything queued on the legacy
+ * default stream when they are called and (2) the most recent hf_set_heights / hf_parameters_changed / hf_zero_grad / hf_adam_step of
+ * the context, whatever stream that call was given (if those calls went to several streams, or into a stream capture, the entry
+ * point synchronises the device instead). Anything else the caller has in flight on a non-blocking stream of its own -- writes
+ * through the pointers hf_heights() / hf_grad() return, hf_backward scattering into the grid -- is the caller's to order (an
+ * event on the legacy stream, or a synchronisation) before the call. */
 int hf_host_alloc(void **out, size_t bytes);
 int hf_host_free(void *p);
 int hf_ray_intersect_host(hf_ctx *ctx, const hf_rays *h_rays, uint32_t ray_flags, const hf_prelim *h_prelim_out,

@@ -174,6 +174,10 @@ struct hf_ctx {
     cudaEvent_t ev_accel = nullptr;   // recorded behind the last pyramid build (hf_bbox waits for it instead of the whole device)
     bool accel_event_ok = false;
     bool slots_ready = false;
+    // what the *_host entry points have to wait for besides the legacy stream (note_mutation / wait_mutations below)
+    cudaEvent_t ev_mut = nullptr;
+    cudaStream_t mut_stream = nullptr;
+    bool mut_pending = false, mut_sync = false;
     // multi-GPU over peer memory (hf_peer_attach): mapped grids of the other ranks, the device-side tables of those pointers, the barrier state
     int peer_n = 1, peer_rank = 0;
     size_t slab_elems = 0;
@@ -289,6 +293,34 @@ static HfLaunchInfo adaptive_launch_info(hf_ctx *c, HfAdaptive &A, size_t units,
 }
 static inline HfLaunchInfo launch_info_for(hf_ctx *c, size_t n, cudaStream_t s) { return adaptive_launch_info(c, c->as_rays, (n + 31) / 32, s); }
 static inline HfLaunchInfo launch_info_for_pixels(hf_ctx *c, size_t npix, cudaStream_t s) { return adaptive_launch_info(c, c->as_pixels, npix, s); }
+
+// Ordering of the host-buffer entry points (hf_ray_intersect_host, hf_forward_backward_host, hf_render_step_l2_host) behind the calls
+// that change what they read. Those entry points run on internal NON-BLOCKING streams, which wait for nothing by themselves; they
+// order themselves behind the legacy default stream with an event. A caller that uploads heights, rebuilds the pyramid, clears the
+// gradient grid or steps the optimiser on a non-blocking stream of its own would otherwise be overtaken. So each of those calls
+// leaves an event behind itself on its stream and the host entries wait for it. One event stands for one stream: mutators on two
+// different streams since the last host entry, or inside a stream capture (such an event cannot be waited for from outside), fall
+// back to one device-wide synchronisation at the next host entry.
+static void note_mutation(hf_ctx *c, cudaStream_t s) {
+    if (s == nullptr || s == cudaStreamLegacy) return;            // the host entries wait for the legacy stream anyway
+    if (s == c->s_in || s == c->s_k || s == c->s_out) return;     // a host entry's own streams: it returns only after they have drained
+    cudaStreamCaptureStatus st = cudaStreamCaptureStatusNone;
+    if (cudaStreamIsCapturing(s, &st) != cudaSuccess) { cudaGetLastError(); c->mut_sync = true; return; }
+    if (st == cudaStreamCaptureStatusActive) { c->mut_sync = true; return; }
+    if (!c->ev_mut && cudaEventCreateWithFlags(&c->ev_mut, cudaEventDisableTiming) != cudaSuccess) { cudaGetLastError(); c->ev_mut = nullptr; c->mut_sync = true; return; }
+    if (c->mut_pending && c->mut_stream != s) c->mut_sync = true;
+    if (cudaEventRecord(c->ev_mut, s) != cudaSuccess) { cudaGetLastError(); c->mut_sync = true; return; }
+    c->mut_pending = true; c->mut_stream = s;
+}
+static int wait_mutations(hf_ctx *c, cudaStream_t a, cudaStream_t b, cudaStream_t d) {
+    if (c->mut_sync) {
+        CU(cudaDeviceSynchronize());
+    } else if (c->mut_pending) {
+        for (cudaStream_t s : { a, b, d }) if (s) CU(cudaStreamWaitEvent(s, c->ev_mut, 0));
+    }
+    c->mut_sync = false; c->mut_pending = false;
+    return HF_OK;
+}
 
 static void layout_pyramid(hf_ctx *c) {
     HfParams &P = c->P;
@@ -414,6 +446,7 @@ extern "C" int hf_destroy(hf_ctx *c) {
     }
     if (c->ev_entry) cudaEventDestroy(c->ev_entry);
     if (c->ev_accel) cudaEventDestroy(c->ev_accel);
+    if (c->ev_mut) cudaEventDestroy(c->ev_mut);
     if (c->s_in) cudaStreamDestroy(c->s_in);
     if (c->s_k) cudaStreamDestroy(c->s_k);
     if (c->s_out) cudaStreamDestroy(c->s_out);
@@ -434,6 +467,7 @@ extern "C" int hf_set_heights(hf_ctx *c, const float *src, int src_on_device, vo
     CU(cudaSetDevice(c->device));
     CU(cudaMemcpyAsync(c->d_heights, src, (size_t) c->W * c->H * sizeof(float),
                        src_on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, (cudaStream_t) stream));
+    note_mutation(c, (cudaStream_t) stream);
     c->have_heights = true;
     c->accel_valid = false;
     return HF_OK;
@@ -458,6 +492,7 @@ extern "C" int hf_zero_grad(hf_ctx *c, void *stream) {
     CHECK_CTX(c);
     CU(cudaSetDevice(c->device));
     CU(cudaMemsetAsync(c->d_grad, 0, (size_t) c->W * c->H * sizeof(float), (cudaStream_t) stream));
+    note_mutation(c, (cudaStream_t) stream);
     return HF_OK;
 }
 
@@ -487,6 +522,7 @@ extern "C" int hf_parameters_changed(hf_ctx *c, void *stream) {
         c->accel_event_ok = (st != cudaStreamCaptureStatusActive);
         if (c->accel_event_ok) CU(cudaEventRecord(c->ev_accel, (cudaStream_t) stream));
     }
+    note_mutation(c, (cudaStream_t) stream);
     c->accel_valid = true;
     return HF_OK;
 }
@@ -780,6 +816,7 @@ extern "C" int hf_adam_step(hf_ctx *c, const hf_adam *cfg, void *stream) {
     CU(hf_launch_adam(c->d_heights, c->d_grad, c->d_m, c->d_v, (size_t) c->W * c->H, c->d_adam_t, c->d_adam_lr_t, c->d_adam_table,
                       HF_ADAM_TABLE, (float) cfg->lr, (float) b1, (float) b2, (float) (1.0 - b1), (float) (1.0 - b2), (float) cfg->epsilon,
                       cfg->mask_updates, c->num_sms, (cudaStream_t) stream));
+    note_mutation(c, (cudaStream_t) stream);
     c->accel_valid = false;       // heights moved: the caller runs hf_parameters_changed (SceneParameters.update)
     return HF_OK;
 }
@@ -800,6 +837,13 @@ extern "C" int hf_comm_init(hf_ctx *c, int rank, int nranks, const uint8_t id_by
     int rc = nccl_load();
     if (rc) return rc;
     CU(cudaSetDevice(c->device));
+    // With nranks > 1 the gradient grid moves into NCCL's memory below and the cudaMalloc grid is freed. Once hf_peer_export has handed
+    // out an IPC handle of that grid, other processes may have it mapped (P.grad_peer, the staging tables): it has to stay where it is.
+    const char *env_mem = getenv("HF_B200_NCCL_MEM");
+    const bool want_move = nranks > 1 && !(env_mem && env_mem[0] == '0') && !c->grad_nccl;
+    if (want_move && (c->peer_n > 1 || c->d_xcounter))
+        return fail(HF_ERR_STATE, "hf_comm_init after hf_peer_export: the gradient grid is shared with the peers and cannot move into NCCL memory; "
+                                  "call hf_comm_init first (hf_peer_export moves the grid back), or set HF_B200_NCCL_MEM=0");
     if (c->comm) {
         if (c->grad_reg && g_nccl.CommDeregister) g_nccl.CommDeregister(c->comm, c->grad_reg);
         c->grad_reg = nullptr;
@@ -818,8 +862,9 @@ extern "C" int hf_comm_init(hf_ctx *c, int rank, int nranks, const uint8_t id_by
         if (!c->grad_nccl) {
             void *nb = nullptr;
             if (g_nccl.MemAlloc(&nb, bytes) == 0 && nb) {
-                CU(cudaDeviceSynchronize());           // (scatters into the old grid on other streams)
-                CU(cudaMemcpy(nb, c->d_grad, bytes, cudaMemcpyDeviceToDevice));
+                cudaError_t ce = cudaDeviceSynchronize();           // (scatters into the old grid on other streams)
+                if (ce == cudaSuccess) ce = cudaMemcpy(nb, c->d_grad, bytes, cudaMemcpyDeviceToDevice);
+                if (ce != cudaSuccess) { g_nccl.MemFree(nb); return fail(HF_ERR_CUDA, "hf_comm_init: moving the gradient grid into NCCL memory failed: %s", cudaGetErrorString(ce)); }
                 cudaFree(c->d_grad);
                 c->d_grad = (float *) nb; c->grad_nccl = true;
             } else cudaGetLastError();
@@ -856,7 +901,7 @@ extern "C" int hf_allreduce_grad(hf_ctx *c, void *stream) {
 // rank that owns the texel, over NVLink), the all-gather is a store kernel (gradient) or is fused into the sharded Adam (heights).
 // One process per GPU: the grids are shared with CUDA IPC handles the caller ships between the ranks (like the NCCL unique id).
 // ------------------------------------------------------------------------------------------
-// HF_PEER_HANDLE_BYTES (include/hf_b200.h): three cudaIpcMemHandle_t -- gradient grid, heights, barrier counter
+// HF_PEER_HANDLE_BYTES (include/hf_b200.h): four cudaIpcMemHandle_t -- gradient grid, heights, barrier counter, staging area
 static_assert(sizeof(cudaIpcMemHandle_t) == 64, "cudaIpcMemHandle_t is 64 bytes");
 
 static void peer_release(hf_ctx *c);
@@ -904,6 +949,13 @@ extern "C" int hf_peer_export(hf_ctx *c, uint8_t out[HF_PEER_HANDLE_BYTES]) {
     if (!c->d_xcounter) {
         CU(cudaMalloc(&c->d_xcounter, size_t(2) << 20));            // an allocation of its own (IPC maps whole allocations)
         CU(cudaMemset(c->d_xcounter, 0, size_t(2) << 20));
+    } else {
+        // A new group starts from a clean barrier: counter [0] and epoch [64] count in units of the OLD group's size (the counter
+        // stands at epoch * old_nranks), so a group of another size would either walk through its first barrier or never leave it.
+        // Every rank exports before any rank attaches, so the exchange of the handles is the host-side barrier between the last
+        // kernel of the old group (finished: the device is synchronised first) and the first of the new one.
+        CU(cudaDeviceSynchronize());
+        CU(cudaMemset(c->d_xcounter, 0, 65 * sizeof(unsigned)));
     }
     {                                                               // one slab per sender, whatever the number of ranks will be
         const size_t bytes = std::max(((size_t) c->W * c->H + (size_t) HF_MAX_PEERS * 2048) * sizeof(float), size_t(2) << 20);
@@ -1236,6 +1288,7 @@ static int host_pipeline(hf_ctx *c, const hf_rays *hr, const hf_si_adj *hadj, ui
     CU(cudaStreamWaitEvent(c->s_in, c->ev_entry, 0));
     CU(cudaStreamWaitEvent(c->s_k, c->ev_entry, 0));
     CU(cudaStreamWaitEvent(c->s_out, c->ev_entry, 0));
+    if ((rc = wait_mutations(c, c->s_in, c->s_k, c->s_out))) return rc;
 
     if (n > 0) {
         float *const *hsi_f = reinterpret_cast<float *const *>(hsi);
@@ -1337,6 +1390,7 @@ extern "C" int hf_render_step_l2_host(hf_ctx *c, const hf_camera *cam, const hf_
     cudaStream_t st = c->s_k;
     CU(cudaEventRecord(c->ev_entry, (cudaStream_t) 0));
     CU(cudaStreamWaitEvent(st, c->ev_entry, 0));
+    if ((rc = wait_mutations(c, st, nullptr, nullptr))) return rc;
     if (h_heights) {
         CU(cudaMemcpyAsync(c->d_heights, h_heights, (size_t) c->W * c->H * sizeof(float), cudaMemcpyHostToDevice, st));
         c->have_heights = true;

@@ -251,3 +251,69 @@ def test_peer_scatter_equals_single_rank(tmp_path):
     port = 29900 + (os.getpid() % 2000)
     mp.spawn(_peer_worker, args=(world, port, str(tmp_path)), nprocs=world, join=True)
     assert os.path.exists(tmp_path / "ok_peer")
+
+
+def _regroup_worker(rank, world, port, out_dir):
+    """Peers attach as a group of `world`, detach, and all but the last rank form a SMALLER group on the same contexts. The barrier
+    state (counter and epoch in each rank's peer-mapped counter block) counts in units of the group size, so hf_peer_export must
+    hand out a clean one: with the leftovers of the larger group the smaller one walks through its barriers without waiting."""
+    import torch.distributed as dist
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    import hfb200
+    from hfb200 import workloads as wl
+    torch.cuda.set_device(rank)
+    dev = torch.device("cuda", rank)
+    hs, img, spp, tile = 257, 128, 8, 16
+    cam = wl.CONFIGS["C1"]["camera"]
+    h = wl.fbm_heights(hs, octaves=5, seed=0xC1, device=dev)
+
+    def trace(shape, pix):
+        o, d = wl.camera_rays(cam["origin"], cam["target"], cam["up"], cam["fov"], img, img, spp, seed=3, device=dev, pixels=pix)
+        ray = hfb200.Ray3f(o, d, device=dev)
+        n = o.shape[1]
+        adj = shape.prepare_adjoints(wl.hashed_adjoints(n, seed=1, device=dev, ids=wl.global_ray_ids(pix, spp)), n)
+        si, pi = shape.ray_intersect(ray, return_prelim=True, fields=("t", "p", "n", "uv"))
+        shape.backward(ray, pi, adj)
+
+    shape = hfb200.load_dict({"type": "heightfield", "heights": h, "max_height": 0.25}, device=dev)
+    one = hfb200.load_dict({"type": "heightfield", "heights": h, "max_height": 0.25}, device=dev)
+    one.zero_grad(); trace(one, torch.arange(img * img, dtype=torch.int64, device=dev)); torch.cuda.synchronize()
+    g1 = one.grad.double().clone()
+
+    def run_group(n_ranks, steps):
+        """every rank takes part in the handle exchange; ranks >= n_ranks stay out of the group"""
+        handles = [None] * world
+        dist.all_gather_object(handles, shape.peer_export())
+        if rank < n_ranks:
+            shape.peer_attach(rank, n_ranks, handles[:n_ranks])
+            pix = wl.tile_pixels(img, img, tile, rank, n_ranks, device=dev)
+            for it in range(steps):
+                shape.peer_zero_grad(); trace(shape, pix); shape.peer_reduce_grad()
+                torch.cuda.synchronize()
+                err = float((shape.grad.double() - g1).norm() / g1.norm())
+                assert err < 1e-4, f"group of {n_ranks}, step {it}: reduced gradient vs single rank {err:.2e}"
+        dist.barrier()
+        if rank < n_ranks:
+            shape.peer_detach()
+        dist.barrier()
+
+    run_group(world, 3)           # counters now stand at a multiple of `world`
+    run_group(world - 1, 3)       # a smaller group on the same contexts
+    run_group(world, 2)           # and a larger one again
+    if rank == 0:
+        with open(os.path.join(out_dir, "ok_regroup"), "w") as f:
+            f.write("ok\n")
+    dist.barrier()
+    del shape, one
+    dist.destroy_process_group()
+
+
+@pytest.mark.skipif(_ngpu() < 3, reason=f"needs >= 3 GPUs on one box (found {_ngpu()})")
+def test_peer_groups_of_different_sizes_on_the_same_contexts(tmp_path):
+    import torch.multiprocessing as mp
+    world = min(_ngpu(), 4)
+    port = 30900 + (os.getpid() % 2000)
+    mp.spawn(_regroup_worker, args=(world, port, str(tmp_path)), nprocs=world, join=True)
+    assert os.path.exists(tmp_path / "ok_regroup")

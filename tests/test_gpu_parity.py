@@ -455,6 +455,50 @@ def test_host_api_matches_device_api(hf, oracle):
     assert _same_bits(hp["t"].numpy()[idx], pc.t).all()
 
 
+def test_host_api_waits_for_a_rebuild_on_a_side_stream(hf, oracle):
+    """include/hf_b200.h, ordering contract of the *_host entry points: new heights and the pyramid rebuild are queued on a non-blocking
+    stream of the caller behind ~100 ms of other work; the host entry that follows must walk the NEW field (its internal streams
+    used to wait for the legacy stream only and read a stale pyramid), and a zero_grad queued the same way must not wipe what the
+    host entry scatters."""
+    from hfb200 import workloads as wl
+    rng = np.random.default_rng(77)
+    H, W = 300, 260
+    h_old, h_new = random_heights(rng, H, W), random_heights(rng, H, W, kind="noise")
+    g, _ = _mk(hf, oracle, h_old, 0.5)
+    ref, _ = _mk(hf, oracle, h_new, 0.5)
+    n = 200000
+    o, d = wl.hemisphere_rays(n, seed=9)
+    adj = wl.hashed_adjoints(n, seed=4)
+    ray = hf.Ray3f(o, d)
+    si, pi = ref.ray_intersect(ray, return_prelim=True)
+    ref.zero_grad(); ref.backward(ray, pi, adj)
+    torch.cuda.synchronize()
+    pin = lambda x: x.contiguous().pin_memory()
+    hr = {"ox": pin(o[0]), "oy": pin(o[1]), "oz": pin(o[2]), "dx": pin(d[0]), "dy": pin(d[1]), "dz": pin(d[2]),
+          "maxt": pin(torch.full((n,), float("inf")))}
+    ha = {"t": pin(adj["t"]), "px": pin(adj["p"][0]), "py": pin(adj["p"][1]), "pz": pin(adj["p"][2]),
+          "nx": pin(adj["n"][0]), "ny": pin(adj["n"][1]), "nz": pin(adj["n"][2]), "uvx": pin(adj["uv"][0]), "uvy": pin(adj["uv"][1])}
+    hs = {k: torch.empty(n).pin_memory() for k in ("t", "px", "nz")}
+    hp = {"t": torch.empty(n).pin_memory(), "u": torch.empty(n).pin_memory(), "v": torch.empty(n).pin_memory(),
+          "prim_index": torch.empty(n, dtype=torch.int32).pin_memory()}
+    hg = torch.empty(H, W).pin_memory()
+    new_dev = torch.from_numpy(h_new).cuda()
+    side = torch.cuda.Stream()                      # torch's side streams are non-blocking
+    torch.cuda.synchronize()
+    with torch.cuda.stream(side):
+        torch.cuda._sleep(200_000_000)              # ~0.1 s at 1.9 GHz: the host entry below is called long before this ends
+        g.heights.copy_(new_dev)
+        g.parameters_changed()
+        g.zero_grad()
+    g.forward_backward_host(hr, ha, hs, hg, n, h_prelim=hp)
+    assert torch.equal(hp["t"], pi.t.cpu()) and torch.equal(hp["prim_index"], pi.prim_index.cpu())
+    assert torch.equal(hs["px"], si.p[0].cpu()) and torch.equal(hs["nz"], si.n[2].cpu())
+    gref = ref.grad.cpu()
+    assert float(gref.abs().sum()) > 0
+    assert torch.allclose(hg, gref, rtol=1e-4, atol=1e-5 * float(gref.abs().max()))
+    torch.cuda.synchronize()
+
+
 def test_host_api_every_si_field_and_empty_batch(hf, oracle):
     """hf_ray_intersect_host / hf_forward_backward_host with ALL 27 surface-interaction members requested (the staging slab is
     derived from sizeof(hf_si): wi_z used to be left without a slot), compared bit for bit with the device API; then the n == 0 call
