@@ -98,7 +98,7 @@ static int nccl_load() {
 #define HF_SCHED_SLOTS 256            // every eager launch of a self-scheduling kernel gets its own counter (launches on different streams overlap)
 #define HF_SCHED_CAPTURE_SLOTS 1024   // launches recorded into a CUDA graph get a counter of their own for good: a graph bakes the pointer in
                                       // and may replay beside eager launches long after the eager ring has wrapped around
-#define HF_ADAM_TABLE 65536            // bias corrections tabulated per (beta1, beta2); 0.999^65535 ~ 3e-29: converged long before the end
+#define HF_ADAM_TABLE 65536            // bias corrections tabulated per (beta1, beta2) with the host's double arithmetic; later steps evaluate it on the device
 #define HF_TOP_NODE_CAP 1366          // (32^2 + 16^2 + ... + 1) rounded up to even: 10.9 KB of shared memory
 #ifndef HF_HOST_CHUNK_LOG2
 #define HF_HOST_CHUNK_LOG2 21
@@ -164,8 +164,10 @@ struct hf_ctx {
     int grad_enabled = 1;
     // Adam: step counter + lr_t on the device (graph replays advance t), bias-correction table per (beta1, beta2)
     int *d_adam_t = nullptr;
-    float *d_adam_lr_t = nullptr, *d_adam_table = nullptr;
+    float *d_adam_lr_t = nullptr, *d_adam_table = nullptr;      // d_adam_table: the table of the betas in use (one of adam_tables)
     double tab_b1 = -1.0, tab_b2 = -1.0;
+    struct AdamTable { double b1, b2; float *d; };
+    std::vector<AdamTable> adam_tables;                         // one per (beta1, beta2) ever used, never rewritten: a CUDA graph keeps the pointer it captured
     hf_nccl_comm comm = nullptr;
     int nranks = 1, rank = 0;
     HostSlot slots[HF_HOST_SLOTS];
@@ -452,7 +454,8 @@ extern "C" int hf_destroy(hf_ctx *c) {
     if (c->s_out) cudaStreamDestroy(c->s_out);
     c->as_rays.release(); c->as_pixels.release();
     cudaFree(c->d_heights); cudaFree(c->d_grad); cudaFree(c->d_m); cudaFree(c->d_v); cudaFree(c->d_pyr); cudaFree(c->d_qpyr); cudaFree(c->d_counters); cudaFree(c->d_scratch);
-    cudaFree(c->d_adam_t); cudaFree(c->d_adam_lr_t); cudaFree(c->d_adam_table);
+    cudaFree(c->d_adam_t); cudaFree(c->d_adam_lr_t);
+    for (auto &e : c->adam_tables) cudaFree(e.d);
     cudaFree(c->d_hs_target); cudaFree(c->d_hs_image); cudaFree(c->d_hs_pixels); cudaFree(c->d_hs_loss);
     delete c;
     return HF_OK;
@@ -790,13 +793,18 @@ static int ensure_adam_table(hf_ctx *c, double b1, double b2, void *stream) {
     cudaStreamCaptureStatus st = cudaStreamCaptureStatusNone;
     if (cudaStreamIsCapturing((cudaStream_t) stream, &st) == cudaSuccess && st == cudaStreamCaptureStatusActive)
         return fail(HF_ERR_STATE, "Adam: run one eager hf_adam_step with these betas before capturing it into a CUDA graph");
+    for (const auto &e : c->adam_tables)
+        if (e.b1 == b1 && e.b2 == b2) { c->d_adam_table = e.d; c->tab_b1 = b1; c->tab_b2 = b2; return HF_OK; }
+    if (c->adam_tables.size() >= 64) return fail(HF_ERR_STATE, "Adam: more than 64 distinct (beta1, beta2) pairs on one context");
     std::vector<float> tab(HF_ADAM_TABLE);
     tab[0] = 1.f;
     for (int t = 1; t < HF_ADAM_TABLE; ++t) tab[t] = (float) (sqrt(1.0 - pow(b2, t)) / (1.0 - pow(b1, t)));
-    if (!c->d_adam_table) CU(cudaMalloc(&c->d_adam_table, HF_ADAM_TABLE * sizeof(float)));
-    CU(cudaStreamSynchronize((cudaStream_t) stream));
-    CU(cudaMemcpy(c->d_adam_table, tab.data(), HF_ADAM_TABLE * sizeof(float), cudaMemcpyHostToDevice));
-    c->tab_b1 = b1; c->tab_b2 = b2;
+    float *d = nullptr;
+    CU(cudaMalloc(&d, HF_ADAM_TABLE * sizeof(float)));
+    cudaError_t ce = cudaMemcpy(d, tab.data(), HF_ADAM_TABLE * sizeof(float), cudaMemcpyHostToDevice);
+    if (ce != cudaSuccess) { cudaFree(d); return fail(HF_ERR_CUDA, "Adam: table upload failed: %s", cudaGetErrorString(ce)); }
+    c->adam_tables.push_back({ b1, b2, d });
+    c->d_adam_table = d; c->tab_b1 = b1; c->tab_b2 = b2;
     return HF_OK;
 }
 
@@ -815,7 +823,7 @@ extern "C" int hf_adam_step(hf_ctx *c, const hf_adam *cfg, void *stream) {
     { int rc = ensure_adam_table(c, b1, b2, stream); if (rc) return rc; }
     CU(hf_launch_adam(c->d_heights, c->d_grad, c->d_m, c->d_v, (size_t) c->W * c->H, c->d_adam_t, c->d_adam_lr_t, c->d_adam_table,
                       HF_ADAM_TABLE, (float) cfg->lr, (float) b1, (float) b2, (float) (1.0 - b1), (float) (1.0 - b2), (float) cfg->epsilon,
-                      cfg->mask_updates, c->num_sms, (cudaStream_t) stream));
+                      cfg->mask_updates, b1, b2, c->num_sms, (cudaStream_t) stream));
     note_mutation(c, (cudaStream_t) stream);
     c->accel_valid = false;       // heights moved: the caller runs hf_parameters_changed (SceneParameters.update)
     return HF_OK;
@@ -1090,14 +1098,14 @@ static int peer_reduce(hf_ctx *c, const hf_adam *cfg, cudaStream_t st) {
         CU(hf_launch_peer_reduce_gather(c->d_grad, c->d_stage, adam ? c->d_peer_heights_tab : c->d_peer_grad_tab, c->peer_n, c->peer_rank, lo, hi, c->slab_elems,
                                         adam, c->d_heights, c->d_m, c->d_v, c->d_adam_t, c->d_adam_lr_t, c->d_adam_table, HF_ADAM_TABLE,
                                         adam ? (float) cfg->lr : 0.f, (float) b1, (float) b2, (float) (1.0 - b1), (float) (1.0 - b2),
-                                        adam ? (float) cfg->epsilon : 0.f, adam ? cfg->mask_updates : 0, c->num_sms, st));
+                                        adam ? (float) cfg->epsilon : 0.f, adam ? cfg->mask_updates : 0, b1, b2, c->num_sms, st));
     } else {
         // the scatter kernels already summed every contribution into the owner's slab: wait for all of them, then all-gather by stores
         if ((rc = peer_barrier(c, st))) return rc;
         if (adam)
             CU(hf_launch_peer_adam(c->d_heights, c->d_grad, c->d_m, c->d_v, c->d_peer_heights_tab, c->peer_n, c->peer_rank, lo, hi, c->d_adam_t, c->d_adam_lr_t,
                                    c->d_adam_table, HF_ADAM_TABLE, (float) cfg->lr, (float) b1, (float) b2, (float) (1.0 - b1), (float) (1.0 - b2),
-                                   (float) cfg->epsilon, cfg->mask_updates, c->num_sms, st));
+                                   (float) cfg->epsilon, cfg->mask_updates, b1, b2, c->num_sms, st));
         else
             CU(hf_launch_peer_push(c->d_grad, c->d_peer_grad_tab, c->peer_n, c->peer_rank, lo, hi, c->num_sms, st));
     }

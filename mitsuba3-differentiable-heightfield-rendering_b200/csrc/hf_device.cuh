@@ -52,7 +52,12 @@ struct HfParams {
 // gradient scatter of one value: the texel's owner takes it (see HfParams::grad_peer)
 __device__ __forceinline__ void hf_grad_add(const HfParams &P, float *__restrict__ grad, uint32_t idx, float val) {
 #ifndef HF_NO_PEER_ATOMICS          // dev builds: measure what the owner lookup costs the single-GPU kernels
-    if (P.peer_n > 1) grad = P.grad_peer[hf_divide(idx, P.slab_magic, P.slab_shift)];
+    if (P.peer_n > 1) {
+        // several GPUs add to the same texel of the owner's grid over NVLink: only system scope makes that atomic across devices
+        // (atomicAdd is device scope, red.gpu)
+        atomicAdd_system(P.grad_peer[hf_divide(idx, P.slab_magic, P.slab_shift)] + idx, val);
+        return;
+    }
 #endif
     atomicAdd(grad + idx, val);
 }

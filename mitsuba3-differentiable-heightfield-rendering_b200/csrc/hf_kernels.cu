@@ -1242,11 +1242,17 @@ __device__ __forceinline__ void adam_one(float &p, float g, float &m, float &v, 
 // Step counter and bias correction live on the DEVICE, so that a CUDA graph which captured an optimisation step replays a correct Adam
 // (t advances with every replay): one thread bumps t and looks lr_scale(t) up in a table the host filled once per (beta1, beta2) with
 // the reference's double-precision expression (optimizers.py:266-269), then lr_t = lr * lr_scale in fp32 as there.
+// Beyond the table (t >= table_len) the same expression is evaluated here in double: for the default betas it has long reached 1, but for
+// betas nearer 1 it has not (beta2 = 0.9999: 0.9993 at t = 65535), and the reference keeps counting (optimizers.py:266-269).
 __global__ void hf_adam_prep_kernel(int *__restrict__ t, float *__restrict__ lr_t, const float *__restrict__ scale_table, const int table_len,
-                                    const float lr) {
-    const int step = min(*t + 1, table_len - 1);          // beyond the table the bias correction has long converged
+                                    const float lr, const double b1, const double b2) {
+    const int prev = *t;
+    const int step = prev < 0x7fffffff ? prev + 1 : prev;
     *t = step;
-    *lr_t = lr * scale_table[step];
+    float scale;
+    if (step < table_len) scale = scale_table[step];
+    else scale = (float) (sqrt(1.0 - pow(b2, (double) step)) / (1.0 - pow(b1, (double) step)));
+    *lr_t = lr * scale;
 }
 
 __global__ void __launch_bounds__(256)
@@ -1434,8 +1440,8 @@ cudaError_t hf_launch_peer_send_partials(const float *local, float *const *d_pee
 }
 cudaError_t hf_launch_peer_reduce_gather(float *local_grad, float *my_stage, float *const *d_peer_out, int nranks, int rank, size_t lo, size_t hi, size_t slab,
                                          bool adam, float *p, float *m, float *v, int *d_t, float *d_lr_t, const float *d_scale_table, int table_len, float lr,
-                                         float beta1, float beta2, float omb1, float omb2, float eps, int mask_updates, int num_sms, cudaStream_t s) {
-    if (adam) hf_adam_prep_kernel<<<1, 1, 0, s>>>(d_t, d_lr_t, d_scale_table, table_len, lr);
+                                         float beta1, float beta2, float omb1, float omb2, float eps, int mask_updates, double beta1_d, double beta2_d, int num_sms, cudaStream_t s) {
+    if (adam) hf_adam_prep_kernel<<<1, 1, 0, s>>>(d_t, d_lr_t, d_scale_table, table_len, lr, beta1_d, beta2_d);
     if (hi > lo) {
         const size_t blocks = ((hi - lo + 3) / 4 + 255) / 256, cap = (size_t) num_sms * 8;
         const int grid = (int) (blocks < cap ? (blocks ? blocks : 1) : cap);
@@ -1457,8 +1463,8 @@ cudaError_t hf_launch_peer_push(const float *local, float *const *d_peers, int n
 }
 cudaError_t hf_launch_peer_adam(float *p, const float *g, float *m, float *v, float *const *d_peer_heights, int nranks, int rank, size_t lo, size_t hi,
                                 int *d_t, float *d_lr_t, const float *d_scale_table, int table_len, float lr, float beta1, float beta2, float omb1,
-                                float omb2, float eps, int mask_updates, int num_sms, cudaStream_t s) {
-    hf_adam_prep_kernel<<<1, 1, 0, s>>>(d_t, d_lr_t, d_scale_table, table_len, lr);
+                                float omb2, float eps, int mask_updates, double beta1_d, double beta2_d, int num_sms, cudaStream_t s) {
+    hf_adam_prep_kernel<<<1, 1, 0, s>>>(d_t, d_lr_t, d_scale_table, table_len, lr, beta1_d, beta2_d);
     if (hi > lo) {
         const size_t blocks = ((hi - lo) / 4 + 255) / 256, cap = (size_t) num_sms * 4;
         hf_peer_adam_kernel<<<(int) (blocks < cap ? (blocks ? blocks : 1) : cap), 256, 0, s>>>(p, g, m, v, d_peer_heights, nranks, rank, lo, hi, d_lr_t, beta1,
@@ -1468,10 +1474,10 @@ cudaError_t hf_launch_peer_adam(float *p, const float *g, float *m, float *v, fl
 }
 
 cudaError_t hf_launch_adam(float *p, const float *g, float *m, float *v, size_t n, int *d_t, float *d_lr_t, const float *d_scale_table,
-                           int table_len, float lr, float beta1, float beta2, float omb1, float omb2, float eps, int mask_updates,
+                           int table_len, float lr, float beta1, float beta2, float omb1, float omb2, float eps, int mask_updates, double beta1_d, double beta2_d,
                            int num_sms, cudaStream_t s) {
     if (n == 0) return cudaSuccess;
-    hf_adam_prep_kernel<<<1, 1, 0, s>>>(d_t, d_lr_t, d_scale_table, table_len, lr);
+    hf_adam_prep_kernel<<<1, 1, 0, s>>>(d_t, d_lr_t, d_scale_table, table_len, lr, beta1_d, beta2_d);
     size_t blocks = (n / 4 + 255) / 256;
     size_t cap = (size_t) num_sms * 8;
     int grid = (int) (blocks < cap ? (blocks ? blocks : 1) : cap);

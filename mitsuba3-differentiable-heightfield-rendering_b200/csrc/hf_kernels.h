@@ -50,7 +50,7 @@ cudaError_t hf_launch_surface_interaction(const HfParams &P, const HfLaunchInfo 
 cudaError_t hf_launch_backward(const HfParams &P, const HfLaunchInfo &li, const hf_rays &rays, const hf_prelim &pi,
                                const hf_si_adj &adj, uint32_t flags, float *grad, size_t n, cudaStream_t s);
 cudaError_t hf_launch_adam(float *p, const float *g, float *m, float *v, size_t n, int *d_t, float *d_lr_t, const float *d_scale_table,
-                           int table_len, float lr, float beta1, float beta2, float omb1, float omb2, float eps, int mask_updates,
+                           int table_len, float lr, float beta1, float beta2, float omb1, float omb2, float eps, int mask_updates, double beta1_d, double beta2_d,
                            int num_sms, cudaStream_t s);
 
 // multi-GPU over peer memory (hf_peer_attach)
@@ -58,12 +58,12 @@ cudaError_t hf_launch_peer_barrier(unsigned *const *d_peer_counter, unsigned *d_
 cudaError_t hf_launch_peer_push(const float *local, float *const *d_peers, int nranks, int rank, size_t lo, size_t hi, int num_sms, cudaStream_t s);
 cudaError_t hf_launch_peer_adam(float *p, const float *g, float *m, float *v, float *const *d_peer_heights, int nranks, int rank, size_t lo, size_t hi,
                                 int *d_t, float *d_lr_t, const float *d_scale_table, int table_len, float lr, float beta1, float beta2, float omb1,
-                                float omb2, float eps, int mask_updates, int num_sms, cudaStream_t s);
+                                float omb2, float eps, int mask_updates, double beta1_d, double beta2_d, int num_sms, cudaStream_t s);
 
 cudaError_t hf_launch_peer_send_partials(const float *local, float *const *d_peer_stage, int nranks, int rank, size_t slab, size_t total, int num_sms, cudaStream_t s);
 cudaError_t hf_launch_peer_reduce_gather(float *local_grad, float *my_stage, float *const *d_peer_out, int nranks, int rank, size_t lo, size_t hi, size_t slab,
                                          bool adam, float *p, float *m, float *v, int *d_t, float *d_lr_t, const float *d_scale_table, int table_len, float lr,
-                                         float beta1, float beta2, float omb1, float omb2, float eps, int mask_updates, int num_sms, cudaStream_t s);
+                                         float beta1, float beta2, float omb1, float omb2, float eps, int mask_updates, double beta1_d, double beta2_d, int num_sms, cudaStream_t s);
 
 // hf_render.cu: mode 0 = forward image (+ hit triangles), 1 = fused forward + L2 adjoint + backward, 2 = backward by re-tracing
 #define HF_RENDER_MAX_SPP_HOST 256

@@ -400,6 +400,38 @@ def test_adam_bit_exact_and_traverse(hf, oracle):
         params["heights"] = torch.zeros(3, 3)
 
 
+def test_adam_bias_correction_beyond_the_table(hf, oracle):
+    """optimizers.py:266-269 keeps counting t for good. The library tabulates lr_scale(t) for t < 65536 and used to stay on the last
+    entry afterwards, which is wrong for betas close to 1 (beta2 = 0.9999: 0.99929 at the end of the table, 0.99954 at t = 70000,
+    1 in the limit). 69 999 steps with a zero gradient leave p, m, v untouched (0 / (0 + eps)) and bring the device counter to
+    t = 69 999; the next step, with a real gradient, must be the oracle's step at t = 70 000. Also: a second pair of betas gets a
+    table of its own and the first pair still works afterwards (tables are never rewritten under a captured graph)."""
+    rng = np.random.default_rng(5)
+    H, W = 8, 12
+    h = random_heights(rng, H, W)
+    g, _ = _mk(hf, oracle, h, 0.5)
+    g.grad.zero_()
+    for _ in range(69999):
+        g.adam_step(1e-2, beta_2=0.9999)
+    torch.cuda.synchronize()
+    assert np.array_equal(_np(g.heights), h)
+    gr = rng.normal(size=(H, W)).astype(f32)
+    g.grad.copy_(torch.from_numpy(gr))
+    g.adam_step(1e-2, beta_2=0.9999)
+    p = h.copy(); m = np.zeros_like(p); v = np.zeros_like(p)
+    oracle.adam_step(p, gr, m, v, lr=1e-2, beta2=0.9999, t=70000)
+    got = _np(g.heights)
+    step, want = got - h, p - h
+    assert np.abs(step).min() > 1e-3                                            # every texel moved
+    assert np.allclose(step, want, rtol=2e-6, atol=0), np.abs(step / want - 1).max()   # the saturated table entry is 2.5e-4 off
+    # other betas, then the first pair again: t = 70001 and 70002
+    g.adam_step(1e-2)
+    oracle.adam_step(p, gr, m, v, lr=1e-2, t=70001)
+    g.adam_step(1e-2, beta_2=0.9999)
+    oracle.adam_step(p, gr, m, v, lr=1e-2, beta2=0.9999, t=70002)
+    assert np.allclose(_np(g.heights), p, rtol=0, atol=1e-6)
+
+
 def test_error_behaviour(hf, oracle):
     with pytest.raises(hf.HeightfieldError):
         hf.load_dict({"type": "sphere"})
