@@ -185,7 +185,7 @@ def main_reference(a):
     sample = f"{res['n']} rays = all {a.spp} spp of every k-th pixel of the {a.image}^2 image (1/{max(1, a.image * a.image * a.spp // res['n'])} of the step)"
     line = {"impl": "reference", "metric": METRIC, "value": res["mrays"], "unit": "Mrays/s", "n_gpus": a.gpus, "steps": a.steps,
             "warmup": a.warmup, "ms_per_step": res["ms_per_step"], "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
-            "dtype": "f32", "data": "synthetic", "config": {"workload": workload_name(a), "sample": sample},
+            "dtype": "f32", "data": "synthetic", "config": {"workload": workload_name(a)},
             "cpu_baseline": {"value": res["mrays"], "unit": "Mrays/s", "cores": res["threads"], "kind": "port", "sample": sample,
                              "note": "CPU restatement of the reference llvm_ad_rgb arithmetic (oracle/hf_oracle.c, OpenMP); the reference "
                                      "plugin is absent from the snapshot and Mitsuba cannot be built here (SURVEY.md F1/F2)"},
@@ -559,8 +559,19 @@ def main_ours(a):
                       "model": f"rays x ({b_trav:.1f} B traversal + 16 B hit cell + 12 B gradient atomics) + 12 B per pixel"}
     rs.pop("kernel_ms_")
     rs["step_model_gbs"] = step_bytes / (rs["ms_per_step"] * 1e-3) / 1e9
-    rs["step_model_frac"] = rs["step_model_gbs"] / peak
+    rs["step_model_frac"] = rs["step_model_gbs"] / (world * peak)       # aggregate bytes/s of the N ranks over N x one GPU's peak
     line["extras"]["render_step"] = rs
+    line["config"]["step_ms"] = {"fwd_bwd": ms_step, "full_step": ms_full, "render_step": rs.get("ms_per_step"),
+                                 "what": "fwd_bwd = the headline; full_step = zero_grad + intersect/SI + backward + collective + Adam + pyramid rebuild "
+                                         "on materialised rays; render_step = the fused inverse-rendering step (hf_render_step_l2 + collective + Adam + rebuild)"}
+    if world > 1:
+        check = {"grad_rel_l2_vs_single_rank": shard_check,
+                 "grad_rel_l2_vs_nccl_step": peer["grad_rel_l2_vs_nccl_step"] if peer is not None else None, "tolerance": 1e-4}
+        line["config"]["multi_gpu_check"] = check
+        line["nccl_step_value"] = nccl_step["mrays"]          # the literal "single ncclAllReduce" step, whichever step is the headline
+        bad = [k for k in ("grad_rel_l2_vs_single_rank", "grad_rel_l2_vs_nccl_step") if check[k] is not None and not (check[k] <= 1e-4)]
+    else:
+        bad = []
     if e2e is not None:
         line["e2e"] = e2e
     if world == 1 and not a.no_cpu:
@@ -572,6 +583,9 @@ def main_ours(a):
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
+    if bad:
+        print(f"bench.py: multi-GPU gradient check failed: {bad} above 1e-4 ({line['config']['multi_gpu_check']})", file=sys.stderr, flush=True)
+        sys.exit(3)
 
 
 def run_render_step(a, shape, h, params, opt, rank, world, dev, timed, ev, peer=False):
