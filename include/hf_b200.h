@@ -30,7 +30,7 @@
 extern "C" {
 #endif
 
-#define HF_B200_ABI_VERSION 3
+#define HF_B200_ABI_VERSION 4
 
 typedef enum {
     HF_OK = 0,
@@ -46,6 +46,7 @@ enum {
     HF_RAY_UV           = 0x2,
     HF_RAY_DPDUV        = 0x4,
     HF_RAY_SHADINGFRAME = 0x8,
+    HF_RAY_BOUNDARYTEST = 0x40,   /* fill hf_si.boundary_test (reparameterised integrators, src/python/python/ad/reparam.py) */
     HF_RAY_FOLLOWSHAPE  = 0x80,
     HF_RAY_DETACHSHAPE  = 0x100,
     HF_RAY_ALL          = 0x2 | 0x4 | 0x8
@@ -89,6 +90,10 @@ typedef struct {
     float *shs_x, *shs_y, *shs_z;
     float *sht_x, *sht_y, *sht_z;
     float *wi_x, *wi_y, *wi_z;
+    /* RayFlags::BoundaryTest (src/render/mesh.cpp:845-888, the branch of a mesh without vertex normals): 0 on an edge of the hit
+     * triangle, 1 at its barycentre; 1e8 where the ray misses (interaction.h:497-498); 0 when the flag is not set. Detached: the
+     * backward entry points have no adjoint for it, as in the reference. (ABI 4: the struct grew by this member.) */
+    float *boundary_test;
 } hf_si;
 
 /* Upstream adjoints of SurfaceInteraction3f fields; NULL = zero. sh_frame.n shares n. */

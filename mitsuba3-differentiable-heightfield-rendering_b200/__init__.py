@@ -77,7 +77,7 @@ class _Prelim(C.Structure):
 SI_FIELDS = ("t", "px", "py", "pz", "nx", "ny", "nz", "uvx", "uvy",
              "dpdu_x", "dpdu_y", "dpdu_z", "dpdv_x", "dpdv_y", "dpdv_z",
              "shn_x", "shn_y", "shn_z", "shs_x", "shs_y", "shs_z", "sht_x", "sht_y", "sht_z",
-             "wi_x", "wi_y", "wi_z")
+             "wi_x", "wi_y", "wi_z", "boundary_test")
 ADJ_FIELDS = SI_FIELDS[:15]
 
 
@@ -279,18 +279,20 @@ class PreliminaryIntersection3f:
 class SurfaceInteraction3f:
     """World-space record (interaction.h). `fields` selects which members are materialised; the kernels skip the
     rest (null pointers in hf_si). Default: everything RayFlags.All produces."""
-    ALL_FIELDS = ("t", "p", "n", "uv", "dp_du", "dp_dv", "sh_n", "sh_s", "sh_t", "wi")
+    ALL_FIELDS = ("t", "p", "n", "uv", "dp_du", "dp_dv", "sh_n", "sh_s", "sh_t", "wi", "boundary_test")
+    DEFAULT_FIELDS = ALL_FIELDS[:-1]          # boundary_test only on request (RayFlags.BoundaryTest)
     _ROWS = {"p": 3, "n": 3, "uv": 2, "dp_du": 3, "dp_dv": 3, "sh_n": 3, "sh_s": 3, "sh_t": 3, "wi": 3}
     _CNAMES = {"p": "p", "n": "n", "dp_du": "dpdu_", "dp_dv": "dpdv_", "sh_n": "shn_", "sh_s": "shs_", "sh_t": "sht_", "wi": "wi_"}
 
     def __init__(self, n, device, shape=None, fields=None):
-        fields = self.ALL_FIELDS if fields is None else tuple(fields)
+        fields = self.DEFAULT_FIELDS if fields is None else tuple(fields)
         unknown = set(fields) - set(self.ALL_FIELDS)
         if unknown:
             raise HeightfieldError(f"unknown surface interaction fields: {sorted(unknown)}")
         self.t = torch.empty(n, dtype=torch.float32, device=device) if "t" in fields else None
         for k, rows in self._ROWS.items():
             setattr(self, k, torch.empty((rows, n), dtype=torch.float32, device=device) if k in fields else None)
+        self.boundary_test = torch.empty(n, dtype=torch.float32, device=device) if "boundary_test" in fields else None
         self.prim_index = None
         self.shape = shape
 
@@ -298,7 +300,7 @@ class SurfaceInteraction3f:
         return self.t != float("inf")
 
     def _c(self):
-        f = {"t": self.t}
+        f = {"t": self.t, "boundary_test": self.boundary_test}
         for key, cname in self._CNAMES.items():
             t = getattr(self, key)
             for k, ax in enumerate("xyz"):

@@ -19,6 +19,18 @@
 #include "hf_kernels.h"
 #include "hf_qpyr.h"
 
+// NVTX ranges around the phases of a step (pyramid build, intersect, backward, collective, Adam, the host pipelines, the render
+// steps), the counterpart of the reference's ScopedPhase profiler (include/mitsuba/core/profiler.h:10-112): they name the host-side
+// spans of an nsys / ncu timeline of the 8-GPU step. NVTX 3 is header-only; without a tool attached a range costs one pointer test.
+#include <nvtx3/nvToolsExt.h>
+struct HfRange {
+    explicit HfRange(const char *name) { nvtxRangePushA(name); }
+    ~HfRange() { nvtxRangePop(); }
+    HfRange(const HfRange &) = delete;
+    HfRange &operator=(const HfRange &) = delete;
+};
+#define HF_RANGE() HfRange hf_range_(__func__)
+
 // ------------------------------------------------------------------------------------------
 // errors
 // ------------------------------------------------------------------------------------------
@@ -113,7 +125,7 @@ static int nccl_load() {
 #define PRE_NFIELDS 4
 #define SI_NFIELDS ((int) (sizeof(hf_si) / sizeof(float *)))
 #define ADJ_NFIELDS ((int) (sizeof(hf_si_adj) / sizeof(const float *)))
-static_assert(sizeof(hf_si) == 27 * sizeof(float *), "hf_si: 27 float* members (t, p3, n3, uv2, dpdu3, dpdv3, shn3, shs3, sht3, wi3)");
+static_assert(sizeof(hf_si) == 28 * sizeof(float *), "hf_si: 28 float* members (t, p3, n3, uv2, dpdu3, dpdv3, shn3, shs3, sht3, wi3, boundary_test)");
 static_assert(sizeof(hf_si_adj) == 15 * sizeof(const float *), "hf_si_adj: 15 members");
 static_assert(sizeof(hf_prelim) == PRE_NFIELDS * sizeof(void *), "hf_prelim: 4 members");
 #define SLAB_RAY 0
@@ -465,6 +477,7 @@ extern "C" int hf_destroy(hf_ctx *c) {
 // parameters
 // ------------------------------------------------------------------------------------------
 extern "C" int hf_set_heights(hf_ctx *c, const float *src, int src_on_device, void *stream) {
+    HF_RANGE();
     CHECK_CTX(c);
     if (!src) return fail(HF_ERR_INVALID, "null heights");
     CU(cudaSetDevice(c->device));
@@ -492,6 +505,7 @@ extern "C" int hf_grad(hf_ctx *c, float **d) {
 }
 
 extern "C" int hf_zero_grad(hf_ctx *c, void *stream) {
+    HF_RANGE();
     CHECK_CTX(c);
     CU(cudaSetDevice(c->device));
     CU(cudaMemsetAsync(c->d_grad, 0, (size_t) c->W * c->H * sizeof(float), (cudaStream_t) stream));
@@ -514,6 +528,7 @@ extern "C" int hf_set_max_height(hf_ctx *c, float mh) {
 }
 
 extern "C" int hf_parameters_changed(hf_ctx *c, void *stream) {
+    HF_RANGE();
     CHECK_CTX(c);
     if (!c->have_heights) return fail(HF_ERR_STATE, "heights were never set");
     CU(cudaSetDevice(c->device));
@@ -671,6 +686,7 @@ static int check_prelim(const hf_prelim *p) {
 }
 
 extern "C" int hf_ray_intersect_preliminary(hf_ctx *c, const hf_rays *rays, const hf_prelim *out, size_t n, void *stream) {
+    HF_RANGE();
     CHECK_CTX(c);
     if (n == 0) return HF_OK;      // empty batch: nothing to do, pointers may be null
     int rc;
@@ -708,6 +724,7 @@ extern "C" int hf_stats_get(hf_ctx *c, hf_stats *out, int reset) {
 }
 
 extern "C" int hf_ray_test(hf_ctx *c, const hf_rays *rays, uint8_t *d_hit, size_t n, void *stream) {
+    HF_RANGE();
     CHECK_CTX(c);
     if (n == 0) return HF_OK;      // empty batch: nothing to do, pointers may be null
     int rc;
@@ -730,6 +747,7 @@ static int check_flags(uint32_t flags) {
 
 extern "C" int hf_compute_surface_interaction(hf_ctx *c, const hf_rays *rays, const hf_prelim *pi, uint32_t flags,
                                               const hf_si *out, size_t n, void *stream) {
+    HF_RANGE();
     CHECK_CTX(c);
     if (n == 0) return HF_OK;      // empty batch: nothing to do, pointers may be null
     int rc;
@@ -743,6 +761,7 @@ extern "C" int hf_compute_surface_interaction(hf_ctx *c, const hf_rays *rays, co
 
 extern "C" int hf_ray_intersect(hf_ctx *c, const hf_rays *rays, uint32_t flags, const hf_prelim *prelim_out,
                                 const hf_si *out, size_t n, void *stream) {
+    HF_RANGE();
     CHECK_CTX(c);
     if (n == 0) return HF_OK;      // empty batch: nothing to do, pointers may be null
     int rc;
@@ -759,6 +778,7 @@ extern "C" int hf_ray_intersect(hf_ctx *c, const hf_rays *rays, uint32_t flags, 
 
 extern "C" int hf_backward(hf_ctx *c, const hf_rays *rays, const hf_prelim *pi, const hf_si_adj *adj, uint32_t flags,
                            size_t n, void *stream) {
+    HF_RANGE();
     CHECK_CTX(c);
     if (n == 0) return HF_OK;      // empty batch: nothing to do, pointers may be null
     int rc;
@@ -809,6 +829,7 @@ static int ensure_adam_table(hf_ctx *c, double b1, double b2, void *stream) {
 }
 
 extern "C" int hf_adam_step(hf_ctx *c, const hf_adam *cfg, void *stream) {
+    HF_RANGE();
     CHECK_CTX(c);
     if (!cfg) return fail(HF_ERR_INVALID, "null Adam configuration");
     // optimizers.py:243-244
@@ -896,6 +917,7 @@ extern "C" int hf_comm_destroy(hf_ctx *c) {
 }
 
 extern "C" int hf_allreduce_grad(hf_ctx *c, void *stream) {
+    HF_RANGE();
     CHECK_CTX(c);
     if (!c->comm) return fail(HF_ERR_STATE, "hf_comm_init was not called");
     CU(cudaSetDevice(c->device));
@@ -1055,6 +1077,7 @@ static inline void peer_slab(const hf_ctx *c, size_t &lo, size_t &hi) {
 }
 
 extern "C" int hf_peer_barrier(hf_ctx *c, void *stream) {
+    HF_RANGE();
     CHECK_CTX(c);
     NEED_PEERS(c);
     CU(cudaSetDevice(c->device));
@@ -1069,6 +1092,7 @@ static int peer_barrier(hf_ctx *c, cudaStream_t st) {
 }
 
 extern "C" int hf_peer_zero_grad(hf_ctx *c, void *stream) {
+    HF_RANGE();
     CHECK_CTX(c);
     NEED_PEERS(c);
     CU(cudaSetDevice(c->device));
@@ -1113,6 +1137,7 @@ static int peer_reduce(hf_ctx *c, const hf_adam *cfg, cudaStream_t st) {
 }
 
 extern "C" int hf_peer_reduce_grad(hf_ctx *c, void *stream) {
+    HF_RANGE();
     CHECK_CTX(c);
     NEED_PEERS(c);
     CU(cudaSetDevice(c->device));
@@ -1120,6 +1145,7 @@ extern "C" int hf_peer_reduce_grad(hf_ctx *c, void *stream) {
 }
 
 extern "C" int hf_peer_adam_step(hf_ctx *c, const hf_adam *cfg, void *stream) {
+    HF_RANGE();
     CHECK_CTX(c);
     NEED_PEERS(c);
     if (!cfg) return fail(HF_ERR_INVALID, "null Adam configuration");
@@ -1169,6 +1195,7 @@ static int check_pixels(const hf_camera *cam, const uint32_t *d_pixels, size_t n
 }
 
 extern "C" int hf_render_rays(hf_ctx *c, const hf_camera *cam, const uint32_t *d_pixels, size_t npix, const hf_rays *d_out, void *stream) {
+    HF_RANGE();
     CHECK_CTX(c);
     int rc;
     if ((rc = check_camera(cam, false)) || (rc = check_pixels(cam, d_pixels, npix))) return rc;
@@ -1181,6 +1208,7 @@ extern "C" int hf_render_rays(hf_ctx *c, const hf_camera *cam, const uint32_t *d
 
 extern "C" int hf_render_forward(hf_ctx *c, const hf_camera *cam, const hf_light *light, const uint32_t *d_pixels, size_t npix,
                                  float *d_image, uint32_t *d_prim, void *stream) {
+    HF_RANGE();
     CHECK_CTX(c);
     int rc;
     if ((rc = check_camera(cam, false)) || (rc = check_light(light)) || (rc = check_pixels(cam, d_pixels, npix))) return rc;
@@ -1196,6 +1224,7 @@ extern "C" int hf_render_forward(hf_ctx *c, const hf_camera *cam, const hf_light
 
 extern "C" int hf_render_backward(hf_ctx *c, const hf_camera *cam, const hf_light *light, const uint32_t *d_pixels, size_t npix,
                                   const float *d_adj_image, const uint32_t *d_prim, void *stream) {
+    HF_RANGE();
     CHECK_CTX(c);
     int rc;
     if ((rc = check_camera(cam, d_prim == nullptr)) || (rc = check_light(light)) || (rc = check_pixels(cam, d_pixels, npix))) return rc;
@@ -1217,6 +1246,7 @@ extern "C" int hf_render_backward(hf_ctx *c, const hf_camera *cam, const hf_ligh
 
 extern "C" int hf_render_step_l2(hf_ctx *c, const hf_camera *cam, const hf_light *light, const uint32_t *d_pixels, size_t npix,
                                  const float *d_target, float *d_image, double *d_loss, void *stream) {
+    HF_RANGE();
     CHECK_CTX(c);
     int rc;
     if ((rc = check_camera(cam, true)) || (rc = check_light(light)) || (rc = check_pixels(cam, d_pixels, npix))) return rc;
@@ -1374,6 +1404,7 @@ static int host_pipeline(hf_ctx *c, const hf_rays *hr, const hf_si_adj *hadj, ui
 extern "C" int hf_render_step_l2_host(hf_ctx *c, const hf_camera *cam, const hf_light *light, const uint32_t *h_pixels, size_t npix,
                                       const float *h_heights, const float *h_target, float *h_image_out, float *h_grad_out,
                                       double *h_loss_out) {
+    HF_RANGE();
     CHECK_CTX(c);
     int rc;
     if ((rc = check_camera(cam, true)) || (rc = check_light(light))) return rc;
@@ -1420,12 +1451,14 @@ extern "C" int hf_render_step_l2_host(hf_ctx *c, const hf_camera *cam, const hf_
 
 extern "C" int hf_ray_intersect_host(hf_ctx *c, const hf_rays *h_rays, uint32_t flags, const hf_prelim *h_prelim_out,
                                      const hf_si *h_out, size_t n) {
+    HF_RANGE();
     CHECK_CTX(c);
     return host_pipeline(c, h_rays, nullptr, flags, h_prelim_out, h_out, nullptr, n, false);
 }
 
 extern "C" int hf_forward_backward_host(hf_ctx *c, const hf_rays *h_rays, const hf_si_adj *h_adj, uint32_t flags,
                                         const hf_prelim *h_prelim_out, const hf_si *h_out, float *h_grad_out, size_t n) {
+    HF_RANGE();
     CHECK_CTX(c);
     return host_pipeline(c, h_rays, h_adj, flags, h_prelim_out, h_out, h_grad_out, n, true);
 }
@@ -1483,6 +1516,7 @@ static int static_scratch_for(int device, HfStaticDevice *out) {
 
 extern "C" int hf_ray_intersect_preliminary_static(const hf_desc *desc, const float *d_heights, const hf_rays *rays, const hf_prelim *out,
                                                    size_t n, void *stream) {
+    HF_RANGE();
     if (!desc) return fail(HF_ERR_INVALID, "null heightfield description");
     if (desc->width < 2 || desc->height < 2) return fail(HF_ERR_INVALID, "heightfield needs at least 2x2 texels (got %ux%u)", desc->width, desc->height);
     if (desc->width > (1u << 23) || desc->height > (1u << 23)) return fail(HF_ERR_INVALID, "heightfield side exceeds 2^23 texels");

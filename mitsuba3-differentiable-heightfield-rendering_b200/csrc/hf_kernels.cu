@@ -335,7 +335,7 @@ __device__ __forceinline__ bool traverse(const HfParams &P, const TopCache &C, f
 // ------------------------------------------------------------------------------------------
 #define STF(ptr, val) do { if (ptr) __stcs((ptr) + i, (val)); } while (0)
 
-__device__ __forceinline__ void write_si_invalid(const hf_si &S, size_t i, f3 dw) {
+__device__ __forceinline__ void write_si_invalid(const hf_si &S, size_t i, f3 dw, uint32_t flags) {
     STF(S.t, HF_INF);
     STF(S.px, 0.f); STF(S.py, 0.f); STF(S.pz, 0.f);
     STF(S.nx, 0.f); STF(S.ny, 0.f); STF(S.nz, 0.f);
@@ -346,6 +346,7 @@ __device__ __forceinline__ void write_si_invalid(const hf_si &S, size_t i, f3 dw
     STF(S.shs_x, 0.f); STF(S.shs_y, 0.f); STF(S.shs_z, 0.f);
     STF(S.sht_x, 0.f); STF(S.sht_y, 0.f); STF(S.sht_z, 0.f);
     STF(S.wi_x, -dw.x); STF(S.wi_y, -dw.y); STF(S.wi_z, -dw.z);
+    STF(S.boundary_test, (flags & HF_RAY_BOUNDARYTEST) ? 1e8f : 0.f);      // interaction.h:497-498
 }
 
 __device__ __forceinline__ void write_si(const HfParams &P, const hf_si &S, size_t i, uint32_t flags,
@@ -410,6 +411,35 @@ __device__ __forceinline__ void write_si(const HfParams &P, const hf_si &S, size
         STF(S.sht_x, st.x); STF(S.sht_y, st.y); STF(S.sht_z, st.z);
         STF(S.wi_x, dot3(md, ss)); STF(S.wi_y, dot3(md, st)); STF(S.wi_z, dot3(md, nw));
     }
+    if (S.boundary_test) {
+        // mesh.cpp:845-888, the branch of a mesh without vertex normals (the heightfield is flat-shaded): least-squares (u, v) of the
+        // hit point inside its triangle, mapped onto an equilateral triangle; distance to the nearest edge, scaled so that the
+        // barycentre is at 1. Evaluated on the object-space triangle (the solve is affine-invariant).
+        float bt = 0.f;
+        if (flags & HF_RAY_BOUNDARYTEST) {
+            const f3 rel = sub3(po, p0);
+            const float bb1 = dot3(dp0, rel), bb2 = dot3(dp1, rel), a11 = dot3(dp0, dp0), a12 = dot3(dp0, dp1), a22 = dot3(dp1, dp1);
+            const float inv_det = rcp_llvm(a11 * a22 - a12 * a12);
+            const float u = fmaf(a22, bb1, -(a12 * bb2)) * inv_det;      // fmsub
+            const float v = fmaf(-a12, bb1, a11 * bb2) * inv_det;        // fnmadd
+            const float hq = 0.5f * 1.7320508075688772f;                 // 0.5f * sqrt(3.f), both rounded to fp32
+            // p = tp0 * w + tp1 * u + tp2 * v, tp0 = (0, 0), tp1 = (1, 0), tp2 = (1/2, sqrt(3)/2): the products with the literals 0 and 1
+            // fold away in Dr.Jit's constant propagation (w drops out)
+            const float qx = u + 0.5f * v, qy = hq * v;
+            const float ex[3] = { 1.f, -0.5f, -0.5f }, ey[3] = { 0.f, hq, -hq };            // e0 = tp1 - tp0, e1 = tp2 - tp1, e2 = tp0 - tp2
+            const float vx[3] = { qx, qx - 1.f, qx - 0.5f }, vy[3] = { qy, qy, qy - hq };     // p - tp0, p - tp1, p - tp2
+            float d2 = HF_INF;
+#pragma unroll
+            for (int e = 0; e < 3; ++e) {
+                const float ve = fmaf(vy[e], ey[e], vx[e] * ex[e]), ee = fmaf(ey[e], ey[e], ex[e] * ex[e]);
+                const float c = fminf(fmaxf(__fdiv_rn(ve, ee), 0.f), 1.f);
+                const float px = vx[e] - ex[e] * c, py = vy[e] - ey[e] * c;
+                d2 = fminf(d2, fmaf(py, py, px * px));
+            }
+            bt = __fdiv_rn(__fsqrt_rn(d2), __fdiv_rn(1.7320508075688772f, 6.f));
+        }
+        STF(S.boundary_test, bt);
+    }
 }
 
 // The common request -- t, p, n, uv only (no dp_du / dp_dv, shading frame, wi, no FollowShape): same arithmetic as write_si for these
@@ -441,7 +471,7 @@ __device__ __forceinline__ void write_si_invalid_lean(const hf_si &S, size_t i) 
 static inline bool hf_si_is_lean(const hf_si &S, uint32_t flags) {
     return !(flags & HF_RAY_FOLLOWSHAPE) && !S.dpdu_x && !S.dpdu_y && !S.dpdu_z && !S.dpdv_x && !S.dpdv_y && !S.dpdv_z &&
            !S.shn_x && !S.shn_y && !S.shn_z && !S.shs_x && !S.shs_y && !S.shs_z && !S.sht_x && !S.sht_y && !S.sht_z &&
-           !S.wi_x && !S.wi_y && !S.wi_z;
+           !S.wi_x && !S.wi_y && !S.wi_z && !S.boundary_test;
 }
 
 // ------------------------------------------------------------------------------------------
@@ -521,7 +551,7 @@ hf_intersect_kernel(const __grid_constant__ HfParams P, const HfLaunchInfo li, c
                 else { p1 = mk3(x1, y1, h.z11); p2 = mk3(x0, y1, h.z01); }
                 write_si(P, S, i, flags, ow, dw, h.t, h.u, h.v, p0, p1, p2);
             } else {
-                write_si_invalid(S, i, dw);
+                write_si_invalid(S, i, dw, flags);
             }
         }
         if (MODE == HF_MODE_COUNTED) { acc_nodes += cn; acc_leaves += cl; acc_hits += hit ? 1 : 0; }
@@ -594,7 +624,7 @@ __device__ __forceinline__ void hf_store_result(const HfParams &P, const hf_rays
         } else {
             f3 dw2 = mk3(0.f, 0.f, 0.f);
             if (S.wi_x || S.wi_y || S.wi_z) dw2 = mk3(__ldcs(R.dx + i), __ldcs(R.dy + i), __ldcs(R.dz + i));
-            write_si_invalid(S, i, dw2);
+            write_si_invalid(S, i, dw2, flags);
         }
     }
 }
@@ -1208,7 +1238,7 @@ hf_si_kernel(const __grid_constant__ HfParams P, const hf_rays R, const hf_preli
         const f3 dw = mk3(__ldcs(R.dx + i), __ldcs(R.dy + i), __ldcs(R.dz + i));
         const float t = __ldcs(PI.t + i);
         const bool active = R.active ? (R.active[i] != 0) : true;
-        if (!active || t == HF_INF) { write_si_invalid(S, i, dw); continue; }
+        if (!active || t == HF_INF) { write_si_invalid(S, i, dw, flags); continue; }
         const float u = __ldcs(PI.u + i), v = __ldcs(PI.v + i);
         const uint32_t prim = __ldcs(PI.prim_index + i);
         f3 p0, p1, p2; uint32_t i0, i1, i2;

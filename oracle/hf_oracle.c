@@ -537,6 +537,7 @@ void hfo_surface_interaction(const hfo_shape *s, const hfo_rays *r, const hfo_pr
             ST(out->shs_x, 0.f); ST(out->shs_y, 0.f); ST(out->shs_z, 0.f);
             ST(out->sht_x, 0.f); ST(out->sht_y, 0.f); ST(out->sht_z, 0.f);
             ST(out->wi_x, -dw[0]); ST(out->wi_y, -dw[1]); ST(out->wi_z, -dw[2]);
+            ST(out->boundary_test, (flags & HFO_RF_BOUNDARYTEST) ? 1e8f : 0.f);   /* interaction.h:497-498 */
             continue;
         }
         int cx, cy, k, vi[3], vj[3];
@@ -616,6 +617,33 @@ void hfo_surface_interaction(const hfo_shape *s, const hfo_rays *r, const hfo_pr
         ST(out->shs_x, ss[0]); ST(out->shs_y, ss[1]); ST(out->shs_z, ss[2]);
         ST(out->sht_x, st[0]); ST(out->sht_y, st[1]); ST(out->sht_z, st[2]);
         ST(out->wi_x, wi[0]); ST(out->wi_y, wi[1]); ST(out->wi_z, wi[2]);
+
+        /* mesh.cpp:845-888, the branch of a mesh WITHOUT vertex normals (the heightfield is flat-shaded): least-squares (u, v) of
+           the hit point inside its triangle, mapped onto an equilateral triangle; distance to the nearest edge, scaled so that the
+           barycentre is at 1. Evaluated on the object-space triangle (the solve is affine-invariant). */
+        float bt = 0.f;
+        if (flags & HFO_RF_BOUNDARYTEST) {
+            float rel[3] = { po[0] - p0[0], po[1] - p0[1], po[2] - p0[2] };
+            float bb1 = dot3(dp0, rel), bb2 = dot3(dp1, rel), a11 = dot3(dp0, dp0), a12 = dot3(dp0, dp1), a22 = dot3(dp1, dp1);
+            float inv_det = rcp_llvm(a11 * a22 - a12 * a12);
+            float u = fmaf(a22, bb1, -(a12 * bb2)) * inv_det;       /* fmsub  */
+            float v = fmaf(-a12, bb1, a11 * bb2) * inv_det;         /* fnmadd */
+            const float hq = 0.5f * sqrtf(3.f);
+            /* p = tp0 * w + tp1 * u + tp2 * v with tp0 = (0, 0), tp1 = (1, 0), tp2 = (1/2, sqrt(3)/2): the products with the literals 0
+               and 1 fold away in Dr.Jit's constant propagation (w drops out) */
+            float qx = u + 0.5f * v, qy = hq * v;
+            const float ex[3] = { 1.f, -0.5f, -0.5f }, ey[3] = { 0.f, hq, -hq };             /* e0 = tp1 - tp0, e1 = tp2 - tp1, e2 = tp0 - tp2 */
+            const float vx[3] = { qx, qx - 1.f, qx - 0.5f }, vy[3] = { qy, qy, qy - hq };      /* p - tp0, p - tp1, p - tp2 */
+            float d2 = INFINITY;
+            for (int e = 0; e < 3; ++e) {
+                float ve = fmaf(vy[e], ey[e], vx[e] * ex[e]), ee = fmaf(ey[e], ey[e], ex[e] * ex[e]);
+                float c = fminf(fmaxf(ve / ee, 0.f), 1.f);
+                float px = vx[e] - ex[e] * c, py = vy[e] - ey[e] * c;
+                d2 = fminf(d2, fmaf(py, py, px * px));
+            }
+            bt = sqrtf(d2) / (sqrtf(3.f) / 6.f);
+        }
+        ST(out->boundary_test, bt);
     }
 }
 

@@ -33,6 +33,7 @@ enum {
     HFO_RF_UV            = 0x2,
     HFO_RF_DPDUV         = 0x4,
     HFO_RF_SHADINGFRAME  = 0x8,
+    HFO_RF_BOUNDARYTEST  = 0x40,
     HFO_RF_FOLLOWSHAPE   = 0x80,
     HFO_RF_DETACHSHAPE   = 0x100,
     HFO_RF_ALL           = 0x2 | 0x4 | 0x8
@@ -70,6 +71,7 @@ typedef struct {
     float *shs_x, *shs_y, *shs_z;
     float *sht_x, *sht_y, *sht_z;
     float *wi_x, *wi_y, *wi_z;
+    float *boundary_test;    /* RayFlags::BoundaryTest (mesh.cpp:845-900, interaction.h:497-498); 0 without the flag */
 } hfo_si;
 
 /* Upstream adjoints; any pointer may be NULL (treated as zero). */

@@ -20,6 +20,7 @@ _LIB_PATH = os.path.join(_HERE, "_build", "libhf_oracle.so")
 _REF_PATH = os.path.join(_HERE, "_ref", "libdrjit_ref.so")
 
 RF_MINIMAL, RF_UV, RF_DPDUV, RF_SHADINGFRAME = 0x1, 0x2, 0x4, 0x8
+RF_BOUNDARYTEST = 0x40
 RF_FOLLOWSHAPE, RF_DETACHSHAPE = 0x80, 0x100
 RF_ALL = RF_UV | RF_DPDUV | RF_SHADINGFRAME
 
@@ -45,7 +46,7 @@ class _Prelim(C.Structure):
 SI_FIELDS = ("t", "px", "py", "pz", "nx", "ny", "nz", "uvx", "uvy",
              "dpdu_x", "dpdu_y", "dpdu_z", "dpdv_x", "dpdv_y", "dpdv_z",
              "shn_x", "shn_y", "shn_z", "shs_x", "shs_y", "shs_z", "sht_x", "sht_y", "sht_z",
-             "wi_x", "wi_y", "wi_z")
+             "wi_x", "wi_y", "wi_z", "boundary_test")
 ADJ_FIELDS = ("t", "px", "py", "pz", "nx", "ny", "nz", "uvx", "uvy",
               "dpdu_x", "dpdu_y", "dpdu_z", "dpdv_x", "dpdv_y", "dpdv_z")
 

@@ -30,7 +30,7 @@ def test_every_declared_symbol_is_exported(lib):
     assert len(names) >= 30 and "hf_ray_intersect_preliminary" in names and "hf_backward" in names
     missing = [n for n in names if not hasattr(lib, n)]
     assert not missing, f"declared in include/hf_b200.h but not exported: {missing}"
-    assert lib.hf_abi_version() == 3
+    assert lib.hf_abi_version() == 4
 
 
 def test_python_mirror_binds_every_compute_symbol(lib):

@@ -57,6 +57,8 @@ SI_MAP = {"p": ("px", "py", "pz"), "n": ("nx", "ny", "nz"), "uv": ("uvx", "uvy")
 
 def _si_dict(si):
     out = {"t": _np(si.t)}
+    if getattr(si, "boundary_test", None) is not None:
+        out["boundary_test"] = _np(si.boundary_test)
     for k, names in SI_MAP.items():
         a = _np(getattr(si, k))
         for i, nm in enumerate(names):
@@ -262,15 +264,17 @@ def test_forward_bit_exact_vs_oracle(hf, oracle, H, W, kind, xf):
             tie = both & (np.abs(t - pb.t) <= 4 * np.spacing(np.abs(pb.t)))
         assert (diff & ~near & ~tie).sum() == 0
 
-    for flags in (oracle.RF_ALL, oracle.RF_UV, oracle.RF_ALL | oracle.RF_FOLLOWSHAPE):
+    every = hf.SurfaceInteraction3f.ALL_FIELDS          # all 28 members, boundary_test included (zero unless its flag is set)
+    for flags in (oracle.RF_ALL, oracle.RF_UV, oracle.RF_ALL | oracle.RF_FOLLOWSHAPE, oracle.RF_ALL | oracle.RF_BOUNDARYTEST):
         sc = c.compute_surface_interaction(cr, pc, ray_flags=flags)
-        sg = _si_dict(g.compute_surface_interaction(ray, pg, ray_flags=flags, active=act_t))
+        sg = _si_dict(g.compute_surface_interaction(ray, pg, ray_flags=flags, active=act_t, fields=every))
         for k in sc:
             ok = _same_bits(sg[k], sc[k])
             assert ok.all(), f"si.{k} differs in {(~ok).sum()} lanes (flags={flags:#x}); first {np.nonzero(~ok)[0][:5]}"
     # fused ray_intersect == preliminary + compute_surface_interaction
-    sf, pf = g.ray_intersect(ray, active=act_t, return_prelim=True)
-    sfd, s2 = _si_dict(sf), _si_dict(g.compute_surface_interaction(ray, pg, active=act_t))
+    bt = hf.RayFlags.All | hf.RayFlags.BoundaryTest
+    sf, pf = g.ray_intersect(ray, ray_flags=bt, active=act_t, return_prelim=True, fields=every)
+    sfd, s2 = _si_dict(sf), _si_dict(g.compute_surface_interaction(ray, pg, ray_flags=bt, active=act_t, fields=every))
     for k in s2:
         assert _same_bits(sfd[k], s2[k]).all(), k
     assert torch.equal(pf.t, pg.t) and torch.equal(pf.prim_index, pg.prim_index)
@@ -432,6 +436,38 @@ def test_adam_bias_correction_beyond_the_table(hf, oracle):
     assert np.allclose(_np(g.heights), p, rtol=0, atol=1e-6)
 
 
+def test_boundary_test_flag(hf, oracle):
+    """RayFlags::BoundaryTest (mesh.cpp:845-888 for a mesh without vertex normals; interaction.h:497-498): the reference's known
+    answers of src/render/tests/test_mesh.py:928-957 on the flat 2 x 2 field (the rectangle [-1, 1]^2 as two triangles), then the
+    GPU against the oracle bit for bit on a rough field under an affine transform, through the fused and the two-call path."""
+    BT = hf.RayFlags.BoundaryTest
+    flat, _ = _mk(hf, oracle, np.zeros((2, 2), f32))
+    o = np.array([[2, 0, 1], [0.9999, 0.9999, 1], [0.99999, 0.0, 1], [0.9, 0.0, 1], [-1 / 3, -1 / 3, 1]], f32)
+    d = np.tile(np.array([[0, 0, -1]], f32), (5, 1))
+    ray, _ = _rays(hf, oracle, o, d)
+    si = flat.ray_intersect(ray, ray_flags=BT, fields=("t", "boundary_test"))
+    b, t = _np(si.boundary_test), _np(si.t)
+    assert np.isinf(t[0]) and b[0] > 1e6               # test22: no intersection
+    assert b[1] < 1e-3 and b[2] < 1e-4 and b[3] > 1e-1 # test22: near a corner, near an edge, far from the silhouette
+    assert abs(b[4] - 1.0) < 1e-5                      # barycentre of the lower-left triangle
+    si0 = flat.ray_intersect(ray, fields=("t", "boundary_test"))
+    assert not _np(si0.boundary_test).any()            # flag not set: the field of a zero-initialised record
+
+    rng = np.random.default_rng(8)
+    h = random_heights(rng, 41, 57, "noise")
+    g, c = _mk(hf, oracle, h, 0.6, to_world=AFFINE)
+    o, d = random_rays(rng, 50000)
+    ray, cr = _rays(hf, oracle, o, d)
+    pc = c.ray_intersect_preliminary(cr)
+    want = c.compute_surface_interaction(cr, pc, ray_flags=0x2 | 0x4 | 0x8 | 0x40)["boundary_test"]
+    hit = pc.valid()
+    assert hit.sum() > 5000 and (want[~hit] == f32(1e8)).all() and (want[hit] >= 0).all() and (want[hit] <= 1.0001).all()
+    si, pi = g.ray_intersect(ray, ray_flags=hf.RayFlags.All | BT, return_prelim=True, fields=hf.SurfaceInteraction3f.ALL_FIELDS)
+    assert _same_bits(_np(si.boundary_test), want).all()
+    si2 = g.compute_surface_interaction(ray, pi, ray_flags=hf.RayFlags.All | BT, fields=("boundary_test",))
+    assert _same_bits(_np(si2.boundary_test), want).all()
+
+
 def test_error_behaviour(hf, oracle):
     with pytest.raises(hf.HeightfieldError):
         hf.load_dict({"type": "sphere"})
@@ -532,7 +568,7 @@ def test_host_api_waits_for_a_rebuild_on_a_side_stream(hf, oracle):
 
 
 def test_host_api_every_si_field_and_empty_batch(hf, oracle):
-    """hf_ray_intersect_host / hf_forward_backward_host with ALL 27 surface-interaction members requested (the staging slab is
+    """hf_ray_intersect_host / hf_forward_backward_host with ALL 28 surface-interaction members requested (the staging slab is
     derived from sizeof(hf_si): wi_z used to be left without a slot), compared bit for bit with the device API; then the n == 0 call
     that only reads the gradient grid back (null rays allowed)."""
     import hfb200
@@ -543,7 +579,8 @@ def test_host_api_every_si_field_and_empty_batch(hf, oracle):
     n = 70001
     o, d = wl.hemisphere_rays(n, seed=9)
     ray = hf.Ray3f(o, d)
-    si, pi = g.ray_intersect(ray, return_prelim=True)                  # every field
+    every = hf.RayFlags.All | hf.RayFlags.BoundaryTest
+    si, pi = g.ray_intersect(ray, ray_flags=every, return_prelim=True, fields=hf.SurfaceInteraction3f.ALL_FIELDS)     # every field
     want = _si_dict(si)
     pin = lambda x: x.contiguous().pin_memory()
     hr = {"ox": pin(o[0]), "oy": pin(o[1]), "oz": pin(o[2]), "dx": pin(d[0]), "dy": pin(d[1]), "dz": pin(d[2]),
@@ -552,8 +589,8 @@ def test_host_api_every_si_field_and_empty_batch(hf, oracle):
     hp = {"t": torch.empty(n).pin_memory(), "u": torch.empty(n).pin_memory(), "v": torch.empty(n).pin_memory(),
           "prim_index": torch.empty(n, dtype=torch.int32).pin_memory()}
     torch.cuda.synchronize()
-    g.ray_intersect_host(hr, hs, n, h_prelim=hp)
-    assert len(hfb200.SI_FIELDS) == 27
+    g.ray_intersect_host(hr, hs, n, ray_flags=every, h_prelim=hp)
+    assert len(hfb200.SI_FIELDS) == 28
     for k in hfb200.SI_FIELDS:
         assert not torch.isnan(hs[k]).any(), f"host API left {k} unwritten"
         assert _same_bits(hs[k].numpy(), want[k]).all(), k
@@ -570,7 +607,7 @@ def test_host_api_every_si_field_and_empty_batch(hf, oracle):
     hg = torch.empty(H, W).pin_memory()
     g.zero_grad()
     torch.cuda.synchronize()
-    g.forward_backward_host(hr, ha, hs, hg, n, h_prelim=hp)
+    g.forward_backward_host(hr, ha, hs, hg, n, ray_flags=every, h_prelim=hp)
     for k in hfb200.SI_FIELDS:
         assert _same_bits(hs[k].numpy(), want[k]).all(), k
     assert torch.allclose(hg, grad_dev, rtol=1e-4, atol=1e-5 * float(grad_dev.abs().max()))
